@@ -1,0 +1,233 @@
+"""ctypes bindings for the CPU checkers (TEST INFRASTRUCTURE ONLY).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this module.  The product package
+(dynolog_b200) never does.
+
+Two implementations of oracle/hbtref_api.h:
+  * ``load("reference")`` -> oracle/_ref/libhbtref.so: the real hbt code
+    (PerfEventsGroup::consume, CpuCountSampleGenerator, GroupReadValues,
+    getRateReducer/getAddReducer) compiled from /root/reference.
+  * ``load("port")`` -> oracle/libhbtoracle.so: plain-C restatement.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+MAX_EVENTS = 64
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("n_events", C.c_uint32),
+        ("n_buckets", C.c_uint32),
+        ("tsc_mask", C.c_uint64),
+        ("time_shift", C.c_uint32),
+        ("time_mult", C.c_uint32),
+        ("time_zero", C.c_uint64),
+        ("t0", C.c_uint64),
+        ("bucket_ns", C.c_uint64),
+    ]
+
+
+class Carry(C.Structure):
+    _fields_ = [
+        ("valid", C.c_uint64),
+        ("tstamp", C.c_uint64),
+        ("te", C.c_uint64),
+        ("tr", C.c_uint64),
+        ("last", C.c_uint64 * MAX_EVENTS),
+    ]
+
+
+class Counters(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in (
+        "lost", "comm", "exit", "throttle", "unthrottle", "fork", "sample", "read",
+        "aux", "itrace_start", "switch_cpu_wide", "num_records",
+        "num_unknown_count_interval", "num_rows", "rows_out_of_range")] + [
+        ("err", C.c_int64), ("err_offset", C.c_uint64), ("last_tstamp", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
+COUNTER_KEYS = [k for k, _ in Counters._fields_]
+
+
+def make_params(n_events, n_buckets=1, t0=0, bucket_ns=1, tsc_mask=0, time_shift=0,
+                time_mult=1, time_zero=0):
+    return Params(n_events, n_buckets, tsc_mask, time_shift, time_mult, time_zero, t0,
+                  bucket_ns)
+
+
+def make_carry(valid=False, tstamp=0, te=0, tr=0, last=()):
+    c = Carry()
+    c.valid = 1 if valid else 0
+    c.tstamp = tstamp
+    c.te = te
+    c.tr = tr
+    for i, v in enumerate(last):
+        c.last[i] = int(v)
+    return c
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t)) if a is not None else None
+
+
+def _u64(a):
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+class Oracle:
+    def __init__(self, path, prefix):
+        self.path = path
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+        f = lambda name: getattr(self.lib, prefix + "_" + name)
+        self._decode = f("decode_stream")
+        self._decode.restype = C.c_int
+        self._scale = f("scale_buckets")
+        self._get_count = f("get_count")
+        self._rate = f("rate")
+        self._add = f("add_reduce")
+        self._t2k = f("tsc_to_ktime")
+        self._k2t = f("ktime_to_tsc")
+        self._psm = f("per_second_mega")
+        self._rr = f("running_ratio")
+        self._run = f("run_capture")
+        self._run.restype = C.c_double
+        d = f("describe")
+        d.restype = C.c_char_p
+        self.description = d().decode()
+
+    # --- A1-A5, A7: stream walk ------------------------------------------------
+    def decode_stream(self, params, data, carry=None, want_records=True, want_rows=True,
+                      want_buckets=True):
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        n = params.n_events
+        carry = carry if carry is not None else make_carry()
+        out = Carry()
+        ctr = Counters()
+        cap = max(1, len(data) // 8)
+        rec_off = np.zeros(cap, np.uint64) if want_records else None
+        rec_type = np.zeros(cap, np.uint32) if want_records else None
+        rec_size = np.zeros(cap, np.uint32) if want_records else None
+        rows = np.zeros((cap, 2 + n), np.uint64) if want_rows else None
+        acc = np.zeros((params.n_buckets, n + 3), np.uint64) if want_buckets else None
+        self._decode(C.byref(params), C.byref(carry), C.byref(out),
+                     _p(data, C.c_uint8), C.c_uint64(len(data)), C.byref(ctr),
+                     _p(rec_off, C.c_uint64), _p(rec_type, C.c_uint32),
+                     _p(rec_size, C.c_uint32), C.c_uint64(cap if want_records else 0),
+                     _p(rows, C.c_uint64), C.c_uint64(cap if want_rows else 0),
+                     _p(acc, C.c_uint64))
+        res = {"counters": ctr.as_dict(), "carry_out": out}
+        if want_records:
+            k = ctr.num_records
+            res["records"] = (rec_off[:k].copy(), rec_type[:k].copy(), rec_size[:k].copy())
+        if want_rows:
+            res["rows"] = rows[:ctr.num_rows].copy()
+        if want_buckets:
+            res["buckets"] = acc
+        return res
+
+    def scale_buckets(self, params, acc):
+        acc = _u64(acc)
+        out = np.zeros((params.n_buckets, params.n_events), np.uint64)
+        self._scale(C.byref(params), _p(acc, C.c_uint64), _p(out, C.c_uint64))
+        return out
+
+    # --- A6, A8, A9, A10, A13: elementwise ------------------------------------------
+    def get_count(self, count, te, tr):
+        count, te, tr = _u64(count), _u64(te), _u64(tr)
+        out = np.zeros_like(count)
+        self._get_count(_p(count, C.c_uint64), _p(te, C.c_uint64), _p(tr, C.c_uint64),
+                        _p(out, C.c_uint64), C.c_uint64(count.size))
+        return out
+
+    def rate(self, num, den):
+        num, den = _u64(num), _u64(den)
+        out = np.zeros(num.shape, np.float64)
+        valid = np.zeros(num.shape, np.uint8)
+        self._rate(_p(num, C.c_uint64), _p(den, C.c_uint64), _p(out, C.c_double),
+                   _p(valid, C.c_uint8), C.c_uint64(num.size))
+        return out, valid.astype(bool)
+
+    def add_reduce(self, vals):
+        vals = _u64(vals)
+        n, k = vals.shape
+        out = np.zeros(n, np.float64)
+        self._add(_p(vals, C.c_uint64), C.c_uint64(k), _p(out, C.c_double), C.c_uint64(n))
+        return out
+
+    def tsc_to_ktime(self, params, tsc):
+        tsc = _u64(tsc)
+        out = np.zeros_like(tsc)
+        self._t2k(C.byref(params), _p(tsc, C.c_uint64), _p(out, C.c_uint64),
+                  C.c_uint64(tsc.size))
+        return out
+
+    def ktime_to_tsc(self, params, kt):
+        kt = _u64(kt)
+        out = np.zeros_like(kt)
+        self._k2t(C.byref(params), _p(kt, C.c_uint64), _p(out, C.c_uint64),
+                  C.c_uint64(kt.size))
+        return out
+
+    def per_second_mega(self, count, tr):
+        count, tr = _u64(count), _u64(tr)
+        out = np.zeros(count.shape, np.float32)
+        self._psm(_p(count, C.c_uint64), _p(tr, C.c_uint64), _p(out, C.c_float),
+                  C.c_uint64(count.size))
+        return out
+
+    def running_ratio(self, te, tr):
+        te, tr = _u64(te), _u64(tr)
+        ratio = np.zeros(te.shape, np.float32)
+        ri = np.zeros(te.shape, np.uint64)
+        mux = np.zeros(te.shape, np.uint8)
+        self._rr(_p(te, C.c_uint64), _p(tr, C.c_uint64), _p(ratio, C.c_float),
+                 _p(ri, C.c_uint64), _p(mux, C.c_uint8), C.c_uint64(te.size))
+        return ratio, ri, mux.astype(bool)
+
+    # --- timed whole-capture CPU path ----------------------------------------------
+    def run_capture(self, params, streams, carries=None, n_threads=1, batch=1024,
+                    want_buckets=True):
+        """streams: list of uint8 arrays (one per CPU). Returns (seconds, acc, counters)."""
+        ns = len(streams)
+        n = params.n_events
+        ptrs = (C.c_void_p * ns)(*[s.ctypes.data for s in streams])
+        lens = np.array([len(s) for s in streams], np.uint64)
+        cin = (Carry * ns)()
+        if carries is not None:
+            for i, c in enumerate(carries):
+                cin[i] = c
+        acc = np.zeros((ns, params.n_buckets, n + 3), np.uint64) if want_buckets else None
+        ctrs = (Counters * ns)()
+        secs = self._run(C.byref(params), C.c_uint32(ns), ptrs, _p(lens, C.c_uint64), cin,
+                         C.c_uint32(n_threads), C.c_uint32(batch), _p(acc, C.c_uint64), ctrs)
+        return secs, acc, [c.as_dict() for c in ctrs]
+
+
+_PATHS = {
+    "reference": (os.path.join(HERE, "_ref", "libhbtref.so"), "hbtref"),
+    "reference_nolog": (os.path.join(HERE, "_ref", "libhbtref_nolog.so"), "hbtref"),
+    "port": (os.path.join(HERE, "libhbtoracle.so"), "hbtoracle"),
+}
+_cache = {}
+
+
+def available(kind):
+    return os.path.exists(_PATHS[kind][0])
+
+
+def load(kind="port"):
+    if kind not in _cache:
+        path, prefix = _PATHS[kind]
+        if not os.path.exists(path):
+            raise FileNotFoundError(
+                f"{path} missing: run `make -C oracle` (or __graft_entry__.build())")
+        _cache[kind] = Oracle(path, prefix)
+    return _cache[kind]

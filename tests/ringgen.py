@@ -1,0 +1,130 @@
+"""Hand-built perf_event ring images for tests (pure Python/numpy, small sizes).
+
+Record layouts follow the kernel ABI as hbt overlays it
+(hbt/src/perf_event/PerfEventsGroup.h:241-298): every record starts with
+perf_event_header {u32 type; u16 misc; u16 size}, all fields little-endian u64
+after that; sizes are multiples of 8.
+"""
+import struct
+
+import numpy as np
+
+LOST, COMM, EXIT, THROTTLE, UNTHROTTLE, FORK, READ, SAMPLE = 2, 3, 4, 5, 6, 7, 8, 9
+AUX, ITRACE_START, SWITCH_CPU_WIDE = 11, 12, 15
+
+
+def header(rtype, size, misc=0):
+    return struct.pack("<IHH", rtype, misc, size)
+
+
+def header_u64(rtype, size, misc=0):
+    return rtype | (misc << 32) | (size << 48)
+
+
+def sample(tstamp, te, tr, values, nr=None, size=None):
+    """PERF_RECORD_SAMPLE for sample_type=TIME|READ, read_format=GROUP|TE|TR (:281-298)."""
+    n = len(values)
+    nr = n if nr is None else nr
+    size = 40 + 8 * n if size is None else size
+    m = (1 << 64) - 1
+    return header(SAMPLE, size) + struct.pack(
+        "<4Q", tstamp & m, nr, te & m, tr & m) + struct.pack(f"<{n}Q", *[v & m for v in values])
+
+
+def read_rec(pid, tid, te, tr, values, size=None):
+    """PERF_RECORD_READ (:267-278)."""
+    n = len(values)
+    size = 40 + 8 * n if size is None else size
+    return header(READ, size) + struct.pack("<IIQQQ", pid, tid, n, te, tr) + struct.pack(
+        f"<{n}Q", *values)
+
+
+def lost(num_lost, ident=7):
+    """PERF_RECORD_LOST, Sampling mode: {hdr, id, num_lost} = 24 B (:245-255)."""
+    return header(LOST, 24) + struct.pack("<QQ", ident, num_lost)
+
+
+def throttle(tstamp, ident=7, stream_id=9):
+    return header(THROTTLE, 32) + struct.pack("<QQQ", tstamp, ident, stream_id)
+
+
+def unthrottle(tstamp, ident=7, stream_id=9):
+    return header(UNTHROTTLE, 32) + struct.pack("<QQQ", tstamp, ident, stream_id)
+
+
+def other(rtype, payload_words):
+    """A record of any other type: header + payload u64 words."""
+    size = 8 + 8 * len(payload_words)
+    return header(rtype, size) + struct.pack(f"<{len(payload_words)}Q", *payload_words)
+
+
+def to_u8(b):
+    return np.frombuffer(bytes(b), dtype=np.uint8).copy()
+
+
+class SplitMix64:
+    def __init__(self, seed):
+        self.s = seed & ((1 << 64) - 1)
+
+    def next(self):
+        m = (1 << 64) - 1
+        self.s = (self.s + 0x9E3779B97F4A7C15) & m
+        z = self.s
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & m
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & m
+        return z ^ (z >> 31)
+
+    def uniform(self, lo, hi):
+        """integer in [lo, hi]"""
+        return lo + self.next() % (hi - lo + 1)
+
+
+def random_stream(seed, n_records, n_events, *, p_lost=0.0, p_throttle=0.0, p_other=0.0,
+                  p_read=0.0, mux=False, forge=0.0, t_start=1_000_000_000, dt=100_000,
+                  big_values=False):
+    """A plausible single-CPU Sampling-mode stream. Returns (bytes, info)."""
+    r = SplitMix64(seed)
+    out = bytearray()
+    ts = t_start
+    te = tr = 0
+    vals = [0] * n_events
+    if big_values:
+        vals = [(1 << 63) + r.next() % (1 << 62) for _ in range(n_events)]
+    f = 1.0
+    for i in range(n_records):
+        u = r.next() / 2.0**64
+        if u < p_lost:
+            out += lost(r.uniform(1, 64))
+            continue
+        u -= p_lost
+        if u < p_throttle:
+            out += throttle(ts) + unthrottle(ts + 10)
+            continue
+        u -= p_throttle
+        if u < p_other:
+            k = r.uniform(0, 6)
+            out += other(r.uniform(16, 40), [r.next() for _ in range(k)])
+            continue
+        u -= p_other
+        if u < p_read:
+            out += read_rec(1, 2, te, tr, vals)
+            continue
+        d = dt + r.uniform(0, dt // 10) - dt // 20
+        ts += d
+        if mux and i % 50 == 0:
+            f = [0.0, 0.25, 0.5, 0.75, 1.0][r.uniform(0, 4)]
+        te += d
+        tr += int(d * f)
+        for e in range(n_events):
+            vals[e] = (vals[e] + r.uniform(0, 300_000)) & ((1 << 64) - 1)
+        v = list(vals)
+        if forge > 0:
+            for e in range(n_events):
+                if r.next() / 2.0**64 < forge:
+                    # a counter value that is bit-identical to a valid header
+                    kind = r.uniform(0, 3)
+                    v[e] = [header_u64(SAMPLE, 40 + 8 * n_events), header_u64(LOST, 24),
+                            header_u64(THROTTLE, 32), header_u64(77, 8 * r.uniform(1, 20))][kind]
+                    vals[e] = v[e]
+        out += sample(ts, te, tr, v)
+    return to_u8(out), {"t_end": ts}
