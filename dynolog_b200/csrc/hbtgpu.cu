@@ -1,0 +1,864 @@
+// hbtgpu.cu -- host side of libhbtgpu.so (C ABI in include/hbtgpu.h).
+//
+// Owns the device arena, the chunk table and the launch sequence
+//   memset -> k_decode<spec> -> k_verify -> [k_resolve -> k_clear -> k_decode<exact>] -> k_derive
+// where the bracketed kernels return immediately unless the speculation was disproved.
+// No CPU fallback exists: every result is produced by the kernels in hbtgpu_kernels.cuh.
+#include "hbtgpu_kernels.cuh"
+
+#include <errno.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+using namespace hbtgpu;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct HostImage {
+  uint64_t base, len;  // arena offset, bytes
+  uint32_t stream;
+};
+
+}  // namespace
+
+struct hbtgpu_ctx {
+  hbtgpu_config cfg;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev_run0 = nullptr, ev_run1 = nullptr, ev_dec0 = nullptr, ev_dec1 = nullptr;
+  std::string err;
+
+  // device memory
+  uint8_t* arena = nullptr;
+  uint64_t arena_cap = 0, arena_used = 0;
+  hbtgpu_carry *d_carry_in = nullptr, *d_carry_out = nullptr;
+  hbtgpu_head_stub* d_head = nullptr;
+  uint64_t* d_counters = nullptr;
+  uint64_t* d_acc = nullptr;
+  uint64_t* d_scaled = nullptr;
+  double* d_metric = nullptr;
+  uint32_t* d_valid = nullptr;
+  uint32_t* d_flags = nullptr;
+  ChunkDesc* d_chunks = nullptr;
+  ChunkIO* d_io = nullptr;
+  ImageDesc* d_images = nullptr;
+  StreamDesc* d_streams = nullptr;
+  size_t cap_chunks = 0, cap_images = 0;
+  uint64_t *d_rows = nullptr, *d_rec_off = nullptr;
+  uint32_t *d_rec_type = nullptr, *d_rec_size = nullptr;
+  size_t cap_rows = 0, cap_recs = 0;
+  void* d_math = nullptr;
+  size_t cap_math = 0;
+  uint8_t* h_stage = nullptr;  // pinned staging for pageable submits
+  size_t cap_stage = 0;
+
+  // host bookkeeping
+  std::vector<hbtgpu_carry> carry_in;
+  std::vector<HostImage> images;  // submission order
+  bool table_dirty = true;
+  bool ran = false, emitted = false;
+  std::vector<ChunkDesc> chunks;
+  std::vector<ImageDesc> img_descs;
+  std::vector<StreamDesc> stream_descs;
+  std::vector<uint64_t> stream_row_base, stream_rec_base, stream_rows, stream_recs;
+  uint64_t chunk_bytes = 0;
+  uint64_t acc_words = 0, n_cells = 0;
+  hbtgpu_stats stats{};
+  std::vector<uint64_t> h_counters;
+  std::vector<hbtgpu_carry> h_carry_out;
+  bool counters_valid = false;
+  uint32_t h_flags[FLAG_COUNT] = {0};
+};
+
+namespace {
+
+int fail(hbtgpu_ctx* c, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (c) c->err = buf;
+  else g_create_error = buf;
+  return code;
+}
+
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return fail(ctx, -EIO, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                  __LINE__);                                                                  \
+  } while (0)
+
+template <class T>
+int ensure(hbtgpu_ctx* ctx, T** p, size_t* cap, size_t need) {
+  if (need <= *cap) return 0;
+  if (*p) CK(cudaFree(*p));
+  *p = nullptr;
+  size_t ncap = std::max(need, *cap * 2);
+  CK(cudaMalloc(reinterpret_cast<void**>(p), ncap * sizeof(T)));
+  *cap = ncap;
+  return 0;
+}
+
+constexpr uint64_t kImageAlign = 128;
+
+// Split every image into chunks; order = stream, then submission order, then position.
+int build_table(hbtgpu_ctx* ctx) {
+  const uint32_t ns = ctx->cfg.max_cpus;
+  ctx->chunks.clear();
+  ctx->img_descs.clear();
+  ctx->stream_descs.assign(ns, StreamDesc{0, 0});
+  uint64_t total = 0;
+  for (auto& im : ctx->images) total += im.len;
+  // enough chunks to fill 148 SMs several times over, but not smaller than one tile
+  uint64_t target = total / (148ull * 12ull);
+  uint64_t cb = TILE_BYTES;
+  while (cb < target && cb < (256ull << 10)) cb <<= 1;
+  ctx->chunk_bytes = cb;
+
+  std::vector<std::vector<uint32_t>> per_stream(ns);
+  for (uint32_t i = 0; i < ctx->images.size(); ++i) per_stream[ctx->images[i].stream].push_back(i);
+  for (uint32_t s = 0; s < ns; ++s) {
+    ctx->stream_descs[s].first_image = static_cast<uint32_t>(ctx->img_descs.size());
+    ctx->stream_descs[s].n_images = static_cast<uint32_t>(per_stream[s].size());
+    uint64_t spos = 0;
+    const HostImage* prev = nullptr;
+    const size_t first_chunk_of_stream = ctx->chunks.size();
+    for (uint32_t ii : per_stream[s]) {
+      const HostImage& im = ctx->images[ii];
+      ImageDesc id{im.base, im.len, spos, s, static_cast<uint32_t>(ctx->chunks.size()), 0, 0};
+      for (uint64_t b = 0; b < im.len; b += cb) {
+        ChunkDesc cd{};
+        cd.img_base = im.base;
+        cd.img_len = im.len;
+        cd.begin = b;
+        cd.end = std::min(im.len, b + cb);
+        cd.stream_pos = spos;
+        cd.stream = s;
+        cd.image = static_cast<uint32_t>(ctx->img_descs.size());
+        cd.flags = 0;
+        if (b == 0) cd.flags |= CH_FIRST_OF_IMAGE;
+        if (cd.end == im.len) cd.flags |= CH_LAST_OF_IMAGE;
+        if (b > 0) {
+          const uint64_t hb = b > HALO_BYTES ? b - HALO_BYTES : 0;
+          cd.halo_off = im.base + hb;
+          cd.halo_len = static_cast<uint32_t>(b - hb);
+          if (hb == 0) cd.flags |= CH_HALO_EXACT_START;
+        } else if (prev) {
+          uint64_t hb = prev->len > HALO_BYTES ? prev->len - HALO_BYTES : 0;
+          if (hb == 0) cd.flags |= CH_HALO_EXACT_START;
+          hb &= ~15ull;  // TMA source must be 16-byte aligned
+          cd.halo_off = prev->base + hb;
+          cd.halo_len = static_cast<uint32_t>(prev->len - hb);
+        } else {
+          cd.halo_len = 0;
+        }
+        ctx->chunks.push_back(cd);
+        ++id.n_chunks;
+      }
+      ctx->img_descs.push_back(id);
+      spos += im.len;
+      prev = &im;
+    }
+    if (ctx->chunks.size() > first_chunk_of_stream) {
+      ctx->chunks[first_chunk_of_stream].flags |= CH_FIRST_OF_STREAM;
+      ctx->chunks.back().flags |= CH_LAST_OF_STREAM;
+    }
+  }
+  const size_t nc = ctx->chunks.size(), ni = ctx->img_descs.size();
+  if (int r = ensure(ctx, &ctx->d_chunks, &ctx->cap_chunks, std::max<size_t>(nc, 1))) return r;
+  {
+    size_t cap_io = 0;
+    if (ctx->d_io) {
+      CK(cudaFree(ctx->d_io));
+      ctx->d_io = nullptr;
+    }
+    if (int r = ensure(ctx, &ctx->d_io, &cap_io, std::max<size_t>(nc, 1))) return r;
+  }
+  if (int r = ensure(ctx, &ctx->d_images, &ctx->cap_images, std::max<size_t>(ni, 1))) return r;
+  if (nc) CK(cudaMemcpyAsync(ctx->d_chunks, ctx->chunks.data(), nc * sizeof(ChunkDesc),
+                             cudaMemcpyHostToDevice, ctx->stream));
+  if (ni) CK(cudaMemcpyAsync(ctx->d_images, ctx->img_descs.data(), ni * sizeof(ImageDesc),
+                             cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(ctx->d_streams, ctx->stream_descs.data(), ns * sizeof(StreamDesc),
+                     cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_io, 0, std::max<size_t>(nc, 1) * sizeof(ChunkIO), ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));  // host vectors may be rebuilt after this
+  ctx->table_dirty = false;
+  ctx->stats.n_chunks = static_cast<uint32_t>(nc);
+  ctx->stats.image_bytes = total;
+  return 0;
+}
+
+Params make_params(hbtgpu_ctx* ctx) {
+  Params P{};
+  P.arena = ctx->arena;
+  P.chunks = ctx->d_chunks;
+  P.io = ctx->d_io;
+  P.images = ctx->d_images;
+  P.streams = ctx->d_streams;
+  P.carry_in = ctx->d_carry_in;
+  P.carry_out = ctx->d_carry_out;
+  P.head = ctx->d_head;
+  P.counters = ctx->d_counters;
+  P.acc = ctx->d_acc;
+  P.flags = ctx->d_flags;
+  P.rows = ctx->d_rows;
+  P.rec_off = ctx->d_rec_off;
+  P.rec_type = ctx->d_rec_type;
+  P.rec_size = ctx->d_rec_size;
+  P.t0 = ctx->cfg.t0;
+  P.bucket_ns = ctx->cfg.bucket_ns;
+  P.tsc_mask = ctx->cfg.tsc_mask;
+  P.time_zero = ctx->cfg.time_zero;
+  P.n_events = ctx->cfg.n_events;
+  P.n_buckets = ctx->cfg.n_buckets;
+  P.n_chunks = static_cast<uint32_t>(ctx->chunks.size());
+  P.n_streams = ctx->cfg.max_cpus;
+  P.time_shift = ctx->cfg.time_shift;
+  P.time_mult = ctx->cfg.time_mult;
+  P.force_general = (ctx->cfg.flags & HBTGPU_F_FORCE_GENERAL) ? 1 : 0;
+  P.external_carry = (ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY) ? 1 : 0;
+  return P;
+}
+
+int launch_derive(hbtgpu_ctx* ctx) {
+  DeriveParams D{};
+  D.acc = ctx->d_acc;
+  D.scaled = ctx->d_scaled;
+  D.metric = ctx->d_metric;
+  D.valid = ctx->d_valid;
+  D.n_cells = ctx->n_cells;
+  D.n_events = ctx->cfg.n_events;
+  D.n_metrics = ctx->cfg.n_metrics;
+  memcpy(D.metrics, ctx->cfg.metrics, sizeof(D.metrics));
+  const uint64_t blocks = (ctx->n_cells + 255) / 256;
+  k_derive<<<static_cast<unsigned>(blocks), 256, 0, ctx->stream>>>(D);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int fetch_counters(hbtgpu_ctx* ctx) {
+  if (ctx->counters_valid) return 0;
+  const size_t n = static_cast<size_t>(ctx->cfg.max_cpus) * C_SLOTS;
+  ctx->h_counters.resize(n);
+  CK(cudaMemcpyAsync(ctx->h_counters.data(), ctx->d_counters, n * 8, cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CK(cudaMemcpyAsync(ctx->h_flags, ctx->d_flags, sizeof(ctx->h_flags), cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  ctx->counters_valid = true;
+  ctx->stats.exact_runs = ctx->h_flags[FLAG_NEED_EXACT] ? 1 : 0;
+  ctx->stats.exact_reason = ctx->h_flags[FLAG_WHY];
+  ctx->stats.exact_chunk = ctx->h_flags[FLAG_WHERE];
+  // getLastTimeStamp() is the carried state: count_.tstamp or kInvalidTimeStamp
+  ctx->h_carry_out.resize(ctx->cfg.max_cpus);
+  CK(cudaMemcpyAsync(ctx->h_carry_out.data(), ctx->d_carry_out,
+                     ctx->cfg.max_cpus * sizeof(hbtgpu_carry), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (ctx->h_flags[FLAG_INTERNAL])
+    return fail(ctx, -EIO, "internal inconsistency: exact pass met an unresolved record (code %u)",
+                ctx->h_flags[FLAG_INTERNAL]);
+  return 0;
+}
+
+// Second pass that writes rows and the record table, using the (verified) chunk entries.
+int ensure_emitted(hbtgpu_ctx* ctx) {
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  if (ctx->emitted) return 0;
+  if (int r = fetch_counters(ctx)) return r;
+  const size_t nc = ctx->chunks.size();
+  const uint32_t ns = ctx->cfg.max_cpus;
+  ctx->stream_row_base.assign(ns, 0);
+  ctx->stream_rec_base.assign(ns, 0);
+  ctx->stream_rows.assign(ns, 0);
+  ctx->stream_recs.assign(ns, 0);
+  uint64_t rows = 0, recs = 0;
+  if (nc) {
+    std::vector<ChunkIO> io(nc);
+    CK(cudaMemcpyAsync(io.data(), ctx->d_io, nc * sizeof(ChunkIO), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    uint32_t cur = 0xFFFFFFFFu;
+    for (size_t c = 0; c < nc; ++c) {
+      const uint32_t s = ctx->chunks[c].stream;
+      if (s != cur) {
+        cur = s;
+        ctx->stream_row_base[s] = rows;
+        ctx->stream_rec_base[s] = recs;
+      }
+      io[c].row_base = rows;
+      io[c].rec_base = recs;
+      rows += io[c].n_rows;
+      recs += io[c].n_records;
+      ctx->stream_rows[s] += io[c].n_rows;
+      ctx->stream_recs[s] += io[c].n_records;
+    }
+    CK(cudaMemcpyAsync(ctx->d_io, io.data(), nc * sizeof(ChunkIO), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  const uint32_t n = ctx->cfg.n_events;
+  if (int r = ensure(ctx, &ctx->d_rows, &ctx->cap_rows, std::max<uint64_t>(rows, 1) * (n + 2))) return r;
+  {
+    size_t c0 = ctx->cap_recs, c1 = ctx->cap_recs, c2 = ctx->cap_recs;
+    if (int r = ensure(ctx, &ctx->d_rec_off, &c0, std::max<uint64_t>(recs, 1))) return r;
+    if (int r = ensure(ctx, &ctx->d_rec_type, &c1, std::max<uint64_t>(recs, 1))) return r;
+    if (int r = ensure(ctx, &ctx->d_rec_size, &c2, std::max<uint64_t>(recs, 1))) return r;
+    ctx->cap_recs = c0;
+  }
+  if (nc) {
+    Params P = make_params(ctx);
+    k_decode<false, MODE_EMIT><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  ctx->emitted = true;
+  return 0;
+}
+
+template <class K>
+int set_smem(hbtgpu_ctx* ctx, K kernel) {
+  CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          static_cast<int>(sizeof(Smem))));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* hbtgpu_version(void) { return "hbtgpu 0.1 (sm_100a)"; }
+
+const char* hbtgpu_last_error(const hbtgpu_ctx* ctx) {
+  return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
+  hbtgpu_ctx* ctx = nullptr;  // for CK/fail before the context exists
+  if (!cfg || !out) return fail(ctx, -EINVAL, "null argument");
+  *out = nullptr;
+  // HBT_ARG_CHECK-style argument validation (hbt/src/common/Defs.h:275-293 throws; the ABI returns)
+  if (cfg->n_events == 0 || cfg->n_events > HBTGPU_MAX_EVENTS)
+    return fail(ctx, -EINVAL, "n_events must be in [1,%d]", HBTGPU_MAX_EVENTS);
+  if (cfg->max_cpus == 0 || cfg->max_cpus > 4096) return fail(ctx, -EINVAL, "max_cpus out of range");
+  if (cfg->n_buckets == 0 || cfg->n_buckets >= 0xFFFFFFFEu) return fail(ctx, -EINVAL, "n_buckets out of range");
+  if (cfg->bucket_ns == 0) return fail(ctx, -EINVAL, "bucket_ns must be >= 1");
+  if (cfg->n_metrics > HBTGPU_MAX_METRICS) return fail(ctx, -EINVAL, "too many metrics");
+  if (cfg->time_shift > 63) return fail(ctx, -EINVAL, "time_shift must be < 64");
+  if (cfg->tsc_mask != 0 && cfg->time_mult == 0) return fail(ctx, -EINVAL, "time_mult must be != 0");
+  for (uint32_t m = 0; m < cfg->n_metrics; ++m) {
+    const hbtgpu_metric& md = cfg->metrics[m];
+    if (md.n_idx > HBTGPU_MAX_METRIC_EVENTS) return fail(ctx, -EINVAL, "metric %u: too many events", m);
+    if (md.kind == HBTGPU_METRIC_PER_SECOND_MEGA && md.n_idx != 1)
+      return fail(ctx, -EINVAL, "metric %u: PER_SECOND_MEGA takes one event", m);
+    for (uint32_t k = 0; k < md.n_idx; ++k)
+      if (md.idx[k] >= cfg->n_events) return fail(ctx, -EINVAL, "metric %u: event index out of range", m);
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(ctx, -ENODEV, "no CUDA device: libhbtgpu has no CPU fallback");
+  if (cfg->device < 0 || cfg->device >= ndev) return fail(ctx, -ENODEV, "device %d not present", cfg->device);
+
+  ctx = new hbtgpu_ctx();
+  ctx->cfg = *cfg;
+  ctx->device = cfg->device;
+  auto bail = [&](int code) {
+    g_create_error = ctx->err;
+    hbtgpu_destroy(ctx);
+    return code;
+  };
+#define CKC(call)                                                                         \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      fail(ctx, -EIO, "%s failed: %s", #call, cudaGetErrorString(e_));                    \
+      return bail(-EIO);                                                                  \
+    }                                                                                     \
+  } while (0)
+  CKC(cudaSetDevice(ctx->device));
+  CKC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CKC(cudaEventCreate(&ctx->ev_run0));
+  CKC(cudaEventCreate(&ctx->ev_run1));
+  CKC(cudaEventCreate(&ctx->ev_dec0));
+  CKC(cudaEventCreate(&ctx->ev_dec1));
+  const uint32_t ns = cfg->max_cpus, n = cfg->n_events;
+  ctx->n_cells = static_cast<uint64_t>(ns) * cfg->n_buckets;
+  ctx->acc_words = ctx->n_cells * (n + 3);
+  ctx->arena_cap = (cfg->arena_bytes + kImageAlign - 1) / kImageAlign * kImageAlign;
+  // slack: image padding plus the staged overlap / 16-byte rounding never leaves the allocation
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->arena), ctx->arena_cap + kImageAlign * ns + STAGE_BYTES));
+  CKC(cudaMemsetAsync(ctx->arena, 0, ctx->arena_cap + kImageAlign * ns + STAGE_BYTES, ctx->stream));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_carry_in), ns * sizeof(hbtgpu_carry)));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_carry_out), ns * sizeof(hbtgpu_carry)));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_head), ns * sizeof(hbtgpu_head_stub)));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_counters), ns * C_SLOTS * 8));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_acc), ctx->acc_words * 8));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_scaled), ctx->n_cells * n * 8));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_metric),
+                 std::max<uint64_t>(ctx->n_cells * cfg->n_metrics, 1) * 8));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_valid), ctx->n_cells * 4));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_flags), FLAG_COUNT * 4));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_streams), ns * sizeof(StreamDesc)));
+  CKC(cudaMemsetAsync(ctx->d_carry_in, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
+  CKC(cudaMemsetAsync(ctx->d_carry_out, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
+  CKC(cudaMemsetAsync(ctx->d_head, 0, ns * sizeof(hbtgpu_head_stub), ctx->stream));
+  CKC(cudaMemsetAsync(ctx->d_counters, 0, ns * C_SLOTS * 8, ctx->stream));
+  CKC(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
+  CKC(cudaMemsetAsync(ctx->d_flags, 0, FLAG_COUNT * 4, ctx->stream));
+  CKC(cudaStreamSynchronize(ctx->stream));
+  ctx->carry_in.assign(ns, hbtgpu_carry{});
+  if (set_smem(ctx, k_decode<true, MODE_AGG>) || set_smem(ctx, k_decode<false, MODE_AGG>) ||
+      set_smem(ctx, k_decode<false, MODE_EMIT>))
+    return bail(-EIO);
+#undef CKC
+  *out = ctx;
+  return 0;
+}
+
+void hbtgpu_destroy(hbtgpu_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  void* ptrs[] = {ctx->arena, ctx->d_carry_in, ctx->d_carry_out, ctx->d_head, ctx->d_counters,
+                  ctx->d_acc, ctx->d_scaled, ctx->d_metric, ctx->d_valid, ctx->d_flags,
+                  ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
+                  ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+  for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1, ctx->ev_dec0, ctx->ev_dec1})
+    if (e) cudaEventDestroy(e);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int hbtgpu_set_carry(hbtgpu_ctx* ctx, uint32_t cpu, const hbtgpu_carry* carry) {
+  if (!ctx || !carry) return -EINVAL;
+  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
+  CK(cudaSetDevice(ctx->device));
+  ctx->carry_in[cpu] = *carry;
+  CK(cudaMemcpyAsync(&ctx->d_carry_in[cpu], &ctx->carry_in[cpu], sizeof(hbtgpu_carry),
+                     cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+static int reserve_image(hbtgpu_ctx* ctx, uint32_t cpu, size_t n, uint64_t* base) {
+  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
+  if (n % 8) return fail(ctx, -EINVAL, "image size %zu is not a multiple of 8 (records are u64-aligned)", n);
+  const uint64_t b = (ctx->arena_used + kImageAlign - 1) / kImageAlign * kImageAlign;
+  if (b + n > ctx->arena_cap + kImageAlign * ctx->cfg.max_cpus)
+    return fail(ctx, -ENOSPC, "arena full: %llu + %zu > %llu bytes",
+                (unsigned long long)b, n, (unsigned long long)ctx->arena_cap);
+  *base = b;
+  return 0;
+}
+
+int hbtgpu_submit_image(hbtgpu_ctx* ctx, uint32_t cpu, const void* first, size_t n1,
+                        const void* second, size_t n2) {
+  if (!ctx) return -EINVAL;
+  if ((n1 && !first) || (n2 && !second)) return fail(ctx, -EINVAL, "null slice");
+  const size_t n = n1 + n2;
+  if (n == 0) return 0;
+  CK(cudaSetDevice(ctx->device));
+  uint64_t base;
+  if (int r = reserve_image(ctx, cpu, n, &base)) return r;
+  if (n1) CK(cudaMemcpyAsync(ctx->arena + base, first, n1, cudaMemcpyHostToDevice, ctx->stream));
+  if (n2) CK(cudaMemcpyAsync(ctx->arena + base + n1, second, n2, cudaMemcpyHostToDevice, ctx->stream));
+  // "copied before the call returns" holds for pageable memory (staged by the driver); for
+  // pinned memory the copy is asynchronous, so wait: the ring may be overwritten right after.
+  cudaPointerAttributes at{};
+  bool pinned = cudaPointerGetAttributes(&at, first ? first : second) == cudaSuccess &&
+                at.type == cudaMemoryTypeHost;
+  (void)cudaGetLastError();
+  if (pinned) CK(cudaStreamSynchronize(ctx->stream));
+  ctx->images.push_back(HostImage{base, n, cpu});
+  ctx->arena_used = base + n;
+  ctx->table_dirty = true;
+  return 0;
+}
+
+int hbtgpu_submit_image_device(hbtgpu_ctx* ctx, uint32_t cpu, const void* device_ptr, size_t n) {
+  if (!ctx) return -EINVAL;
+  if (n == 0) return 0;
+  if (!device_ptr) return fail(ctx, -EINVAL, "null image");
+  CK(cudaSetDevice(ctx->device));
+  uint64_t base;
+  if (int r = reserve_image(ctx, cpu, n, &base)) return r;
+  CK(cudaMemcpyAsync(ctx->arena + base, device_ptr, n, cudaMemcpyDeviceToDevice, ctx->stream));
+  ctx->images.push_back(HostImage{base, n, cpu});
+  ctx->arena_used = base + n;
+  ctx->table_dirty = true;
+  return 0;
+}
+
+int hbtgpu_reset(hbtgpu_ctx* ctx, int keep_carry) {
+  if (!ctx) return -EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  const uint32_t ns = ctx->cfg.max_cpus;
+  if (keep_carry && ctx->ran) {
+    CK(cudaMemcpyAsync(ctx->carry_in.data(), ctx->d_carry_out, ns * sizeof(hbtgpu_carry),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpyAsync(ctx->d_carry_in, ctx->carry_in.data(), ns * sizeof(hbtgpu_carry),
+                       cudaMemcpyHostToDevice, ctx->stream));
+  }
+  ctx->images.clear();
+  ctx->arena_used = 0;
+  ctx->table_dirty = true;
+  ctx->ran = false;
+  ctx->emitted = false;
+  ctx->counters_valid = false;
+  CK(cudaMemsetAsync(ctx->d_counters, 0, ns * C_SLOTS * 8, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int hbtgpu_run(hbtgpu_ctx* ctx) {
+  if (!ctx) return -EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  if (ctx->table_dirty)
+    if (int r = build_table(ctx)) return r;
+  const uint32_t ns = ctx->cfg.max_cpus;
+  const size_t nc = ctx->chunks.size();
+  const bool force_exact = (ctx->cfg.flags & HBTGPU_F_FORCE_EXACT) != 0;
+  uint32_t launches = 0;
+  Params P = make_params(ctx);
+
+  CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_counters, 0, ns * C_SLOTS * 8, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_flags, force_exact ? 1 : 0, 1, ctx->stream));  // byte 0 of NEED_EXACT
+  CK(cudaMemsetAsync(reinterpret_cast<uint8_t*>(ctx->d_flags) + 1, 0, FLAG_COUNT * 4 - 1, ctx->stream));
+  // streams without images keep their carry: carry_out := carry_in
+  CK(cudaMemcpyAsync(ctx->d_carry_out, ctx->d_carry_in, ns * sizeof(hbtgpu_carry),
+                     cudaMemcpyDeviceToDevice, ctx->stream));
+  if (nc) {
+    CK(cudaEventRecord(ctx->ev_dec0, ctx->stream));
+    if (!force_exact) {
+      k_decode<true, MODE_AGG><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
+      ++launches;
+    }
+    CK(cudaEventRecord(ctx->ev_dec1, ctx->stream));
+    if (!force_exact) {
+      k_verify<<<static_cast<unsigned>((nc + 255) / 256), 256, 0, ctx->stream>>>(P);
+      ++launches;
+    }
+    k_resolve<<<(ns + RES_WARPS - 1) / RES_WARPS, RES_WARPS * 32, 0, ctx->stream>>>(P);
+    k_clear<<<148 * 4, 256, 0, ctx->stream>>>(P, force_exact ? 0 : ctx->acc_words);
+    k_decode<false, MODE_AGG><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
+    launches += 3;
+    CK(cudaGetLastError());
+  } else {
+    CK(cudaEventRecord(ctx->ev_dec0, ctx->stream));
+    CK(cudaEventRecord(ctx->ev_dec1, ctx->stream));
+  }
+  if (int r = launch_derive(ctx)) return r;
+  ++launches;
+  CK(cudaEventRecord(ctx->ev_run1, ctx->stream));
+  ctx->stats.kernel_launches = launches;
+  ctx->ran = true;
+  ctx->emitted = false;
+  ctx->counters_valid = false;
+  return 0;
+}
+
+int hbtgpu_sync(hbtgpu_ctx* ctx) {
+  if (!ctx) return -EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (ctx->ran) {
+    CK(cudaEventElapsedTime(&ctx->stats.last_run_ms, ctx->ev_run0, ctx->ev_run1));
+    CK(cudaEventElapsedTime(&ctx->stats.last_decode_ms, ctx->ev_dec0, ctx->ev_dec1));
+  }
+  return 0;
+}
+
+int hbtgpu_derive(hbtgpu_ctx* ctx) {
+  if (!ctx) return -EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  return launch_derive(ctx);
+}
+
+int hbtgpu_get_counters(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_counters* out) {
+  if (!ctx || !out) return -EINVAL;
+  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  CK(cudaSetDevice(ctx->device));
+  if (int r = fetch_counters(ctx)) return r;
+  const uint64_t* c = &ctx->h_counters[static_cast<size_t>(cpu) * C_SLOTS];
+  memset(out, 0, sizeof(*out));
+  out->lost = c[C_LOST];
+  out->throttle = c[C_THROTTLE];
+  out->unthrottle = c[C_UNTHROTTLE];
+  out->sample = c[C_SAMPLE];
+  out->read = c[C_READ];
+  // comm/exit/fork/aux/itrace_start/switch_cpu_wide stay 0: Sampling mode has void record
+  // types for them (PerfEventsGroup.h:241-308), consume() only skips them by size
+  out->num_records = c[C_RECORDS];
+  out->num_unknown_count_interval = c[C_UNKNOWN];
+  out->num_rows = c[C_ROWS];
+  out->rows_out_of_range = c[C_OOR];
+  out->err = c[C_ERR] ? -EPERM : 0;
+  // data_tail after the walk: the stalled record on error, else the whole stream
+  uint64_t stream_len = 0;
+  for (const HostImage& im : ctx->images)
+    if (im.stream == cpu) stream_len += im.len;
+  out->err_offset = c[C_ERR] ? c[C_ERR_OFF] : stream_len;
+  out->last_tstamp = ctx->h_carry_out[cpu].valid ? ctx->h_carry_out[cpu].tstamp : ~0ull;
+  return 0;
+}
+
+int hbtgpu_get_carry(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_carry* out) {
+  if (!ctx || !out) return -EINVAL;
+  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaMemcpyAsync(out, &ctx->d_carry_out[cpu], sizeof(hbtgpu_carry), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int hbtgpu_get_rows(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* rows, size_t cap_rows, size_t* n_rows) {
+  if (!ctx || !n_rows) return -EINVAL;
+  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
+  CK(cudaSetDevice(ctx->device));
+  if (int r = ensure_emitted(ctx)) return r;
+  const uint64_t have = ctx->stream_rows[cpu];
+  *n_rows = have;
+  const uint64_t k = std::min<uint64_t>(have, cap_rows);
+  if (k && rows) {
+    const uint32_t w = ctx->cfg.n_events + 2;
+    CK(cudaMemcpyAsync(rows, ctx->d_rows + ctx->stream_row_base[cpu] * w, k * w * 8,
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  return 0;
+}
+
+int hbtgpu_get_records(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* off, uint32_t* type, uint32_t* size,
+                       size_t cap, size_t* n_records) {
+  if (!ctx || !n_records) return -EINVAL;
+  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
+  CK(cudaSetDevice(ctx->device));
+  if (int r = ensure_emitted(ctx)) return r;
+  const uint64_t have = ctx->stream_recs[cpu];
+  *n_records = have;
+  const uint64_t k = std::min<uint64_t>(have, cap);
+  const uint64_t b = ctx->stream_rec_base[cpu];
+  if (k) {
+    if (off) CK(cudaMemcpyAsync(off, ctx->d_rec_off + b, k * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (type) CK(cudaMemcpyAsync(type, ctx->d_rec_type + b, k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (size) CK(cudaMemcpyAsync(size, ctx->d_rec_size + b, k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  return 0;
+}
+
+int hbtgpu_get_buckets_device(hbtgpu_ctx* ctx, hbtgpu_bucket_view* v) {
+  if (!ctx || !v) return -EINVAL;
+  v->acc = ctx->d_acc;
+  v->scaled = ctx->d_scaled;
+  v->metric = ctx->d_metric;
+  v->valid = ctx->d_valid;
+  v->max_cpus = ctx->cfg.max_cpus;
+  v->n_buckets = ctx->cfg.n_buckets;
+  v->n_events = ctx->cfg.n_events;
+  v->n_metrics = ctx->cfg.n_metrics;
+  return 0;
+}
+
+int hbtgpu_get_buckets_host(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scaled, double* metric,
+                            uint32_t* valid) {
+  if (!ctx) return -EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  const uint32_t n = ctx->cfg.n_events;
+  if (acc) CK(cudaMemcpyAsync(acc, ctx->d_acc, ctx->acc_words * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (scaled) CK(cudaMemcpyAsync(scaled, ctx->d_scaled, ctx->n_cells * n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (metric && ctx->cfg.n_metrics)
+    CK(cudaMemcpyAsync(metric, ctx->d_metric, ctx->n_cells * ctx->cfg.n_metrics * 8,
+                       cudaMemcpyDeviceToHost, ctx->stream));
+  if (valid) CK(cudaMemcpyAsync(valid, ctx->d_valid, ctx->n_cells * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int hbtgpu_get_head_stub(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_head_stub* out) {
+  if (!ctx || !out) return -EINVAL;
+  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
+  return fail(ctx, -ENOSYS, "head stubs: not built yet");
+}
+
+int hbtgpu_apply_boundary(hbtgpu_ctx* ctx, uint32_t cpu, const hbtgpu_carry* prev_tail) {
+  if (!ctx || !prev_tail) return -EINVAL;
+  (void)cpu;
+  return fail(ctx, -ENOSYS, "boundary rows: not built yet");
+}
+
+int hbtgpu_acc_device(hbtgpu_ctx* ctx, void** device_ptr, size_t* bytes) {
+  if (!ctx || !device_ptr || !bytes) return -EINVAL;
+  *device_ptr = ctx->d_acc;
+  *bytes = ctx->acc_words * 8;
+  return 0;
+}
+
+void* hbtgpu_stream(hbtgpu_ctx* ctx) { return ctx ? ctx->stream : nullptr; }
+
+int hbtgpu_get_stats(hbtgpu_ctx* ctx, hbtgpu_stats* out) {
+  if (!ctx || !out) return -EINVAL;
+  *out = ctx->stats;
+  return 0;
+}
+
+}  // extern "C"
+
+// ---- elementwise arithmetic ---------------------------------------------------------
+
+namespace {
+struct MathBuf {
+  hbtgpu_ctx* ctx;
+  uint8_t* base;
+  size_t off = 0;
+  template <class T>
+  T* take(size_t n) {
+    T* p = reinterpret_cast<T*>(base + off);
+    off += (n * sizeof(T) + 255) / 256 * 256;
+    return p;
+  }
+};
+int math_reserve(hbtgpu_ctx* ctx, size_t bytes, MathBuf* mb) {
+  CK(cudaSetDevice(ctx->device));
+  uint8_t* p = static_cast<uint8_t*>(ctx->d_math);
+  if (int r = ensure(ctx, &p, &ctx->cap_math, bytes)) {
+    ctx->d_math = p;
+    return r;
+  }
+  ctx->d_math = p;
+  mb->ctx = ctx;
+  mb->base = p;
+  return 0;
+}
+inline size_t pad256(size_t b) { return (b + 255) / 256 * 256; }
+inline unsigned nblk(size_t n) { return static_cast<unsigned>((n + 255) / 256); }
+}  // namespace
+
+extern "C" {
+
+#define H2D(dst, src, bytes) CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream))
+#define D2H(dst, src, bytes) CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream))
+
+int hbtgpu_math_get_count(hbtgpu_ctx* ctx, const uint64_t* count, const uint64_t* te,
+                          const uint64_t* tr, uint64_t* out, size_t n) {
+  if (!ctx) return -EINVAL;
+  if (n == 0) return 0;
+  MathBuf mb;
+  if (int r = math_reserve(ctx, 4 * pad256(n * 8), &mb)) return r;
+  uint64_t *dc = mb.take<uint64_t>(n), *de = mb.take<uint64_t>(n), *dr = mb.take<uint64_t>(n),
+           *dout = mb.take<uint64_t>(n);
+  H2D(dc, count, n * 8);
+  H2D(de, te, n * 8);
+  H2D(dr, tr, n * 8);
+  k_get_count<<<nblk(n), 256, 0, ctx->stream>>>(dc, de, dr, dout, n);
+  D2H(out, dout, n * 8);
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int hbtgpu_math_rate(hbtgpu_ctx* ctx, const uint64_t* num, const uint64_t* den, double* out,
+                     uint8_t* valid, size_t n) {
+  if (!ctx) return -EINVAL;
+  if (n == 0) return 0;
+  MathBuf mb;
+  if (int r = math_reserve(ctx, 3 * pad256(n * 8) + pad256(n), &mb)) return r;
+  uint64_t *dn = mb.take<uint64_t>(n), *dd = mb.take<uint64_t>(n);
+  double* dout = mb.take<double>(n);
+  uint8_t* dv = mb.take<uint8_t>(n);
+  H2D(dn, num, n * 8);
+  H2D(dd, den, n * 8);
+  k_rate<<<nblk(n), 256, 0, ctx->stream>>>(dn, dd, dout, dv, n);
+  D2H(out, dout, n * 8);
+  D2H(valid, dv, n);
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int hbtgpu_math_add_reduce(hbtgpu_ctx* ctx, const uint64_t* vals, size_t k, double* out, size_t n) {
+  if (!ctx) return -EINVAL;
+  if (n == 0) return 0;
+  MathBuf mb;
+  if (int r = math_reserve(ctx, pad256(n * k * 8) + pad256(n * 8), &mb)) return r;
+  uint64_t* dv = mb.take<uint64_t>(n * k);
+  double* dout = mb.take<double>(n);
+  H2D(dv, vals, n * k * 8);
+  k_add_reduce<<<nblk(n), 256, 0, ctx->stream>>>(dv, k, dout, n);
+  D2H(out, dout, n * 8);
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+static int math_tsc(hbtgpu_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n, int inverse) {
+  if (!ctx) return -EINVAL;
+  if (n == 0) return 0;
+  if (inverse && ctx->cfg.time_mult == 0) return fail(ctx, -EINVAL, "time_mult must be != 0");
+  MathBuf mb;
+  if (int r = math_reserve(ctx, 2 * pad256(n * 8), &mb)) return r;
+  uint64_t *di = mb.take<uint64_t>(n), *dout = mb.take<uint64_t>(n);
+  H2D(di, in, n * 8);
+  k_tsc<<<nblk(n), 256, 0, ctx->stream>>>(di, dout, n, ctx->cfg.time_shift, ctx->cfg.time_mult,
+                                          ctx->cfg.time_zero, inverse);
+  D2H(out, dout, n * 8);
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+int hbtgpu_math_tsc_to_ktime(hbtgpu_ctx* ctx, const uint64_t* tsc, uint64_t* out, size_t n) {
+  return math_tsc(ctx, tsc, out, n, 0);
+}
+int hbtgpu_math_ktime_to_tsc(hbtgpu_ctx* ctx, const uint64_t* kt, uint64_t* out, size_t n) {
+  return math_tsc(ctx, kt, out, n, 1);
+}
+
+int hbtgpu_math_per_second_mega(hbtgpu_ctx* ctx, const uint64_t* count, const uint64_t* tr,
+                                float* out, size_t n) {
+  if (!ctx) return -EINVAL;
+  if (n == 0) return 0;
+  MathBuf mb;
+  if (int r = math_reserve(ctx, 2 * pad256(n * 8) + pad256(n * 4), &mb)) return r;
+  uint64_t *dc = mb.take<uint64_t>(n), *dr = mb.take<uint64_t>(n);
+  float* dout = mb.take<float>(n);
+  H2D(dc, count, n * 8);
+  H2D(dr, tr, n * 8);
+  k_per_second_mega<<<nblk(n), 256, 0, ctx->stream>>>(dc, dr, dout, n);
+  D2H(out, dout, n * 4);
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int hbtgpu_math_running_ratio(hbtgpu_ctx* ctx, const uint64_t* te, const uint64_t* tr, float* ratio,
+                              uint64_t* ratio_int100, uint8_t* has_mux, size_t n) {
+  if (!ctx) return -EINVAL;
+  if (n == 0) return 0;
+  MathBuf mb;
+  if (int r = math_reserve(ctx, 3 * pad256(n * 8) + pad256(n * 4) + pad256(n), &mb)) return r;
+  uint64_t *de = mb.take<uint64_t>(n), *dr = mb.take<uint64_t>(n), *dri = mb.take<uint64_t>(n);
+  float* drat = mb.take<float>(n);
+  uint8_t* dm = mb.take<uint8_t>(n);
+  H2D(de, te, n * 8);
+  H2D(dr, tr, n * 8);
+  k_running_ratio<<<nblk(n), 256, 0, ctx->stream>>>(de, dr, drat, dri, dm, n);
+  D2H(ratio, drat, n * 4);
+  D2H(ratio_int100, dri, n * 8);
+  D2H(has_mux, dm, n);
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,1228 @@
+// hbtgpu_kernels.cuh -- sm_100a device code for the hbt perf_event ring decode +
+// aggregate path.  See DESIGN.md for the algorithm; reference semantics:
+//   record walk      hbt/src/perf_event/PerfEventsGroup.h:1394-1589 (consume)
+//   sample handling  hbt/src/perf_event/PerCpuCountSampleGenerator.h:110-202
+//   scaling/reducers hbt/src/perf_event/PerfEventsGroup.h:467-481,
+//                    hbt/src/perf_event/BuiltinMetrics.cpp:88-118
+//
+// Kernel inventory
+//   k_decode<SPEC,MODE>  one CTA per chunk of one image; tiles of 16 KiB are staged
+//                        into shared memory with TMA bulk copies (double buffered);
+//                        every 8-byte word is speculatively parsed as a record
+//                        header; the true chain is recovered inside the tile
+//                        (contiguity shortcut, else pointer jumping); samples are
+//                        linked to their predecessor with a block scan and the
+//                        per-(cpu,bucket) sums are formed as a telescoped segmented
+//                        reduction (one RED.64 set per bucket boundary, not per row).
+//                        SPEC=true: the chunk's entry point and predecessor sample
+//                        are speculated from a 2 KiB halo before the chunk.
+//   k_verify             proves every speculation (entry, predecessor, gap) equal to
+//                        what the previous chunk actually produced; any mismatch or
+//                        decode error raises NEED_EXACT.
+//   k_resolve            (only if NEED_EXACT) warp-per-stream sequential walk that
+//                        yields exact chunk entries and the first error per stream.
+//   k_clear / k_decode<false,...>  (only if NEED_EXACT) recompute from exact entries.
+//   k_derive             multiplex scaling + metric reducers per (cpu,bucket).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "hbtgpu.h"
+
+namespace hbtgpu {
+
+constexpr int NT = 256;  // threads per CTA
+constexpr int NWARP = NT / 32;
+constexpr int TILE_BYTES = 16384;
+constexpr int TILE_WORDS = TILE_BYTES / 8;
+constexpr int OV_BYTES = 576;  // >= 40 + 8*64: any SAMPLE/READ/LOST whose header is in the tile is fully staged
+constexpr int STAGE_BYTES = TILE_BYTES + OV_BYTES;
+constexpr int STAGE_WORDS = STAGE_BYTES / 8;
+constexpr int HALO_BYTES = 2048;
+constexpr int HALO_WORDS = HALO_BYTES / 8;
+constexpr int MAXC = TILE_WORDS;  // worst case: every word is a candidate header
+constexpr int WPT = TILE_WORDS / NT;  // words classified per thread (8)
+
+constexpr uint16_t IDX_NONE = 0xFFFF;
+constexpr uint16_t NX_EXIT = 0xFFFF;  // chain leaves the tile
+constexpr uint16_t NX_DEAD = 0xFFFE;  // chain lands on a word that is no valid header
+constexpr uint32_t BKT_OOR = 0xFFFFFFFFu;
+
+constexpr uint64_t OFF_NONE = ~0ull;           // "no such offset"
+constexpr uint64_t PRED_CARRY_IN = ~0ull - 1;  // predecessor is the stream's carry-in state
+constexpr uint64_t PRED_UNKNOWN = ~0ull - 2;   // speculation could not find it
+
+// record types (linux/perf_event.h), as switched on at PerfEventsGroup.h:1439
+enum : uint32_t { REC_LOST = 2, REC_THROTTLE = 5, REC_UNTHROTTLE = 6, REC_READ = 8, REC_SAMPLE = 9 };
+
+// per-candidate flags
+enum : uint8_t { FL_REACH = 1, FL_SAMPLE = 2, FL_LOST = 4, FL_ROW = 8 };
+
+// chunk flags
+enum : uint32_t {
+  CH_FIRST_OF_STREAM = 1,
+  CH_FIRST_OF_IMAGE = 2,
+  CH_LAST_OF_STREAM = 4,
+  CH_LAST_OF_IMAGE = 8,
+  CH_HALO_EXACT_START = 16,  // halo begins at an image start: its chain start is known
+};
+
+// device flag words
+enum { FLAG_NEED_EXACT = 0, FLAG_INTERNAL = 1, FLAG_WHY = 2, FLAG_WHERE = 3, FLAG_COUNT = 8 };
+
+// why the speculative pass was disproved (first reporter wins; diagnostics only)
+enum : uint32_t {
+  WHY_HALO_NO_START = 1, WHY_HALO_DEAD = 2, WHY_HALO_ERR = 3, WHY_HALO_NO_SAMPLE = 4,
+  WHY_IMAGE_SEAM = 5, WHY_TILE_DEAD = 6, WHY_TILE_ERR = 7, WHY_PAST_END = 8,
+  WHY_V_ENTRY = 10, WHY_V_PRED = 11, WHY_V_GAP = 12, WHY_V_IMAGE_END = 13, WHY_V_FIRST = 14
+};
+
+__device__ __forceinline__ void raise_exact(uint32_t* flags, uint32_t why, uint32_t where) {
+  if (atomicCAS(&flags[FLAG_WHY], 0u, why) == 0u) flags[FLAG_WHERE] = where;
+  atomicExch(&flags[FLAG_NEED_EXACT], 1u);
+}
+
+enum { MODE_AGG = 0, MODE_EMIT = 1 };
+
+struct ChunkDesc {
+  uint64_t img_base;    // arena offset of the image
+  uint64_t img_len;     // bytes
+  uint64_t begin, end;  // chunk range, image-relative bytes (begin multiple of TILE_BYTES)
+  uint64_t stream_pos;  // stream byte offset of the image start
+  uint64_t halo_off;    // arena offset (16-aligned) of the halo
+  uint32_t halo_len;    // bytes (multiple of 8); 0: none
+  uint32_t stream;
+  uint32_t flags;
+  uint32_t image;
+};
+
+struct ChunkIO {
+  // what the chunk assumed on entry (SPEC: written by k_decode; exact: written by k_resolve)
+  uint64_t in_entry;  // arena offset of the first record at/after chunk begin
+  uint64_t in_pred;   // arena offset of the predecessor SAMPLE | PRED_CARRY_IN | PRED_UNKNOWN
+  uint64_t limit;     // exact mode: decode nothing at/after this arena offset
+  uint32_t in_gap;    // a LOST lies between predecessor and chunk
+  uint32_t pad0;
+  // what the chunk produced
+  uint64_t out_exit;  // arena offset of the first record after the chunk
+  uint64_t out_last;  // arena offset of the last SAMPLE up to chunk end (pass-through of in_pred if none)
+  uint32_t out_gap;   // a LOST lies after out_last
+  uint32_t n_records;
+  uint32_t n_rows;
+  uint32_t pad1;
+  uint64_t row_base;  // MODE_EMIT: global row index of the chunk's first row
+  uint64_t rec_base;  // MODE_EMIT: global record index of the chunk's first record
+};
+
+struct ImageDesc {
+  uint64_t base, len, stream_pos;
+  uint32_t stream, first_chunk, n_chunks, pad;
+};
+
+struct StreamDesc {
+  uint32_t first_image, n_images;
+};
+
+// per-stream counters as u64 slots
+enum {
+  C_LOST = 0, C_THROTTLE, C_UNTHROTTLE, C_SAMPLE, C_READ, C_RECORDS, C_UNKNOWN, C_ROWS, C_OOR,
+  C_ERR, C_ERR_OFF, C_LAST_TS, C_HEAD_SET, C_SLOTS = 16
+};
+
+struct Params {
+  const uint8_t* arena;
+  const ChunkDesc* chunks;
+  ChunkIO* io;
+  const ImageDesc* images;
+  const StreamDesc* streams;
+  const hbtgpu_carry* carry_in;
+  hbtgpu_carry* carry_out;
+  hbtgpu_head_stub* head;
+  uint64_t* counters;  // [stream][C_SLOTS]
+  uint64_t* acc;       // [stream][bucket][F]
+  uint32_t* flags;
+  uint64_t* rows;      // MODE_EMIT
+  uint64_t* rec_off;   // MODE_EMIT
+  uint32_t* rec_type;
+  uint32_t* rec_size;
+  uint64_t t0, bucket_ns, tsc_mask, time_zero;
+  uint32_t n_events, n_buckets, n_chunks, n_streams;
+  uint32_t time_shift, time_mult;
+  uint32_t force_general, external_carry;
+};
+
+// ------------------------------------------------------------------------------------
+// small device helpers
+
+__device__ __forceinline__ uint64_t umin64(uint64_t a, uint64_t b) { return a < b ? a : b; }
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+// TMA 1-D bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// PerfEventsGroup::kernelTimeFromTsc, PerfEventsGroup.h:1645-1658
+__device__ __forceinline__ uint64_t tsc_to_ktime(uint64_t tsc, uint32_t shift, uint32_t mult,
+                                                 uint64_t zero) {
+  const uint64_t rem_flags = (1ull << shift) - 1;  // tsc_rem_flags_, :1193
+  const uint64_t quot = tsc >> shift;
+  const uint64_t rem = tsc & rem_flags;
+  return zero + quot * mult + ((rem * mult) >> shift);
+}
+// PerfEventsGroup::tscFromKernelTime, PerfEventsGroup.h:1661-1678
+__device__ __forceinline__ uint64_t ktime_to_tsc(uint64_t kt, uint32_t shift, uint32_t mult,
+                                                 uint64_t zero) {
+  const uint64_t delta = kt - zero;
+  const uint64_t quot = delta / mult;
+  const uint64_t rem = delta % mult;
+  return (quot << shift) + (rem << shift) / mult;
+}
+// GroupReadValues::getCount, PerfEventsGroup.h:467-481.  Explicit rounding intrinsics so
+// that nvcc can neither contract nor reorder: u64->f64 RN, mul RN, div RN, f64->u64 RZ.
+__device__ __forceinline__ uint64_t get_count(uint64_t count, uint64_t te, uint64_t tr) {
+  if (te == 0) return 0;
+  if (tr == 0) return 0;
+  const double c = __ull2double_rn(count), e = __ull2double_rn(te), r = __ull2double_rn(tr);
+  const double q = __ddiv_rn(__dmul_rn(c, e), r);
+  // q >= 2^64 is undefined behaviour in the reference's static_cast<uint64_t>; its x86-64
+  // build (cvttsd2si on q - 2^63, xor the sign bit) yields 0 there, and so do we.
+  if (!(q < 18446744073709551616.0)) return 0;
+  return __double2ull_rz(q);
+}
+
+// ------------------------------------------------------------------------------------
+// shared memory of k_decode
+
+struct __align__(128) Smem {
+  uint64_t data[2][STAGE_WORDS];  // TMA destinations (16-byte aligned)
+  uint16_t pos[MAXC];             // candidate word positions, ascending
+  union {
+    struct {                      // chain phase
+      uint16_t jump[2][MAXC];
+      uint16_t map[TILE_WORDS];   // word -> candidate index
+    } ch;
+    struct {                      // decode phase
+      uint32_t bkt[MAXC];
+      uint16_t pred[MAXC];
+    } de;
+  } u;
+  uint16_t next[MAXC];
+  uint8_t fl[MAXC];
+  // carry (generator state up to the current tile)
+  uint64_t c_ts, c_te, c_tr;
+  uint64_t c_last[HBTGPU_MAX_EVENTS];
+  uint64_t c_last_off;            // arena offset of the last SAMPLE so far (or in_pred)
+  uint32_t c_valid, c_gap;
+  // scratch
+  uint64_t bar[2];
+  uint32_t wcnt[WPT * NWARP + 1];
+  uint32_t scan_a[NWARP], scan_b[NWARP], scan_c[NWARP];
+  uint32_t e_idx, term_tgt, term_kind, red_key;
+  uint32_t tile_err;
+  uint32_t cnt[C_SLOTS];          // chunk-local counters (u32), lost is u64 below
+  unsigned long long lost_sum;
+};
+
+__device__ __forceinline__ bool is_header(uint64_t w) {
+  const uint32_t hi = static_cast<uint32_t>(w >> 32);
+  // size = hi >> 16: valid iff >= 8 and a multiple of 8
+  return (hi & 0xFFF80000u) != 0 && (hi & 0x00070000u) == 0;
+}
+__device__ __forceinline__ uint32_t rec_words(uint64_t w) { return static_cast<uint32_t>(w >> 51); }
+
+// exclusive block scan of (a: per-half max via vmaxu2, b: sum).  Returns exclusive prefix of
+// this thread and block totals through tot_a / tot_b.  Contains two __syncthreads.
+__device__ __forceinline__ void block_scan(Smem& s, uint32_t a, uint32_t b, uint32_t& ex_a,
+                                           uint32_t& ex_b, uint32_t& tot_a, uint32_t& tot_b) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t ia = a, ib = b;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t ya = __shfl_up_sync(0xffffffffu, ia, d);
+    const uint32_t yb = __shfl_up_sync(0xffffffffu, ib, d);
+    if (lane >= d) {
+      ia = __vmaxu2(ia, ya);
+      ib += yb;
+    }
+  }
+  if (lane == 31) {
+    s.scan_a[warp] = ia;
+    s.scan_b[warp] = ib;
+  }
+  __syncthreads();
+  uint32_t wa = 0, wb = 0, ta = 0, tb = 0;
+#pragma unroll
+  for (int w = 0; w < NWARP; ++w) {
+    const uint32_t xa = s.scan_a[w], xb = s.scan_b[w];
+    if (w < warp) {
+      wa = __vmaxu2(wa, xa);
+      wb += xb;
+    }
+    ta = __vmaxu2(ta, xa);
+    tb += xb;
+  }
+  uint32_t pa = __shfl_up_sync(0xffffffffu, ia, 1);
+  uint32_t pb = __shfl_up_sync(0xffffffffu, ib, 1);
+  if (lane == 0) {
+    pa = 0;
+    pb = 0;
+  }
+  ex_a = __vmaxu2(wa, pa);
+  ex_b = wb + pb;
+  tot_a = ta;
+  tot_b = tb;
+  __syncthreads();
+}
+
+// Classify words [0, wt) of `buf` as candidate headers and compact their positions in
+// ascending order into s.pos.  Returns K.  Contains __syncthreads.
+__device__ __forceinline__ uint32_t classify(Smem& s, const uint64_t* buf, uint32_t wt) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t ballots[WPT];
+#pragma unroll
+  for (int i = 0; i < WPT; ++i) {
+    const uint32_t w = i * NT + threadIdx.x;
+    const bool c = (w < wt) && is_header(buf[w]);
+    ballots[i] = __ballot_sync(0xffffffffu, c);
+    if (lane == 0) s.wcnt[i * NWARP + warp] = __popc(ballots[i]);
+  }
+  __syncthreads();
+  if (warp == 0) {
+    // exclusive scan of the 64 counts in (round, warp) order: 2 per lane
+    const uint32_t v0 = s.wcnt[2 * lane], v1 = s.wcnt[2 * lane + 1];
+    uint32_t incl = v0 + v1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += y;
+    }
+    const uint32_t excl = incl - (v0 + v1);
+    s.wcnt[2 * lane] = excl;
+    s.wcnt[2 * lane + 1] = excl + v0;
+    if (lane == 31) s.wcnt[WPT * NWARP] = incl;
+  }
+  __syncthreads();
+  const uint32_t lt = (1u << lane) - 1;
+#pragma unroll
+  for (int i = 0; i < WPT; ++i) {
+    if ((ballots[i] >> lane) & 1u) {
+      const uint32_t idx = s.wcnt[i * NWARP + warp] + __popc(ballots[i] & lt);
+      s.pos[idx] = static_cast<uint16_t>(i * NT + threadIdx.x);
+    }
+  }
+  const uint32_t K = s.wcnt[WPT * NWARP];
+  __syncthreads();
+  return K;
+}
+
+// Build word->candidate map and the successor of every candidate (into s.u.ch.jump[0]).
+__device__ __forceinline__ void build_links(Smem& s, const uint64_t* buf, uint32_t wt, uint32_t K) {
+  for (uint32_t w = threadIdx.x; w < wt; w += NT) s.u.ch.map[w] = IDX_NONE;
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j < K; j += NT) s.u.ch.map[s.pos[j]] = static_cast<uint16_t>(j);
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j < K; j += NT) {
+    const uint32_t p = s.pos[j];
+    const uint32_t tgt = p + rec_words(buf[p]);
+    uint16_t nx;
+    if (tgt >= wt) {
+      nx = NX_EXIT;
+    } else {
+      const uint16_t m = s.u.ch.map[tgt];
+      nx = (m == IDX_NONE) ? NX_DEAD : m;
+    }
+    s.u.ch.jump[0][j] = nx;
+  }
+  __syncthreads();
+}
+
+// Recover the chain that starts at word `entry` inside a tile of `wt` valid words with K
+// candidates: sets FL_REACH in s.fl[j] for the candidates on it, and reports its end:
+//   s.term_kind = 0: leaves the tile, next header at word s.term_tgt (>= wt)
+//   s.term_kind = 1: lands on an invalid header at word s.term_tgt (or the entry itself is none)
+// Contiguity shortcut first; pointer jumping otherwise.
+__device__ __forceinline__ void recover_chain(Smem& s, const uint64_t* buf, uint32_t wt, uint32_t K,
+                                              uint32_t entry, bool force_general) {
+  if (threadIdx.x == 0) {
+    s.e_idx = IDX_NONE;
+    s.term_kind = 1;
+    s.term_tgt = entry;
+  }
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j < K; j += NT) {
+    s.fl[j] = 0;
+    if (s.pos[j] == entry) s.e_idx = j;
+  }
+  __syncthreads();
+  const uint32_t e = s.e_idx;
+  if (e == IDX_NONE) return;  // entry is not a valid header: term_kind=1 at entry
+
+  // Shortcut: from e on, every candidate's record ends exactly where the next candidate
+  // begins (and the last one leaves the tile).  Then the chain is pos[e..K).
+  int good = 1;
+  if (!force_general) {
+    for (uint32_t j = e + threadIdx.x; j < K; j += NT) {
+      const uint32_t p = s.pos[j];
+      const uint32_t tgt = p + rec_words(buf[p]);
+      const uint32_t nxt_pos = (j + 1 < K) ? s.pos[j + 1] : 0xFFFFFFFFu;
+      if (j + 1 < K ? (tgt != nxt_pos) : (tgt < wt)) good = 0;
+    }
+  } else {
+    good = 0;
+  }
+  good = __syncthreads_and(good);
+  if (good) {
+    for (uint32_t j = e + threadIdx.x; j < K; j += NT) s.fl[j] = FL_REACH;
+    if (threadIdx.x == 0) {
+      const uint32_t p = s.pos[K - 1];
+      s.term_kind = 0;
+      s.term_tgt = p + rec_words(buf[p]);
+    }
+    __syncthreads();
+    return;
+  }
+
+  // General: pointer jumping.  After round r every candidate within 2^(r+1) hops of e is marked.
+  build_links(s, buf, wt, K);
+  if (threadIdx.x == 0) s.fl[e] = FL_REACH;
+  __syncthreads();
+  int cur = 0;
+  for (;;) {
+    int marked = 0;
+    for (uint32_t j = threadIdx.x; j < K; j += NT) {
+      const uint16_t jn = s.u.ch.jump[cur][j];
+      if (s.fl[j] && jn < NX_DEAD && !s.fl[jn]) {
+        s.fl[jn] = FL_REACH;
+        marked = 1;
+      }
+    }
+    marked = __syncthreads_or(marked);
+    if (!marked) break;
+    for (uint32_t j = threadIdx.x; j < K; j += NT) {
+      const uint16_t jn = s.u.ch.jump[cur][j];
+      s.u.ch.jump[cur ^ 1][j] = (jn < NX_DEAD) ? s.u.ch.jump[cur][jn] : jn;
+    }
+    cur ^= 1;
+    __syncthreads();
+  }
+  // the unique reachable candidate whose successor is a sentinel ends the chain
+  for (uint32_t j = threadIdx.x; j < K; j += NT) {
+    if (s.fl[j]) {
+      const uint32_t p = s.pos[j];
+      const uint32_t tgt = p + rec_words(buf[p]);
+      if (tgt >= wt) {
+        s.term_kind = 0;
+        s.term_tgt = tgt;
+      } else if (s.u.ch.map[tgt] == IDX_NONE) {
+        s.term_kind = 1;
+        s.term_tgt = tgt;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// For the halo: choose the candidate whose chain (a) leaves the halo and (b) is longest.
+// K <= HALO_WORDS <= NT so one candidate per thread.  Returns the word position or ~0.
+__device__ __forceinline__ uint32_t scout_start(Smem& s, const uint64_t* buf, uint32_t wt,
+                                                uint32_t K) {
+  build_links(s, buf, wt, K);
+  const uint32_t j = threadIdx.x;
+  uint32_t t = 0, h = 0;
+  if (j < K) {
+    const uint16_t nx = s.u.ch.jump[0][j];
+    t = (nx >= NX_DEAD) ? j : nx;
+    h = (nx >= NX_DEAD) ? 0 : 1;
+  }
+  // t[j] -> terminal candidate of j's chain, h[j] -> hops to it (jump[1] holds t, next holds h)
+  for (int r = 0; r < 9; ++r) {
+    if (j < K) {
+      s.u.ch.jump[1][j] = static_cast<uint16_t>(t);
+      s.next[j] = static_cast<uint16_t>(h);
+    }
+    __syncthreads();
+    uint32_t t2 = t, h2 = 0;
+    if (j < K) {
+      t2 = s.u.ch.jump[1][t];
+      h2 = s.next[t];
+    }
+    __syncthreads();
+    t = t2;
+    h += h2;
+  }
+  if (threadIdx.x == 0) s.red_key = 0;
+  __syncthreads();
+  if (j < K && s.u.ch.jump[0][t] == NX_EXIT) {
+    const uint32_t key = ((h + 1) << 16) | (0xFFFFu - j);  // longest chain, then earliest
+    atomicMax(&s.red_key, key);
+  }
+  __syncthreads();
+  const uint32_t key = s.red_key;
+  __syncthreads();
+  if (key == 0) return 0xFFFFFFFFu;
+  return s.pos[0xFFFFu - (key & 0xFFFFu)];
+}
+
+__device__ __forceinline__ uint32_t bucket_of(const Params& P, uint64_t ts) {
+  if (ts < P.t0) return BKT_OOR;
+  const uint64_t q = (ts - P.t0) / P.bucket_ns;
+  return q < P.n_buckets ? static_cast<uint32_t>(q) : BKT_OOR;
+}
+
+__device__ __forceinline__ uint64_t xform(const Params& P, uint32_t e, uint64_t v) {
+  return ((P.tsc_mask >> e) & 1ull) ? tsc_to_ktime(v, P.time_shift, P.time_mult, P.time_zero) : v;
+}
+
+__device__ __forceinline__ void red_add(uint64_t* p, uint64_t v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(p), static_cast<unsigned long long>(v));
+}
+
+struct TileCtx {
+  uint64_t tile_abs;    // arena offset of word 0 of the buffer
+  uint64_t stream_off;  // stream byte offset of word 0 of the buffer
+  uint32_t stream;
+  uint32_t rows_before, recs_before;  // MODE_EMIT: already emitted in this chunk
+  uint64_t row_base, rec_base;
+};
+
+// Decode the reachable records of one staged tile and fold them into the carry, the
+// counters and (if AGG) the bucket sums.  SCOUT: only the carry is updated.
+template <bool SCOUT, int MODE>
+__device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint64_t* buf,
+                                            uint32_t K, TileCtx& tc) {
+  const uint32_t n = P.n_events;
+  const uint32_t ipt = (K + NT - 1) / NT;  // candidates per thread (blocked)
+  const uint32_t j0 = threadIdx.x * ipt;
+  const uint32_t j1 = min(j0 + ipt, K);
+
+  // pass 0: type checks, counters, scan inputs
+  uint32_t a = 0, b = 0;
+  uint32_t n_thr = 0, n_unthr = 0, n_read = 0, n_rec = 0;
+  unsigned long long lost = 0;
+  for (uint32_t j = j0; j < j1; ++j) {
+    uint8_t f = s.fl[j];
+    if (f & FL_REACH) {
+      const uint32_t p = s.pos[j];
+      const uint64_t h = buf[p];
+      const uint32_t type = static_cast<uint32_t>(h);
+      const uint32_t size = static_cast<uint32_t>(h >> 48);
+      ++n_rec;
+      if (type == REC_SAMPLE) {
+        // recordSize check (:1502-1507) + nr == kNumEvents (fenced DCHECK, gen :133)
+        const uint64_t nr = (size >= 24) ? buf[p + 2] : ~0ull;
+        if (size < 40 || nr != ((size - 40u) >> 3) || nr != n) {
+          atomicMin(&s.tile_err, p);
+        } else {
+          f |= FL_SAMPLE;
+          a = __vmaxu2(a, (j + 1) << 16);
+          b += 1;
+          s.next[j] = IDX_NONE;
+        }
+      } else if (type == REC_LOST) {
+        if (size < 24) {
+          atomicMin(&s.tile_err, p);
+        } else {
+          f |= FL_LOST;
+          a = __vmaxu2(a, j + 1);
+          lost += buf[p + 2];  // num_lost (:1448)
+        }
+      } else if (type == REC_READ) {
+        const uint64_t nr = (size >= 24) ? buf[p + 2] : ~0ull;
+        if (size < 40 || nr != ((size - 40u) >> 3)) atomicMin(&s.tile_err, p);  // :1518-1523
+        else ++n_read;
+      } else if (type == REC_THROTTLE) {
+        ++n_thr;
+      } else if (type == REC_UNTHROTTLE) {
+        ++n_unthr;
+      }
+      s.fl[j] = f;
+    }
+  }
+  uint32_t ex_a, ex_b, tot_a, tot_b;
+  block_scan(s, a, b, ex_a, ex_b, tot_a, tot_b);  // also orders the fl/next writes above
+
+  // pass 1: link every sample to its predecessor
+  const bool c_valid = s.c_valid != 0, c_gap = s.c_gap != 0;
+  const uint64_t c_ts = s.c_ts;
+  uint32_t run_a = ex_a, run_b = ex_b;
+  uint32_t n_rows = 0, n_unknown = 0, n_sample = 0;
+  for (uint32_t j = j0; j < j1; ++j) {
+    const uint8_t f = s.fl[j];
+    if (f & FL_SAMPLE) {
+      const uint32_t prev_s = run_a >> 16, prev_l = run_a & 0xFFFFu;
+      const bool in_tile = prev_s != 0;
+      const bool gap = in_tile ? (prev_l > prev_s) : (c_gap || prev_l != 0);
+      const bool link = (in_tile || c_valid) && !gap;
+      const uint32_t p = s.pos[j];
+      const uint64_t ts = buf[p + 1];
+      const uint64_t pts = in_tile ? buf[s.pos[prev_s - 1] + 1] : c_ts;
+      if (link && pts > ts) atomicMin(&s.tile_err, p);  // time regression (gen :156-163)
+      if (!SCOUT) {
+        s.u.de.bkt[j] = bucket_of(P, ts);
+        s.u.de.pred[j] = in_tile ? static_cast<uint16_t>(prev_s - 1) : IDX_NONE;
+        if (in_tile) s.next[prev_s - 1] = static_cast<uint16_t>(j);
+        if (link) {
+          s.fl[j] = f | FL_ROW;
+          ++n_rows;
+        } else {
+          ++n_unknown;
+        }
+        ++n_sample;
+      }
+      run_a = __vmaxu2(run_a, (j + 1) << 16);
+      run_b += 1;
+    } else if (f & FL_LOST) {
+      run_a = __vmaxu2(run_a, j + 1);
+    }
+  }
+  if (!SCOUT) {
+    // counters: warp-aggregate then shared atomics
+    const uint32_t vals[7] = {n_thr, n_unthr, n_sample, n_read, n_rec, n_unknown, n_rows};
+    const int slots[7] = {C_THROTTLE, C_UNTHROTTLE, C_SAMPLE, C_READ, C_RECORDS, C_UNKNOWN, C_ROWS};
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+      const uint32_t v = __reduce_add_sync(0xffffffffu, vals[k]);
+      if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s.cnt[slots[k]], v);
+    }
+    if (__any_sync(0xffffffffu, lost != 0)) {
+      unsigned long long l = lost;
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) l += __shfl_xor_sync(0xffffffffu, l, d);
+      if ((threadIdx.x & 31) == 0) atomicAdd(&s.lost_sum, l);
+    }
+  }
+  __syncthreads();
+
+  // MODE_EMIT needs the rank of each row / record inside the tile
+  uint32_t ex_row = 0, ex_rec = 0;
+  if (!SCOUT && MODE == MODE_EMIT) {
+    uint32_t r = 0, q = 0;
+    for (uint32_t j = j0; j < j1; ++j) {
+      r += (s.fl[j] & FL_ROW) ? 1u : 0u;
+      q += (s.fl[j] & FL_REACH) ? 1u : 0u;
+    }
+    uint32_t d0, d1, t0_, t1_;
+    block_scan(s, 0, r | (q << 16), d0, d1, t0_, t1_);
+    (void)d0;
+    (void)t0_;
+    ex_row = d1 & 0xFFFFu;
+    ex_rec = d1 >> 16;
+    if (threadIdx.x == 0) {
+      // totals for the next tile (t1_ packs rows | records<<16; both <= 2048)
+      s.scan_c[0] = t1_ & 0xFFFFu;
+      s.scan_c[1] = t1_ >> 16;
+    }
+  }
+
+  // pass 2: telescoped bucket sums / row emission
+  if (!SCOUT) {
+    uint32_t ord = ex_b;  // ordinal of the sample inside the tile; predecessor's is ord-1
+    for (uint32_t j = j0; j < j1; ++j) {
+      const uint8_t f = s.fl[j];
+      if (MODE == MODE_EMIT && (f & FL_REACH)) {
+        const uint32_t p = s.pos[j];
+        const uint64_t h = buf[p];
+        const uint64_t gi = tc.rec_base + tc.recs_before + ex_rec;
+        P.rec_off[gi] = tc.stream_off + 8ull * p;
+        P.rec_type[gi] = static_cast<uint32_t>(h);
+        P.rec_size[gi] = static_cast<uint32_t>(h >> 48);
+        ++ex_rec;
+      }
+      if (f & FL_SAMPLE) {
+        if (f & FL_ROW) {
+          const uint32_t p = s.pos[j];
+          const uint32_t bk = s.u.de.bkt[j];
+          const uint16_t pj = s.u.de.pred[j];
+          const uint16_t nj = s.next[j];
+          if (MODE == MODE_AGG) {
+            const bool pred_cancel =
+                pj != IDX_NONE && (s.fl[pj] & FL_ROW) && s.u.de.bkt[pj] == bk;
+            const bool next_cancel =
+                nj != IDX_NONE && (s.fl[nj] & FL_ROW) && s.u.de.bkt[nj] == bk;
+            if (bk == BKT_OOR) {
+              atomicAdd(&s.cnt[C_OOR], 1u);
+            } else if (!pred_cancel || !next_cancel) {
+              uint64_t* base = P.acc + (static_cast<uint64_t>(tc.stream) * P.n_buckets + bk) * (n + 3);
+              const uint32_t pp = (pj != IDX_NONE) ? s.pos[pj] : 0;
+              // field order: delta[0..n), dTE, dTR, n_rows
+              for (uint32_t e = 0; e < n + 3; ++e) {
+                uint64_t plus, minus;
+                if (e < n) {
+                  plus = xform(P, e, buf[p + 5 + e]);
+                  minus = (pj != IDX_NONE) ? xform(P, e, buf[pp + 5 + e]) : s.c_last[e];
+                } else if (e == n) {
+                  plus = buf[p + 3];
+                  minus = (pj != IDX_NONE) ? buf[pp + 3] : s.c_te;
+                } else if (e == n + 1) {
+                  plus = buf[p + 4];
+                  minus = (pj != IDX_NONE) ? buf[pp + 4] : s.c_tr;
+                } else {
+                  plus = ord;
+                  minus = static_cast<uint64_t>(ord) - 1;
+                }
+                const uint64_t v = (next_cancel ? 0 : plus) - (pred_cancel ? 0 : minus);
+                red_add(base + e, v);
+              }
+            }
+          } else {  // MODE_EMIT: the row as CpuCountSampleGenerator writes it (:165-182)
+            const uint32_t pp = (pj != IDX_NONE) ? s.pos[pj] : 0;
+            const uint64_t ts = buf[p + 1];
+            const uint64_t pts = (pj != IDX_NONE) ? buf[pp + 1] : s.c_ts;
+            uint64_t* row = P.rows + (tc.row_base + tc.rows_before + ex_row) * (n + 2);
+            row[0] = pts;
+            row[1] = ts - pts;
+            for (uint32_t e = 0; e < n; ++e) {
+              const uint64_t cur = xform(P, e, buf[p + 5 + e]);
+              const uint64_t prv = (pj != IDX_NONE) ? xform(P, e, buf[pp + 5 + e]) : s.c_last[e];
+              row[2 + e] = cur - prv;
+            }
+            ++ex_row;
+          }
+        }
+        ++ord;
+      }
+    }
+  }
+  __syncthreads();  // all reads of the carry are done
+
+  // fold the tile into the carry
+  const uint32_t last_s = tot_a >> 16, last_l = tot_a & 0xFFFFu;
+  if (last_s != 0) {
+    const uint32_t p = s.pos[last_s - 1];
+    for (uint32_t e = threadIdx.x; e < n; e += NT) s.c_last[e] = xform(P, e, buf[p + 5 + e]);
+    if (threadIdx.x == 0) {
+      s.c_ts = buf[p + 1];
+      s.c_te = buf[p + 3];
+      s.c_tr = buf[p + 4];
+      s.c_valid = 1;
+      s.c_gap = last_l > last_s;
+      s.c_last_off = tc.tile_abs + 8ull * p;
+    }
+  } else if (last_l != 0) {
+    if (threadIdx.x == 0) s.c_gap = 1;
+  }
+  if (MODE == MODE_EMIT && !SCOUT) {
+    __syncthreads();
+    tc.rows_before += s.scan_c[0];
+    tc.recs_before += s.scan_c[1];
+  }
+  __syncthreads();
+}
+
+// Initialise the carry from a predecessor SAMPLE in global memory / the stream carry-in.
+__device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t stream, uint64_t pred,
+                                           uint32_t gap) {
+  const uint32_t n = P.n_events;
+  if (pred == PRED_CARRY_IN) {
+    const hbtgpu_carry& c = P.carry_in[stream];
+    for (uint32_t e = threadIdx.x; e < n; e += NT) s.c_last[e] = c.last[e];
+    if (threadIdx.x == 0) {
+      s.c_ts = c.tstamp;
+      s.c_te = c.te;
+      s.c_tr = c.tr;
+      s.c_valid = c.valid != 0;
+      s.c_gap = gap;
+      s.c_last_off = PRED_CARRY_IN;
+    }
+  } else if (pred == PRED_UNKNOWN) {
+    if (threadIdx.x == 0) {
+      s.c_valid = 0;
+      s.c_gap = 1;
+      s.c_last_off = PRED_UNKNOWN;
+    }
+  } else {
+    const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + pred);
+    for (uint32_t e = threadIdx.x; e < n; e += NT) s.c_last[e] = xform(P, e, r[5 + e]);
+    if (threadIdx.x == 0) {
+      s.c_ts = r[1];
+      s.c_te = r[3];
+      s.c_tr = r[4];
+      s.c_valid = 1;
+      s.c_gap = gap;
+      s.c_last_off = pred;
+    }
+  }
+}
+
+template <bool SPEC, int MODE>
+__global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw);
+  if (!SPEC && MODE == MODE_AGG && P.flags[FLAG_NEED_EXACT] == 0) return;  // exact pass not needed
+
+  const uint32_t c = blockIdx.x;
+  const ChunkDesc cd = P.chunks[c];
+  ChunkIO& io = P.io[c];
+
+  if (threadIdx.x == 0) {
+    mbar_init(&s.bar[0], 1);
+    mbar_init(&s.bar[1], 1);
+    fence_barrier_init();
+    s.tile_err = 0xFFFFFFFFu;
+    s.lost_sum = 0;
+  }
+  if (threadIdx.x < C_SLOTS) s.cnt[threadIdx.x] = 0;
+  __syncthreads();
+
+  uint32_t phase[2] = {0, 0};
+  uint32_t bad = 0;  // fast mode: why this chunk's result is untrustworthy (WHY_*), 0 if fine
+
+  // ---- where does the chain enter this chunk, and who is the predecessor sample? ----
+  uint64_t entry_abs;
+  const uint64_t chunk_abs = cd.img_base + cd.begin;
+  uint64_t limit_abs = cd.img_base + cd.img_len;
+  if (SPEC) {
+    if (cd.halo_len == 0) {
+      entry_abs = chunk_abs;
+      load_carry(s, P, cd.stream, PRED_CARRY_IN, 0);
+      __syncthreads();
+    } else {
+      // stage the halo and scout it
+      const uint32_t hw = cd.halo_len / 8;
+      if (threadIdx.x == 0) {
+        // like a tile, the halo is staged with an overlap so that a record whose header is in
+        // the halo but whose body runs into the chunk is fully readable (a halo taken from the
+        // previous image ends on a record boundary and needs none)
+        uint32_t bytes = (cd.halo_len + 15u) & ~15u;
+        if (!(cd.flags & CH_FIRST_OF_IMAGE)) {
+          const uint64_t avail = (cd.img_base + cd.img_len - cd.halo_off + 15ull) & ~15ull;
+          bytes = static_cast<uint32_t>(umin64(cd.halo_len + OV_BYTES, avail));
+        }
+        mbar_expect_tx(&s.bar[0], bytes);
+        tma_load_1d(s.data[0], P.arena + cd.halo_off, bytes, &s.bar[0]);
+      }
+      mbar_wait(&s.bar[0], phase[0]);
+      phase[0] ^= 1;
+      const uint64_t* hb = s.data[0];
+      const uint32_t K = classify(s, hb, hw);
+      uint32_t start = 0xFFFFFFFFu;
+      if (K > 0) {
+        if (cd.flags & CH_HALO_EXACT_START) start = 0;
+        else start = scout_start(s, hb, hw, K);
+      }
+      load_carry(s, P, cd.stream, PRED_UNKNOWN, 0);
+      __syncthreads();
+      entry_abs = chunk_abs;
+      if (start == 0xFFFFFFFFu) {
+        bad = WHY_HALO_NO_START;
+      } else {
+        recover_chain(s, hb, hw, K, start, P.force_general != 0);
+        if (s.term_kind != 0) {
+          bad = WHY_HALO_DEAD;
+        } else {
+          entry_abs = cd.halo_off + 8ull * s.term_tgt;
+          TileCtx tc{cd.halo_off, 0, cd.stream, 0, 0, 0, 0};
+          decode_tile<true, MODE_AGG>(s, P, hb, K, tc);
+          if (s.tile_err != 0xFFFFFFFFu) bad = WHY_HALO_ERR;
+          else if (!s.c_valid) bad = WHY_HALO_NO_SAMPLE;  // predecessor unknown
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) s.tile_err = 0xFFFFFFFFu;
+      // a halo inside the previous image must end exactly on this image's first byte
+      if ((cd.flags & CH_FIRST_OF_IMAGE) && !bad && entry_abs != cd.halo_off + cd.halo_len) bad = WHY_IMAGE_SEAM;
+      if (cd.flags & CH_FIRST_OF_IMAGE) entry_abs = chunk_abs;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      io.in_entry = entry_abs;
+      io.in_pred = s.c_last_off;
+      io.in_gap = s.c_gap;
+      io.limit = ~0ull;
+    }
+  } else {
+    entry_abs = io.in_entry;
+    limit_abs = min(limit_abs, io.limit);
+    load_carry(s, P, cd.stream, io.in_pred, io.in_gap);
+    __syncthreads();
+  }
+
+  // ---- tiles ----
+  const uint64_t img_end_abs = cd.img_base + cd.img_len;
+  const uint64_t chunk_end_abs = min(cd.img_base + cd.end, limit_abs);
+  const uint32_t n_tiles = static_cast<uint32_t>((cd.end - cd.begin + TILE_BYTES - 1) / TILE_BYTES);
+  TileCtx tc{0, 0, cd.stream, 0, 0, io.row_base, io.rec_base};
+  uint64_t next_abs = entry_abs;  // arena offset of the next record header on the chain
+
+  auto issue = [&](uint32_t t) {
+    const uint64_t off = chunk_abs + static_cast<uint64_t>(t) * TILE_BYTES;
+    uint64_t avail = img_end_abs - off;
+    avail = (avail + 15ull) & ~15ull;
+    const uint32_t bytes = static_cast<uint32_t>(umin64(avail, STAGE_BYTES));
+    mbar_expect_tx(&s.bar[t & 1], bytes);
+    tma_load_1d(s.data[t & 1], P.arena + off, bytes, &s.bar[t & 1]);
+  };
+  const bool any_work = next_abs < chunk_end_abs;
+  if (any_work && threadIdx.x == 0) issue(0);
+  for (uint32_t t = 0; any_work && t < n_tiles; ++t) {
+    const uint64_t tile_abs = chunk_abs + static_cast<uint64_t>(t) * TILE_BYTES;
+    if (tile_abs >= chunk_end_abs) break;
+    if (threadIdx.x == 0 && t + 1 < n_tiles && tile_abs + TILE_BYTES < chunk_end_abs) issue(t + 1);
+    mbar_wait(&s.bar[t & 1], phase[t & 1]);
+    phase[t & 1] ^= 1;
+    const uint64_t* buf = s.data[t & 1];
+    const uint32_t wt = static_cast<uint32_t>(umin64(TILE_BYTES, chunk_end_abs - tile_abs) / 8);
+    if (next_abs < tile_abs + 8ull * wt) {
+      const uint32_t entry = static_cast<uint32_t>((next_abs - tile_abs) / 8);
+      const uint32_t K = classify(s, buf, wt);
+      recover_chain(s, buf, wt, K, entry, P.force_general != 0);
+      tc.tile_abs = tile_abs;
+      tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base);
+      const uint32_t term_kind = s.term_kind, term_tgt = s.term_tgt;
+      decode_tile<false, MODE>(s, P, buf, K, tc);
+      const uint64_t tgt_abs = tile_abs + 8ull * term_tgt;
+      if (term_kind != 0 || s.tile_err != 0xFFFFFFFFu) {
+        bad = term_kind != 0 ? WHY_TILE_DEAD : WHY_TILE_ERR;
+        break;
+      }
+      if (tgt_abs > limit_abs) {  // record runs past the image end (or the exact-mode limit)
+        bad = WHY_PAST_END;
+        break;
+      }
+      next_abs = tgt_abs;
+    }
+    __syncthreads();  // buffer (t&1) is free for tile t+2
+  }
+
+  // ---- publish ----
+  if (threadIdx.x == 0) {
+    io.out_exit = next_abs;
+    io.out_last = s.c_last_off;
+    io.out_gap = s.c_gap;
+    io.n_records = s.cnt[C_RECORDS];
+    io.n_rows = s.cnt[C_ROWS];
+    if (bad) {
+      if (SPEC) raise_exact(P.flags, bad, c);
+      else atomicExch(&P.flags[FLAG_INTERNAL], bad);
+    }
+  }
+  if (MODE == MODE_AGG) {
+    uint64_t* ctr = P.counters + static_cast<uint64_t>(cd.stream) * C_SLOTS;
+    if (threadIdx.x < C_SLOTS && threadIdx.x != C_LOST && s.cnt[threadIdx.x])
+      red_add(&ctr[threadIdx.x], s.cnt[threadIdx.x]);
+    if (threadIdx.x == 0 && s.lost_sum) red_add(&ctr[C_LOST], s.lost_sum);
+    // stream carry-out: in exact mode k_resolve owns it
+    if (SPEC && (cd.flags & CH_LAST_OF_STREAM)) {
+      hbtgpu_carry& co = P.carry_out[cd.stream];
+      for (uint32_t e = threadIdx.x; e < P.n_events; e += NT) co.last[e] = s.c_last[e];
+      if (threadIdx.x == 0) {
+        const bool v = s.c_valid && !s.c_gap;
+        co.valid = v;
+        co.tstamp = v ? s.c_ts : ~0ull;
+        co.te = s.c_te;
+        co.tr = s.c_tr;
+        ctr[C_LAST_TS] = co.tstamp;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------
+// k_verify: one thread per chunk.  Induction over stream order: chunk 0 of a stream is exact
+// by construction; chunk c is exact if what it assumed equals what chunk c-1 produced.
+__global__ void k_verify(const Params P) {
+  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= P.n_chunks) return;
+  const ChunkDesc cd = P.chunks[c];
+  const ChunkIO& io = P.io[c];
+  uint32_t why = 0;
+  if (cd.flags & CH_FIRST_OF_STREAM) {
+    if (!(io.in_entry == cd.img_base + cd.begin && io.in_pred == PRED_CARRY_IN && io.in_gap == 0))
+      why = WHY_V_FIRST;
+  } else {
+    const ChunkDesc pd = P.chunks[c - 1];
+    const ChunkIO& pio = P.io[c - 1];
+    if (cd.flags & CH_FIRST_OF_IMAGE) {
+      if (!(pio.out_exit == pd.img_base + pd.img_len && io.in_entry == cd.img_base)) why = WHY_V_ENTRY;
+    } else if (pio.out_exit != io.in_entry) {
+      why = WHY_V_ENTRY;
+    }
+    if (!why && pio.out_last != io.in_pred) why = WHY_V_PRED;
+    if (!why && pio.out_gap != io.in_gap) why = WHY_V_GAP;
+  }
+  if (!why && (cd.flags & CH_LAST_OF_IMAGE) && io.out_exit != cd.img_base + cd.img_len)
+    why = WHY_V_IMAGE_END;
+  if (why) raise_exact(P.flags, why, c);
+}
+
+// ------------------------------------------------------------------------------------
+// k_resolve: exact sequential walk, one warp per stream (lane 0 walks; the warp stages
+// 4 KiB windows into shared memory so the dependent loads hit on-chip memory).
+constexpr int RES_WIN_BYTES = 4096;
+constexpr int RES_WARPS = 4;
+
+__global__ void __launch_bounds__(RES_WARPS * 32) k_resolve(const Params P) {
+  if (P.flags[FLAG_NEED_EXACT] == 0) return;
+  __shared__ __align__(16) uint64_t win[RES_WARPS][RES_WIN_BYTES / 8 + 80];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t sidx = blockIdx.x * RES_WARPS + warp;
+  if (sidx >= P.n_streams) return;
+  const StreamDesc sd = P.streams[sidx];
+  const uint32_t n = P.n_events;
+  uint64_t* ctr = P.counters + static_cast<uint64_t>(sidx) * C_SLOTS;
+
+  // walker state (lane 0)
+  const hbtgpu_carry& cin = P.carry_in[sidx];
+  bool valid = cin.valid != 0;        // count_.tstamp != kInvalidTimeStamp
+  uint64_t st_ts = cin.tstamp;        // count_.tstamp
+  uint64_t last_off = PRED_CARRY_IN;  // last SAMPLE seen
+  bool gap = false;                   // LOST after last_off
+  int64_t err = 0;
+  uint64_t err_off = 0;
+  bool stopped = false;
+  constexpr int WIN_WORDS = RES_WIN_BYTES / 8 + 80;
+
+  for (uint32_t ii = 0; ii < sd.n_images; ++ii) {
+    const ImageDesc im = P.images[sd.first_image + ii];
+    uint32_t ch = im.first_chunk;
+    const uint32_t ch_end = im.first_chunk + im.n_chunks;
+    uint64_t pos = 0;  // image-relative
+    while (true) {
+      const bool more = !stopped && pos < im.len;
+      if (!__shfl_sync(0xffffffffu, more, 0)) break;
+      // stage [wbase, wbase + WIN) (+ overlap for record fields)
+      const uint64_t wbase = __shfl_sync(0xffffffffu, pos, 0) & ~15ull;
+      const uint64_t avail_words = (im.len - wbase + 7) / 8;
+      const uint32_t words = static_cast<uint32_t>(umin64(WIN_WORDS, avail_words));
+      const uint64_t* src = reinterpret_cast<const uint64_t*>(P.arena + im.base + wbase);
+      for (uint32_t w = lane; w < words; w += 32) win[warp][w] = src[w];
+      __syncwarp();
+      if (lane == 0) {
+        while (pos < im.len && pos - wbase < RES_WIN_BYTES) {
+          const uint32_t wi = static_cast<uint32_t>((pos - wbase) / 8);
+          const uint64_t h = win[warp][wi];
+          const uint32_t type = static_cast<uint32_t>(h);
+          const uint32_t size = static_cast<uint32_t>(h >> 48);
+          // hand the chunks that begin at or before this record their entry
+          while (ch < ch_end && P.chunks[ch].begin <= pos) {
+            ChunkIO& io = P.io[ch];
+            io.in_entry = im.base + pos;
+            io.in_pred = last_off;
+            io.in_gap = gap;
+            io.limit = ~0ull;
+            ++ch;
+          }
+          bool bad = size < 8 || (size & 7) || pos + size > im.len;  // fences, see oracle
+          uint64_t nr = 0, ts = 0;
+          if (!bad && (type == REC_SAMPLE || type == REC_READ)) {
+            // fields may lie beyond the staged window only for oversized records
+            nr = (size >= 24) ? win[warp][wi + 2] : ~0ull;
+            ts = win[warp][wi + 1];
+            bad = size < 40 || nr != ((size - 40u) >> 3) || (type == REC_SAMPLE && nr != n);
+          }
+          if (!bad && type == REC_LOST) bad = size < 24;
+          if (!bad && type == REC_SAMPLE && valid && !gap && st_ts > ts) {
+            bad = true;     // time regression: state is invalidated (gen :156-163)
+            valid = false;
+          }
+          if (bad) {
+            err = -1;  // -EPERM
+            err_off = im.stream_pos + pos;
+            stopped = true;
+            break;
+          }
+          if (type == REC_SAMPLE) {
+            st_ts = ts;
+            valid = true;
+            gap = false;
+            last_off = im.base + pos;
+          } else if (type == REC_LOST) {
+            gap = true;
+          }
+          pos += size;
+        }
+      }
+      __syncwarp();
+    }
+    if (lane == 0) {
+      // chunks the walk never reached (after an error, or jumped over by a long record)
+      const uint64_t stop_abs = im.base + pos;
+      for (uint32_t k = im.first_chunk; k < ch_end; ++k) {
+        ChunkIO& io = P.io[k];
+        if (k >= ch) {
+          io.in_entry = stopped ? ~0ull : stop_abs;
+          io.in_pred = last_off;
+          io.in_gap = gap;
+        }
+        io.limit = stopped ? stop_abs : ~0ull;
+      }
+    }
+    __syncwarp();
+  }
+  if (lane == 0) {
+    // images after the error: nothing is decoded
+    // (their chunks were visited above with stopped=true: in_entry = ~0)
+    hbtgpu_carry& co = P.carry_out[sidx];
+    const bool v = valid && !gap;
+    if (last_off == PRED_CARRY_IN) {
+      for (uint32_t e = 0; e < n; ++e) co.last[e] = cin.last[e];
+      co.te = cin.te;
+      co.tr = cin.tr;
+    } else {
+      const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + last_off);
+      for (uint32_t e = 0; e < n; ++e) co.last[e] = xform(P, e, r[5 + e]);
+      co.te = r[3];
+      co.tr = r[4];
+    }
+    co.valid = v;
+    co.tstamp = v ? st_ts : ~0ull;
+    ctr[C_ERR] = static_cast<uint64_t>(err);
+    ctr[C_ERR_OFF] = err_off;
+    ctr[C_LAST_TS] = co.tstamp;
+  }
+}
+
+// zero result buffers when the exact path has to recompute them
+__global__ void k_clear(const Params P, uint64_t acc_words) {
+  if (P.flags[FLAG_NEED_EXACT] == 0) return;
+  const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+  const uint64_t i0 = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (uint64_t i = i0; i < acc_words; i += stride) P.acc[i] = 0;
+  const uint64_t nctr = static_cast<uint64_t>(P.n_streams) * C_SLOTS;
+  for (uint64_t i = i0; i < nctr; i += stride)
+    if ((i % C_SLOTS) < C_ERR) P.counters[i] = 0;
+}
+
+// ------------------------------------------------------------------------------------
+// k_derive: per (cpu,bucket): scaled = getCount(acc), metrics = reducers(scaled)
+struct DeriveParams {
+  const uint64_t* acc;
+  uint64_t* scaled;
+  double* metric;
+  uint32_t* valid;
+  uint64_t n_cells;  // cpus * buckets
+  uint32_t n_events, n_metrics;
+  hbtgpu_metric metrics[HBTGPU_MAX_METRICS];
+};
+
+__device__ __forceinline__ double add_reduce_int(const uint64_t* v, uint32_t k) {
+  // std::accumulate(begin, end, 0): int accumulator (BuiltinMetrics.cpp:94)
+  int32_t acc = 0;
+  for (uint32_t i = 0; i < k; ++i)
+    acc = static_cast<int32_t>(static_cast<uint32_t>(static_cast<uint64_t>(static_cast<int64_t>(acc)) + v[i]));
+  return static_cast<double>(acc);
+}
+
+__global__ void __launch_bounds__(256) k_derive(const DeriveParams D) {
+  const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= D.n_cells) return;
+  const uint32_t n = D.n_events;
+  const uint64_t* a = D.acc + i * (n + 3);
+  const uint64_t te = a[n], tr = a[n + 1];
+  uint64_t* sc = D.scaled + i * n;
+  for (uint32_t e = 0; e < n; ++e) sc[e] = get_count(a[e], te, tr);
+  uint32_t vmask = 0;
+  for (uint32_t m = 0; m < D.n_metrics; ++m) {
+    const hbtgpu_metric& md = D.metrics[m];
+    double out = 0.0;
+    bool ok = false;
+    if (md.kind == HBTGPU_METRIC_RATE) {
+      // getRateReducer: exactly two values, denominator != 0 (BuiltinMetrics.cpp:104-116)
+      if (md.n_idx == 2) {
+        const uint64_t num = sc[md.idx[0]], den = sc[md.idx[1]];
+        if (den != 0) {
+          out = __ddiv_rn(__ull2double_rn(num), __ull2double_rn(den));
+          ok = true;
+        }
+      }
+    } else if (md.kind == HBTGPU_METRIC_ADD) {
+      if (md.n_idx > 0) {
+        uint64_t v[HBTGPU_MAX_METRIC_EVENTS];
+        for (uint32_t k = 0; k < md.n_idx; ++k) v[k] = sc[md.idx[k]];
+        out = add_reduce_int(v, md.n_idx);
+        ok = true;
+      }
+    } else if (md.kind == HBTGPU_METRIC_PER_SECOND_MEGA) {
+      // float(double(count) * 1e3 / double(time_running)) (PerfMonitor.cpp:63-66)
+      const double c = __ull2double_rn(sc[md.idx[0]]);
+      const float f = __double2float_rn(__ddiv_rn(__dmul_rn(c, 1e3), __ull2double_rn(tr)));
+      out = static_cast<double>(f);
+      ok = true;
+    }
+    D.metric[i * D.n_metrics + m] = out;
+    if (ok) vmask |= 1u << m;
+  }
+  D.valid[i] = vmask;
+}
+
+// ------------------------------------------------------------------------------------
+// elementwise arithmetic kernels (device pointers)
+__global__ void k_get_count(const uint64_t* c, const uint64_t* te, const uint64_t* tr, uint64_t* out,
+                            size_t n) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = get_count(c[i], te[i], tr[i]);
+}
+__global__ void k_rate(const uint64_t* num, const uint64_t* den, double* out, uint8_t* valid, size_t n) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const bool ok = den[i] != 0;
+  valid[i] = ok;
+  out[i] = ok ? __ddiv_rn(__ull2double_rn(num[i]), __ull2double_rn(den[i])) : 0.0;
+}
+__global__ void k_add_reduce(const uint64_t* vals, size_t k, double* out, size_t n) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int32_t acc = 0;
+  for (size_t j = 0; j < k; ++j)
+    acc = static_cast<int32_t>(static_cast<uint32_t>(static_cast<uint64_t>(static_cast<int64_t>(acc)) + vals[i * k + j]));
+  out[i] = static_cast<double>(acc);
+}
+__global__ void k_tsc(const uint64_t* in, uint64_t* out, size_t n, uint32_t shift, uint32_t mult,
+                      uint64_t zero, int inverse) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = inverse ? ktime_to_tsc(in[i], shift, mult, zero) : tsc_to_ktime(in[i], shift, mult, zero);
+}
+__global__ void k_per_second_mega(const uint64_t* c, const uint64_t* tr, float* out, size_t n) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = __double2float_rn(__ddiv_rn(__dmul_rn(__ull2double_rn(c[i]), 1e3), __ull2double_rn(tr[i])));
+}
+__global__ void k_running_ratio(const uint64_t* te, const uint64_t* tr, float* ratio, uint64_t* ri,
+                                uint8_t* mux, size_t n) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  // getRunningRatio returns te/tr despite its comment (:513-522)
+  ratio[i] = te[i] == 0 ? 1.0f : __fdiv_rn(__ull2float_rn(te[i]), __ull2float_rn(tr[i]));
+  ri[i] = te[i] == 0 ? 100ull : (100ull * tr[i]) / te[i];
+  mux[i] = te[i] != 0 && tr[i] != te[i];
+}
+
+}  // namespace hbtgpu

@@ -1,0 +1,352 @@
+"""ctypes binding of libhbtgpu.so (C ABI: include/hbtgpu.h).
+
+This is plumbing for tests and bench.py: the product is the shared library.
+There is no CPU fallback -- importing works anywhere, but creating a context
+without the built library or without a CUDA device raises.
+"""
+import ctypes as C
+import errno
+import os
+
+import numpy as np
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libhbtgpu.so")
+
+MAX_EVENTS = 64
+MAX_METRICS = 8
+MAX_METRIC_EVENTS = 8
+
+F_FORCE_EXACT = 0x1
+F_FORCE_GENERAL = 0x2
+F_EXTERNAL_CARRY = 0x4
+
+METRIC_RATE = 1
+METRIC_ADD = 2
+METRIC_PER_SECOND_MEGA = 3
+
+
+class Metric(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("n_idx", C.c_uint32),
+                ("idx", C.c_uint32 * MAX_METRIC_EVENTS)]
+
+
+class Config(C.Structure):
+    _fields_ = [
+        ("device", C.c_int32), ("n_events", C.c_uint32), ("tsc_mask", C.c_uint64),
+        ("time_shift", C.c_uint32), ("time_mult", C.c_uint32), ("time_zero", C.c_uint64),
+        ("max_cpus", C.c_uint32), ("n_buckets", C.c_uint32), ("t0", C.c_uint64),
+        ("bucket_ns", C.c_uint64), ("arena_bytes", C.c_uint64), ("n_metrics", C.c_uint32),
+        ("flags", C.c_uint32), ("metrics", Metric * MAX_METRICS),
+    ]
+
+
+class Carry(C.Structure):
+    _fields_ = [("valid", C.c_uint64), ("tstamp", C.c_uint64), ("te", C.c_uint64),
+                ("tr", C.c_uint64), ("last", C.c_uint64 * MAX_EVENTS)]
+
+
+class HeadStub(C.Structure):
+    _fields_ = [("has_sample", C.c_uint64), ("lost_before", C.c_uint64), ("tstamp", C.c_uint64),
+                ("te", C.c_uint64), ("tr", C.c_uint64), ("value", C.c_uint64 * MAX_EVENTS)]
+
+
+COUNTER_KEYS = ["lost", "comm", "exit", "throttle", "unthrottle", "fork", "sample", "read", "aux",
+                "itrace_start", "switch_cpu_wide", "num_records", "num_unknown_count_interval",
+                "num_rows", "rows_out_of_range", "err", "err_offset", "last_tstamp"]
+
+
+class Counters(C.Structure):
+    _fields_ = [(k, C.c_int64 if k == "err" else C.c_uint64) for k in COUNTER_KEYS]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k in COUNTER_KEYS}
+
+
+class BucketView(C.Structure):
+    _fields_ = [("acc", C.c_void_p), ("scaled", C.c_void_p), ("metric", C.c_void_p),
+                ("valid", C.c_void_p), ("max_cpus", C.c_uint32), ("n_buckets", C.c_uint32),
+                ("n_events", C.c_uint32), ("n_metrics", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("image_bytes", C.c_uint64), ("n_chunks", C.c_uint32), ("exact_runs", C.c_uint32),
+                ("kernel_launches", C.c_uint32), ("last_run_ms", C.c_float),
+                ("last_decode_ms", C.c_float), ("exact_reason", C.c_uint32),
+                ("exact_chunk", C.c_uint32)]
+
+
+# every symbol include/hbtgpu.h declares (tests check that the library exports them all)
+ABI_SYMBOLS = [
+    "hbtgpu_create", "hbtgpu_destroy", "hbtgpu_last_error", "hbtgpu_set_carry",
+    "hbtgpu_submit_image", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
+    "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows",
+    "hbtgpu_get_records", "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_derive",
+    "hbtgpu_get_head_stub", "hbtgpu_apply_boundary", "hbtgpu_acc_device", "hbtgpu_stream",
+    "hbtgpu_math_get_count", "hbtgpu_math_rate", "hbtgpu_math_add_reduce",
+    "hbtgpu_math_tsc_to_ktime", "hbtgpu_math_ktime_to_tsc", "hbtgpu_math_per_second_mega",
+    "hbtgpu_math_running_ratio", "hbtgpu_get_stats", "hbtgpu_version",
+]
+
+_lib = None
+
+
+class HbtGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"hbtgpu error {code} ({errno.errorcode.get(-code, '?')}): {msg}")
+        self.code = code
+
+
+def lib():
+    """Load libhbtgpu.so; fail loudly if it was never built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(
+                f"{LIB_PATH} not built: run __graft_entry__.build() or "
+                "`make -C dynolog_b200/csrc`. There is no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        L.hbtgpu_last_error.restype = C.c_char_p
+        L.hbtgpu_last_error.argtypes = [C.c_void_p]
+        L.hbtgpu_version.restype = C.c_char_p
+        L.hbtgpu_stream.restype = C.c_void_p
+        L.hbtgpu_stream.argtypes = [C.c_void_p]
+        L.hbtgpu_destroy.restype = None
+        L.hbtgpu_destroy.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+def _u64(a):
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+def make_carry(valid=False, tstamp=0, te=0, tr=0, last=()):
+    c = Carry()
+    c.valid = 1 if valid else 0
+    c.tstamp = tstamp
+    c.te = te
+    c.tr = tr
+    for i, v in enumerate(last):
+        c.last[i] = int(v)
+    return c
+
+
+class Context:
+    """One hbtgpu context (one CUDA device + one stream)."""
+
+    def __init__(self, n_events, max_cpus=1, n_buckets=1, t0=0, bucket_ns=1, arena_bytes=1 << 20,
+                 tsc_mask=0, time_shift=0, time_mult=1, time_zero=0, metrics=(), flags=0, device=0):
+        self.L = lib()
+        cfg = Config()
+        cfg.device = device
+        cfg.n_events = n_events
+        cfg.tsc_mask = tsc_mask
+        cfg.time_shift = time_shift
+        cfg.time_mult = time_mult
+        cfg.time_zero = time_zero
+        cfg.max_cpus = max_cpus
+        cfg.n_buckets = n_buckets
+        cfg.t0 = t0
+        cfg.bucket_ns = bucket_ns
+        cfg.arena_bytes = arena_bytes
+        cfg.flags = flags
+        cfg.n_metrics = len(metrics)
+        for m, (kind, idx) in enumerate(metrics):
+            cfg.metrics[m].kind = kind
+            cfg.metrics[m].n_idx = len(idx)
+            for k, i in enumerate(idx):
+                cfg.metrics[m].idx[k] = i
+        self.cfg = cfg
+        self.h = C.c_void_p()
+        rc = self.L.hbtgpu_create(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            raise HbtGpuError(rc, self.L.hbtgpu_last_error(None).decode())
+        self.n_events, self.max_cpus, self.n_buckets = n_events, max_cpus, n_buckets
+        self.n_metrics = len(metrics)
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise HbtGpuError(rc, self.L.hbtgpu_last_error(self.h).decode())
+
+    def close(self):
+        if self.h:
+            self.L.hbtgpu_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- input
+    def set_carry(self, cpu, carry):
+        self._ck(self.L.hbtgpu_set_carry(self.h, C.c_uint32(cpu), C.byref(carry)))
+
+    def submit_image(self, cpu, first, second=None):
+        first = np.ascontiguousarray(first, dtype=np.uint8)
+        n2 = 0
+        p2 = C.c_void_p(0)
+        if second is not None:
+            second = np.ascontiguousarray(second, dtype=np.uint8)
+            n2 = second.size
+            p2 = _ptr(second)
+        self._ck(self.L.hbtgpu_submit_image(self.h, C.c_uint32(cpu), _ptr(first),
+                                            C.c_size_t(first.size), p2, C.c_size_t(n2)))
+
+    def submit_image_ptr(self, cpu, host_ptr, nbytes):
+        self._ck(self.L.hbtgpu_submit_image(self.h, C.c_uint32(cpu), C.c_void_p(host_ptr),
+                                            C.c_size_t(nbytes), C.c_void_p(0), C.c_size_t(0)))
+
+    def submit_image_device(self, cpu, device_ptr, nbytes):
+        self._ck(self.L.hbtgpu_submit_image_device(self.h, C.c_uint32(cpu), C.c_void_p(device_ptr),
+                                                   C.c_size_t(nbytes)))
+
+    def reset(self, keep_carry=False):
+        self._ck(self.L.hbtgpu_reset(self.h, C.c_int(1 if keep_carry else 0)))
+
+    # ---- hot path
+    def run(self):
+        self._ck(self.L.hbtgpu_run(self.h))
+
+    def sync(self):
+        self._ck(self.L.hbtgpu_sync(self.h))
+
+    def derive(self):
+        self._ck(self.L.hbtgpu_derive(self.h))
+
+    # ---- results
+    def counters(self, cpu):
+        c = Counters()
+        self._ck(self.L.hbtgpu_get_counters(self.h, C.c_uint32(cpu), C.byref(c)))
+        return c.as_dict()
+
+    def carry(self, cpu):
+        c = Carry()
+        self._ck(self.L.hbtgpu_get_carry(self.h, C.c_uint32(cpu), C.byref(c)))
+        return c
+
+    def rows(self, cpu):
+        n = C.c_size_t(0)
+        self._ck(self.L.hbtgpu_get_rows(self.h, C.c_uint32(cpu), C.c_void_p(0), C.c_size_t(0),
+                                        C.byref(n)))
+        out = np.zeros((n.value, self.n_events + 2), np.uint64)
+        if n.value:
+            self._ck(self.L.hbtgpu_get_rows(self.h, C.c_uint32(cpu), _ptr(out),
+                                            C.c_size_t(n.value), C.byref(n)))
+        return out
+
+    def records(self, cpu):
+        n = C.c_size_t(0)
+        z = C.c_void_p(0)
+        self._ck(self.L.hbtgpu_get_records(self.h, C.c_uint32(cpu), z, z, z, C.c_size_t(0),
+                                           C.byref(n)))
+        off = np.zeros(n.value, np.uint64)
+        typ = np.zeros(n.value, np.uint32)
+        siz = np.zeros(n.value, np.uint32)
+        if n.value:
+            self._ck(self.L.hbtgpu_get_records(self.h, C.c_uint32(cpu), _ptr(off), _ptr(typ),
+                                               _ptr(siz), C.c_size_t(n.value), C.byref(n)))
+        return off, typ, siz
+
+    def buckets(self, want_acc=True, want_scaled=True, want_metric=True, want_valid=True):
+        """Returns dict of host arrays: acc[cpu,bucket,n+3], scaled[cpu,bucket,n], metric, valid."""
+        s = (self.max_cpus, self.n_buckets)
+        acc = np.zeros(s + (self.n_events + 3,), np.uint64) if want_acc else None
+        scaled = np.zeros(s + (self.n_events,), np.uint64) if want_scaled else None
+        metric = np.zeros(s + (self.n_metrics,), np.float64) if (
+            want_metric and self.n_metrics) else None
+        valid = np.zeros(s, np.uint32) if want_valid else None
+        self._ck(self.L.hbtgpu_get_buckets_host(self.h, _ptr(acc), _ptr(scaled), _ptr(metric),
+                                                _ptr(valid)))
+        return {"acc": acc, "scaled": scaled, "metric": metric, "valid": valid}
+
+    def bucket_view(self):
+        v = BucketView()
+        self._ck(self.L.hbtgpu_get_buckets_device(self.h, C.byref(v)))
+        return v
+
+    def acc_device(self):
+        p = C.c_void_p()
+        n = C.c_size_t()
+        self._ck(self.L.hbtgpu_acc_device(self.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def stream(self):
+        return self.L.hbtgpu_stream(self.h)
+
+    def stats(self):
+        s = Stats()
+        self._ck(self.L.hbtgpu_get_stats(self.h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+    def head_stub(self, cpu):
+        h = HeadStub()
+        self._ck(self.L.hbtgpu_get_head_stub(self.h, C.c_uint32(cpu), C.byref(h)))
+        return h
+
+    def apply_boundary(self, cpu, prev_tail):
+        self._ck(self.L.hbtgpu_apply_boundary(self.h, C.c_uint32(cpu), C.byref(prev_tail)))
+
+    # ---- elementwise arithmetic
+    def get_count(self, count, te, tr):
+        count, te, tr = _u64(count), _u64(te), _u64(tr)
+        out = np.zeros_like(count)
+        self._ck(self.L.hbtgpu_math_get_count(self.h, _ptr(count), _ptr(te), _ptr(tr), _ptr(out),
+                                              C.c_size_t(count.size)))
+        return out
+
+    def rate(self, num, den):
+        num, den = _u64(num), _u64(den)
+        out = np.zeros(num.shape, np.float64)
+        valid = np.zeros(num.shape, np.uint8)
+        self._ck(self.L.hbtgpu_math_rate(self.h, _ptr(num), _ptr(den), _ptr(out), _ptr(valid),
+                                         C.c_size_t(num.size)))
+        return out, valid.astype(bool)
+
+    def add_reduce(self, vals):
+        vals = _u64(vals)
+        n, k = vals.shape
+        out = np.zeros(n, np.float64)
+        self._ck(self.L.hbtgpu_math_add_reduce(self.h, _ptr(vals), C.c_size_t(k), _ptr(out),
+                                               C.c_size_t(n)))
+        return out
+
+    def tsc_to_ktime(self, tsc):
+        tsc = _u64(tsc)
+        out = np.zeros_like(tsc)
+        self._ck(self.L.hbtgpu_math_tsc_to_ktime(self.h, _ptr(tsc), _ptr(out), C.c_size_t(tsc.size)))
+        return out
+
+    def ktime_to_tsc(self, kt):
+        kt = _u64(kt)
+        out = np.zeros_like(kt)
+        self._ck(self.L.hbtgpu_math_ktime_to_tsc(self.h, _ptr(kt), _ptr(out), C.c_size_t(kt.size)))
+        return out
+
+    def per_second_mega(self, count, tr):
+        count, tr = _u64(count), _u64(tr)
+        out = np.zeros(count.shape, np.float32)
+        self._ck(self.L.hbtgpu_math_per_second_mega(self.h, _ptr(count), _ptr(tr), _ptr(out),
+                                                    C.c_size_t(count.size)))
+        return out
+
+    def running_ratio(self, te, tr):
+        te, tr = _u64(te), _u64(tr)
+        ratio = np.zeros(te.shape, np.float32)
+        ri = np.zeros(te.shape, np.uint64)
+        mux = np.zeros(te.shape, np.uint8)
+        self._ck(self.L.hbtgpu_math_running_ratio(self.h, _ptr(te), _ptr(tr), _ptr(ratio), _ptr(ri),
+                                                  _ptr(mux), C.c_size_t(te.size)))
+        return ratio, ri, mux.astype(bool)

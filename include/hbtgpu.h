@@ -1,0 +1,254 @@
+/*
+ * hbtgpu.h -- C ABI of libhbtgpu.so: B200 (sm_100a) decode + aggregate of hbt
+ * perf_event ring-buffer images.
+ *
+ * This is the drop-in boundary for ONE path of dynolog/hbt: what
+ * PerfEventsGroup<CpuCountSampleGenerator, mode::Sampling>::consume() and its
+ * handlers compute from the bytes of a per-CPU perf_event ring, plus the
+ * GroupReadValues / BuiltinMetrics arithmetic applied to the result.  The
+ * reference has no FFI layer (its boundary is a C++ template surface), so every
+ * entry point cites the reference code it replaces (paths relative to the
+ * dynolog tree).  dynolog_b200/shim/HbtGpuShim.h re-exposes these entry points
+ * with the reference's class shapes; INTEGRATION.md shows the binding.
+ *
+ * Conventions (mirroring hbt):
+ *   - return 0 on success or a NEGATIVE errno (hbt's hot path returns negative
+ *     errno in ssize_t: -EPERM bad record / time regression,
+ *     hbt/src/perf_event/PerfEventsGroup.h:1505,1521 and
+ *     hbt/src/perf_event/PerCpuCountSampleGenerator.h:162).  CUDA failures map to
+ *     -EIO; hbtgpu_last_error() returns the text.  No exceptions cross the ABI.
+ *   - one context = one CUDA device + one stream; not thread-safe; callers
+ *     serialise, exactly as they do around a generator
+ *     (hbt/src/mon/TraceCollector.h:390).
+ *   - all pointers are HOST pointers unless the name says "device".
+ *   - there is NO CPU fallback: without a CUDA device hbtgpu_create fails.
+ */
+#ifndef HBTGPU_H
+#define HBTGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HBTGPU_MAX_EVENTS 64 /* CpuCountSampleGenerator::kMaxNumEvents, PerCpuCountSampleGenerator.h:44 */
+#define HBTGPU_MAX_METRICS 8
+#define HBTGPU_MAX_METRIC_EVENTS 8
+
+/* hbtgpu_config.flags */
+#define HBTGPU_F_FORCE_EXACT 0x1u   /* always run the exact (sequential-resolver) path */
+#define HBTGPU_F_FORCE_GENERAL 0x2u /* always run pointer-jumping, never the contiguous-chain shortcut */
+#define HBTGPU_F_EXTERNAL_CARRY 0x4u /* shard mode: predecessor of each stream lives on another GPU (see hbtgpu_get_stubs) */
+
+/* metric kinds (hbtgpu_metric.kind) */
+#define HBTGPU_METRIC_RATE 1 /* getRateReducer, hbt/src/perf_event/BuiltinMetrics.cpp:102-118 */
+#define HBTGPU_METRIC_ADD 2  /* getAddReducer (int accumulator), BuiltinMetrics.cpp:88-97 */
+#define HBTGPU_METRIC_PER_SECOND_MEGA 3 /* mips / mega_cycles_per_second, dynolog/src/PerfMonitor.cpp:63-72 */
+
+typedef struct hbtgpu_ctx hbtgpu_ctx;
+
+/* One derived metric over the multiplex-scaled counts of a bucket: the device
+ * form of MetricDesc::reducer (hbt/src/perf_event/Metrics.h:46-214) as applied
+ * by GroupReadValues::getReducedCount (PerfEventsGroup.h:502-511). */
+typedef struct {
+  uint32_t kind;
+  uint32_t n_idx;                          /* RATE: 2 (num, denom); PER_SECOND_MEGA: 1 */
+  uint32_t idx[HBTGPU_MAX_METRIC_EVENTS];  /* event indices */
+} hbtgpu_metric;
+
+typedef struct {
+  int32_t device;      /* CUDA ordinal */
+  uint32_t n_events;   /* events in the group = nr of every SAMPLE (kNumEvents, PerCpuCountSampleGenerator.h:47) */
+  uint64_t tsc_mask;   /* bit i: event i has EventValueTransforms::TscToKernelTime (hbt/src/perf_event/PmuEvent.h:248-256) */
+  uint32_t time_shift; /* perf_event_mmap_page time_shift/mult/zero = TscConversionParams (PerfEventsGroup.h:829-841) */
+  uint32_t time_mult;
+  uint64_t time_zero;
+  uint32_t max_cpus;   /* streams: cpu ids 0..max_cpus-1 (kMaxCpus = 512, hbt/src/common/System.h:204) */
+  uint32_t n_buckets;  /* time buckets per cpu (>= 1) */
+  uint64_t t0;         /* bucket b covers [t0 + b*bucket_ns, t0 + (b+1)*bucket_ns) */
+  uint64_t bucket_ns;  /* >= 1 */
+  uint64_t arena_bytes; /* device capacity for submitted images (bytes) */
+  uint32_t n_metrics;
+  uint32_t flags;
+  hbtgpu_metric metrics[HBTGPU_MAX_METRICS];
+} hbtgpu_config;
+
+/* Generator state that crosses image boundaries: CpuCountSampleGenerator's
+ * count_.tstamp / last_[] (PerCpuCountSampleGenerator.h:222-228), plus the
+ * previous sample's time_enabled/time_running for the bucket dTE/dTR sums.
+ * valid=1,last=0 is the state enableImpl() leaves (:91-106); valid=0 is the
+ * state after a PERF_RECORD_LOST (:110-124). */
+typedef struct {
+  uint64_t valid;
+  uint64_t tstamp;
+  uint64_t te, tr;
+  uint64_t last[HBTGPU_MAX_EVENTS]; /* already transformed values */
+} hbtgpu_carry;
+
+/* Per-cpu counters: the 11 getNumRecord*() of PerfEventsGroup.h:791-824 (same
+ * order as the members :887-897) and the generator's bookkeeping. */
+typedef struct {
+  uint64_t lost;       /* SUM of num_lost, not #LOST records (:1448) */
+  uint64_t comm, exit, throttle, unthrottle, fork, sample, read, aux, itrace_start,
+      switch_cpu_wide;
+  uint64_t num_records;                /* every record walked, any type (:1569) */
+  uint64_t num_unknown_count_interval; /* PerCpuCountSampleGenerator.h:152 */
+  uint64_t num_rows;                   /* rows written to the output ring (:182) */
+  uint64_t rows_out_of_range;          /* rows whose bucket is outside [0, n_buckets) */
+  int64_t err;                         /* 0 or the negative errno consume() would return */
+  uint64_t err_offset;                 /* stream byte offset of the record consume() stalls on */
+  uint64_t last_tstamp;                /* getLastTimeStamp(), PerCpuCountSampleGenerator.h:209-211 */
+} hbtgpu_counters;
+
+/* Layout of the result tensors (row-major, packed):
+ *   acc    [max_cpus][n_buckets][n_events+3] u64: sum delta[e], sum dTE, sum dTR, n_rows
+ *   scaled [max_cpus][n_buckets][n_events]   u64: GroupReadValues::getCount on the accumulated triple
+ *   metric [max_cpus][n_buckets][n_metrics]  f64
+ *   valid  [max_cpus][n_buckets]             u32 bitmask: bit m set when metric m has a value
+ *          (std::optional has_value of the reducer) */
+typedef struct {
+  const uint64_t* acc;
+  const uint64_t* scaled;
+  const double* metric;
+  const uint32_t* valid;
+  uint32_t max_cpus, n_buckets, n_events, n_metrics;
+} hbtgpu_bucket_view;
+
+/* ---- lifetime --------------------------------------------------------------------- */
+
+/* Allocates the device arena, result tensors and a stream.  Replaces the
+ * constructor + open() of PerCpuCountSampleGenerator
+ * (PerCpuCountSampleGenerator.h:234-294) for the purposes of this path. */
+int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out);
+void hbtgpu_destroy(hbtgpu_ctx* ctx);
+const char* hbtgpu_last_error(const hbtgpu_ctx* ctx); /* ctx may be NULL: error of the last failed create */
+
+/* Initial generator state per cpu; default is valid=0 (as after a LOST).
+ * Replaces enableImpl() (PerCpuCountSampleGenerator.h:91-106), with now()
+ * passed explicitly. */
+int hbtgpu_set_carry(hbtgpu_ctx* ctx, uint32_t cpu, const hbtgpu_carry* carry);
+
+/* ---- input ------------------------------------------------------------------------- */
+
+/* Append one ring image of `cpu`: the bytes PerfEventsGroup::onCpuDataBufferRead
+ * hands to its callback (PerfEventsGroup.h:1592-1637, RbDataSlices :45-62):
+ * `first` then the optional wrapped `second` slice.  The image must start and
+ * end on record boundaries (data_tail .. data_head).  Images of one cpu are
+ * decoded in submission order as one stream.  The bytes are copied (H2D) before
+ * the call returns, so the caller may consume the ring immediately. */
+int hbtgpu_submit_image(hbtgpu_ctx* ctx, uint32_t cpu, const void* first, size_t n1,
+                        const void* second, size_t n2);
+
+/* Same, for an image that already lives in device memory (copied D2D). */
+int hbtgpu_submit_image_device(hbtgpu_ctx* ctx, uint32_t cpu, const void* device_ptr, size_t n);
+
+/* Forget all submitted images, counters and bucket sums (carry-in is kept as
+ * last set).  With keep_carry != 0 each cpu's carry-in becomes the carry-out
+ * of the previous run, i.e. the next images continue the same streams. */
+int hbtgpu_reset(hbtgpu_ctx* ctx, int keep_carry);
+
+/* ---- the hot path ------------------------------------------------------------------ */
+
+/* Decode every submitted image and aggregate: the device form of calling
+ * consume() until -ENODATA on every cpu (PerCpuSampleGeneratorBase::accumUntil,
+ * hbt/src/perf_event/PerCpuSampleGeneratorBase.h:69-94) followed by the bucket
+ * sums, multiplex scaling and metric reducers.  Asynchronous on the context's
+ * stream; may be called repeatedly on the same images (results are recomputed).
+ * A per-cpu decode error does not fail the call: see hbtgpu_counters.err. */
+int hbtgpu_run(hbtgpu_ctx* ctx);
+int hbtgpu_sync(hbtgpu_ctx* ctx);
+
+/* ---- results ----------------------------------------------------------------------- */
+
+/* getNumRecord*(), getLastTimeStamp(), getNumEntries() of one cpu. */
+int hbtgpu_get_counters(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_counters* out);
+/* State after the last record: feed to hbtgpu_set_carry of the next window. */
+int hbtgpu_get_carry(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_carry* out);
+
+/* Rows of one cpu as CpuCountSampleGenerator writes them to its output ring:
+ * [tstamp, duration, delta_0..n-1] u64 (PerCpuCountSampleGenerator.h:34,165-182;
+ * consumer callback shape hbt/src/mon/TraceMonitor.h:35-108).  *n_rows is
+ * set to the number available; at most `cap_rows` are copied. */
+int hbtgpu_get_rows(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* rows, size_t cap_rows, size_t* n_rows);
+
+/* Record table of one cpu: (stream byte offset, type, size) of every record the
+ * walk visits, in order -- what consume()'s loop steps through (:1415-1572). */
+int hbtgpu_get_records(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* off, uint32_t* type, uint32_t* size,
+                       size_t cap, size_t* n_records);
+
+/* Bucket tensors.  _device returns pointers into the context's device memory
+ * (valid until destroy; contents change on run/reset); _host copies them into
+ * caller buffers (any may be NULL). */
+int hbtgpu_get_buckets_device(hbtgpu_ctx* ctx, hbtgpu_bucket_view* view);
+int hbtgpu_get_buckets_host(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scaled, double* metric,
+                            uint32_t* valid);
+
+/* Re-run only the derive step (scale + metrics) from the current acc tensor,
+ * e.g. after partial aggregates of other GPUs were summed into it. */
+int hbtgpu_derive(hbtgpu_ctx* ctx);
+
+/* ---- multi-GPU (time-window sharding) ---------------------------------------------- */
+
+/* With HBTGPU_F_EXTERNAL_CARRY the first SAMPLE of each stream has its
+ * predecessor on the GPU that holds the previous time window.  After run, each
+ * rank exports per cpu a head stub (first SAMPLE and whether a LOST precedes
+ * it) and a tail stub (state after the last record); ranks exchange stubs
+ * (all_gather) and call hbtgpu_apply_boundary with the tail of the previous
+ * non-empty rank to add the one row that straddles the shard boundary. */
+typedef struct {
+  uint64_t has_sample;  /* stream contains at least one SAMPLE */
+  uint64_t lost_before; /* a LOST precedes the first SAMPLE */
+  uint64_t tstamp, te, tr;
+  uint64_t value[HBTGPU_MAX_EVENTS]; /* transformed values of the first SAMPLE */
+} hbtgpu_head_stub;
+
+int hbtgpu_get_head_stub(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_head_stub* out);
+/* prev_tail: carry-out of the stream's previous shard (hbtgpu_get_carry there). */
+int hbtgpu_apply_boundary(hbtgpu_ctx* ctx, uint32_t cpu, const hbtgpu_carry* prev_tail);
+/* Device address/size of the acc tensor, for a collective (NCCL all-reduce over u64 as i64). */
+int hbtgpu_acc_device(hbtgpu_ctx* ctx, void** device_ptr, size_t* bytes);
+/* The CUDA stream the context launches on (a cudaStream_t). */
+void* hbtgpu_stream(hbtgpu_ctx* ctx);
+
+/* ---- elementwise arithmetic of the path (host in, host out; computed on the GPU) --- */
+
+/* GroupReadValues::getCount (PerfEventsGroup.h:467-481). */
+int hbtgpu_math_get_count(hbtgpu_ctx* ctx, const uint64_t* count, const uint64_t* te,
+                          const uint64_t* tr, uint64_t* out, size_t n);
+/* getRateReducer (BuiltinMetrics.cpp:102-118); valid[i]=0 where it returns nullopt. */
+int hbtgpu_math_rate(hbtgpu_ctx* ctx, const uint64_t* num, const uint64_t* den, double* out,
+                     uint8_t* valid, size_t n);
+/* getAddReducer (BuiltinMetrics.cpp:88-97) over n rows of k values. */
+int hbtgpu_math_add_reduce(hbtgpu_ctx* ctx, const uint64_t* vals, size_t k, double* out, size_t n);
+/* kernelTimeFromTsc / tscFromKernelTime (PerfEventsGroup.h:1645-1678) with the context's params. */
+int hbtgpu_math_tsc_to_ktime(hbtgpu_ctx* ctx, const uint64_t* tsc, uint64_t* out, size_t n);
+int hbtgpu_math_ktime_to_tsc(hbtgpu_ctx* ctx, const uint64_t* kt, uint64_t* out, size_t n);
+/* float(double(count)*1e3/double(time_running)) (dynolog/src/PerfMonitor.cpp:63-72). */
+int hbtgpu_math_per_second_mega(hbtgpu_ctx* ctx, const uint64_t* count, const uint64_t* tr,
+                                float* out, size_t n);
+/* getRunningRatio / getRunningRatioInteger<100> / hasMultiplexing (PerfEventsGroup.h:513-540). */
+int hbtgpu_math_running_ratio(hbtgpu_ctx* ctx, const uint64_t* te, const uint64_t* tr, float* ratio,
+                              uint64_t* ratio_int100, uint8_t* has_mux, size_t n);
+
+/* ---- introspection ------------------------------------------------------------------ */
+
+typedef struct {
+  uint64_t image_bytes;   /* algorithmic bytes: sum of image sizes */
+  uint32_t n_chunks;      /* CTAs of the decode kernel */
+  uint32_t exact_runs;    /* times the last run fell back to the exact path (0 or 1) */
+  uint32_t kernel_launches; /* kernels launched by the last hbtgpu_run */
+  float last_run_ms;      /* CUDA-event time of the last hbtgpu_run (after hbtgpu_sync) */
+  float last_decode_ms;   /* ... of its decode+aggregate kernel alone */
+  uint32_t exact_reason;  /* diagnostics: why the speculative pass was disproved (0: it held) */
+  uint32_t exact_chunk;   /* ... and the first chunk that reported it */
+} hbtgpu_stats;
+int hbtgpu_get_stats(hbtgpu_ctx* ctx, hbtgpu_stats* out);
+
+const char* hbtgpu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HBTGPU_H */
