@@ -32,7 +32,11 @@ struct hbtgpu_ctx {
   hbtgpu_config cfg;
   int device = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev_run0 = nullptr, ev_run1 = nullptr, ev_dec0 = nullptr, ev_dec1 = nullptr;
+  cudaEvent_t ev_run0 = nullptr, ev_run1 = nullptr;
+  // one event pair per hbtgpu_run around the decode+aggregate kernel, harvested at sync
+  static constexpr int kEvRing = 128;
+  cudaEvent_t ev_dec0[kEvRing] = {nullptr}, ev_dec1[kEvRing] = {nullptr};
+  int ev_pending = 0;
   std::string err;
 
   // device memory
@@ -228,6 +232,13 @@ Params make_params(hbtgpu_ctx* ctx) {
   P.time_mult = ctx->cfg.time_mult;
   P.force_general = (ctx->cfg.flags & HBTGPU_F_FORCE_GENERAL) ? 1 : 0;
   P.external_carry = (ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY) ? 1 : 0;
+  {
+    const unsigned __int128 range = static_cast<unsigned __int128>(ctx->cfg.n_buckets) * ctx->cfg.bucket_ns;
+    P.range_ns = range > ~0ull ? ~0ull : static_cast<uint64_t>(range);
+    P.inv_bucket = 1.0 / static_cast<double>(ctx->cfg.bucket_ns);
+    const uint64_t b = ctx->cfg.bucket_ns;
+    P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
+  }
   return P;
 }
 
@@ -387,8 +398,10 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   CKC(cudaEventCreate(&ctx->ev_run0));
   CKC(cudaEventCreate(&ctx->ev_run1));
-  CKC(cudaEventCreate(&ctx->ev_dec0));
-  CKC(cudaEventCreate(&ctx->ev_dec1));
+  for (int i = 0; i < hbtgpu_ctx::kEvRing; ++i) {
+    CKC(cudaEventCreate(&ctx->ev_dec0[i]));
+    CKC(cudaEventCreate(&ctx->ev_dec1[i]));
+  }
   const uint32_t ns = cfg->max_cpus, n = cfg->n_events;
   ctx->n_cells = static_cast<uint64_t>(ns) * cfg->n_buckets;
   ctx->acc_words = ctx->n_cells * (n + 3);
@@ -434,8 +447,12 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
-  for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1, ctx->ev_dec0, ctx->ev_dec1})
+  for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
     if (e) cudaEventDestroy(e);
+  for (int i = 0; i < hbtgpu_ctx::kEvRing; ++i) {
+    if (ctx->ev_dec0[i]) cudaEventDestroy(ctx->ev_dec0[i]);
+    if (ctx->ev_dec1[i]) cudaEventDestroy(ctx->ev_dec1[i]);
+  }
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -542,13 +559,14 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   // streams without images keep their carry: carry_out := carry_in
   CK(cudaMemcpyAsync(ctx->d_carry_out, ctx->d_carry_in, ns * sizeof(hbtgpu_carry),
                      cudaMemcpyDeviceToDevice, ctx->stream));
+  const bool timed = ctx->ev_pending < hbtgpu_ctx::kEvRing;
   if (nc) {
-    CK(cudaEventRecord(ctx->ev_dec0, ctx->stream));
+    if (timed) CK(cudaEventRecord(ctx->ev_dec0[ctx->ev_pending], ctx->stream));
     if (!force_exact) {
       k_decode<true, MODE_AGG><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
       ++launches;
     }
-    CK(cudaEventRecord(ctx->ev_dec1, ctx->stream));
+    if (timed) CK(cudaEventRecord(ctx->ev_dec1[ctx->ev_pending++], ctx->stream));
     if (!force_exact) {
       k_verify<<<static_cast<unsigned>((nc + 255) / 256), 256, 0, ctx->stream>>>(P);
       ++launches;
@@ -558,9 +576,6 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
     k_decode<false, MODE_AGG><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
     launches += 3;
     CK(cudaGetLastError());
-  } else {
-    CK(cudaEventRecord(ctx->ev_dec0, ctx->stream));
-    CK(cudaEventRecord(ctx->ev_dec1, ctx->stream));
   }
   if (int r = launch_derive(ctx)) return r;
   ++launches;
@@ -576,10 +591,15 @@ int hbtgpu_sync(hbtgpu_ctx* ctx) {
   if (!ctx) return -EINVAL;
   CK(cudaSetDevice(ctx->device));
   CK(cudaStreamSynchronize(ctx->stream));
-  if (ctx->ran) {
-    CK(cudaEventElapsedTime(&ctx->stats.last_run_ms, ctx->ev_run0, ctx->ev_run1));
-    CK(cudaEventElapsedTime(&ctx->stats.last_decode_ms, ctx->ev_dec0, ctx->ev_dec1));
+  if (ctx->ran) CK(cudaEventElapsedTime(&ctx->stats.last_run_ms, ctx->ev_run0, ctx->ev_run1));
+  for (int i = 0; i < ctx->ev_pending; ++i) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, ctx->ev_dec0[i], ctx->ev_dec1[i]));
+    ctx->stats.last_decode_ms = ms;
+    ctx->stats.decode_ms_sum += ms;
+    ctx->stats.decode_runs += 1;
   }
+  ctx->ev_pending = 0;
   return 0;
 }
 

@@ -150,6 +150,11 @@ struct Params {
   uint32_t n_events, n_buckets, n_chunks, n_streams;
   uint32_t time_shift, time_mult;
   uint32_t force_general, external_carry;
+  // bucket index = (ts - t0) / bucket_ns without a 64-bit division (set by the host)
+  uint64_t range_ns;    // n_buckets * bucket_ns, saturated
+  double inv_bucket;    // 1.0 / bucket_ns
+  uint32_t bucket_shift;  // log2(bucket_ns) when it is a power of two, else 0xFFFFFFFF
+  uint32_t pad;
 };
 
 // ------------------------------------------------------------------------------------
@@ -502,8 +507,15 @@ __device__ __forceinline__ uint32_t scout_start(Smem& s, const uint64_t* buf, ui
 
 __device__ __forceinline__ uint32_t bucket_of(const Params& P, uint64_t ts) {
   if (ts < P.t0) return BKT_OOR;
-  const uint64_t q = (ts - P.t0) / P.bucket_ns;
-  return q < P.n_buckets ? static_cast<uint32_t>(q) : BKT_OOR;
+  const uint64_t d = ts - P.t0;
+  if (d >= P.range_ns) return BKT_OOR;
+  if (P.bucket_shift != 0xFFFFFFFFu) return static_cast<uint32_t>(d >> P.bucket_shift);
+  // q < 2^32 here, so the double estimate is off by at most one; fix it up exactly
+  uint64_t q = __double2ull_rz(__dmul_rn(__ull2double_rn(d), P.inv_bucket));
+  const uint64_t r = d - q * P.bucket_ns;
+  if (static_cast<int64_t>(r) < 0) --q;
+  else if (r >= P.bucket_ns) ++q;
+  return static_cast<uint32_t>(q);
 }
 
 __device__ __forceinline__ uint64_t xform(const Params& P, uint32_t e, uint64_t v) {
@@ -746,6 +758,84 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
   __syncthreads();
 }
 
+// Fast path for a tile in which every record from `entry` on is a SAMPLE of the configured
+// group (type 9, size 40+8n, nr == n).  Then record j sits at entry + j*S and each equality
+// test IS the chain link (record j's size carries the walk to record j+1), so the chain is
+// proven without parsing the other words; the predecessor of sample j is j-1 and there is no
+// LOST, so no scan is needed either.  Returns false (nothing touched) if the tile is not
+// uniform; the caller then takes the general path.
+__device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uint64_t* buf,
+                                             uint32_t wt, uint32_t entry, const TileCtx& tc,
+                                             uint32_t& exit_word) {
+  const uint32_t n = P.n_events;
+  const uint32_t S = 5 + n;  // words per SAMPLE
+  const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
+  const uint32_t K = (wt - entry + S - 1) / S;  // records whose header lies inside the tile
+  int ok = 1;
+  for (uint32_t j = threadIdx.x; j < K; j += NT) {
+    const uint32_t p = entry + j * S;
+    // misc (bits 32..47) is free; type and size must match, and so must nr
+    if ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + 2] != n) ok = 0;
+  }
+  if (!__syncthreads_and(ok)) return false;
+
+  const bool link0 = s.c_valid != 0 && s.c_gap == 0;
+  const uint64_t c_ts = s.c_ts;
+  for (uint32_t j = threadIdx.x; j < K; j += NT) {
+    const uint32_t p = entry + j * S;
+    const uint64_t ts = buf[p + 1];
+    const uint64_t pts = j ? buf[p - S + 1] : c_ts;
+    if ((j || link0) && pts > ts) atomicMin(&s.tile_err, p);  // time regression (gen :156-163)
+    s.u.de.bkt[j] = bucket_of(P, ts);
+  }
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j < K; j += NT) {
+    if (j == 0 && !link0) continue;  // re-base: no row (gen :135-154)
+    const uint32_t p = entry + j * S;
+    const uint32_t bk = s.u.de.bkt[j];
+    const bool pred_cancel = j > 0 && (j > 1 || link0) && s.u.de.bkt[j - 1] == bk;
+    const bool next_cancel = j + 1 < K && s.u.de.bkt[j + 1] == bk;
+    if (bk == BKT_OOR) {
+      atomicAdd(&s.cnt[C_OOR], 1u);
+    } else if (!pred_cancel || !next_cancel) {
+      uint64_t* base = P.acc + (static_cast<uint64_t>(tc.stream) * P.n_buckets + bk) * (n + 3);
+      const uint64_t* cur = buf + p + 3;       // te, tr, value[0..n)
+      const uint64_t* prv = buf + p - S + 3;   // same fields of sample j-1 (j > 0)
+      const uint64_t fp = next_cancel ? 0 : ~0ull, fm = pred_cancel ? 0 : ~0ull;
+      for (uint32_t e = 0; e < n; ++e) {
+        const uint64_t plus = xform(P, e, cur[2 + e]);
+        const uint64_t minus = j ? xform(P, e, prv[2 + e]) : s.c_last[e];
+        red_add(base + e, (plus & fp) - (minus & fm));
+      }
+      red_add(base + n, (cur[0] & fp) - ((j ? prv[0] : s.c_te) & fm));
+      red_add(base + n + 1, (cur[1] & fp) - ((j ? prv[1] : s.c_tr) & fm));
+      red_add(base + n + 2, (static_cast<uint64_t>(j) & fp) - ((static_cast<uint64_t>(j) - 1) & fm));
+    }
+  }
+  if (threadIdx.x == 0) {
+    s.cnt[C_SAMPLE] += K;
+    s.cnt[C_RECORDS] += K;
+    s.cnt[C_ROWS] += link0 ? K : K - 1;
+    s.cnt[C_UNKNOWN] += link0 ? 0 : 1;
+  }
+  __syncthreads();  // all reads of the carry are done
+  {
+    const uint32_t p = entry + (K - 1) * S;
+    for (uint32_t e = threadIdx.x; e < n; e += NT) s.c_last[e] = xform(P, e, buf[p + 5 + e]);
+    if (threadIdx.x == 0) {
+      s.c_ts = buf[p + 1];
+      s.c_te = buf[p + 3];
+      s.c_tr = buf[p + 4];
+      s.c_valid = 1;
+      s.c_gap = 0;
+      s.c_last_off = tc.tile_abs + 8ull * p;
+    }
+  }
+  __syncthreads();
+  exit_word = entry + K * S;
+  return true;
+}
+
 // Initialise the carry from a predecessor SAMPLE in global memory / the stream carry-in.
 __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t stream, uint64_t pred,
                                            uint32_t gap) {
@@ -890,23 +980,37 @@ __global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
     tma_load_1d(s.data[t & 1], P.arena + off, bytes, &s.bar[t & 1]);
   };
   const bool any_work = next_abs < chunk_end_abs;
-  if (any_work && threadIdx.x == 0) issue(0);
+  uint32_t n_issued = 0, n_waited = 0;
+  if (any_work) {
+    if (threadIdx.x == 0) issue(0);
+    n_issued = 1;
+  }
   for (uint32_t t = 0; any_work && t < n_tiles; ++t) {
     const uint64_t tile_abs = chunk_abs + static_cast<uint64_t>(t) * TILE_BYTES;
     if (tile_abs >= chunk_end_abs) break;
-    if (threadIdx.x == 0 && t + 1 < n_tiles && tile_abs + TILE_BYTES < chunk_end_abs) issue(t + 1);
+    if (t + 1 < n_tiles && tile_abs + TILE_BYTES < chunk_end_abs) {
+      if (threadIdx.x == 0) issue(t + 1);
+      ++n_issued;
+    }
     mbar_wait(&s.bar[t & 1], phase[t & 1]);
     phase[t & 1] ^= 1;
+    ++n_waited;
     const uint64_t* buf = s.data[t & 1];
     const uint32_t wt = static_cast<uint32_t>(umin64(TILE_BYTES, chunk_end_abs - tile_abs) / 8);
     if (next_abs < tile_abs + 8ull * wt) {
       const uint32_t entry = static_cast<uint32_t>((next_abs - tile_abs) / 8);
-      const uint32_t K = classify(s, buf, wt);
-      recover_chain(s, buf, wt, K, entry, P.force_general != 0);
       tc.tile_abs = tile_abs;
       tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base);
-      const uint32_t term_kind = s.term_kind, term_tgt = s.term_tgt;
-      decode_tile<false, MODE>(s, P, buf, K, tc);
+      uint32_t term_kind = 0, term_tgt = 0;
+      bool done = false;
+      if (MODE == MODE_AGG && !P.force_general) done = uniform_tile(s, P, buf, wt, entry, tc, term_tgt);
+      if (!done) {
+        const uint32_t K = classify(s, buf, wt);
+        recover_chain(s, buf, wt, K, entry, P.force_general != 0);
+        term_kind = s.term_kind;
+        term_tgt = s.term_tgt;
+        decode_tile<false, MODE>(s, P, buf, K, tc);
+      }
       const uint64_t tgt_abs = tile_abs + 8ull * term_tgt;
       if (term_kind != 0 || s.tile_err != 0xFFFFFFFFu) {
         bad = term_kind != 0 ? WHY_TILE_DEAD : WHY_TILE_ERR;
@@ -920,6 +1024,8 @@ __global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
     }
     __syncthreads();  // buffer (t&1) is free for tile t+2
   }
+  // never exit with a bulk copy still in flight into this CTA's shared memory
+  if (n_waited < n_issued) mbar_wait(&s.bar[n_waited & 1], phase[n_waited & 1]);
 
   // ---- publish ----
   if (threadIdx.x == 0) {
@@ -1039,7 +1145,7 @@ __global__ void __launch_bounds__(RES_WARPS * 32) k_resolve(const Params P) {
             io.limit = ~0ull;
             ++ch;
           }
-          bool bad = size < 8 || (size & 7) || pos + size > im.len;  // fences, see oracle
+          bool bad = size < 8 || (size & 7) || pos + size > im.len;  // fences, see DESIGN.md
           uint64_t nr = 0, ts = 0;
           if (!bad && (type == REC_SAMPLE || type == REC_READ)) {
             // fields may lie beyond the staged window only for oversized records

@@ -73,7 +73,8 @@ class Stats(C.Structure):
     _fields_ = [("image_bytes", C.c_uint64), ("n_chunks", C.c_uint32), ("exact_runs", C.c_uint32),
                 ("kernel_launches", C.c_uint32), ("last_run_ms", C.c_float),
                 ("last_decode_ms", C.c_float), ("exact_reason", C.c_uint32),
-                ("exact_chunk", C.c_uint32)]
+                ("exact_chunk", C.c_uint32), ("decode_ms_sum", C.c_double),
+                ("decode_runs", C.c_uint64)]
 
 
 # every symbol include/hbtgpu.h declares (tests check that the library exports them all)

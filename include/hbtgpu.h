@@ -243,6 +243,8 @@ typedef struct {
   float last_decode_ms;   /* ... of its decode+aggregate kernel alone */
   uint32_t exact_reason;  /* diagnostics: why the speculative pass was disproved (0: it held) */
   uint32_t exact_chunk;   /* ... and the first chunk that reported it */
+  double decode_ms_sum;   /* CUDA-event time of the decode+aggregate kernel, summed over ... */
+  uint64_t decode_runs;   /* ... this many runs since create (harvested at hbtgpu_sync) */
 } hbtgpu_stats;
 int hbtgpu_get_stats(hbtgpu_ctx* ctx, hbtgpu_stats* out);
 
