@@ -238,6 +238,8 @@ Params make_params(hbtgpu_ctx* ctx) {
     P.inv_bucket = 1.0 / static_cast<double>(ctx->cfg.bucket_ns);
     const uint64_t b = ctx->cfg.bucket_ns;
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
+    const uint64_t S = 5ull + ctx->cfg.n_events;
+    P.s_magic = static_cast<uint32_t>(((1ull << 32) + S - 1) / S);
   }
   return P;
 }

@@ -41,8 +41,12 @@ constexpr int STAGE_BYTES = TILE_BYTES + OV_BYTES;
 constexpr int STAGE_WORDS = STAGE_BYTES / 8;
 constexpr int HALO_BYTES = 2048;
 constexpr int HALO_WORDS = HALO_BYTES / 8;
-constexpr int MAXC = TILE_WORDS;  // worst case: every word is a candidate header
-constexpr int WPT = TILE_WORDS / NT;  // words classified per thread (8)
+// The general path (classify + pointer jumping + scan) works on sub-tiles of GT_WORDS words so
+// that its per-candidate arrays stay small (shared memory decides how many CTAs fit on an SM).
+constexpr int GT_WORDS = 1024;
+constexpr int MAXC = GT_WORDS;    // worst case: every word is a candidate header
+constexpr int WPT = GT_WORDS / NT;  // words classified per thread (4)
+static_assert(WPT * NWARP == 32, "classify() scans one (round, warp) count per lane");
 
 constexpr uint16_t IDX_NONE = 0xFFFF;
 constexpr uint16_t NX_EXIT = 0xFFFF;  // chain leaves the tile
@@ -154,7 +158,7 @@ struct Params {
   uint64_t range_ns;    // n_buckets * bucket_ns, saturated
   double inv_bucket;    // 1.0 / bucket_ns
   uint32_t bucket_shift;  // log2(bucket_ns) when it is a power of two, else 0xFFFFFFFF
-  uint32_t pad;
+  uint32_t s_magic;       // ceil(2^32 / (5 + n_events)): x / S == (x * s_magic) >> 32 for x < 2^16
 };
 
 // ------------------------------------------------------------------------------------
@@ -235,13 +239,20 @@ __device__ __forceinline__ uint64_t get_count(uint64_t count, uint64_t te, uint6
 // ------------------------------------------------------------------------------------
 // shared memory of k_decode
 
+struct Carry {
+  uint64_t ts, te, tr;                // previous SAMPLE: time, time_enabled, time_running
+  uint64_t last[HBTGPU_MAX_EVENTS];   // ... and its (transformed) values
+  uint64_t last_off;                  // arena offset of that SAMPLE (or in_pred)
+  uint32_t valid, gap;                // a predecessor exists / a LOST came after it
+};
+
 struct __align__(128) Smem {
   uint64_t data[2][STAGE_WORDS];  // TMA destinations (16-byte aligned)
   uint16_t pos[MAXC];             // candidate word positions, ascending
   union {
     struct {                      // chain phase
       uint16_t jump[2][MAXC];
-      uint16_t map[TILE_WORDS];   // word -> candidate index
+      uint16_t map[GT_WORDS];     // word -> candidate index
     } ch;
     struct {                      // decode phase
       uint32_t bkt[MAXC];
@@ -250,11 +261,9 @@ struct __align__(128) Smem {
   } u;
   uint16_t next[MAXC];
   uint8_t fl[MAXC];
-  // carry (generator state up to the current tile)
-  uint64_t c_ts, c_te, c_tr;
-  uint64_t c_last[HBTGPU_MAX_EVENTS];
-  uint64_t c_last_off;            // arena offset of the last SAMPLE so far (or in_pred)
-  uint32_t c_valid, c_gap;
+  // carry = generator state up to the current tile.  Two copies: the uniform fast path reads
+  // one and writes the other, which saves a block barrier per tile.
+  Carry c[2];
   // scratch
   uint64_t bar[2];
   uint32_t wcnt[WPT * NWARP + 1];
@@ -330,17 +339,15 @@ __device__ __forceinline__ uint32_t classify(Smem& s, const uint64_t* buf, uint3
   }
   __syncthreads();
   if (warp == 0) {
-    // exclusive scan of the 64 counts in (round, warp) order: 2 per lane
-    const uint32_t v0 = s.wcnt[2 * lane], v1 = s.wcnt[2 * lane + 1];
-    uint32_t incl = v0 + v1;
+    // exclusive scan of the 32 counts in (round, warp) order: one per lane
+    const uint32_t v = s.wcnt[lane];
+    uint32_t incl = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
       if (lane >= d) incl += y;
     }
-    const uint32_t excl = incl - (v0 + v1);
-    s.wcnt[2 * lane] = excl;
-    s.wcnt[2 * lane + 1] = excl + v0;
+    s.wcnt[lane] = incl - v;
     if (lane == 31) s.wcnt[WPT * NWARP] = incl;
   }
   __syncthreads();
@@ -523,6 +530,9 @@ __device__ __forceinline__ uint64_t xform(const Params& P, uint32_t e, uint64_t 
 }
 
 __device__ __forceinline__ void red_add(uint64_t* p, uint64_t v) {
+#ifdef HBT_DEBUG_NO_RED
+  if (v == 0x123456789ull)
+#endif
   atomicAdd(reinterpret_cast<unsigned long long*>(p), static_cast<unsigned long long>(v));
 }
 
@@ -538,7 +548,8 @@ struct TileCtx {
 // counters and (if AGG) the bucket sums.  SCOUT: only the carry is updated.
 template <bool SCOUT, int MODE>
 __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint64_t* buf,
-                                            uint32_t K, TileCtx& tc) {
+                                            uint32_t K, TileCtx& tc, uint32_t cur) {
+  Carry& C = s.c[cur];
   const uint32_t n = P.n_events;
   const uint32_t ipt = (K + NT - 1) / NT;  // candidates per thread (blocked)
   const uint32_t j0 = threadIdx.x * ipt;
@@ -591,8 +602,8 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
   block_scan(s, a, b, ex_a, ex_b, tot_a, tot_b);  // also orders the fl/next writes above
 
   // pass 1: link every sample to its predecessor
-  const bool c_valid = s.c_valid != 0, c_gap = s.c_gap != 0;
-  const uint64_t c_ts = s.c_ts;
+  const bool c_valid = C.valid != 0, c_gap = C.gap != 0;
+  const uint64_t c_ts = C.ts;
   uint32_t run_a = ex_a, run_b = ex_b;
   uint32_t n_rows = 0, n_unknown = 0, n_sample = 0;
   for (uint32_t j = j0; j < j1; ++j) {
@@ -698,13 +709,13 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
                 uint64_t plus, minus;
                 if (e < n) {
                   plus = xform(P, e, buf[p + 5 + e]);
-                  minus = (pj != IDX_NONE) ? xform(P, e, buf[pp + 5 + e]) : s.c_last[e];
+                  minus = (pj != IDX_NONE) ? xform(P, e, buf[pp + 5 + e]) : C.last[e];
                 } else if (e == n) {
                   plus = buf[p + 3];
-                  minus = (pj != IDX_NONE) ? buf[pp + 3] : s.c_te;
+                  minus = (pj != IDX_NONE) ? buf[pp + 3] : C.te;
                 } else if (e == n + 1) {
                   plus = buf[p + 4];
-                  minus = (pj != IDX_NONE) ? buf[pp + 4] : s.c_tr;
+                  minus = (pj != IDX_NONE) ? buf[pp + 4] : C.tr;
                 } else {
                   plus = ord;
                   minus = static_cast<uint64_t>(ord) - 1;
@@ -716,13 +727,13 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
           } else {  // MODE_EMIT: the row as CpuCountSampleGenerator writes it (:165-182)
             const uint32_t pp = (pj != IDX_NONE) ? s.pos[pj] : 0;
             const uint64_t ts = buf[p + 1];
-            const uint64_t pts = (pj != IDX_NONE) ? buf[pp + 1] : s.c_ts;
+            const uint64_t pts = (pj != IDX_NONE) ? buf[pp + 1] : C.ts;
             uint64_t* row = P.rows + (tc.row_base + tc.rows_before + ex_row) * (n + 2);
             row[0] = pts;
             row[1] = ts - pts;
             for (uint32_t e = 0; e < n; ++e) {
               const uint64_t cur = xform(P, e, buf[p + 5 + e]);
-              const uint64_t prv = (pj != IDX_NONE) ? xform(P, e, buf[pp + 5 + e]) : s.c_last[e];
+              const uint64_t prv = (pj != IDX_NONE) ? xform(P, e, buf[pp + 5 + e]) : C.last[e];
               row[2 + e] = cur - prv;
             }
             ++ex_row;
@@ -738,17 +749,17 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
   const uint32_t last_s = tot_a >> 16, last_l = tot_a & 0xFFFFu;
   if (last_s != 0) {
     const uint32_t p = s.pos[last_s - 1];
-    for (uint32_t e = threadIdx.x; e < n; e += NT) s.c_last[e] = xform(P, e, buf[p + 5 + e]);
+    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, buf[p + 5 + e]);
     if (threadIdx.x == 0) {
-      s.c_ts = buf[p + 1];
-      s.c_te = buf[p + 3];
-      s.c_tr = buf[p + 4];
-      s.c_valid = 1;
-      s.c_gap = last_l > last_s;
-      s.c_last_off = tc.tile_abs + 8ull * p;
+      C.ts = buf[p + 1];
+      C.te = buf[p + 3];
+      C.tr = buf[p + 4];
+      C.valid = 1;
+      C.gap = last_l > last_s;
+      C.last_off = tc.tile_abs + 8ull * p;
     }
   } else if (last_l != 0) {
-    if (threadIdx.x == 0) s.c_gap = 1;
+    if (threadIdx.x == 0) C.gap = 1;
   }
   if (MODE == MODE_EMIT && !SCOUT) {
     __syncthreads();
@@ -762,76 +773,153 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
 // group (type 9, size 40+8n, nr == n).  Then record j sits at entry + j*S and each equality
 // test IS the chain link (record j's size carries the walk to record j+1), so the chain is
 // proven without parsing the other words; the predecessor of sample j is j-1 and there is no
-// LOST, so no scan is needed either.  Returns false (nothing touched) if the tile is not
-// uniform; the caller then takes the general path.
+// LOST, so no scan is needed either.
+//
+// Warp-local: a warp takes 30 consecutive records on lanes 1..30, lanes 0 and 31 hold the
+// neighbours (record -1 is the carry), so bucket boundaries are found with shuffles and the
+// only block barrier is the vote that the whole tile is uniform.  The carry is read from
+// s.c[cur] and the new one written to s.c[cur^1]; the caller's end-of-tile barrier publishes it.
+// Returns false (no side effects) if the tile is not uniform; the caller then takes the
+// general path.
 __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uint64_t* buf,
                                              uint32_t wt, uint32_t entry, const TileCtx& tc,
-                                             uint32_t& exit_word) {
+                                             uint32_t cur, uint32_t& exit_word) {
+  const Carry& C = s.c[cur];
   const uint32_t n = P.n_events;
   const uint32_t S = 5 + n;  // words per SAMPLE
   const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
-  const uint32_t K = (wt - entry + S - 1) / S;  // records whose header lies inside the tile
-  int ok = 1;
-  for (uint32_t j = threadIdx.x; j < K; j += NT) {
-    const uint32_t p = entry + j * S;
-    // misc (bits 32..47) is free; type and size must match, and so must nr
-    if ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + 2] != n) ok = 0;
-  }
-  if (!__syncthreads_and(ok)) return false;
+  // records whose header lies inside the tile: ceil((wt - entry) / S) by multiply-shift
+  const uint32_t K = static_cast<uint32_t>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
+  const bool link0 = C.valid != 0 && C.gap == 0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int OWN = 30;  // records owned per warp-iteration
+  const uint32_t F = n + 3;
+  const bool any_tsc = P.tsc_mask != 0;
 
-  const bool link0 = s.c_valid != 0 && s.c_gap == 0;
-  const uint64_t c_ts = s.c_ts;
-  for (uint32_t j = threadIdx.x; j < K; j += NT) {
-    const uint32_t p = entry + j * S;
-    const uint64_t ts = buf[p + 1];
-    const uint64_t pts = j ? buf[p - S + 1] : c_ts;
-    if ((j || link0) && pts > ts) atomicMin(&s.tile_err, p);  // time regression (gen :156-163)
-    s.u.de.bkt[j] = bucket_of(P, ts);
-  }
-  __syncthreads();
-  for (uint32_t j = threadIdx.x; j < K; j += NT) {
-    if (j == 0 && !link0) continue;  // re-base: no row (gen :135-154)
-    const uint32_t p = entry + j * S;
-    const uint32_t bk = s.u.de.bkt[j];
-    const bool pred_cancel = j > 0 && (j > 1 || link0) && s.u.de.bkt[j - 1] == bk;
-    const bool next_cancel = j + 1 < K && s.u.de.bkt[j + 1] == bk;
-    if (bk == BKT_OOR) {
-      atomicAdd(&s.cnt[C_OOR], 1u);
-    } else if (!pred_cancel || !next_cancel) {
-      uint64_t* base = P.acc + (static_cast<uint64_t>(tc.stream) * P.n_buckets + bk) * (n + 3);
-      const uint64_t* cur = buf + p + 3;       // te, tr, value[0..n)
-      const uint64_t* prv = buf + p - S + 3;   // same fields of sample j-1 (j > 0)
-      const uint64_t fp = next_cancel ? 0 : ~0ull, fm = pred_cancel ? 0 : ~0ull;
-      for (uint32_t e = 0; e < n; ++e) {
-        const uint64_t plus = xform(P, e, cur[2 + e]);
-        const uint64_t minus = j ? xform(P, e, prv[2 + e]) : s.c_last[e];
-        red_add(base + e, (plus & fp) - (minus & fm));
+  // pass 1: every owned record is checked; keep what pass 2 needs in registers (<= 2 groups
+  // per warp for K <= TILE_WORDS/6 = 341 records)
+  constexpr int MAXG = 2;
+  uint64_t ts_[MAXG];
+  uint32_t bk_[MAXG];
+  int ok = 1;
+  uint32_t regress = 0xFFFFFFFFu;
+#pragma unroll
+  for (int g = 0; g < MAXG; ++g) {
+    if ((g * NWARP + warp) * OWN >= static_cast<int>(K)) break;  // warp-uniform: nothing owned
+    const int jr = (g * NWARP + warp) * OWN - 1 + lane;  // record index; -1 is the carry
+    ts_[g] = 0;
+    bk_[g] = BKT_OOR;
+    if (jr >= 0 && jr < static_cast<int>(K)) {
+      const uint32_t p = entry + jr * S;
+      if (lane >= 1 && lane <= OWN) {
+        // misc (bits 32..47) is free; type and size must match, and so must nr
+        if ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + 2] != n) ok = 0;
       }
-      red_add(base + n, (cur[0] & fp) - ((j ? prv[0] : s.c_te) & fm));
-      red_add(base + n + 1, (cur[1] & fp) - ((j ? prv[1] : s.c_tr) & fm));
-      red_add(base + n + 2, (static_cast<uint64_t>(j) & fp) - ((static_cast<uint64_t>(j) - 1) & fm));
+      ts_[g] = buf[p + 1];
+      bk_[g] = bucket_of(P, ts_[g]);
+    } else if (jr == -1) {
+      ts_[g] = C.ts;
+    }
+    const uint64_t pts = __shfl_up_sync(0xffffffffu, ts_[g], 1);
+    if (lane >= 1 && lane <= OWN && jr >= 0 && jr < static_cast<int>(K) && (jr > 0 || link0) &&
+        pts > ts_[g])
+      regress = min(regress, entry + jr * S);  // time regression (gen :156-163)
+  }
+  if (K > MAXG * NWARP * OWN) ok = 0;  // cannot happen for n >= 1 (K <= 341 < 480); be safe
+  if (!__syncthreads_and(ok)) return false;
+  if (regress != 0xFFFFFFFFu) atomicMin(&s.tile_err, regress);
+
+  // pass 2: telescoping.  Inside a run of rows that fall into the same bucket the +value of
+  // one row cancels the -value its successor subtracts, so only bucket boundaries contribute.
+  uint32_t n_oor = 0;
+  // lane -> field of the accumulator record (delta[0..n), dTE, dTR, n_rows) and where that
+  // field sits in a SAMPLE (value[e] at word 5+e, time_enabled at 3, time_running at 4)
+  const bool two = F <= 16;
+  const uint32_t e0 = two ? (lane & 15) : lane;
+  const uint32_t woff0 = e0 < n ? 5 + e0 : (e0 == n ? 3 : 4);
+  const uint64_t cfield0 = e0 < n ? C.last[e0] : (e0 == n ? C.te : C.tr);
+#pragma unroll
+  for (int g = 0; g < MAXG; ++g) {
+    if ((g * NWARP + warp) * OWN >= static_cast<int>(K)) break;
+    const int jr = (g * NWARP + warp) * OWN - 1 + lane;
+    const bool valid = jr >= 0 && jr < static_cast<int>(K);
+    const bool own = valid && lane >= 1 && lane <= OWN;
+    const bool row = valid && (jr > 0 || link0);  // sample 0 re-bases if the carry is invalid
+    const uint32_t bk = bk_[g];
+    const uint32_t bk_prev = __shfl_up_sync(0xffffffffu, bk, 1);
+    const uint32_t bk_next = __shfl_down_sync(0xffffffffu, bk, 1);
+    const bool row_prev = __shfl_up_sync(0xffffffffu, row ? 1 : 0, 1) != 0;
+    const bool pred_cancel = row_prev && bk_prev == bk;
+    const bool next_cancel = jr + 1 < static_cast<int>(K) && bk_next == bk;
+    const bool oor = own && row && bk == BKT_OOR;
+    const bool boundary = own && row && bk != BKT_OOR && !(pred_cancel && next_cancel);
+    n_oor += __popc(__ballot_sync(0xffffffffu, oor));
+    uint32_t mask = __ballot_sync(0xffffffffu, boundary);
+    const uint32_t flags = (next_cancel ? 0u : 1u) | (pred_cancel ? 0u : 2u);
+    // one group of lanes per boundary sample, one lane per field: the REDs of a sample go to
+    // consecutive addresses
+    while (mask) {
+      const int b0 = __ffs(mask) - 1;
+      mask &= mask - 1;
+      int src = b0;
+      if (two) {
+        const int b1 = mask ? __ffs(mask) - 1 : -1;
+        if (mask) mask &= mask - 1;
+        if (lane >= 16) src = b1;
+      }
+      const int srcl = src < 0 ? 0 : src;
+      const int j = __shfl_sync(0xffffffffu, jr, srcl);
+      const uint32_t pk = __shfl_sync(0xffffffffu, flags, srcl);
+      const uint32_t bkj = __shfl_sync(0xffffffffu, bk, srcl);
+      if (src >= 0) {
+        const uint64_t fp = (pk & 1u) ? ~0ull : 0, fm = (pk & 2u) ? ~0ull : 0;
+        const uint32_t p = entry + j * S;
+        uint64_t* base = P.acc + (static_cast<uint64_t>(tc.stream) * P.n_buckets + bkj) * F;
+        uint32_t e = e0, woff = woff0;
+        uint64_t cfield = cfield0;
+        for (;;) {
+          if (e < F) {
+            uint64_t plus, minus;
+            if (e == n + 2) {
+              plus = static_cast<uint64_t>(j);
+              minus = static_cast<uint64_t>(j) - 1;
+            } else {
+              plus = buf[p + woff];
+              minus = j ? buf[p - S + woff] : cfield;
+              if (any_tsc && e < n) {
+                plus = xform(P, e, plus);
+                if (j) minus = xform(P, e, minus);
+              }
+            }
+            red_add(base + e, (plus & fp) - (minus & fm));
+          }
+          if (two || e + 32 >= F) break;
+          e += 32;  // n > 13: a lane serves several fields
+          woff = e < n ? 5 + e : (e == n ? 3 : 4);
+          cfield = e < n ? C.last[e] : (e == n ? C.te : C.tr);
+        }
+      }
     }
   }
-  if (threadIdx.x == 0) {
-    s.cnt[C_SAMPLE] += K;
-    s.cnt[C_RECORDS] += K;
-    s.cnt[C_ROWS] += link0 ? K : K - 1;
-    s.cnt[C_UNKNOWN] += link0 ? 0 : 1;
-  }
-  __syncthreads();  // all reads of the carry are done
-  {
+  if (lane == 0 && n_oor) atomicAdd(&s.cnt[C_OOR], n_oor);
+  // the new carry (other copy): last record of the tile
+  if (warp == NWARP - 1) {
+    Carry& N = s.c[cur ^ 1];
     const uint32_t p = entry + (K - 1) * S;
-    for (uint32_t e = threadIdx.x; e < n; e += NT) s.c_last[e] = xform(P, e, buf[p + 5 + e]);
-    if (threadIdx.x == 0) {
-      s.c_ts = buf[p + 1];
-      s.c_te = buf[p + 3];
-      s.c_tr = buf[p + 4];
-      s.c_valid = 1;
-      s.c_gap = 0;
-      s.c_last_off = tc.tile_abs + 8ull * p;
+    for (uint32_t e = lane; e < n; e += 32) N.last[e] = xform(P, e, buf[p + 5 + e]);
+    if (lane == 0) {
+      N.ts = buf[p + 1];
+      N.te = buf[p + 3];
+      N.tr = buf[p + 4];
+      N.valid = 1;
+      N.gap = 0;
+      N.last_off = tc.tile_abs + 8ull * p;
+      s.cnt[C_SAMPLE] += K;
+      s.cnt[C_RECORDS] += K;
+      s.cnt[C_ROWS] += link0 ? K : K - 1;
+      s.cnt[C_UNKNOWN] += link0 ? 0 : 1;
     }
   }
-  __syncthreads();
   exit_word = entry + K * S;
   return true;
 }
@@ -839,40 +927,41 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
 // Initialise the carry from a predecessor SAMPLE in global memory / the stream carry-in.
 __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t stream, uint64_t pred,
                                            uint32_t gap) {
+  Carry& C = s.c[0];
   const uint32_t n = P.n_events;
   if (pred == PRED_CARRY_IN) {
     const hbtgpu_carry& c = P.carry_in[stream];
-    for (uint32_t e = threadIdx.x; e < n; e += NT) s.c_last[e] = c.last[e];
+    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = c.last[e];
     if (threadIdx.x == 0) {
-      s.c_ts = c.tstamp;
-      s.c_te = c.te;
-      s.c_tr = c.tr;
-      s.c_valid = c.valid != 0;
-      s.c_gap = gap;
-      s.c_last_off = PRED_CARRY_IN;
+      C.ts = c.tstamp;
+      C.te = c.te;
+      C.tr = c.tr;
+      C.valid = c.valid != 0;
+      C.gap = gap;
+      C.last_off = PRED_CARRY_IN;
     }
   } else if (pred == PRED_UNKNOWN) {
     if (threadIdx.x == 0) {
-      s.c_valid = 0;
-      s.c_gap = 1;
-      s.c_last_off = PRED_UNKNOWN;
+      C.valid = 0;
+      C.gap = 1;
+      C.last_off = PRED_UNKNOWN;
     }
   } else {
     const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + pred);
-    for (uint32_t e = threadIdx.x; e < n; e += NT) s.c_last[e] = xform(P, e, r[5 + e]);
+    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, r[5 + e]);
     if (threadIdx.x == 0) {
-      s.c_ts = r[1];
-      s.c_te = r[3];
-      s.c_tr = r[4];
-      s.c_valid = 1;
-      s.c_gap = gap;
-      s.c_last_off = pred;
+      C.ts = r[1];
+      C.te = r[3];
+      C.tr = r[4];
+      C.valid = 1;
+      C.gap = gap;
+      C.last_off = pred;
     }
   }
 }
 
 template <bool SPEC, int MODE>
-__global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
+__global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   if (!SPEC && MODE == MODE_AGG && P.flags[FLAG_NEED_EXACT] == 0) return;  // exact pass not needed
@@ -892,6 +981,7 @@ __global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
   __syncthreads();
 
   uint32_t phase[2] = {0, 0};
+  uint32_t cur = 0;  // which copy of the carry is current
   uint32_t bad = 0;  // fast mode: why this chunk's result is untrustworthy (WHY_*), 0 if fine
 
   // ---- where does the chain enter this chunk, and who is the predecessor sample? ----
@@ -939,9 +1029,9 @@ __global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
         } else {
           entry_abs = cd.halo_off + 8ull * s.term_tgt;
           TileCtx tc{cd.halo_off, 0, cd.stream, 0, 0, 0, 0};
-          decode_tile<true, MODE_AGG>(s, P, hb, K, tc);
+          decode_tile<true, MODE_AGG>(s, P, hb, K, tc, 0);
           if (s.tile_err != 0xFFFFFFFFu) bad = WHY_HALO_ERR;
-          else if (!s.c_valid) bad = WHY_HALO_NO_SAMPLE;  // predecessor unknown
+          else if (!s.c[0].valid) bad = WHY_HALO_NO_SAMPLE;  // predecessor unknown
         }
       }
       __syncthreads();
@@ -953,8 +1043,8 @@ __global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
     }
     if (threadIdx.x == 0) {
       io.in_entry = entry_abs;
-      io.in_pred = s.c_last_off;
-      io.in_gap = s.c_gap;
+      io.in_pred = s.c[0].last_off;
+      io.in_gap = s.c[0].gap;
       io.limit = ~0ull;
     }
   } else {
@@ -1003,17 +1093,30 @@ __global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
       tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base);
       uint32_t term_kind = 0, term_tgt = 0;
       bool done = false;
-      if (MODE == MODE_AGG && !P.force_general) done = uniform_tile(s, P, buf, wt, entry, tc, term_tgt);
+      if (MODE == MODE_AGG && !P.force_general) {
+        done = uniform_tile(s, P, buf, wt, entry, tc, cur, term_tgt);
+        if (done) cur ^= 1;
+      }
       if (!done) {
-        const uint32_t K = classify(s, buf, wt);
-        recover_chain(s, buf, wt, K, entry, P.force_general != 0);
-        term_kind = s.term_kind;
-        term_tgt = s.term_tgt;
-        decode_tile<false, MODE>(s, P, buf, K, tc);
+        uint32_t ew = entry;  // chain position, tile-relative words
+        for (uint32_t w0 = 0; w0 < wt && term_kind == 0; w0 += GT_WORDS) {
+          const uint32_t wh = min(static_cast<uint32_t>(GT_WORDS), wt - w0);
+          if (ew >= w0 + wh) continue;  // a long record jumps over this sub-tile
+          const uint64_t* sb = buf + w0;
+          const uint32_t K = classify(s, sb, wh);
+          recover_chain(s, sb, wh, K, ew - w0, P.force_general != 0);
+          const uint32_t tk = s.term_kind, tt = s.term_tgt;
+          tc.tile_abs = tile_abs + 8ull * w0;
+          tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base) + 8ull * w0;
+          decode_tile<false, MODE>(s, P, sb, K, tc, cur);
+          term_kind = (tk != 0 || s.tile_err != 0xFFFFFFFFu) ? 1u + tk : 0u;
+          ew = w0 + tt;
+        }
+        term_tgt = ew;
       }
       const uint64_t tgt_abs = tile_abs + 8ull * term_tgt;
       if (term_kind != 0 || s.tile_err != 0xFFFFFFFFu) {
-        bad = term_kind != 0 ? WHY_TILE_DEAD : WHY_TILE_ERR;
+        bad = term_kind > 1 ? WHY_TILE_DEAD : WHY_TILE_ERR;
         break;
       }
       if (tgt_abs > limit_abs) {  // record runs past the image end (or the exact-mode limit)
@@ -1028,10 +1131,12 @@ __global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
   if (n_waited < n_issued) mbar_wait(&s.bar[n_waited & 1], phase[n_waited & 1]);
 
   // ---- publish ----
+  __syncthreads();
+  const Carry& C = s.c[cur];
   if (threadIdx.x == 0) {
     io.out_exit = next_abs;
-    io.out_last = s.c_last_off;
-    io.out_gap = s.c_gap;
+    io.out_last = C.last_off;
+    io.out_gap = C.gap;
     io.n_records = s.cnt[C_RECORDS];
     io.n_rows = s.cnt[C_ROWS];
     if (bad) {
@@ -1047,13 +1152,13 @@ __global__ void __launch_bounds__(NT, 3) k_decode(const Params P) {
     // stream carry-out: in exact mode k_resolve owns it
     if (SPEC && (cd.flags & CH_LAST_OF_STREAM)) {
       hbtgpu_carry& co = P.carry_out[cd.stream];
-      for (uint32_t e = threadIdx.x; e < P.n_events; e += NT) co.last[e] = s.c_last[e];
+      for (uint32_t e = threadIdx.x; e < P.n_events; e += NT) co.last[e] = C.last[e];
       if (threadIdx.x == 0) {
-        const bool v = s.c_valid && !s.c_gap;
+        const bool v = C.valid && !C.gap;
         co.valid = v;
-        co.tstamp = v ? s.c_ts : ~0ull;
-        co.te = s.c_te;
-        co.tr = s.c_tr;
+        co.tstamp = v ? C.ts : ~0ull;
+        co.te = C.te;
+        co.tr = C.tr;
         ctr[C_LAST_TS] = co.tstamp;
       }
     }
