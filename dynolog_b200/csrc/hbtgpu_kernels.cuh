@@ -775,10 +775,15 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
 // proven without parsing the other words; the predecessor of sample j is j-1 and there is no
 // LOST, so no scan is needed either.
 //
-// Warp-local: a warp takes 30 consecutive records on lanes 1..30, lanes 0 and 31 hold the
-// neighbours (record -1 is the carry), so bucket boundaries are found with shuffles and the
-// only block barrier is the vote that the whole tile is uniform.  The carry is read from
-// s.c[cur] and the new one written to s.c[cur^1]; the caller's end-of-tile barrier publishes it.
+// Telescoping.  Row j adds V_j - V_{j-1} to bucket(j), V = (value[], te, tr, ordinal).  So the
+// vector V_j is used twice: +V_j into bucket(j) (if row j exists) and -V_j into bucket(j+1)
+// (if row j+1 exists); when both exist and the buckets are equal the two cancel.  Only records
+// at a bucket transition (and the tile's two edges) touch global memory.
+//
+// Warp-local: a warp takes 31 consecutive records on lanes 0..30 (record -1 is the carry),
+// lane 31 holds the right neighbour, so transitions are found with shuffles and the only block
+// barrier is the vote that the whole tile is uniform.  The carry is read from s.c[cur] and the
+// new one written to s.c[cur^1]; the caller's end-of-tile barrier publishes it.
 // Returns false (no side effects) if the tile is not uniform; the caller then takes the
 // general path.
 __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uint64_t* buf,
@@ -789,48 +794,43 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
   const uint32_t S = 5 + n;  // words per SAMPLE
   const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
   // records whose header lies inside the tile: ceil((wt - entry) / S) by multiply-shift
-  const uint32_t K = static_cast<uint32_t>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
+  const int K = static_cast<int>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
   const bool link0 = C.valid != 0 && C.gap == 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int OWN = 30;  // records owned per warp-iteration
+  constexpr int OWN = 31;  // records owned per warp-iteration (lanes 0..30)
+  constexpr int MAXG = 2;  // K + 1 <= 342 items <= MAXG * NWARP * OWN = 496
   const uint32_t F = n + 3;
   const bool any_tsc = P.tsc_mask != 0;
 
-  // pass 1: every owned record is checked; keep what pass 2 needs in registers (<= 2 groups
-  // per warp for K <= TILE_WORDS/6 = 341 records)
-  constexpr int MAXG = 2;
-  uint64_t ts_[MAXG];
+  // pass 1: check every record, compute its bucket
   uint32_t bk_[MAXG];
   int ok = 1;
   uint32_t regress = 0xFFFFFFFFu;
 #pragma unroll
   for (int g = 0; g < MAXG; ++g) {
-    if ((g * NWARP + warp) * OWN >= static_cast<int>(K)) break;  // warp-uniform: nothing owned
-    const int jr = (g * NWARP + warp) * OWN - 1 + lane;  // record index; -1 is the carry
-    ts_[g] = 0;
+    const int j0 = (g * NWARP + warp) * OWN - 1;  // first item of this warp-iteration
+    if (j0 >= K) break;                           // warp-uniform: nothing here
+    const int jr = j0 + lane;                     // record index; -1 is the carry
+    uint64_t ts = 0;
     bk_[g] = BKT_OOR;
-    if (jr >= 0 && jr < static_cast<int>(K)) {
+    if (jr >= 0 && jr < K) {
       const uint32_t p = entry + jr * S;
-      if (lane >= 1 && lane <= OWN) {
-        // misc (bits 32..47) is free; type and size must match, and so must nr
-        if ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + 2] != n) ok = 0;
-      }
-      ts_[g] = buf[p + 1];
-      bk_[g] = bucket_of(P, ts_[g]);
+      // misc (bits 32..47) is free; type and size must match, and so must nr
+      if (lane < 31 && ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + 2] != n)) ok = 0;
+      ts = buf[p + 1];
+      bk_[g] = bucket_of(P, ts);
     } else if (jr == -1) {
-      ts_[g] = C.ts;
+      ts = C.ts;
     }
-    const uint64_t pts = __shfl_up_sync(0xffffffffu, ts_[g], 1);
-    if (lane >= 1 && lane <= OWN && jr >= 0 && jr < static_cast<int>(K) && (jr > 0 || link0) &&
-        pts > ts_[g])
-      regress = min(regress, entry + jr * S);  // time regression (gen :156-163)
+    const uint64_t nts = __shfl_down_sync(0xffffffffu, ts, 1);
+    // row jr+1 exists and goes back in time (gen :156-163)
+    if (lane < 31 && jr + 1 < K && (jr >= 0 || link0) && ts > nts)
+      regress = min(regress, entry + (jr + 1) * S);
   }
-  if (K > MAXG * NWARP * OWN) ok = 0;  // cannot happen for n >= 1 (K <= 341 < 480); be safe
   if (!__syncthreads_and(ok)) return false;
   if (regress != 0xFFFFFFFFu) atomicMin(&s.tile_err, regress);
 
-  // pass 2: telescoping.  Inside a run of rows that fall into the same bucket the +value of
-  // one row cancels the -value its successor subtracts, so only bucket boundaries contribute.
+  // pass 2
   uint32_t n_oor = 0;
   // lane -> field of the accumulator record (delta[0..n), dTE, dTR, n_rows) and where that
   // field sits in a SAMPLE (value[e] at word 5+e, time_enabled at 3, time_running at 4)
@@ -838,60 +838,55 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
   const uint32_t e0 = two ? (lane & 15) : lane;
   const uint32_t woff0 = e0 < n ? 5 + e0 : (e0 == n ? 3 : 4);
   const uint64_t cfield0 = e0 < n ? C.last[e0] : (e0 == n ? C.te : C.tr);
+  uint64_t* const acc_s = P.acc + static_cast<uint64_t>(tc.stream) * P.n_buckets * F;
 #pragma unroll
   for (int g = 0; g < MAXG; ++g) {
-    if ((g * NWARP + warp) * OWN >= static_cast<int>(K)) break;
-    const int jr = (g * NWARP + warp) * OWN - 1 + lane;
-    const bool valid = jr >= 0 && jr < static_cast<int>(K);
-    const bool own = valid && lane >= 1 && lane <= OWN;
-    const bool row = valid && (jr > 0 || link0);  // sample 0 re-bases if the carry is invalid
+    const int j0 = (g * NWARP + warp) * OWN - 1;
+    if (j0 >= K) break;
+    const int jr = j0 + lane;
     const uint32_t bk = bk_[g];
-    const uint32_t bk_prev = __shfl_up_sync(0xffffffffu, bk, 1);
     const uint32_t bk_next = __shfl_down_sync(0xffffffffu, bk, 1);
-    const bool row_prev = __shfl_up_sync(0xffffffffu, row ? 1 : 0, 1) != 0;
-    const bool pred_cancel = row_prev && bk_prev == bk;
-    const bool next_cancel = jr + 1 < static_cast<int>(K) && bk_next == bk;
-    const bool oor = own && row && bk == BKT_OOR;
-    const bool boundary = own && row && bk != BKT_OOR && !(pred_cancel && next_cancel);
-    n_oor += __popc(__ballot_sync(0xffffffffu, oor));
-    uint32_t mask = __ballot_sync(0xffffffffu, boundary);
-    const uint32_t flags = (next_cancel ? 0u : 1u) | (pred_cancel ? 0u : 2u);
-    // one group of lanes per boundary sample, one lane per field: the REDs of a sample go to
+    const bool own = lane < 31 && jr < K;                    // jr >= -1 always
+    const bool rowA = jr >= 1 || (jr == 0 && link0);         // row jr exists
+    const bool rowB = jr + 1 < K && (jr >= 0 || link0);      // row jr+1 exists
+    const bool cancel = rowA && rowB && bk == bk_next;
+    const bool doA = own && rowA && !cancel && bk != BKT_OOR;
+    const bool doB = own && rowB && !cancel && bk_next != BKT_OOR;
+    n_oor += __popc(__ballot_sync(0xffffffffu, own && rowA && bk == BKT_OOR));
+    uint32_t mask = __ballot_sync(0xffffffffu, doA || doB);
+    const uint32_t flags = (doA ? 1u : 0u) | (doB ? 2u : 0u);
+    // one group of lanes per such record, one lane per field: the REDs of a record go to
     // consecutive addresses
     while (mask) {
-      const int b0 = __ffs(mask) - 1;
+      int src = __ffs(mask) - 1;
       mask &= mask - 1;
-      int src = b0;
       if (two) {
         const int b1 = mask ? __ffs(mask) - 1 : -1;
-        if (mask) mask &= mask - 1;
+        mask &= mask - 1;  // no-op when mask is already 0
         if (lane >= 16) src = b1;
       }
       const int srcl = src < 0 ? 0 : src;
-      const int j = __shfl_sync(0xffffffffu, jr, srcl);
       const uint32_t pk = __shfl_sync(0xffffffffu, flags, srcl);
-      const uint32_t bkj = __shfl_sync(0xffffffffu, bk, srcl);
+      const uint32_t bkA = __shfl_sync(0xffffffffu, bk, srcl);
+      const uint32_t bkB = __shfl_sync(0xffffffffu, bk_next, srcl);
       if (src >= 0) {
-        const uint64_t fp = (pk & 1u) ? ~0ull : 0, fm = (pk & 2u) ? ~0ull : 0;
+        const int j = j0 + src;
         const uint32_t p = entry + j * S;
-        uint64_t* base = P.acc + (static_cast<uint64_t>(tc.stream) * P.n_buckets + bkj) * F;
         uint32_t e = e0, woff = woff0;
         uint64_t cfield = cfield0;
         for (;;) {
           if (e < F) {
-            uint64_t plus, minus;
+            uint64_t v;
             if (e == n + 2) {
-              plus = static_cast<uint64_t>(j);
-              minus = static_cast<uint64_t>(j) - 1;
+              v = static_cast<uint64_t>(static_cast<int64_t>(j));  // ordinal; -1 for the carry
+            } else if (j < 0) {
+              v = cfield;  // carry values are already transformed
             } else {
-              plus = buf[p + woff];
-              minus = j ? buf[p - S + woff] : cfield;
-              if (any_tsc && e < n) {
-                plus = xform(P, e, plus);
-                if (j) minus = xform(P, e, minus);
-              }
+              v = buf[p + woff];
+              if (any_tsc && e < n) v = xform(P, e, v);
             }
-            red_add(base + e, (plus & fp) - (minus & fm));
+            if (pk & 1u) red_add(acc_s + static_cast<uint64_t>(bkA) * F + e, v);
+            if (pk & 2u) red_add(acc_s + static_cast<uint64_t>(bkB) * F + e, 0ull - v);
           }
           if (two || e + 32 >= F) break;
           e += 32;  // n > 13: a lane serves several fields
@@ -1054,41 +1049,42 @@ __global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
     __syncthreads();
   }
 
-  // ---- tiles ----
+  // ---- tiles ----  (positions are chunk-relative bytes in 32 bits: a chunk is <= 256 KiB and a
+  // record can leave it by at most 64 KiB)
   const uint64_t img_end_abs = cd.img_base + cd.img_len;
   const uint64_t chunk_end_abs = min(cd.img_base + cd.end, limit_abs);
-  const uint32_t n_tiles = static_cast<uint32_t>((cd.end - cd.begin + TILE_BYTES - 1) / TILE_BYTES);
   TileCtx tc{0, 0, cd.stream, 0, 0, io.row_base, io.rec_base};
-  uint64_t next_abs = entry_abs;  // arena offset of the next record header on the chain
+  const bool any_work = entry_abs < chunk_end_abs;  // also false for exact-mode "skip" (~0)
+  const uint32_t chunk_len = any_work ? static_cast<uint32_t>(chunk_end_abs - chunk_abs) : 0;
+  const uint32_t limit_rel = static_cast<uint32_t>(umin64(limit_abs - chunk_abs, 0xFFFFFFF0ull));
+  const uint32_t avail_rel = static_cast<uint32_t>(umin64((img_end_abs - chunk_abs + 15ull) & ~15ull, 0xFFFFFFF0ull));
+  uint32_t next_rel = any_work ? static_cast<uint32_t>(entry_abs - chunk_abs) : 0;
+  const uint8_t* const chunk_ptr = P.arena + chunk_abs;
 
-  auto issue = [&](uint32_t t) {
-    const uint64_t off = chunk_abs + static_cast<uint64_t>(t) * TILE_BYTES;
-    uint64_t avail = img_end_abs - off;
-    avail = (avail + 15ull) & ~15ull;
-    const uint32_t bytes = static_cast<uint32_t>(umin64(avail, STAGE_BYTES));
-    mbar_expect_tx(&s.bar[t & 1], bytes);
-    tma_load_1d(s.data[t & 1], P.arena + off, bytes, &s.bar[t & 1]);
+  auto issue = [&](uint32_t tile_rel, uint32_t b) {
+    const uint32_t bytes = min(avail_rel - tile_rel, static_cast<uint32_t>(STAGE_BYTES));
+    mbar_expect_tx(&s.bar[b], bytes);
+    tma_load_1d(s.data[b], chunk_ptr + tile_rel, bytes, &s.bar[b]);
   };
-  const bool any_work = next_abs < chunk_end_abs;
   uint32_t n_issued = 0, n_waited = 0;
   if (any_work) {
-    if (threadIdx.x == 0) issue(0);
+    if (threadIdx.x == 0) issue(0, 0);
     n_issued = 1;
   }
-  for (uint32_t t = 0; any_work && t < n_tiles; ++t) {
-    const uint64_t tile_abs = chunk_abs + static_cast<uint64_t>(t) * TILE_BYTES;
-    if (tile_abs >= chunk_end_abs) break;
-    if (t + 1 < n_tiles && tile_abs + TILE_BYTES < chunk_end_abs) {
-      if (threadIdx.x == 0) issue(t + 1);
+  for (uint32_t tile_rel = 0; tile_rel < chunk_len; tile_rel += TILE_BYTES) {
+    const uint32_t b = (tile_rel / TILE_BYTES) & 1;
+    if (tile_rel + TILE_BYTES < chunk_len) {
+      if (threadIdx.x == 0) issue(tile_rel + TILE_BYTES, b ^ 1);
       ++n_issued;
     }
-    mbar_wait(&s.bar[t & 1], phase[t & 1]);
-    phase[t & 1] ^= 1;
+    mbar_wait(&s.bar[b], phase[b]);
+    phase[b] ^= 1;
     ++n_waited;
-    const uint64_t* buf = s.data[t & 1];
-    const uint32_t wt = static_cast<uint32_t>(umin64(TILE_BYTES, chunk_end_abs - tile_abs) / 8);
-    if (next_abs < tile_abs + 8ull * wt) {
-      const uint32_t entry = static_cast<uint32_t>((next_abs - tile_abs) / 8);
+    const uint64_t* buf = s.data[b];
+    const uint32_t wt = min(static_cast<uint32_t>(TILE_BYTES), chunk_len - tile_rel) / 8;
+    if (next_rel < tile_rel + 8 * wt) {
+      const uint32_t entry = (next_rel - tile_rel) / 8;
+      const uint64_t tile_abs = chunk_abs + tile_rel;
       tc.tile_abs = tile_abs;
       tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base);
       uint32_t term_kind = 0, term_tgt = 0;
@@ -1114,21 +1110,22 @@ __global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
         }
         term_tgt = ew;
       }
-      const uint64_t tgt_abs = tile_abs + 8ull * term_tgt;
       if (term_kind != 0 || s.tile_err != 0xFFFFFFFFu) {
         bad = term_kind > 1 ? WHY_TILE_DEAD : WHY_TILE_ERR;
         break;
       }
-      if (tgt_abs > limit_abs) {  // record runs past the image end (or the exact-mode limit)
+      const uint32_t tgt_rel = tile_rel + 8 * term_tgt;
+      if (tgt_rel > limit_rel) {  // record runs past the image end (or the exact-mode limit)
         bad = WHY_PAST_END;
         break;
       }
-      next_abs = tgt_abs;
+      next_rel = tgt_rel;
     }
-    __syncthreads();  // buffer (t&1) is free for tile t+2
+    __syncthreads();  // buffer b is free for the tile after next; publishes the new carry
   }
   // never exit with a bulk copy still in flight into this CTA's shared memory
   if (n_waited < n_issued) mbar_wait(&s.bar[n_waited & 1], phase[n_waited & 1]);
+  const uint64_t next_abs = any_work ? chunk_abs + next_rel : entry_abs;
 
   // ---- publish ----
   __syncthreads();
