@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -881,6 +882,229 @@ int hbtgpu_math_running_ratio(hbtgpu_ctx* ctx, const uint64_t* te, const uint64_
   D2H(has_mux, dm, n);
   CK(cudaStreamSynchronize(ctx->stream));
   return 0;
+}
+
+}  // extern "C"
+
+
+// =======================================================================================
+// hbtgpu_decode_image_noalloc: the decode pipeline for callers that cannot allocate.
+//
+// Everything the kernels need besides the caller's image and accumulator lives in this one
+// file-scope device array.  In host code the NAME of a __device__ variable is only a handle for
+// the runtime, not an address a kernel could use; the usable address is fetched once per device
+// with cudaGetSymbolAddress (below) and handed to the kernels through Params.
+// =======================================================================================
+namespace {
+
+constexpr uint32_t kNaMaxChunks = 1024;
+struct NaScratch {                       // layout of g_noalloc_scratch
+  uint32_t flags[FLAG_COUNT];            //   must start at zero each call
+  uint64_t counters[C_SLOTS];            //   must start at zero each call
+  hbtgpu_carry carry_in, carry_out;
+  hbtgpu_head_stub head;
+  StreamDesc stream;
+  ImageDesc image;
+  ChunkDesc chunks[kNaMaxChunks];
+  ChunkIO io[kNaMaxChunks];              //   must start at zero each call
+};
+constexpr size_t kNaScratchBytes = (sizeof(NaScratch) + 255) / 256 * 256;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaScratchBytes];
+
+// Fills the tables for one image of one stream and clears what has to start from zero.
+__global__ void k_na_setup(NaScratch* sc, uint64_t image_bytes, uint64_t chunk_bytes,
+                           uint32_t n_chunks, hbtgpu_carry carry_in) {
+  const uint32_t tid = threadIdx.x;
+  if (tid < FLAG_COUNT) sc->flags[tid] = 0;
+  if (tid < C_SLOTS) sc->counters[tid] = 0;
+  if (tid == 0) {
+    sc->carry_in = carry_in;
+    sc->carry_out = carry_in;  // an empty image leaves the state as it was
+    sc->stream = StreamDesc{0, image_bytes ? 1u : 0u};
+    sc->image = ImageDesc{0, image_bytes, 0, 0, 0, n_chunks, 0};
+  }
+  for (uint32_t c = tid; c < n_chunks; c += blockDim.x) {
+    ChunkDesc cd{};
+    cd.img_base = 0;
+    cd.img_len = image_bytes;
+    cd.begin = static_cast<uint64_t>(c) * chunk_bytes;
+    cd.end = cd.begin + chunk_bytes < image_bytes ? cd.begin + chunk_bytes : image_bytes;
+    cd.stream_pos = 0;
+    cd.stream = 0;
+    cd.image = 0;
+    cd.flags = (c == 0 ? (CH_FIRST_OF_IMAGE | CH_FIRST_OF_STREAM) : 0u) |
+               (c + 1 == n_chunks ? (CH_LAST_OF_IMAGE | CH_LAST_OF_STREAM) : 0u);
+    if (c > 0) {
+      const uint64_t hb = cd.begin > HALO_BYTES ? cd.begin - HALO_BYTES : 0;
+      cd.halo_off = hb;
+      cd.halo_len = static_cast<uint32_t>(cd.begin - hb);
+      if (hb == 0) cd.flags |= CH_HALO_EXACT_START;
+    }
+    sc->chunks[c] = cd;
+    ChunkIO z{};
+    sc->io[c] = z;
+  }
+}
+
+thread_local char g_na_error[512];
+int na_fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_na_error, sizeof(g_na_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+constexpr int kNaMaxDevices = 64;
+NaScratch* g_na_ptr[kNaMaxDevices] = {nullptr};  // device address of the array, per device
+std::mutex g_na_mutex;
+
+// Once per device, with that device current: resolve the array's device address.
+int na_device_setup(int dev, NaScratch** out) {
+  std::lock_guard<std::mutex> lock(g_na_mutex);
+  if (!g_na_ptr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p)
+      return na_fail(-EIO, "cudaGetSymbolAddress(scratch) failed on device %d: %s", dev,
+                     cudaGetErrorString(e));
+    for (auto k : {(const void*)k_decode<true, MODE_AGG>, (const void*)k_decode<false, MODE_AGG>}) {
+      e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               static_cast<int>(sizeof(Smem)));
+      if (e != cudaSuccess)
+        return na_fail(-EIO, "cudaFuncSetAttribute failed on device %d: %s", dev, cudaGetErrorString(e));
+    }
+    g_na_ptr[dev] = static_cast<NaScratch*>(p);
+  }
+  *out = g_na_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* hbtgpu_noalloc_last_error(void) { return g_na_error; }
+
+int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* carry_in,
+                                const void* device_image, size_t image_bytes,
+                                uint64_t* device_acc, hbtgpu_counters* counters_out,
+                                hbtgpu_carry* carry_out, void* cuda_stream) {
+#define NCK(call)                                                                        \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) return na_fail(-EIO, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+  g_na_error[0] = 0;
+  if (!cfg || !device_acc || !counters_out) return na_fail(-EINVAL, "null argument");
+  if (image_bytes && !device_image) return na_fail(-EINVAL, "null image");
+  if (cfg->n_events == 0 || cfg->n_events > HBTGPU_MAX_EVENTS)
+    return na_fail(-EINVAL, "n_events must be in [1,%d]", HBTGPU_MAX_EVENTS);
+  if (cfg->n_buckets == 0 || cfg->n_buckets >= 0xFFFFFFFEu || cfg->bucket_ns == 0)
+    return na_fail(-EINVAL, "n_buckets / bucket_ns out of range");
+  if (cfg->time_shift > 63 || (cfg->tsc_mask != 0 && cfg->time_mult == 0))
+    return na_fail(-EINVAL, "bad TSC conversion parameters");
+  if (image_bytes > HBTGPU_NOALLOC_MAX_IMAGE_BYTES)
+    return na_fail(-E2BIG,
+                   "image of %zu bytes exceeds HBTGPU_NOALLOC_MAX_IMAGE_BYTES (%llu): this entry "
+                   "point works out of a fixed static scratch array; use a context for larger images",
+                   image_bytes, (unsigned long long)HBTGPU_NOALLOC_MAX_IMAGE_BYTES);
+  if (image_bytes % 8) return na_fail(-EINVAL, "image size %zu is not a multiple of 8", image_bytes);
+  if (reinterpret_cast<uintptr_t>(device_image) % 16)
+    return na_fail(-EINVAL, "device_image must be 16-byte aligned");
+  if (cfg->device < 0 || cfg->device >= kNaMaxDevices) return na_fail(-ENODEV, "device %d out of range", cfg->device);
+  NCK(cudaSetDevice(cfg->device));
+  NaScratch* sc = nullptr;
+  if (int r = na_device_setup(cfg->device, &sc)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+
+  // chunks: as many as fill the GPU, never more than the static table holds
+  uint64_t cb = TILE_BYTES;
+  const uint64_t target = image_bytes / (148ull * 12ull);
+  while (cb < target && cb < (256ull << 10)) cb <<= 1;
+  while ((image_bytes + cb - 1) / cb > kNaMaxChunks) cb <<= 1;
+  const uint32_t nc = static_cast<uint32_t>((image_bytes + cb - 1) / cb);
+
+  const uint32_t n = cfg->n_events;
+  const uint64_t acc_words = static_cast<uint64_t>(cfg->n_buckets) * (n + 3);
+  hbtgpu_carry cin{};
+  if (carry_in) cin = *carry_in;
+  NCK(cudaMemsetAsync(device_acc, 0, acc_words * 8, st));
+  k_na_setup<<<1, 256, 0, st>>>(sc, image_bytes, cb, nc, cin);
+
+  Params P{};
+  P.arena = static_cast<const uint8_t*>(device_image);
+  P.chunks = sc->chunks;
+  P.io = sc->io;
+  P.images = &sc->image;
+  P.streams = &sc->stream;
+  P.carry_in = &sc->carry_in;
+  P.carry_out = &sc->carry_out;
+  P.head = &sc->head;
+  P.counters = sc->counters;
+  P.acc = device_acc;
+  P.flags = sc->flags;
+  P.t0 = cfg->t0;
+  P.bucket_ns = cfg->bucket_ns;
+  P.tsc_mask = cfg->tsc_mask;
+  P.time_zero = cfg->time_zero;
+  P.n_events = n;
+  P.n_buckets = cfg->n_buckets;
+  P.n_chunks = nc;
+  P.n_streams = 1;
+  P.time_shift = cfg->time_shift;
+  P.time_mult = cfg->time_mult;
+  P.force_general = (cfg->flags & HBTGPU_F_FORCE_GENERAL) ? 1 : 0;
+  {
+    const unsigned __int128 range = static_cast<unsigned __int128>(cfg->n_buckets) * cfg->bucket_ns;
+    P.range_ns = range > ~0ull ? ~0ull : static_cast<uint64_t>(range);
+    P.inv_bucket = 1.0 / static_cast<double>(cfg->bucket_ns);
+    const uint64_t b = cfg->bucket_ns;
+    P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
+    const uint64_t S = 5ull + n;
+    P.s_magic = static_cast<uint32_t>(((1ull << 32) + S - 1) / S);
+  }
+  if (nc) {
+    const bool force_exact = (cfg->flags & HBTGPU_F_FORCE_EXACT) != 0;
+    if (force_exact) NCK(cudaMemsetAsync(&sc->flags[FLAG_NEED_EXACT], 1, 1, st));
+    if (!force_exact) {
+      k_decode<true, MODE_AGG><<<nc, NT, sizeof(Smem), st>>>(P);
+      k_verify<<<(nc + 255) / 256, 256, 0, st>>>(P);
+    }
+    k_resolve<<<1, RES_WARPS * 32, 0, st>>>(P);
+    k_clear<<<148 * 4, 256, 0, st>>>(P, force_exact ? 0 : acc_words);
+    k_decode<false, MODE_AGG><<<nc, NT, sizeof(Smem), st>>>(P);
+  }
+  NCK(cudaGetLastError());
+
+  // results: three small device-to-host copies into stack / caller memory
+  uint64_t ctr[C_SLOTS];
+  uint32_t flags[FLAG_COUNT];
+  hbtgpu_carry cout_;
+  NCK(cudaMemcpyAsync(ctr, sc->counters, sizeof(ctr), cudaMemcpyDeviceToHost, st));
+  NCK(cudaMemcpyAsync(flags, sc->flags, sizeof(flags), cudaMemcpyDeviceToHost, st));
+  NCK(cudaMemcpyAsync(&cout_, &sc->carry_out, sizeof(cout_), cudaMemcpyDeviceToHost, st));
+  NCK(cudaStreamSynchronize(st));
+  if (flags[FLAG_INTERNAL])
+    return na_fail(-EIO, "internal inconsistency: exact pass met an unresolved record (code %u)",
+                   flags[FLAG_INTERNAL]);
+  memset(counters_out, 0, sizeof(*counters_out));
+  counters_out->lost = ctr[C_LOST];
+  counters_out->throttle = ctr[C_THROTTLE];
+  counters_out->unthrottle = ctr[C_UNTHROTTLE];
+  counters_out->sample = ctr[C_SAMPLE];
+  counters_out->read = ctr[C_READ];
+  counters_out->num_records = ctr[C_RECORDS];
+  counters_out->num_unknown_count_interval = ctr[C_UNKNOWN];
+  counters_out->num_rows = ctr[C_ROWS];
+  counters_out->rows_out_of_range = ctr[C_OOR];
+  counters_out->err = ctr[C_ERR] ? -EPERM : 0;
+  counters_out->err_offset = ctr[C_ERR] ? ctr[C_ERR_OFF] : image_bytes;
+  counters_out->last_tstamp = cout_.valid ? cout_.tstamp : ~0ull;
+  if (carry_out) *carry_out = cout_;
+  return 0;
+#undef NCK
 }
 
 }  // extern "C"

@@ -87,7 +87,10 @@ ABI_SYMBOLS = [
     "hbtgpu_math_get_count", "hbtgpu_math_rate", "hbtgpu_math_add_reduce",
     "hbtgpu_math_tsc_to_ktime", "hbtgpu_math_ktime_to_tsc", "hbtgpu_math_per_second_mega",
     "hbtgpu_math_running_ratio", "hbtgpu_get_stats", "hbtgpu_version",
+    "hbtgpu_decode_image_noalloc", "hbtgpu_noalloc_last_error",
 ]
+
+NOALLOC_MAX_IMAGE_BYTES = 64 << 20
 
 _lib = None
 
@@ -114,6 +117,7 @@ def lib():
         L.hbtgpu_stream.argtypes = [C.c_void_p]
         L.hbtgpu_destroy.restype = None
         L.hbtgpu_destroy.argtypes = [C.c_void_p]
+        L.hbtgpu_noalloc_last_error.restype = C.c_char_p
         _lib = L
     return _lib
 
@@ -351,3 +355,19 @@ class Context:
         self._ck(self.L.hbtgpu_math_running_ratio(self.h, _ptr(te), _ptr(tr), _ptr(ratio), _ptr(ri),
                                                   _ptr(mux), C.c_size_t(te.size)))
         return ratio, ri, mux.astype(bool)
+
+
+def decode_image_noalloc(cfg, device_image, image_bytes, device_acc, carry_in=None, stream=0):
+    """hbtgpu_decode_image_noalloc: for callers that may not allocate (see include/hbtgpu.h).
+    cfg: a Config; device_image / device_acc: raw device pointers (ints) the caller owns.
+    Returns (counters dict, carry_out)."""
+    L = lib()
+    ctr = Counters()
+    cout = Carry()
+    rc = L.hbtgpu_decode_image_noalloc(
+        C.byref(cfg), C.byref(carry_in) if carry_in is not None else C.c_void_p(0),
+        C.c_void_p(device_image), C.c_size_t(image_bytes), C.c_void_p(device_acc), C.byref(ctr),
+        C.byref(cout), C.c_void_p(stream))
+    if rc != 0:
+        raise HbtGpuError(rc, L.hbtgpu_noalloc_last_error().decode())
+    return ctr.as_dict(), cout

@@ -250,6 +250,51 @@ int hbtgpu_get_stats(hbtgpu_ctx* ctx, hbtgpu_stats* out);
 
 const char* hbtgpu_version(void);
 
+/* ---- for callers that must not allocate ----------------------------------------------- */
+
+/* Largest image hbtgpu_decode_image_noalloc accepts. */
+#define HBTGPU_NOALLOC_MAX_IMAGE_BYTES (64ull << 20)
+
+/* Decode + aggregate ONE ring image of ONE cpu without allocating anything, neither on the
+ * device nor on the host.  (No counterpart in the reference: hbt never touches a GPU.)
+ *
+ * Who needs this: dynolog is an always-on daemon that shares the GPU with the training job it
+ * watches.  That job typically owns almost all device memory, so a cudaMalloc from the
+ * monitor's sampling loop can fail at any moment, and even when it succeeds cudaMalloc and
+ * cudaFree synchronise the whole device, i.e. they stall the very job being observed.  The
+ * same holds for a caller that runs inside somebody else's memory budget (a plugin loaded into
+ * the trainer process) and for one that has frozen its memory pool.  Such callers create no
+ * context; they hand in device buffers they already own and call this one function.
+ *
+ * The working memory the decode kernels need (chunk table, per-chunk hand-over records, flags,
+ * carry, counters; about 160 KiB) lives in a static __device__ array inside the library, which
+ * every GPU that loads the library holds until the process exits.  The price of that fixed
+ * array is the size limit above: a larger image is refused with -E2BIG and a message, nothing
+ * is truncated.
+ *
+ *   cfg           device, n_events, tsc_*, time_*, t0, bucket_ns, n_buckets and flags are used;
+ *                 max_cpus, arena_bytes and the metrics are ignored
+ *   carry_in      host pointer, may be NULL (= invalid state, as after a LOST)
+ *   device_image  device pointer, 16-byte aligned; the bytes of one image (start and end on
+ *                 record boundaries); must be readable up to image_bytes rounded up to 16
+ *   device_acc    device pointer to n_buckets * (n_events + 3) u64; overwritten with the bucket
+ *                 sums (same layout as hbtgpu_bucket_view.acc for one cpu)
+ *   counters_out  host pointer; carry_out host pointer or NULL
+ *   cuda_stream   a cudaStream_t (NULL = default stream); the call returns after the stream
+ *                 has drained, results are then complete
+ *
+ * First call on a device: looks up the address of the static array (cudaGetSymbolAddress) and
+ * raises the kernels' shared-memory limit.  Make that first call before any stream capture.
+ * All calls on one device share the one array and it keeps what the previous call left; every
+ * call re-initialises the parts that must start from zero.  Two calls whose GPU work overlaps
+ * (different streams, different threads) therefore race on it: serialise them. */
+int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* carry_in,
+                                const void* device_image, size_t image_bytes,
+                                uint64_t* device_acc, hbtgpu_counters* counters_out,
+                                hbtgpu_carry* carry_out, void* cuda_stream);
+/* Message of the last failed hbtgpu_decode_image_noalloc on this thread. */
+const char* hbtgpu_noalloc_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif
