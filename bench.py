@@ -204,10 +204,12 @@ def main():
     t0 = 1_000_000_000 + rank * SAMPLES_PER_CPU * 100_000
     metrics = [(hbtgpu.METRIC_RATE, [0, 1]),  # IPC = instructions / cycles (BuiltinMetrics.cpp:616-666)
                (hbtgpu.METRIC_RATE, [2, 0])]  # LLC misses per instruction (BuiltinMetrics.cpp:792-818)
+    # N > 1: time-window shards; every rank decodes from an invalid state and the rows that
+    # straddle shard boundaries are added after a small all_gather of per-cpu stubs
     ctx = hbtgpu.Context(n_events=N_EVENTS, max_cpus=N_CPUS, n_buckets=N_BUCKETS, t0=t0,
                          bucket_ns=BUCKET_NS, arena_bytes=image_bytes + (1 << 20), metrics=metrics,
-                         device=local_rank)
-    carry = hbtgpu.make_carry(valid=True, tstamp=t0, last=[0] * N_EVENTS)
+                         device=local_rank, flags=hbtgpu.F_EXTERNAL_CARRY if world > 1 else 0)
+    carry = hbtgpu.make_carry(valid=True, tstamp=1_000_000_000, last=[0] * N_EVENTS)
     for cpu in range(N_CPUS):
         ctx.set_carry(cpu, carry)
     ext = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
@@ -217,11 +219,25 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    if world > 1:
+        sb = ctx.stub_bytes()
+        send = torch.empty(sb, dtype=torch.uint8, device="cuda")
+        recv = torch.empty(world * sb, dtype=torch.uint8, device="cuda")
+
+    def gpu_step():
+        """One pass of the hot path over this rank's resident shard (+ the boundary exchange)."""
+        ctx.run()
+        if world > 1:
+            with torch.cuda.stream(ext):
+                ctx.export_stubs_device(send.data_ptr())
+                dist.all_gather_into_tensor(recv, send)  # NCCL, ordered on the context stream
+                ctx.apply_boundaries_gathered(recv.data_ptr(), world, rank)
+
     # ---- resident leg: images already in HBM --------------------------------------------
     for cpu, s in enumerate(streams):
         ctx.submit_image(cpu, s)
     for _ in range(args.warmup):
-        ctx.run()
+        gpu_step()
     ctx.sync()
     st0 = ctx.stats()
     n_records = sum(ctx.counters(c)["num_records"] for c in range(N_CPUS))
@@ -233,7 +249,7 @@ def main():
     barrier()
     ev0.record(ext)
     for _ in range(args.steps):
-        ctx.run()
+        gpu_step()
     ev1.record(ext)
     ctx.sync()
     barrier()
@@ -243,6 +259,7 @@ def main():
     dec_runs = st1["decode_runs"] - st0["decode_runs"]
     dec_ms = (st1["decode_ms_sum"] - st0["decode_ms_sum"]) / max(1, dec_runs)
     launches_per_step = st1["kernel_launches"]
+    exact_runs = st1["exact_runs"]
 
     # ---- end-to-end leg: host buffers in, host results out ---------------------------------
     out_scaled = torch.empty((N_CPUS, N_BUCKETS, N_EVENTS), dtype=torch.int64, pin_memory=True)
@@ -254,7 +271,7 @@ def main():
         ctx.reset(keep_carry=False)
         for cpu, s in enumerate(streams):
             ctx.submit_image(cpu, s)
-        ctx.run()
+        gpu_step()
         ctx._ck(ctx.L.hbtgpu_get_buckets_host(ctx.h, C.c_void_p(0), C.c_void_p(out_scaled.data_ptr()),
                                               C.c_void_p(out_metric.data_ptr()),
                                               C.c_void_p(out_valid.data_ptr())))

@@ -43,7 +43,7 @@ struct hbtgpu_ctx {
   // device memory
   uint8_t* arena = nullptr;
   uint64_t arena_cap = 0, arena_used = 0;
-  hbtgpu_carry *d_carry_in = nullptr, *d_carry_out = nullptr;
+  hbtgpu_carry *d_carry_in = nullptr, *d_carry_out = nullptr, *d_carry_init = nullptr;
   hbtgpu_head_stub* d_head = nullptr;
   uint64_t* d_counters = nullptr;
   uint64_t* d_acc = nullptr;
@@ -414,6 +414,8 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaMemsetAsync(ctx->arena, 0, ctx->arena_cap + kImageAlign * ns + STAGE_BYTES, ctx->stream));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_carry_in), ns * sizeof(hbtgpu_carry)));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_carry_out), ns * sizeof(hbtgpu_carry)));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_carry_init), ns * sizeof(hbtgpu_carry)));
+  CKC(cudaMemsetAsync(ctx->d_carry_init, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_head), ns * sizeof(hbtgpu_head_stub)));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_counters), ns * C_SLOTS * 8));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_acc), ctx->acc_words * 8));
@@ -443,7 +445,7 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  void* ptrs[] = {ctx->arena, ctx->d_carry_in, ctx->d_carry_out, ctx->d_head, ctx->d_counters,
+  void* ptrs[] = {ctx->arena, ctx->d_carry_in, ctx->d_carry_out, ctx->d_carry_init, ctx->d_head, ctx->d_counters,
                   ctx->d_acc, ctx->d_scaled, ctx->d_metric, ctx->d_valid, ctx->d_flags,
                   ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
                   ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math};
@@ -466,6 +468,8 @@ int hbtgpu_set_carry(hbtgpu_ctx* ctx, uint32_t cpu, const hbtgpu_carry* carry) {
   CK(cudaSetDevice(ctx->device));
   ctx->carry_in[cpu] = *carry;
   CK(cudaMemcpyAsync(&ctx->d_carry_in[cpu], &ctx->carry_in[cpu], sizeof(hbtgpu_carry),
+                     cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(&ctx->d_carry_init[cpu], &ctx->carry_in[cpu], sizeof(hbtgpu_carry),
                      cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   return 0;
@@ -559,6 +563,9 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
   CK(cudaMemsetAsync(ctx->d_flags, force_exact ? 1 : 0, 1, ctx->stream));  // byte 0 of NEED_EXACT
   CK(cudaMemsetAsync(reinterpret_cast<uint8_t*>(ctx->d_flags) + 1, 0, FLAG_COUNT * 4 - 1, ctx->stream));
+  const bool external = (ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY) != 0;
+  // shard mode: every stream starts from an invalid state; the boundary row is added later
+  if (external) CK(cudaMemsetAsync(ctx->d_carry_in, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
   // streams without images keep their carry: carry_out := carry_in
   CK(cudaMemcpyAsync(ctx->d_carry_out, ctx->d_carry_in, ns * sizeof(hbtgpu_carry),
                      cudaMemcpyDeviceToDevice, ctx->stream));
@@ -580,8 +587,14 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
     launches += 3;
     CK(cudaGetLastError());
   }
-  if (int r = launch_derive(ctx)) return r;
-  ++launches;
+  if (external) {
+    k_head<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(P);
+    CK(cudaGetLastError());
+    ++launches;
+  } else {
+    if (int r = launch_derive(ctx)) return r;
+    ++launches;
+  }
   CK(cudaEventRecord(ctx->ev_run1, ctx->stream));
   ctx->stats.kernel_launches = launches;
   ctx->ran = true;
@@ -715,16 +728,89 @@ int hbtgpu_get_buckets_host(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scaled, do
   return 0;
 }
 
-int hbtgpu_get_head_stub(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_head_stub* out) {
-  if (!ctx || !out) return -EINVAL;
-  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
-  return fail(ctx, -ENOSYS, "head stubs: not built yet");
+int hbtgpu_get_stubs(hbtgpu_ctx* ctx, hbtgpu_head_stub* head, hbtgpu_carry* tail) {
+  if (!ctx || !head || !tail) return -EINVAL;
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  if (!(ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY))
+    return fail(ctx, -EINVAL, "context was not created with HBTGPU_F_EXTERNAL_CARRY");
+  CK(cudaSetDevice(ctx->device));
+  const uint32_t ns = ctx->cfg.max_cpus;
+  CK(cudaMemcpyAsync(head, ctx->d_head, ns * sizeof(hbtgpu_head_stub), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(tail, ctx->d_carry_out, ns * sizeof(hbtgpu_carry), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
 }
 
-int hbtgpu_apply_boundary(hbtgpu_ctx* ctx, uint32_t cpu, const hbtgpu_carry* prev_tail) {
-  if (!ctx || !prev_tail) return -EINVAL;
-  (void)cpu;
-  return fail(ctx, -ENOSYS, "boundary rows: not built yet");
+void hbtgpu_compose_tail(const hbtgpu_carry* prev, const hbtgpu_head_stub* head,
+                         const hbtgpu_carry* own_tail, hbtgpu_carry* out) {
+  if (head->has_sample) {
+    *out = *own_tail;  // the last SAMPLE (and any LOST after it) decides, whatever came before
+  } else {
+    hbtgpu_carry t = *prev;  // last_[] survives; a LOST invalidates count_.tstamp
+    if (head->lost_before) {
+      t.valid = 0;
+      t.tstamp = ~0ull;
+    }
+    *out = t;
+  }
+}
+
+int hbtgpu_apply_boundaries(hbtgpu_ctx* ctx, const hbtgpu_carry* prev_tails) {
+  if (!ctx || !prev_tails) return -EINVAL;
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  if (!(ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY))
+    return fail(ctx, -EINVAL, "context was not created with HBTGPU_F_EXTERNAL_CARRY");
+  CK(cudaSetDevice(ctx->device));
+  const uint32_t ns = ctx->cfg.max_cpus;
+  // d_carry_in is free in shard mode (the decode used an invalid state): stage prev_tails there
+  CK(cudaMemcpyAsync(ctx->d_carry_in, prev_tails, ns * sizeof(hbtgpu_carry), cudaMemcpyHostToDevice, ctx->stream));
+  Params P = make_params(ctx);
+  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in);
+  CK(cudaGetLastError());
+  // streams without a SAMPLE pass the previous state through: fix their carry-out on the host side
+  CK(cudaStreamSynchronize(ctx->stream));  // prev_tails may be reused by the caller after this
+  ctx->counters_valid = false;
+  ctx->emitted = false;
+  return launch_derive(ctx);
+}
+
+size_t hbtgpu_stub_bytes(const hbtgpu_ctx* ctx) {
+  return ctx ? static_cast<size_t>(ctx->cfg.max_cpus) * (sizeof(hbtgpu_head_stub) + sizeof(hbtgpu_carry)) : 0;
+}
+
+int hbtgpu_export_stubs_device(hbtgpu_ctx* ctx, void* device_dst) {
+  if (!ctx || !device_dst) return -EINVAL;
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  if (!(ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY))
+    return fail(ctx, -EINVAL, "context was not created with HBTGPU_F_EXTERNAL_CARRY");
+  CK(cudaSetDevice(ctx->device));
+  const size_t ns = ctx->cfg.max_cpus;
+  uint8_t* d = static_cast<uint8_t*>(device_dst);
+  CK(cudaMemcpyAsync(d, ctx->d_head, ns * sizeof(hbtgpu_head_stub), cudaMemcpyDeviceToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(d + ns * sizeof(hbtgpu_head_stub), ctx->d_carry_out, ns * sizeof(hbtgpu_carry),
+                     cudaMemcpyDeviceToDevice, ctx->stream));
+  return 0;
+}
+
+int hbtgpu_apply_boundaries_gathered(hbtgpu_ctx* ctx, const void* device_gathered, uint32_t world,
+                                     uint32_t rank) {
+  if (!ctx || !device_gathered) return -EINVAL;
+  if (rank >= world) return fail(ctx, -EINVAL, "rank %u >= world %u", rank, world);
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  if (!(ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY))
+    return fail(ctx, -EINVAL, "context was not created with HBTGPU_F_EXTERNAL_CARRY");
+  CK(cudaSetDevice(ctx->device));
+  const uint32_t ns = ctx->cfg.max_cpus;
+  Params P = make_params(ctx);
+  // d_carry_in is free in shard mode (the decode used an invalid state): it receives the fold
+  k_fold<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(static_cast<const uint8_t*>(device_gathered), rank,
+                                                    ns, ctx->d_carry_init, ctx->d_carry_in);
+  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in);
+  CK(cudaGetLastError());
+  ctx->counters_valid = false;
+  ctx->emitted = false;
+  ctx->stats.kernel_launches += 3;
+  return launch_derive(ctx);
 }
 
 int hbtgpu_acc_device(hbtgpu_ctx* ctx, void** device_ptr, size_t* bytes) {

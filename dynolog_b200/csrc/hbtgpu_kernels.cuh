@@ -1329,6 +1329,113 @@ __global__ void k_clear(const Params P, uint64_t acc_words) {
 }
 
 // ------------------------------------------------------------------------------------
+// Shard mode (HBTGPU_F_EXTERNAL_CARRY): head stubs and boundary rows.
+
+// One thread per stream: walk from the stream start to its first SAMPLE (normally the very
+// first record).  The stream start is a record boundary, so this walk is exact.
+__global__ void k_head(const Params P) {
+  const uint32_t sidx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (sidx >= P.n_streams) return;
+  hbtgpu_head_stub& hs = P.head[sidx];
+  hs.has_sample = 0;
+  hs.lost_before = 0;
+  hs.offset = 0;
+  const StreamDesc sd = P.streams[sidx];
+  const uint32_t n = P.n_events;
+  for (uint32_t ii = 0; ii < sd.n_images; ++ii) {
+    const ImageDesc im = P.images[sd.first_image + ii];
+    uint64_t pos = 0;
+    while (pos < im.len) {
+      const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + im.base + pos);
+      const uint64_t h = r[0];
+      const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
+      if (size < 8 || (size & 7) || pos + size > im.len) return;  // the decode reports the error
+      if (type == REC_SAMPLE) {
+        if (size < 40 || r[2] != ((size - 40u) >> 3) || r[2] != n) return;
+        hs.tstamp = r[1];
+        hs.te = r[3];
+        hs.tr = r[4];
+        for (uint32_t e = 0; e < n; ++e) hs.value[e] = xform(P, e, r[5 + e]);
+        hs.offset = im.stream_pos + pos;
+        hs.has_sample = 1;
+        return;
+      }
+      if (type == REC_LOST) {
+        if (size < 24) return;
+        hs.lost_before = 1;
+      } else if (type == REC_READ) {
+        if (size < 40 || r[2] != ((size - 40u) >> 3)) return;
+      }
+      pos += size;
+    }
+  }
+}
+
+// Device form of hbtgpu_compose_tail folded over the ranks before `rank`: one thread per cpu.
+// gathered = `world` blocks of [n_streams head stubs | n_streams tails].
+__global__ void k_fold(const uint8_t* gathered, uint32_t rank, uint32_t n_streams,
+                       const hbtgpu_carry* init, hbtgpu_carry* prev_out) {
+  const uint32_t cpu = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cpu >= n_streams) return;
+  const size_t block = static_cast<size_t>(n_streams) * (sizeof(hbtgpu_head_stub) + sizeof(hbtgpu_carry));
+  const hbtgpu_carry* src = &init[cpu];
+  bool invalidated = false;
+  for (uint32_t r = 0; r < rank; ++r) {
+    const uint8_t* b = gathered + static_cast<size_t>(r) * block;
+    const hbtgpu_head_stub& hs = reinterpret_cast<const hbtgpu_head_stub*>(b)[cpu];
+    const hbtgpu_carry* tails =
+        reinterpret_cast<const hbtgpu_carry*>(b + static_cast<size_t>(n_streams) * sizeof(hbtgpu_head_stub));
+    if (hs.has_sample) {
+      src = &tails[cpu];  // a shard with a SAMPLE determines the state by itself
+      invalidated = false;
+    } else if (hs.lost_before) {
+      invalidated = true;  // only LOSTs: count_.tstamp invalid, last_[] kept
+    }
+  }
+  hbtgpu_carry o = *src;
+  if (invalidated) {
+    o.valid = 0;
+    o.tstamp = ~0ull;
+  }
+  prev_out[cpu] = o;
+}
+
+// One block per stream: add the row that straddles the shard boundary.
+__global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_carry* prev_tails) {
+  const uint32_t sidx = blockIdx.x;
+  const hbtgpu_head_stub& hs = P.head[sidx];
+  const hbtgpu_carry& pt = prev_tails[sidx];
+  // handleRecordSample emits a row iff the state is valid when the SAMPLE arrives (:135,165-182)
+  if (!hs.has_sample || hs.lost_before || !pt.valid) return;
+  uint64_t* ctr = P.counters + static_cast<uint64_t>(sidx) * C_SLOTS;
+  if (ctr[C_ERR] != 0 && ctr[C_ERR_OFF] <= hs.offset) return;  // the walk never got this far
+  if (pt.tstamp > hs.tstamp) {  // time regression across the boundary (:156-163)
+    if (threadIdx.x == 0) {
+      ctr[C_ERR] = static_cast<uint64_t>(-1);
+      ctr[C_ERR_OFF] = hs.offset;
+    }
+    return;
+  }
+  const uint32_t n = P.n_events;
+  const uint32_t bk = bucket_of(P, hs.tstamp);
+  if (threadIdx.x == 0) {
+    ctr[C_ROWS] += 1;
+    ctr[C_UNKNOWN] -= 1;  // the shard counted its first SAMPLE as a re-base
+    if (bk == BKT_OOR) ctr[C_OOR] += 1;
+  }
+  if (bk == BKT_OOR) return;
+  uint64_t* base = P.acc + (static_cast<uint64_t>(sidx) * P.n_buckets + bk) * (n + 3);
+  for (uint32_t e = threadIdx.x; e < n + 3; e += blockDim.x) {
+    uint64_t v;
+    if (e < n) v = hs.value[e] - pt.last[e];
+    else if (e == n) v = hs.te - pt.te;
+    else if (e == n + 1) v = hs.tr - pt.tr;
+    else v = 1;
+    red_add(base + e, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------
 // k_derive: per (cpu,bucket): scaled = getCount(acc), metrics = reducers(scaled)
 struct DeriveParams {
   const uint64_t* acc;

@@ -47,8 +47,9 @@ class Carry(C.Structure):
 
 
 class HeadStub(C.Structure):
-    _fields_ = [("has_sample", C.c_uint64), ("lost_before", C.c_uint64), ("tstamp", C.c_uint64),
-                ("te", C.c_uint64), ("tr", C.c_uint64), ("value", C.c_uint64 * MAX_EVENTS)]
+    _fields_ = [("has_sample", C.c_uint64), ("lost_before", C.c_uint64), ("offset", C.c_uint64),
+                ("tstamp", C.c_uint64), ("te", C.c_uint64), ("tr", C.c_uint64),
+                ("value", C.c_uint64 * MAX_EVENTS)]
 
 
 COUNTER_KEYS = ["lost", "comm", "exit", "throttle", "unthrottle", "fork", "sample", "read", "aux",
@@ -83,7 +84,8 @@ ABI_SYMBOLS = [
     "hbtgpu_submit_image", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
     "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows",
     "hbtgpu_get_records", "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_derive",
-    "hbtgpu_get_head_stub", "hbtgpu_apply_boundary", "hbtgpu_acc_device", "hbtgpu_stream",
+    "hbtgpu_get_stubs", "hbtgpu_compose_tail", "hbtgpu_apply_boundaries", "hbtgpu_stub_bytes",
+    "hbtgpu_export_stubs_device", "hbtgpu_apply_boundaries_gathered", "hbtgpu_acc_device", "hbtgpu_stream",
     "hbtgpu_math_get_count", "hbtgpu_math_rate", "hbtgpu_math_add_reduce",
     "hbtgpu_math_tsc_to_ktime", "hbtgpu_math_ktime_to_tsc", "hbtgpu_math_per_second_mega",
     "hbtgpu_math_running_ratio", "hbtgpu_get_stats", "hbtgpu_version",
@@ -118,6 +120,9 @@ def lib():
         L.hbtgpu_destroy.restype = None
         L.hbtgpu_destroy.argtypes = [C.c_void_p]
         L.hbtgpu_noalloc_last_error.restype = C.c_char_p
+        L.hbtgpu_compose_tail.restype = None
+        L.hbtgpu_stub_bytes.restype = C.c_size_t
+        L.hbtgpu_stub_bytes.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -296,13 +301,26 @@ class Context:
         self._ck(self.L.hbtgpu_get_stats(self.h, C.byref(s)))
         return {k: getattr(s, k) for k, _ in Stats._fields_}
 
-    def head_stub(self, cpu):
-        h = HeadStub()
-        self._ck(self.L.hbtgpu_get_head_stub(self.h, C.c_uint32(cpu), C.byref(h)))
-        return h
+    def get_stubs(self):
+        """Shard mode: (head stubs, tails) as ctypes arrays of max_cpus entries."""
+        heads = (HeadStub * self.max_cpus)()
+        tails = (Carry * self.max_cpus)()
+        self._ck(self.L.hbtgpu_get_stubs(self.h, heads, tails))
+        return heads, tails
 
-    def apply_boundary(self, cpu, prev_tail):
-        self._ck(self.L.hbtgpu_apply_boundary(self.h, C.c_uint32(cpu), C.byref(prev_tail)))
+    def stub_bytes(self):
+        return int(self.L.hbtgpu_stub_bytes(self.h))
+
+    def export_stubs_device(self, device_dst):
+        self._ck(self.L.hbtgpu_export_stubs_device(self.h, C.c_void_p(device_dst)))
+
+    def apply_boundaries_gathered(self, device_gathered, world, rank):
+        self._ck(self.L.hbtgpu_apply_boundaries_gathered(self.h, C.c_void_p(device_gathered),
+                                                         C.c_uint32(world), C.c_uint32(rank)))
+
+    def apply_boundaries(self, prev_tails):
+        """prev_tails: ctypes array (Carry * max_cpus): state before this shard, per cpu."""
+        self._ck(self.L.hbtgpu_apply_boundaries(self.h, prev_tails))
 
     # ---- elementwise arithmetic
     def get_count(self, count, te, tr):
@@ -371,3 +389,10 @@ def decode_image_noalloc(cfg, device_image, image_bytes, device_acc, carry_in=No
     if rc != 0:
         raise HbtGpuError(rc, L.hbtgpu_noalloc_last_error().decode())
     return ctr.as_dict(), cout
+
+
+def compose_tail(prev, head, own_tail):
+    """hbtgpu_compose_tail (host only): state after a shard."""
+    out = Carry()
+    lib().hbtgpu_compose_tail(C.byref(prev), C.byref(head), C.byref(own_tail), C.byref(out))
+    return out

@@ -191,22 +191,56 @@ int hbtgpu_derive(hbtgpu_ctx* ctx);
 
 /* ---- multi-GPU (time-window sharding) ---------------------------------------------- */
 
-/* With HBTGPU_F_EXTERNAL_CARRY the first SAMPLE of each stream has its
- * predecessor on the GPU that holds the previous time window.  After run, each
- * rank exports per cpu a head stub (first SAMPLE and whether a LOST precedes
- * it) and a tail stub (state after the last record); ranks exchange stubs
- * (all_gather) and call hbtgpu_apply_boundary with the tail of the previous
- * non-empty rank to add the one row that straddles the shard boundary. */
+/* A capture is sharded by TIME WINDOW: rank r holds window r of every cpu (images start on
+ * record boundaries, so no boundary search crosses GPUs).  With HBTGPU_F_EXTERNAL_CARRY a
+ * context decodes its shard as if every stream started from an invalid state (as after a
+ * LOST): the first SAMPLE of a stream only re-bases.  What is then missing is, per cpu, the ONE
+ * row that straddles the shard boundary.  Protocol (no data-path collective):
+ *   1. every rank: hbtgpu_run, then hbtgpu_get_stubs -> head[cpu], tail[cpu]
+ *   2. all_gather of the stubs (about 1 KB per cpu and rank)
+ *   3. every rank folds the tails of the ranks before it, per cpu, with hbtgpu_compose_tail
+ *      (start value: the state enableImpl() leaves, i.e. what a single-GPU run passes to
+ *      hbtgpu_set_carry)
+ *   4. every rank: hbtgpu_apply_boundaries(prev_tails) adds the boundary rows to its own
+ *      buckets, fixes the counters and runs the derive step.
+ * The union of the ranks' results then equals the single-stream result bit for bit. */
 typedef struct {
-  uint64_t has_sample;  /* stream contains at least one SAMPLE */
-  uint64_t lost_before; /* a LOST precedes the first SAMPLE */
+  uint64_t has_sample;  /* the shard's stream contains at least one SAMPLE */
+  uint64_t lost_before; /* a LOST precedes the first SAMPLE (or: any LOST, if there is no SAMPLE) */
+  uint64_t offset;      /* stream byte offset of the first SAMPLE */
   uint64_t tstamp, te, tr;
   uint64_t value[HBTGPU_MAX_EVENTS]; /* transformed values of the first SAMPLE */
 } hbtgpu_head_stub;
 
-int hbtgpu_get_head_stub(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_head_stub* out);
-/* prev_tail: carry-out of the stream's previous shard (hbtgpu_get_carry there). */
-int hbtgpu_apply_boundary(hbtgpu_ctx* ctx, uint32_t cpu, const hbtgpu_carry* prev_tail);
+/* head and tail: arrays of max_cpus entries (host). tail[cpu] is the carry-out of the shard. */
+int hbtgpu_get_stubs(hbtgpu_ctx* ctx, hbtgpu_head_stub* head, hbtgpu_carry* tail);
+/* Host-only, no GPU work: generator state after a shard, given the state before it (prev),
+ * the shard's head stub and the shard's own carry-out (computed from an invalid state).
+ * Mirrors handleRecordLost / handleRecordSample: a shard with a SAMPLE determines the state by
+ * itself; one without keeps prev, invalidated if it contains a LOST
+ * (PerCpuCountSampleGenerator.h:110-124,135-154,198-199). */
+void hbtgpu_compose_tail(const hbtgpu_carry* prev, const hbtgpu_head_stub* head,
+                         const hbtgpu_carry* own_tail, hbtgpu_carry* out);
+/* prev_tails: max_cpus entries (host), the state before this shard per cpu.  Adds the row
+ * first_sample - prev_tail to the bucket of the first SAMPLE where handleRecordSample would
+ * have emitted it (:165-182), updates num_rows / num_unknown_count_interval / err, then runs
+ * the derive step. Call once per hbtgpu_run. */
+int hbtgpu_apply_boundaries(hbtgpu_ctx* ctx, const hbtgpu_carry* prev_tails);
+
+/* The same exchange without host round trips (what bench.py uses at N > 1): the stubs stay in
+ * device memory, the collective (e.g. ncclAllGather through torch.distributed, enqueued on
+ * hbtgpu_stream) moves them, and the fold runs in a kernel.
+ *   hbtgpu_stub_bytes            size of one rank's stub block: max_cpus heads, then max_cpus tails
+ *   hbtgpu_export_stubs_device   copy this rank's block to device_dst (async, context stream)
+ *   hbtgpu_apply_boundaries_gathered
+ *                                device_gathered = `world` blocks in rank order; folds the tails
+ *                                of ranks < rank starting from the carry set with
+ *                                hbtgpu_set_carry, adds the boundary rows, runs the derive step
+ *                                (all async on the context stream) */
+size_t hbtgpu_stub_bytes(const hbtgpu_ctx* ctx);
+int hbtgpu_export_stubs_device(hbtgpu_ctx* ctx, void* device_dst);
+int hbtgpu_apply_boundaries_gathered(hbtgpu_ctx* ctx, const void* device_gathered, uint32_t world,
+                                     uint32_t rank);
 /* Device address/size of the acc tensor, for a collective (NCCL all-reduce over u64 as i64). */
 int hbtgpu_acc_device(hbtgpu_ctx* ctx, void** device_ptr, size_t* bytes);
 /* The CUDA stream the context launches on (a cudaStream_t). */
