@@ -1,0 +1,239 @@
+// HbtGpuShim.h -- header-only C++ shim over the C ABI (include/hbtgpu.h) that keeps the
+// reference's class shapes for this path, so that code written against hbt reads the same:
+//
+//   reference (hbt/src/perf_event/...)                      shim (namespace hbtgpu_shim)
+//   DataSlice / RbDataSlices      PerfEventsGroup.h:45-62   DataSlice / RbDataSlices
+//   CpuCountSampleGenerator       PerCpuCountSampleGenerator.h:27-231
+//     consume(max) -> ssize_t       PerfEventsGroup.h:1394      CpuCountSampleGenerator::consume
+//     getNumRecord{Lost,...}()      :791-824                    same names
+//     getLastTimeStamp()            gen :209-211                same
+//     getNumEntries()               gen :86-89                  same (rows available)
+//   PerCpuCountSampleGenerator    gen :234-347              PerCpuCountSampleGenerator
+//     getCpuGenerator(cpu)          PerCpuBase.h                same
+//     accumUntil(batch, stop_ts)    PerCpuSampleGeneratorBase.h:69-94   same (decodes everything submitted)
+//   TraceMonitor::applyToCountSamplesAndConsume  mon/TraceMonitor.h:35-108   applyToCountSamples
+//
+// Error conventions follow the reference: the hot path returns negative errno in ssize_t
+// (-ENODATA drained, -EPERM bad record / time regression), argument and environment errors
+// throw (std::invalid_argument like HBT_ARG_CHECK, std::runtime_error like HBT_THROW_ASSERT).
+// The work itself happens on the GPU behind hbtgpu_run; there is no CPU path in here.
+#pragma once
+
+#include <errno.h>
+#include <sys/types.h>
+
+#include <cstdint>
+#include <functional>
+#include <optional>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+extern "C" {
+#include "hbtgpu.h"
+}
+
+namespace hbtgpu_shim {
+
+using CpuId = int;
+using TimeStamp = uint64_t;
+constexpr TimeStamp kInvalidTimeStamp = ~0ull;  // hbt/src/common/System.h:106
+
+struct DataSlice {
+  DataSlice(const void* from, size_t size) : from{from}, size{size} {}
+  const void* from;
+  size_t size;
+};
+
+struct RbDataSlices {
+  RbDataSlices(const void* p1, size_t s1) : first{p1, s1}, second{std::nullopt} {}
+  RbDataSlices(const void* p1, size_t s1, const void* p2, size_t s2)
+      : first{p1, s1}, second{DataSlice{p2, s2}} {}
+  DataSlice first;
+  std::optional<DataSlice> second;
+};
+
+struct TscConversionParams {  // hbt/src/common/System.h:184-188
+  uint16_t time_shift = 0;
+  uint32_t time_mult = 1;
+  uint64_t time_zero = 0;
+};
+
+class PerCpuCountSampleGenerator;
+
+// Per-CPU view; same accessor names as the reference's generator.
+class CpuCountSampleGenerator {
+ public:
+  /// Decode what was submitted for this CPU (all CPUs are decoded together on the GPU).
+  /// Return convention of PerfEventsGroup::consume (:1574-1588): the errno wins whenever
+  /// the ring was drained or a record stalled the walk.
+  ssize_t consume(unsigned max_num_records);
+
+  uint64_t getNumRecordLost() const { return c_.lost; }
+  uint64_t getNumRecordComm() const { return c_.comm; }
+  uint64_t getNumRecordExit() const { return c_.exit; }
+  uint64_t getNumRecordThrottle() const { return c_.throttle; }
+  uint64_t getNumRecordUnThrottle() const { return c_.unthrottle; }
+  uint64_t getNumRecordFork() const { return c_.fork; }
+  uint64_t getNumRecordSample() const { return c_.sample; }
+  uint64_t getNumRecordRead() const { return c_.read; }
+  uint64_t getNumRecordAux() const { return c_.aux; }
+  uint64_t getNumRecordItraceStart() const { return c_.itrace_start; }
+  uint64_t getNumRecordSwitchCpuWide() const { return c_.switch_cpu_wide; }
+  TimeStamp getLastTimeStamp() const { return c_.last_tstamp; }
+  size_t getNumEntries() const { return c_.num_rows; }
+  CpuId getCpu() const { return cpu_; }
+
+ private:
+  friend class PerCpuCountSampleGenerator;
+  CpuCountSampleGenerator(PerCpuCountSampleGenerator* owner, CpuId cpu) : owner_{owner}, cpu_{cpu} {}
+  PerCpuCountSampleGenerator* owner_;
+  CpuId cpu_;
+  hbtgpu_counters c_{};
+};
+
+class PerCpuCountSampleGenerator {
+ public:
+  struct Options {
+    int device = 0;
+    uint32_t num_cpus = 1;
+    std::vector<bool> tsc_to_kernel_time;  // per event: EventValueTransforms::TscToKernelTime
+    TscConversionParams tsc;
+    TimeStamp t0 = 0;
+    uint64_t bucket_ns = 1'000'000;
+    uint32_t n_buckets = 1;
+    size_t arena_bytes = 64u << 20;
+    std::vector<hbtgpu_metric> metrics;
+  };
+
+  PerCpuCountSampleGenerator(const std::vector<std::string>& event_names, const Options& opt)
+      : event_names_{event_names}, opt_{opt} {
+    if (event_names.empty() || event_names.size() > HBTGPU_MAX_EVENTS)
+      throw std::invalid_argument("number of events must be in [1, 64]");  // HBT_ARG_CHECK_LE, gen :76
+    hbtgpu_config cfg{};
+    cfg.device = opt.device;
+    cfg.n_events = static_cast<uint32_t>(event_names.size());
+    for (size_t i = 0; i < opt.tsc_to_kernel_time.size() && i < event_names.size(); ++i)
+      if (opt.tsc_to_kernel_time[i]) cfg.tsc_mask |= 1ull << i;
+    cfg.time_shift = opt.tsc.time_shift;
+    cfg.time_mult = opt.tsc.time_mult;
+    cfg.time_zero = opt.tsc.time_zero;
+    cfg.max_cpus = opt.num_cpus;
+    cfg.n_buckets = opt.n_buckets;
+    cfg.t0 = opt.t0;
+    cfg.bucket_ns = opt.bucket_ns;
+    cfg.arena_bytes = opt.arena_bytes;
+    cfg.n_metrics = static_cast<uint32_t>(opt.metrics.size());
+    if (cfg.n_metrics > HBTGPU_MAX_METRICS) throw std::invalid_argument("too many metrics");
+    for (uint32_t m = 0; m < cfg.n_metrics; ++m) cfg.metrics[m] = opt.metrics[m];
+    int rc = hbtgpu_create(&cfg, &ctx_);
+    if (rc == -EINVAL) throw std::invalid_argument(hbtgpu_last_error(nullptr));
+    if (rc != 0) throw std::runtime_error(hbtgpu_last_error(nullptr));
+    for (uint32_t c = 0; c < opt.num_cpus; ++c) gens_.push_back(CpuCountSampleGenerator(this, static_cast<CpuId>(c)));
+  }
+  ~PerCpuCountSampleGenerator() { hbtgpu_destroy(ctx_); }
+  PerCpuCountSampleGenerator(const PerCpuCountSampleGenerator&) = delete;
+  PerCpuCountSampleGenerator& operator=(const PerCpuCountSampleGenerator&) = delete;
+
+  size_t getNumEvents() const { return event_names_.size(); }
+  const std::vector<std::string>& getEventNicknames() const { return event_names_; }
+
+  /// State enableImpl() leaves (gen :91-106): interval starts at `now`, last_ = 0.
+  void enable(CpuId cpu, TimeStamp now) {
+    hbtgpu_carry c{};
+    c.valid = 1;
+    c.tstamp = now;
+    check(hbtgpu_set_carry(ctx_, static_cast<uint32_t>(cpu), &c));
+  }
+
+  /// The callback to hand to PerfEventsGroup::onCpuDataBufferRead (:1592-1637).
+  void onCpuDataBufferRead(CpuId cpu, const RbDataSlices& s) {
+    check(hbtgpu_submit_image(ctx_, static_cast<uint32_t>(cpu), s.first.from, s.first.size,
+                              s.second ? s.second->from : nullptr, s.second ? s.second->size : 0));
+    decoded_ = false;
+  }
+
+  CpuCountSampleGenerator& getCpuGenerator(CpuId cpu) { return gens_.at(static_cast<size_t>(cpu)); }
+
+  /// PerCpuSampleGeneratorBase::accumUntil (:69-94): consume every CPU until drained; returns
+  /// the number of CPUs that finished without an unexpected error; throws on one, as the
+  /// reference does (HBT_THROW_ASSERT_IF, :76-79).
+  unsigned accumUntil(unsigned batch_size, TimeStamp /*stop_ts*/) {
+    if (batch_size == 0) throw std::invalid_argument("batch_size must be > 0");  // HBT_ARG_CHECK_GT
+    unsigned done = 0;
+    for (auto& g : gens_) {
+      ssize_t ret = g.consume(batch_size);
+      if (ret < 0 && ret != -ENODATA && ret != -EAGAIN)
+        throw std::runtime_error("Unexpected error processing batch: " + std::to_string(ret));
+      ++done;
+    }
+    return done;
+  }
+
+  /// TraceMonitor::applyToCountSamplesAndConsume (mon/TraceMonitor.h:35-108):
+  /// func(cpu, count_idx, nicknames, tstamp, duration, counts, n)
+  using CountFunc = std::function<void(CpuId, size_t, const std::vector<std::string>&, TimeStamp,
+                                       TimeStamp, const uint64_t*, size_t)>;
+  void applyToCountSamples(const CountFunc& func) {
+    decode();
+    const size_t n = getNumEvents();
+    std::vector<uint64_t> rows;
+    for (auto& g : gens_) {
+      size_t have = 0;
+      check(hbtgpu_get_rows(ctx_, static_cast<uint32_t>(g.cpu_), nullptr, 0, &have));
+      rows.resize(have * (n + 2));
+      if (have) check(hbtgpu_get_rows(ctx_, static_cast<uint32_t>(g.cpu_), rows.data(), have, &have));
+      for (size_t i = 0; i < have; ++i) {
+        const uint64_t* r = &rows[i * (n + 2)];
+        func(g.cpu_, i, event_names_, r[0], r[1], r + 2, n);
+      }
+    }
+  }
+
+  /// Bucketed aggregates (scaled counts, metrics, validity) on the host.
+  void getBuckets(std::vector<uint64_t>* acc, std::vector<uint64_t>* scaled, std::vector<double>* metric,
+                  std::vector<uint32_t>* valid) {
+    decode();
+    const size_t cells = static_cast<size_t>(opt_.num_cpus) * opt_.n_buckets, n = getNumEvents();
+    if (acc) acc->resize(cells * (n + 3));
+    if (scaled) scaled->resize(cells * n);
+    if (metric) metric->resize(cells * opt_.metrics.size());
+    if (valid) valid->resize(cells);
+    check(hbtgpu_get_buckets_host(ctx_, acc ? acc->data() : nullptr, scaled ? scaled->data() : nullptr,
+                                  metric && !metric->empty() ? metric->data() : nullptr,
+                                  valid ? valid->data() : nullptr));
+  }
+
+  hbtgpu_ctx* raw() { return ctx_; }
+
+ private:
+  friend class CpuCountSampleGenerator;
+  void check(int rc) {
+    if (rc == -EINVAL) throw std::invalid_argument(hbtgpu_last_error(ctx_));
+    if (rc != 0) throw std::runtime_error(hbtgpu_last_error(ctx_));
+  }
+  void decode() {
+    if (decoded_) return;
+    check(hbtgpu_run(ctx_));
+    check(hbtgpu_sync(ctx_));
+    for (auto& g : gens_) check(hbtgpu_get_counters(ctx_, static_cast<uint32_t>(g.cpu_), &g.c_));
+    decoded_ = true;
+  }
+
+  std::vector<std::string> event_names_;
+  Options opt_;
+  hbtgpu_ctx* ctx_ = nullptr;
+  std::vector<CpuCountSampleGenerator> gens_;
+  bool decoded_ = false;
+};
+
+inline ssize_t CpuCountSampleGenerator::consume(unsigned max_num_records) {
+  if (max_num_records == 0) return 0;
+  owner_->decode();
+  if (c_.err < 0) return static_cast<ssize_t>(c_.err);  // stalled on a bad record: -EPERM
+  // everything submitted was walked: the ring is drained, and consume() reports that as
+  // -ENODATA instead of the count (quirk at :1574-1588)
+  return -ENODATA;
+}
+
+}  // namespace hbtgpu_shim

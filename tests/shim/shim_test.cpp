@@ -1,0 +1,129 @@
+// Reference-shaped test of the C++ shim (dynolog_b200/shim/HbtGpuShim.h): written the way
+// hbt/src/perf_event/tests/PerCpuGeneratorsTest.cpp:53-88 drives a generator -- feed the ring,
+// consume(), check ret >= 0 || ret == -ENODATA and the getNumRecord*() counters -- but on a
+// synthetic ring image with known answers (the survey's probe: 10 SAMPLE + LOST(3) + THROTTLE
+// => samples 10, lost 3, throttle 1, 9 rows).
+#include <cassert>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "HbtGpuShim.h"
+
+using namespace hbtgpu_shim;
+
+static void put(std::vector<uint8_t>& b, uint64_t v) {
+  for (int i = 0; i < 8; ++i) b.push_back((v >> (8 * i)) & 255);
+}
+static uint64_t hdr(uint32_t type, uint32_t size) { return type | (uint64_t(size) << 48); }
+
+#define EXPECT(cond)                                                       \
+  do {                                                                     \
+    if (!(cond)) {                                                         \
+      std::fprintf(stderr, "EXPECT failed: %s (line %d)\n", #cond, __LINE__); \
+      return 1;                                                            \
+    }                                                                      \
+  } while (0)
+
+int main() {
+  std::vector<uint8_t> ring;
+  for (int i = 0; i < 10; ++i) {
+    put(ring, hdr(9, 72));
+    put(ring, 1000 + 100 * i);  // time
+    put(ring, 4);               // nr
+    put(ring, 100 * i);         // time_enabled
+    put(ring, 50 * i);          // time_running: multiplexed at 50 %
+    for (int e = 0; e < 4; ++e) put(ring, 10 * i * (e + 1));
+    if (i == 4) {
+      put(ring, hdr(2, 24));  // LOST
+      put(ring, 7);
+      put(ring, 3);
+    }
+  }
+  put(ring, hdr(5, 32));  // THROTTLE
+  put(ring, 5);
+  put(ring, 7);
+  put(ring, 9);
+
+  PerCpuCountSampleGenerator::Options opt;
+  opt.num_cpus = 2;
+  opt.t0 = 1000;
+  opt.bucket_ns = 300;
+  opt.n_buckets = 4;
+  opt.metrics.push_back(hbtgpu_metric{HBTGPU_METRIC_RATE, 2, {1, 0}});
+  PerCpuCountSampleGenerator gen({"cycles", "instructions", "llc_misses", "branch_misses"}, opt);
+  gen.enable(0, 900);
+
+  // the ring wrapped: hand over the image as two slices, as onCpuDataBufferRead would (:1626-1632)
+  const size_t cut = 72 * 3;
+  gen.onCpuDataBufferRead(0, RbDataSlices(ring.data(), cut, ring.data() + cut, ring.size() - cut));
+
+  auto& g0 = gen.getCpuGenerator(0);
+  ssize_t ret = g0.consume(1000);
+  EXPECT(ret >= 0 || ret == -ENODATA);  // PerCpuGeneratorsTest.cpp:77
+  EXPECT(g0.getNumRecordSample() == 10);
+  EXPECT(g0.getNumRecordLost() == 3);  // SUM of num_lost
+  EXPECT(g0.getNumRecordThrottle() == 1);
+  EXPECT(g0.getNumRecordUnThrottle() == 0);
+  EXPECT(g0.getNumEntries() == 9);
+  EXPECT(g0.getLastTimeStamp() == 1900);
+  EXPECT(gen.getCpuGenerator(1).getNumRecordSample() == 0);
+  EXPECT(gen.accumUntil(100, 0) == 2);
+
+  size_t n_rows = 0;
+  uint64_t first[6] = {0};
+  gen.applyToCountSamples([&](CpuId cpu, size_t idx, const std::vector<std::string>& names, TimeStamp ts,
+                              TimeStamp dur, const uint64_t* counts, size_t n) {
+    if (cpu == 0 && idx == 1) {
+      first[0] = ts;
+      first[1] = dur;
+      for (size_t i = 0; i < n && i < 4; ++i) first[2 + i] = counts[i];
+    }
+    (void)names;
+    ++n_rows;
+  });
+  EXPECT(n_rows == 9);
+  EXPECT(first[0] == 1000 && first[1] == 100 && first[2] == 10 && first[5] == 40);
+
+  std::vector<uint64_t> acc, scaled;
+  std::vector<double> metric;
+  std::vector<uint32_t> valid;
+  gen.getBuckets(&acc, &scaled, &metric, &valid);
+  // bucket 0 of cpu 0 = [1000,1300): rows at 1000 (from 900), 1100, 1200 -> cycles 0+10+10,
+  // dTE = 200, dTR = 100 -> scaled = 20 * 200 / 100 = 40 (GroupReadValues::getCount)
+  EXPECT(acc[0] == 20 && acc[4] == 200 && acc[5] == 100 && acc[6] == 3);
+  EXPECT(scaled[0] == 40 && scaled[1] == 80);
+  EXPECT(valid[0] == 1 && metric[0] == 2.0);  // instructions / cycles
+
+  // a malformed record stalls the walk with -EPERM, like consume() (:1502-1507)
+  PerCpuCountSampleGenerator bad({"a", "b"}, PerCpuCountSampleGenerator::Options{});
+  std::vector<uint8_t> r2;
+  put(r2, hdr(9, 56));
+  put(r2, 10);
+  put(r2, 2);
+  put(r2, 1);
+  put(r2, 1);
+  put(r2, 5);
+  put(r2, 6);
+  put(r2, hdr(9, 64));  // size says 3 values, nr says 2
+  for (int i = 0; i < 7; ++i) put(r2, 2);
+  bad.onCpuDataBufferRead(0, RbDataSlices(r2.data(), r2.size()));
+  EXPECT(bad.getCpuGenerator(0).consume(10) == -EPERM);
+  EXPECT(bad.getCpuGenerator(0).getNumRecordSample() == 1);
+  bool threw = false;
+  try {
+    bad.accumUntil(10, 0);
+  } catch (const std::runtime_error&) {
+    threw = true;  // accumUntil throws on unexpected errors (:76-79)
+  }
+  EXPECT(threw);
+  threw = false;
+  try {
+    PerCpuCountSampleGenerator none({}, PerCpuCountSampleGenerator::Options{});
+  } catch (const std::invalid_argument&) {
+    threw = true;
+  }
+  EXPECT(threw);
+  std::puts("SHIM OK");
+  return 0;
+}

@@ -1,0 +1,132 @@
+"""-m gpu: BASELINE.json configurations at their full sizes.  The C oracle is fast enough
+(all host cores) to check them completely: every bucket sum, counter and carry bit-exact, plus
+size-independent properties (telescoping identity: the sums over all buckets equal last - first
+counter values; n_rows adds up; decode of window shards equals decode of the whole)."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+hbtgpu = pytest.importorskip("dynolog_b200.hbtgpu")
+from dynolog_b200 import synth  # noqa: E402
+
+
+def _run_gpu(streams, n, nb, t0, bns, flags=0, metrics=()):
+    total = sum(len(s) for s in streams)
+    g = hbtgpu.Context(n_events=n, max_cpus=len(streams), n_buckets=nb, t0=t0, bucket_ns=bns,
+                       arena_bytes=total + 256 * len(streams) + (1 << 20), flags=flags, metrics=metrics)
+    carry = hbtgpu.make_carry(valid=True, tstamp=t0, last=[0] * n)
+    for cpu, s in enumerate(streams):
+        g.set_carry(cpu, carry)
+        g.submit_image(cpu, s)
+    g.run()
+    g.sync()
+    return g
+
+
+def _check_against_oracle(g, port, streams, n, nb, t0, bns, threads=16):
+    p = po.make_params(n, n_buckets=nb, t0=t0, bucket_ns=bns)
+    carries = [po.make_carry(valid=True, tstamp=t0, last=[0] * n) for _ in streams]
+    _, acc, ctrs = port.run_capture(p, streams, carries, n_threads=threads)
+    b = g.buckets(want_metric=False, want_valid=False)
+    assert np.array_equal(b["acc"], acc), "bucket sums differ from the oracle"
+    for cpu in range(len(streams)):
+        assert g.counters(cpu) == ctrs[cpu], f"cpu {cpu}: counters differ"
+    # scaled counts: check a slice of cpus completely
+    for cpu in range(0, len(streams), max(1, len(streams) // 8)):
+        assert np.array_equal(b["scaled"][cpu], port.scale_buckets(p, acc[cpu]))
+    return acc, ctrs
+
+
+def test_cfg1_4mib_ring_with_forged_headers(port_oracle):
+    for forge in (0, 10_000):
+        spec, streams = synth.capture(1, 1, max_bytes_per_cpu=4 << 20, forge_ppm=forge)
+        g = _run_gpu(streams, 4, 6000, synth.T_START, 1_000_000)
+        try:
+            _check_against_oracle(g, port_oracle, streams, 4, 6000, synth.T_START, 1_000_000, threads=1)
+            p = po.make_params(4, n_buckets=6000, t0=synth.T_START, bucket_ns=1_000_000)
+            exp = port_oracle.decode_stream(p, streams[0], po.make_carry(valid=True, tstamp=synth.T_START,
+                                                                        last=[0] * 4))
+            for a, e in zip(g.records(0), exp["records"]):
+                assert np.array_equal(a, e)  # every record boundary
+            assert np.array_equal(g.rows(0), exp["rows"])
+        finally:
+            g.close()
+
+
+def test_cfg2_192cpu_full_capture(port_oracle):
+    n, nb, t0, bns = 8, 10_100, synth.T_START, 1_000_000
+    spec, streams = synth.capture(2, 192, n_samples=100_000)
+    g = _run_gpu(streams, n, nb, t0, bns, metrics=[(hbtgpu.METRIC_RATE, [0, 1])])
+    try:
+        assert g.stats()["exact_runs"] == 0
+        acc, ctrs = _check_against_oracle(g, port_oracle, streams, n, nb, t0, bns)
+        # telescoping identity per cpu: sum over buckets == last sample's counters (carry started at 0)
+        for cpu in (0, 95, 191):
+            co = g.carry(cpu)
+            tot = acc[cpu].sum(axis=0, dtype=np.uint64)
+            oor = ctrs[cpu]["rows_out_of_range"]
+            assert ctrs[cpu]["num_rows"] == 100_000 and int(tot[n + 2]) + oor == 100_000
+            if oor == 0:
+                assert [int(x) for x in tot[:n]] == [int(co.last[i]) for i in range(n)]
+                assert int(tot[n]) == int(co.te)
+    finally:
+        g.close()
+
+
+def test_cfg3_multiplexed_lost_throttle_4gib(port_oracle):
+    n, bns, t0 = 8, 1_000_000, synth.T_START
+    per_cpu = 64 << 20
+    spec, streams = synth.capture(3, 64, max_bytes_per_cpu=per_cpu)
+    nb = 70_000
+    g = _run_gpu(streams, n, nb, t0, bns)
+    try:
+        assert g.stats()["exact_runs"] == 0
+        acc, ctrs = _check_against_oracle(g, port_oracle, streams, n, nb, t0, bns)
+        assert sum(c["lost"] for c in ctrs) > 10_000 and sum(c["throttle"] for c in ctrs) > 1_000
+        assert all(c["err"] == 0 for c in ctrs)
+    finally:
+        g.close()
+
+
+def test_cfg5_windows_sharded_equals_whole(port_oracle):
+    """Windows contiguous in time per cpu; 2 emulated ranks x 3 windows of 16 MiB x 12 cpus."""
+    from dynolog_b200 import shard
+    n, bns, t0, ncpu, W = 8, 1_000_000, synth.T_START, 12, 6
+    cap = synth.Capture(synth.make_spec(5), ncpu)
+    windows = [[s.copy() for s in cap.window(max_bytes_per_cpu=16 << 20)] for _ in range(W)]
+    whole = [np.concatenate([windows[w][c] for w in range(W)]) for c in range(ncpu)]
+    nb = 110_000
+    p = po.make_params(n, n_buckets=nb, t0=t0, bucket_ns=bns)
+    carries = [po.make_carry(valid=True, tstamp=t0, last=[0] * n) for _ in range(ncpu)]
+    _, acc_ref, ctr_ref = port_oracle.run_capture(p, whole, carries, n_threads=12)
+    initial = (hbtgpu.Carry * ncpu)()
+    for c in range(ncpu):
+        initial[c] = hbtgpu.make_carry(valid=True, tstamp=t0, last=[0] * n)
+    ctxs = []
+    try:
+        for r in range(2):
+            ws = windows[3 * r:3 * r + 3]
+            total = sum(len(s) for w in ws for s in w)
+            g = hbtgpu.Context(n_events=n, max_cpus=ncpu, n_buckets=nb, t0=t0, bucket_ns=bns,
+                               arena_bytes=total + (1 << 20), flags=hbtgpu.F_EXTERNAL_CARRY)
+            for w in ws:  # several images per cpu, submitted window by window
+                for c in range(ncpu):
+                    g.submit_image(c, w[c])
+            g.run()
+            g.sync()
+            ctxs.append(g)
+        stubs = [g.get_stubs() for g in ctxs]
+        acc = np.zeros_like(acc_ref)
+        rows = 0
+        for r, g in enumerate(ctxs):
+            g.apply_boundaries(shard.fold_prev_tails(stubs, initial, r))
+            g.sync()
+            acc += g.buckets(want_scaled=False, want_metric=False, want_valid=False)["acc"]
+            rows += sum(g.counters(c)["num_rows"] for c in range(ncpu))
+    finally:
+        for g in ctxs:
+            g.close()
+    assert np.array_equal(acc, acc_ref)
+    assert rows == sum(c["num_rows"] for c in ctr_ref)
