@@ -526,6 +526,7 @@ __device__ __forceinline__ uint32_t bucket_of(const Params& P, uint64_t ts) {
 }
 
 __device__ __forceinline__ uint64_t xform(const Params& P, uint32_t e, uint64_t v) {
+  if (P.tsc_mask == 0) return v;  // uniform: no event is transformed (the usual case)
   return ((P.tsc_mask >> e) & 1ull) ? tsc_to_ktime(v, P.time_shift, P.time_mult, P.time_zero) : v;
 }
 
@@ -837,7 +838,6 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
   const bool two = F <= 16;
   const uint32_t e0 = two ? (lane & 15) : lane;
   const uint32_t woff0 = e0 < n ? 5 + e0 : (e0 == n ? 3 : 4);
-  const uint64_t cfield0 = e0 < n ? C.last[e0] : (e0 == n ? C.te : C.tr);
   uint64_t* const acc_s = P.acc + static_cast<uint64_t>(tc.stream) * P.n_buckets * F;
 #pragma unroll
   for (int g = 0; g < MAXG; ++g) {
@@ -873,14 +873,13 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
         const int j = j0 + src;
         const uint32_t p = entry + j * S;
         uint32_t e = e0, woff = woff0;
-        uint64_t cfield = cfield0;
         for (;;) {
           if (e < F) {
             uint64_t v;
             if (e == n + 2) {
               v = static_cast<uint64_t>(static_cast<int64_t>(j));  // ordinal; -1 for the carry
             } else if (j < 0) {
-              v = cfield;  // carry values are already transformed
+              v = e < n ? C.last[e] : (e == n ? C.te : C.tr);  // carry values are already transformed
             } else {
               v = buf[p + woff];
               if (any_tsc && e < n) v = xform(P, e, v);
@@ -891,7 +890,6 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
           if (two || e + 32 >= F) break;
           e += 32;  // n > 13: a lane serves several fields
           woff = e < n ? 5 + e : (e == n ? 3 : 4);
-          cfield = e < n ? C.last[e] : (e == n ? C.te : C.tr);
         }
       }
     }
@@ -1006,16 +1004,57 @@ __global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
       mbar_wait(&s.bar[0], phase[0]);
       phase[0] ^= 1;
       const uint64_t* hb = s.data[0];
-      const uint32_t K = classify(s, hb, hw);
-      uint32_t start = 0xFFFFFFFFu;
-      if (K > 0) {
-        if (cd.flags & CH_HALO_EXACT_START) start = 0;
-        else start = scout_start(s, hb, hw, K);
-      }
       load_carry(s, P, cd.stream, PRED_UNKNOWN, 0);
-      __syncthreads();
       entry_abs = chunk_abs;
-      if (start == 0xFFFFFFFFu) {
+      // Quick scout: the last word of the halo that looks like a SAMPLE header of the configured
+      // group, confirmed by the record before it, and whose record reaches the chunk.  It is a
+      // guess like any other -- k_verify proves or refutes it against the previous chunk.
+      bool quick = false;
+      if (!P.force_general && !(cd.flags & CH_FIRST_OF_IMAGE)) {
+        const uint32_t n = P.n_events, S = 5 + n;
+        const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
+        if (threadIdx.x == 0) s.red_key = 0;
+        __syncthreads();
+        const uint32_t w = threadIdx.x;  // hw <= HALO_WORDS == NT
+        const bool m = w < hw && (hb[w] & 0xFFFF0000FFFFFFFFull) == want && hb[w + 2] == n;
+        const uint32_t bal = __ballot_sync(0xffffffffu, m);
+        if ((threadIdx.x & 31) == 0 && bal) atomicMax(&s.red_key, (threadIdx.x & ~31u) + (31 - __clz(bal)) + 1);
+        __syncthreads();
+        const uint32_t wl = s.red_key;  // 1 + last matching word, 0 if none
+        if (wl != 0) {
+          const uint32_t p = wl - 1;
+          const bool confirmed = p >= S && (hb[p - S] & 0xFFFF0000FFFFFFFFull) == want && hb[p - S + 2] == n &&
+                                 hb[p - S + 1] <= hb[p + 1];
+          if (confirmed && p + S >= hw) {
+            quick = true;
+            entry_abs = cd.halo_off + 8ull * (p + S);
+            Carry& C0 = s.c[0];
+            for (uint32_t e = threadIdx.x; e < n; e += NT) C0.last[e] = xform(P, e, hb[p + 5 + e]);
+            if (threadIdx.x == 0) {
+              C0.ts = hb[p + 1];
+              C0.te = hb[p + 3];
+              C0.tr = hb[p + 4];
+              C0.valid = 1;
+              C0.gap = 0;
+              C0.last_off = cd.halo_off + 8ull * p;
+            }
+          }
+        }
+        __syncthreads();
+      }
+      uint32_t K = 0;
+      uint32_t start = 0xFFFFFFFFu;
+      if (!quick) {
+        K = classify(s, hb, hw);
+        if (K > 0) {
+          if (cd.flags & CH_HALO_EXACT_START) start = 0;
+          else start = scout_start(s, hb, hw, K);
+        }
+      }
+      __syncthreads();
+      if (quick) {
+        // nothing more to do
+      } else if (start == 0xFFFFFFFFu) {
         bad = WHY_HALO_NO_START;
       } else {
         recover_chain(s, hb, hw, K, start, P.force_general != 0);
