@@ -269,8 +269,7 @@ def main():
 
     def e2e_step():
         ctx.reset(keep_carry=False)
-        for cpu, s in enumerate(streams):
-            ctx.submit_image(cpu, s)
+        ctx.submit_images(list(range(N_CPUS)), streams)
         gpu_step()
         ctx._ck(ctx.L.hbtgpu_get_buckets_host(ctx.h, C.c_void_p(0), C.c_void_p(out_scaled.data_ptr()),
                                               C.c_void_p(out_metric.data_ptr()),

@@ -255,8 +255,14 @@ int launch_derive(hbtgpu_ctx* ctx) {
   D.n_events = ctx->cfg.n_events;
   D.n_metrics = ctx->cfg.n_metrics;
   memcpy(D.metrics, ctx->cfg.metrics, sizeof(D.metrics));
+  D.n_magic = ((1ull << 32) + D.n_events - 1) / D.n_events;
   const uint64_t blocks = (ctx->n_cells + 255) / 256;
-  k_derive<<<static_cast<unsigned>(blocks), 256, 0, ctx->stream>>>(D);
+  if (D.n_events <= 16) {
+    const size_t smem = static_cast<size_t>(DERIVE_CELLS) * (D.n_events + 3) * 8;  // <= 38.9 KB
+    k_derive_tiled<<<static_cast<unsigned>(blocks), DERIVE_CELLS, smem, ctx->stream>>>(D);
+  } else {
+    k_derive<<<static_cast<unsigned>(blocks), 256, 0, ctx->stream>>>(D);
+  }
   CK(cudaGetLastError());
   return 0;
 }
@@ -507,6 +513,37 @@ int hbtgpu_submit_image(hbtgpu_ctx* ctx, uint32_t cpu, const void* first, size_t
   ctx->images.push_back(HostImage{base, n, cpu});
   ctx->arena_used = base + n;
   ctx->table_dirty = true;
+  return 0;
+}
+
+int hbtgpu_submit_images(hbtgpu_ctx* ctx, size_t n, const uint32_t* cpus, const void* const* images,
+                         const size_t* sizes) {
+  if (!ctx) return -EINVAL;
+  if (n && (!cpus || !images || !sizes)) return fail(ctx, -EINVAL, "null argument");
+  CK(cudaSetDevice(ctx->device));
+  // validate everything first so that a failure leaves the context unchanged
+  uint64_t used = ctx->arena_used;
+  for (size_t i = 0; i < n; ++i) {
+    if (cpus[i] >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpus[i]);
+    if (sizes[i] % 8) return fail(ctx, -EINVAL, "image size %zu is not a multiple of 8", sizes[i]);
+    if (sizes[i] && !images[i]) return fail(ctx, -EINVAL, "null image");
+    if (!sizes[i]) continue;
+    const uint64_t b = (used + kImageAlign - 1) / kImageAlign * kImageAlign;
+    if (b + sizes[i] > ctx->arena_cap + kImageAlign * ctx->cfg.max_cpus)
+      return fail(ctx, -ENOSPC, "arena full: %llu + %zu > %llu bytes", (unsigned long long)b, sizes[i],
+                  (unsigned long long)ctx->arena_cap);
+    used = b + sizes[i];
+  }
+  for (size_t i = 0; i < n; ++i) {
+    if (!sizes[i]) continue;
+    uint64_t base;
+    if (int r = reserve_image(ctx, cpus[i], sizes[i], &base)) return r;
+    CK(cudaMemcpyAsync(ctx->arena + base, images[i], sizes[i], cudaMemcpyHostToDevice, ctx->stream));
+    ctx->images.push_back(HostImage{base, sizes[i], cpus[i]});
+    ctx->arena_used = base + sizes[i];
+  }
+  ctx->table_dirty = true;
+  CK(cudaStreamSynchronize(ctx->stream));  // the caller may overwrite the rings after this
   return 0;
 }
 

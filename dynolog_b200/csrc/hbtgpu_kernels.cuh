@@ -1483,6 +1483,7 @@ struct DeriveParams {
   uint32_t* valid;
   uint64_t n_cells;  // cpus * buckets
   uint32_t n_events, n_metrics;
+  uint64_t n_magic;  // ceil(2^32 / n_events): x / n == (x * n_magic) >> 32 for x < 2^16
   hbtgpu_metric metrics[HBTGPU_MAX_METRICS];
 };
 
@@ -1494,14 +1495,9 @@ __device__ __forceinline__ double add_reduce_int(const uint64_t* v, uint32_t k) 
   return static_cast<double>(acc);
 }
 
-__global__ void __launch_bounds__(256) k_derive(const DeriveParams D) {
-  const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= D.n_cells) return;
-  const uint32_t n = D.n_events;
-  const uint64_t* a = D.acc + i * (n + 3);
-  const uint64_t te = a[n], tr = a[n + 1];
-  uint64_t* sc = D.scaled + i * n;
-  for (uint32_t e = 0; e < n; ++e) sc[e] = get_count(a[e], te, tr);
+// metrics of one cell from its scaled counts `sc` (any address space) and accumulated time_running
+__device__ __forceinline__ uint32_t derive_metrics(const DeriveParams& D, const uint64_t* sc, uint64_t tr,
+                                                   double* out_row) {
   uint32_t vmask = 0;
   for (uint32_t m = 0; m < D.n_metrics; ++m) {
     const hbtgpu_metric& md = D.metrics[m];
@@ -1530,10 +1526,48 @@ __global__ void __launch_bounds__(256) k_derive(const DeriveParams D) {
       out = static_cast<double>(f);
       ok = true;
     }
-    D.metric[i * D.n_metrics + m] = out;
+    out_row[m] = out;
     if (ok) vmask |= 1u << m;
   }
-  D.valid[i] = vmask;
+  return vmask;
+}
+
+// generic form: one thread per cell, straight from global memory (any n_events)
+__global__ void __launch_bounds__(256) k_derive(const DeriveParams D) {
+  const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= D.n_cells) return;
+  const uint32_t n = D.n_events;
+  const uint64_t* a = D.acc + i * (n + 3);
+  const uint64_t te = a[n], tr = a[n + 1];
+  uint64_t* sc = D.scaled + i * n;
+  for (uint32_t e = 0; e < n; ++e) sc[e] = get_count(a[e], te, tr);
+  D.valid[i] = derive_metrics(D, sc, tr, D.metric + i * D.n_metrics);
+}
+
+// tiled form (n_events <= 16): a block stages the accumulators of 256 cells with coalesced
+// loads, each thread scales its cell in shared memory, the scaled counts leave coalesced again
+constexpr int DERIVE_CELLS = 256;
+__global__ void __launch_bounds__(DERIVE_CELLS) k_derive_tiled(const DeriveParams D) {
+  extern __shared__ __align__(16) uint64_t dsm[];  // [DERIVE_CELLS][n + 3]
+  const uint32_t n = D.n_events, F = n + 3;
+  const uint64_t cell0 = static_cast<uint64_t>(blockIdx.x) * DERIVE_CELLS;
+  const uint32_t cells = static_cast<uint32_t>(umin64(DERIVE_CELLS, D.n_cells - cell0));
+  const uint64_t* src = D.acc + cell0 * F;
+  for (uint32_t i = threadIdx.x; i < cells * F; i += DERIVE_CELLS) dsm[i] = src[i];
+  __syncthreads();
+  if (threadIdx.x < cells) {
+    uint64_t* a = dsm + threadIdx.x * F;
+    const uint64_t te = a[n], tr = a[n + 1];
+    for (uint32_t e = 0; e < n; ++e) a[e] = get_count(a[e], te, tr);
+    const uint64_t i = cell0 + threadIdx.x;
+    D.valid[i] = derive_metrics(D, a, tr, D.metric + i * D.n_metrics);
+  }
+  __syncthreads();
+  uint64_t* dst = D.scaled + cell0 * n;
+  for (uint32_t o = threadIdx.x; o < cells * n; o += DERIVE_CELLS) {
+    const uint32_t c = static_cast<uint32_t>((static_cast<uint64_t>(o) * D.n_magic) >> 32);
+    dst[o] = dsm[c * F + (o - c * n)];
+  }
 }
 
 // ------------------------------------------------------------------------------------

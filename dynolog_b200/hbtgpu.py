@@ -81,7 +81,7 @@ class Stats(C.Structure):
 # every symbol include/hbtgpu.h declares (tests check that the library exports them all)
 ABI_SYMBOLS = [
     "hbtgpu_create", "hbtgpu_destroy", "hbtgpu_last_error", "hbtgpu_set_carry",
-    "hbtgpu_submit_image", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
+    "hbtgpu_submit_image", "hbtgpu_submit_images", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
     "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows",
     "hbtgpu_get_records", "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_derive",
     "hbtgpu_get_stubs", "hbtgpu_compose_tail", "hbtgpu_apply_boundaries", "hbtgpu_stub_bytes",
@@ -214,6 +214,15 @@ class Context:
             p2 = _ptr(second)
         self._ck(self.L.hbtgpu_submit_image(self.h, C.c_uint32(cpu), _ptr(first),
                                             C.c_size_t(first.size), p2, C.c_size_t(n2)))
+
+    def submit_images(self, cpus, arrays):
+        """One call for many images (array order = submission order)."""
+        n = len(cpus)
+        arrays = [np.ascontiguousarray(a, dtype=np.uint8) for a in arrays]
+        c = (C.c_uint32 * n)(*cpus)
+        ptrs = (C.c_void_p * n)(*[a.ctypes.data for a in arrays])
+        sizes = (C.c_size_t * n)(*[a.size for a in arrays])
+        self._ck(self.L.hbtgpu_submit_images(self.h, C.c_size_t(n), c, ptrs, sizes))
 
     def submit_image_ptr(self, cpu, host_ptr, nbytes):
         self._ck(self.L.hbtgpu_submit_image(self.h, C.c_uint32(cpu), C.c_void_p(host_ptr),

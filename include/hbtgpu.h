@@ -141,6 +141,12 @@ int hbtgpu_set_carry(hbtgpu_ctx* ctx, uint32_t cpu, const hbtgpu_carry* carry);
 int hbtgpu_submit_image(hbtgpu_ctx* ctx, uint32_t cpu, const void* first, size_t n1,
                         const void* second, size_t n2);
 
+/* Several images in one call (e.g. every cpu's slice from TraceCollector::onCpusDataBufferRead,
+ * hbt/src/mon/TraceCollector.h:406-420): same contract as n calls of hbtgpu_submit_image in
+ * array order, but the copies are queued back to back and waited for once. */
+int hbtgpu_submit_images(hbtgpu_ctx* ctx, size_t n, const uint32_t* cpus, const void* const* images,
+                         const size_t* sizes);
+
 /* Same, for an image that already lives in device memory (copied D2D). */
 int hbtgpu_submit_image_device(hbtgpu_ctx* ctx, uint32_t cpu, const void* device_ptr, size_t n);
 

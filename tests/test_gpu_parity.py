@@ -237,6 +237,27 @@ def test_rerun_and_reset(port_oracle):
         assert np.array_equal(a1 + a2, whole["buckets"])
 
 
+def test_submit_images_batch(port_oracle):
+    """hbtgpu_submit_images == the same images submitted one by one."""
+    n = 2
+    streams = [rg.random_stream(600 + i, 3000 + 500 * i, n, p_lost=0.01)[0] for i in range(4)]
+    p = po.make_params(n, n_buckets=64, t0=1_000_000_000, bucket_ns=10_000_000)
+    total = sum(len(s) for s in streams)
+    with hbtgpu.Context(n_events=n, max_cpus=3, n_buckets=64, t0=p.t0, bucket_ns=p.bucket_ns,
+                        arena_bytes=total + 65536) as g:
+        # cpu 1 gets two images (one stream), cpu 0 and 2 one each
+        g.submit_images([1, 0, 1, 2], [streams[0], streams[1], streams[2], streams[3]])
+        g.run()
+        g.sync()
+        acc = g.buckets()["acc"]
+        exp1 = port_oracle.decode_stream(p, np.concatenate([streams[0], streams[2]]), po.make_carry())
+        assert np.array_equal(acc[1], exp1["buckets"])
+        assert np.array_equal(acc[0], port_oracle.decode_stream(p, streams[1], po.make_carry())["buckets"])
+        assert g.counters(2) == port_oracle.decode_stream(p, streams[3], po.make_carry())["counters"]
+        with pytest.raises(hbtgpu.HbtGpuError):
+            g.submit_images([0, 9], [streams[0], streams[1]])  # bad cpu: nothing is submitted
+
+
 def test_argument_errors():
     with pytest.raises(hbtgpu.HbtGpuError) as e:
         hbtgpu.Context(n_events=0)
