@@ -785,17 +785,21 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
 // lane 31 holds the right neighbour, so transitions are found with shuffles and the only block
 // barrier is the vote that the whole tile is uniform.  The carry is read from s.c[cur] and the
 // new one written to s.c[cur^1]; the caller's end-of-tile barrier publishes it.
-// Returns false (no side effects) if the tile is not uniform; the caller then takes the
-// general path.
-__device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uint64_t* buf,
-                                             uint32_t wt, uint32_t entry, const TileCtx& tc,
-                                             uint32_t cur, uint32_t& exit_word) {
+// Returns how many records from `entry` on were proven and committed: all of them for a
+// uniform tile, else the run up to the first record that is something else (possibly 0); the
+// caller deals with that record (odd_record) and calls again behind it.  Nothing is committed
+// for records at or after the first mismatch.
+__device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, const uint64_t* buf,
+                                                    uint32_t wt, uint32_t entry, const TileCtx& tc,
+                                                    uint32_t cur, uint32_t& k_all) {
   const Carry& C = s.c[cur];
   const uint32_t n = P.n_events;
   const uint32_t S = 5 + n;  // words per SAMPLE
   const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
   // records whose header lies inside the tile: ceil((wt - entry) / S) by multiply-shift
-  const int K = static_cast<int>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
+  const int Kall = static_cast<int>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
+  k_all = static_cast<uint32_t>(Kall);
+  int K = Kall;
   const bool link0 = C.valid != 0 && C.gap == 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int OWN = 31;  // records owned per warp-iteration (lanes 0..30)
@@ -805,8 +809,8 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
 
   // pass 1: check every record, compute its bucket
   uint32_t bk_[MAXG];
-  int ok = 1;
-  uint32_t regress = 0xFFFFFFFFu;
+  int first_bad = 0x7FFFFFFF;   // first record index that is not such a SAMPLE (this lane's view)
+  int regress = 0x7FFFFFFF;     // first record index whose row would go back in time
 #pragma unroll
   for (int g = 0; g < MAXG; ++g) {
     const int j0 = (g * NWARP + warp) * OWN - 1;  // first item of this warp-iteration
@@ -817,7 +821,8 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
     if (jr >= 0 && jr < K) {
       const uint32_t p = entry + jr * S;
       // misc (bits 32..47) is free; type and size must match, and so must nr
-      if (lane < 31 && ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + 2] != n)) ok = 0;
+      if (lane < 31 && ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + 2] != n))
+        first_bad = min(first_bad, jr);
       ts = buf[p + 1];
       bk_[g] = bucket_of(P, ts);
     } else if (jr == -1) {
@@ -825,11 +830,19 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
     }
     const uint64_t nts = __shfl_down_sync(0xffffffffu, ts, 1);
     // row jr+1 exists and goes back in time (gen :156-163)
-    if (lane < 31 && jr + 1 < K && (jr >= 0 || link0) && ts > nts)
-      regress = min(regress, entry + (jr + 1) * S);
+    if (lane < 31 && jr + 1 < K && (jr >= 0 || link0) && ts > nts) regress = min(regress, jr + 1);
   }
-  if (!__syncthreads_and(ok)) return false;
-  if (regress != 0xFFFFFFFFu) atomicMin(&s.tile_err, regress);
+  if (!__syncthreads_and(first_bad == 0x7FFFFFFF)) {
+    // not uniform to the end: agree on the first record that breaks the run
+    if (threadIdx.x == 0) s.red_key = static_cast<uint32_t>(Kall);
+    __syncthreads();
+    if (first_bad != 0x7FFFFFFF) atomicMin(&s.red_key, static_cast<uint32_t>(first_bad));
+    __syncthreads();
+    K = static_cast<int>(s.red_key);
+    __syncthreads();  // red_key may be reused right away
+    if (K == 0) return 0;
+  }
+  if (regress < K) atomicMin(&s.tile_err, entry + regress * S);
 
   // pass 2
   uint32_t n_oor = 0;
@@ -913,8 +926,34 @@ __device__ __forceinline__ bool uniform_tile(Smem& s, const Params& P, const uin
       s.cnt[C_UNKNOWN] += link0 ? 0 : 1;
     }
   }
-  exit_word = entry + K * S;
-  return true;
+  return static_cast<uint32_t>(K);
+}
+
+// The record at word `ew` is not a SAMPLE of the configured group.  If it is a well-formed
+// record of another type, account for it exactly as consume() does (LOST: sum num_lost and
+// invalidate the interval, :1440-1450 / gen :110-124; THROTTLE/UNTHROTTLE: count, :1476-1487;
+// READ: size check, :1515-1530; anything else: skip by size, :1565-1570) and return its size in
+// words; else return 0 and let the general path (which owns the error reporting) look at it.
+__device__ __forceinline__ uint32_t odd_record(Smem& s, const uint64_t* buf, uint32_t ew, uint32_t cur) {
+  const uint64_t h = buf[ew];
+  const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
+  if (size < 8 || (size & 7) || type == REC_SAMPLE) return 0;
+  if (type == REC_LOST && size < 24) return 0;
+  if (type == REC_READ && (size < 40 || buf[ew + 2] != ((size - 40u) >> 3))) return 0;
+  if (threadIdx.x == 0) {
+    s.cnt[C_RECORDS] += 1;
+    if (type == REC_LOST) {
+      s.lost_sum += buf[ew + 2];
+      s.c[cur].gap = 1;
+    } else if (type == REC_THROTTLE) {
+      s.cnt[C_THROTTLE] += 1;
+    } else if (type == REC_UNTHROTTLE) {
+      s.cnt[C_UNTHROTTLE] += 1;
+    } else if (type == REC_READ) {
+      s.cnt[C_READ] += 1;
+    }
+  }
+  return size >> 3;
 }
 
 // Initialise the carry from a predecessor SAMPLE in global memory / the stream carry-in.
@@ -1128,12 +1167,33 @@ __global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
       tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base);
       uint32_t term_kind = 0, term_tgt = 0;
       bool done = false;
+      uint32_t ew = entry;  // chain position, tile-relative words
       if (MODE == MODE_AGG && !P.force_general) {
-        done = uniform_tile(s, P, buf, wt, entry, tc, cur, term_tgt);
-        if (done) cur ^= 1;
+        // runs of configured SAMPLEs in parallel, the few other records in between one by one;
+        // a tile with many of those goes to the general path
+        const uint32_t S = 5 + P.n_events;
+        for (int odd = 0;;) {
+          uint32_t k_all = 0;
+          const uint32_t k = uniform_segment(s, P, buf, wt, ew, tc, cur, k_all);
+          if (k) cur ^= 1;
+          ew += k * S;
+          if (k == k_all) {  // ran to the end of the tile
+            done = true;
+            break;
+          }
+          __syncthreads();  // the segment's carry is published
+          const uint32_t sz = (++odd <= 8) ? odd_record(s, buf, ew, cur) : 0;
+          if (sz == 0) break;
+          ew += sz;
+          __syncthreads();  // thread 0's update of the carry (gap) is visible
+          if (ew >= wt) {
+            done = true;
+            break;
+          }
+        }
+        term_tgt = ew;
       }
       if (!done) {
-        uint32_t ew = entry;  // chain position, tile-relative words
         for (uint32_t w0 = 0; w0 < wt && term_kind == 0; w0 += GT_WORDS) {
           const uint32_t wh = min(static_cast<uint32_t>(GT_WORDS), wt - w0);
           if (ew >= w0 + wh) continue;  // a long record jumps over this sub-tile
