@@ -9,6 +9,7 @@
 #include <errno.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -126,8 +127,13 @@ int build_table(hbtgpu_ctx* ctx) {
   for (auto& im : ctx->images) total += im.len;
   // enough chunks to fill 148 SMs several times over, but not smaller than one tile
   uint64_t target = total / (148ull * 12ull);
+  uint64_t cap = 512ull << 10;
+  if (const char* e = getenv("HBTGPU_CHUNK_KB")) {  // tuning knob
+    const long kb = atol(e);
+    if (kb >= 16 && kb <= 4096) cap = static_cast<uint64_t>(kb) << 10;
+  }
   uint64_t cb = TILE_BYTES;
-  while (cb < target && cb < (256ull << 10)) cb <<= 1;
+  while (cb < target && cb < cap) cb <<= 1;
   ctx->chunk_bytes = cb;
 
   std::vector<std::vector<uint32_t>> per_stream(ns);
@@ -161,7 +167,7 @@ int build_table(hbtgpu_ctx* ctx) {
         } else if (prev) {
           uint64_t hb = prev->len > HALO_BYTES ? prev->len - HALO_BYTES : 0;
           if (hb == 0) cd.flags |= CH_HALO_EXACT_START;
-          hb &= ~15ull;  // TMA source must be 16-byte aligned
+          if (hb & 15ull) hb += 8;  // TMA source must be 16-byte aligned (and the halo <= HALO_BYTES)
           cd.halo_off = prev->base + hb;
           cd.halo_len = static_cast<uint32_t>(prev->len - hb);
         } else {
@@ -1145,7 +1151,7 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
   // chunks: as many as fill the GPU, never more than the static table holds
   uint64_t cb = TILE_BYTES;
   const uint64_t target = image_bytes / (148ull * 12ull);
-  while (cb < target && cb < (256ull << 10)) cb <<= 1;
+  while (cb < target && cb < (512ull << 10)) cb <<= 1;
   while ((image_bytes + cb - 1) / cb > kNaMaxChunks) cb <<= 1;
   const uint32_t nc = static_cast<uint32_t>((image_bytes + cb - 1) / cb);
 

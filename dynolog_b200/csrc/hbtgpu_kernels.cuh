@@ -32,14 +32,17 @@
 
 namespace hbtgpu {
 
-constexpr int NT = 256;  // threads per CTA
+#ifndef HBT_NT
+#define HBT_NT 256
+#endif
+constexpr int NT = HBT_NT;  // threads per CTA
 constexpr int NWARP = NT / 32;
 constexpr int TILE_BYTES = 16384;
 constexpr int TILE_WORDS = TILE_BYTES / 8;
 constexpr int OV_BYTES = 576;  // >= 40 + 8*64: any SAMPLE/READ/LOST whose header is in the tile is fully staged
 constexpr int STAGE_BYTES = TILE_BYTES + OV_BYTES;
 constexpr int STAGE_WORDS = STAGE_BYTES / 8;
-constexpr int HALO_BYTES = 2048;
+constexpr int HALO_BYTES = NT * 8;  // one halo word per thread (scout_start, quick scout)
 constexpr int HALO_WORDS = HALO_BYTES / 8;
 // The general path (classify + pointer jumping + scan) works on sub-tiles of GT_WORDS words so
 // that its per-candidate arrays stay small (shared memory decides how many CTAs fit on an SM).
@@ -803,7 +806,7 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   const bool link0 = C.valid != 0 && C.gap == 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int OWN = 31;  // records owned per warp-iteration (lanes 0..30)
-  constexpr int MAXG = 2;  // K + 1 <= 342 items <= MAXG * NWARP * OWN = 496
+  constexpr int MAXG = (342 + NWARP * OWN - 1) / (NWARP * OWN);  // K + 1 <= 342 items
   const uint32_t F = n + 3;
   const bool any_tsc = P.tsc_mask != 0;
 
@@ -992,8 +995,11 @@ __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t st
   }
 }
 
+#ifndef HBT_MINB
+#define HBT_MINB 4
+#endif
 template <bool SPEC, int MODE>
-__global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
+__global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   if (!SPEC && MODE == MODE_AGG && P.flags[FLAG_NEED_EXACT] == 0) return;  // exact pass not needed
@@ -1020,6 +1026,17 @@ __global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
   uint64_t entry_abs;
   const uint64_t chunk_abs = cd.img_base + cd.begin;
   uint64_t limit_abs = cd.img_base + cd.img_len;
+  const uint64_t img_end_abs = cd.img_base + cd.img_len;
+  const uint32_t avail_rel = static_cast<uint32_t>(umin64((img_end_abs - chunk_abs + 15ull) & ~15ull, 0xFFFFFFF0ull));
+  const uint8_t* const chunk_ptr = P.arena + chunk_abs;
+  auto issue = [&](uint32_t tile_rel, uint32_t b) {
+    const uint32_t bytes = min(avail_rel - tile_rel, static_cast<uint32_t>(STAGE_BYTES));
+    mbar_expect_tx(&s.bar[b], bytes);
+    tma_load_1d(s.data[b], chunk_ptr + tile_rel, bytes, &s.bar[b]);
+  };
+  // tile t lives in buffer (t + boff) & 1; with a halo in buffer 0 the first tile is fetched
+  // into buffer 1 at once, so the two DRAM latencies at the start of a chunk overlap
+  uint32_t boff = 0, n_issued = 0, n_waited = 0;
   if (SPEC) {
     if (cd.halo_len == 0) {
       entry_abs = chunk_abs;
@@ -1039,7 +1056,10 @@ __global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
         }
         mbar_expect_tx(&s.bar[0], bytes);
         tma_load_1d(s.data[0], P.arena + cd.halo_off, bytes, &s.bar[0]);
+        issue(0, 1);
       }
+      boff = 1;
+      n_issued = 1;
       mbar_wait(&s.bar[0], phase[0]);
       phase[0] ^= 1;
       const uint64_t* hb = s.data[0];
@@ -1127,30 +1147,21 @@ __global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
     __syncthreads();
   }
 
-  // ---- tiles ----  (positions are chunk-relative bytes in 32 bits: a chunk is <= 256 KiB and a
+  // ---- tiles ----  (positions are chunk-relative bytes in 32 bits: a chunk is <= 1 MiB and a
   // record can leave it by at most 64 KiB)
-  const uint64_t img_end_abs = cd.img_base + cd.img_len;
   const uint64_t chunk_end_abs = min(cd.img_base + cd.end, limit_abs);
   TileCtx tc{0, 0, cd.stream, 0, 0, io.row_base, io.rec_base};
   const bool any_work = entry_abs < chunk_end_abs;  // also false for exact-mode "skip" (~0)
   const uint32_t chunk_len = any_work ? static_cast<uint32_t>(chunk_end_abs - chunk_abs) : 0;
   const uint32_t limit_rel = static_cast<uint32_t>(umin64(limit_abs - chunk_abs, 0xFFFFFFF0ull));
-  const uint32_t avail_rel = static_cast<uint32_t>(umin64((img_end_abs - chunk_abs + 15ull) & ~15ull, 0xFFFFFFF0ull));
   uint32_t next_rel = any_work ? static_cast<uint32_t>(entry_abs - chunk_abs) : 0;
-  const uint8_t* const chunk_ptr = P.arena + chunk_abs;
 
-  auto issue = [&](uint32_t tile_rel, uint32_t b) {
-    const uint32_t bytes = min(avail_rel - tile_rel, static_cast<uint32_t>(STAGE_BYTES));
-    mbar_expect_tx(&s.bar[b], bytes);
-    tma_load_1d(s.data[b], chunk_ptr + tile_rel, bytes, &s.bar[b]);
-  };
-  uint32_t n_issued = 0, n_waited = 0;
-  if (any_work) {
-    if (threadIdx.x == 0) issue(0, 0);
+  if (any_work && n_issued == 0) {
+    if (threadIdx.x == 0) issue(0, boff);
     n_issued = 1;
   }
   for (uint32_t tile_rel = 0; tile_rel < chunk_len; tile_rel += TILE_BYTES) {
-    const uint32_t b = (tile_rel / TILE_BYTES) & 1;
+    const uint32_t b = ((tile_rel / TILE_BYTES) + boff) & 1;
     if (tile_rel + TILE_BYTES < chunk_len) {
       if (threadIdx.x == 0) issue(tile_rel + TILE_BYTES, b ^ 1);
       ++n_issued;
@@ -1223,7 +1234,7 @@ __global__ void __launch_bounds__(NT, 4) k_decode(const Params P) {
     __syncthreads();  // buffer b is free for the tile after next; publishes the new carry
   }
   // never exit with a bulk copy still in flight into this CTA's shared memory
-  if (n_waited < n_issued) mbar_wait(&s.bar[n_waited & 1], phase[n_waited & 1]);
+  if (n_waited < n_issued) mbar_wait(&s.bar[(n_waited + boff) & 1], phase[(n_waited + boff) & 1]);
   const uint64_t next_abs = any_work ? chunk_abs + next_rel : entry_abs;
 
   // ---- publish ----
