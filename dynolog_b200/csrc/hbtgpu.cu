@@ -867,6 +867,10 @@ void* hbtgpu_stream(hbtgpu_ctx* ctx) { return ctx ? ctx->stream : nullptr; }
 
 int hbtgpu_get_stats(hbtgpu_ctx* ctx, hbtgpu_stats* out) {
   if (!ctx || !out) return -EINVAL;
+  if (ctx->ran && !ctx->counters_valid) {  // exact_runs / exact_reason come from device flags
+    CK(cudaSetDevice(ctx->device));
+    if (int r = fetch_counters(ctx)) return r;
+  }
   *out = ctx->stats;
   return 0;
 }

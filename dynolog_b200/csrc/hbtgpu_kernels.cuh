@@ -474,45 +474,67 @@ __device__ __forceinline__ void recover_chain(Smem& s, const uint64_t* buf, uint
   __syncthreads();
 }
 
-// For the halo: choose the candidate whose chain (a) leaves the halo and (b) is longest.
+// For the halo: choose the candidate whose chain (a) leaves the halo, (b) holds the most
+// records that look exactly like what this capture contains (a SAMPLE of the configured group,
+// a 24-byte LOST, a 32-byte THROTTLE/UNTHROTTLE) and (c) is longest.  Criterion (b) matters for
+// counters whose values happen to carry a plausible size in their top 16 bits: such a counter
+// forms a false chain in lock step with the true one, equally long, but made of records of
+// nonsense types.  A wrong pick is only a lost bet: k_verify refutes it.
 // K <= HALO_WORDS <= NT so one candidate per thread.  Returns the word position or ~0.
-__device__ __forceinline__ uint32_t scout_start(Smem& s, const uint64_t* buf, uint32_t wt,
-                                                uint32_t K) {
+__device__ __forceinline__ uint32_t scout_start(Smem& s, const Params& P, const uint64_t* buf,
+                                                uint32_t wt, uint32_t K) {
   build_links(s, buf, wt, K);
   const uint32_t j = threadIdx.x;
-  uint32_t t = 0, h = 0;
+  uint32_t t = 0, h = 0, own = 0;  // h, own: (plausible records << 16) | hops
   if (j < K) {
+    const uint32_t p = s.pos[j];
+    const uint64_t hd = buf[p];
+    const uint32_t type = static_cast<uint32_t>(hd), size = static_cast<uint32_t>(hd >> 48);
+    const uint32_t n = P.n_events;
+    const bool plausible = (type == REC_SAMPLE && size == 40 + 8 * n && buf[p + 2] == n) ||
+                           (type == REC_LOST && size == 24) ||
+                           ((type == REC_THROTTLE || type == REC_UNTHROTTLE) && size == 32);
+    own = (plausible ? 0x10000u : 0u) | 1u;
     const uint16_t nx = s.u.ch.jump[0][j];
     t = (nx >= NX_DEAD) ? j : nx;
-    h = (nx >= NX_DEAD) ? 0 : 1;
+    h = (nx >= NX_DEAD) ? 0 : own;  // weight of [j, t[j]); the terminal's own weight is added last
   }
-  // t[j] -> terminal candidate of j's chain, h[j] -> hops to it (jump[1] holds t, next holds h)
+  // t[j] -> terminal candidate of j's chain (jump[1] holds t, bkt holds h)
   for (int r = 0; r < 9; ++r) {
     if (j < K) {
       s.u.ch.jump[1][j] = static_cast<uint16_t>(t);
-      s.next[j] = static_cast<uint16_t>(h);
+      s.next[j] = static_cast<uint16_t>(h & 0xFFFFu);
+      s.fl[j] = static_cast<uint8_t>(h >> 16);  // plausible count < 256
     }
     __syncthreads();
     uint32_t t2 = t, h2 = 0;
     if (j < K) {
       t2 = s.u.ch.jump[1][t];
-      h2 = s.next[t];
+      h2 = s.next[t] | (static_cast<uint32_t>(s.fl[t]) << 16);
     }
     __syncthreads();
     t = t2;
     h += h2;
   }
+  // add the terminal's own weight: publish `own`, read the terminal's
+  if (j < K) {
+    s.next[j] = static_cast<uint16_t>(own & 0xFFFFu);
+    s.fl[j] = static_cast<uint8_t>(own >> 16);
+  }
   if (threadIdx.x == 0) s.red_key = 0;
   __syncthreads();
   if (j < K && s.u.ch.jump[0][t] == NX_EXIT) {
-    const uint32_t key = ((h + 1) << 16) | (0xFFFFu - j);  // longest chain, then earliest
-    atomicMax(&s.red_key, key);
+    h += s.next[t] | (static_cast<uint32_t>(s.fl[t]) << 16);
+    const uint32_t plaus = h >> 16, hops = h & 0xFFFFu;
+    // most plausible records, then longest chain, then earliest start
+    const uint32_t key = (min(plaus, 1023u) << 20) | (min(hops, 1023u) << 10) | (1023u - j);
+    atomicMax(&s.red_key, key + 1);
   }
   __syncthreads();
   const uint32_t key = s.red_key;
   __syncthreads();
   if (key == 0) return 0xFFFFFFFFu;
-  return s.pos[0xFFFFu - (key & 0xFFFFu)];
+  return s.pos[1023u - ((key - 1) & 1023u)];
 }
 
 __device__ __forceinline__ uint32_t bucket_of(const Params& P, uint64_t ts) {
@@ -1107,7 +1129,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
         K = classify(s, hb, hw);
         if (K > 0) {
           if (cd.flags & CH_HALO_EXACT_START) start = 0;
-          else start = scout_start(s, hb, hw, K);
+          else start = scout_start(s, P, hb, hw, K);
         }
       }
       __syncthreads();
@@ -1332,6 +1354,7 @@ __global__ void __launch_bounds__(RES_WARPS * 32) k_resolve(const Params P) {
     uint32_t ch = im.first_chunk;
     const uint32_t ch_end = im.first_chunk + im.n_chunks;
     uint64_t pos = 0;  // image-relative
+    uint64_t next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;  // lane 0's copy is the live one
     while (true) {
       const bool more = !stopped && pos < im.len;
       if (!__shfl_sync(0xffffffffu, more, 0)) break;
@@ -1349,13 +1372,14 @@ __global__ void __launch_bounds__(RES_WARPS * 32) k_resolve(const Params P) {
           const uint32_t type = static_cast<uint32_t>(h);
           const uint32_t size = static_cast<uint32_t>(h >> 48);
           // hand the chunks that begin at or before this record their entry
-          while (ch < ch_end && P.chunks[ch].begin <= pos) {
+          while (pos >= next_begin) {
             ChunkIO& io = P.io[ch];
             io.in_entry = im.base + pos;
             io.in_pred = last_off;
             io.in_gap = gap;
             io.limit = ~0ull;
             ++ch;
+            next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
           }
           bool bad = size < 8 || (size & 7) || pos + size > im.len;  // fences, see DESIGN.md
           uint64_t nr = 0, ts = 0;

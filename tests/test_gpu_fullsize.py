@@ -90,6 +90,26 @@ def test_cfg3_multiplexed_lost_throttle_4gib(port_oracle):
         g.close()
 
 
+def test_forged_counters_keep_speculation(port_oracle):
+    """Counters whose values carry a plausible record size in their top bits form false chains in
+    lock step with the true one.  Results must be exact, and the speculative pass should still
+    hold (it prefers chains made of records this capture can contain)."""
+    n, bns, t0 = 8, 1_000_000, synth.T_START
+    spec, streams = synth.capture(3, 8, max_bytes_per_cpu=8 << 20, forge_ppm=10_000)
+    g = _run_gpu(streams, n, 9000, t0, bns)
+    try:
+        _check_against_oracle(g, port_oracle, streams, n, 9000, t0, bns, threads=8)
+        assert g.stats()["exact_runs"] == 0, g.stats()
+    finally:
+        g.close()
+    g = _run_gpu(streams, n, 9000, t0, bns, flags=hbtgpu.F_FORCE_GENERAL)
+    try:
+        _check_against_oracle(g, port_oracle, streams, n, 9000, t0, bns, threads=8)
+        assert g.stats()["exact_runs"] == 0, g.stats()
+    finally:
+        g.close()
+
+
 def test_cfg5_windows_sharded_equals_whole(port_oracle):
     """Windows contiguous in time per cpu; 2 emulated ranks x 3 windows of 16 MiB x 12 cpus."""
     from dynolog_b200 import shard
