@@ -46,10 +46,13 @@ constexpr int HALO_BYTES = NT * 8;  // one halo word per thread (scout_start, qu
 constexpr int HALO_WORDS = HALO_BYTES / 8;
 // The general path (classify + pointer jumping + scan) works on sub-tiles of GT_WORDS words so
 // that its per-candidate arrays stay small (shared memory decides how many CTAs fit on an SM).
-constexpr int GT_WORDS = 1024;
+#ifndef HBT_GT_WORDS
+#define HBT_GT_WORDS 512
+#endif
+constexpr int GT_WORDS = HBT_GT_WORDS;
 constexpr int MAXC = GT_WORDS;    // worst case: every word is a candidate header
 constexpr int WPT = GT_WORDS / NT;  // words classified per thread (4)
-static_assert(WPT * NWARP == 32, "classify() scans one (round, warp) count per lane");
+static_assert(WPT * NWARP <= 32 && WPT >= 1, "classify() scans one (round, warp) count per lane");
 
 constexpr uint16_t IDX_NONE = 0xFFFF;
 constexpr uint16_t NX_EXIT = 0xFFFF;  // chain leaves the tile
@@ -342,15 +345,15 @@ __device__ __forceinline__ uint32_t classify(Smem& s, const uint64_t* buf, uint3
   }
   __syncthreads();
   if (warp == 0) {
-    // exclusive scan of the 32 counts in (round, warp) order: one per lane
-    const uint32_t v = s.wcnt[lane];
+    // exclusive scan of the (up to 32) counts in (round, warp) order: one per lane
+    const uint32_t v = lane < WPT * NWARP ? s.wcnt[lane] : 0;
     uint32_t incl = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
       if (lane >= d) incl += y;
     }
-    s.wcnt[lane] = incl - v;
+    if (lane < WPT * NWARP) s.wcnt[lane] = incl - v;
     if (lane == 31) s.wcnt[WPT * NWARP] = incl;
   }
   __syncthreads();
@@ -1018,7 +1021,7 @@ __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t st
 }
 
 #ifndef HBT_MINB
-#define HBT_MINB 4
+#define HBT_MINB 5
 #endif
 template <bool SPEC, int MODE>
 __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
