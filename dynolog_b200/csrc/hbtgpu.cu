@@ -624,7 +624,7 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
       k_verify<<<static_cast<unsigned>((nc + 255) / 256), 256, 0, ctx->stream>>>(P);
       ++launches;
     }
-    k_resolve<<<(ns + RES_WARPS - 1) / RES_WARPS, RES_WARPS * 32, 0, ctx->stream>>>(P);
+    k_resolve<<<ns, RES_THREADS, 0, ctx->stream>>>(P);
     k_clear<<<148 * 4, 256, 0, ctx->stream>>>(P, force_exact ? 0 : ctx->acc_words);
     k_decode<false, MODE_AGG><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
     launches += 3;
@@ -1205,7 +1205,7 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
       k_decode<true, MODE_AGG><<<nc, NT, sizeof(Smem), st>>>(P);
       k_verify<<<(nc + 255) / 256, 256, 0, st>>>(P);
     }
-    k_resolve<<<1, RES_WARPS * 32, 0, st>>>(P);
+    k_resolve<<<1, RES_THREADS, 0, st>>>(P);
     k_clear<<<148 * 4, 256, 0, st>>>(P, force_exact ? 0 : acc_words);
     k_decode<false, MODE_AGG><<<nc, NT, sizeof(Smem), st>>>(P);
   }

@@ -1329,19 +1329,36 @@ __global__ void k_verify(const Params P) {
 // k_resolve: exact sequential walk, one warp per stream (lane 0 walks; the warp stages
 // 4 KiB windows into shared memory so the dependent loads hit on-chip memory).
 constexpr int RES_WIN_BYTES = 4096;
-constexpr int RES_WARPS = 4;
+constexpr int RES_OV_BYTES = 64;  // header + the fields the walk reads (time, nr / num_lost)
+constexpr int RES_THREADS = 32;   // one walker (lane 0) per block
 
-__global__ void __launch_bounds__(RES_WARPS * 32) k_resolve(const Params P) {
+// k_resolve: exact sequential walk, one walker per stream.  Windows of 4 KiB (+64 B overlap) are
+// brought into shared memory with TMA bulk copies, double buffered, so the dependent loads of
+// the walk hit on-chip memory while the next window is in flight.
+__global__ void __launch_bounds__(RES_THREADS) k_resolve(const Params P) {
   if (P.flags[FLAG_NEED_EXACT] == 0) return;
-  __shared__ __align__(16) uint64_t win[RES_WARPS][RES_WIN_BYTES / 8 + 80];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t sidx = blockIdx.x * RES_WARPS + warp;
+  __shared__ __align__(128) uint64_t win[2][(RES_WIN_BYTES + RES_OV_BYTES) / 8];
+  __shared__ __align__(8) uint64_t bar[2];
+  const uint32_t sidx = blockIdx.x;
   if (sidx >= P.n_streams) return;
+  // The whole warp runs the walk with identical state (reads of shared memory are broadcasts);
+  // lane 0 alone issues copies and writes results.  Runs of configured SAMPLEs are skipped 32
+  // records at a time: lane l tests the record at pos + l*S.
+  const uint32_t lane = threadIdx.x;
+  const bool writer = lane == 0;
+  if (writer) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  uint32_t phase[2] = {0, 0};
+  const uint32_t S8 = 8 * (5 + P.n_events);  // bytes of a configured SAMPLE
+  const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S8) << 48);
   const StreamDesc sd = P.streams[sidx];
   const uint32_t n = P.n_events;
   uint64_t* ctr = P.counters + static_cast<uint64_t>(sidx) * C_SLOTS;
 
-  // walker state (lane 0)
   const hbtgpu_carry& cin = P.carry_in[sidx];
   bool valid = cin.valid != 0;        // count_.tstamp != kInvalidTimeStamp
   uint64_t st_ts = cin.tstamp;        // count_.tstamp
@@ -1350,108 +1367,159 @@ __global__ void __launch_bounds__(RES_WARPS * 32) k_resolve(const Params P) {
   int64_t err = 0;
   uint64_t err_off = 0;
   bool stopped = false;
-  constexpr int WIN_WORDS = RES_WIN_BYTES / 8 + 80;
 
   for (uint32_t ii = 0; ii < sd.n_images; ++ii) {
     const ImageDesc im = P.images[sd.first_image + ii];
     uint32_t ch = im.first_chunk;
     const uint32_t ch_end = im.first_chunk + im.n_chunks;
+    uint64_t next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
     uint64_t pos = 0;  // image-relative
-    uint64_t next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;  // lane 0's copy is the live one
-    while (true) {
-      const bool more = !stopped && pos < im.len;
-      if (!__shfl_sync(0xffffffffu, more, 0)) break;
-      // stage [wbase, wbase + WIN) (+ overlap for record fields)
-      const uint64_t wbase = __shfl_sync(0xffffffffu, pos, 0) & ~15ull;
-      const uint64_t avail_words = (im.len - wbase + 7) / 8;
-      const uint32_t words = static_cast<uint32_t>(umin64(WIN_WORDS, avail_words));
-      const uint64_t* src = reinterpret_cast<const uint64_t*>(P.arena + im.base + wbase);
-      for (uint32_t w = lane; w < words; w += 32) win[warp][w] = src[w];
-      __syncwarp();
-      if (lane == 0) {
-        while (pos < im.len && pos - wbase < RES_WIN_BYTES) {
-          const uint32_t wi = static_cast<uint32_t>((pos - wbase) / 8);
-          const uint64_t h = win[warp][wi];
-          const uint32_t type = static_cast<uint32_t>(h);
-          const uint32_t size = static_cast<uint32_t>(h >> 48);
-          // hand the chunks that begin at or before this record their entry
-          while (pos >= next_begin) {
+    const uint8_t* const img = P.arena + im.base;
+    auto issue = [&](uint64_t wb, uint32_t b) {
+      const uint64_t avail = (im.len - wb + 15ull) & ~15ull;
+      const uint32_t bytes = static_cast<uint32_t>(umin64(avail, RES_WIN_BYTES + RES_OV_BYTES));
+      mbar_expect_tx(&bar[b], bytes);
+      tma_load_1d(win[b], img + wb, bytes, &bar[b]);
+    };
+    uint32_t issued = 0, waited = 0;
+    if (!stopped && im.len > 0) {
+      if (writer) issue(0, 0);
+      issued = 1;
+    }
+    for (uint64_t wb = 0; !stopped && wb < im.len; wb += RES_WIN_BYTES) {
+      const uint32_t b = static_cast<uint32_t>(wb / RES_WIN_BYTES) & 1;
+      __syncwarp();  // every lane is done with buffer b^1
+      if (wb + RES_WIN_BYTES < im.len) {
+        if (writer) issue(wb + RES_WIN_BYTES, b ^ 1);
+        ++issued;
+      }
+      mbar_wait(&bar[b], phase[b]);
+      phase[b] ^= 1;
+      ++waited;
+      const uint64_t* wd = win[b];
+      const uint64_t wend = umin64(wb + RES_WIN_BYTES, im.len);
+      while (pos < wend) {
+        // ---- a run of configured SAMPLEs: 32 at a time ----
+        {
+          const uint64_t q = pos + static_cast<uint64_t>(lane) * S8;
+          bool ok = q < wend && q + S8 <= im.len;
+          uint64_t tsl = 0;
+          if (ok) {
+            const uint32_t qi = static_cast<uint32_t>((q - wb) / 8);
+            ok = (wd[qi] & 0xFFFF0000FFFFFFFFull) == want && wd[qi + 2] == n;
+            tsl = wd[qi + 1];
+          }
+          const uint64_t pts = __shfl_up_sync(0xffffffffu, tsl, 1);
+          if (lane == 0) ok = ok && !(valid && !gap && st_ts > tsl);
+          else ok = ok && pts <= tsl;
+          const uint32_t okm = __ballot_sync(0xffffffffu, ok);
+          const uint32_t run = okm == 0xFFFFFFFFu ? 32u : static_cast<uint32_t>(__ffs(~okm) - 1);  // leading lanes that hold
+          if (run > 0) {
+            const uint64_t last_rec = pos + static_cast<uint64_t>(run - 1) * S8;
+            while (next_begin <= last_rec) {  // chunks that begin inside the run
+              const uint64_t j = next_begin <= pos ? 0 : (next_begin - pos + S8 - 1) / S8;
+              if (writer) {
+                ChunkIO& io = P.io[ch];
+                io.in_entry = im.base + pos + j * S8;
+                io.in_pred = j ? im.base + pos + (j - 1) * S8 : last_off;
+                io.in_gap = j ? 0u : static_cast<uint32_t>(gap);
+                io.limit = ~0ull;
+              }
+              ++ch;
+              next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
+            }
+            st_ts = __shfl_sync(0xffffffffu, tsl, run - 1);
+            valid = true;
+            gap = false;
+            last_off = im.base + last_rec;
+            pos = last_rec + S8;
+            continue;
+          }
+        }
+        // ---- any other record: one step ----
+        const uint32_t wi = static_cast<uint32_t>((pos - wb) / 8);
+        const uint64_t h = wd[wi];
+        const uint32_t type = static_cast<uint32_t>(h);
+        const uint32_t size = static_cast<uint32_t>(h >> 48);
+        // hand the chunks that begin at or before this record their entry
+        while (pos >= next_begin) {
+          if (writer) {
             ChunkIO& io = P.io[ch];
             io.in_entry = im.base + pos;
             io.in_pred = last_off;
             io.in_gap = gap;
             io.limit = ~0ull;
-            ++ch;
-            next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
           }
-          bool bad = size < 8 || (size & 7) || pos + size > im.len;  // fences, see DESIGN.md
-          uint64_t nr = 0, ts = 0;
-          if (!bad && (type == REC_SAMPLE || type == REC_READ)) {
-            // fields may lie beyond the staged window only for oversized records
-            nr = (size >= 24) ? win[warp][wi + 2] : ~0ull;
-            ts = win[warp][wi + 1];
-            bad = size < 40 || nr != ((size - 40u) >> 3) || (type == REC_SAMPLE && nr != n);
-          }
-          if (!bad && type == REC_LOST) bad = size < 24;
-          if (!bad && type == REC_SAMPLE && valid && !gap && st_ts > ts) {
-            bad = true;     // time regression: state is invalidated (gen :156-163)
-            valid = false;
-          }
-          if (bad) {
-            err = -1;  // -EPERM
-            err_off = im.stream_pos + pos;
-            stopped = true;
-            break;
-          }
-          if (type == REC_SAMPLE) {
-            st_ts = ts;
-            valid = true;
-            gap = false;
-            last_off = im.base + pos;
-          } else if (type == REC_LOST) {
-            gap = true;
-          }
-          pos += size;
+          ++ch;
+          next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
         }
+        bool bad = size < 8 || (size & 7) || pos + size > im.len;  // fences, see DESIGN.md
+        uint64_t ts = 0;
+        if (!bad && (type == REC_SAMPLE || type == REC_READ)) {
+          const uint64_t nr = (size >= 24) ? wd[wi + 2] : ~0ull;
+          ts = wd[wi + 1];
+          bad = size < 40 || nr != ((size - 40u) >> 3) || (type == REC_SAMPLE && nr != n);
+        }
+        if (!bad && type == REC_LOST) bad = size < 24;
+        if (!bad && type == REC_SAMPLE && valid && !gap && st_ts > ts) {
+          bad = true;     // time regression: state is invalidated (gen :156-163)
+          valid = false;
+        }
+        if (bad) {
+          err = -1;  // -EPERM
+          err_off = im.stream_pos + pos;
+          stopped = true;
+          break;
+        }
+        if (type == REC_SAMPLE) {
+          st_ts = ts;
+          valid = true;
+          gap = false;
+          last_off = im.base + pos;
+        } else if (type == REC_LOST) {
+          gap = true;
+        }
+        pos += size;
       }
-      __syncwarp();
     }
-    if (lane == 0) {
-      // chunks the walk never reached (after an error, or jumped over by a long record)
-      const uint64_t stop_abs = im.base + pos;
-      for (uint32_t k = im.first_chunk; k < ch_end; ++k) {
-        ChunkIO& io = P.io[k];
-        if (k >= ch) {
-          io.in_entry = stopped ? ~0ull : stop_abs;
-          io.in_pred = last_off;
-          io.in_gap = gap;
-        }
-        io.limit = stopped ? stop_abs : ~0ull;
-      }
+    // never leave a bulk copy in flight
+    if (waited < issued) {
+      const uint32_t b = waited & 1;
+      mbar_wait(&bar[b], phase[b]);
+      phase[b] ^= 1;
     }
     __syncwarp();
-  }
-  if (lane == 0) {
-    // images after the error: nothing is decoded
-    // (their chunks were visited above with stopped=true: in_entry = ~0)
-    hbtgpu_carry& co = P.carry_out[sidx];
-    const bool v = valid && !gap;
-    if (last_off == PRED_CARRY_IN) {
-      for (uint32_t e = 0; e < n; ++e) co.last[e] = cin.last[e];
-      co.te = cin.te;
-      co.tr = cin.tr;
-    } else {
-      const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + last_off);
-      for (uint32_t e = 0; e < n; ++e) co.last[e] = xform(P, e, r[5 + e]);
-      co.te = r[3];
-      co.tr = r[4];
+    // chunks the walk never reached (after an error, or jumped over by a long record)
+    const uint64_t stop_abs = im.base + pos;
+    for (uint32_t k = im.first_chunk + lane; k < ch_end; k += 32) {
+      ChunkIO& io = P.io[k];
+      if (k >= ch) {
+        io.in_entry = stopped ? ~0ull : stop_abs;
+        io.in_pred = last_off;
+        io.in_gap = gap;
+      }
+      io.limit = stopped ? stop_abs : ~0ull;
     }
-    co.valid = v;
-    co.tstamp = v ? st_ts : ~0ull;
-    ctr[C_ERR] = static_cast<uint64_t>(err);
-    ctr[C_ERR_OFF] = err_off;
-    ctr[C_LAST_TS] = co.tstamp;
   }
+  // images after an error were visited above with stopped=true: in_entry = ~0, nothing decoded
+  if (!writer) return;
+  hbtgpu_carry& co = P.carry_out[sidx];
+  const bool v = valid && !gap;
+  if (last_off == PRED_CARRY_IN) {
+    for (uint32_t e = 0; e < n; ++e) co.last[e] = cin.last[e];
+    co.te = cin.te;
+    co.tr = cin.tr;
+  } else {
+    const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + last_off);
+    for (uint32_t e = 0; e < n; ++e) co.last[e] = xform(P, e, r[5 + e]);
+    co.te = r[3];
+    co.tr = r[4];
+  }
+  co.valid = v;
+  co.tstamp = v ? st_ts : ~0ull;
+  ctr[C_ERR] = static_cast<uint64_t>(err);
+  ctr[C_ERR_OFF] = err_off;
+  ctr[C_LAST_TS] = co.tstamp;
 }
 
 // zero result buffers when the exact path has to recompute them
