@@ -176,7 +176,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=5)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -262,18 +262,23 @@ def main():
     exact_runs = st1["exact_runs"]
 
     # ---- end-to-end leg: host buffers in, host results out ---------------------------------
-    out_scaled = torch.empty((N_CPUS, N_BUCKETS, N_EVENTS), dtype=torch.int64, pin_memory=True)
-    out_metric = torch.empty((N_CPUS, N_BUCKETS, len(metrics)), dtype=torch.float64, pin_memory=True)
-    out_valid = torch.empty((N_CPUS, N_BUCKETS), dtype=torch.int32, pin_memory=True)
+    # two sets of pinned result buffers: step k+1 must not overwrite what step k is still copying
+    out_scaled = [torch.empty((N_CPUS, N_BUCKETS, N_EVENTS), dtype=torch.int64, pin_memory=True) for _ in range(2)]
+    out_metric = [torch.empty((N_CPUS, N_BUCKETS, len(metrics)), dtype=torch.float64, pin_memory=True) for _ in range(2)]
+    out_valid = [torch.empty((N_CPUS, N_BUCKETS), dtype=torch.int32, pin_memory=True) for _ in range(2)]
     import ctypes as C
 
     def e2e_step():
         ctx.reset(keep_carry=False)
         ctx.submit_images(list(range(N_CPUS)), streams)
         gpu_step()
-        ctx._ck(ctx.L.hbtgpu_get_buckets_host(ctx.h, C.c_void_p(0), C.c_void_p(out_scaled.data_ptr()),
-                                              C.c_void_p(out_metric.data_ptr()),
-                                              C.c_void_p(out_valid.data_ptr())))
+        # D2H of this step's results is queued on the context's second stream: it overlaps the
+        # next step's H2D (full-duplex PCIe); ctx.sync() below completes the last one
+        k = e2e_step.k = (getattr(e2e_step, "k", 0) + 1) % 2
+        ctx._ck(ctx.L.hbtgpu_get_buckets_host_async(ctx.h, C.c_void_p(0),
+                                                    C.c_void_p(out_scaled[k].data_ptr()),
+                                                    C.c_void_p(out_metric[k].data_ptr()),
+                                                    C.c_void_p(out_valid[k].data_ptr())))
     e2e_step()
     barrier()
     t_a = time.perf_counter()
@@ -286,7 +291,7 @@ def main():
     barrier()
     e2e_wall_ms = 1e3 * (time.perf_counter() - t_a) / args.e2e_steps
     e2e_ms = max(eva.elapsed_time(evb) / args.e2e_steps, e2e_wall_ms)
-    d2h = out_scaled.numel() * 8 + out_metric.numel() * 8 + out_valid.numel() * 4
+    d2h = out_scaled[0].numel() * 8 + out_metric[0].numel() * 8 + out_valid[0].numel() * 4
 
     # ---- max over ranks, whole-job aggregate ---------------------------------------------------
     t = torch.tensor([ms_total, e2e_ms, dec_ms], dtype=torch.float64, device="cuda")

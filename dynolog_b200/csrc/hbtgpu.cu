@@ -34,6 +34,9 @@ struct hbtgpu_ctx {
   hbtgpu_config cfg;
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t d2h_stream = nullptr;  // result copies that overlap the next submit
+  cudaEvent_t ev_results = nullptr, ev_d2h = nullptr;
+  bool d2h_pending = false;
   cudaEvent_t ev_run0 = nullptr, ev_run1 = nullptr;
   // one event pair per hbtgpu_run around the decode+aggregate kernel, harvested at sync
   static constexpr int kEvRing = 128;
@@ -252,6 +255,10 @@ Params make_params(hbtgpu_ctx* ctx) {
 }
 
 int launch_derive(hbtgpu_ctx* ctx) {
+  if (ctx->d2h_pending) {  // do not overwrite tensors that are still being copied out
+    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));
+    ctx->d2h_pending = false;
+  }
   DeriveParams D{};
   D.acc = ctx->d_acc;
   D.scaled = ctx->d_scaled;
@@ -411,6 +418,9 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   } while (0)
   CKC(cudaSetDevice(ctx->device));
   CKC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CKC(cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_results, cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_d2h, cudaEventDisableTiming));
   CKC(cudaEventCreate(&ctx->ev_run0));
   CKC(cudaEventCreate(&ctx->ev_run1));
   for (int i = 0; i < hbtgpu_ctx::kEvRing; ++i) {
@@ -470,6 +480,12 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
     if (ctx->ev_dec0[i]) cudaEventDestroy(ctx->ev_dec0[i]);
     if (ctx->ev_dec1[i]) cudaEventDestroy(ctx->ev_dec1[i]);
   }
+  if (ctx->d2h_stream) {
+    cudaStreamSynchronize(ctx->d2h_stream);
+    cudaStreamDestroy(ctx->d2h_stream);
+  }
+  for (cudaEvent_t e : {ctx->ev_results, ctx->ev_d2h})
+    if (e) cudaEventDestroy(e);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -584,9 +600,8 @@ int hbtgpu_reset(hbtgpu_ctx* ctx, int keep_carry) {
   ctx->ran = false;
   ctx->emitted = false;
   ctx->counters_valid = false;
-  CK(cudaMemsetAsync(ctx->d_counters, 0, ns * C_SLOTS * 8, ctx->stream));
-  CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
+  // result tensors are cleared by the next hbtgpu_run; nothing here waits for result copies
+  // that are still in flight, so the next submit can overlap them
   return 0;
 }
 
@@ -601,6 +616,7 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   uint32_t launches = 0;
   Params P = make_params(ctx);
 
+  if (ctx->d2h_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));  // acc may still be copied out
   CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
   CK(cudaMemsetAsync(ctx->d_counters, 0, ns * C_SLOTS * 8, ctx->stream));
   CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
@@ -650,6 +666,7 @@ int hbtgpu_sync(hbtgpu_ctx* ctx) {
   if (!ctx) return -EINVAL;
   CK(cudaSetDevice(ctx->device));
   CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaStreamSynchronize(ctx->d2h_stream));
   if (ctx->ran) CK(cudaEventElapsedTime(&ctx->stats.last_run_ms, ctx->ev_run0, ctx->ev_run1));
   for (int i = 0; i < ctx->ev_pending; ++i) {
     float ms = 0.f;
@@ -768,6 +785,24 @@ int hbtgpu_get_buckets_host(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scaled, do
                        cudaMemcpyDeviceToHost, ctx->stream));
   if (valid) CK(cudaMemcpyAsync(valid, ctx->d_valid, ctx->n_cells * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int hbtgpu_get_buckets_host_async(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scaled, double* metric,
+                                  uint32_t* valid) {
+  if (!ctx) return -EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  const uint32_t n = ctx->cfg.n_events;
+  CK(cudaEventRecord(ctx->ev_results, ctx->stream));
+  CK(cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_results, 0));
+  cudaStream_t s2 = ctx->d2h_stream;
+  if (acc) CK(cudaMemcpyAsync(acc, ctx->d_acc, ctx->acc_words * 8, cudaMemcpyDeviceToHost, s2));
+  if (scaled) CK(cudaMemcpyAsync(scaled, ctx->d_scaled, ctx->n_cells * n * 8, cudaMemcpyDeviceToHost, s2));
+  if (metric && ctx->cfg.n_metrics)
+    CK(cudaMemcpyAsync(metric, ctx->d_metric, ctx->n_cells * ctx->cfg.n_metrics * 8, cudaMemcpyDeviceToHost, s2));
+  if (valid) CK(cudaMemcpyAsync(valid, ctx->d_valid, ctx->n_cells * 4, cudaMemcpyDeviceToHost, s2));
+  CK(cudaEventRecord(ctx->ev_d2h, s2));
+  ctx->d2h_pending = true;
   return 0;
 }
 

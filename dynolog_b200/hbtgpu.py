@@ -83,7 +83,8 @@ ABI_SYMBOLS = [
     "hbtgpu_create", "hbtgpu_destroy", "hbtgpu_last_error", "hbtgpu_set_carry",
     "hbtgpu_submit_image", "hbtgpu_submit_images", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
     "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows",
-    "hbtgpu_get_records", "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_derive",
+    "hbtgpu_get_records", "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_get_buckets_host_async",
+    "hbtgpu_derive",
     "hbtgpu_get_stubs", "hbtgpu_compose_tail", "hbtgpu_apply_boundaries", "hbtgpu_stub_bytes",
     "hbtgpu_export_stubs_device", "hbtgpu_apply_boundaries_gathered", "hbtgpu_acc_device", "hbtgpu_stream",
     "hbtgpu_math_get_count", "hbtgpu_math_rate", "hbtgpu_math_add_reduce",

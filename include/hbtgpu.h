@@ -191,6 +191,13 @@ int hbtgpu_get_buckets_device(hbtgpu_ctx* ctx, hbtgpu_bucket_view* view);
 int hbtgpu_get_buckets_host(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scaled, double* metric,
                             uint32_t* valid);
 
+/* Asynchronous form of hbtgpu_get_buckets_host: the device-to-host copies are queued on a
+ * second stream behind the last run and may overlap the next hbtgpu_submit_image(s) (PCIe is
+ * full duplex); the buffers (ideally pinned) are complete after hbtgpu_sync, and the next run's
+ * derive step waits for the copies before it overwrites the tensors. */
+int hbtgpu_get_buckets_host_async(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scaled, double* metric,
+                                  uint32_t* valid);
+
 /* Re-run only the derive step (scale + metrics) from the current acc tensor,
  * e.g. after partial aggregates of other GPUs were summed into it. */
 int hbtgpu_derive(hbtgpu_ctx* ctx);

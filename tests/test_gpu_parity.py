@@ -258,6 +258,39 @@ def test_submit_images_batch(port_oracle):
             g.submit_images([0, 9], [streams[0], streams[1]])  # bad cpu: nothing is submitted
 
 
+def test_async_result_copy_matches_sync(port_oracle):
+    """hbtgpu_get_buckets_host_async: buffers complete after sync; a following run waits for it."""
+    import ctypes as C
+    n = 4
+    a, _ = rg.random_stream(810, 20000, n, mux=True)
+    b, _ = rg.random_stream(811, 15000, n, p_lost=0.01)
+    nb = 2100
+    with hbtgpu.Context(n_events=n, max_cpus=1, n_buckets=nb, t0=1_000_000_000, bucket_ns=1_000_000,
+                        arena_bytes=len(a) + len(b) + 65536, metrics=[(hbtgpu.METRIC_RATE, [1, 0])]) as g:
+        outs = []
+        for data in (a, b):
+            g.reset()
+            g.submit_image(0, data)
+            g.run()
+            acc = np.zeros((1, nb, n + 3), np.uint64)
+            scaled = np.zeros((1, nb, n), np.uint64)
+            metric = np.zeros((1, nb, 1), np.float64)
+            valid = np.zeros((1, nb), np.uint32)
+            g._ck(g.L.hbtgpu_get_buckets_host_async(g.h, C.c_void_p(acc.ctypes.data),
+                                                    C.c_void_p(scaled.ctypes.data),
+                                                    C.c_void_p(metric.ctypes.data),
+                                                    C.c_void_p(valid.ctypes.data)))
+            outs.append((acc, scaled, metric, valid))
+        g.sync()
+        p = po.make_params(n, n_buckets=nb, t0=1_000_000_000, bucket_ns=1_000_000)
+        for data, (acc, scaled, metric, valid) in zip((a, b), outs):
+            exp = port_oracle.decode_stream(p, data, po.make_carry())
+            assert np.array_equal(acc[0], exp["buckets"])
+            assert np.array_equal(scaled[0], port_oracle.scale_buckets(p, exp["buckets"]))
+        s = g.buckets()
+        assert np.array_equal(s["acc"], outs[1][0]) and np.array_equal(s["metric"], outs[1][2])
+
+
 def test_argument_errors():
     with pytest.raises(hbtgpu.HbtGpuError) as e:
         hbtgpu.Context(n_events=0)
