@@ -1196,6 +1196,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
     ++n_waited;
     const uint64_t* buf = s.data[b];
     const uint32_t wt = min(static_cast<uint32_t>(TILE_BYTES), chunk_len - tile_rel) / 8;
+    uint32_t tile_kind = 0;
     if (next_rel < tile_rel + 8 * wt) {
       const uint32_t entry = (next_rel - tile_rel) / 8;
       const uint64_t tile_abs = chunk_abs + tile_rel;
@@ -1245,18 +1246,19 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
         }
         term_tgt = ew;
       }
-      if (term_kind != 0 || s.tile_err != 0xFFFFFFFFu) {
-        bad = term_kind > 1 ? WHY_TILE_DEAD : WHY_TILE_ERR;
-        break;
-      }
-      const uint32_t tgt_rel = tile_rel + 8 * term_tgt;
-      if (tgt_rel > limit_rel) {  // record runs past the image end (or the exact-mode limit)
-        bad = WHY_PAST_END;
-        break;
-      }
-      next_rel = tgt_rel;
+      // decided after the barrier below: s.tile_err may still be written by other warps
+      tile_kind = term_kind;
+      next_rel = tile_rel + 8 * term_tgt;
     }
     __syncthreads();  // buffer b is free for the tile after next; publishes the new carry
+    if (tile_kind != 0 || s.tile_err != 0xFFFFFFFFu) {
+      bad = tile_kind > 1 ? WHY_TILE_DEAD : WHY_TILE_ERR;
+      break;
+    }
+    if (next_rel > limit_rel) {  // record runs past the image end (or the exact-mode limit)
+      bad = WHY_PAST_END;
+      break;
+    }
   }
   // never exit with a bulk copy still in flight into this CTA's shared memory
   if (n_waited < n_issued) mbar_wait(&s.bar[(n_waited + boff) & 1], phase[(n_waited + boff) & 1]);

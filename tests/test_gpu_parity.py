@@ -237,6 +237,33 @@ def test_rerun_and_reset(port_oracle):
         assert np.array_equal(a1 + a2, whole["buckets"])
 
 
+def test_512_cpus_ragged_streams(port_oracle):
+    """kMaxCpus streams (hbt/src/common/System.h:204) of ragged lengths, some empty, some with
+    several images, all in one context."""
+    n = 3
+    ncpu = 512
+    streams, splits = [], []
+    for cpu in range(ncpu):
+        nrec = [0, 1, 7, 40, 333, 1500][cpu % 6]
+        data, _ = rg.random_stream(20_000 + cpu, nrec, n, p_lost=0.02 if cpu % 3 == 0 else 0.0,
+                                   p_throttle=0.01 if cpu % 5 == 0 else 0.0)
+        streams.append(data)
+        if cpu % 7 == 0 and nrec >= 40:
+            offs = port_oracle.decode_stream(po.make_params(n), data, po.make_carry())["records"][0]
+            c1 = int(offs[len(offs) // 3])
+            splits.append([c1, len(data) - c1])
+        else:
+            splits.append([len(data)])
+    p = po.make_params(n, n_buckets=40, t0=1_000_000_000, bucket_ns=5_000_000)
+    carries = [po.make_carry(valid=(cpu % 2 == 0), tstamp=999_999_999, last=[1, 2, 3]) for cpu in range(ncpu)]
+    got, extra = gpu_decode(p, streams, carries, split=splits, want_tables=False)
+    assert extra["stats"]["exact_runs"] == 0
+    for cpu in range(ncpu):
+        exp = port_oracle.decode_stream(p, streams[cpu], carries[cpu])
+        exp["scaled"] = port_oracle.scale_buckets(p, exp["buckets"])
+        assert_matches_oracle(got[cpu], exp, n, f"cpu{cpu}", tables=False)
+
+
 def test_submit_images_batch(port_oracle):
     """hbtgpu_submit_images == the same images submitted one by one."""
     n = 2
