@@ -349,18 +349,21 @@ int ensure_emitted(hbtgpu_ctx* ctx) {
   }
   if (nc) {
     Params P = make_params(ctx);
-    k_decode<false, MODE_EMIT><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
+    CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
+    k_decode<false, MODE_EMIT><<<static_cast<unsigned>(nc), NT, sizeof(Smem) + EMIT_STAGE_BYTES, ctx->stream>>>(P);
     CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev_run1, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->stats.last_emit_ms, ctx->ev_run0, ctx->ev_run1));
   }
   ctx->emitted = true;
   return 0;
 }
 
 template <class K>
-int set_smem(hbtgpu_ctx* ctx, K kernel) {
+int set_smem(hbtgpu_ctx* ctx, K kernel, size_t extra = 0) {
   CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                          static_cast<int>(sizeof(Smem))));
+                          static_cast<int>(sizeof(Smem) + extra)));
   return 0;
 }
 
@@ -456,7 +459,7 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaStreamSynchronize(ctx->stream));
   ctx->carry_in.assign(ns, hbtgpu_carry{});
   if (set_smem(ctx, k_decode<true, MODE_AGG>) || set_smem(ctx, k_decode<false, MODE_AGG>) ||
-      set_smem(ctx, k_decode<false, MODE_EMIT>))
+      set_smem(ctx, k_decode<false, MODE_EMIT>, EMIT_STAGE_BYTES))
     return bail(-EIO);
 #undef CKC
   *out = ctx;

@@ -817,8 +817,16 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
 // uniform tile, else the run up to the first record that is something else (possibly 0); the
 // caller deals with that record (odd_record) and calls again behind it.  Nothing is committed
 // for records at or after the first mismatch.
+// MODE_EMIT writes, instead of bucket sums, the rows exactly as CpuCountSampleGenerator writes
+// them to its output ring ([tstamp, duration, delta...], gen :165-182) and the record table;
+// a warp assembles its (consecutive) rows in shared memory and copies them out coalesced.
+constexpr int EMIT_MAX_ROW_WORDS = 16;                     // n_events <= 14 on this path
+constexpr int EMIT_STAGE_WORDS = 31 * EMIT_MAX_ROW_WORDS;  // per warp
+constexpr size_t EMIT_STAGE_BYTES = static_cast<size_t>(NWARP) * EMIT_STAGE_WORDS * 8;
+
+template <int MODE>
 __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, const uint64_t* buf,
-                                                    uint32_t wt, uint32_t entry, const TileCtx& tc,
+                                                    uint32_t wt, uint32_t entry, TileCtx& tc,
                                                     uint32_t cur, uint32_t& k_all) {
   const Carry& C = s.c[cur];
   const uint32_t n = P.n_events;
@@ -872,6 +880,49 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   }
   if (regress < K) atomicMin(&s.tile_err, entry + regress * S);
 
+  if (MODE == MODE_EMIT) {
+    // rows of this segment are consecutive: record jr's row has ordinal jr - (link0 ? 0 : 1)
+    uint64_t* stage = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(&s) + sizeof(Smem)) +
+                      warp * EMIT_STAGE_WORDS;
+    const uint32_t RW = n + 2;
+    const int skip = link0 ? 0 : 1;
+#pragma unroll
+    for (int g = 0; g < MAXG; ++g) {
+      const int j0 = (g * NWARP + warp) * OWN - 1;
+      if (j0 >= K) break;
+      const int jr = j0 + lane;
+      if (lane < 31 && jr >= 0 && jr < K) {  // record table
+        const uint64_t gi = tc.rec_base + tc.recs_before + jr;
+        P.rec_off[gi] = tc.stream_off + 8ull * (entry + jr * S);
+        P.rec_type[gi] = REC_SAMPLE;
+        P.rec_size[gi] = 8 * S;
+      }
+      const int jlo = max(max(j0, 0), skip), jhi = min(j0 + 31, K);  // records with a row here
+      __syncwarp();  // the previous copy-out has read the stage
+      if (lane < 31 && jr >= jlo && jr < jhi) {
+        const uint32_t p = entry + jr * S;
+        uint64_t* row = stage + (jr - jlo) * RW;
+        const uint64_t ts = buf[p + 1];
+        const uint64_t pts = jr ? buf[p - S + 1] : C.ts;
+        row[0] = pts;
+        row[1] = ts - pts;
+        for (uint32_t e = 0; e < n; ++e) {
+          const uint64_t cv = xform(P, e, buf[p + 5 + e]);
+          const uint64_t pv = jr ? xform(P, e, buf[p - S + 5 + e]) : C.last[e];
+          row[2 + e] = cv - pv;
+        }
+      }
+      __syncwarp();
+      if (jhi > jlo) {
+        uint64_t* dst = P.rows + (tc.row_base + tc.rows_before + static_cast<uint64_t>(jlo - skip)) * RW;
+        const uint32_t words = static_cast<uint32_t>(jhi - jlo) * RW;
+        for (uint32_t w = lane; w < words; w += 32) dst[w] = stage[w];
+      }
+    }
+    tc.rows_before += static_cast<uint32_t>(K - skip);
+    tc.recs_before += static_cast<uint32_t>(K);
+  }
+
   // pass 2
   uint32_t n_oor = 0;
   // lane -> field of the accumulator record (delta[0..n), dTE, dTR, n_rows) and where that
@@ -882,6 +933,7 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   uint64_t* const acc_s = P.acc + static_cast<uint64_t>(tc.stream) * P.n_buckets * F;
 #pragma unroll
   for (int g = 0; g < MAXG; ++g) {
+    if (MODE != MODE_AGG) break;
     const int j0 = (g * NWARP + warp) * OWN - 1;
     if (j0 >= K) break;
     const int jr = j0 + lane;
@@ -962,7 +1014,9 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
 // invalidate the interval, :1440-1450 / gen :110-124; THROTTLE/UNTHROTTLE: count, :1476-1487;
 // READ: size check, :1515-1530; anything else: skip by size, :1565-1570) and return its size in
 // words; else return 0 and let the general path (which owns the error reporting) look at it.
-__device__ __forceinline__ uint32_t odd_record(Smem& s, const uint64_t* buf, uint32_t ew, uint32_t cur) {
+template <int MODE>
+__device__ __forceinline__ uint32_t odd_record(Smem& s, const Params& P, const uint64_t* buf, uint32_t ew,
+                                               uint32_t cur, TileCtx& tc) {
   const uint64_t h = buf[ew];
   const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
   if (size < 8 || (size & 7) || type == REC_SAMPLE) return 0;
@@ -980,7 +1034,14 @@ __device__ __forceinline__ uint32_t odd_record(Smem& s, const uint64_t* buf, uin
     } else if (type == REC_READ) {
       s.cnt[C_READ] += 1;
     }
+    if (MODE == MODE_EMIT) {
+      const uint64_t gi = tc.rec_base + tc.recs_before;
+      P.rec_off[gi] = tc.stream_off + 8ull * ew;
+      P.rec_type[gi] = type;
+      P.rec_size[gi] = size;
+    }
   }
+  if (MODE == MODE_EMIT) tc.recs_before += 1;
   return size >> 3;
 }
 
@@ -1205,13 +1266,13 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
       uint32_t term_kind = 0, term_tgt = 0;
       bool done = false;
       uint32_t ew = entry;  // chain position, tile-relative words
-      if (MODE == MODE_AGG && !P.force_general) {
+      if (!P.force_general && (MODE == MODE_AGG || P.n_events + 2 <= EMIT_MAX_ROW_WORDS)) {
         // runs of configured SAMPLEs in parallel, the few other records in between one by one;
         // a tile with many of those goes to the general path
         const uint32_t S = 5 + P.n_events;
         for (int odd = 0;;) {
           uint32_t k_all = 0;
-          const uint32_t k = uniform_segment(s, P, buf, wt, ew, tc, cur, k_all);
+          const uint32_t k = uniform_segment<MODE>(s, P, buf, wt, ew, tc, cur, k_all);
           if (k) cur ^= 1;
           ew += k * S;
           if (k == k_all) {  // ran to the end of the tile
@@ -1219,7 +1280,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
             break;
           }
           __syncthreads();  // the segment's carry is published
-          const uint32_t sz = (++odd <= 8) ? odd_record(s, buf, ew, cur) : 0;
+          const uint32_t sz = (++odd <= 8) ? odd_record<MODE>(s, P, buf, ew, cur, tc) : 0;
           if (sz == 0) break;
           ew += sz;
           __syncthreads();  // thread 0's update of the carry (gap) is visible

@@ -75,7 +75,7 @@ class Stats(C.Structure):
                 ("kernel_launches", C.c_uint32), ("last_run_ms", C.c_float),
                 ("last_decode_ms", C.c_float), ("exact_reason", C.c_uint32),
                 ("exact_chunk", C.c_uint32), ("decode_ms_sum", C.c_double),
-                ("decode_runs", C.c_uint64)]
+                ("decode_runs", C.c_uint64), ("last_emit_ms", C.c_float), ("pad", C.c_uint32)]
 
 
 # every symbol include/hbtgpu.h declares (tests check that the library exports them all)

@@ -292,6 +292,8 @@ typedef struct {
   uint32_t exact_chunk;   /* ... and the first chunk that reported it */
   double decode_ms_sum;   /* CUDA-event time of the decode+aggregate kernel, summed over ... */
   uint64_t decode_runs;   /* ... this many runs since create (harvested at hbtgpu_sync) */
+  float last_emit_ms;     /* CUDA-event time of the last row / record-table emission pass */
+  uint32_t pad;
 } hbtgpu_stats;
 int hbtgpu_get_stats(hbtgpu_ctx* ctx, hbtgpu_stats* out);
 

@@ -23,9 +23,11 @@ def probe(name, cfg, ncpu, n, nb, flags=0, forge=0, **kw):
     s1 = g.stats()
     dec = (s1["decode_ms_sum"] - s0["decode_ms_sum"]) / (s1["decode_runs"] - s0["decode_runs"])
     nrec = sum(g.counters(i)["num_records"] for i in range(ncpu))
+    g.rows(0)  # triggers the emission pass (rows + record table of every cpu)
+    emit = g.stats()["last_emit_ms"]
     print(f"{name:34s} {total/1e9:6.2f} GB  decode {dec:7.3f} ms  {total/1e6/dec:7.1f} GB/s "
           f"({100*total/1e6/dec/6547.5:4.1f}% of 6547.5)  step {s1['last_run_ms']:.3f} ms  "
-          f"{nrec/1e6/ (s1['last_run_ms']):.1f} Grec/s  exact_runs={s1['exact_runs']} why={s1['exact_reason']}")
+          f"{nrec/1e6/ (s1['last_run_ms']):.1f} Grec/s  emit {emit:.3f} ms  exact_runs={s1['exact_runs']} why={s1['exact_reason']}")
     g.close()
 
 if __name__ == "__main__":
