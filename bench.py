@@ -38,6 +38,15 @@ WORKLOAD = ("cfg2: 192-CPU capture, 8-event group, 10 kHz x 10 s, 1 ms buckets, 
             "IPC + LLC-miss-rate (synthetic, 19.2M SAMPLE records, 2.0 GB per GPU)")
 
 
+def ncu_traffic():
+    """dram read+write bytes per launch of the dominant kernel, from the committed ncu capture."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["traffic_bytes_per_launch"])
+    return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -317,7 +326,8 @@ def main():
                        "l2": "inputs (2.0 GB) larger than L2 (126 MB); no flush needed",
                        "step_gbs": (all_bytes / 1e9) / (ms_step * 1e-3)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
+                         "traffic_source": "profiles/r01_traffic.json (ncu --set full, dram read+write per launch)",
                          "kernel": "k_decode<spec,agg>", "kernel_ms": dec_ms,
                          "algorithmic_bytes_per_launch": image_bytes,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
