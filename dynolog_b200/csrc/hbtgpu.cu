@@ -245,7 +245,7 @@ Params make_params(hbtgpu_ctx* ctx) {
   {
     const unsigned __int128 range = static_cast<unsigned __int128>(ctx->cfg.n_buckets) * ctx->cfg.bucket_ns;
     P.range_ns = range > ~0ull ? ~0ull : static_cast<uint64_t>(range);
-    P.inv_bucket = 1.0 / static_cast<double>(ctx->cfg.bucket_ns);
+    P.bucket_magic = static_cast<uint64_t>((static_cast<unsigned __int128>(1) << 64) / ctx->cfg.bucket_ns);
     const uint64_t b = ctx->cfg.bucket_ns;
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
     const uint64_t S = 5ull + ctx->cfg.n_events;
@@ -1230,7 +1230,7 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
   {
     const unsigned __int128 range = static_cast<unsigned __int128>(cfg->n_buckets) * cfg->bucket_ns;
     P.range_ns = range > ~0ull ? ~0ull : static_cast<uint64_t>(range);
-    P.inv_bucket = 1.0 / static_cast<double>(cfg->bucket_ns);
+    P.bucket_magic = static_cast<uint64_t>((static_cast<unsigned __int128>(1) << 64) / cfg->bucket_ns);
     const uint64_t b = cfg->bucket_ns;
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
     const uint64_t S = 5ull + n;

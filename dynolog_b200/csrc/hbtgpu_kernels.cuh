@@ -162,7 +162,7 @@ struct Params {
   uint32_t force_general, external_carry;
   // bucket index = (ts - t0) / bucket_ns without a 64-bit division (set by the host)
   uint64_t range_ns;    // n_buckets * bucket_ns, saturated
-  double inv_bucket;    // 1.0 / bucket_ns
+  uint64_t bucket_magic;  // floor(2^64 / bucket_ns) (bucket_ns not a power of two)
   uint32_t bucket_shift;  // log2(bucket_ns) when it is a power of two, else 0xFFFFFFFF
   uint32_t s_magic;       // ceil(2^32 / (5 + n_events)): x / S == (x * s_magic) >> 32 for x < 2^16
 };
@@ -541,15 +541,12 @@ __device__ __forceinline__ uint32_t scout_start(Smem& s, const Params& P, const 
 }
 
 __device__ __forceinline__ uint32_t bucket_of(const Params& P, uint64_t ts) {
-  if (ts < P.t0) return BKT_OOR;
-  const uint64_t d = ts - P.t0;
-  if (d >= P.range_ns) return BKT_OOR;
+  const uint64_t d = ts - P.t0;                // wraps to a huge value when ts < t0 ...
+  if (d >= P.range_ns) return BKT_OOR;         // ... which this catches too (range_ns <= 2^64 - 1)
   if (P.bucket_shift != 0xFFFFFFFFu) return static_cast<uint32_t>(d >> P.bucket_shift);
-  // q < 2^32 here, so the double estimate is off by at most one; fix it up exactly
-  uint64_t q = __double2ull_rz(__dmul_rn(__ull2double_rn(d), P.inv_bucket));
-  const uint64_t r = d - q * P.bucket_ns;
-  if (static_cast<int64_t>(r) < 0) --q;
-  else if (r >= P.bucket_ns) ++q;
+  // d / bucket_ns by multiply-high with floor(2^64 / bucket_ns): one below the quotient at most
+  uint64_t q = __umul64hi(d, P.bucket_magic);
+  if (d - q * P.bucket_ns >= P.bucket_ns) ++q;
   return static_cast<uint32_t>(q);
 }
 
@@ -1262,7 +1259,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
       const uint32_t entry = (next_rel - tile_rel) / 8;
       const uint64_t tile_abs = chunk_abs + tile_rel;
       tc.tile_abs = tile_abs;
-      tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base);
+      if (MODE == MODE_EMIT) tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base);
       uint32_t term_kind = 0, term_tgt = 0;
       bool done = false;
       uint32_t ew = entry;  // chain position, tile-relative words
