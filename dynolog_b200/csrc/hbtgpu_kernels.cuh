@@ -33,7 +33,7 @@
 namespace hbtgpu {
 
 #ifndef HBT_NT
-#define HBT_NT 256
+#define HBT_NT 192
 #endif
 constexpr int NT = HBT_NT;  // threads per CTA
 constexpr int NWARP = NT / 32;
@@ -47,7 +47,7 @@ constexpr int HALO_WORDS = HALO_BYTES / 8;
 // The general path (classify + pointer jumping + scan) works on sub-tiles of GT_WORDS words so
 // that its per-candidate arrays stay small (shared memory decides how many CTAs fit on an SM).
 #ifndef HBT_GT_WORDS
-#define HBT_GT_WORDS 512
+#define HBT_GT_WORDS 384
 #endif
 constexpr int GT_WORDS = HBT_GT_WORDS;
 constexpr int MAXC = GT_WORDS;    // worst case: every word is a candidate header
