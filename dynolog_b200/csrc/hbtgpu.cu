@@ -59,14 +59,12 @@ struct hbtgpu_ctx {
   ChunkIO* d_io = nullptr;
   ImageDesc* d_images = nullptr;
   StreamDesc* d_streams = nullptr;
-  size_t cap_chunks = 0, cap_images = 0;
+  size_t cap_chunks = 0, cap_io = 0, cap_images = 0;
   uint64_t *d_rows = nullptr, *d_rec_off = nullptr;
   uint32_t *d_rec_type = nullptr, *d_rec_size = nullptr;
   size_t cap_rows = 0, cap_recs = 0;
   void* d_math = nullptr;
   size_t cap_math = 0;
-  uint8_t* h_stage = nullptr;  // pinned staging for pageable submits
-  size_t cap_stage = 0;
 
   // host bookkeeping
   std::vector<hbtgpu_carry> carry_in;
@@ -190,14 +188,7 @@ int build_table(hbtgpu_ctx* ctx) {
   }
   const size_t nc = ctx->chunks.size(), ni = ctx->img_descs.size();
   if (int r = ensure(ctx, &ctx->d_chunks, &ctx->cap_chunks, std::max<size_t>(nc, 1))) return r;
-  {
-    size_t cap_io = 0;
-    if (ctx->d_io) {
-      CK(cudaFree(ctx->d_io));
-      ctx->d_io = nullptr;
-    }
-    if (int r = ensure(ctx, &ctx->d_io, &cap_io, std::max<size_t>(nc, 1))) return r;
-  }
+  if (int r = ensure(ctx, &ctx->d_io, &ctx->cap_io, std::max<size_t>(nc, 1))) return r;
   if (int r = ensure(ctx, &ctx->d_images, &ctx->cap_images, std::max<size_t>(ni, 1))) return r;
   if (nc) CK(cudaMemcpyAsync(ctx->d_chunks, ctx->chunks.data(), nc * sizeof(ChunkDesc),
                              cudaMemcpyHostToDevice, ctx->stream));
@@ -476,7 +467,6 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
                   ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math};
   for (void* p : ptrs)
     if (p) cudaFree(p);
-  if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
   for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
     if (e) cudaEventDestroy(e);
   for (int i = 0; i < hbtgpu_ctx::kEvRing; ++i) {

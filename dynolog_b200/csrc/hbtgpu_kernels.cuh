@@ -59,7 +59,6 @@ constexpr uint16_t NX_EXIT = 0xFFFF;  // chain leaves the tile
 constexpr uint16_t NX_DEAD = 0xFFFE;  // chain lands on a word that is no valid header
 constexpr uint32_t BKT_OOR = 0xFFFFFFFFu;
 
-constexpr uint64_t OFF_NONE = ~0ull;           // "no such offset"
 constexpr uint64_t PRED_CARRY_IN = ~0ull - 1;  // predecessor is the stream's carry-in state
 constexpr uint64_t PRED_UNKNOWN = ~0ull - 2;   // speculation could not find it
 
@@ -137,7 +136,7 @@ struct StreamDesc {
 // per-stream counters as u64 slots
 enum {
   C_LOST = 0, C_THROTTLE, C_UNTHROTTLE, C_SAMPLE, C_READ, C_RECORDS, C_UNKNOWN, C_ROWS, C_OOR,
-  C_ERR, C_ERR_OFF, C_LAST_TS, C_HEAD_SET, C_SLOTS = 16
+  C_ERR, C_ERR_OFF, C_LAST_TS, C_SLOTS = 16
 };
 
 struct Params {
@@ -181,9 +180,6 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 }
 __device__ __forceinline__ void fence_barrier_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() {
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),

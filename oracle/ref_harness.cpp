@@ -64,12 +64,6 @@ struct NullBuf : std::streambuf {
 
 // "stderr to /dev/null": hbt logs through std::cerr (Defs.h:177-181); formatting
 // still happens, only the write is dropped.
-struct CerrSilencer {
-  NullBuf nb;
-  std::streambuf* old;
-  CerrSilencer() : old(std::cerr.rdbuf(&nb)) {}
-  ~CerrSilencer() { std::cerr.rdbuf(old); }
-};
 std::atomic<int> g_silence_depth{0};
 NullBuf g_nullbuf;
 std::streambuf* g_old = nullptr;
