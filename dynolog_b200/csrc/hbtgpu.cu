@@ -239,7 +239,9 @@ Params make_params(hbtgpu_ctx* ctx) {
     P.bucket_magic = static_cast<uint64_t>((static_cast<unsigned __int128>(1) << 64) / ctx->cfg.bucket_ns);
     const uint64_t b = ctx->cfg.bucket_ns;
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
-    const uint64_t S = 5ull + ctx->cfg.n_events;
+    P.pre = ctx->cfg.sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ ? 2 : 0;
+    P.fix = 40 + 8 * P.pre;
+    const uint64_t S = 5ull + P.pre + ctx->cfg.n_events;
     P.s_magic = static_cast<uint32_t>(((1ull << 32) + S - 1) / S);
   }
   return P;
@@ -380,6 +382,7 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   if (cfg->bucket_ns == 0) return fail(ctx, -EINVAL, "bucket_ns must be >= 1");
   if (cfg->n_metrics > HBTGPU_MAX_METRICS) return fail(ctx, -EINVAL, "too many metrics");
   if (cfg->time_shift > 63) return fail(ctx, -EINVAL, "time_shift must be < 64");
+  if (cfg->sample_format > HBTGPU_SAMPLE_IP_TID_TIME_READ) return fail(ctx, -EINVAL, "unknown sample_format");
   if (cfg->tsc_mask != 0 && cfg->time_mult == 0) return fail(ctx, -EINVAL, "time_mult must be != 0");
   for (uint32_t m = 0; m < cfg->n_metrics; ++m) {
     const hbtgpu_metric& md = cfg->metrics[m];
@@ -1223,7 +1226,9 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
     P.bucket_magic = static_cast<uint64_t>((static_cast<unsigned __int128>(1) << 64) / cfg->bucket_ns);
     const uint64_t b = cfg->bucket_ns;
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
-    const uint64_t S = 5ull + n;
+    P.pre = cfg->sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ ? 2 : 0;
+    P.fix = 40 + 8 * P.pre;
+    const uint64_t S = 5ull + P.pre + n;
     P.s_magic = static_cast<uint32_t>(((1ull << 32) + S - 1) / S);
   }
   if (nc) {

@@ -159,6 +159,10 @@ struct Params {
   uint32_t n_events, n_buckets, n_chunks, n_streams;
   uint32_t time_shift, time_mult;
   uint32_t force_general, external_carry;
+  // SAMPLE layout: {hdr, [ip, pid|tid,] time, nr, time_enabled, time_running, value[nr]}.
+  // pre = words between the header and `time` (0 for sample_type TIME|READ as hbt opens it,
+  // 2 with IP|TID in front); fix = bytes of a SAMPLE without its values (40 + 8*pre).
+  uint32_t pre, fix;
   // bucket index = (ts - t0) / bucket_ns without a 64-bit division (set by the host)
   uint64_t range_ns;    // n_buckets * bucket_ns, saturated
   uint64_t bucket_magic;  // floor(2^64 / bucket_ns) (bucket_ns not a power of two)
@@ -490,7 +494,7 @@ __device__ __forceinline__ uint32_t scout_start(Smem& s, const Params& P, const 
     const uint64_t hd = buf[p];
     const uint32_t type = static_cast<uint32_t>(hd), size = static_cast<uint32_t>(hd >> 48);
     const uint32_t n = P.n_events;
-    const bool plausible = (type == REC_SAMPLE && size == 40 + 8 * n && buf[p + 2] == n) ||
+    const bool plausible = (type == REC_SAMPLE && size == P.fix + 8 * n && buf[p + P.pre + 2] == n) ||
                            (type == REC_LOST && size == 24) ||
                            ((type == REC_THROTTLE || type == REC_UNTHROTTLE) && size == 32);
     own = (plausible ? 0x10000u : 0u) | 1u;
@@ -591,8 +595,8 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
       ++n_rec;
       if (type == REC_SAMPLE) {
         // recordSize check (:1502-1507) + nr == kNumEvents (fenced DCHECK, gen :133)
-        const uint64_t nr = (size >= 24) ? buf[p + 2] : ~0ull;
-        if (size < 40 || nr != ((size - 40u) >> 3) || nr != n) {
+        const uint64_t nr = (size + 16 >= P.fix) ? buf[p + P.pre + 2] : ~0ull;
+        if (size < P.fix || nr != ((size - P.fix) >> 3) || nr != n) {
           atomicMin(&s.tile_err, p);
         } else {
           f |= FL_SAMPLE;
@@ -636,8 +640,8 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
       const bool gap = in_tile ? (prev_l > prev_s) : (c_gap || prev_l != 0);
       const bool link = (in_tile || c_valid) && !gap;
       const uint32_t p = s.pos[j];
-      const uint64_t ts = buf[p + 1];
-      const uint64_t pts = in_tile ? buf[s.pos[prev_s - 1] + 1] : c_ts;
+      const uint64_t ts = buf[p + P.pre + 1];
+      const uint64_t pts = in_tile ? buf[s.pos[prev_s - 1] + P.pre + 1] : c_ts;
       if (link && pts > ts) atomicMin(&s.tile_err, p);  // time regression (gen :156-163)
       if (!SCOUT) {
         s.u.de.bkt[j] = bucket_of(P, ts);
@@ -730,14 +734,14 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
               for (uint32_t e = 0; e < n + 3; ++e) {
                 uint64_t plus, minus;
                 if (e < n) {
-                  plus = xform(P, e, buf[p + 5 + e]);
-                  minus = (pj != IDX_NONE) ? xform(P, e, buf[pp + 5 + e]) : C.last[e];
+                  plus = xform(P, e, buf[p + P.pre + 5 + e]);
+                  minus = (pj != IDX_NONE) ? xform(P, e, buf[pp + P.pre + 5 + e]) : C.last[e];
                 } else if (e == n) {
-                  plus = buf[p + 3];
-                  minus = (pj != IDX_NONE) ? buf[pp + 3] : C.te;
+                  plus = buf[p + P.pre + 3];
+                  minus = (pj != IDX_NONE) ? buf[pp + P.pre + 3] : C.te;
                 } else if (e == n + 1) {
-                  plus = buf[p + 4];
-                  minus = (pj != IDX_NONE) ? buf[pp + 4] : C.tr;
+                  plus = buf[p + P.pre + 4];
+                  minus = (pj != IDX_NONE) ? buf[pp + P.pre + 4] : C.tr;
                 } else {
                   plus = ord;
                   minus = static_cast<uint64_t>(ord) - 1;
@@ -748,14 +752,14 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
             }
           } else {  // MODE_EMIT: the row as CpuCountSampleGenerator writes it (:165-182)
             const uint32_t pp = (pj != IDX_NONE) ? s.pos[pj] : 0;
-            const uint64_t ts = buf[p + 1];
-            const uint64_t pts = (pj != IDX_NONE) ? buf[pp + 1] : C.ts;
+            const uint64_t ts = buf[p + P.pre + 1];
+            const uint64_t pts = (pj != IDX_NONE) ? buf[pp + P.pre + 1] : C.ts;
             uint64_t* row = P.rows + (tc.row_base + tc.rows_before + ex_row) * (n + 2);
             row[0] = pts;
             row[1] = ts - pts;
             for (uint32_t e = 0; e < n; ++e) {
-              const uint64_t cur = xform(P, e, buf[p + 5 + e]);
-              const uint64_t prv = (pj != IDX_NONE) ? xform(P, e, buf[pp + 5 + e]) : C.last[e];
+              const uint64_t cur = xform(P, e, buf[p + P.pre + 5 + e]);
+              const uint64_t prv = (pj != IDX_NONE) ? xform(P, e, buf[pp + P.pre + 5 + e]) : C.last[e];
               row[2 + e] = cur - prv;
             }
             ++ex_row;
@@ -771,11 +775,11 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
   const uint32_t last_s = tot_a >> 16, last_l = tot_a & 0xFFFFu;
   if (last_s != 0) {
     const uint32_t p = s.pos[last_s - 1];
-    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, buf[p + 5 + e]);
+    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, buf[p + P.pre + 5 + e]);
     if (threadIdx.x == 0) {
-      C.ts = buf[p + 1];
-      C.te = buf[p + 3];
-      C.tr = buf[p + 4];
+      C.ts = buf[p + P.pre + 1];
+      C.te = buf[p + P.pre + 3];
+      C.tr = buf[p + P.pre + 4];
       C.valid = 1;
       C.gap = last_l > last_s;
       C.last_off = tc.tile_abs + 8ull * p;
@@ -823,7 +827,8 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
                                                     uint32_t cur, uint32_t& k_all) {
   const Carry& C = s.c[cur];
   const uint32_t n = P.n_events;
-  const uint32_t S = 5 + n;  // words per SAMPLE
+  const uint32_t pre = P.pre;
+  const uint32_t S = 5 + pre + n;  // words per SAMPLE
   const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
   // records whose header lies inside the tile: ceil((wt - entry) / S) by multiply-shift
   const int Kall = static_cast<int>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
@@ -850,9 +855,9 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
     if (jr >= 0 && jr < K) {
       const uint32_t p = entry + jr * S;
       // misc (bits 32..47) is free; type and size must match, and so must nr
-      if (lane < 31 && ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + 2] != n))
+      if (lane < 31 && ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + pre + 2] != n))
         first_bad = min(first_bad, jr);
-      ts = buf[p + 1];
+      ts = buf[p + pre + 1];
       bk_[g] = bucket_of(P, ts);
     } else if (jr == -1) {
       ts = C.ts;
@@ -895,13 +900,13 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
       if (lane < 31 && jr >= jlo && jr < jhi) {
         const uint32_t p = entry + jr * S;
         uint64_t* row = stage + (jr - jlo) * RW;
-        const uint64_t ts = buf[p + 1];
-        const uint64_t pts = jr ? buf[p - S + 1] : C.ts;
+        const uint64_t ts = buf[p + pre + 1];
+        const uint64_t pts = jr ? buf[p - S + pre + 1] : C.ts;
         row[0] = pts;
         row[1] = ts - pts;
         for (uint32_t e = 0; e < n; ++e) {
-          const uint64_t cv = xform(P, e, buf[p + 5 + e]);
-          const uint64_t pv = jr ? xform(P, e, buf[p - S + 5 + e]) : C.last[e];
+          const uint64_t cv = xform(P, e, buf[p + pre + 5 + e]);
+          const uint64_t pv = jr ? xform(P, e, buf[p - S + pre + 5 + e]) : C.last[e];
           row[2 + e] = cv - pv;
         }
       }
@@ -922,7 +927,7 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   // field sits in a SAMPLE (value[e] at word 5+e, time_enabled at 3, time_running at 4)
   const bool two = F <= 16;
   const uint32_t e0 = two ? (lane & 15) : lane;
-  const uint32_t woff0 = e0 < n ? 5 + e0 : (e0 == n ? 3 : 4);
+  const uint32_t woff0 = pre + (e0 < n ? 5 + e0 : (e0 == n ? 3 : 4));
   uint64_t* const acc_s = P.acc + static_cast<uint64_t>(tc.stream) * P.n_buckets * F;
 #pragma unroll
   for (int g = 0; g < MAXG; ++g) {
@@ -975,7 +980,7 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
           }
           if (two || e + 32 >= F) break;
           e += 32;  // n > 13: a lane serves several fields
-          woff = e < n ? 5 + e : (e == n ? 3 : 4);
+          woff = pre + (e < n ? 5 + e : (e == n ? 3 : 4));
         }
       }
     }
@@ -985,11 +990,11 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   if (warp == NWARP - 1) {
     Carry& N = s.c[cur ^ 1];
     const uint32_t p = entry + (K - 1) * S;
-    for (uint32_t e = lane; e < n; e += 32) N.last[e] = xform(P, e, buf[p + 5 + e]);
+    for (uint32_t e = lane; e < n; e += 32) N.last[e] = xform(P, e, buf[p + pre + 5 + e]);
     if (lane == 0) {
-      N.ts = buf[p + 1];
-      N.te = buf[p + 3];
-      N.tr = buf[p + 4];
+      N.ts = buf[p + pre + 1];
+      N.te = buf[p + pre + 3];
+      N.tr = buf[p + pre + 4];
       N.valid = 1;
       N.gap = 0;
       N.last_off = tc.tile_abs + 8ull * p;
@@ -1062,11 +1067,11 @@ __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t st
     }
   } else {
     const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + pred);
-    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, r[5 + e]);
+    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, r[P.pre + 5 + e]);
     if (threadIdx.x == 0) {
-      C.ts = r[1];
-      C.te = r[3];
-      C.tr = r[4];
+      C.ts = r[P.pre + 1];
+      C.te = r[P.pre + 3];
+      C.tr = r[P.pre + 4];
       C.valid = 1;
       C.gap = gap;
       C.last_off = pred;
@@ -1149,29 +1154,29 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
       // guess like any other -- k_verify proves or refutes it against the previous chunk.
       bool quick = false;
       if (!P.force_general && !(cd.flags & CH_FIRST_OF_IMAGE)) {
-        const uint32_t n = P.n_events, S = 5 + n;
+        const uint32_t n = P.n_events, pre = P.pre, S = 5 + pre + n;
         const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
         if (threadIdx.x == 0) s.red_key = 0;
         __syncthreads();
         const uint32_t w = threadIdx.x;  // hw <= HALO_WORDS == NT
-        const bool m = w < hw && (hb[w] & 0xFFFF0000FFFFFFFFull) == want && hb[w + 2] == n;
+        const bool m = w < hw && (hb[w] & 0xFFFF0000FFFFFFFFull) == want && hb[w + pre + 2] == n;
         const uint32_t bal = __ballot_sync(0xffffffffu, m);
         if ((threadIdx.x & 31) == 0 && bal) atomicMax(&s.red_key, (threadIdx.x & ~31u) + (31 - __clz(bal)) + 1);
         __syncthreads();
         const uint32_t wl = s.red_key;  // 1 + last matching word, 0 if none
         if (wl != 0) {
           const uint32_t p = wl - 1;
-          const bool confirmed = p >= S && (hb[p - S] & 0xFFFF0000FFFFFFFFull) == want && hb[p - S + 2] == n &&
-                                 hb[p - S + 1] <= hb[p + 1];
+          const bool confirmed = p >= S && (hb[p - S] & 0xFFFF0000FFFFFFFFull) == want &&
+                                 hb[p - S + pre + 2] == n && hb[p - S + pre + 1] <= hb[p + pre + 1];
           if (confirmed && p + S >= hw) {
             quick = true;
             entry_abs = cd.halo_off + 8ull * (p + S);
             Carry& C0 = s.c[0];
-            for (uint32_t e = threadIdx.x; e < n; e += NT) C0.last[e] = xform(P, e, hb[p + 5 + e]);
+            for (uint32_t e = threadIdx.x; e < n; e += NT) C0.last[e] = xform(P, e, hb[p + pre + 5 + e]);
             if (threadIdx.x == 0) {
-              C0.ts = hb[p + 1];
-              C0.te = hb[p + 3];
-              C0.tr = hb[p + 4];
+              C0.ts = hb[p + pre + 1];
+              C0.te = hb[p + pre + 3];
+              C0.tr = hb[p + pre + 4];
               C0.valid = 1;
               C0.gap = 0;
               C0.last_off = cd.halo_off + 8ull * p;
@@ -1262,7 +1267,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
       if (!P.force_general && (MODE == MODE_AGG || P.n_events + 2 <= EMIT_MAX_ROW_WORDS)) {
         // runs of configured SAMPLEs in parallel, the few other records in between one by one;
         // a tile with many of those goes to the general path
-        const uint32_t S = 5 + P.n_events;
+        const uint32_t S = 5 + P.pre + P.n_events;
         for (int odd = 0;;) {
           uint32_t k_all = 0;
           const uint32_t k = uniform_segment<MODE>(s, P, buf, wt, ew, tc, cur, k_all);
@@ -1409,7 +1414,8 @@ __global__ void __launch_bounds__(RES_THREADS) k_resolve(const Params P) {
   }
   __syncwarp();
   uint32_t phase[2] = {0, 0};
-  const uint32_t S8 = 8 * (5 + P.n_events);  // bytes of a configured SAMPLE
+  const uint32_t pre = P.pre;
+  const uint32_t S8 = 8 * (5 + pre + P.n_events);  // bytes of a configured SAMPLE
   const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S8) << 48);
   const StreamDesc sd = P.streams[sidx];
   const uint32_t n = P.n_events;
@@ -1462,8 +1468,8 @@ __global__ void __launch_bounds__(RES_THREADS) k_resolve(const Params P) {
           uint64_t tsl = 0;
           if (ok) {
             const uint32_t qi = static_cast<uint32_t>((q - wb) / 8);
-            ok = (wd[qi] & 0xFFFF0000FFFFFFFFull) == want && wd[qi + 2] == n;
-            tsl = wd[qi + 1];
+            ok = (wd[qi] & 0xFFFF0000FFFFFFFFull) == want && wd[qi + pre + 2] == n;
+            tsl = wd[qi + pre + 1];
           }
           const uint64_t pts = __shfl_up_sync(0xffffffffu, tsl, 1);
           if (lane == 0) ok = ok && !(valid && !gap && st_ts > tsl);
@@ -1511,10 +1517,14 @@ __global__ void __launch_bounds__(RES_THREADS) k_resolve(const Params P) {
         }
         bool bad = size < 8 || (size & 7) || pos + size > im.len;  // fences, see DESIGN.md
         uint64_t ts = 0;
-        if (!bad && (type == REC_SAMPLE || type == REC_READ)) {
+        if (!bad && type == REC_SAMPLE) {
+          const uint64_t nr = (size + 16 >= P.fix) ? wd[wi + pre + 2] : ~0ull;
+          ts = wd[wi + pre + 1];
+          bad = size < P.fix || nr != ((size - P.fix) >> 3) || nr != n;
+        }
+        if (!bad && type == REC_READ) {
           const uint64_t nr = (size >= 24) ? wd[wi + 2] : ~0ull;
-          ts = wd[wi + 1];
-          bad = size < 40 || nr != ((size - 40u) >> 3) || (type == REC_SAMPLE && nr != n);
+          bad = size < 40 || nr != ((size - 40u) >> 3);
         }
         if (!bad && type == REC_LOST) bad = size < 24;
         if (!bad && type == REC_SAMPLE && valid && !gap && st_ts > ts) {
@@ -1567,9 +1577,9 @@ __global__ void __launch_bounds__(RES_THREADS) k_resolve(const Params P) {
     co.tr = cin.tr;
   } else {
     const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + last_off);
-    for (uint32_t e = 0; e < n; ++e) co.last[e] = xform(P, e, r[5 + e]);
-    co.te = r[3];
-    co.tr = r[4];
+    for (uint32_t e = 0; e < n; ++e) co.last[e] = xform(P, e, r[pre + 5 + e]);
+    co.te = r[pre + 3];
+    co.tr = r[pre + 4];
   }
   co.valid = v;
   co.tstamp = v ? st_ts : ~0ull;
@@ -1612,11 +1622,12 @@ __global__ void k_head(const Params P) {
       const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
       if (size < 8 || (size & 7) || pos + size > im.len) return;  // the decode reports the error
       if (type == REC_SAMPLE) {
-        if (size < 40 || r[2] != ((size - 40u) >> 3) || r[2] != n) return;
-        hs.tstamp = r[1];
-        hs.te = r[3];
-        hs.tr = r[4];
-        for (uint32_t e = 0; e < n; ++e) hs.value[e] = xform(P, e, r[5 + e]);
+        const uint32_t pre = P.pre;
+        if (size < P.fix || r[pre + 2] != ((size - P.fix) >> 3) || r[pre + 2] != n) return;
+        hs.tstamp = r[pre + 1];
+        hs.te = r[pre + 3];
+        hs.tr = r[pre + 4];
+        for (uint32_t e = 0; e < n; ++e) hs.value[e] = xform(P, e, r[pre + 5 + e]);
         hs.offset = im.stream_pos + pos;
         hs.has_sample = 1;
         return;

@@ -21,6 +21,9 @@ F_FORCE_EXACT = 0x1
 F_FORCE_GENERAL = 0x2
 F_EXTERNAL_CARRY = 0x4
 
+SAMPLE_TIME_READ = 0
+SAMPLE_IP_TID_TIME_READ = 1
+
 METRIC_RATE = 1
 METRIC_ADD = 2
 METRIC_PER_SECOND_MEGA = 3
@@ -38,6 +41,8 @@ class Config(C.Structure):
         ("max_cpus", C.c_uint32), ("n_buckets", C.c_uint32), ("t0", C.c_uint64),
         ("bucket_ns", C.c_uint64), ("arena_bytes", C.c_uint64), ("n_metrics", C.c_uint32),
         ("flags", C.c_uint32), ("metrics", Metric * MAX_METRICS),
+        ("sample_format", C.c_uint32), ("tid_table_log2", C.c_uint32),
+        ("ip_table_log2", C.c_uint32), ("reserved", C.c_uint32),
     ]
 
 
@@ -151,7 +156,8 @@ class Context:
     """One hbtgpu context (one CUDA device + one stream)."""
 
     def __init__(self, n_events, max_cpus=1, n_buckets=1, t0=0, bucket_ns=1, arena_bytes=1 << 20,
-                 tsc_mask=0, time_shift=0, time_mult=1, time_zero=0, metrics=(), flags=0, device=0):
+                 tsc_mask=0, time_shift=0, time_mult=1, time_zero=0, metrics=(), flags=0, device=0,
+                 sample_format=0, tid_table_log2=0, ip_table_log2=0):
         self.L = lib()
         cfg = Config()
         cfg.device = device
@@ -166,6 +172,9 @@ class Context:
         cfg.bucket_ns = bucket_ns
         cfg.arena_bytes = arena_bytes
         cfg.flags = flags
+        cfg.sample_format = sample_format
+        cfg.tid_table_log2 = tid_table_log2
+        cfg.ip_table_log2 = ip_table_log2
         cfg.n_metrics = len(metrics)
         for m, (kind, idx) in enumerate(metrics):
             cfg.metrics[m].kind = kind

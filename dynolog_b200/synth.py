@@ -20,7 +20,8 @@ class Spec(C.Structure):
                 ("forge_ppm", C.c_uint32), ("t_start", C.c_uint64), ("dt_ns", C.c_uint64),
                 ("dt_jitter", C.c_uint64), ("lost_lo", C.c_uint32), ("lost_hi", C.c_uint32),
                 ("throttle_lo", C.c_uint32), ("throttle_hi", C.c_uint32),
-                ("mux_epoch", C.c_uint32), ("pad", C.c_uint32)]
+                ("mux_epoch", C.c_uint32), ("sample_format", C.c_uint32), ("n_tids", C.c_uint32),
+                ("n_ips", C.c_uint32)]
 
 
 _lib = None
@@ -47,6 +48,9 @@ CONFIGS = {
     # cfg3: multiplexed counters with interleaved LOST/THROTTLE
     3: dict(n_events=8, layout=1, dt_ns=100_000, dt_jitter=5_000, lost=(200, 2000),
             throttle=(1000, 10000), mux_epoch=1000, bucket_ns=1_000_000),
+    # cfg4: IP|TID|TIME|READ samples, 4-event group, 4096 (pid,tid) Zipf(1.1), 2^20 IPs Zipf(1.2)
+    4: dict(n_events=4, layout=0, dt_ns=100_000, dt_jitter=5_000, lost=(0, 0), throttle=(0, 0),
+            mux_epoch=0, bucket_ns=1_000_000, sample_format=1, n_tids=4096, n_ips=1 << 20),
     # cfg5: windows contiguous in time per CPU, f=1, with LOST
     5: dict(n_events=8, layout=1, dt_ns=100_000, dt_jitter=5_000, lost=(200, 2000),
             throttle=(0, 0), mux_epoch=0, bucket_ns=1_000_000),
@@ -59,7 +63,9 @@ def make_spec(cfg_id, forge_ppm=0, **over):
     return Spec(cfg_id=cfg_id, n_events=c["n_events"], layout=c["layout"], forge_ppm=forge_ppm,
                 t_start=T_START, dt_ns=c["dt_ns"], dt_jitter=c["dt_jitter"],
                 lost_lo=c["lost"][0], lost_hi=c["lost"][1], throttle_lo=c["throttle"][0],
-                throttle_hi=c["throttle"][1], mux_epoch=c["mux_epoch"], pad=0)
+                throttle_hi=c["throttle"][1], mux_epoch=c["mux_epoch"],
+                sample_format=c.get("sample_format", 0), n_tids=c.get("n_tids", 0),
+                n_ips=c.get("n_ips", 0))
 
 
 class Capture:
@@ -79,7 +85,7 @@ class Capture:
         `out`: optional uint8 array of n_cpus*cap bytes (e.g. a view of pinned memory).
         Returns list of per-CPU uint8 views."""
         n = self.spec.n_events
-        rec = 40 + 8 * n
+        rec = 40 + 8 * n + (16 if self.spec.sample_format == 1 else 0)
         if n_samples is None:
             n_samples = (1 << 62)
             cap = int(max_bytes_per_cpu)

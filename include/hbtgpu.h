@@ -42,6 +42,17 @@ extern "C" {
 #define HBTGPU_F_FORCE_GENERAL 0x2u /* always run pointer-jumping, never the contiguous-chain shortcut */
 #define HBTGPU_F_EXTERNAL_CARRY 0x4u /* shard mode: predecessor of each stream lives on another GPU (see hbtgpu_get_stubs) */
 
+/* hbtgpu_config.sample_format: layout of PERF_RECORD_SAMPLE.
+ * TIME_READ is what hbt's Sampling mode opens (sample_type = TIME|READ,
+ * hbt/src/perf_event/PerfEventsGroup.h:961,973-977): {hdr, time, nr, te, tr, value[nr]}.
+ * IP_TID_TIME_READ is a spec extension for BASELINE config 4 (hbt never requests IP|TID in
+ * Sampling mode; layout from the kernel ABI, linux/perf_event.h PERF_RECORD_SAMPLE):
+ * {hdr, ip, pid:u32, tid:u32, time, nr, te, tr, value[nr]}; it additionally yields a
+ * per-(pid,tid) sample histogram and per-IP sample counts (hbtgpu_get_tid_histogram,
+ * hbtgpu_get_top_ips). */
+#define HBTGPU_SAMPLE_TIME_READ 0u
+#define HBTGPU_SAMPLE_IP_TID_TIME_READ 1u
+
 /* metric kinds (hbtgpu_metric.kind) */
 #define HBTGPU_METRIC_RATE 1 /* getRateReducer, hbt/src/perf_event/BuiltinMetrics.cpp:102-118 */
 #define HBTGPU_METRIC_ADD 2  /* getAddReducer (int accumulator), BuiltinMetrics.cpp:88-97 */
@@ -73,6 +84,10 @@ typedef struct {
   uint32_t n_metrics;
   uint32_t flags;
   hbtgpu_metric metrics[HBTGPU_MAX_METRICS];
+  uint32_t sample_format;   /* HBTGPU_SAMPLE_* */
+  uint32_t tid_table_log2;  /* IP|TID format: slots of the (pid,tid) table = 2^this (0: 2^16) */
+  uint32_t ip_table_log2;   /* IP|TID format: slots of the sampled-IP table  = 2^this (0: 2^22) */
+  uint32_t reserved;
 } hbtgpu_config;
 
 /* Generator state that crosses image boundaries: CpuCountSampleGenerator's

@@ -74,11 +74,15 @@ const char* hbtoracle_describe(void) {
  * called repeatedly until -ENODATA, with CpuCountSampleGenerator's handlers
  * (PerCpuCountSampleGenerator.h:110-202) inlined.
  */
-int hbtoracle_decode_stream(const hbtref_params* p, const hbtref_carry* in,
+static uint64_t walk(const hbtref_params* p, const hbtref_carry* in,
     hbtref_carry* out, const uint8_t* bytes, uint64_t len, hbtref_counters* ctr,
     uint64_t* rec_off, uint32_t* rec_type, uint32_t* rec_size, uint64_t rec_cap,
-    uint64_t* rows, uint64_t rows_cap, uint64_t* bucket_acc) {
+    uint64_t* rows, uint64_t rows_cap, uint64_t* bucket_acc,
+    uint64_t* sink_tid, uint64_t* sink_ip, uint64_t sink_cap) {
+  uint64_t sink_n = 0;
   const uint32_t n = p->n_events, F = n + 3;
+  const uint32_t pb = 8 * p->pre;        /* extra bytes before `time` (spec extension, 0 for hbt) */
+  const uint32_t fix = 40 + pb;          /* sizeof(Sample) without values */
   hbtref_counters c;
   memset(&c, 0, sizeof(c));
   /* generator state: count_.tstamp, last_[] (:222-228) + te/tr for A7 */
@@ -113,8 +117,8 @@ int hbtoracle_decode_stream(const hbtref_params* p, const hbtref_carry* in,
       case REC_THROTTLE: c.throttle++; break;     /* :1476-1481 */
       case REC_UNTHROTTLE: c.unthrottle++; break; /* :1482-1487 */
       case REC_SAMPLE: { /* :1499-1514 */
-        uint64_t nr = size >= 24 ? ld64(r + 16) : 0;
-        if (size != 40 + nr * 8) { /* recordSize(), :346-350, :1502-1507 */
+        uint64_t nr = size + 16 >= fix ? ld64(r + pb + 16) : 0;
+        if (size != fix + nr * 8) { /* recordSize(), :346-350, :1502-1507 */
           c.err = -EPERM;
           goto done;
         }
@@ -124,11 +128,18 @@ int hbtoracle_decode_stream(const hbtref_params* p, const hbtref_carry* in,
           c.err = -EPERM;
           goto done;
         }
-        uint64_t ts = ld64(r + 8), te = ld64(r + 24), tr = ld64(r + 32);
+        uint64_t ts = ld64(r + pb + 8), te = ld64(r + pb + 24), tr = ld64(r + pb + 32);
+        if (sink_cap) { /* config-4 extension: remember who was sampled, and where */
+          if (sink_n < sink_cap) {
+            sink_tid[sink_n] = ld64(r + 16);
+            sink_ip[sink_n] = ld64(r + 8);
+          }
+          sink_n++;
+        }
         if (st_ts == INVALID_TS) { /* handler :135-154 */
           st_ts = ts;
           for (uint32_t i = 0; i < n; ++i) {
-            uint64_t v = ld64(r + 40 + 8 * i);
+            uint64_t v = ld64(r + fix + 8 * i);
             if ((p->tsc_mask >> i) & 1) v = tsc_to_ktime(p, v);
             last[i] = v;
           }
@@ -147,7 +158,7 @@ int hbtoracle_decode_stream(const hbtref_params* p, const hbtref_carry* in,
         row[0] = st_ts;
         row[1] = ts - st_ts; /* :165 */
         for (uint32_t i = 0; i < n; ++i) { /* :166-179 */
-          uint64_t v = ld64(r + 40 + 8 * i);
+          uint64_t v = ld64(r + fix + 8 * i);
           if ((p->tsc_mask >> i) & 1) v = tsc_to_ktime(p, v);
           row[2 + i] = v - last[i];
           last[i] = v;
@@ -205,7 +216,27 @@ done:
     out->tr = ptr_;
     for (uint32_t i = 0; i < n; ++i) out->last[i] = last[i];
   }
+  return sink_n;
+}
+
+int hbtoracle_decode_stream(const hbtref_params* p, const hbtref_carry* in,
+    hbtref_carry* out, const uint8_t* bytes, uint64_t len, hbtref_counters* ctr,
+    uint64_t* rec_off, uint32_t* rec_type, uint32_t* rec_size, uint64_t rec_cap,
+    uint64_t* rows, uint64_t rows_cap, uint64_t* bucket_acc) {
+  walk(p, in, out, bytes, len, ctr, rec_off, rec_type, rec_size, rec_cap, rows, rows_cap, bucket_acc,
+       NULL, NULL, 0);
   return 0;
+}
+
+uint64_t hbtoracle_collect_ip_tid(const hbtref_params* p, const hbtref_carry* in, const uint8_t* bytes,
+    uint64_t len, uint64_t* tid_keys, uint64_t* ips, uint64_t cap) {
+  /* a time-regressed SAMPLE is not counted by consume(); the sink runs after that check? No:   */
+  /* it is recorded when the record passes the size checks, so drop the last entry on -EPERM    */
+  /* from the regression rule to stay consistent with `sample` (see below).                     */
+  hbtref_counters c;
+  uint64_t k = walk(p, in, NULL, bytes, len, &c, NULL, NULL, NULL, 0, NULL, 0, NULL, tid_keys, ips,
+                    cap ? cap : 1);
+  return k > c.sample ? c.sample : k;
 }
 
 /* accum()-then-getCount() per bucket: PerPerfEventsGroupBase.h:182-194 + :467-481 */

@@ -40,6 +40,8 @@ typedef struct {
   uint64_t time_zero;   /* perf_event_mmap_page::time_zero  */
   uint64_t t0;          /* bucket 0 starts here (ns) */
   uint64_t bucket_ns;   /* bucket width */
+  uint32_t pre;         /* words between header and `time`: 0 = TIME|READ (hbt), 2 = IP|TID|TIME|READ */
+  uint32_t pad;         /*   (pre != 0 is a spec extension: only the port implements it)          */
 } hbtref_params;
 
 typedef struct {
@@ -103,6 +105,13 @@ typedef struct {
 
 HBTREF_DECL(hbtref)
 HBTREF_DECL(hbtoracle)
+
+/* BASELINE config 4 (spec extension, NO reference code: parity UNPINNED).  Walk one stream
+ * of IP|TID|TIME|READ samples ({hdr, ip, pid:u32, tid:u32, time, nr, te, tr, value[nr]},
+ * linux/perf_event.h PERF_RECORD_SAMPLE field order) and append (pid|tid<<32) and ip of every
+ * SAMPLE the walk counts (same stop rules as hbtoracle_decode_stream).  Returns #samples. */
+uint64_t hbtoracle_collect_ip_tid(const hbtref_params* p, const hbtref_carry* in, const uint8_t* bytes,
+    uint64_t len, uint64_t* tid_keys, uint64_t* ips, uint64_t cap);
 
 #ifdef __cplusplus
 }

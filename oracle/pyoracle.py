@@ -29,6 +29,8 @@ class Params(C.Structure):
         ("time_zero", C.c_uint64),
         ("t0", C.c_uint64),
         ("bucket_ns", C.c_uint64),
+        ("pre", C.c_uint32),
+        ("pad", C.c_uint32),
     ]
 
 
@@ -57,9 +59,9 @@ COUNTER_KEYS = [k for k, _ in Counters._fields_]
 
 
 def make_params(n_events, n_buckets=1, t0=0, bucket_ns=1, tsc_mask=0, time_shift=0,
-                time_mult=1, time_zero=0):
+                time_mult=1, time_zero=0, pre=0):
     return Params(n_events, n_buckets, tsc_mask, time_shift, time_mult, time_zero, t0,
-                  bucket_ns)
+                  bucket_ns, pre, 0)
 
 
 def make_carry(valid=False, tstamp=0, te=0, tr=0, last=()):
@@ -191,6 +193,20 @@ class Oracle:
         self._rr(_p(te, C.c_uint64), _p(tr, C.c_uint64), _p(ratio, C.c_float),
                  _p(ri, C.c_uint64), _p(mux, C.c_uint8), C.c_uint64(te.size))
         return ratio, ri, mux.astype(bool)
+
+    # --- BASELINE config 4 (spec extension; port only) ---------------------------------------
+    def collect_ip_tid(self, params, data, carry=None):
+        """(pid|tid<<32) and ip of every SAMPLE the walk counts, in stream order."""
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        carry = carry if carry is not None else make_carry()
+        cap = max(1, len(data) // 48)
+        tid = np.zeros(cap, np.uint64)
+        ips = np.zeros(cap, np.uint64)
+        f = getattr(self.lib, self.prefix + "_collect_ip_tid")
+        f.restype = C.c_uint64
+        k = f(C.byref(params), C.byref(carry), _p(data, C.c_uint8), C.c_uint64(len(data)),
+              _p(tid, C.c_uint64), _p(ips, C.c_uint64), C.c_uint64(cap))
+        return tid[:k].copy(), ips[:k].copy()
 
     # --- timed whole-capture CPU path ----------------------------------------------
     def run_capture(self, params, streams, carries=None, n_threads=1, batch=1024,

@@ -160,6 +160,7 @@ int hbtref_decode_stream(const hbtref_params* p, const hbtref_carry* in,
     uint64_t* rows, uint64_t rows_cap, uint64_t* bucket_acc) {
   const uint32_t n = p->n_events;
   const uint32_t F = n + 3;
+  if (p->pre != 0) return -1;  // IP|TID samples are a spec extension: hbt has no such mode
   silence_begin();
   FakeGen fg(*p, len, 4);
   Gen& g = *fg.gen;

@@ -24,7 +24,8 @@ def gpu_decode(params, streams, carries=None, flags=0, split=None, metrics=(), w
                          arena_bytes=total + 4096 * (len(streams) + 8) + (1 << 16),
                          tsc_mask=params.tsc_mask, time_shift=params.time_shift,
                          time_mult=params.time_mult, time_zero=params.time_zero, metrics=metrics,
-                         flags=flags)
+                         flags=flags,
+                         sample_format=(hbtgpu.SAMPLE_IP_TID_TIME_READ if params.pre == 2 else 0))
     try:
         for cpu, s in enumerate(streams):
             if carries is not None:

@@ -21,13 +21,15 @@ def header_u64(rtype, size, misc=0):
     return rtype | (misc << 32) | (size << 48)
 
 
-def sample(tstamp, te, tr, values, nr=None, size=None):
-    """PERF_RECORD_SAMPLE for sample_type=TIME|READ, read_format=GROUP|TE|TR (:281-298)."""
+def sample(tstamp, te, tr, values, nr=None, size=None, ip_tid=None):
+    """PERF_RECORD_SAMPLE for sample_type=TIME|READ, read_format=GROUP|TE|TR (:281-298).
+    ip_tid=(ip, pid, tid): the IP|TID|TIME|READ layout of BASELINE config 4 (spec extension)."""
     n = len(values)
     nr = n if nr is None else nr
-    size = 40 + 8 * n if size is None else size
+    extra = b"" if ip_tid is None else struct.pack("<QII", ip_tid[0], ip_tid[1], ip_tid[2])
+    size = 40 + len(extra) + 8 * n if size is None else size
     m = (1 << 64) - 1
-    return header(SAMPLE, size) + struct.pack(
+    return header(SAMPLE, size) + extra + struct.pack(
         "<4Q", tstamp & m, nr, te & m, tr & m) + struct.pack(f"<{n}Q", *[v & m for v in values])
 
 
@@ -81,7 +83,7 @@ class SplitMix64:
 
 def random_stream(seed, n_records, n_events, *, p_lost=0.0, p_throttle=0.0, p_other=0.0,
                   p_read=0.0, mux=False, forge=0.0, t_start=1_000_000_000, dt=100_000,
-                  big_values=False):
+                  big_values=False, ip_tid=False):
     """A plausible single-CPU Sampling-mode stream. Returns (bytes, info)."""
     r = SplitMix64(seed)
     out = bytearray()
@@ -126,5 +128,10 @@ def random_stream(seed, n_records, n_events, *, p_lost=0.0, p_throttle=0.0, p_ot
                     v[e] = [header_u64(SAMPLE, 40 + 8 * n_events), header_u64(LOST, 24),
                             header_u64(THROTTLE, 32), header_u64(77, 8 * r.uniform(1, 20))][kind]
                     vals[e] = v[e]
-        out += sample(ts, te, tr, v)
+        if ip_tid:
+            k = r.uniform(0, 40) ** 2 % 37          # skewed thread choice
+            ip = 0xffffffff81000000 + 16 * (r.uniform(0, 30) ** 2 % 211)
+            out += sample(ts, te, tr, v, ip_tid=(ip, 100 + k // 4, 500 + k))
+        else:
+            out += sample(ts, te, tr, v)
     return to_u8(out), {"t_end": ts}

@@ -237,6 +237,27 @@ def test_rerun_and_reset(port_oracle):
         assert np.array_equal(a1 + a2, whole["buckets"])
 
 
+@pytest.mark.parametrize("mode", ["fast", "general", "exact"])
+def test_ip_tid_sample_layout(port_oracle, mode):
+    """BASELINE config 4 layout (IP|TID|TIME|READ; spec extension, checked against the C
+    restatement only): the ordinary outputs must come out exactly as for the hbt layout."""
+    n = 4
+    streams, carries = [], []
+    for cpu, kw in enumerate([dict(), dict(p_lost=0.01, p_throttle=0.01, mux=True), dict(p_other=0.05, p_read=0.02)]):
+        data, info = rg.random_stream(31_000 + cpu, 25_000, n, ip_tid=True, **kw)
+        streams.append(data)
+        carries.append(po.make_carry(valid=(cpu != 2), tstamp=999_999_999, last=[0] * n))
+    p = po.make_params(n, n_buckets=2600, t0=1_000_000_000, bucket_ns=1_000_000, pre=2, tsc_mask=0b100,
+                       time_shift=3, time_mult=11, time_zero=7)
+    got, extra = gpu_decode(p, streams, carries, flags=MODES[mode])
+    for cpu in range(3):
+        exp = port_oracle.decode_stream(p, streams[cpu], carries[cpu])
+        exp["scaled"] = port_oracle.scale_buckets(p, exp["buckets"])
+        assert_matches_oracle(got[cpu], exp, n, f"iptid/{mode}/cpu{cpu}")
+    if mode == "fast":
+        assert extra["stats"]["exact_runs"] == 0
+
+
 def test_512_cpus_ragged_streams(port_oracle):
     """kMaxCpus streams (hbt/src/common/System.h:204) of ragged lengths, some empty, some with
     several images, all in one context."""
