@@ -55,6 +55,10 @@ struct hbtgpu_ctx {
   double* d_metric = nullptr;
   uint32_t* d_valid = nullptr;
   uint32_t* d_flags = nullptr;
+  // IP|TID format: attribution tables
+  uint64_t *d_tid_keys = nullptr, *d_ip_keys = nullptr;
+  unsigned long long *d_tid_cnt = nullptr, *d_ip_cnt = nullptr, *d_attr_special = nullptr;
+  uint32_t tid_slots = 0, ip_slots = 0;
   ChunkDesc* d_chunks = nullptr;
   ChunkIO* d_io = nullptr;
   ImageDesc* d_images = nullptr;
@@ -241,6 +245,13 @@ Params make_params(hbtgpu_ctx* ctx) {
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
     P.pre = ctx->cfg.sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ ? 2 : 0;
     P.fix = 40 + 8 * P.pre;
+    P.tid_keys = ctx->d_tid_keys;
+    P.tid_cnt = ctx->d_tid_cnt;
+    P.ip_keys = ctx->d_ip_keys;
+    P.ip_cnt = ctx->d_ip_cnt;
+    P.attr_special = ctx->d_attr_special;
+    P.tid_mask = ctx->tid_slots ? ctx->tid_slots - 1 : 0;
+    P.ip_mask = ctx->ip_slots ? ctx->ip_slots - 1 : 0;
     const uint64_t S = 5ull + P.pre + ctx->cfg.n_events;
     P.s_magic = static_cast<uint32_t>(((1ull << 32) + S - 1) / S);
   }
@@ -362,6 +373,34 @@ int set_smem(hbtgpu_ctx* ctx, K kernel, size_t extra = 0) {
 
 }  // namespace
 
+namespace {
+struct MathBuf {
+  hbtgpu_ctx* ctx;
+  uint8_t* base;
+  size_t off = 0;
+  template <class T>
+  T* take(size_t n) {
+    T* p = reinterpret_cast<T*>(base + off);
+    off += (n * sizeof(T) + 255) / 256 * 256;
+    return p;
+  }
+};
+int math_reserve(hbtgpu_ctx* ctx, size_t bytes, MathBuf* mb) {
+  CK(cudaSetDevice(ctx->device));
+  uint8_t* p = static_cast<uint8_t*>(ctx->d_math);
+  if (int r = ensure(ctx, &p, &ctx->cap_math, bytes)) {
+    ctx->d_math = p;
+    return r;
+  }
+  ctx->d_math = p;
+  mb->ctx = ctx;
+  mb->base = p;
+  return 0;
+}
+inline size_t pad256(size_t b) { return (b + 255) / 256 * 256; }
+inline unsigned nblk(size_t n) { return static_cast<unsigned>((n + 255) / 256); }
+}  // namespace
+
 extern "C" {
 
 const char* hbtgpu_version(void) { return "hbtgpu 0.1 (sm_100a)"; }
@@ -444,6 +483,20 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_valid), ctx->n_cells * 4));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_flags), FLAG_COUNT * 4));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_streams), ns * sizeof(StreamDesc)));
+  if (cfg->sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ) {
+    const uint32_t tl = cfg->tid_table_log2 ? cfg->tid_table_log2 : 16, il = cfg->ip_table_log2 ? cfg->ip_table_log2 : 22;
+    if (tl < 4 || tl > 28 || il < 4 || il > 28) {
+      fail(ctx, -EINVAL, "table_log2 out of range [4,28]");
+      return bail(-EINVAL);
+    }
+    ctx->tid_slots = 1u << tl;
+    ctx->ip_slots = 1u << il;
+    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tid_keys), ctx->tid_slots * 8ull));
+    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tid_cnt), ctx->tid_slots * 8ull));
+    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_keys), ctx->ip_slots * 8ull));
+    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_cnt), ctx->ip_slots * 8ull));
+    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_attr_special), 4 * 8));
+  }
   CKC(cudaMemsetAsync(ctx->d_carry_in, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
   CKC(cudaMemsetAsync(ctx->d_carry_out, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
   CKC(cudaMemsetAsync(ctx->d_head, 0, ns * sizeof(hbtgpu_head_stub), ctx->stream));
@@ -467,7 +520,8 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
   void* ptrs[] = {ctx->arena, ctx->d_carry_in, ctx->d_carry_out, ctx->d_carry_init, ctx->d_head, ctx->d_counters,
                   ctx->d_acc, ctx->d_scaled, ctx->d_metric, ctx->d_valid, ctx->d_flags,
                   ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
-                  ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math};
+                  ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_tid_keys,
+                  ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
@@ -621,6 +675,13 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   const bool external = (ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY) != 0;
   // shard mode: every stream starts from an invalid state; the boundary row is added later
   if (external) CK(cudaMemsetAsync(ctx->d_carry_in, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
+  if (ctx->tid_slots) {  // attribution tables start empty
+    CK(cudaMemsetAsync(ctx->d_tid_keys, 0xFF, ctx->tid_slots * 8ull, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_tid_cnt, 0, ctx->tid_slots * 8ull, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_ip_keys, 0xFF, ctx->ip_slots * 8ull, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_ip_cnt, 0, ctx->ip_slots * 8ull, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_attr_special, 0, 4 * 8, ctx->stream));
+  }
   // streams without images keep their carry: carry_out := carry_in
   CK(cudaMemcpyAsync(ctx->d_carry_out, ctx->d_carry_in, ns * sizeof(hbtgpu_carry),
                      cudaMemcpyDeviceToDevice, ctx->stream));
@@ -753,6 +814,86 @@ int hbtgpu_get_records(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* off, uint32_t* t
     if (size) CK(cudaMemcpyAsync(size, ctx->d_rec_size + b, k * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
   }
+  return 0;
+}
+
+int hbtgpu_get_tid_histogram(hbtgpu_ctx* ctx, uint32_t* pid, uint32_t* tid, uint64_t* count, size_t cap,
+                             size_t* n) {
+  if (!ctx || !n) return -EINVAL;
+  if (!ctx->tid_slots) return fail(ctx, -EINVAL, "context was not created with HBTGPU_SAMPLE_IP_TID_TIME_READ");
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  CK(cudaSetDevice(ctx->device));
+  if (int r = fetch_counters(ctx)) return r;  // surfaces exact-path / internal errors first
+  std::vector<uint64_t> keys(ctx->tid_slots), cnt(ctx->tid_slots);
+  unsigned long long special[4];
+  CK(cudaMemcpyAsync(keys.data(), ctx->d_tid_keys, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(cnt.data(), ctx->d_tid_cnt, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(special, ctx->d_attr_special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (special[2]) return fail(ctx, -ENOSPC, "(pid,tid) table overflowed: raise hbtgpu_config.tid_table_log2");
+  size_t k = 0;
+  auto put = [&](uint64_t key, uint64_t c) {
+    if (k < cap) {
+      if (pid) pid[k] = static_cast<uint32_t>(key);
+      if (tid) tid[k] = static_cast<uint32_t>(key >> 32);
+      if (count) count[k] = c;
+    }
+    ++k;
+  };
+  for (uint32_t i = 0; i < ctx->tid_slots; ++i)
+    if (keys[i] != ~0ull) put(keys[i], cnt[i]);
+  if (special[0]) put(~0ull, special[0]);
+  *n = k;
+  return 0;
+}
+
+int hbtgpu_get_top_ips(hbtgpu_ctx* ctx, uint32_t k, uint64_t* ip, uint64_t* count, size_t* n) {
+  if (!ctx || !n) return -EINVAL;
+  if (!ctx->ip_slots) return fail(ctx, -EINVAL, "context was not created with HBTGPU_SAMPLE_IP_TID_TIME_READ");
+  if (!ctx->ran) return fail(ctx, -EINVAL, "hbtgpu_run has not been called");
+  if (k > 65536) return fail(ctx, -EINVAL, "k must be <= 65536");
+  CK(cudaSetDevice(ctx->device));
+  if (int r = fetch_counters(ctx)) return r;
+  *n = 0;
+  if (k == 0) return 0;
+  // scratch: compacted (key, count) of the occupied slots, block partials, results, counter
+  const size_t slots = ctx->ip_slots;
+  const size_t bytes = (slots + 1) * 16 + TOPK_BLOCKS * sizeof(TopBest) + static_cast<size_t>(k) * 16 + 256;
+  MathBuf mb;
+  if (int r = math_reserve(ctx, bytes + 8 * 256, &mb)) return r;
+  uint64_t* ckey = mb.take<uint64_t>(slots + 1);
+  unsigned long long* ccnt = mb.take<unsigned long long>(slots + 1);
+  TopBest* partial = mb.take<TopBest>(TOPK_BLOCKS);
+  uint64_t* rkey = mb.take<uint64_t>(k);
+  unsigned long long* rcnt = mb.take<unsigned long long>(k);
+  unsigned int* d_m = mb.take<unsigned int>(1);
+  CK(cudaMemsetAsync(d_m, 0, 4, ctx->stream));
+  k_attr_compact<<<148 * 8, 256, 0, ctx->stream>>>(ctx->d_ip_keys, ctx->d_ip_cnt, ctx->ip_slots - 1, ckey, ccnt, d_m);
+  unsigned int m = 0;
+  unsigned long long special[4];
+  CK(cudaMemcpyAsync(&m, d_m, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(special, ctx->d_attr_special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (special[3]) return fail(ctx, -ENOSPC, "IP table overflowed: raise hbtgpu_config.ip_table_log2");
+  if (special[1]) {  // samples whose ip equals the empty-slot marker live in a side counter
+    const uint64_t key = ~0ull;
+    CK(cudaMemcpyAsync(ckey + m, &key, 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ccnt + m, &special[1], 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ++m;
+  }
+  const uint32_t kk = std::min<uint32_t>(k, m);
+  for (uint32_t r = 0; r < kk; ++r) {
+    k_topk_partial<<<TOPK_BLOCKS, TOPK_THREADS, 0, ctx->stream>>>(ckey, ccnt, m, partial);
+    k_topk_pick<<<1, TOPK_THREADS, 0, ctx->stream>>>(partial, TOPK_BLOCKS, ccnt, r, rkey, rcnt);
+  }
+  CK(cudaGetLastError());
+  if (kk) {
+    if (ip) CK(cudaMemcpyAsync(ip, rkey, kk * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+    if (count) CK(cudaMemcpyAsync(count, rcnt, kk * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  *n = kk;
   return 0;
 }
 
@@ -910,33 +1051,6 @@ int hbtgpu_get_stats(hbtgpu_ctx* ctx, hbtgpu_stats* out) {
 
 // ---- elementwise arithmetic ---------------------------------------------------------
 
-namespace {
-struct MathBuf {
-  hbtgpu_ctx* ctx;
-  uint8_t* base;
-  size_t off = 0;
-  template <class T>
-  T* take(size_t n) {
-    T* p = reinterpret_cast<T*>(base + off);
-    off += (n * sizeof(T) + 255) / 256 * 256;
-    return p;
-  }
-};
-int math_reserve(hbtgpu_ctx* ctx, size_t bytes, MathBuf* mb) {
-  CK(cudaSetDevice(ctx->device));
-  uint8_t* p = static_cast<uint8_t*>(ctx->d_math);
-  if (int r = ensure(ctx, &p, &ctx->cap_math, bytes)) {
-    ctx->d_math = p;
-    return r;
-  }
-  ctx->d_math = p;
-  mb->ctx = ctx;
-  mb->base = p;
-  return 0;
-}
-inline size_t pad256(size_t b) { return (b + 255) / 256 * 256; }
-inline unsigned nblk(size_t n) { return static_cast<unsigned>((n + 255) / 256); }
-}  // namespace
 
 extern "C" {
 
@@ -1169,6 +1283,8 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
     return na_fail(-EINVAL, "n_buckets / bucket_ns out of range");
   if (cfg->time_shift > 63 || (cfg->tsc_mask != 0 && cfg->time_mult == 0))
     return na_fail(-EINVAL, "bad TSC conversion parameters");
+  if (cfg->sample_format != HBTGPU_SAMPLE_TIME_READ)
+    return na_fail(-EINVAL, "only HBTGPU_SAMPLE_TIME_READ is supported here (the IP|TID tables need allocations)");
   if (image_bytes > HBTGPU_NOALLOC_MAX_IMAGE_BYTES)
     return na_fail(-E2BIG,
                    "image of %zu bytes exceeds HBTGPU_NOALLOC_MAX_IMAGE_BYTES (%llu): this entry "

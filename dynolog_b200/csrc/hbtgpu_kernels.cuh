@@ -163,6 +163,14 @@ struct Params {
   // pre = words between the header and `time` (0 for sample_type TIME|READ as hbt opens it,
   // 2 with IP|TID in front); fix = bytes of a SAMPLE without its values (40 + 8*pre).
   uint32_t pre, fix;
+  // IP|TID format only: open-addressing tables key -> sample count (key ~0 = empty slot; a
+  // sample whose key is ~0 itself is counted in attr_special[0] / [1])
+  uint64_t* tid_keys;
+  unsigned long long* tid_cnt;
+  uint64_t* ip_keys;
+  unsigned long long* ip_cnt;
+  unsigned long long* attr_special;  // [0] tid key ~0, [1] ip ~0, [2] tid overflow, [3] ip overflow
+  uint32_t tid_mask, ip_mask;
   // bucket index = (ts - t0) / bucket_ns without a 64-bit division (set by the host)
   uint64_t range_ns;    // n_buckets * bucket_ns, saturated
   uint64_t bucket_magic;  // floor(2^64 / bucket_ns) (bucket_ns not a power of two)
@@ -562,6 +570,41 @@ __device__ __forceinline__ void red_add(uint64_t* p, uint64_t v) {
   atomicAdd(reinterpret_cast<unsigned long long*>(p), static_cast<unsigned long long>(v));
 }
 
+constexpr uint64_t ATTR_EMPTY = ~0ull;
+
+__device__ __forceinline__ uint32_t attr_hash(uint64_t k) {
+  k ^= k >> 30;
+  k *= 0xBF58476D1CE4E5B9ull;
+  k ^= k >> 27;
+  k *= 0x94D049BB133111EBull;
+  k ^= k >> 31;
+  return static_cast<uint32_t>(k);
+}
+
+// count += c for `key` in an open-addressing table (linear probing, insert on first use)
+__device__ __forceinline__ void attr_add(uint64_t* keys, unsigned long long* cnt, uint32_t mask, uint64_t key,
+                                         unsigned long long c, unsigned long long* special,
+                                         unsigned long long* overflow) {
+  if (key == ATTR_EMPTY) {
+    atomicAdd(special, c);
+    return;
+  }
+  uint32_t slot = attr_hash(key) & mask;
+  for (uint32_t probe = 0; probe <= mask; ++probe) {
+    uint64_t k = reinterpret_cast<volatile uint64_t*>(keys)[slot];
+    if (k == ATTR_EMPTY) {
+      k = atomicCAS(reinterpret_cast<unsigned long long*>(keys + slot), ATTR_EMPTY, key);
+      if (k == ATTR_EMPTY) k = key;
+    }
+    if (k == key) {
+      atomicAdd(cnt + slot, c);
+      return;
+    }
+    slot = (slot + 1) & mask;
+  }
+  atomicAdd(overflow, c);  // table full: reported, never silently dropped
+}
+
 struct TileCtx {
   uint64_t tile_abs;    // arena offset of word 0 of the buffer
   uint64_t stream_off;  // stream byte offset of word 0 of the buffer
@@ -603,6 +646,10 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
           a = __vmaxu2(a, (j + 1) << 16);
           b += 1;
           s.next[j] = IDX_NONE;
+          if (!SCOUT && MODE == MODE_AGG && P.pre == 2) {
+            attr_add(P.ip_keys, P.ip_cnt, P.ip_mask, buf[p + 1], 1, P.attr_special + 1, P.attr_special + 3);
+            attr_add(P.tid_keys, P.tid_cnt, P.tid_mask, buf[p + 2], 1, P.attr_special + 0, P.attr_special + 2);
+          }
         }
       } else if (type == REC_LOST) {
         if (size < 24) {
@@ -919,6 +966,27 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
     }
     tc.rows_before += static_cast<uint32_t>(K - skip);
     tc.recs_before += static_cast<uint32_t>(K);
+  }
+
+  if (MODE == MODE_AGG && pre == 2) {
+    // who was sampled and where: one table update per distinct key per warp
+#pragma unroll
+    for (int g = 0; g < MAXG; ++g) {
+      const int j0 = (g * NWARP + warp) * OWN - 1;
+      if (j0 >= K) break;
+      const int jr = j0 + lane;
+      const bool own = lane < 31 && jr >= 0 && jr < K;
+      const uint32_t p = entry + (own ? jr : 0) * S;
+      // lanes without a record get keys no other lane can have
+      const uint64_t ip = own ? buf[p + 1] : (0x8000000000000000ull | lane);
+      const uint64_t tk = own ? buf[p + 2] : (0x8000000000000000ull | lane);
+      const uint32_t gi = __match_any_sync(0xffffffffu, ip);
+      const uint32_t gt = __match_any_sync(0xffffffffu, tk);
+      if (own && static_cast<int>(__ffs(gi)) - 1 == lane)
+        attr_add(P.ip_keys, P.ip_cnt, P.ip_mask, ip, __popc(gi), P.attr_special + 1, P.attr_special + 3);
+      if (own && static_cast<int>(__ffs(gt)) - 1 == lane)
+        attr_add(P.tid_keys, P.tid_cnt, P.tid_mask, tk, __popc(gt), P.attr_special + 0, P.attr_special + 2);
+    }
   }
 
   // pass 2
@@ -1597,6 +1665,90 @@ __global__ void k_clear(const Params P, uint64_t acc_words) {
   const uint64_t nctr = static_cast<uint64_t>(P.n_streams) * C_SLOTS;
   for (uint64_t i = i0; i < nctr; i += stride)
     if ((i % C_SLOTS) < C_ERR) P.counters[i] = 0;
+  if (P.pre == 2) {
+    for (uint64_t i = i0; i <= P.tid_mask; i += stride) {
+      P.tid_keys[i] = ATTR_EMPTY;
+      P.tid_cnt[i] = 0;
+    }
+    for (uint64_t i = i0; i <= P.ip_mask; i += stride) {
+      P.ip_keys[i] = ATTR_EMPTY;
+      P.ip_cnt[i] = 0;
+    }
+    if (i0 < 4) P.attr_special[i0] = 0;
+  }
+}
+
+// ------------------------------------------------------------------------------------
+// top-K of the sampled-IP table by (count descending, ip ascending): compact the table, then
+// K rounds of arg-max (a few MB per round; K is ~100).
+__global__ void k_attr_compact(const uint64_t* keys, const unsigned long long* cnt, uint32_t mask,
+                               uint64_t* out_key, unsigned long long* out_cnt, unsigned int* n_out) {
+  const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+  for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i <= mask; i += stride) {
+    const uint64_t k = keys[i];
+    if (k != ATTR_EMPTY) {
+      const unsigned int o = atomicAdd(n_out, 1u);
+      out_key[o] = k;
+      out_cnt[o] = cnt[i];
+    }
+  }
+}
+
+struct TopBest {
+  unsigned long long cnt;
+  uint64_t key;
+  uint32_t idx;
+};
+__device__ __forceinline__ bool top_better(unsigned long long c, uint64_t k, unsigned long long bc, uint64_t bk) {
+  return c > bc || (c == bc && k < bk);
+}
+constexpr int TOPK_BLOCKS = 296, TOPK_THREADS = 256;
+
+// stage 1: every block finds its best remaining entry (count 0 = already taken / none)
+__global__ void __launch_bounds__(TOPK_THREADS) k_topk_partial(const uint64_t* key, const unsigned long long* cnt,
+                                                               uint32_t m, TopBest* partial) {
+  __shared__ TopBest sh[TOPK_THREADS];
+  TopBest b{0, ~0ull, 0xFFFFFFFFu};
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+    const unsigned long long c = cnt[i];
+    const uint64_t k = key[i];
+    if (c && top_better(c, k, b.cnt, b.key)) b = TopBest{c, k, i};
+  }
+  sh[threadIdx.x] = b;
+  __syncthreads();
+  for (int d = TOPK_THREADS / 2; d > 0; d >>= 1) {
+    if (threadIdx.x < d) {
+      const TopBest o = sh[threadIdx.x + d];
+      if (o.cnt && top_better(o.cnt, o.key, sh[threadIdx.x].cnt, sh[threadIdx.x].key)) sh[threadIdx.x] = o;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+}
+// stage 2: one block picks the winner, records it as result `r`, and takes it out of the pool
+__global__ void __launch_bounds__(TOPK_THREADS) k_topk_pick(const TopBest* partial, uint32_t n_partial,
+                                                            unsigned long long* cnt, uint32_t r,
+                                                            uint64_t* out_key, unsigned long long* out_cnt) {
+  __shared__ TopBest sh[TOPK_THREADS];
+  TopBest b{0, ~0ull, 0xFFFFFFFFu};
+  for (uint32_t i = threadIdx.x; i < n_partial; i += blockDim.x) {
+    const TopBest o = partial[i];
+    if (o.cnt && top_better(o.cnt, o.key, b.cnt, b.key)) b = o;
+  }
+  sh[threadIdx.x] = b;
+  __syncthreads();
+  for (int d = TOPK_THREADS / 2; d > 0; d >>= 1) {
+    if (threadIdx.x < d) {
+      const TopBest o = sh[threadIdx.x + d];
+      if (o.cnt && top_better(o.cnt, o.key, sh[threadIdx.x].cnt, sh[threadIdx.x].key)) sh[threadIdx.x] = o;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    out_key[r] = sh[0].key;
+    out_cnt[r] = sh[0].cnt;
+    if (sh[0].cnt) cnt[sh[0].idx] = 0;
+  }
 }
 
 // ------------------------------------------------------------------------------------

@@ -88,7 +88,8 @@ ABI_SYMBOLS = [
     "hbtgpu_create", "hbtgpu_destroy", "hbtgpu_last_error", "hbtgpu_set_carry",
     "hbtgpu_submit_image", "hbtgpu_submit_images", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
     "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows",
-    "hbtgpu_get_records", "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_get_buckets_host_async",
+    "hbtgpu_get_records", "hbtgpu_get_tid_histogram", "hbtgpu_get_top_ips",
+    "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_get_buckets_host_async",
     "hbtgpu_derive",
     "hbtgpu_get_stubs", "hbtgpu_compose_tail", "hbtgpu_apply_boundaries", "hbtgpu_stub_bytes",
     "hbtgpu_export_stubs_device", "hbtgpu_apply_boundaries_gathered", "hbtgpu_acc_device", "hbtgpu_stream",
@@ -288,6 +289,27 @@ class Context:
             self._ck(self.L.hbtgpu_get_records(self.h, C.c_uint32(cpu), _ptr(off), _ptr(typ),
                                                _ptr(siz), C.c_size_t(n.value), C.byref(n)))
         return off, typ, siz
+
+    def tid_histogram(self):
+        """IP|TID format: dict {(pid, tid): samples} over all cpus."""
+        n = C.c_size_t(0)
+        z = C.c_void_p(0)
+        self._ck(self.L.hbtgpu_get_tid_histogram(self.h, z, z, z, C.c_size_t(0), C.byref(n)))
+        pid = np.zeros(n.value, np.uint32)
+        tid = np.zeros(n.value, np.uint32)
+        cnt = np.zeros(n.value, np.uint64)
+        if n.value:
+            self._ck(self.L.hbtgpu_get_tid_histogram(self.h, _ptr(pid), _ptr(tid), _ptr(cnt),
+                                                     C.c_size_t(n.value), C.byref(n)))
+        return {(int(a), int(b)): int(c) for a, b, c in zip(pid, tid, cnt)}
+
+    def top_ips(self, k):
+        """IP|TID format: [(ip, samples)] of the k most-sampled IPs, (count desc, ip asc)."""
+        ip = np.zeros(k, np.uint64)
+        cnt = np.zeros(k, np.uint64)
+        n = C.c_size_t(0)
+        self._ck(self.L.hbtgpu_get_top_ips(self.h, C.c_uint32(k), _ptr(ip), _ptr(cnt), C.byref(n)))
+        return [(int(a), int(b)) for a, b in zip(ip[:n.value], cnt[:n.value])]
 
     def buckets(self, want_acc=True, want_scaled=True, want_metric=True, want_valid=True):
         """Returns dict of host arrays: acc[cpu,bucket,n+3], scaled[cpu,bucket,n], metric, valid."""

@@ -199,6 +199,16 @@ int hbtgpu_get_rows(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* rows, size_t cap_ro
 int hbtgpu_get_records(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* off, uint32_t* type, uint32_t* size,
                        size_t cap, size_t* n_records);
 
+/* HBTGPU_SAMPLE_IP_TID_TIME_READ only (BASELINE config 4; spec extension, no reference code).
+ * Per-(pid,tid) sample histogram over all cpus: one entry per distinct (pid,tid) seen in a
+ * SAMPLE the walk counted, in unspecified order.  *n is set to the number of entries; at most
+ * `cap` are written.  -ENOSPC if the table (hbtgpu_config.tid_table_log2) overflowed. */
+int hbtgpu_get_tid_histogram(hbtgpu_ctx* ctx, uint32_t* pid, uint32_t* tid, uint64_t* count, size_t cap,
+                             size_t* n);
+/* The k most-sampled instruction pointers over all cpus, ordered by (count descending, ip
+ * ascending).  *n = min(k, distinct IPs).  -ENOSPC if the IP table overflowed. */
+int hbtgpu_get_top_ips(hbtgpu_ctx* ctx, uint32_t k, uint64_t* ip, uint64_t* count, size_t* n);
+
 /* Bucket tensors.  _device returns pointers into the context's device memory
  * (valid until destroy; contents change on run/reset); _host copies them into
  * caller buffers (any may be NULL). */

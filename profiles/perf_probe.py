@@ -4,11 +4,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from dynolog_b200 import hbtgpu, synth
 
-def probe(name, cfg, ncpu, n, nb, flags=0, forge=0, **kw):
+def probe(name, cfg, ncpu, n, nb, flags=0, forge=0, fmt=0, **kw):
     spec, streams = synth.capture(cfg, ncpu, forge_ppm=forge, **kw)
     total = sum(len(s) for s in streams)
     g = hbtgpu.Context(n_events=n, max_cpus=ncpu, n_buckets=nb, t0=synth.T_START, bucket_ns=1_000_000,
-                       arena_bytes=total + 256 * ncpu + (1 << 20), flags=flags)
+                       arena_bytes=total + 256 * ncpu + (1 << 20), flags=flags, sample_format=fmt)
     c = hbtgpu.make_carry(valid=True, tstamp=synth.T_START, last=[0] * n)
     for cpu in range(ncpu):
         g.set_carry(cpu, c)
@@ -39,3 +39,4 @@ if __name__ == "__main__":
     probe("cfg3 force_exact", 3, 64, 8, 70000, max_bytes_per_cpu=16 << 20, flags=hbtgpu.F_FORCE_EXACT)
     probe("cfg5 192cpu x 16MiB LOST", 5, 192, 8, 20000, max_bytes_per_cpu=16 << 20)
     probe("n=4 72B records 64cpu x 32MiB", 1, 64, 4, 50000, max_bytes_per_cpu=32 << 20)
+    probe("cfg4 IP|TID 88B 64cpu x 32MiB", 4, 64, 4, 50000, fmt=1, max_bytes_per_cpu=32 << 20)

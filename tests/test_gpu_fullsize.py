@@ -150,3 +150,41 @@ def test_cfg5_windows_sharded_equals_whole(port_oracle):
             g.close()
     assert np.array_equal(acc, acc_ref)
     assert rows == sum(c["num_rows"] for c in ctr_ref)
+
+
+def test_cfg4_ip_tid_attribution(port_oracle):
+    """BASELINE config 4 shape (scaled to 32 cpus x 16 MiB = 5.6 M samples): 4096 (pid,tid)
+    Zipf(1.1), 2^20 IPs Zipf(1.2), top-100.  Spec extension: oracle = C restatement + numpy."""
+    n, ncpu = 4, 32
+    spec, streams = synth.capture(4, ncpu, max_bytes_per_cpu=16 << 20)
+    t0, nb = synth.T_START, 20_000
+    total = sum(len(s) for s in streams)
+    p = po.make_params(n, n_buckets=nb, t0=t0, bucket_ns=1_000_000, pre=2)
+    carries = [po.make_carry(valid=True, tstamp=t0, last=[0] * n) for _ in streams]
+    with hbtgpu.Context(n_events=n, max_cpus=ncpu, n_buckets=nb, t0=t0, bucket_ns=1_000_000,
+                        arena_bytes=total + (1 << 20), sample_format=hbtgpu.SAMPLE_IP_TID_TIME_READ) as g:
+        c = hbtgpu.make_carry(valid=True, tstamp=t0, last=[0] * n)
+        for cpu in range(ncpu):
+            g.set_carry(cpu, c)
+        g.submit_images(list(range(ncpu)), streams)
+        g.run()
+        g.sync()
+        assert g.stats()["exact_runs"] == 0
+        hist = g.tid_histogram()
+        top = g.top_ips(100)
+        acc = g.buckets(want_scaled=False, want_metric=False, want_valid=False)["acc"]
+        nsamp = sum(g.counters(i)["sample"] for i in range(ncpu))
+    tids, ips = [], []
+    for s, cin in zip(streams, carries):
+        a, b = port_oracle.collect_ip_tid(p, s, cin)
+        tids.append(a)
+        ips.append(b)
+    tids, ips = np.concatenate(tids), np.concatenate(ips)
+    assert nsamp == len(tids)
+    tk, tc = np.unique(tids, return_counts=True)
+    assert hist == {(int(k & 0xFFFFFFFF), int(k >> 32)): int(c) for k, c in zip(tk, tc)}
+    ik, ic = np.unique(ips, return_counts=True)
+    order = np.lexsort((ik, -ic.astype(np.int64)))[:100]
+    assert top == [(int(ik[i]), int(ic[i])) for i in order]
+    _, acc_ref, _ = port_oracle.run_capture(p, streams, carries, n_threads=16)
+    assert np.array_equal(acc, acc_ref)

@@ -258,6 +258,69 @@ def test_ip_tid_sample_layout(port_oracle, mode):
         assert extra["stats"]["exact_runs"] == 0
 
 
+def _attribution_oracle(port_oracle, p, streams, carries):
+    """(pid,tid) histogram and IP counts from the C restatement's walk (spec extension: the
+    counting itself is restated here with numpy)."""
+    tids, ips = [], []
+    for s, c in zip(streams, carries):
+        a, b = port_oracle.collect_ip_tid(p, s, c)
+        tids.append(a)
+        ips.append(b)
+    tids, ips = np.concatenate(tids), np.concatenate(ips)
+    tk, tc = np.unique(tids, return_counts=True)
+    hist = {(int(k & 0xFFFFFFFF), int(k >> 32)): int(c) for k, c in zip(tk, tc)}
+    ik, ic = np.unique(ips, return_counts=True)
+    order = np.lexsort((ik, -ic.astype(np.int64)))  # count desc, ip asc
+    return hist, [(int(ik[i]), int(ic[i])) for i in order]
+
+
+@pytest.mark.parametrize("mode", ["fast", "general", "exact"])
+def test_tid_histogram_and_top_ips(port_oracle, mode):
+    """BASELINE config 4: per-(pid,tid) histogram + top-K sampled IPs (K=100, ties by ip)."""
+    n = 4
+    streams, carries = [], []
+    for cpu, kw in enumerate([dict(), dict(p_lost=0.01, p_throttle=0.01), dict(p_other=0.05)]):
+        data, _ = rg.random_stream(41_000 + cpu, 30_000, n, ip_tid=True, **kw)
+        streams.append(data)
+        carries.append(po.make_carry())
+    # a stream with an error in the middle: nothing after it may be counted
+    good = [rg.sample(1000 + 10 * i, i, i, [i] * n, ip_tid=(0x1000 + (i % 5), 1, 2 + (i % 3))) for i in range(1, 600)]
+    bad = good[:400] + [rg.sample(9, 1, 1, [0] * n, ip_tid=(0x9999, 7, 7))] + good[400:]
+    streams.append(rg.to_u8(b"".join(bad)))
+    carries.append(po.make_carry())
+    p = po.make_params(n, n_buckets=64, t0=1_000_000_000, bucket_ns=50_000_000, pre=2)
+    total = sum(len(s) for s in streams)
+    with hbtgpu.Context(n_events=n, max_cpus=len(streams), n_buckets=64, t0=p.t0, bucket_ns=p.bucket_ns,
+                        arena_bytes=total + (1 << 20), flags=MODES[mode],
+                        sample_format=hbtgpu.SAMPLE_IP_TID_TIME_READ, tid_table_log2=10,
+                        ip_table_log2=12) as g:
+        g.submit_images(list(range(len(streams))), streams)
+        g.run()
+        g.sync()
+        hist = g.tid_histogram()
+        top = g.top_ips(100)
+        top_all = g.top_ips(5000)
+        assert g.counters(3)["err"] == -errno.EPERM and g.counters(3)["sample"] == 400
+    exp_hist, exp_ips = _attribution_oracle(port_oracle, p, streams, carries)
+    assert hist == exp_hist
+    assert top == exp_ips[:100]
+    assert top_all == exp_ips            # fewer distinct IPs than asked for: all of them, ordered
+    assert sum(hist.values()) == sum(c for _, c in exp_ips)
+
+
+def test_attribution_table_overflow_is_reported():
+    n = 2
+    data, _ = rg.random_stream(5, 4000, n, ip_tid=True)
+    with hbtgpu.Context(n_events=n, n_buckets=4, t0=0, bucket_ns=1 << 40, arena_bytes=len(data) + 65536,
+                        sample_format=hbtgpu.SAMPLE_IP_TID_TIME_READ, tid_table_log2=4, ip_table_log2=4) as g:
+        g.submit_image(0, data)
+        g.run()
+        g.sync()
+        with pytest.raises(hbtgpu.HbtGpuError) as e:
+            g.top_ips(10)
+        assert e.value.code == -errno.ENOSPC
+
+
 def test_512_cpus_ragged_streams(port_oracle):
     """kMaxCpus streams (hbt/src/common/System.h:204) of ragged lengths, some empty, some with
     several images, all in one context."""
