@@ -354,7 +354,8 @@ int ensure_emitted(hbtgpu_ctx* ctx) {
   if (nc) {
     Params P = make_params(ctx);
     CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
-    k_decode<false, MODE_EMIT><<<static_cast<unsigned>(nc), NT, sizeof(Smem) + EMIT_STAGE_BYTES, ctx->stream>>>(P);
+    if (P.pre) k_decode<false, MODE_EMIT, 2><<<static_cast<unsigned>(nc), NT, sizeof(Smem) + EMIT_STAGE_BYTES, ctx->stream>>>(P);
+    else k_decode<false, MODE_EMIT, 0><<<static_cast<unsigned>(nc), NT, sizeof(Smem) + EMIT_STAGE_BYTES, ctx->stream>>>(P);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ctx->ev_run1, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -505,8 +506,11 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaMemsetAsync(ctx->d_flags, 0, FLAG_COUNT * 4, ctx->stream));
   CKC(cudaStreamSynchronize(ctx->stream));
   ctx->carry_in.assign(ns, hbtgpu_carry{});
-  if (set_smem(ctx, k_decode<true, MODE_AGG>) || set_smem(ctx, k_decode<false, MODE_AGG>) ||
-      set_smem(ctx, k_decode<false, MODE_EMIT>, EMIT_STAGE_BYTES))
+  if (set_smem(ctx, k_decode<true, MODE_AGG, 0>) || set_smem(ctx, k_decode<false, MODE_AGG, 0>) ||
+      set_smem(ctx, k_decode<false, MODE_EMIT, 0>, EMIT_STAGE_BYTES) ||
+      set_smem(ctx, k_decode<true, MODE_AGG, 2>, ATTR_SMEM_BYTES - sizeof(Smem)) ||
+      set_smem(ctx, k_decode<false, MODE_AGG, 2>, ATTR_SMEM_BYTES - sizeof(Smem)) ||
+      set_smem(ctx, k_decode<false, MODE_EMIT, 2>, EMIT_STAGE_BYTES))
     return bail(-EIO);
 #undef CKC
   *out = ctx;
@@ -689,7 +693,8 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   if (nc) {
     if (timed) CK(cudaEventRecord(ctx->ev_dec0[ctx->ev_pending], ctx->stream));
     if (!force_exact) {
-      k_decode<true, MODE_AGG><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
+      if (P.pre) k_decode<true, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, ATTR_SMEM_BYTES, ctx->stream>>>(P);
+      else k_decode<true, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
       ++launches;
     }
     if (timed) CK(cudaEventRecord(ctx->ev_dec1[ctx->ev_pending++], ctx->stream));
@@ -699,7 +704,8 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
     }
     k_resolve<<<ns, RES_THREADS, 0, ctx->stream>>>(P);
     k_clear<<<148 * 4, 256, 0, ctx->stream>>>(P, force_exact ? 0 : ctx->acc_words);
-    k_decode<false, MODE_AGG><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
+    if (P.pre) k_decode<false, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, ATTR_SMEM_BYTES, ctx->stream>>>(P);
+    else k_decode<false, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
     launches += 3;
     CK(cudaGetLastError());
   }
@@ -1247,7 +1253,7 @@ int na_device_setup(int dev, NaScratch** out) {
     if (e != cudaSuccess || !p)
       return na_fail(-EIO, "cudaGetSymbolAddress(scratch) failed on device %d: %s", dev,
                      cudaGetErrorString(e));
-    for (auto k : {(const void*)k_decode<true, MODE_AGG>, (const void*)k_decode<false, MODE_AGG>}) {
+    for (auto k : {(const void*)k_decode<true, MODE_AGG, 0>, (const void*)k_decode<false, MODE_AGG, 0>}) {
       e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(sizeof(Smem)));
       if (e != cudaSuccess)
@@ -1351,12 +1357,12 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
     const bool force_exact = (cfg->flags & HBTGPU_F_FORCE_EXACT) != 0;
     if (force_exact) NCK(cudaMemsetAsync(&sc->flags[FLAG_NEED_EXACT], 1, 1, st));
     if (!force_exact) {
-      k_decode<true, MODE_AGG><<<nc, NT, sizeof(Smem), st>>>(P);
+      k_decode<true, MODE_AGG, 0><<<nc, NT, sizeof(Smem), st>>>(P);
       k_verify<<<(nc + 255) / 256, 256, 0, st>>>(P);
     }
     k_resolve<<<1, RES_THREADS, 0, st>>>(P);
     k_clear<<<148 * 4, 256, 0, st>>>(P, force_exact ? 0 : acc_words);
-    k_decode<false, MODE_AGG><<<nc, NT, sizeof(Smem), st>>>(P);
+    k_decode<false, MODE_AGG, 0><<<nc, NT, sizeof(Smem), st>>>(P);
   }
   NCK(cudaGetLastError());
 

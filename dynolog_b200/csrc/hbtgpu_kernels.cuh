@@ -492,6 +492,7 @@ __device__ __forceinline__ void recover_chain(Smem& s, const uint64_t* buf, uint
 // forms a false chain in lock step with the true one, equally long, but made of records of
 // nonsense types.  A wrong pick is only a lost bet: k_verify refutes it.
 // K <= HALO_WORDS <= NT so one candidate per thread.  Returns the word position or ~0.
+template <int PRE>
 __device__ __forceinline__ uint32_t scout_start(Smem& s, const Params& P, const uint64_t* buf,
                                                 uint32_t wt, uint32_t K) {
   build_links(s, buf, wt, K);
@@ -502,7 +503,7 @@ __device__ __forceinline__ uint32_t scout_start(Smem& s, const Params& P, const 
     const uint64_t hd = buf[p];
     const uint32_t type = static_cast<uint32_t>(hd), size = static_cast<uint32_t>(hd >> 48);
     const uint32_t n = P.n_events;
-    const bool plausible = (type == REC_SAMPLE && size == P.fix + 8 * n && buf[p + P.pre + 2] == n) ||
+    const bool plausible = (type == REC_SAMPLE && size == (40 + 8 * PRE) + 8 * n && buf[p + PRE + 2] == n) ||
                            (type == REC_LOST && size == 24) ||
                            ((type == REC_THROTTLE || type == REC_UNTHROTTLE) && size == 32);
     own = (plausible ? 0x10000u : 0u) | 1u;
@@ -572,26 +573,28 @@ __device__ __forceinline__ void red_add(uint64_t* p, uint64_t v) {
 
 constexpr uint64_t ATTR_EMPTY = ~0ull;
 
+// 32-bit arithmetic only: the decode kernel is short of issue slots and a 64-bit multiply is
+// four instructions.  attr_hash0 alone places a key in the per-CTA cache.
+__device__ __forceinline__ uint32_t attr_hash0(uint64_t k) {
+  return static_cast<uint32_t>(k) * 0x9E3779B1u ^ static_cast<uint32_t>(k >> 32) * 0x85EBCA6Bu;
+}
 __device__ __forceinline__ uint32_t attr_hash(uint64_t k) {
-  k ^= k >> 30;
-  k *= 0xBF58476D1CE4E5B9ull;
-  k ^= k >> 27;
-  k *= 0x94D049BB133111EBull;
-  k ^= k >> 31;
-  return static_cast<uint32_t>(k);
+  uint32_t x = attr_hash0(k);
+  x ^= x >> 15;
+  x *= 0x2C1B3C6Du;
+  x ^= x >> 12;
+  x *= 0x297A2D39u;
+  x ^= x >> 15;
+  return x;
 }
 
-// count += c for `key` in an open-addressing table (linear probing, insert on first use)
-__device__ __forceinline__ void attr_add(uint64_t* keys, unsigned long long* cnt, uint32_t mask, uint64_t key,
-                                         unsigned long long c, unsigned long long* special,
-                                         unsigned long long* overflow) {
-  if (key == ATTR_EMPTY) {
-    atomicAdd(special, c);
-    return;
-  }
-  uint32_t slot = attr_hash(key) & mask;
+// count += c for `key` (!= ATTR_EMPTY) starting at its home slot, whose key word the caller has
+// already loaded (so that several lookups can be in flight at once)
+__device__ __forceinline__ void attr_add_from(uint64_t* keys, unsigned long long* cnt, uint32_t mask, uint64_t key,
+                                              unsigned long long c, unsigned long long* overflow, uint32_t slot,
+                                              uint64_t k) {
   for (uint32_t probe = 0; probe <= mask; ++probe) {
-    uint64_t k = reinterpret_cast<volatile uint64_t*>(keys)[slot];
+    if (probe) k = reinterpret_cast<volatile uint64_t*>(keys)[slot];
     if (k == ATTR_EMPTY) {
       k = atomicCAS(reinterpret_cast<unsigned long long*>(keys + slot), ATTR_EMPTY, key);
       if (k == ATTR_EMPTY) k = key;
@@ -604,6 +607,90 @@ __device__ __forceinline__ void attr_add(uint64_t* keys, unsigned long long* cnt
   }
   atomicAdd(overflow, c);  // table full: reported, never silently dropped
 }
+// count += c for `key` in an open-addressing table (linear probing, insert on first use)
+__device__ __forceinline__ void attr_add(uint64_t* keys, unsigned long long* cnt, uint32_t mask, uint64_t key,
+                                         unsigned long long c, unsigned long long* special,
+                                         unsigned long long* overflow) {
+  if (key == ATTR_EMPTY) {
+    atomicAdd(special, c);
+    return;
+  }
+  const uint32_t slot = attr_hash(key) & mask;
+  attr_add_from(keys, cnt, mask, key, c, overflow, slot, reinterpret_cast<volatile uint64_t*>(keys)[slot]);
+}
+
+// Per-CTA front of the two attribution tables (AGG kernels of the IP|TID layout only; it sits
+// behind Smem in dynamic shared memory, which leaves 4 CTAs per SM).  A chunk's samples are
+// counted here first and the distinct keys are flushed once at the end of the chunk, so a hot
+// thread or a hot instruction costs one global atomic per chunk instead of one per sample.
+// Keys that find no slot in two probes go straight to the global table.  The decode kernel is
+// close to issue-bound, so this path is kept short: a multiplicative hash, two unrolled
+// probes, no warp-level matching (shared-memory atomics resolve duplicates within a warp).
+constexpr uint32_t ATTR_C_TID_LOG2 = 8, ATTR_C_IP_LOG2 = 10;
+struct AttrCache {
+  uint64_t ip_key[1u << ATTR_C_IP_LOG2];
+  uint64_t tid_key[1u << ATTR_C_TID_LOG2];  // pid | tid << 32
+  uint32_t ip_cnt[1u << ATTR_C_IP_LOG2];
+  uint32_t tid_cnt[1u << ATTR_C_TID_LOG2];
+};
+constexpr size_t ATTR_CACHE_OFF = (sizeof(Smem) + 127) & ~static_cast<size_t>(127);
+constexpr size_t ATTR_SMEM_BYTES = ATTR_CACHE_OFF + sizeof(AttrCache);
+__device__ __forceinline__ AttrCache& attr_cache() {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  return *reinterpret_cast<AttrCache*>(smem_raw + ATTR_CACHE_OFF);
+}
+template <bool IP>
+__device__ __forceinline__ void attr_global(const Params& P, uint64_t key, unsigned long long c) {
+  if (IP) attr_add(P.ip_keys, P.ip_cnt, P.ip_mask, key, c, P.attr_special + 1, P.attr_special + 3);
+  else attr_add(P.tid_keys, P.tid_cnt, P.tid_mask, key, c, P.attr_special + 0, P.attr_special + 2);
+}
+// true if the per-CTA cache took the sample; false: the caller owes the global table one count
+template <bool IP>
+__device__ __forceinline__ bool attr_cache_try(uint64_t key) {
+  constexpr uint32_t LOG2 = IP ? ATTR_C_IP_LOG2 : ATTR_C_TID_LOG2;
+  AttrCache& A = attr_cache();
+  uint64_t* const keys = IP ? A.ip_key : A.tid_key;
+  uint32_t* const cnts = IP ? A.ip_cnt : A.tid_cnt;
+  if (key == ATTR_EMPTY) return false;
+  uint32_t slot = attr_hash0(key) >> (32 - LOG2);
+#pragma unroll
+  for (uint32_t probe = 0; probe < 2; ++probe) {
+    uint64_t k = reinterpret_cast<volatile uint64_t*>(keys)[slot];
+    if (k == ATTR_EMPTY) {
+      k = atomicCAS(reinterpret_cast<unsigned long long*>(keys + slot), ATTR_EMPTY, key);
+      if (k == ATTR_EMPTY) k = key;
+    }
+    if (k == key) {
+      atomicAdd(cnts + slot, 1u);
+      return true;
+    }
+    slot = (slot + 1) & ((1u << LOG2) - 1);
+  }
+  return false;
+}
+template <bool IP>
+__device__ __forceinline__ void attr_count(const Params& P, uint64_t key) {
+  if (!attr_cache_try<IP>(key)) attr_global<IP>(P, key, 1);
+}
+__device__ __forceinline__ void attr_cache_init() {
+  AttrCache& A = attr_cache();
+  for (uint32_t i = threadIdx.x; i < (1u << ATTR_C_IP_LOG2); i += NT) {
+    A.ip_key[i] = ATTR_EMPTY;
+    A.ip_cnt[i] = 0;
+  }
+  for (uint32_t i = threadIdx.x; i < (1u << ATTR_C_TID_LOG2); i += NT) {
+    A.tid_key[i] = ATTR_EMPTY;
+    A.tid_cnt[i] = 0;
+  }
+}
+// after a __syncthreads: every distinct key of the chunk goes to the global tables once
+__device__ __forceinline__ void attr_cache_flush(const Params& P) {
+  AttrCache& A = attr_cache();
+  for (uint32_t i = threadIdx.x; i < (1u << ATTR_C_IP_LOG2); i += NT)
+    if (A.ip_key[i] != ATTR_EMPTY) attr_global<true>(P, A.ip_key[i], A.ip_cnt[i]);
+  for (uint32_t i = threadIdx.x; i < (1u << ATTR_C_TID_LOG2); i += NT)
+    if (A.tid_key[i] != ATTR_EMPTY) attr_global<false>(P, A.tid_key[i], A.tid_cnt[i]);
+}
 
 struct TileCtx {
   uint64_t tile_abs;    // arena offset of word 0 of the buffer
@@ -615,7 +702,7 @@ struct TileCtx {
 
 // Decode the reachable records of one staged tile and fold them into the carry, the
 // counters and (if AGG) the bucket sums.  SCOUT: only the carry is updated.
-template <bool SCOUT, int MODE>
+template <bool SCOUT, int MODE, int PRE>
 __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint64_t* buf,
                                             uint32_t K, TileCtx& tc, uint32_t cur) {
   Carry& C = s.c[cur];
@@ -638,17 +725,17 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
       ++n_rec;
       if (type == REC_SAMPLE) {
         // recordSize check (:1502-1507) + nr == kNumEvents (fenced DCHECK, gen :133)
-        const uint64_t nr = (size + 16 >= P.fix) ? buf[p + P.pre + 2] : ~0ull;
-        if (size < P.fix || nr != ((size - P.fix) >> 3) || nr != n) {
+        const uint64_t nr = (size + 16 >= (40u + 8u * PRE)) ? buf[p + PRE + 2] : ~0ull;
+        if (size < (40u + 8u * PRE) || nr != ((size - (40u + 8u * PRE)) >> 3) || nr != n) {
           atomicMin(&s.tile_err, p);
         } else {
           f |= FL_SAMPLE;
           a = __vmaxu2(a, (j + 1) << 16);
           b += 1;
           s.next[j] = IDX_NONE;
-          if (!SCOUT && MODE == MODE_AGG && P.pre == 2) {
-            attr_add(P.ip_keys, P.ip_cnt, P.ip_mask, buf[p + 1], 1, P.attr_special + 1, P.attr_special + 3);
-            attr_add(P.tid_keys, P.tid_cnt, P.tid_mask, buf[p + 2], 1, P.attr_special + 0, P.attr_special + 2);
+          if (!SCOUT && MODE == MODE_AGG && PRE == 2) {
+            attr_count<true>(P, buf[p + 1]);
+            attr_count<false>(P, buf[p + 2]);
           }
         }
       } else if (type == REC_LOST) {
@@ -687,8 +774,8 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
       const bool gap = in_tile ? (prev_l > prev_s) : (c_gap || prev_l != 0);
       const bool link = (in_tile || c_valid) && !gap;
       const uint32_t p = s.pos[j];
-      const uint64_t ts = buf[p + P.pre + 1];
-      const uint64_t pts = in_tile ? buf[s.pos[prev_s - 1] + P.pre + 1] : c_ts;
+      const uint64_t ts = buf[p + PRE + 1];
+      const uint64_t pts = in_tile ? buf[s.pos[prev_s - 1] + PRE + 1] : c_ts;
       if (link && pts > ts) atomicMin(&s.tile_err, p);  // time regression (gen :156-163)
       if (!SCOUT) {
         s.u.de.bkt[j] = bucket_of(P, ts);
@@ -781,14 +868,14 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
               for (uint32_t e = 0; e < n + 3; ++e) {
                 uint64_t plus, minus;
                 if (e < n) {
-                  plus = xform(P, e, buf[p + P.pre + 5 + e]);
-                  minus = (pj != IDX_NONE) ? xform(P, e, buf[pp + P.pre + 5 + e]) : C.last[e];
+                  plus = xform(P, e, buf[p + PRE + 5 + e]);
+                  minus = (pj != IDX_NONE) ? xform(P, e, buf[pp + PRE + 5 + e]) : C.last[e];
                 } else if (e == n) {
-                  plus = buf[p + P.pre + 3];
-                  minus = (pj != IDX_NONE) ? buf[pp + P.pre + 3] : C.te;
+                  plus = buf[p + PRE + 3];
+                  minus = (pj != IDX_NONE) ? buf[pp + PRE + 3] : C.te;
                 } else if (e == n + 1) {
-                  plus = buf[p + P.pre + 4];
-                  minus = (pj != IDX_NONE) ? buf[pp + P.pre + 4] : C.tr;
+                  plus = buf[p + PRE + 4];
+                  minus = (pj != IDX_NONE) ? buf[pp + PRE + 4] : C.tr;
                 } else {
                   plus = ord;
                   minus = static_cast<uint64_t>(ord) - 1;
@@ -799,14 +886,14 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
             }
           } else {  // MODE_EMIT: the row as CpuCountSampleGenerator writes it (:165-182)
             const uint32_t pp = (pj != IDX_NONE) ? s.pos[pj] : 0;
-            const uint64_t ts = buf[p + P.pre + 1];
-            const uint64_t pts = (pj != IDX_NONE) ? buf[pp + P.pre + 1] : C.ts;
+            const uint64_t ts = buf[p + PRE + 1];
+            const uint64_t pts = (pj != IDX_NONE) ? buf[pp + PRE + 1] : C.ts;
             uint64_t* row = P.rows + (tc.row_base + tc.rows_before + ex_row) * (n + 2);
             row[0] = pts;
             row[1] = ts - pts;
             for (uint32_t e = 0; e < n; ++e) {
-              const uint64_t cur = xform(P, e, buf[p + P.pre + 5 + e]);
-              const uint64_t prv = (pj != IDX_NONE) ? xform(P, e, buf[pp + P.pre + 5 + e]) : C.last[e];
+              const uint64_t cur = xform(P, e, buf[p + PRE + 5 + e]);
+              const uint64_t prv = (pj != IDX_NONE) ? xform(P, e, buf[pp + PRE + 5 + e]) : C.last[e];
               row[2 + e] = cur - prv;
             }
             ++ex_row;
@@ -822,11 +909,11 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
   const uint32_t last_s = tot_a >> 16, last_l = tot_a & 0xFFFFu;
   if (last_s != 0) {
     const uint32_t p = s.pos[last_s - 1];
-    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, buf[p + P.pre + 5 + e]);
+    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, buf[p + PRE + 5 + e]);
     if (threadIdx.x == 0) {
-      C.ts = buf[p + P.pre + 1];
-      C.te = buf[p + P.pre + 3];
-      C.tr = buf[p + P.pre + 4];
+      C.ts = buf[p + PRE + 1];
+      C.te = buf[p + PRE + 3];
+      C.tr = buf[p + PRE + 4];
       C.valid = 1;
       C.gap = last_l > last_s;
       C.last_off = tc.tile_abs + 8ull * p;
@@ -868,13 +955,13 @@ constexpr int EMIT_MAX_ROW_WORDS = 16;                     // n_events <= 14 on 
 constexpr int EMIT_STAGE_WORDS = 31 * EMIT_MAX_ROW_WORDS;  // per warp
 constexpr size_t EMIT_STAGE_BYTES = static_cast<size_t>(NWARP) * EMIT_STAGE_WORDS * 8;
 
-template <int MODE>
+template <int MODE, int PRE>
 __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, const uint64_t* buf,
                                                     uint32_t wt, uint32_t entry, TileCtx& tc,
                                                     uint32_t cur, uint32_t& k_all) {
   const Carry& C = s.c[cur];
   const uint32_t n = P.n_events;
-  const uint32_t pre = P.pre;
+  constexpr uint32_t pre = PRE;
   const uint32_t S = 5 + pre + n;  // words per SAMPLE
   const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
   // records whose header lies inside the tile: ceil((wt - entry) / S) by multiply-shift
@@ -969,23 +1056,15 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   }
 
   if (MODE == MODE_AGG && pre == 2) {
-    // who was sampled and where: one table update per distinct key per warp
+    // who was sampled and where
 #pragma unroll
     for (int g = 0; g < MAXG; ++g) {
-      const int j0 = (g * NWARP + warp) * OWN - 1;
-      if (j0 >= K) break;
-      const int jr = j0 + lane;
-      const bool own = lane < 31 && jr >= 0 && jr < K;
-      const uint32_t p = entry + (own ? jr : 0) * S;
-      // lanes without a record get keys no other lane can have
-      const uint64_t ip = own ? buf[p + 1] : (0x8000000000000000ull | lane);
-      const uint64_t tk = own ? buf[p + 2] : (0x8000000000000000ull | lane);
-      const uint32_t gi = __match_any_sync(0xffffffffu, ip);
-      const uint32_t gt = __match_any_sync(0xffffffffu, tk);
-      if (own && static_cast<int>(__ffs(gi)) - 1 == lane)
-        attr_add(P.ip_keys, P.ip_cnt, P.ip_mask, ip, __popc(gi), P.attr_special + 1, P.attr_special + 3);
-      if (own && static_cast<int>(__ffs(gt)) - 1 == lane)
-        attr_add(P.tid_keys, P.tid_cnt, P.tid_mask, tk, __popc(gt), P.attr_special + 0, P.attr_special + 2);
+      const int jr = (g * NWARP + warp) * OWN - 1 + lane;
+      if (lane < 31 && jr >= 0 && jr < K) {
+        const uint32_t p = entry + jr * S;
+        attr_count<true>(P, buf[p + 1]);
+        attr_count<false>(P, buf[p + 2]);
+      }
     }
   }
 
@@ -1112,6 +1191,7 @@ __device__ __forceinline__ uint32_t odd_record(Smem& s, const Params& P, const u
 }
 
 // Initialise the carry from a predecessor SAMPLE in global memory / the stream carry-in.
+template <int PRE>
 __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t stream, uint64_t pred,
                                            uint32_t gap) {
   Carry& C = s.c[0];
@@ -1135,11 +1215,11 @@ __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t st
     }
   } else {
     const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + pred);
-    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, r[P.pre + 5 + e]);
+    for (uint32_t e = threadIdx.x; e < n; e += NT) C.last[e] = xform(P, e, r[PRE + 5 + e]);
     if (threadIdx.x == 0) {
-      C.ts = r[P.pre + 1];
-      C.te = r[P.pre + 3];
-      C.tr = r[P.pre + 4];
+      C.ts = r[PRE + 1];
+      C.te = r[PRE + 3];
+      C.tr = r[PRE + 4];
       C.valid = 1;
       C.gap = gap;
       C.last_off = pred;
@@ -1150,8 +1230,8 @@ __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t st
 #ifndef HBT_MINB
 #define HBT_MINB 5
 #endif
-template <bool SPEC, int MODE>
-__global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
+template <bool SPEC, int MODE, int PRE>
+__global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_MINB) k_decode(const Params P) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   if (!SPEC && MODE == MODE_AGG && P.flags[FLAG_NEED_EXACT] == 0) return;  // exact pass not needed
@@ -1168,6 +1248,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
     s.lost_sum = 0;
   }
   if (threadIdx.x < C_SLOTS) s.cnt[threadIdx.x] = 0;
+  if (MODE == MODE_AGG && PRE == 2) attr_cache_init();
   __syncthreads();
 
   uint32_t phase[2] = {0, 0};
@@ -1192,7 +1273,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
   if (SPEC) {
     if (cd.halo_len == 0) {
       entry_abs = chunk_abs;
-      load_carry(s, P, cd.stream, PRED_CARRY_IN, 0);
+      load_carry<PRE>(s, P, cd.stream, PRED_CARRY_IN, 0);
       __syncthreads();
     } else {
       // stage the halo and scout it
@@ -1215,14 +1296,14 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
       mbar_wait(&s.bar[0], phase[0]);
       phase[0] ^= 1;
       const uint64_t* hb = s.data[0];
-      load_carry(s, P, cd.stream, PRED_UNKNOWN, 0);
+      load_carry<PRE>(s, P, cd.stream, PRED_UNKNOWN, 0);
       entry_abs = chunk_abs;
       // Quick scout: the last word of the halo that looks like a SAMPLE header of the configured
       // group, confirmed by the record before it, and whose record reaches the chunk.  It is a
       // guess like any other -- k_verify proves or refutes it against the previous chunk.
       bool quick = false;
       if (!P.force_general && !(cd.flags & CH_FIRST_OF_IMAGE)) {
-        const uint32_t n = P.n_events, pre = P.pre, S = 5 + pre + n;
+        const uint32_t n = P.n_events, pre = PRE, S = 5 + pre + n;
         const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
         if (threadIdx.x == 0) s.red_key = 0;
         __syncthreads();
@@ -1259,7 +1340,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
         K = classify(s, hb, hw);
         if (K > 0) {
           if (cd.flags & CH_HALO_EXACT_START) start = 0;
-          else start = scout_start(s, P, hb, hw, K);
+          else start = scout_start<PRE>(s, P, hb, hw, K);
         }
       }
       __syncthreads();
@@ -1274,7 +1355,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
         } else {
           entry_abs = cd.halo_off + 8ull * s.term_tgt;
           TileCtx tc{cd.halo_off, 0, cd.stream, 0, 0, 0, 0};
-          decode_tile<true, MODE_AGG>(s, P, hb, K, tc, 0);
+          decode_tile<true, MODE_AGG, PRE>(s, P, hb, K, tc, 0);
           if (s.tile_err != 0xFFFFFFFFu) bad = WHY_HALO_ERR;
           else if (!s.c[0].valid) bad = WHY_HALO_NO_SAMPLE;  // predecessor unknown
         }
@@ -1295,7 +1376,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
   } else {
     entry_abs = io.in_entry;
     limit_abs = min(limit_abs, io.limit);
-    load_carry(s, P, cd.stream, io.in_pred, io.in_gap);
+    load_carry<PRE>(s, P, cd.stream, io.in_pred, io.in_gap);
     __syncthreads();
   }
 
@@ -1335,10 +1416,10 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
       if (!P.force_general && (MODE == MODE_AGG || P.n_events + 2 <= EMIT_MAX_ROW_WORDS)) {
         // runs of configured SAMPLEs in parallel, the few other records in between one by one;
         // a tile with many of those goes to the general path
-        const uint32_t S = 5 + P.pre + P.n_events;
+        const uint32_t S = 5 + PRE + P.n_events;
         for (int odd = 0;;) {
           uint32_t k_all = 0;
-          const uint32_t k = uniform_segment<MODE>(s, P, buf, wt, ew, tc, cur, k_all);
+          const uint32_t k = uniform_segment<MODE, PRE>(s, P, buf, wt, ew, tc, cur, k_all);
           if (k) cur ^= 1;
           ew += k * S;
           if (k == k_all) {  // ran to the end of the tile
@@ -1367,7 +1448,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
           const uint32_t tk = s.term_kind, tt = s.term_tgt;
           tc.tile_abs = tile_abs + 8ull * w0;
           tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base) + 8ull * w0;
-          decode_tile<false, MODE>(s, P, sb, K, tc, cur);
+          decode_tile<false, MODE, PRE>(s, P, sb, K, tc, cur);
           term_kind = (tk != 0 || s.tile_err != 0xFFFFFFFFu) ? 1u + tk : 0u;
           ew = w0 + tt;
         }
@@ -1393,6 +1474,7 @@ __global__ void __launch_bounds__(NT, HBT_MINB) k_decode(const Params P) {
 
   // ---- publish ----
   __syncthreads();
+  if (MODE == MODE_AGG && PRE == 2) attr_cache_flush(P);
   const Carry& C = s.c[cur];
   if (threadIdx.x == 0) {
     io.out_exit = next_abs;
