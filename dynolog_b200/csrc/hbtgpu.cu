@@ -123,6 +123,17 @@ int ensure(hbtgpu_ctx* ctx, T** p, size_t* cap, size_t need) {
 constexpr uint64_t kImageAlign = 128;
 
 // Split every image into chunks; order = stream, then submission order, then position.
+// tile size of a context (see tile_bytes_for) and a chunk size that is a whole number of tiles
+uint32_t cfg_tile_bytes(const hbtgpu_config& cfg) {
+  return tile_bytes_for(5u + (cfg.sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ ? 2u : 0u) + cfg.n_events);
+}
+uint32_t ctx_tile_bytes(const hbtgpu_ctx* ctx) { return cfg_tile_bytes(ctx->cfg); }
+uint64_t chunk_bytes_for(uint64_t target, uint64_t cap, uint32_t tile) {
+  const uint64_t kmax = std::max<uint64_t>(1, (cap + tile / 2) / tile);
+  const uint64_t k = std::min(kmax, std::max<uint64_t>(1, (target + tile - 1) / tile));
+  return k * tile;
+}
+
 int build_table(hbtgpu_ctx* ctx) {
   const uint32_t ns = ctx->cfg.max_cpus;
   ctx->chunks.clear();
@@ -137,8 +148,7 @@ int build_table(hbtgpu_ctx* ctx) {
     const long kb = atol(e);
     if (kb >= 16 && kb <= 4096) cap = static_cast<uint64_t>(kb) << 10;
   }
-  uint64_t cb = TILE_BYTES;
-  while (cb < target && cb < cap) cb <<= 1;
+  const uint64_t cb = chunk_bytes_for(target, cap, ctx_tile_bytes(ctx));
   ctx->chunk_bytes = cb;
 
   std::vector<std::vector<uint32_t>> per_stream(ns);
@@ -245,6 +255,7 @@ Params make_params(hbtgpu_ctx* ctx) {
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
     P.pre = ctx->cfg.sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ ? 2 : 0;
     P.fix = 40 + 8 * P.pre;
+    P.tile_bytes = ctx_tile_bytes(ctx);
     P.tid_keys = ctx->d_tid_keys;
     P.tid_cnt = ctx->d_tid_cnt;
     P.ip_keys = ctx->d_ip_keys;
@@ -354,8 +365,8 @@ int ensure_emitted(hbtgpu_ctx* ctx) {
   if (nc) {
     Params P = make_params(ctx);
     CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
-    if (P.pre) k_decode<false, MODE_EMIT, 2><<<static_cast<unsigned>(nc), NT, sizeof(Smem) + EMIT_STAGE_BYTES, ctx->stream>>>(P);
-    else k_decode<false, MODE_EMIT, 0><<<static_cast<unsigned>(nc), NT, sizeof(Smem) + EMIT_STAGE_BYTES, ctx->stream>>>(P);
+    if (P.pre) k_decode<false, MODE_EMIT, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_EMIT, 2>(P.tile_bytes), ctx->stream>>>(P);
+    else k_decode<false, MODE_EMIT, 0><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_EMIT, 0>(P.tile_bytes), ctx->stream>>>(P);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ctx->ev_run1, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -366,9 +377,8 @@ int ensure_emitted(hbtgpu_ctx* ctx) {
 }
 
 template <class K>
-int set_smem(hbtgpu_ctx* ctx, K kernel, size_t extra = 0) {
-  CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                          static_cast<int>(sizeof(Smem) + extra)));
+int set_smem(hbtgpu_ctx* ctx, K kernel, size_t bytes) {
+  CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
   return 0;
 }
 
@@ -469,8 +479,8 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   ctx->acc_words = ctx->n_cells * (n + 3);
   ctx->arena_cap = (cfg->arena_bytes + kImageAlign - 1) / kImageAlign * kImageAlign;
   // slack: image padding plus the staged overlap / 16-byte rounding never leaves the allocation
-  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->arena), ctx->arena_cap + kImageAlign * ns + STAGE_BYTES));
-  CKC(cudaMemsetAsync(ctx->arena, 0, ctx->arena_cap + kImageAlign * ns + STAGE_BYTES, ctx->stream));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->arena), ctx->arena_cap + kImageAlign * ns + TILE_MAX_BYTES + OV_BYTES));
+  CKC(cudaMemsetAsync(ctx->arena, 0, ctx->arena_cap + kImageAlign * ns + TILE_MAX_BYTES + OV_BYTES, ctx->stream));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_carry_in), ns * sizeof(hbtgpu_carry)));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_carry_out), ns * sizeof(hbtgpu_carry)));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_carry_init), ns * sizeof(hbtgpu_carry)));
@@ -506,11 +516,12 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaMemsetAsync(ctx->d_flags, 0, FLAG_COUNT * 4, ctx->stream));
   CKC(cudaStreamSynchronize(ctx->stream));
   ctx->carry_in.assign(ns, hbtgpu_carry{});
-  if (set_smem(ctx, k_decode<true, MODE_AGG, 0>) || set_smem(ctx, k_decode<false, MODE_AGG, 0>) ||
-      set_smem(ctx, k_decode<false, MODE_EMIT, 0>, EMIT_STAGE_BYTES) ||
-      set_smem(ctx, k_decode<true, MODE_AGG, 2>, ATTR_SMEM_BYTES - sizeof(Smem)) ||
-      set_smem(ctx, k_decode<false, MODE_AGG, 2>, ATTR_SMEM_BYTES - sizeof(Smem)) ||
-      set_smem(ctx, k_decode<false, MODE_EMIT, 2>, EMIT_STAGE_BYTES))
+  if (set_smem(ctx, k_decode<true, MODE_AGG, 0>, decode_smem_bytes<MODE_AGG, 0>(TILE_MAX_BYTES)) ||
+      set_smem(ctx, k_decode<false, MODE_AGG, 0>, decode_smem_bytes<MODE_AGG, 0>(TILE_MAX_BYTES)) ||
+      set_smem(ctx, k_decode<false, MODE_EMIT, 0>, decode_smem_bytes<MODE_EMIT, 0>(TILE_MAX_BYTES)) ||
+      set_smem(ctx, k_decode<true, MODE_AGG, 2>, decode_smem_bytes<MODE_AGG, 2>(TILE_MAX_BYTES)) ||
+      set_smem(ctx, k_decode<false, MODE_AGG, 2>, decode_smem_bytes<MODE_AGG, 2>(TILE_MAX_BYTES)) ||
+      set_smem(ctx, k_decode<false, MODE_EMIT, 2>, decode_smem_bytes<MODE_EMIT, 2>(TILE_MAX_BYTES)))
     return bail(-EIO);
 #undef CKC
   *out = ctx;
@@ -693,8 +704,8 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   if (nc) {
     if (timed) CK(cudaEventRecord(ctx->ev_dec0[ctx->ev_pending], ctx->stream));
     if (!force_exact) {
-      if (P.pre) k_decode<true, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, ATTR_SMEM_BYTES, ctx->stream>>>(P);
-      else k_decode<true, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
+      if (P.pre) k_decode<true, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P);
+      else k_decode<true, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
       ++launches;
     }
     if (timed) CK(cudaEventRecord(ctx->ev_dec1[ctx->ev_pending++], ctx->stream));
@@ -704,8 +715,8 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
     }
     k_resolve<<<ns, RES_THREADS, 0, ctx->stream>>>(P);
     k_clear<<<148 * 4, 256, 0, ctx->stream>>>(P, force_exact ? 0 : ctx->acc_words);
-    if (P.pre) k_decode<false, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, ATTR_SMEM_BYTES, ctx->stream>>>(P);
-    else k_decode<false, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, sizeof(Smem), ctx->stream>>>(P);
+    if (P.pre) k_decode<false, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P);
+    else k_decode<false, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
     launches += 3;
     CK(cudaGetLastError());
   }
@@ -1255,7 +1266,7 @@ int na_device_setup(int dev, NaScratch** out) {
                      cudaGetErrorString(e));
     for (auto k : {(const void*)k_decode<true, MODE_AGG, 0>, (const void*)k_decode<false, MODE_AGG, 0>}) {
       e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               static_cast<int>(sizeof(Smem)));
+                               static_cast<int>(decode_smem_bytes<MODE_AGG, 0>(TILE_MAX_BYTES)));
       if (e != cudaSuccess)
         return na_fail(-EIO, "cudaFuncSetAttribute failed on device %d: %s", dev, cudaGetErrorString(e));
     }
@@ -1306,9 +1317,8 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
 
   // chunks: as many as fill the GPU, never more than the static table holds
-  uint64_t cb = TILE_BYTES;
-  const uint64_t target = image_bytes / (148ull * 12ull);
-  while (cb < target && cb < (512ull << 10)) cb <<= 1;
+  const uint32_t tile = cfg_tile_bytes(*cfg);
+  uint64_t cb = chunk_bytes_for(image_bytes / (148ull * 12ull), 512ull << 10, tile);
   while ((image_bytes + cb - 1) / cb > kNaMaxChunks) cb <<= 1;
   const uint32_t nc = static_cast<uint32_t>((image_bytes + cb - 1) / cb);
 
@@ -1350,6 +1360,7 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
     P.pre = cfg->sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ ? 2 : 0;
     P.fix = 40 + 8 * P.pre;
+    P.tile_bytes = tile;
     const uint64_t S = 5ull + P.pre + n;
     P.s_magic = static_cast<uint32_t>(((1ull << 32) + S - 1) / S);
   }
@@ -1357,12 +1368,12 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
     const bool force_exact = (cfg->flags & HBTGPU_F_FORCE_EXACT) != 0;
     if (force_exact) NCK(cudaMemsetAsync(&sc->flags[FLAG_NEED_EXACT], 1, 1, st));
     if (!force_exact) {
-      k_decode<true, MODE_AGG, 0><<<nc, NT, sizeof(Smem), st>>>(P);
+      k_decode<true, MODE_AGG, 0><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
       k_verify<<<(nc + 255) / 256, 256, 0, st>>>(P);
     }
     k_resolve<<<1, RES_THREADS, 0, st>>>(P);
     k_clear<<<148 * 4, 256, 0, st>>>(P, force_exact ? 0 : acc_words);
-    k_decode<false, MODE_AGG, 0><<<nc, NT, sizeof(Smem), st>>>(P);
+    k_decode<false, MODE_AGG, 0><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
   }
   NCK(cudaGetLastError());
 

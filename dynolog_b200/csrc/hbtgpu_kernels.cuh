@@ -37,11 +37,19 @@ namespace hbtgpu {
 #endif
 constexpr int NT = HBT_NT;  // threads per CTA
 constexpr int NWARP = NT / 32;
-constexpr int TILE_BYTES = 16384;
-constexpr int TILE_WORDS = TILE_BYTES / 8;
+// A tile is sized per context so that the records of the configured group that start in it
+// fill one pass of the uniform path exactly (PASS_RECORDS lanes, see uniform_segment): with a
+// fixed 16 KiB tile a 104-byte record left 15 % of the lanes idle and a 72-byte record needed a
+// second, mostly empty pass.  tile_bytes = min(TILE_MAX_BYTES, PASS_RECORDS * record bytes)
+// rounded down to 16 (TMA).  TILE_MAX_BYTES keeps 5 CTAs per SM: 5 * (fixed 5.5 KiB +
+// 2 * (19392 + 576) + 1 KiB reserved) <= 228 KiB.
+constexpr int TILE_MAX_BYTES = 19392;
+constexpr int PASS_RECORDS = (NT / 32) * 31 - 1;  // 185 for NT = 192
 constexpr int OV_BYTES = 576;  // >= 40 + 8*64: any SAMPLE/READ/LOST whose header is in the tile is fully staged
-constexpr int STAGE_BYTES = TILE_BYTES + OV_BYTES;
-constexpr int STAGE_WORDS = STAGE_BYTES / 8;
+__host__ __device__ inline uint32_t tile_bytes_for(uint32_t sample_words) {
+  const uint64_t b = static_cast<uint64_t>(PASS_RECORDS) * sample_words * 8ull;
+  return static_cast<uint32_t>((b < TILE_MAX_BYTES ? b : TILE_MAX_BYTES) & ~15ull);
+}
 constexpr int HALO_BYTES = NT * 8;  // one halo word per thread (scout_start, quick scout)
 constexpr int HALO_WORDS = HALO_BYTES / 8;
 // The general path (classify + pointer jumping + scan) works on sub-tiles of GT_WORDS words so
@@ -97,7 +105,7 @@ enum { MODE_AGG = 0, MODE_EMIT = 1 };
 struct ChunkDesc {
   uint64_t img_base;    // arena offset of the image
   uint64_t img_len;     // bytes
-  uint64_t begin, end;  // chunk range, image-relative bytes (begin multiple of TILE_BYTES)
+  uint64_t begin, end;  // chunk range, image-relative bytes (begin multiple of the tile size)
   uint64_t stream_pos;  // stream byte offset of the image start
   uint64_t halo_off;    // arena offset (16-aligned) of the halo
   uint32_t halo_len;    // bytes (multiple of 8); 0: none
@@ -163,6 +171,7 @@ struct Params {
   // pre = words between the header and `time` (0 for sample_type TIME|READ as hbt opens it,
   // 2 with IP|TID in front); fix = bytes of a SAMPLE without its values (40 + 8*pre).
   uint32_t pre, fix;
+  uint32_t tile_bytes;    // tile_bytes_for(5 + pre + n_events)
   // IP|TID format only: open-addressing tables key -> sample count (key ~0 = empty slot; a
   // sample whose key is ~0 itself is counted in attr_special[0] / [1])
   uint64_t* tid_keys;
@@ -261,7 +270,6 @@ struct Carry {
 };
 
 struct __align__(128) Smem {
-  uint64_t data[2][STAGE_WORDS];  // TMA destinations (16-byte aligned)
   uint16_t pos[MAXC];             // candidate word positions, ascending
   union {
     struct {                      // chain phase
@@ -955,6 +963,19 @@ constexpr int EMIT_MAX_ROW_WORDS = 16;                     // n_events <= 14 on 
 constexpr int EMIT_STAGE_WORDS = 31 * EMIT_MAX_ROW_WORDS;  // per warp
 constexpr size_t EMIT_STAGE_BYTES = static_cast<size_t>(NWARP) * EMIT_STAGE_WORDS * 8;
 
+// Dynamic shared memory of k_decode: [Smem][EMIT row staging | AttrCache | nothing][two tile
+// buffers of tile_bytes + OV_BYTES each].  The tile buffers come last because their size is a
+// launch parameter.
+template <int MODE, int PRE>
+__host__ __device__ constexpr size_t decode_data_off() {
+  return (sizeof(Smem) + (MODE == MODE_EMIT ? EMIT_STAGE_BYTES : (PRE == 2 ? sizeof(AttrCache) : 0)) + 127) &
+         ~static_cast<size_t>(127);
+}
+template <int MODE, int PRE>
+__host__ __device__ constexpr size_t decode_smem_bytes(uint32_t tile_bytes) {
+  return decode_data_off<MODE, PRE>() + 2 * (static_cast<size_t>(tile_bytes) + OV_BYTES);
+}
+
 template <int MODE, int PRE>
 __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, const uint64_t* buf,
                                                     uint32_t wt, uint32_t entry, TileCtx& tc,
@@ -967,11 +988,12 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   // records whose header lies inside the tile: ceil((wt - entry) / S) by multiply-shift
   const int Kall = static_cast<int>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
   k_all = static_cast<uint32_t>(Kall);
-  int K = Kall;
+  int K = min(Kall, PASS_RECORDS);  // never more by construction of the tile size
   const bool link0 = C.valid != 0 && C.gap == 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int OWN = 31;  // records owned per warp-iteration (lanes 0..30)
-  constexpr int MAXG = (342 + NWARP * OWN - 1) / (NWARP * OWN);  // K + 1 <= 342 items
+  // the tile is sized so that K + 1 <= NWARP * OWN items: one pass (tile_bytes_for)
+  constexpr int MAXG = 1;
   const uint32_t F = n + 3;
   const bool any_tsc = P.tsc_mask != 0;
 
@@ -1235,6 +1257,10 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   if (!SPEC && MODE == MODE_AGG && P.flags[FLAG_NEED_EXACT] == 0) return;  // exact pass not needed
+  const uint32_t tb = P.tile_bytes;
+  const uint32_t stage_bytes = tb + OV_BYTES;
+  uint64_t* const data0 = reinterpret_cast<uint64_t*>(smem_raw + decode_data_off<MODE, PRE>());
+  uint64_t* const data1 = data0 + stage_bytes / 8;
 
   const uint32_t c = blockIdx.x;
   const ChunkDesc cd = P.chunks[c];
@@ -1263,9 +1289,9 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
   const uint32_t avail_rel = static_cast<uint32_t>(umin64((img_end_abs - chunk_abs + 15ull) & ~15ull, 0xFFFFFFF0ull));
   const uint8_t* const chunk_ptr = P.arena + chunk_abs;
   auto issue = [&](uint32_t tile_rel, uint32_t b) {
-    const uint32_t bytes = min(avail_rel - tile_rel, static_cast<uint32_t>(STAGE_BYTES));
+    const uint32_t bytes = min(avail_rel - tile_rel, stage_bytes);
     mbar_expect_tx(&s.bar[b], bytes);
-    tma_load_1d(s.data[b], chunk_ptr + tile_rel, bytes, &s.bar[b]);
+    tma_load_1d(b ? data1 : data0, chunk_ptr + tile_rel, bytes, &s.bar[b]);
   };
   // tile t lives in buffer (t + boff) & 1; with a halo in buffer 0 the first tile is fetched
   // into buffer 1 at once, so the two DRAM latencies at the start of a chunk overlap
@@ -1288,14 +1314,14 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
           bytes = static_cast<uint32_t>(umin64(cd.halo_len + OV_BYTES, avail));
         }
         mbar_expect_tx(&s.bar[0], bytes);
-        tma_load_1d(s.data[0], P.arena + cd.halo_off, bytes, &s.bar[0]);
+        tma_load_1d(data0, P.arena + cd.halo_off, bytes, &s.bar[0]);
         issue(0, 1);
       }
       boff = 1;
       n_issued = 1;
       mbar_wait(&s.bar[0], phase[0]);
       phase[0] ^= 1;
-      const uint64_t* hb = s.data[0];
+      const uint64_t* hb = data0;
       load_carry<PRE>(s, P, cd.stream, PRED_UNKNOWN, 0);
       entry_abs = chunk_abs;
       // Quick scout: the last word of the halo that looks like a SAMPLE header of the configured
@@ -1393,18 +1419,21 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
     if (threadIdx.x == 0) issue(0, boff);
     n_issued = 1;
   }
-  for (uint32_t tile_rel = 0; tile_rel < chunk_len; tile_rel += TILE_BYTES) {
-    const uint32_t b = ((tile_rel / TILE_BYTES) + boff) & 1;
-    if (tile_rel + TILE_BYTES < chunk_len) {
-      if (threadIdx.x == 0) issue(tile_rel + TILE_BYTES, b ^ 1);
+  for (uint32_t tile_rel = 0, b = boff; tile_rel < chunk_len; tile_rel += tb, b ^= 1) {
+    if (tile_rel + tb < chunk_len) {
+      if (threadIdx.x == 0) issue(tile_rel + tb, b ^ 1);
       ++n_issued;
     }
     mbar_wait(&s.bar[b], phase[b]);
     phase[b] ^= 1;
     ++n_waited;
-    const uint64_t* buf = s.data[b];
-    const uint32_t wt = min(static_cast<uint32_t>(TILE_BYTES), chunk_len - tile_rel) / 8;
+    const uint64_t* buf = b ? data1 : data0;
+    const uint32_t wt = min(tb, chunk_len - tile_rel) / 8;
     uint32_t tile_kind = 0;
+#ifdef HBT_DBG_LOAD_ONLY
+    if (buf[threadIdx.x] == 0x123456789ull) s.cnt[0] = 1;
+    next_rel = tile_rel + 8 * wt;
+#endif
     if (next_rel < tile_rel + 8 * wt) {
       const uint32_t entry = (next_rel - tile_rel) / 8;
       const uint64_t tile_abs = chunk_abs + tile_rel;
