@@ -227,6 +227,75 @@ class Oracle:
         return secs, acc, [c.as_dict() for c in ctrs]
 
 
+
+# --- ContextSwitch-mode decode (oracle/hbtcs_api.h) ----------------------------------------------
+class CsEvent(C.Structure):
+    _fields_ = [("tstamp", C.c_uint64), ("type", C.c_uint8), ("level", C.c_uint8),
+                ("comp_unit_id", C.c_uint16), ("tag", C.c_uint32)]
+
+
+class CsThread(C.Structure):
+    _fields_ = [("vid", C.c_uint32), ("ppid", C.c_int32), ("ptid", C.c_int32), ("pid", C.c_int32),
+                ("tid", C.c_int32), ("n_names", C.c_uint32), ("fork_ts", C.c_uint64),
+                ("end_ts", C.c_uint64)]
+
+
+class CsName(C.Structure):
+    _fields_ = [("vid", C.c_uint32), ("is_exec", C.c_uint8), ("len", C.c_uint8),
+                ("pad", C.c_uint8 * 2), ("tstamp", C.c_uint64), ("name", C.c_char * 16)]
+
+
+class CsState(C.Structure):
+    _fields_ = [("last_tstamp", C.c_uint64), ("in_write_errors", C.c_uint32), ("pad", C.c_uint32)]
+
+
+CS_EVENT_DTYPE = np.dtype([("tstamp", "<u8"), ("type", "u1"), ("level", "u1"),
+                           ("comp_unit_id", "<u2"), ("tag", "<u4")])
+
+
+def cs_run(kind, streams, tid_level=1, batch=256, states=None):
+    """Decode per-CPU ContextSwitch-mode streams with the reference ("reference") or the C
+    restatement ("port").  Returns dict(events=[structured arrays], counters=[dict],
+    states=[(last_tstamp, in_write_errors)], threads=[tuples], names=[tuples])."""
+    o = load(kind)
+    f = getattr(o.lib, o.prefix + "_cs_run")
+    f.restype = C.c_int
+    ns = len(streams)
+    streams = [np.ascontiguousarray(s, dtype=np.uint8) for s in streams]
+    ptrs = (C.c_void_p * ns)(*[s.ctypes.data for s in streams])
+    lens = np.array([len(s) for s in streams], np.uint64)
+    caps = np.array([len(s) // 16 + 8 for s in streams], np.uint64)   # <= 2 events per >= 32 bytes
+    offs = np.concatenate([[0], np.cumsum(caps)[:-1]]).astype(np.uint64)
+    ev = np.zeros(int(caps.sum()), CS_EVENT_DTYPE)
+    nev = np.zeros(ns, np.uint64)
+    ctrs = (Counters * ns)()
+    sin = None
+    if states is not None:
+        sin = (CsState * ns)()
+        for i, (lt, we) in enumerate(states):
+            sin[i].last_tstamp = lt
+            sin[i].in_write_errors = we
+    sout = (CsState * ns)()
+    tcap = sum(len(s) for s in streams) // 32 + 16
+    th = (CsThread * tcap)()
+    nm = (CsName * tcap)()
+    nt = C.c_uint64(0)
+    nn = C.c_uint64(0)
+    rc = f(C.c_uint32(ns), ptrs, _p(lens, C.c_uint64), C.c_uint32(tid_level), C.c_uint32(batch), sin, sout,
+           C.c_void_p(ev.ctypes.data), _p(offs, C.c_uint64), _p(caps, C.c_uint64), _p(nev, C.c_uint64),
+           ctrs, th, C.c_uint64(tcap), C.byref(nt), nm, C.c_uint64(tcap), C.byref(nn))
+    assert rc == 0
+    return {
+        "events": [ev[int(offs[i]):int(offs[i]) + int(nev[i])].copy() for i in range(ns)],
+        "counters": [c.as_dict() for c in ctrs],
+        "states": [(int(s.last_tstamp), int(s.in_write_errors)) for s in sout],
+        "threads": [(t.vid, t.ppid, t.ptid, t.pid, t.tid, t.n_names, t.fork_ts, t.end_ts)
+                    for t in th[:nt.value]],
+        "names": sorted((n.vid, n.tstamp, bytes(n.name[:0]) + C.string_at(C.addressof(n) + 16, n.len), n.is_exec)
+                        for n in nm[:nn.value]),
+    }
+
+
 _PATHS = {
     "reference": (os.path.join(HERE, "_ref", "libhbtref.so"), "hbtref"),
     "reference_nolog": (os.path.join(HERE, "_ref", "libhbtref_nolog.so"), "hbtref"),

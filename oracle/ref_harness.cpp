@@ -417,3 +417,153 @@ double hbtref_run_capture(const hbtref_params* p, uint32_t n_streams,
 }
 
 }  // extern "C"
+
+// =====================================================================================
+// ContextSwitch-mode decode: the real
+// PerfEventsGroup<CpuThreadSwitchGenerator, mode::ContextSwitch>::consume and the handlers of
+// hbt/src/perf_event/PerCpuThreadSwitchGenerator.h:219-407 over a fake mmap page.  Harness
+// glue: the fake page, draining the output ring (ringbuffer::Consumer) after every consume
+// call, exporting PerThreadStats::info.  The third-party `pfs` /proc reader that
+// ProcFsHelpers.h includes is replaced by oracle/stubs/pfs/procfs.hpp (cmdline := nullopt).
+#include "hbt/src/perf_event/PerCpuThreadSwitchGenerator.h"
+
+#include "hbtcs_api.h"
+
+namespace {
+using CsGen = hp::CpuThreadSwitchGenerator;
+static_assert(sizeof(hbtcs_event) == sizeof(facebook::hbt::tagstack::Event));
+
+struct FakeCsGen {
+  std::unique_ptr<CsGen> gen;
+  uint8_t* base = nullptr;
+  volatile perf_event_mmap_page* page = nullptr;
+  FakeCsGen(uint32_t cpu, uint32_t tid_level, std::shared_ptr<hp::PerThreadStats> stats, size_t len,
+            size_t rb_events) {
+    gen = std::make_unique<CsGen>(static_cast<facebook::hbt::CpuId>(cpu), -1,
+                                  static_cast<facebook::hbt::tagstack::Level>(tid_level), stats, rb_events);
+    size_t data_size = 4096;
+    while (data_size < len) data_size <<= 1;
+    base = static_cast<uint8_t*>(aligned_alloc(4096, 4096 + data_size));
+    memset(base, 0, 4096);
+    page = reinterpret_cast<volatile perf_event_mmap_page*>(base);
+    page->data_offset = 4096;
+    page->data_size = data_size;
+    gen->mmap_base_ = base;
+    gen->event_fds_[0] = 3;  // isOpen(); never used by consume
+  }
+  ~FakeCsGen() {
+    gen->event_fds_[0] = -1;
+    gen->mmap_base_ = nullptr;
+    gen.reset();
+    free(base);
+  }
+  void load(const uint8_t* bytes, size_t len) {
+    memcpy(base + 4096, bytes, len);
+    page->data_tail = 0;
+    page->data_head = len;
+  }
+};
+}  // namespace
+
+extern "C" int hbtref_cs_run(uint32_t n_streams, const uint8_t* const* bytes, const uint64_t* lens,
+    uint32_t tid_level, uint32_t batch, const hbtcs_state* in, hbtcs_state* out,
+    hbtcs_event* events, const uint64_t* ev_off, const uint64_t* ev_cap, uint64_t* n_events,
+    hbtref_counters* ctrs, hbtcs_thread* threads, uint64_t thread_cap, uint64_t* n_threads,
+    hbtcs_name* names, uint64_t name_cap, uint64_t* n_names) {
+  silence_begin();
+  auto stats = std::make_shared<hp::PerThreadStats>();
+  if (batch == 0) batch = 1;
+  for (uint32_t s = 0; s < n_streams; ++s) {
+    // every record writes at most two events (a pending WriteErrorsEnd and its own)
+    FakeCsGen fg(s, tid_level, stats, lens[s], 2ull * batch + 16);
+    CsGen& g = *fg.gen;
+    if (in) {
+      g.last_tstamp_ = in[s].last_tstamp;
+      g.in_write_errors_ = in[s].in_write_errors != 0;
+    }
+    fg.load(bytes[s], lens[s]);
+    hr::Consumer<CsGen::RbExtraData> cons(g.getOutput());
+    hbtref_counters c;
+    memset(&c, 0, sizeof(c));
+    uint64_t nev = 0;
+    for (;;) {
+      const uint64_t tail0 = fg.page->data_tail;
+      ssize_t ret = g.consume(batch);
+      // consume() returns -ENODATA instead of the count when it drains the ring (:1574-1588),
+      // so the records it took are counted here from how far data_tail moved (glue)
+      for (uint64_t t = tail0; t < fg.page->data_tail;) {
+        t += reinterpret_cast<const perf_event_header*>(fg.base + 4096 + t)->size;
+        c.num_records += 1;
+      }
+      while (g.getNumEntries() > 0) {
+        hbtcs_event ev;
+        if (cons.copy(sizeof(ev), &ev) < 0) abort();
+        if (events && nev < ev_cap[s]) events[ev_off[s] + nev] = ev;
+        ++nev;
+      }
+      if (ret == -ENODATA) break;
+      if (ret < 0) {
+        c.err = ret;
+        break;
+      }
+    }
+    c.lost = g.getNumRecordLost();
+    c.comm = g.getNumRecordComm();
+    c.exit = g.getNumRecordExit();
+    c.throttle = g.getNumRecordThrottle();
+    c.unthrottle = g.getNumRecordUnThrottle();
+    c.fork = g.getNumRecordFork();
+    c.sample = g.getNumRecordSample();
+    c.read = g.getNumRecordRead();
+    c.aux = g.getNumRecordAux();
+    c.itrace_start = g.getNumRecordItraceStart();
+    c.switch_cpu_wide = g.getNumRecordSwitchCpuWide();
+    c.num_rows = nev;
+    c.err_offset = fg.page->data_tail;
+    c.last_tstamp = g.getLastTimeStamp();
+    if (ctrs) ctrs[s] = c;
+    if (n_events) n_events[s] = nev;
+    if (out) {
+      out[s].last_tstamp = g.last_tstamp_;
+      out[s].in_write_errors = g.in_write_errors_ ? 1 : 0;
+      out[s].pad = 0;
+    }
+  }
+  // threads by vid (vids are 1..next_vid-1)
+  uint64_t nt = 0, nn = 0;
+  for (facebook::hbt::tagstack::Tag vid = 1; vid < stats->next_vid; ++vid) {
+    auto it = stats->info.find(vid);
+    if (it == stats->info.end()) continue;
+    const hp::ThreadInfo& ti = it->second;
+    uint32_t cnt = 0;
+    for (const auto& p : ti.names.getPoints()) {
+      if (names && nn < name_cap) {
+        hbtcs_name& o = names[nn];
+        memset(&o, 0, sizeof(o));
+        o.vid = vid;
+        o.is_exec = p.value.is_exec;
+        o.len = static_cast<uint8_t>(std::min<size_t>(p.value.new_name.size(), 16));
+        o.tstamp = p.tstamp;
+        memcpy(o.name, p.value.new_name.data(), o.len);
+      }
+      ++nn;
+      ++cnt;
+    }
+    if (threads && nt < thread_cap) {
+      hbtcs_thread& o = threads[nt];
+      o.vid = vid;
+      o.ppid = ti.ppid;
+      o.ptid = ti.ptid;
+      o.pid = ti.pid;
+      o.tid = ti.tid;
+      o.n_names = cnt;
+      o.fork_ts = ti.fork_timestamp;
+      o.end_ts = ti.end_timestamp;
+    }
+    ++nt;
+  }
+  if (n_threads) *n_threads = nt;
+  if (n_names) *n_names = nn;
+  silence_end();
+  return 0;
+}

@@ -135,3 +135,99 @@ def random_stream(seed, n_records, n_events, *, p_lost=0.0, p_throttle=0.0, p_ot
         else:
             out += sample(ts, te, tr, v)
     return to_u8(out), {"t_end": ts}
+
+
+# --- ContextSwitch mode (mode::ContextSwitch, PerfEventsGroup.h:105-191): sample_type TIME|TID
+# with sample_id_all, so every record ends in sample_id {u32 pid, tid; u64 time} -------------
+MISC_SWITCH_OUT = 1 << 13
+MISC_SWITCH_OUT_PREEMPT = 1 << 14
+EV_CREATE, EV_DESTROY, EV_IN, EV_OUT_PREEMPT, EV_OUT_YIELD, EV_WE_START, EV_WE_END = 2, 3, 4, 5, 6, 7, 8
+
+
+def sample_id(pid, tid, ts):
+    return struct.pack("<IIQ", pid, tid, ts & ((1 << 64) - 1))
+
+
+def cs_lost(num_lost, ts, pid=0, tid=0, ident=7):
+    return header(LOST, 40) + struct.pack("<QQ", ident, num_lost) + sample_id(pid, tid, ts)
+
+
+def cs_comm(pid, tid, name, ts, misc=0):
+    name = bytes(name) + b"\0"
+    name += b"\0" * (-len(name) % 8)
+    return header(COMM, 16 + len(name) + 16, misc) + struct.pack("<II", pid, tid) + name + sample_id(pid, tid, ts)
+
+
+def cs_exit(pid, ppid, tid, ptid, ts, rtype=EXIT):
+    return header(rtype, 48) + struct.pack("<IIIIQ", pid, ppid, tid, ptid, ts) + sample_id(pid, tid, ts)
+
+
+def cs_fork(pid, ppid, tid, ptid, ts):
+    return cs_exit(pid, ppid, tid, ptid, ts, rtype=FORK)
+
+
+def cs_switch(ts, pid, tid, out=False, preempt=False, np_pid=0, np_tid=0):
+    misc = (MISC_SWITCH_OUT if out else 0) | (MISC_SWITCH_OUT_PREEMPT if out and preempt else 0)
+    return header(SWITCH_CPU_WIDE, 32, misc) + struct.pack("<II", np_pid, np_tid) + sample_id(pid, tid, ts)
+
+
+def cs_throttle(ts, rtype=THROTTLE, pid=0, tid=0):
+    return header(rtype, 48) + struct.pack("<QQQ", ts, 7, 9) + sample_id(pid, tid, ts)
+
+
+def random_cs_streams(seed, n_cpus, n_records, *, p_lost=0.0, p_life=0.0, p_comm=0.0, p_throttle=0.0,
+                      p_other=0.0, n_tids=64, t_start=1_000_000_000, dt=20_000, tid_base=5_000_000):
+    """Per-CPU ContextSwitch-mode streams that keep the reference's handlers inside their
+    contract: lifecycle records (FORK/EXIT/COMM) of a tid only on its home CPU (tid % n_cpus) in
+    fork -> comm* -> exit order with increasing time, tids above pid_max so /proc lookups of the
+    test host find nothing.  tid 0 (idle) only switches."""
+    r = SplitMix64(seed)
+    streams = []
+    for cpu in range(n_cpus):
+        out = bytearray()
+        ts = t_start + cpu * 7
+        home = [t for t in range(n_tids) if t % n_cpus == cpu]
+        alive = {}
+        cur = 0
+        for _ in range(n_records):
+            ts += dt + r.uniform(0, dt // 4)
+            u = r.next() / 2.0**64
+            if u < p_lost:
+                out += cs_lost(r.uniform(1, 90), ts, 1, cur)
+                alive.clear()      # the reference forgets which tids are active
+                continue
+            u -= p_lost
+            if u < p_life and home:
+                k = home[r.uniform(0, len(home) - 1)]
+                tid = tid_base + k
+                pid = tid_base + (k // 4) * 4
+                if not alive.get(k):
+                    out += cs_fork(pid, 1, tid, 1, ts)
+                    alive[k] = True
+                else:
+                    out += cs_exit(pid, 1, tid, 1, ts)
+                    alive[k] = False
+                continue
+            u -= p_life
+            if u < p_comm and home:
+                k = home[r.uniform(0, len(home) - 1)]
+                name = b"t%d_%d" % (k, r.uniform(0, 99999)) + b"x" * r.uniform(0, 6)
+                out += cs_comm(tid_base + (k // 4) * 4, tid_base + k, name[:15], ts)
+                continue
+            u -= p_comm
+            if u < p_throttle:
+                out += cs_throttle(ts) + cs_throttle(ts + 5, rtype=UNTHROTTLE)
+                continue
+            u -= p_throttle
+            if u < p_other:
+                out += other(r.uniform(16, 40), [r.next() for _ in range(r.uniform(0, 5))])
+                continue
+            # a context switch: current thread out, next thread in
+            nxt = r.uniform(0, n_tids - 1)
+            nxt_tid = 0 if nxt == 0 else tid_base + nxt
+            out += cs_switch(ts, 1, cur, out=True, preempt=r.uniform(0, 1) == 1, np_tid=nxt_tid)
+            ts += 800 + r.uniform(0, 400)
+            out += cs_switch(ts, 1, nxt_tid, np_tid=cur)
+            cur = nxt_tid
+        streams.append(to_u8(out))
+    return streams
