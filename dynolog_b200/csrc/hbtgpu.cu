@@ -1407,3 +1407,5 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
 }
 
 }  // extern "C"
+
+#include "hbtgpu_cs_host.inc"

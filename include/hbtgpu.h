@@ -369,6 +369,128 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
 /* Message of the last failed hbtgpu_decode_image_noalloc on this thread. */
 const char* hbtgpu_noalloc_last_error(void);
 
+/* ---- ContextSwitch-mode decode -------------------------------------
+ *
+ * Replaces, for captured ring images of hbt's ContextSwitch mode (sample_type TIME|TID with
+ * sample_id_all, hbt/src/perf_event/PerfEventsGroup.h:963-970; record layouts :105-191),
+ *   PerfEventsGroup<CpuThreadSwitchGenerator, mode::ContextSwitch>::consume      :1394-1589
+ *   CpuThreadSwitchGenerator::handleRecord{Lost,Comm,Exit,Fork,SwitchCpuWide}
+ *       hbt/src/perf_event/PerCpuThreadSwitchGenerator.h:219-446
+ * The GPU turns records into the 16-byte tagstack::Event stream; the tid -> virtual id
+ * dictionary (PerThreadStats, PerCpuThreadSwitchGenerator.h:52-135), which is order-dependent
+ * and shared by all CPUs, is the host function hbtgpu_cs_assign_vids below.
+ */
+
+/* tagstack::Event, hbt/src/tagstack/Event.h:28-56: same size, field order and type codes */
+typedef struct {
+  uint64_t tstamp;
+  uint8_t type;          /* 2 ThreadCreation, 3 ThreadDestruction, 4 SwitchIn, 5 SwitchOutPreempt,
+                            6 SwitchOutYield, 7 WriteErrorsStart, 8 WriteErrorsEnd */
+  uint8_t level;         /* tid_level; 255 (kInvalidLevel) for the WriteErrors events */
+  uint16_t comp_unit_id; /* cpu */
+  uint32_t tag;          /* as decoded: the raw tid; after hbtgpu_cs_assign_vids: the virtual id.
+                            0xFFFFFFFF (kNA) for events that carry none */
+} hbtgpu_cs_event;
+
+/* A record that changes the thread dictionary and is not a plain switch-in: LOST (clears the
+ * active tids, :243-247), COMM, EXIT, FORK.  event_index is the position, in the cpu's event
+ * array, of the event this record wrote (COMM writes none: the position its next event has). */
+typedef struct {
+  uint64_t tstamp;
+  uint64_t event_index;
+  uint32_t type;         /* perf record type: 2 LOST, 3 COMM, 4 EXIT, 7 FORK */
+  uint32_t misc;
+  int32_t pid, ppid, tid, ptid;
+  uint32_t name_len;     /* COMM: bytes of the comm field (size - 32) */
+  uint32_t pad;
+  char name[16];         /* COMM: first 16 bytes of the comm field */
+} hbtgpu_cs_op;
+
+/* CpuThreadSwitchGenerator::last_tstamp_ / in_write_errors_ (:418-421) */
+typedef struct {
+  uint64_t last_tstamp;
+  uint32_t in_write_errors;
+  uint32_t pad;
+} hbtgpu_cs_state;
+
+typedef struct {
+  int32_t device;
+  uint32_t max_cpus;
+  uint32_t tid_level;    /* tagstack::Level of the thread ids (ctor argument, :187-197) */
+  uint32_t flags;        /* HBTGPU_F_FORCE_EXACT */
+  uint64_t arena_bytes;  /* device memory for submitted images */
+} hbtgpu_cs_config;
+
+typedef struct hbtgpu_cs_ctx hbtgpu_cs_ctx;
+
+hbtgpu_cs_ctx* hbtgpu_cs_create(const hbtgpu_cs_config* cfg);
+void hbtgpu_cs_destroy(hbtgpu_cs_ctx* ctx);
+const char* hbtgpu_cs_last_error(hbtgpu_cs_ctx* ctx);
+/* Generator state a cpu starts from (default: last_tstamp 0, not in write errors, as after
+ * construction).  After hbtgpu_cs_run the state to carry into the next window is
+ * hbtgpu_cs_get_state. */
+int hbtgpu_cs_set_state(hbtgpu_cs_ctx* ctx, uint32_t cpu, const hbtgpu_cs_state* st);
+/* Append one ring image (whole records, oldest first) of one cpu; host memory, copied
+ * asynchronously (pin it for speed).  Images of a cpu form its stream in submission order. */
+int hbtgpu_cs_submit_image(hbtgpu_cs_ctx* ctx, uint32_t cpu, const void* bytes, uint64_t len);
+/* Forget the submitted images (states are kept). */
+int hbtgpu_cs_reset(hbtgpu_cs_ctx* ctx);
+/* Decode everything submitted since the last reset.  Asynchronous on the context's stream
+ * except for one read-back of the event totals. */
+int hbtgpu_cs_run(hbtgpu_cs_ctx* ctx);
+int hbtgpu_cs_sync(hbtgpu_cs_ctx* ctx);
+/* getNumRecord*() (:791-824) of the cpu; num_rows = events written; err / err_offset as for
+ * the Sampling path (-EPERM at the first record that trips a fence). */
+int hbtgpu_cs_get_counters(hbtgpu_cs_ctx* ctx, uint32_t cpu, hbtgpu_counters* out);
+int hbtgpu_cs_get_state(hbtgpu_cs_ctx* ctx, uint32_t cpu, hbtgpu_cs_state* out);
+int hbtgpu_cs_num_events(hbtgpu_cs_ctx* ctx, uint32_t cpu, uint64_t* n_events, uint64_t* n_ops);
+/* Events of a cpu in ring order, tag = raw tid; pids (may be NULL) gets, per event, the pid
+ * the record carried (SwitchIn: sample_id.pid; ThreadCreation/Destruction: pid). */
+int hbtgpu_cs_get_events(hbtgpu_cs_ctx* ctx, uint32_t cpu, hbtgpu_cs_event* out, uint32_t* pids,
+                         uint64_t cap, uint64_t* n);
+int hbtgpu_cs_get_ops(hbtgpu_cs_ctx* ctx, uint32_t cpu, hbtgpu_cs_op* out, uint64_t cap, uint64_t* n);
+/* Device views for consumers that stay on the GPU: events / pids of all cpus, cpu c at
+ * [base[c], base[c+1]). */
+int hbtgpu_cs_events_device(hbtgpu_cs_ctx* ctx, const hbtgpu_cs_event** events, const uint32_t** pids,
+                            const uint64_t** base);
+typedef struct {
+  uint64_t image_bytes;
+  uint32_t n_chunks, exact_runs, exact_reason, exact_chunk;
+  float last_count_ms, last_emit_ms, last_run_ms;
+  uint32_t kernel_launches;
+} hbtgpu_cs_stats;
+int hbtgpu_cs_get_stats(hbtgpu_cs_ctx* ctx, hbtgpu_cs_stats* out);
+
+/* Host mirror of PerThreadStats (PerCpuThreadSwitchGenerator.h:52-135): assigns virtual ids in
+ * encounter order.  Feed it one cpu's window at a time, cpus in the order the reference's
+ * consumer loop visits them; events[i].tag is rewritten from tid to vid in place.  /proc
+ * lookups (cmdline, comm of threads first seen in a switch) are the caller's business. */
+typedef struct hbtgpu_cs_threads hbtgpu_cs_threads;
+typedef struct {
+  uint32_t vid;
+  int32_t ppid, ptid, pid, tid;
+  uint32_t n_names;
+  uint64_t fork_ts, end_ts;  /* ~0 (kInvalidTimeStamp) when unset */
+} hbtgpu_cs_thread;
+typedef struct {
+  uint32_t vid;
+  uint8_t is_exec;           /* always 1: `misc | PERF_RECORD_MISC_COMM_EXEC`, :273 */
+  uint8_t len;
+  uint8_t pad[2];
+  uint64_t tstamp;
+  char name[16];
+} hbtgpu_cs_name;
+hbtgpu_cs_threads* hbtgpu_cs_threads_create(void);
+void hbtgpu_cs_threads_destroy(hbtgpu_cs_threads* t);
+/* -EINVAL for input on which the reference's handlers would throw. */
+int hbtgpu_cs_assign_vids(hbtgpu_cs_threads* t, hbtgpu_cs_event* events, const uint32_t* pids,
+                          uint64_t n_events, const hbtgpu_cs_op* ops, uint64_t n_ops);
+uint64_t hbtgpu_cs_threads_count(const hbtgpu_cs_threads* t);
+uint64_t hbtgpu_cs_threads_name_count(const hbtgpu_cs_threads* t);
+/* threads by vid; names grouped by thread, each thread's in series (time) order */
+int hbtgpu_cs_threads_get(const hbtgpu_cs_threads* t, hbtgpu_cs_thread* threads, uint64_t thread_cap,
+                          hbtgpu_cs_name* names, uint64_t name_cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,7 +30,8 @@ def test_library_exports_every_declared_symbol(built):
     assert len(decl) >= 25
     for s in decl:
         assert hasattr(lib, s), f"{s} declared in include/hbtgpu.h but not exported"
-    assert sorted(built.ABI_SYMBOLS) == decl, "ctypes binding list out of sync with the header"
+    from dynolog_b200 import hbtgpu_cs
+    assert sorted(built.ABI_SYMBOLS + hbtgpu_cs.ABI_SYMBOLS) == decl, "ctypes binding lists out of sync with the header"
 
 
 def test_struct_sizes_match_header(built, tmp_path):
@@ -47,6 +48,54 @@ def test_struct_sizes_match_header(built, tmp_path):
     assert sizes == [ctypes.sizeof(h.Config), ctypes.sizeof(h.Carry), ctypes.sizeof(h.Counters),
                      ctypes.sizeof(h.BucketView), ctypes.sizeof(h.HeadStub), ctypes.sizeof(h.Stats),
                      ctypes.sizeof(h.Metric)]
+
+
+def test_cs_struct_sizes_match_header(built, tmp_path):
+    from dynolog_b200 import hbtgpu_cs as cs
+    src = tmp_path / "szcs.c"
+    src.write_text('#include <stdio.h>\n#include "hbtgpu.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu\\n",'
+                   "sizeof(hbtgpu_cs_event),sizeof(hbtgpu_cs_op),sizeof(hbtgpu_cs_state),"
+                   "sizeof(hbtgpu_cs_config),sizeof(hbtgpu_cs_stats),sizeof(hbtgpu_cs_thread),"
+                   "sizeof(hbtgpu_cs_name));return 0;}\n")
+    exe = tmp_path / "szcs"
+    subprocess.check_call(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    sizes = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert sizes == [cs.EVENT_DTYPE.itemsize, cs.OP_DTYPE.itemsize, ctypes.sizeof(cs.CsState),
+                     ctypes.sizeof(cs.CsConfig), ctypes.sizeof(cs.CsStats), cs.THREAD_DTYPE.itemsize,
+                     cs.NAME_DTYPE.itemsize]
+
+
+def test_cs_thread_dictionary_on_host(built):
+    """hbtgpu_cs_assign_vids is host code (mirror of PerThreadStats): hand-made events and ops."""
+    import numpy as np
+    from dynolog_b200 import hbtgpu_cs as cs
+    T = 5_000_000
+    ev = np.zeros(6, cs.EVENT_DTYPE)
+    ev["type"] = [4, 5, 2, 4, 3, 4]          # in(T+1), out, create(T+2), in(T+2), destroy(T+2), in(0)
+    ev["tag"] = [T + 1, 0xFFFFFFFF, T + 2, T + 2, T + 2, 0]
+    ev["tstamp"] = [10, 20, 30, 40, 50, 60]
+    pids = np.array([7, 0, 8, 8, 8, 0], np.uint32)
+    ops = np.zeros(3, cs.OP_DTYPE)
+    ops["type"] = [7, 3, 4]                   # FORK at event 2, COMM before event 3, EXIT at event 4
+    ops["event_index"] = [2, 3, 4]
+    ops["tstamp"] = [30, 35, 50]
+    ops["pid"], ops["tid"], ops["ppid"], ops["ptid"] = 8, T + 2, 1, 1
+    ops["name_len"][1] = 8
+    ops["name"][1] = b"worker"
+    th = cs.Threads()
+    th.assign(ev, pids, ops)
+    assert ev["tag"].tolist() == [1, 0xFFFFFFFF, 2, 2, 2, 0]
+    threads, names = th.table()
+    assert threads == [(1, -1, -1, 7, T + 1, 0, 2**64 - 1, 2**64 - 1), (2, 1, 1, 8, T + 2, 1, 30, 50)]
+    assert names == [(2, 35, b"worker\0\0", 1)]
+    # after the exit the tid is new again; a LOST forgets every active tid
+    ev2 = np.zeros(3, cs.EVENT_DTYPE)
+    ev2["type"] = [4, 7, 4]
+    ev2["tag"] = [T + 2, 0xFFFFFFFF, T + 1]
+    ops2 = np.zeros(1, cs.OP_DTYPE)
+    ops2["type"], ops2["event_index"] = 2, 1
+    th.assign(ev2, np.zeros(3, np.uint32), ops2)
+    assert ev2["tag"].tolist() == [3, 0xFFFFFFFF, 4]
 
 
 def test_header_is_plain_c(tmp_path):

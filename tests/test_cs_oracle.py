@@ -68,7 +68,7 @@ def test_lost_after_lost_and_state_carry():
 
 def test_fences():
     good = rg.cs_switch(1000, 1, 0)
-    for bad in (rg.header(rg.SWITCH_CPU_WIDE, 0), rg.header(rg.SWITCH_CPU_WIDE, 28) + b"\0" * 20,
+    for bad in (rg.header(rg.SWITCH_CPU_WIDE, 0), rg.header(rg.SWITCH_CPU_WIDE, 28) + b"\0" * 24,
                 rg.header(rg.LOST, 32) + b"\0" * 24, rg.header(rg.FORK, 64) + b"\0" * 8):
         r = pyoracle.cs_run("port", [rg.to_u8(good + bad)])
         c = r["counters"][0]
