@@ -99,7 +99,7 @@ __device__ __forceinline__ void cs_store_event(const CsOut& O, uint64_t idx, uin
 }
 
 // One record that is not a 32-byte SWITCH, handled by thread 0 exactly as consume() + the
-// handlers do.  `r` points at the record in global memory (it may be longer than a tile).
+// handlers do.  `r` points at the record (shared memory, or the arena for one longer than the tile).
 // Returns its size in bytes, or 0 if it trips a fence (size 0 / not a multiple of 8 / past the
 // image end / too short for its handler).
 template <bool EMIT>
@@ -402,9 +402,13 @@ __global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
           const uint64_t abs_off = chunk_abs + tile_rel + 8ull * ew;
           const uint64_t room = limit_abs - abs_off;
           uint32_t sz = 0;
-          if (room >= 8)
-            sz = cs_odd_record<EMIT>(s, O, reinterpret_cast<const uint64_t*>(P.arena + abs_off), abs_off, room, cu,
-                                     ev0, op0);
+          if (room >= 8) {
+            // read it from the staged tile when it lies inside (nearly always), else from the arena
+            const uint32_t staged = min(avail_rel - tile_rel, static_cast<uint32_t>(CS_TILE_BYTES + CS_OV_BYTES)) / 8;
+            const uint32_t rw = static_cast<uint32_t>(buf[ew] >> 51);  // size / 8
+            const uint64_t* r = ew + rw <= staged ? buf + ew : reinterpret_cast<const uint64_t*>(P.arena + abs_off);
+            sz = cs_odd_record<EMIT>(s, O, r, abs_off, room, cu, ev0, op0);
+          }
           s.seg_k = sz;
         }
         __syncthreads();
@@ -592,16 +596,30 @@ __global__ void __launch_bounds__(32) k_cs_scan(const Params P, const CsOut O, u
   }
 }
 
-// exclusive scan of the stream totals (one block) and rebase of every chunk
-__global__ void k_cs_bases(const Params P, const CsOut O, const uint64_t* totals) {
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    uint64_t ev = 0, op = 0;
-    for (uint32_t s = 0; s < P.n_streams; ++s) {
-      O.ev_base[s] = ev;
-      O.op_base[s] = op;
-      ev += totals[2 * s];
-      op += totals[2 * s + 1];
+// exclusive scan of the stream totals (one warp, 32 streams per step) and rebase of every chunk
+__global__ void __launch_bounds__(32) k_cs_bases(const Params P, const CsOut O, const uint64_t* totals) {
+  const uint32_t lane = threadIdx.x;
+  uint64_t ev = 0, op = 0;
+  for (uint32_t s0 = 0; s0 < P.n_streams; s0 += 32) {
+    const uint32_t s = s0 + lane;
+    const uint64_t a = s < P.n_streams ? totals[2 * s] : 0, b = s < P.n_streams ? totals[2 * s + 1] : 0;
+    uint64_t ia = a, ib = b;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint64_t ya = __shfl_up_sync(0xffffffffu, ia, d), yb = __shfl_up_sync(0xffffffffu, ib, d);
+      if (lane >= d) {
+        ia += ya;
+        ib += yb;
+      }
     }
+    if (s < P.n_streams) {
+      O.ev_base[s] = ev + ia - a;
+      O.op_base[s] = op + ib - b;
+    }
+    ev += __shfl_sync(0xffffffffu, ia, 31);
+    op += __shfl_sync(0xffffffffu, ib, 31);
+  }
+  if (lane == 0) {
     O.ev_base[P.n_streams] = ev;
     O.op_base[P.n_streams] = op;
   }

@@ -111,3 +111,26 @@ def capture(cfg_id, n_cpus, n_samples=None, max_bytes_per_cpu=None, forge_ppm=0,
     spec = make_spec(cfg_id, forge_ppm=forge_ppm, **over)
     cap = Capture(spec, n_cpus)
     return spec, cap.window(n_samples=n_samples, max_bytes_per_cpu=max_bytes_per_cpu, out=out)
+
+
+# --- ContextSwitch-mode captures ------------------------------------------------
+class CsSpec(C.Structure):
+    _fields_ = [("n_cpus", C.c_uint32), ("n_tids", C.c_uint32), ("life_ppm", C.c_uint32),
+                ("comm_ppm", C.c_uint32), ("lost_ppm", C.c_uint32), ("throttle_ppm", C.c_uint32),
+                ("t_start", C.c_uint64), ("dt_ns", C.c_uint64), ("seed", C.c_uint64)]
+
+
+def cs_capture(n_cpus, bytes_per_cpu, n_tids=4096, life_ppm=2000, comm_ppm=500, lost_ppm=20,
+               throttle_ppm=10, seed=1, out=None, n_threads=None):
+    """Per-CPU context-switch streams of ~bytes_per_cpu bytes each: pairs of 32-byte
+    SWITCH_CPU_WIDE records with FORK / COMM / EXIT / LOST / THROTTLE at the given rates per
+    million pairs.  Returns a list of uint8 views."""
+    L = lib()
+    spec = CsSpec(n_cpus, n_tids, life_ppm, comm_ppm, lost_ppm, throttle_ppm, T_START, 20_000, seed)
+    cap = (int(bytes_per_cpu) + 127) // 128 * 128
+    if out is None:
+        out = np.empty(n_cpus * cap, np.uint8)
+    lens = np.zeros(n_cpus, np.uint64)
+    L.hbtsynth_cs_capture(C.byref(spec), C.c_void_p(out.ctypes.data), C.c_uint64(cap),
+                          C.c_void_p(lens.ctypes.data), C.c_uint32(n_threads or min(n_cpus, os.cpu_count() or 1)))
+    return [out[i * cap:i * cap + int(lens[i])] for i in range(n_cpus)]
