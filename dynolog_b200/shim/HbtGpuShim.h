@@ -12,6 +12,12 @@
 //     getCpuGenerator(cpu)          PerCpuBase.h                same
 //     accumUntil(batch, stop_ts)    PerCpuSampleGeneratorBase.h:69-94   same (decodes everything submitted)
 //   TraceMonitor::applyToCountSamplesAndConsume  mon/TraceMonitor.h:35-108   applyToCountSamples
+//   CpuThreadSwitchGenerator      PerCpuThreadSwitchGenerator.h:168-446   CpuThreadSwitchGenerator
+//     consume / getNumRecord* / getLastTimeStamp / getNumEntries         same names
+//   PerCpuThreadSwitchGenerator   :449-489                  PerCpuThreadSwitchGenerator
+//     onCpusThreadSwitchBufferRead :480-484                   onCpuThreadSwitchBufferRead(cpu, slices)
+//     getThreadsInfo()             :476-478                   same (ThreadInfo without /proc strings)
+//   tagstack::Event               tagstack/Event.h:28-56    Event (= hbtgpu_cs_event)
 //
 // Error conventions follow the reference: the hot path returns negative errno in ssize_t
 // (-ENODATA drained, -EPERM bad record / time regression), argument and environment errors
@@ -234,6 +240,144 @@ inline ssize_t CpuCountSampleGenerator::consume(unsigned max_num_records) {
   // everything submitted was walked: the ring is drained, and consume() reports that as
   // -ENODATA instead of the count (quirk at :1574-1588)
   return -ENODATA;
+}
+
+// ---- ContextSwitch mode ---------------------------------------------------------------------
+using Event = hbtgpu_cs_event;  // layout of tagstack::Event
+
+struct ThreadNameChange {  // PerCpuThreadSwitchGenerator.h:24-34
+  TimeStamp tstamp;
+  std::string new_name;
+  bool is_exec;
+};
+struct ThreadInfo {  // :36-47 (cmdline and /proc comm are the caller's lookups)
+  uint32_t vid;
+  pid_t ppid, ptid, pid, tid;
+  TimeStamp fork_timestamp, end_timestamp;
+  std::vector<ThreadNameChange> names;
+};
+
+class PerCpuThreadSwitchGenerator;
+
+class CpuThreadSwitchGenerator {
+ public:
+  ssize_t consume(unsigned max_num_records);
+  uint64_t getNumRecordLost() const { return c_.lost; }
+  uint64_t getNumRecordComm() const { return c_.comm; }
+  uint64_t getNumRecordExit() const { return c_.exit; }
+  uint64_t getNumRecordFork() const { return c_.fork; }
+  uint64_t getNumRecordThrottle() const { return c_.throttle; }
+  uint64_t getNumRecordUnThrottle() const { return c_.unthrottle; }
+  uint64_t getNumRecordSwitchCpuWide() const { return c_.switch_cpu_wide; }
+  TimeStamp getLastTimeStamp() const { return c_.last_tstamp; }
+  size_t getNumEntries() const { return events_.size(); }
+  // the events the reference would have written to its output ring, tags already virtual ids
+  const std::vector<Event>& events() const { return events_; }
+
+ private:
+  friend class PerCpuThreadSwitchGenerator;
+  PerCpuThreadSwitchGenerator* owner_ = nullptr;
+  CpuId cpu_ = 0;
+  hbtgpu_counters c_{};
+  std::vector<Event> events_;
+};
+
+class PerCpuThreadSwitchGenerator {
+ public:
+  PerCpuThreadSwitchGenerator(int num_cpus, uint8_t tid_level, uint64_t arena_bytes = 64ull << 20, int device = 0) {
+    if (num_cpus <= 0) throw std::invalid_argument("num_cpus must be positive");
+    hbtgpu_cs_config cfg{};
+    cfg.device = device;
+    cfg.max_cpus = static_cast<uint32_t>(num_cpus);
+    cfg.tid_level = tid_level;
+    cfg.arena_bytes = arena_bytes;
+    ctx_ = hbtgpu_cs_create(&cfg);
+    if (!ctx_) throw std::runtime_error(hbtgpu_cs_last_error(nullptr));
+    threads_ = hbtgpu_cs_threads_create();
+    gens_.resize(num_cpus);
+    for (int c = 0; c < num_cpus; ++c) {
+      gens_[c].owner_ = this;
+      gens_[c].cpu_ = c;
+    }
+  }
+  ~PerCpuThreadSwitchGenerator() {
+    hbtgpu_cs_threads_destroy(threads_);
+    hbtgpu_cs_destroy(ctx_);
+  }
+  PerCpuThreadSwitchGenerator(const PerCpuThreadSwitchGenerator&) = delete;
+  PerCpuThreadSwitchGenerator& operator=(const PerCpuThreadSwitchGenerator&) = delete;
+
+  CpuThreadSwitchGenerator& getCpuGenerator(CpuId cpu) { return gens_.at(cpu); }
+
+  // what the callback of onCpusThreadSwitchBufferRead(callback, consume=true) hands over
+  void onCpuThreadSwitchBufferRead(CpuId cpu, const RbDataSlices& s) {
+    if (decoded_) {  // a new window: forget the previous images, keep the generators' state
+      check(hbtgpu_cs_reset(ctx_));
+      decoded_ = false;
+    }
+    check(hbtgpu_cs_submit_image(ctx_, static_cast<uint32_t>(cpu), s.first.from, s.first.size));
+    if (s.second) check(hbtgpu_cs_submit_image(ctx_, static_cast<uint32_t>(cpu), s.second->from, s.second->size));
+  }
+
+  std::vector<ThreadInfo> getThreadsInfo() const {
+    const uint64_t nt = hbtgpu_cs_threads_count(threads_), nn = hbtgpu_cs_threads_name_count(threads_);
+    std::vector<hbtgpu_cs_thread> th(nt);
+    std::vector<hbtgpu_cs_name> nm(nn);
+    hbtgpu_cs_threads_get(threads_, th.data(), nt, nm.data(), nn);
+    std::vector<ThreadInfo> out;
+    size_t k = 0;
+    for (const auto& t : th) {
+      ThreadInfo ti{t.vid, t.ppid, t.ptid, t.pid, t.tid, t.fork_ts, t.end_ts, {}};
+      for (uint32_t i = 0; i < t.n_names; ++i, ++k)
+        ti.names.push_back(ThreadNameChange{nm[k].tstamp, std::string(nm[k].name, nm[k].len), nm[k].is_exec != 0});
+      out.push_back(std::move(ti));
+    }
+    return out;
+  }
+
+ private:
+  friend class CpuThreadSwitchGenerator;
+  void check(int rc) {
+    if (rc == -EINVAL) throw std::invalid_argument(hbtgpu_cs_last_error(ctx_));
+    if (rc != 0) throw std::runtime_error(hbtgpu_cs_last_error(ctx_));
+  }
+  // decode the window on the GPU, then run the thread dictionary over the cpus in index order
+  void decode() {
+    if (decoded_) return;
+    check(hbtgpu_cs_run(ctx_));
+    check(hbtgpu_cs_sync(ctx_));
+    std::vector<uint32_t> pids;
+    std::vector<hbtgpu_cs_op> ops;
+    for (auto& g : gens_) {
+      const uint32_t cpu = static_cast<uint32_t>(g.cpu_);
+      uint64_t ne = 0, no = 0;
+      check(hbtgpu_cs_num_events(ctx_, cpu, &ne, &no));
+      g.events_.resize(ne);
+      pids.resize(ne);
+      ops.resize(no);
+      check(hbtgpu_cs_get_events(ctx_, cpu, g.events_.data(), pids.data(), ne, &ne));
+      check(hbtgpu_cs_get_ops(ctx_, cpu, ops.data(), no, &no));
+      if (hbtgpu_cs_assign_vids(threads_, g.events_.data(), pids.data(), ne, ops.data(), no) != 0)
+        throw std::runtime_error("thread records outside the reference's contract (HBT_THROW_ASSERT there)");
+      check(hbtgpu_cs_get_counters(ctx_, cpu, &g.c_));
+      hbtgpu_cs_state st{};
+      check(hbtgpu_cs_get_state(ctx_, cpu, &st));
+      check(hbtgpu_cs_set_state(ctx_, cpu, &st));  // last_tstamp_ / in_write_errors_ carry over
+    }
+    decoded_ = true;
+  }
+
+  hbtgpu_cs_ctx* ctx_ = nullptr;
+  hbtgpu_cs_threads* threads_ = nullptr;
+  std::vector<CpuThreadSwitchGenerator> gens_;
+  bool decoded_ = false;
+};
+
+inline ssize_t CpuThreadSwitchGenerator::consume(unsigned max_num_records) {
+  if (max_num_records == 0) return 0;
+  owner_->decode();
+  if (c_.err < 0) return static_cast<ssize_t>(c_.err);
+  return -ENODATA;  // drained (:1574-1588)
 }
 
 }  // namespace hbtgpu_shim

@@ -124,6 +124,59 @@ int main() {
     threw = true;
   }
   EXPECT(threw);
+  // ---- ContextSwitch mode: the stream of tests/test_cs_oracle.py::test_known_answer_small ----
+  {
+    const uint32_t T = 5000001;
+    std::vector<uint8_t> cs;
+    auto sid = [&](uint32_t pid, uint32_t tid, uint64_t ts) {
+      put(cs, pid | (uint64_t(tid) << 32));
+      put(cs, ts);
+    };
+    auto sw = [&](uint64_t ts, uint32_t tid, uint32_t misc) {
+      put(cs, 15 | (uint64_t(misc) << 32) | (32ull << 48));
+      put(cs, 0);
+      sid(1, tid, ts);
+    };
+    sw(1000, T, (1u << 13) | (1u << 14));  // out, preempted
+    sw(1100, T + 1, 0);                    // in
+    put(cs, hdr(2, 40));                   // LOST
+    put(cs, 7);
+    put(cs, 7);
+    sid(0, 0, 1500);
+    sw(1600, T + 1, 1u << 13);             // out, yield
+    put(cs, hdr(7, 48));                   // FORK
+    put(cs, (T + 8) | (1ull << 32));
+    put(cs, (T + 9) | (1ull << 32));
+    put(cs, 1700);
+    sid(T + 8, T + 9, 1700);
+    put(cs, hdr(4, 48));                   // EXIT
+    put(cs, (T + 8) | (1ull << 32));
+    put(cs, (T + 9) | (1ull << 32));
+    put(cs, 1900);
+    sid(T + 8, T + 9, 1900);
+    sw(2000, 0, 0);                        // idle in
+    PerCpuThreadSwitchGenerator tsg(2, 3);
+    tsg.onCpuThreadSwitchBufferRead(0, RbDataSlices(cs.data(), cs.size()));
+    auto& t0 = tsg.getCpuGenerator(0);
+    ssize_t r = t0.consume(1000);
+    EXPECT(r >= 0 || r == -ENODATA);
+    EXPECT(t0.getNumRecordSwitchCpuWide() == 4 && t0.getNumRecordLost() == 7);
+    EXPECT(t0.getNumRecordFork() == 1 && t0.getNumRecordExit() == 1);
+    EXPECT(t0.getNumEntries() == 8 && t0.getLastTimeStamp() == 2000);
+    const auto& ev = t0.events();
+    EXPECT(ev[0].type == 5 && ev[0].tag == 0xFFFFFFFFu && ev[0].level == 3);   // SwitchOutPreempt
+    EXPECT(ev[1].type == 4 && ev[1].tag == 1);                                  // SwitchIn, vid 1
+    EXPECT(ev[2].type == 7 && ev[2].tstamp == 1101 && ev[2].level == 255);      // WriteErrorsStart
+    EXPECT(ev[3].type == 8 && ev[3].tstamp == 1600);                            // WriteErrorsEnd
+    EXPECT(ev[4].type == 6);                                                    // SwitchOutYield
+    EXPECT(ev[5].type == 2 && ev[5].tag == 2);                                  // ThreadCreation, vid 2
+    EXPECT(ev[6].type == 3 && ev[6].tag == 2);                                  // ThreadDestruction
+    EXPECT(ev[7].type == 4 && ev[7].tag == 0);                                  // tid 0 is never remapped
+    auto info = tsg.getThreadsInfo();
+    EXPECT(info.size() == 2 && info[1].tid == pid_t(T + 9) && info[1].fork_timestamp == 1700 &&
+           info[1].end_timestamp == 1900 && info[0].ppid == -1);
+    EXPECT(tsg.getCpuGenerator(1).getNumEntries() == 0);
+  }
   std::puts("SHIM OK");
   return 0;
 }
