@@ -976,17 +976,20 @@ __host__ __device__ constexpr size_t decode_smem_bytes(uint32_t tile_bytes) {
   return decode_data_off<MODE, PRE>() + 2 * (static_cast<size_t>(tile_bytes) + OV_BYTES);
 }
 
-template <int MODE, int PRE>
+template <int MODE, int PRE, int NEV>
 __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, const uint64_t* buf,
                                                     uint32_t wt, uint32_t entry, TileCtx& tc,
                                                     uint32_t cur, uint32_t& k_all) {
   const Carry& C = s.c[cur];
-  const uint32_t n = P.n_events;
+  // NEV != 0: the kernel is specialised for this group size (the strides, the field map of the
+  // accumulator record and the division by the record size become constants)
+  const uint32_t n = NEV ? static_cast<uint32_t>(NEV) : P.n_events;
   constexpr uint32_t pre = PRE;
   const uint32_t S = 5 + pre + n;  // words per SAMPLE
   const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
   // records whose header lies inside the tile: ceil((wt - entry) / S) by multiply-shift
-  const int Kall = static_cast<int>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
+  const int Kall = NEV ? static_cast<int>((wt - entry + S - 1) / S)
+                       : static_cast<int>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
   k_all = static_cast<uint32_t>(Kall);
   int K = min(Kall, PASS_RECORDS);  // never more by construction of the tile size
   const bool link0 = C.valid != 0 && C.gap == 0;
@@ -1252,7 +1255,7 @@ __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t st
 #ifndef HBT_MINB
 #define HBT_MINB 5
 #endif
-template <bool SPEC, int MODE, int PRE>
+template <bool SPEC, int MODE, int PRE, int NEV = 0>
 __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_MINB) k_decode(const Params P) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
@@ -1277,7 +1280,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
   if (MODE == MODE_AGG && PRE == 2) attr_cache_init();
   __syncthreads();
 
-  uint32_t phase[2] = {0, 0};
+  uint32_t phase_bits = 0;  // parity of the two TMA barriers (a bit each: no local array)
   uint32_t cur = 0;  // which copy of the carry is current
   uint32_t bad = 0;  // fast mode: why this chunk's result is untrustworthy (WHY_*), 0 if fine
 
@@ -1319,8 +1322,8 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
       }
       boff = 1;
       n_issued = 1;
-      mbar_wait(&s.bar[0], phase[0]);
-      phase[0] ^= 1;
+      mbar_wait(&s.bar[0], phase_bits & 1u);
+      phase_bits ^= 1u;
       const uint64_t* hb = data0;
       load_carry<PRE>(s, P, cd.stream, PRED_UNKNOWN, 0);
       entry_abs = chunk_abs;
@@ -1329,7 +1332,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
       // guess like any other -- k_verify proves or refutes it against the previous chunk.
       bool quick = false;
       if (!P.force_general && !(cd.flags & CH_FIRST_OF_IMAGE)) {
-        const uint32_t n = P.n_events, pre = PRE, S = 5 + pre + n;
+        const uint32_t n = NEV ? static_cast<uint32_t>(NEV) : P.n_events, pre = PRE, S = 5 + pre + n;
         const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
         if (threadIdx.x == 0) s.red_key = 0;
         __syncthreads();
@@ -1424,8 +1427,8 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
       if (threadIdx.x == 0) issue(tile_rel + tb, b ^ 1);
       ++n_issued;
     }
-    mbar_wait(&s.bar[b], phase[b]);
-    phase[b] ^= 1;
+    mbar_wait(&s.bar[b], (phase_bits >> b) & 1u);
+    phase_bits ^= 1u << b;
     ++n_waited;
     const uint64_t* buf = b ? data1 : data0;
     const uint32_t wt = min(tb, chunk_len - tile_rel) / 8;
@@ -1445,10 +1448,10 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
       if (!P.force_general && (MODE == MODE_AGG || P.n_events + 2 <= EMIT_MAX_ROW_WORDS)) {
         // runs of configured SAMPLEs in parallel, the few other records in between one by one;
         // a tile with many of those goes to the general path
-        const uint32_t S = 5 + PRE + P.n_events;
+        const uint32_t S = 5 + PRE + (NEV ? static_cast<uint32_t>(NEV) : P.n_events);
         for (int odd = 0;;) {
           uint32_t k_all = 0;
-          const uint32_t k = uniform_segment<MODE, PRE>(s, P, buf, wt, ew, tc, cur, k_all);
+          const uint32_t k = uniform_segment<MODE, PRE, NEV>(s, P, buf, wt, ew, tc, cur, k_all);
           if (k) cur ^= 1;
           ew += k * S;
           if (k == k_all) {  // ran to the end of the tile
@@ -1498,7 +1501,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
     }
   }
   // never exit with a bulk copy still in flight into this CTA's shared memory
-  if (n_waited < n_issued) mbar_wait(&s.bar[(n_waited + boff) & 1], phase[(n_waited + boff) & 1]);
+  if (n_waited < n_issued) mbar_wait(&s.bar[(n_waited + boff) & 1], (phase_bits >> ((n_waited + boff) & 1)) & 1u);
   const uint64_t next_abs = any_work ? chunk_abs + next_rel : entry_abs;
 
   // ---- publish ----
