@@ -706,6 +706,7 @@ struct TileCtx {
   uint32_t stream;
   uint32_t rows_before, recs_before;  // MODE_EMIT: already emitted in this chunk
   uint64_t row_base, rec_base;
+  uint64_t* acc_s;      // MODE_AGG: accumulator records of this stream (computed once per chunk)
 };
 
 // Decode the reachable records of one staged tile and fold them into the carry, the
@@ -1013,10 +1014,12 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
     bk_[g] = BKT_OOR;
     if (jr >= 0 && jr < K) {
       const uint32_t p = entry + jr * S;
-      // misc (bits 32..47) is free; type and size must match, and so must nr
-      if (lane < 31 && ((buf[p] & 0xFFFF0000FFFFFFFFull) != want || buf[p + pre + 2] != n))
-        first_bad = min(first_bad, jr);
+      // misc (bits 32..47) is free; type and size must match, and so must nr (three loads
+      // issued together, one combined test: no short-circuit branches)
+      const uint64_t hd = buf[p], nr = buf[p + pre + 2];
       ts = buf[p + pre + 1];
+      const bool mismatch = ((hd & 0xFFFF0000FFFFFFFFull) != want) | (nr != n);
+      if (lane < 31 && mismatch) first_bad = min(first_bad, jr);
       bk_[g] = bucket_of(P, ts);
     } else if (jr == -1) {
       ts = C.ts;
@@ -1100,7 +1103,9 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   const bool two = F <= 16;
   const uint32_t e0 = two ? (lane & 15) : lane;
   const uint32_t woff0 = pre + (e0 < n ? 5 + e0 : (e0 == n ? 3 : 4));
-  uint64_t* const acc_s = P.acc + static_cast<uint64_t>(tc.stream) * P.n_buckets * F;
+  uint64_t* const acc_s = tc.acc_s;                       // this stream's accumulator records
+  uint64_t* const acc_lane = acc_s + e0;                  // ... and this lane's field in bucket 0
+  const bool lane_tsc = any_tsc && e0 < n && ((P.tsc_mask >> e0) & 1ull);  // field e0 is transformed
 #pragma unroll
   for (int g = 0; g < MAXG; ++g) {
     if (MODE != MODE_AGG) break;
@@ -1145,10 +1150,11 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
               v = e < n ? C.last[e] : (e == n ? C.te : C.tr);  // carry values are already transformed
             } else {
               v = buf[p + woff];
-              if (any_tsc && e < n) v = xform(P, e, v);
+              if (two ? lane_tsc : (any_tsc && e < n)) v = xform(P, e, v);
             }
-            if (pk & 1u) red_add(acc_s + static_cast<uint64_t>(bkA) * F + e, v);
-            if (pk & 2u) red_add(acc_s + static_cast<uint64_t>(bkB) * F + e, 0ull - v);
+            uint64_t* const fa = two ? acc_lane : acc_s + e;
+            if (pk & 1u) red_add(fa + static_cast<uint64_t>(bkA) * F, v);
+            if (pk & 2u) red_add(fa + static_cast<uint64_t>(bkB) * F, 0ull - v);
           }
           if (two || e + 32 >= F) break;
           e += 32;  // n > 13: a lane serves several fields
@@ -1383,7 +1389,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
           bad = WHY_HALO_DEAD;
         } else {
           entry_abs = cd.halo_off + 8ull * s.term_tgt;
-          TileCtx tc{cd.halo_off, 0, cd.stream, 0, 0, 0, 0};
+          TileCtx tc{cd.halo_off, 0, cd.stream, 0, 0, 0, 0, nullptr};
           decode_tile<true, MODE_AGG, PRE>(s, P, hb, K, tc, 0);
           if (s.tile_err != 0xFFFFFFFFu) bad = WHY_HALO_ERR;
           else if (!s.c[0].valid) bad = WHY_HALO_NO_SAMPLE;  // predecessor unknown
@@ -1412,7 +1418,8 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
   // ---- tiles ----  (positions are chunk-relative bytes in 32 bits: a chunk is <= 1 MiB and a
   // record can leave it by at most 64 KiB)
   const uint64_t chunk_end_abs = min(cd.img_base + cd.end, limit_abs);
-  TileCtx tc{0, 0, cd.stream, 0, 0, io.row_base, io.rec_base};
+  TileCtx tc{0, 0, cd.stream, 0, 0, io.row_base, io.rec_base,
+             P.acc + static_cast<uint64_t>(cd.stream) * P.n_buckets * (P.n_events + 3)};
   const bool any_work = entry_abs < chunk_end_abs;  // also false for exact-mode "skip" (~0)
   const uint32_t chunk_len = any_work ? static_cast<uint32_t>(chunk_end_abs - chunk_abs) : 0;
   const uint32_t limit_rel = static_cast<uint32_t>(umin64(limit_abs - chunk_abs, 0xFFFFFFF0ull));
