@@ -253,6 +253,8 @@ Params make_params(hbtgpu_ctx* ctx) {
     P.bucket_magic = static_cast<uint64_t>((static_cast<unsigned __int128>(1) << 64) / ctx->cfg.bucket_ns);
     const uint64_t b = ctx->cfg.bucket_ns;
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
+    P.bucket_f64 = (b < (1ull << 32) && P.range_ns < (1ull << 53)) ? 1u : 0u;
+    P.bucket_inv = 1.0 / static_cast<double>(b);
     P.pre = ctx->cfg.sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ ? 2 : 0;
     P.fix = 40 + 8 * P.pre;
     P.tile_bytes = ctx_tile_bytes(ctx);
@@ -1362,6 +1364,8 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
     P.bucket_magic = static_cast<uint64_t>((static_cast<unsigned __int128>(1) << 64) / cfg->bucket_ns);
     const uint64_t b = cfg->bucket_ns;
     P.bucket_shift = (b & (b - 1)) == 0 ? static_cast<uint32_t>(__builtin_ctzll(b)) : 0xFFFFFFFFu;
+    P.bucket_f64 = (b < (1ull << 32) && P.range_ns < (1ull << 53)) ? 1u : 0u;
+    P.bucket_inv = 1.0 / static_cast<double>(b);
     P.pre = cfg->sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ ? 2 : 0;
     P.fix = 40 + 8 * P.pre;
     P.tile_bytes = tile;

@@ -418,3 +418,38 @@ def test_argument_errors():
             g.submit_image(0, np.zeros(12, np.uint8))
         with pytest.raises(hbtgpu.HbtGpuError):
             g.counters(0)  # run() not called
+
+
+@pytest.mark.parametrize("bucket_ns,t0,span", [
+    (1_000_000, 1_000_000_000, 1),            # f64-assisted division (bucket_ns < 2^32, range < 2^53)
+    (999_983, 7, 1),                          # prime width
+    (3, 0, 1),                                # tiny buckets
+    ((1 << 32) - 5, 12345, 1 << 20),          # widest 32-bit width
+    (1 << 20, 1 << 40, 1),                    # power of two: shift
+    ((1 << 32) + 7, 99, 1 << 21),             # width >= 2^32: 64-bit multiply-high
+    (1_000_003, (1 << 52) + 11, 1),           # t0 so large that range_ns >= 2^53 is not the issue, ts is
+])
+def test_bucket_boundaries(port_oracle, bucket_ns, t0, span):
+    """Samples placed on, one before and one after bucket boundaries land in the bucket the
+    integer division says (A7: bucket = (ts - t0) / bucket_ns), for every division path."""
+    n, nb = 2, 5000
+    r = rg.SplitMix64(bucket_ns ^ t0)
+    ts_list = []
+    for _ in range(1500):
+        b = r.uniform(0, nb + 20)             # some beyond the range
+        ts_list += [t0 + b * bucket_ns + off for off in (-1, 0, 1) if t0 + b * bucket_ns + off > 0]
+        ts_list.append(t0 + r.uniform(0, nb * bucket_ns))
+    ts_list = sorted(set(ts_list))
+    out = bytearray()
+    v = [0, 0]
+    for i, ts in enumerate(ts_list):
+        v = [v[0] + 3, v[1] + (i % 7)]
+        out += rg.sample(ts, 10 * i, 10 * i, v)
+    data = rg.to_u8(out)
+    p = po.make_params(n, n_buckets=nb, t0=t0, bucket_ns=bucket_ns)
+    carries = [po.make_carry(valid=True, tstamp=ts_list[0] - 1 if ts_list[0] else 0, last=[0, 0])]
+    got, _ = gpu_decode(p, [data], carries)
+    exp = port_oracle.decode_stream(p, data, carries[0])
+    exp["scaled"] = port_oracle.scale_buckets(p, exp["buckets"])
+    assert_matches_oracle(got[0], exp, n, f"bucket_ns={bucket_ns}")
+    assert exp["counters"]["rows_out_of_range"] > 0
