@@ -224,12 +224,27 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   } while (!ok);
 }
 // TMA 1-D bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP).
+// The images are read exactly once, so their lines are marked evict-first in L2: what stays
+// resident instead are the accumulator records the REDs update (zeroed just before by the
+// memset), which saves their fetch from and a second write-back to DRAM.
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
 __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes,
                                             uint64_t* bar) {
+#ifdef HBT_NO_L2_HINT
   asm volatile(
       "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
       ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
+#else
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+      ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(l2_evict_first_policy())
+      : "memory");
+#endif
 }
 
 // PerfEventsGroup::kernelTimeFromTsc, PerfEventsGroup.h:1645-1658
