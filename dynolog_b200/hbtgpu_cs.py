@@ -26,6 +26,9 @@ ABI_SYMBOLS = [
     "hbtgpu_cs_get_ops", "hbtgpu_cs_events_device", "hbtgpu_cs_get_stats",
     "hbtgpu_cs_threads_create", "hbtgpu_cs_threads_destroy", "hbtgpu_cs_assign_vids",
     "hbtgpu_cs_threads_count", "hbtgpu_cs_threads_name_count", "hbtgpu_cs_threads_get",
+    "hbtgpu_cs_vids_create", "hbtgpu_cs_vids_destroy", "hbtgpu_cs_vids_last_error",
+    "hbtgpu_cs_assign_vids_device", "hbtgpu_cs_vids_count", "hbtgpu_cs_vids_name_count",
+    "hbtgpu_cs_vids_last_ms", "hbtgpu_cs_vids_get",
 ]
 
 
@@ -64,6 +67,17 @@ def _lib():
         L.hbtgpu_cs_threads_count.argtypes = [C.c_void_p]
         L.hbtgpu_cs_threads_name_count.restype = C.c_uint64
         L.hbtgpu_cs_threads_name_count.argtypes = [C.c_void_p]
+        L.hbtgpu_cs_vids_create.restype = C.c_void_p
+        L.hbtgpu_cs_vids_destroy.restype = None
+        L.hbtgpu_cs_vids_destroy.argtypes = [C.c_void_p]
+        L.hbtgpu_cs_vids_last_error.restype = C.c_char_p
+        L.hbtgpu_cs_vids_last_error.argtypes = [C.c_void_p]
+        L.hbtgpu_cs_vids_count.restype = C.c_uint64
+        L.hbtgpu_cs_vids_count.argtypes = [C.c_void_p]
+        L.hbtgpu_cs_vids_name_count.restype = C.c_uint64
+        L.hbtgpu_cs_vids_name_count.argtypes = [C.c_void_p]
+        L.hbtgpu_cs_vids_last_ms.restype = C.c_float
+        L.hbtgpu_cs_vids_last_ms.argtypes = [C.c_void_p]
         _ready = True
     return L
 
@@ -180,14 +194,58 @@ class Threads:
         rc = self.L.hbtgpu_cs_threads_get(C.c_void_p(self.h), C.c_void_p(th.ctypes.data), C.c_uint64(nt),
                                           C.c_void_p(nm.ctypes.data), C.c_uint64(nn))
         assert rc == 0
-        threads = [tuple(int(x) for x in (t["vid"], t["ppid"], t["ptid"], t["pid"], t["tid"], t["n_names"],
-                                          t["fork_ts"], t["end_ts"])) for t in th[:nt]]
-        names = sorted((int(n["vid"]), int(n["tstamp"]), bytes(n["name"])[:int(n["len"])], int(n["is_exec"]))
-                       for n in nm[:nn])
-        return threads, names
+        return _table(th, nm, nt, nn)
 
 
-def decode(streams, tid_level=1, states=None, flags=0, ctx=None):
+def _table(th, nm, nt, nn):
+    threads = [tuple(int(x) for x in (t["vid"], t["ppid"], t["ptid"], t["pid"], t["tid"], t["n_names"],
+                                      t["fork_ts"], t["end_ts"])) for t in th[:nt]]
+    names = sorted((int(n["vid"]), int(n["tstamp"]), bytes(n["name"])[:int(n["len"])], int(n["is_exec"]))
+                   for n in nm[:nn])
+    return threads, names
+
+
+class DeviceThreads:
+    """The thread dictionary kept on the GPU (hbtgpu_cs_vids): assign() rewrites the tags of a
+    whole decoded window on the device."""
+
+    def __init__(self, device=0):
+        self.L = _lib()
+        self.h = self.L.hbtgpu_cs_vids_create(C.c_int(device))
+        if not self.h:
+            raise HbtGpuError(-5, "hbtgpu_cs_vids_create failed (no CUDA device?)")
+
+    def close(self):
+        if self.h:
+            self.L.hbtgpu_cs_vids_destroy(C.c_void_p(self.h))
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def assign(self, ctx):
+        rc = self.L.hbtgpu_cs_assign_vids_device(C.c_void_p(ctx.h), C.c_void_p(self.h))
+        if rc != 0:
+            raise HbtGpuError(rc, self.L.hbtgpu_cs_vids_last_error(C.c_void_p(self.h)).decode())
+
+    def last_ms(self):
+        return float(self.L.hbtgpu_cs_vids_last_ms(C.c_void_p(self.h)))
+
+    def count(self):
+        return int(self.L.hbtgpu_cs_vids_count(C.c_void_p(self.h)))
+
+    def table(self):
+        nt = self.count()
+        nn = int(self.L.hbtgpu_cs_vids_name_count(C.c_void_p(self.h)))
+        th = np.zeros(max(nt, 1), THREAD_DTYPE)
+        nm = np.zeros(max(nn, 1), NAME_DTYPE)
+        rc = self.L.hbtgpu_cs_vids_get(C.c_void_p(self.h), C.c_void_p(th.ctypes.data), C.c_uint64(nt),
+                                       C.c_void_p(nm.ctypes.data), C.c_uint64(nn))
+        assert rc == 0
+        return _table(th, nm, nt, nn)
+
+
+def decode(streams, tid_level=1, states=None, flags=0, ctx=None, device_dictionary=False):
     """Decode per-CPU ContextSwitch-mode streams on the GPU and map tids to virtual ids on the
     host, cpus in index order.  Returns dict(events, counters, states, threads, names, stats)."""
     ns = len(streams)
@@ -203,12 +261,15 @@ def decode(streams, tid_level=1, states=None, flags=0, ctx=None):
             ctx.submit(cpu, s)
         ctx.run()
         ctx.sync()
-        th = Threads()
+        th = DeviceThreads() if device_dictionary else Threads()
+        if device_dictionary:
+            th.assign(ctx)
         out = {"events": [], "counters": [], "states": [], "stats": ctx.stats()}
         for cpu in range(ns):
             ev, pid = ctx.events(cpu)
             ev = ev.copy()
-            th.assign(ev, pid, ctx.ops(cpu))
+            if not device_dictionary:
+                th.assign(ev, pid, ctx.ops(cpu))
             out["events"].append(ev)
             out["counters"].append(ctx.counters(cpu))
             out["states"].append(ctx.state(cpu))

@@ -491,6 +491,25 @@ uint64_t hbtgpu_cs_threads_name_count(const hbtgpu_cs_threads* t);
 int hbtgpu_cs_threads_get(const hbtgpu_cs_threads* t, hbtgpu_cs_thread* threads, uint64_t thread_cap,
                           hbtgpu_cs_name* names, uint64_t name_cap);
 
+/* The same dictionary on the GPU (for windows whose events should not make the round trip
+ * through one host thread first): after hbtgpu_cs_run, rewrites the tags of ALL cpus of the
+ * window from tid to virtual id in place on the device, cpus in index order, and keeps the
+ * dictionary (active tids, thread table) on the device between windows.  Same results as
+ * feeding hbtgpu_cs_assign_vids cpu by cpu.  -EINVAL for COMM/EXIT/FORK of tid 0 and for a FORK
+ * of an already forked active tid; the reference's time-order assertions (:125-131,262-265) are
+ * not checked here. */
+typedef struct hbtgpu_cs_vids hbtgpu_cs_vids;
+hbtgpu_cs_vids* hbtgpu_cs_vids_create(int device);
+void hbtgpu_cs_vids_destroy(hbtgpu_cs_vids* v);
+const char* hbtgpu_cs_vids_last_error(hbtgpu_cs_vids* v);
+int hbtgpu_cs_assign_vids_device(hbtgpu_cs_ctx* ctx, hbtgpu_cs_vids* v);
+uint64_t hbtgpu_cs_vids_count(const hbtgpu_cs_vids* v);
+uint64_t hbtgpu_cs_vids_name_count(const hbtgpu_cs_vids* v);
+float hbtgpu_cs_vids_last_ms(const hbtgpu_cs_vids* v);   /* device time of the last call */
+/* thread table and names as hbtgpu_cs_threads_get returns them */
+int hbtgpu_cs_vids_get(hbtgpu_cs_vids* v, hbtgpu_cs_thread* threads, uint64_t thread_cap,
+                       hbtgpu_cs_name* names, uint64_t name_cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -154,3 +154,76 @@ def test_many_small_images_per_cpu():
         assert ctx.state(cpu) == want["states"][cpu]
     assert th.table() == (want["threads"], want["names"])
     ctx.close()
+
+
+# ---- the thread dictionary on the GPU (hbtgpu_cs_assign_vids_device) -----------------------------
+@pytest.mark.parametrize("seed,kw", [
+    (1, dict()),
+    (2, dict(p_lost=0.01)),
+    (3, dict(p_life=0.05, p_comm=0.03)),
+    (4, dict(p_lost=0.005, p_life=0.05, p_comm=0.03, p_throttle=0.01, p_other=0.02)),
+    (5, dict(p_lost=0.2, p_life=0.1)),
+    (6, dict(p_life=0.3, p_comm=0.3)),
+])
+def test_device_dictionary_matches_reference_order(seed, kw):
+    streams = rg.random_cs_streams(seed, 4, 6000, n_tids=48, **kw)
+    want = pyoracle.cs_run("port", streams, tid_level=2)
+    got = hbtgpu_cs.decode(streams, tid_level=2, device_dictionary=True)
+    for cpu in range(len(streams)):
+        for f in ("tstamp", "type", "level", "comp_unit_id", "tag"):
+            assert np.array_equal(got["events"][cpu][f], want["events"][cpu][f]), (cpu, f)
+    assert got["threads"] == want["threads"]
+    assert got["names"] == want["names"]
+
+
+def test_device_dictionary_carries_over_windows():
+    """Windows decoded one after the other: the device dictionary keeps the active tids and the
+    thread table, so the result equals the host mirror fed the same windows in the same order."""
+    streams = rg.random_cs_streams(77, 3, 5000, n_tids=40, p_lost=0.002, p_life=0.04, p_comm=0.03)
+    cuts = []
+    for s in streams:
+        pos, target = 0, (len(s) // 3)
+        marks = []
+        while pos < len(s):
+            if len(marks) < 2 and pos >= target * (len(marks) + 1):
+                marks.append(pos)
+            pos += int(s[pos + 6]) | int(s[pos + 7]) << 8
+        cuts.append([0] + marks + [len(s)])
+    ctx = hbtgpu_cs.CsContext(3, sum(len(s) for s in streams) + (1 << 16), tid_level=1)
+    ctx2 = hbtgpu_cs.CsContext(3, sum(len(s) for s in streams) + (1 << 16), tid_level=1)
+    dev, host = hbtgpu_cs.DeviceThreads(), hbtgpu_cs.Threads()
+    for w in range(3):
+        for c in (ctx, ctx2):
+            c.reset()
+            for cpu, s in enumerate(streams):
+                if w:
+                    c.set_state(cpu, *states[cpu])
+                c.submit(cpu, s[cuts[cpu][w]:cuts[cpu][w + 1]])
+            c.run()
+            c.sync()
+        states = [ctx.state(cpu) for cpu in range(3)]
+        dev.assign(ctx)
+        for cpu in range(3):
+            ev_h, pid = ctx2.events(cpu)
+            ev_h = ev_h.copy()
+            host.assign(ev_h, pid, ctx2.ops(cpu))
+            ev_d, _ = ctx.events(cpu)
+            for f in ("tstamp", "type", "tag"):
+                assert np.array_equal(ev_d[f], ev_h[f]), (w, cpu, f)
+    assert dev.table() == host.table()
+    with pytest.raises(hbtgpu.HbtGpuError):
+        dev.assign(ctx)     # the window's tags are virtual ids already
+    ctx.close()
+    ctx2.close()
+
+
+def test_device_dictionary_rejects_out_of_contract_records():
+    T = 5_000_001
+    s = rg.to_u8(rg.cs_switch(1000, 1, T) + rg.cs_fork(T, 1, T + 5, 1, 1100) + rg.cs_fork(T, 1, T + 5, 1, 1200))
+    ctx = hbtgpu_cs.CsContext(1, 1 << 16)
+    ctx.submit(0, s)
+    ctx.run()
+    ctx.sync()
+    with pytest.raises(hbtgpu.HbtGpuError):
+        hbtgpu_cs.DeviceThreads().assign(ctx)
+    ctx.close()
