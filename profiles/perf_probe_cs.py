@@ -39,6 +39,12 @@ def probe(name, ncpu, bytes_per_cpu, flags=0, host=False, **kw):
         print(f"{'':34s} host: D2H of events+pids+ops (pageable) {t1-t0:.3f} s; thread dictionary (hbtgpu_cs_assign_vids, 1 thread) "
               f"{t2-t1:.3f} s = {nev/1e6/(t2-t1):.0f} M events/s, {th.L.hbtgpu_cs_threads_count(__import__("ctypes").c_void_p(th.h))} vids")
         th.close()
+        dev = hbtgpu_cs.DeviceThreads()
+        g.run(); g.sync()
+        dev.assign(g)
+        print(f"{'':34s} device: thread dictionary (hbtgpu_cs_assign_vids_device) {dev.last_ms():.2f} ms = "
+              f"{nev/1e3/dev.last_ms():.0f} M events/s, {dev.count()} vids")
+        dev.close()
     g.close()
 
 if __name__ == "__main__":
