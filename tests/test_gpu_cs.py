@@ -227,3 +227,41 @@ def test_device_dictionary_rejects_out_of_contract_records():
     with pytest.raises(hbtgpu.HbtGpuError):
         hbtgpu_cs.DeviceThreads().assign(ctx)
     ctx.close()
+
+
+def test_garbage_and_hostile_payloads():
+    """Random bytes, a valid stream that turns into noise, and COMM names / pid fields made of
+    bytes that look like record headers: the walk stops where the restatement stops (or never
+    leaves the chain), nothing hangs, nothing is decoded behind an error."""
+    r = np.random.default_rng(5)
+    good = rg.random_cs_streams(51, 1, 2500, p_life=0.02, p_comm=0.02)[0]
+    noise = r.integers(0, 256, 40000, dtype=np.uint8)
+    noise = noise[: len(noise) // 8 * 8]
+    sw32 = rg.header(rg.SWITCH_CPU_WIDE, 32)                       # 8 bytes that are a SWITCH header
+    hostile = bytearray()
+    ts = 1_000_000_000
+    for i in range(3000):
+        ts += 1000
+        if i % 3 == 0:   # comm field = two fake headers; pid/tid words = fake header halves
+            hostile += rg.header(rg.COMM, 48) + sw32 + sw32 + sw32 + rg.sample_id(15, 0x00200000, ts)
+        else:            # next_prev_pid/tid and sample_id words that read as type 15 / size 32
+            hostile += rg.header(rg.SWITCH_CPU_WIDE, 32, rg.MISC_SWITCH_OUT if i % 2 else 0) \
+                + bytes(sw32) + rg.sample_id(15, 0x00200000, ts)
+    streams = [noise, np.concatenate([good, noise[:8000]]), rg.to_u8(hostile), good]
+    want = pyoracle.cs_run("port", streams)
+    for flags in (0, hbtgpu.F_FORCE_EXACT):
+        ctx = hbtgpu_cs.CsContext(len(streams), sum(len(s) for s in streams) + (1 << 16), flags=flags)
+        for cpu, s in enumerate(streams):
+            ctx.submit(cpu, s)
+        ctx.run()
+        ctx.sync()
+        for cpu in range(len(streams)):
+            c = ctx.counters(cpu)
+            for k in CMP_COUNTERS:
+                assert c[k] == want["counters"][cpu][k], (flags, cpu, k, c, want["counters"][cpu])
+            ev, _ = ctx.events(cpu)
+            assert len(ev) == len(want["events"][cpu])
+            for f in ("tstamp", "type"):
+                assert np.array_equal(ev[f], want["events"][cpu][f]), (flags, cpu, f)
+            assert ctx.state(cpu) == want["states"][cpu]
+        ctx.close()
