@@ -47,7 +47,55 @@ def probe(name, ncpu, bytes_per_cpu, flags=0, host=False, **kw):
         dev.close()
     g.close()
 
+def e2e(ncpu, bytes_per_cpu, ref_cpus=4):
+    """Host images in, events with virtual ids out (pinned host memory both ways), against the
+    reference's own code on a bounded sample (it is single-threaded by design: one shared
+    PerThreadStats)."""
+    import time
+    import torch
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from oracle import pyoracle
+    cap = (bytes_per_cpu + 127) // 128 * 128
+    pin_in = torch.empty(ncpu * cap, dtype=torch.uint8, pin_memory=True).numpy()
+    streams = synth.cs_capture(ncpu, bytes_per_cpu, out=pin_in)
+    total = sum(len(s) for s in streams)
+    g = hbtgpu_cs.CsContext(ncpu, total + 256 * ncpu + (1 << 20))
+    # at most one event per 20 bytes of input (a 40-byte LOST writes two)
+    ev_out = torch.empty((total // 20 + 64) * 16, dtype=torch.uint8, pin_memory=True).numpy().view(hbtgpu_cs.EVENT_DTYPE)
+    import ctypes as C
+    best = None
+    for it in range(3):
+        dev = hbtgpu_cs.DeviceThreads()
+        t0 = time.time()
+        g.reset()
+        for cpu, s in enumerate(streams):
+            g.submit(cpu, s)
+        g.run()
+        dev.assign(g)
+        off = 0
+        for cpu in range(ncpu):
+            n, _ = g.num_events(cpu)
+            got = C.c_uint64(0)
+            g._ck(g.L.hbtgpu_cs_get_events(C.c_void_p(g.h), C.c_uint32(cpu), C.c_void_p(ev_out[off:].ctypes.data),
+                                           None, C.c_uint64(n), C.byref(got)))
+            off += n
+        dt = time.time() - t0
+        best = dt if best is None else min(best, dt)
+        dev.close()
+    nrec = sum(g.counters(i)["num_records"] for i in range(ncpu))
+    t0 = time.time()
+    ref = pyoracle.cs_run("reference_nolog" if pyoracle.available("reference_nolog") else "port", streams[:ref_cpus], batch=1024)
+    tr = time.time() - t0
+    nref = sum(c["num_records"] for c in ref["counters"])
+    print(f"e2e {ncpu} cpus x {bytes_per_cpu >> 20} MiB: H2D {total/1e9:.2f} GB + decode + GPU dictionary + D2H {off*16/1e9:.2f} GB of events: "
+          f"{best*1e3:.1f} ms = {nrec/1e6/best:.0f} M records/s;  reference code ({ref_cpus} cpus, {nref/1e6:.1f} M records, 1 thread): "
+          f"{tr:.2f} s = {nref/1e6/tr:.2f} M records/s")
+    g.close()
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "e2e":
+        e2e(192, 10 << 20)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "one":   # for ncu
         probe("192 cpus x 10 MiB", 192, 10 << 20)
         sys.exit(0)
