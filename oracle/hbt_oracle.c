@@ -351,3 +351,54 @@ double hbtoracle_run_capture(const hbtref_params* p, uint32_t n_streams,
   free(th);
   return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
 }
+
+/* ---- series reductions (sink side) ---------------------------------
+ * Restates facebook::dynolog::MetricSeries<uint64_t> (dynolog/src/metric_frame/MetricSeries.h):
+ *   avg<R>      std::accumulate(begin, end, R{0}) / (end - begin)   :207-213 (difference is int)
+ *   percentile  nth_element at lround(percentage * (size - 1)), float arithmetic   :215-226
+ *   diff        *(end - 1) - *begin                                                 :228-234
+ *   rate<R>     integral: value * (period / duration) or value / (duration / period);
+ *               floating: R(value) * double(period in us) / (duration in us)        :246-263
+ * Pinned against the real class by tests/test_series_oracle.py. */
+#include <math.h>
+#include <stdlib.h>
+
+#include "hbtseries_api.h"
+
+static int cmp_u64(const void* a, const void* b) {
+  const uint64_t x = *(const uint64_t*)a, y = *(const uint64_t*)b;
+  return x < y ? -1 : x > y;
+}
+
+int hbtoracle_series_reduce(const uint64_t* series, uint64_t n_series, uint64_t len, float percentage,
+    int64_t period_ns, int64_t duration_ns, double* avg_f64, uint64_t* avg_u64, uint64_t* percentile,
+    uint64_t* diff, double* rate_f64, uint64_t* rate_u64) {
+  if (len == 0 || percentage < 0.f || percentage > 1.f || period_ns <= 0 || duration_ns <= 0) return -1;
+  uint64_t* copy = percentile ? (uint64_t*)malloc(len * sizeof(uint64_t)) : NULL;
+  const int count = (int)len;
+  for (uint64_t s = 0; s < n_series; ++s) {
+    const uint64_t* v = series + s * len;
+    double accd = 0.0;
+    uint64_t accu = 0;
+    for (uint64_t i = 0; i < len; ++i) {
+      accd = accd + (double)v[i];
+      accu += v[i];
+    }
+    if (avg_f64) avg_f64[s] = accd / count;
+    if (avg_u64) avg_u64[s] = accu / (uint64_t)count;
+    if (percentile) {
+      memcpy(copy, v, len * sizeof(uint64_t));
+      qsort(copy, len, sizeof(uint64_t), cmp_u64);
+      const long nth = lroundf(percentage * (float)(len - 1));
+      percentile[s] = copy[nth];
+    }
+    const uint64_t d = v[len - 1] - v[0];
+    if (diff) diff[s] = d;
+    if (rate_f64) rate_f64[s] = (double)d * (double)(period_ns / 1000) / (double)(duration_ns / 1000);
+    if (rate_u64)
+      rate_u64[s] = period_ns > duration_ns ? d * (uint64_t)(period_ns / duration_ns)
+                                            : d / (uint64_t)(duration_ns / period_ns);
+  }
+  free(copy);
+  return 0;
+}

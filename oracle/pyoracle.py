@@ -296,6 +296,27 @@ def cs_run(kind, streams, tid_level=1, batch=256, states=None):
     }
 
 
+# --- series reductions (oracle/hbtseries_api.h) ---------------------------------------------------
+def series_reduce(kind, series, percentage, period_ns, duration_ns):
+    """series: [n_series, len] u64.  Returns dict of per-series arrays (MetricSeries<uint64_t>:
+    avg<double>, avg<uint64_t>, percentile, diff, rate<double>, rate<uint64_t>)."""
+    o = load(kind)
+    f = getattr(o.lib, o.prefix + "_series_reduce")
+    f.restype = C.c_int
+    series = np.ascontiguousarray(series, dtype=np.uint64)
+    ns, ln = series.shape
+    out = {"avg_f64": np.zeros(ns, np.float64), "avg_u64": np.zeros(ns, np.uint64),
+           "percentile": np.zeros(ns, np.uint64), "diff": np.zeros(ns, np.uint64),
+           "rate_f64": np.zeros(ns, np.float64), "rate_u64": np.zeros(ns, np.uint64)}
+    rc = f(_p(series, C.c_uint64), C.c_uint64(ns), C.c_uint64(ln), C.c_float(percentage),
+           C.c_int64(period_ns), C.c_int64(duration_ns), _p(out["avg_f64"], C.c_double),
+           _p(out["avg_u64"], C.c_uint64), _p(out["percentile"], C.c_uint64), _p(out["diff"], C.c_uint64),
+           _p(out["rate_f64"], C.c_double), _p(out["rate_u64"], C.c_uint64))
+    if rc != 0:
+        raise ValueError("series_reduce: bad arguments")
+    return out
+
+
 _PATHS = {
     "reference": (os.path.join(HERE, "_ref", "libhbtref.so"), "hbtref"),
     "reference_nolog": (os.path.join(HERE, "_ref", "libhbtref_nolog.so"), "hbtref"),

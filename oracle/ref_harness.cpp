@@ -567,3 +567,31 @@ extern "C" int hbtref_cs_run(uint32_t n_streams, const uint8_t* const* bytes, co
   silence_end();
   return 0;
 }
+
+// =====================================================================================
+// Series reductions (sink side): the real
+// facebook::dynolog::MetricSeries<uint64_t> (dynolog/src/metric_frame/MetricSeries.h).
+// Glue: filling the series with addSample, mapping the template arguments.
+#include <string>
+
+#include "dynolog/src/metric_frame/MetricSeries.h"
+#include "hbtseries_api.h"
+
+extern "C" int hbtref_series_reduce(const uint64_t* series, uint64_t n_series, uint64_t len,
+    float percentage, int64_t period_ns, int64_t duration_ns, double* avg_f64, uint64_t* avg_u64,
+    uint64_t* percentile, uint64_t* diff, double* rate_f64, uint64_t* rate_u64) {
+  using facebook::dynolog::MetricSeries;
+  if (len == 0 || percentage < 0.f || percentage > 1.f || period_ns <= 0 || duration_ns <= 0) return -1;
+  const std::chrono::steady_clock::duration period{period_ns}, duration{duration_ns};
+  for (uint64_t s = 0; s < n_series; ++s) {
+    MetricSeries<uint64_t> ms(len, "series", "");
+    for (uint64_t i = 0; i < len; ++i) ms.addSample(series[s * len + i]);
+    if (avg_f64) avg_f64[s] = ms.avg<double>();
+    if (avg_u64) avg_u64[s] = ms.avg<uint64_t>();
+    if (percentile) percentile[s] = ms.percentile(percentage);
+    if (diff) diff[s] = ms.diff();
+    if (rate_f64) rate_f64[s] = ms.rate<double>(period, duration);
+    if (rate_u64) rate_u64[s] = ms.rate<uint64_t>(period, duration);
+  }
+  return 0;
+}
