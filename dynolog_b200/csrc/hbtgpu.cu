@@ -69,6 +69,8 @@ struct hbtgpu_ctx {
   size_t cap_rows = 0, cap_recs = 0;
   void* d_math = nullptr;
   size_t cap_math = 0;
+  uint64_t* d_series = nullptr;  // hbtgpu_series_reduce results
+  size_t cap_series = 0;
 
   // host bookkeeping
   std::vector<hbtgpu_carry> carry_in;
@@ -540,7 +542,7 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
                   ctx->d_acc, ctx->d_scaled, ctx->d_metric, ctx->d_valid, ctx->d_flags,
                   ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
                   ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_tid_keys,
-                  ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special};
+                  ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special, ctx->d_series};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
@@ -1416,4 +1418,5 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
 
 }  // extern "C"
 
+#include "hbtgpu_series.inc"
 #include "hbtgpu_cs_host.inc"

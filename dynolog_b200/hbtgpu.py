@@ -96,7 +96,7 @@ ABI_SYMBOLS = [
     "hbtgpu_math_get_count", "hbtgpu_math_rate", "hbtgpu_math_add_reduce",
     "hbtgpu_math_tsc_to_ktime", "hbtgpu_math_ktime_to_tsc", "hbtgpu_math_per_second_mega",
     "hbtgpu_math_running_ratio", "hbtgpu_get_stats", "hbtgpu_version",
-    "hbtgpu_decode_image_noalloc", "hbtgpu_noalloc_last_error",
+    "hbtgpu_decode_image_noalloc", "hbtgpu_noalloc_last_error", "hbtgpu_series_reduce",
 ]
 
 NOALLOC_MAX_IMAGE_BYTES = 64 << 20
@@ -322,6 +322,20 @@ class Context:
         self._ck(self.L.hbtgpu_get_buckets_host(self.h, _ptr(acc), _ptr(scaled), _ptr(metric),
                                                 _ptr(valid)))
         return {"acc": acc, "scaled": scaled, "metric": metric, "valid": valid}
+
+    def series_reduce(self, percentage, period_ns, duration_ns, first_bucket=0, count=None):
+        """MetricSeries reductions of every (cpu, event) series of scaled counts over the buckets
+        [first_bucket, first_bucket + count).  Returns dict of [max_cpus, n_events] arrays."""
+        count = self.n_buckets - first_bucket if count is None else count
+        s = (self.max_cpus, self.n_events)
+        out = {"avg_f64": np.zeros(s, np.float64), "avg_u64": np.zeros(s, np.uint64),
+               "percentile": np.zeros(s, np.uint64), "diff": np.zeros(s, np.uint64),
+               "rate_f64": np.zeros(s, np.float64), "rate_u64": np.zeros(s, np.uint64)}
+        self._ck(self.L.hbtgpu_series_reduce(self.h, C.c_uint32(first_bucket), C.c_uint32(count),
+                                             C.c_float(percentage), C.c_int64(period_ns), C.c_int64(duration_ns),
+                                             _ptr(out["avg_f64"]), _ptr(out["avg_u64"]), _ptr(out["percentile"]),
+                                             _ptr(out["diff"]), _ptr(out["rate_f64"]), _ptr(out["rate_u64"])))
+        return out
 
     def bucket_view(self):
         v = BucketView()

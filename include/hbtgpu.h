@@ -369,6 +369,19 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
 /* Message of the last failed hbtgpu_decode_image_noalloc on this thread. */
 const char* hbtgpu_noalloc_last_error(void);
 
+/* ---- series reductions over the buckets (the sink side) --------------
+ * dynolog keeps every logged metric in a facebook::dynolog::MetricSeries<T> and reduces it
+ * before handing it to a Logger (dynolog/src/metric_frame/MetricSeries.h): avg<R> :207-213,
+ * percentile :215-226, diff :228-234, rate<R> :198-205,246-263.  Here the series of (cpu, event)
+ * is scaled[cpu][first_bucket .. first_bucket + count)[event] of the last hbtgpu_run (T =
+ * uint64_t), reduced on the GPU with the reference's arithmetic (the f64 mean adds left to
+ * right).  Outputs are host arrays [max_cpus][n_events]; any may be NULL.
+ * period_ns / duration_ns: std::chrono::steady_clock::duration ticks of rate().
+ * -EINVAL for percentage outside [0, 1] (the reference would index past the end). */
+int hbtgpu_series_reduce(hbtgpu_ctx* ctx, uint32_t first_bucket, uint32_t count, float percentage,
+                         int64_t period_ns, int64_t duration_ns, double* avg_f64, uint64_t* avg_u64,
+                         uint64_t* percentile, uint64_t* diff, double* rate_f64, uint64_t* rate_u64);
+
 /* ---- ContextSwitch-mode decode -------------------------------------
  *
  * Replaces, for captured ring images of hbt's ContextSwitch mode (sample_type TIME|TID with

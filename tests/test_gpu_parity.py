@@ -453,3 +453,29 @@ def test_bucket_boundaries(port_oracle, bucket_ns, t0, span):
     exp["scaled"] = port_oracle.scale_buckets(p, exp["buckets"])
     assert_matches_oracle(got[0], exp, n, f"bucket_ns={bucket_ns}")
     assert exp["counters"]["rows_out_of_range"] > 0
+
+
+@pytest.mark.parametrize("pct,period,duration,first,count", [
+    (0.5, 1_000_000_000, 10_000_000_000, 0, None), (0.95, 60_000_000_000, 1_000_000_000, 0, None),
+    (0.0, 1_000_000, 1_000_000, 7, 100), (1.0, 3_000_000, 7_000_000, 300, 1), (0.333, 1_500_000_000, 999_999_000, 1, 399)])
+def test_series_reductions(port_oracle, pct, period, duration, first, count):
+    """MetricSeries<uint64_t> avg / percentile / diff / rate of every (cpu, event) series of scaled
+    counts, bit-exact (f64 included) against the C restatement of the reference class."""
+    n, nb = 8, 400
+    streams = [rg.random_stream(60 + i, 6000, n, mux=(i % 2 == 0), big_values=(i == 2))[0] for i in range(3)]
+    with hbtgpu.Context(n_events=n, max_cpus=3, n_buckets=nb, t0=1_000_000_000, bucket_ns=1_500_000,
+                        arena_bytes=sum(len(s) for s in streams) + (1 << 16)) as g:
+        for cpu, s in enumerate(streams):
+            g.submit_image(cpu, s)
+        g.run()
+        g.sync()
+        scaled = g.buckets(want_acc=False, want_metric=False, want_valid=False)["scaled"]
+        got = g.series_reduce(pct, period, duration, first_bucket=first, count=count)
+        with pytest.raises(hbtgpu.HbtGpuError):
+            g.series_reduce(1.5, period, duration)
+    cnt = nb - first if count is None else count
+    series = np.ascontiguousarray(scaled[:, first:first + cnt, :].transpose(0, 2, 1)).reshape(3 * n, cnt)
+    assert series.any()
+    exp = po.series_reduce("port", series, pct, period, duration)
+    for k, v in exp.items():
+        assert np.array_equal(got[k].reshape(-1).view(np.uint64), v.view(np.uint64)), (k, got[k].reshape(-1)[:4], v[:4])
