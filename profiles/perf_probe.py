@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from dynolog_b200 import hbtgpu, synth
 
-def probe(name, cfg, ncpu, n, nb, flags=0, forge=0, fmt=0, **kw):
+def probe(name, cfg, ncpu, n, nb, flags=0, forge=0, fmt=0, series=False, **kw):
     spec, streams = synth.capture(cfg, ncpu, forge_ppm=forge, **kw)
     total = sum(len(s) for s in streams)
     g = hbtgpu.Context(n_events=n, max_cpus=ncpu, n_buckets=nb, t0=synth.T_START, bucket_ns=1_000_000,
@@ -28,11 +28,19 @@ def probe(name, cfg, ncpu, n, nb, flags=0, forge=0, fmt=0, **kw):
     print(f"{name:34s} {total/1e9:6.2f} GB  decode {dec:7.3f} ms  {total/1e6/dec:7.1f} GB/s "
           f"({100*total/1e6/dec/6547.5:4.1f}% of 6547.5)  step {s1['last_run_ms']:.3f} ms  "
           f"{nrec/1e6/ (s1['last_run_ms']):.1f} Grec/s  emit {emit:.3f} ms  exact_runs={s1['exact_runs']} why={s1['exact_reason']}")
+    if series:
+        import time
+        g.series_reduce(0.95, 1_000_000_000, 10_000_000_000)
+        t0 = time.time()
+        for _ in range(5):
+            g.series_reduce(0.95, 1_000_000_000, 10_000_000_000)
+        dt = (time.time() - t0) / 5
+        print(f"{'':34s} series reductions (avg, p95, diff, rate) of {ncpu * n} series x {nb} buckets: {dt*1e3:.2f} ms per call")
     g.close()
 
 if __name__ == "__main__":
     probe("cfg1 4MiB 1cpu n=4", 1, 1, 4, 6000, max_bytes_per_cpu=4 << 20)
-    probe("cfg2 192cpu n=8 (bench)", 2, 192, 8, 10100, n_samples=100_000)
+    probe("cfg2 192cpu n=8 (bench)", 2, 192, 8, 10100, n_samples=100_000, series=True)
     probe("cfg3 64cpu x 64MiB mux+LOST", 3, 64, 8, 70000, max_bytes_per_cpu=64 << 20)
     probe("cfg3 forged 1% (exact path)", 3, 64, 8, 70000, max_bytes_per_cpu=16 << 20, forge=10_000)
     probe("cfg3 force_general", 3, 64, 8, 70000, max_bytes_per_cpu=16 << 20, flags=hbtgpu.F_FORCE_GENERAL)
