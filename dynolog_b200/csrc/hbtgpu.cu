@@ -70,6 +70,8 @@ struct hbtgpu_ctx {
   void* d_math = nullptr;
   size_t cap_math = 0;
   uint64_t* d_series = nullptr;  // hbtgpu_series_reduce results
+  uint64_t* d_boundary_cell = nullptr;  // [max_cpus] cell a shard-boundary row was added to, or ~0
+  bool derived = false;                 // k_derive has run over the current accumulators
   size_t cap_series = 0;
 
   // host bookkeeping
@@ -273,11 +275,7 @@ Params make_params(hbtgpu_ctx* ctx) {
   return P;
 }
 
-int launch_derive(hbtgpu_ctx* ctx) {
-  if (ctx->d2h_pending) {  // do not overwrite tensors that are still being copied out
-    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));
-    ctx->d2h_pending = false;
-  }
+DeriveParams derive_params(hbtgpu_ctx* ctx) {
   DeriveParams D{};
   D.acc = ctx->d_acc;
   D.scaled = ctx->d_scaled;
@@ -288,6 +286,15 @@ int launch_derive(hbtgpu_ctx* ctx) {
   D.n_metrics = ctx->cfg.n_metrics;
   memcpy(D.metrics, ctx->cfg.metrics, sizeof(D.metrics));
   D.n_magic = ((1ull << 32) + D.n_events - 1) / D.n_events;
+  return D;
+}
+
+int launch_derive(hbtgpu_ctx* ctx) {
+  if (ctx->d2h_pending) {  // do not overwrite tensors that are still being copied out
+    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));
+    ctx->d2h_pending = false;
+  }
+  const DeriveParams D = derive_params(ctx);
   const uint64_t blocks = (ctx->n_cells + 255) / 256;
   if (D.n_events <= 16) {
     const size_t smem = static_cast<size_t>(DERIVE_CELLS) * (D.n_events + 3) * 8;  // <= 38.9 KB
@@ -295,6 +302,17 @@ int launch_derive(hbtgpu_ctx* ctx) {
   } else {
     k_derive<<<static_cast<unsigned>(blocks), 256, 0, ctx->stream>>>(D);
   }
+  CK(cudaGetLastError());
+  ctx->derived = true;
+  return 0;
+}
+
+// After shard-boundary rows were added: a full derive, or -- if the caller already derived
+// after hbtgpu_run (to overlap it with the stub exchange) -- only the cells those rows touched.
+int derive_after_boundaries(hbtgpu_ctx* ctx) {
+  if (!ctx->derived) return launch_derive(ctx);
+  const uint32_t ns = ctx->cfg.max_cpus;
+  k_derive_cells<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(derive_params(ctx), ctx->d_boundary_cell, ns);
   CK(cudaGetLastError());
   return 0;
 }
@@ -498,6 +516,7 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_valid), ctx->n_cells * 4));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_flags), FLAG_COUNT * 4));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_streams), ns * sizeof(StreamDesc)));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_boundary_cell), ns * 8ull));
   if (cfg->sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ) {
     const uint32_t tl = cfg->tid_table_log2 ? cfg->tid_table_log2 : 16, il = cfg->ip_table_log2 ? cfg->ip_table_log2 : 22;
     if (tl < 4 || tl > 28 || il < 4 || il > 28) {
@@ -542,7 +561,7 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
                   ctx->d_acc, ctx->d_scaled, ctx->d_metric, ctx->d_valid, ctx->d_flags,
                   ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
                   ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_tid_keys,
-                  ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special, ctx->d_series};
+                  ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special, ctx->d_series, ctx->d_boundary_cell};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
@@ -706,6 +725,7 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   // streams without images keep their carry: carry_out := carry_in
   CK(cudaMemcpyAsync(ctx->d_carry_out, ctx->d_carry_in, ns * sizeof(hbtgpu_carry),
                      cudaMemcpyDeviceToDevice, ctx->stream));
+  ctx->derived = false;
   const bool timed = ctx->ev_pending < hbtgpu_ctx::kEvRing;
   if (nc) {
     if (timed) CK(cudaEventRecord(ctx->ev_dec0[ctx->ev_pending], ctx->stream));
@@ -1005,13 +1025,13 @@ int hbtgpu_apply_boundaries(hbtgpu_ctx* ctx, const hbtgpu_carry* prev_tails) {
   // d_carry_in is free in shard mode (the decode used an invalid state): stage prev_tails there
   CK(cudaMemcpyAsync(ctx->d_carry_in, prev_tails, ns * sizeof(hbtgpu_carry), cudaMemcpyHostToDevice, ctx->stream));
   Params P = make_params(ctx);
-  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in);
+  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in, ctx->d_boundary_cell);
   CK(cudaGetLastError());
   // streams without a SAMPLE pass the previous state through: fix their carry-out on the host side
   CK(cudaStreamSynchronize(ctx->stream));  // prev_tails may be reused by the caller after this
   ctx->counters_valid = false;
   ctx->emitted = false;
-  return launch_derive(ctx);
+  return derive_after_boundaries(ctx);
 }
 
 size_t hbtgpu_stub_bytes(const hbtgpu_ctx* ctx) {
@@ -1045,12 +1065,12 @@ int hbtgpu_apply_boundaries_gathered(hbtgpu_ctx* ctx, const void* device_gathere
   // d_carry_in is free in shard mode (the decode used an invalid state): it receives the fold
   k_fold<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(static_cast<const uint8_t*>(device_gathered), rank,
                                                     ns, ctx->d_carry_init, ctx->d_carry_in);
-  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in);
+  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in, ctx->d_boundary_cell);
   CK(cudaGetLastError());
   ctx->counters_valid = false;
   ctx->emitted = false;
   ctx->stats.kernel_launches += 3;
-  return launch_derive(ctx);
+  return derive_after_boundaries(ctx);
 }
 
 int hbtgpu_acc_device(hbtgpu_ctx* ctx, void** device_ptr, size_t* bytes) {

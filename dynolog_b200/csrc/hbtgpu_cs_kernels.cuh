@@ -462,11 +462,25 @@ __global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
 // ------------------------------------------------------------------------------------
 // k_cs_resolve (only if NEED_EXACT): exact sequential walk, one warp per stream; runs of
 // 32-byte SWITCH records are skipped 32 at a time (lane l tests the header at pos + 32*l).
+// Windows of 8 KiB arrive in shared memory by double-buffered TMA copies, so the dependent
+// loads of the walk hit on-chip memory while the next window is in flight.
 // Hands every chunk its exact entry and predecessor, finds the first fence violation.
+constexpr int CS_RES_WIN_BYTES = 8192;
+constexpr int CS_RES_OV_BYTES = 16;  // only headers are read: one word past the window at most
 __global__ void __launch_bounds__(32) k_cs_resolve(const Params P) {
   if (P.flags[FLAG_NEED_EXACT] == 0) return;
+  __shared__ __align__(128) uint64_t win[2][(CS_RES_WIN_BYTES + CS_RES_OV_BYTES) / 8];
+  __shared__ __align__(8) uint64_t bar[2];
   const uint32_t sidx = blockIdx.x, lane = threadIdx.x;
   if (sidx >= P.n_streams) return;
+  const bool writer = lane == 0;
+  if (writer) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  uint32_t phase_bits = 0;
   const StreamDesc sd = P.streams[sidx];
   uint64_t* ctr = P.counters + static_cast<uint64_t>(sidx) * C_SLOTS;
   uint64_t last_off = PRED_CARRY_IN;
@@ -480,55 +494,85 @@ __global__ void __launch_bounds__(32) k_cs_resolve(const Params P) {
     uint64_t next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
     uint64_t pos = 0;
     const uint8_t* const img = P.arena + im.base;
-    while (!stopped && pos < im.len) {
-      const uint64_t q = pos + 32ull * lane;
-      const bool ok = q + 32 <= im.len && cs_is_switch32(*reinterpret_cast<const uint64_t*>(img + q));
-      const uint32_t okm = __ballot_sync(0xffffffffu, ok);
-      const uint32_t run = okm == 0xFFFFFFFFu ? 32u : static_cast<uint32_t>(__ffs(~okm) - 1);
-      if (run > 0) {
-        const uint64_t last_rec = pos + 32ull * (run - 1);
-        while (next_begin <= last_rec) {
-          const uint64_t j = next_begin <= pos ? 0 : (next_begin - pos + 31) / 32;
-          if (lane == 0) {
+    auto issue = [&](uint64_t wb, uint32_t b) {
+      const uint64_t avail = (im.len - wb + 15ull) & ~15ull;
+      const uint32_t bytes = static_cast<uint32_t>(umin64(avail, CS_RES_WIN_BYTES + CS_RES_OV_BYTES));
+      mbar_expect_tx(&bar[b], bytes);
+      tma_load_1d(win[b], img + wb, bytes, &bar[b]);
+    };
+    uint32_t issued = 0, waited = 0;
+    if (!stopped && im.len > 0) {
+      if (writer) issue(0, 0);
+      issued = 1;
+    }
+    for (uint64_t wb = 0; !stopped && wb < im.len; wb += CS_RES_WIN_BYTES) {
+      const uint32_t b = static_cast<uint32_t>(wb / CS_RES_WIN_BYTES) & 1;
+      __syncwarp();  // every lane is done with buffer b^1
+      if (wb + CS_RES_WIN_BYTES < im.len) {
+        if (writer) issue(wb + CS_RES_WIN_BYTES, b ^ 1);
+        ++issued;
+      }
+      mbar_wait(&bar[b], (phase_bits >> b) & 1u);
+      phase_bits ^= 1u << b;
+      ++waited;
+      const uint64_t* wd = win[b];
+      const uint64_t wend = umin64(wb + CS_RES_WIN_BYTES, im.len);
+      while (pos < wend) {
+        const uint64_t q = pos + 32ull * lane;
+        const bool ok = q < wend && q + 32 <= im.len && cs_is_switch32(wd[(q - wb) / 8]);
+        const uint32_t okm = __ballot_sync(0xffffffffu, ok);
+        const uint32_t run = okm == 0xFFFFFFFFu ? 32u : static_cast<uint32_t>(__ffs(~okm) - 1);
+        if (run > 0) {
+          const uint64_t last_rec = pos + 32ull * (run - 1);
+          while (next_begin <= last_rec) {
+            const uint64_t j = next_begin <= pos ? 0 : (next_begin - pos + 31) / 32;
+            if (writer) {
+              ChunkIO& io = P.io[ch];
+              io.in_entry = im.base + pos + 32 * j;
+              io.in_pred = j ? im.base + pos + 32 * (j - 1) : last_off;
+              io.in_gap = 0;
+              io.limit = ~0ull;
+            }
+            ++ch;
+            next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
+          }
+          last_off = im.base + last_rec;
+          pos = last_rec + 32;
+          continue;
+        }
+        while (pos >= next_begin) {
+          if (writer) {
             ChunkIO& io = P.io[ch];
-            io.in_entry = im.base + pos + 32 * j;
-            io.in_pred = j ? im.base + pos + 32 * (j - 1) : last_off;
+            io.in_entry = im.base + pos;
+            io.in_pred = last_off;
             io.in_gap = 0;
             io.limit = ~0ull;
           }
           ++ch;
           next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
         }
-        last_off = im.base + last_rec;
-        pos = last_rec + 32;
-        continue;
-      }
-      while (pos >= next_begin) {
-        if (lane == 0) {
-          ChunkIO& io = P.io[ch];
-          io.in_entry = im.base + pos;
-          io.in_pred = last_off;
-          io.in_gap = 0;
-          io.limit = ~0ull;
+        uint32_t type = 0, size = 0;
+        if (pos + 8 <= im.len) {
+          const uint64_t h = wd[(pos - wb) / 8];
+          type = static_cast<uint32_t>(h);
+          size = static_cast<uint32_t>(h >> 48);
         }
-        ++ch;
-        next_begin = ch < ch_end ? P.chunks[ch].begin : ~0ull;
+        if (size < 8 || (size & 7) || pos + size > im.len || size < cs_min_size(type)) {
+          err = -1;  // -EPERM
+          err_off = im.stream_pos + pos;
+          stopped = true;
+          break;
+        }
+        if (cs_handled(type)) last_off = im.base + pos;
+        pos += size;
       }
-      uint32_t type = 0, size = 0;
-      if (pos + 8 <= im.len) {
-        const uint64_t h = *reinterpret_cast<const uint64_t*>(img + pos);
-        type = static_cast<uint32_t>(h);
-        size = static_cast<uint32_t>(h >> 48);
-      }
-      if (size < 8 || (size & 7) || pos + size > im.len || size < cs_min_size(type)) {
-        err = -1;  // -EPERM
-        err_off = im.stream_pos + pos;
-        stopped = true;
-        break;
-      }
-      if (cs_handled(type)) last_off = im.base + pos;
-      pos += size;
     }
+    if (waited < issued) {  // never leave a bulk copy in flight
+      const uint32_t b = waited & 1;
+      mbar_wait(&bar[b], (phase_bits >> b) & 1u);
+      phase_bits ^= 1u << b;
+    }
+    __syncwarp();
     const uint64_t stop_abs = im.base + pos;
     for (uint32_t k = im.first_chunk + lane; k < ch_end; k += 32) {
       ChunkIO& io = P.io[k];
@@ -540,7 +584,7 @@ __global__ void __launch_bounds__(32) k_cs_resolve(const Params P) {
       io.limit = stopped ? stop_abs : ~0ull;
     }
   }
-  if (lane == 0) {
+  if (writer) {
     ctr[CSC_ERR] = static_cast<uint64_t>(err);
     ctr[CSC_ERR_OFF] = err_off;
   }

@@ -1973,8 +1973,10 @@ __global__ void k_fold(const uint8_t* gathered, uint32_t rank, uint32_t n_stream
 }
 
 // One block per stream: add the row that straddles the shard boundary.
-__global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_carry* prev_tails) {
+__global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_carry* prev_tails,
+                                                  uint64_t* touched_cell) {
   const uint32_t sidx = blockIdx.x;
+  if (threadIdx.x == 0) touched_cell[sidx] = ~0ull;  // which (cpu, bucket) cell got the boundary row
   const hbtgpu_head_stub& hs = P.head[sidx];
   const hbtgpu_carry& pt = prev_tails[sidx];
   // handleRecordSample emits a row iff the state is valid when the SAMPLE arrives (:135,165-182)
@@ -1996,6 +1998,7 @@ __global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_c
     if (bk == BKT_OOR) ctr[C_OOR] += 1;
   }
   if (bk == BKT_OOR) return;
+  if (threadIdx.x == 0) touched_cell[sidx] = static_cast<uint64_t>(sidx) * P.n_buckets + bk;
   uint64_t* base = P.acc + (static_cast<uint64_t>(sidx) * P.n_buckets + bk) * (n + 3);
   for (uint32_t e = threadIdx.x; e < n + 3; e += blockDim.x) {
     uint64_t v;
@@ -2069,6 +2072,21 @@ __device__ __forceinline__ uint32_t derive_metrics(const DeriveParams& D, const 
 __global__ void __launch_bounds__(256) k_derive(const DeriveParams D) {
   const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= D.n_cells) return;
+  const uint32_t n = D.n_events;
+  const uint64_t* a = D.acc + i * (n + 3);
+  const uint64_t te = a[n], tr = a[n + 1];
+  uint64_t* sc = D.scaled + i * n;
+  for (uint32_t e = 0; e < n; ++e) sc[e] = get_count(a[e], te, tr);
+  D.valid[i] = derive_metrics(D, sc, tr, D.metric + i * D.n_metrics);
+}
+
+// the same for a short list of cells (those a shard-boundary row was added to after the full
+// derive had already run); entries of ~0 are skipped
+__global__ void __launch_bounds__(128) k_derive_cells(const DeriveParams D, const uint64_t* cells, uint32_t n_cells) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_cells) return;
+  const uint64_t i = cells[t];
+  if (i == ~0ull) return;
   const uint32_t n = D.n_events;
   const uint64_t* a = D.acc + i * (n + 3);
   const uint64_t te = a[n], tr = a[n + 1];

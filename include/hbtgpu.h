@@ -274,7 +274,10 @@ int hbtgpu_apply_boundaries(hbtgpu_ctx* ctx, const hbtgpu_carry* prev_tails);
  *                                device_gathered = `world` blocks in rank order; folds the tails
  *                                of ranks < rank starting from the carry set with
  *                                hbtgpu_set_carry, adds the boundary rows, runs the derive step
- *                                (all async on the context stream) */
+ *                                (all async on the context stream).  If hbtgpu_derive was
+ *                                called after hbtgpu_run (say, while the collective was in
+ *                                flight on another stream), only the cells the boundary rows
+ *                                touched are derived again. */
 size_t hbtgpu_stub_bytes(const hbtgpu_ctx* ctx);
 int hbtgpu_export_stubs_device(hbtgpu_ctx* ctx, void* device_dst);
 int hbtgpu_apply_boundaries_gathered(hbtgpu_ctx* ctx, const void* device_gathered, uint32_t world,

@@ -113,3 +113,30 @@ def test_three_window_shards_match_single_stream(port_oracle, flags, device_fold
         if co.valid:
             assert int(final[c].tstamp) == int(co.tstamp)
         assert [int(final[c].last[i]) for i in range(N)] == [int(co.last[i]) for i in range(N)]
+
+
+def test_derive_before_boundaries_equals_derive_after():
+    """A caller may derive right after hbtgpu_run (to overlap it with the stub exchange);
+    hbtgpu_apply_boundaries* then re-derives only the cells the boundary rows touched.  Every
+    output must equal the plain order (boundaries, then one full derive)."""
+    n, ncpu, nb = 4, 5, 300
+    streams = [rg.random_stream(200 + i, 3000, n, mux=True, p_lost=0.01 if i == 3 else 0.0)[0] for i in range(ncpu)]
+    prev = (hbtgpu.Carry * ncpu)()
+    for c in range(ncpu):
+        prev[c] = to_gpu_carry(po.make_carry(valid=(c != 2), tstamp=999_000_000, te=5, tr=3, last=[1] * n))
+    outs = []
+    for early in (False, True):
+        with hbtgpu.Context(n_events=n, max_cpus=ncpu, n_buckets=nb, t0=1_000_000_000, bucket_ns=1_200_000,
+                            arena_bytes=sum(len(s) for s in streams) + (1 << 16), flags=hbtgpu.F_EXTERNAL_CARRY,
+                            metrics=[(hbtgpu.METRIC_RATE, [1, 0])]) as g:
+            for c, s in enumerate(streams):
+                g.submit_image(c, s)
+            g.run()
+            if early:
+                g.derive()
+            g.apply_boundaries(prev)
+            g.sync()
+            outs.append(g.buckets())
+    for k in ("acc", "scaled", "metric", "valid"):
+        assert np.array_equal(outs[0][k].view(np.uint8), outs[1][k].view(np.uint8)), k
+    assert outs[0]["scaled"].any()
