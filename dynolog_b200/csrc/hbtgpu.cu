@@ -295,13 +295,17 @@ int launch_derive(hbtgpu_ctx* ctx) {
     ctx->d2h_pending = false;
   }
   const DeriveParams D = derive_params(ctx);
-  const uint64_t blocks = (ctx->n_cells + 255) / 256;
-  if (D.n_events <= 16) {
-    const size_t smem = static_cast<size_t>(DERIVE_CELLS) * (D.n_events + 3) * 8;  // <= 38.9 KB
-    k_derive_tiled<<<static_cast<unsigned>(blocks), DERIVE_CELLS, smem, ctx->stream>>>(D);
-  } else {
-    k_derive<<<static_cast<unsigned>(blocks), 256, 0, ctx->stream>>>(D);
-  }
+  // cells per block: the largest power of two <= 256 whose tile fits 40 KiB of shared memory
+  const uint32_t F = D.n_events + 3;
+  uint32_t cb = DERIVE_CELLS;
+  while (cb > 32 && static_cast<size_t>(cb) * F * 8 > (40u << 10)) cb >>= 1;
+  const uint64_t blocks = (ctx->n_cells + cb - 1) / cb;
+  const size_t smem = static_cast<size_t>(cb) * F * 8;
+  const unsigned grid = static_cast<unsigned>(blocks);
+  if (cb == 256) k_derive_tiled<256><<<grid, 256, smem, ctx->stream>>>(D);
+  else if (cb == 128) k_derive_tiled<128><<<grid, 128, smem, ctx->stream>>>(D);
+  else if (cb == 64) k_derive_tiled<64><<<grid, 64, smem, ctx->stream>>>(D);
+  else k_derive_tiled<32><<<grid, 32, smem, ctx->stream>>>(D);
   CK(cudaGetLastError());
   ctx->derived = true;
   return 0;

@@ -2095,16 +2095,18 @@ __global__ void __launch_bounds__(128) k_derive_cells(const DeriveParams D, cons
   D.valid[i] = derive_metrics(D, sc, tr, D.metric + i * D.n_metrics);
 }
 
-// tiled form (n_events <= 16): a block stages the accumulators of 256 cells with coalesced
-// loads, each thread scales its cell in shared memory, the scaled counts leave coalesced again
+// tiled form: a block stages the accumulators of blockDim.x cells with coalesced loads, each
+// thread scales its cell in shared memory, the scaled counts leave coalesced again.  The host
+// picks CB (a power of two <= 256) so that the tile fits ~40 KiB of shared memory.
 constexpr int DERIVE_CELLS = 256;
-__global__ void __launch_bounds__(DERIVE_CELLS) k_derive_tiled(const DeriveParams D) {
-  extern __shared__ __align__(16) uint64_t dsm[];  // [DERIVE_CELLS][n + 3]
+template <uint32_t CB>  // cells per block = threads per block (compile-time: the copy loops unroll)
+__global__ void __launch_bounds__(CB) k_derive_tiled(const DeriveParams D) {
+  extern __shared__ __align__(16) uint64_t dsm[];  // [CB][n + 3]
   const uint32_t n = D.n_events, F = n + 3;
-  const uint64_t cell0 = static_cast<uint64_t>(blockIdx.x) * DERIVE_CELLS;
-  const uint32_t cells = static_cast<uint32_t>(umin64(DERIVE_CELLS, D.n_cells - cell0));
+  const uint64_t cell0 = static_cast<uint64_t>(blockIdx.x) * CB;
+  const uint32_t cells = static_cast<uint32_t>(umin64(CB, D.n_cells - cell0));
   const uint64_t* src = D.acc + cell0 * F;
-  for (uint32_t i = threadIdx.x; i < cells * F; i += DERIVE_CELLS) dsm[i] = src[i];
+  for (uint32_t i = threadIdx.x; i < cells * F; i += CB) dsm[i] = src[i];
   __syncthreads();
   if (threadIdx.x < cells) {
     uint64_t* a = dsm + threadIdx.x * F;
@@ -2115,8 +2117,8 @@ __global__ void __launch_bounds__(DERIVE_CELLS) k_derive_tiled(const DeriveParam
   }
   __syncthreads();
   uint64_t* dst = D.scaled + cell0 * n;
-  for (uint32_t o = threadIdx.x; o < cells * n; o += DERIVE_CELLS) {
-    const uint32_t c = static_cast<uint32_t>((static_cast<uint64_t>(o) * D.n_magic) >> 32);
+  for (uint32_t o = threadIdx.x; o < cells * n; o += CB) {
+    const uint32_t c = static_cast<uint32_t>((static_cast<uint64_t>(o) * D.n_magic) >> 32);  // o / n, o < 2^16
     dst[o] = dsm[c * F + (o - c * n)];
   }
 }
