@@ -987,7 +987,7 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
 // MODE_EMIT writes, instead of bucket sums, the rows exactly as CpuCountSampleGenerator writes
 // them to its output ring ([tstamp, duration, delta...], gen :165-182) and the record table;
 // a warp assembles its (consecutive) rows in shared memory and copies them out coalesced.
-constexpr int EMIT_MAX_ROW_WORDS = 16;                     // n_events <= 14 on this path
+constexpr int EMIT_MAX_ROW_WORDS = 16;                     // rows of up to 14 events go through the stage
 constexpr int EMIT_STAGE_WORDS = 31 * EMIT_MAX_ROW_WORDS;  // per warp
 constexpr size_t EMIT_STAGE_BYTES = static_cast<size_t>(NWARP) * EMIT_STAGE_WORDS * 8;
 
@@ -1085,6 +1085,33 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
         P.rec_size[gi] = 8 * S;
       }
       const int jlo = max(max(j0, 0), skip), jhi = min(j0 + 31, K);  // records with a row here
+      if (RW > EMIT_MAX_ROW_WORDS) {
+        // wide rows (more than 14 events) do not fit the stage and do not need it: the warp's
+        // rows are one contiguous run of words in the output; lane l computes words l, l+32, ...
+        // of that run straight from the tile
+        if (jhi > jlo) {
+          uint64_t* dst = P.rows + (tc.row_base + tc.rows_before + static_cast<uint64_t>(jlo - skip)) * RW;
+          const uint32_t words = static_cast<uint32_t>(jhi - jlo) * RW;
+          for (uint32_t o = lane; o < words; o += 32) {
+            const uint32_t r = o / RW, w = o - r * RW;
+            const int j = jlo + static_cast<int>(r);
+            const uint32_t p = entry + j * S;
+            uint64_t v;
+            if (w < 2) {
+              const uint64_t ts = buf[p + pre + 1];
+              const uint64_t pts = j ? buf[p - S + pre + 1] : C.ts;
+              v = w == 0 ? pts : ts - pts;
+            } else {
+              const uint32_t e = w - 2;
+              const uint64_t cv = xform(P, e, buf[p + pre + 5 + e]);
+              const uint64_t pv = j ? xform(P, e, buf[p - S + pre + 5 + e]) : C.last[e];
+              v = cv - pv;
+            }
+            dst[o] = v;
+          }
+        }
+        continue;
+      }
       __syncwarp();  // the previous copy-out has read the stage
       if (lane < 31 && jr >= jlo && jr < jhi) {
         const uint32_t p = entry + jr * S;
@@ -1479,7 +1506,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
       uint32_t term_kind = 0, term_tgt = 0;
       bool done = false;
       uint32_t ew = entry;  // chain position, tile-relative words
-      if (!P.force_general && (MODE == MODE_AGG || P.n_events + 2 <= EMIT_MAX_ROW_WORDS)) {
+      if (!P.force_general) {
         // runs of configured SAMPLEs in parallel, the few other records in between one by one;
         // a tile with many of those goes to the general path
         const uint32_t S = 5 + PRE + (NEV ? static_cast<uint32_t>(NEV) : P.n_events);

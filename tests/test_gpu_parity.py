@@ -60,6 +60,7 @@ BIG_CASES = [
     (4, 30_000, dict(forge=0.01, p_lost=0.001)),
     (1, 50_000, dict(p_lost=0.3)),
     (64, 3_000, dict(p_lost=0.01)),
+    (20, 8_000, dict(p_lost=0.002, p_throttle=0.002)),   # rows wider than the emission stage
     (2, 20_000, dict(p_other=0.5)),
 ]
 
