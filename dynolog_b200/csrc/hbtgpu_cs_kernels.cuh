@@ -197,13 +197,11 @@ __device__ __forceinline__ void cs_pred_state(const Params& P, const CsOut& O, u
 constexpr uint32_t WHY_CS_NO_TRIPLE = 20, WHY_CS_HALO_WALK = 21, WHY_CS_SEAM = 22, WHY_CS_RECORD = 23,
                    WHY_CS_PAST_END = 24;
 
+// One chunk, one pass (COUNT or EMIT).  Called once per CTA by k_cs, twice (COUNT, look-back,
+// EMIT) by k_cs_fused.  ev_base / op_base: where this chunk's events / ops go (EMIT).
 template <bool SPEC, bool EMIT>
-__global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
-  extern __shared__ __align__(128) unsigned char cs_smem_raw[];
-  CsSmem& s = *reinterpret_cast<CsSmem*>(cs_smem_raw);
-  if (!SPEC && !EMIT && P.flags[FLAG_NEED_EXACT] == 0) return;  // exact count pass not needed
-
-  const uint32_t c = blockIdx.x;
+__device__ __forceinline__ void cs_chunk(const Params& P, const CsOut& O, CsSmem& s, const uint32_t c,
+                                         const uint64_t ev_base, const uint64_t op_base) {
   const ChunkDesc cd = P.chunks[c];
   ChunkIO& io = P.io[c];
   const uint32_t cu = cd.stream;
@@ -220,7 +218,7 @@ __global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
   if (threadIdx.x < 16) s.cnt[threadIdx.x] = 0;
   __syncthreads();
 
-  uint32_t phase[2] = {0, 0};
+  uint32_t phase_bits = 0;  // parity of the two TMA barriers
   const uint64_t chunk_abs = cd.img_base + cd.begin;
   const uint64_t img_end_abs = cd.img_base + cd.img_len;
   uint64_t limit_abs = img_end_abs;
@@ -250,8 +248,8 @@ __global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
       }
       boff = 1;
       n_issued = 1;
-      mbar_wait(&s.bar[0], phase[0]);
-      phase[0] ^= 1;
+      mbar_wait(&s.bar[0], phase_bits & 1u);
+      phase_bits ^= 1u;
       const uint64_t* hb = s.data[0];
       const uint32_t w = threadIdx.x;
       const bool m = w >= 8 && w < hw && cs_is_switch32(hb[w]) && cs_is_switch32(hb[w - 4]) &&
@@ -319,7 +317,7 @@ __global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
   __syncthreads();
 
   // ---- tiles ----
-  const uint64_t ev0 = EMIT ? io.row_base : 0, op0 = EMIT ? io.rec_base : 0;
+  const uint64_t ev0 = EMIT ? ev_base : 0, op0 = EMIT ? op_base : 0;
   const uint64_t chunk_end_abs = min(cd.img_base + cd.end, limit_abs);
   const bool any_work = !bad && entry_abs < chunk_end_abs;
   const uint32_t chunk_len = any_work ? static_cast<uint32_t>(chunk_end_abs - chunk_abs) : 0;
@@ -334,8 +332,8 @@ __global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
       if (threadIdx.x == 0) issue(tile_rel + CS_TILE_BYTES, b ^ 1);
       ++n_issued;
     }
-    mbar_wait(&s.bar[b], phase[b]);
-    phase[b] ^= 1;
+    mbar_wait(&s.bar[b], (phase_bits >> b) & 1u);
+    phase_bits ^= 1u << b;
     ++n_waited;
     const uint64_t* buf = s.data[b];
     const uint32_t wt = min(static_cast<uint32_t>(CS_TILE_BYTES), chunk_len - tile_rel) / 8;
@@ -430,7 +428,7 @@ __global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
       break;
     }
   }
-  if (n_waited < n_issued) mbar_wait(&s.bar[(n_waited + boff) & 1], phase[(n_waited + boff) & 1]);
+  if (n_waited < n_issued) mbar_wait(&s.bar[(n_waited + boff) & 1], (phase_bits >> ((n_waited + boff) & 1)) & 1u);
   const uint64_t next_abs = any_work ? chunk_abs + next_rel : entry_abs;
 
   // ---- publish ----
@@ -457,6 +455,16 @@ __global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O) {
       if (s.n_ops) red_add(&ctr[CSC_OPS], s.n_ops);
     }
   }
+}
+
+template <bool SPEC, bool EMIT>
+__global__ void __launch_bounds__(NT, 5) k_cs(const Params P, const CsOut O, const uint32_t gated) {
+  extern __shared__ __align__(128) unsigned char cs_smem_raw[];
+  CsSmem& s = *reinterpret_cast<CsSmem*>(cs_smem_raw);
+  // the exact passes run only when the speculation was disproved
+  if (!SPEC && (!EMIT || gated) && P.flags[FLAG_NEED_EXACT] == 0) return;
+  const uint32_t c = blockIdx.x;
+  cs_chunk<SPEC, EMIT>(P, O, s, c, EMIT ? P.io[c].row_base : 0, EMIT ? P.io[c].rec_base : 0);
 }
 
 // ------------------------------------------------------------------------------------
