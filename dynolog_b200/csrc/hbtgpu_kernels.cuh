@@ -308,6 +308,8 @@ struct __align__(128) Smem {
   uint32_t wcnt[WPT * NWARP + 1];
   uint32_t scan_a[NWARP], scan_b[NWARP], scan_c[NWARP];
   uint32_t e_idx, term_tgt, term_kind, red_key;
+  uint32_t idx_n, idx_end, idx_gap, idx_bad;  // index_tile: samples listed, chain position after the tile,
+                                              // a LOST after the last sample, word of a record consume() stalls on
   uint32_t tile_err;
   uint32_t cnt[C_SLOTS];          // chunk-local counters (u32), lost is u64 below
   unsigned long long lost_sum;
@@ -965,6 +967,81 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
   __syncthreads();
 }
 
+// Index of a mixed tile (MODE_AGG).  A tile that holds other records than configured SAMPLEs
+// (THROTTLE / UNTHROTTLE pairs under a high sample rate, LOST) used to be cut at each of them
+// and every piece cost a full pass.  Instead warp 0 walks the chain once -- runs of SAMPLEs 32
+// at a time (lane l tests the record at p + l*S), any other record by its size, with the
+// checks and the accounting of consume() (:1440-1450 LOST, :1476-1487 THROTTLE, :1515-1530
+// READ, :1565-1570 anything else) -- and lists the SAMPLEs: s.pos[j] = word position,
+// s.fl[j] = 1 if a LOST lies between sample j-1 and j (its row does not exist, gen :110-124).
+// One pass of uniform_segment<..., IDX = true> over the list then does what the plain pass does
+// for a contiguous run.  Must be called by all threads; contains barriers.
+template <int PRE, int NEV>
+__device__ __forceinline__ void index_tile(Smem& s, const Params& P, const uint64_t* buf, uint32_t wt,
+                                           uint32_t ew, uint32_t cur) {
+  if (threadIdx.x < 32) {
+    const uint32_t lane = threadIdx.x;
+    const uint32_t n = NEV ? static_cast<uint32_t>(NEV) : P.n_events;
+    const uint32_t S = 5 + PRE + n;
+    const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
+    uint32_t p = ew, nrec = 0, bad = 0xFFFFFFFFu, n_flagged = 0;
+    uint32_t n_rec_other = 0, n_thr = 0, n_unthr = 0, n_read = 0;
+    unsigned long long lost = 0;
+    bool gap = false;  // a LOST since the last listed sample
+    while (p < wt) {
+      const uint32_t q = p + lane * S;
+      const bool ok = q < wt && (buf[q] & 0xFFFF0000FFFFFFFFull) == want && buf[q + PRE + 2] == n;
+      const uint32_t okm = __ballot_sync(0xffffffffu, ok);
+      const uint32_t run = okm == 0xFFFFFFFFu ? 32u : static_cast<uint32_t>(__ffs(~okm) - 1);
+      if (run > 0) {
+        if (lane < run) {
+          s.pos[nrec + lane] = static_cast<uint16_t>(q);
+          s.fl[nrec + lane] = (lane == 0 && gap) ? 1 : 0;
+        }
+        nrec += run;
+        n_flagged += gap ? 1 : 0;
+        gap = false;
+        p += run * S;
+        continue;
+      }
+      const uint64_t h = buf[p];
+      const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
+      // what consume() stalls on (or the fences of DESIGN.md): the general path reports it
+      if (size < 8 || (size & 7) || type == REC_SAMPLE || (type == REC_LOST && size < 24) ||
+          (type == REC_READ && (size < 40 || buf[p + 2] != ((size - 40u) >> 3)))) {
+        bad = p;
+        break;
+      }
+      n_rec_other += 1;
+      if (type == REC_LOST) {
+        lost += buf[p + 2];
+        gap = true;
+      } else if (type == REC_THROTTLE) {
+        n_thr += 1;
+      } else if (type == REC_UNTHROTTLE) {
+        n_unthr += 1;
+      } else if (type == REC_READ) {
+        n_read += 1;
+      }
+      p += size >> 3;
+    }
+    if (lane == 0) {
+      s.idx_n = nrec;
+      s.idx_end = p;
+      s.idx_gap = (gap ? 1u : 0u) | (n_flagged << 1);  // bit 0: LOST behind the last sample
+      s.idx_bad = bad;
+      s.cnt[C_RECORDS] += n_rec_other;
+      s.cnt[C_THROTTLE] += n_thr;
+      s.cnt[C_UNTHROTTLE] += n_unthr;
+      s.cnt[C_READ] += n_read;
+      s.lost_sum += lost;
+      // no sample behind the last LOST of this tile: the carry remembers it
+      if (nrec == 0 && gap) s.c[cur].gap = 1;
+    }
+  }
+  __syncthreads();
+}
+
 // Fast path for a tile in which every record from `entry` on is a SAMPLE of the configured
 // group (type 9, size 40+8n, nr == n).  Then record j sits at entry + j*S and each equality
 // test IS the chain link (record j's size carries the walk to record j+1), so the chain is
@@ -1004,7 +1081,9 @@ __host__ __device__ constexpr size_t decode_smem_bytes(uint32_t tile_bytes) {
   return decode_data_off<MODE, PRE>() + 2 * (static_cast<size_t>(tile_bytes) + OV_BYTES);
 }
 
-template <int MODE, int PRE, int NEV>
+// IDX: the records are the s.idx_n samples index_tile listed (MODE_AGG only): positions from
+// s.pos, s.fl[j] = a LOST lies before sample j; they are valid by construction, so no vote.
+template <int MODE, int PRE, int NEV, bool IDX = false>
 __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, const uint64_t* buf,
                                                     uint32_t wt, uint32_t entry, TileCtx& tc,
                                                     uint32_t cur, uint32_t& k_all) {
@@ -1018,8 +1097,11 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   // records whose header lies inside the tile: ceil((wt - entry) / S) by multiply-shift
   const int Kall = NEV ? static_cast<int>((wt - entry + S - 1) / S)
                        : static_cast<int>((static_cast<uint64_t>(wt - entry + S - 1) * P.s_magic) >> 32);
-  k_all = static_cast<uint32_t>(Kall);
-  int K = min(Kall, PASS_RECORDS);  // never more by construction of the tile size
+  k_all = static_cast<uint32_t>(IDX ? s.idx_n : Kall);
+  int K = min(IDX ? static_cast<int>(s.idx_n) : Kall, PASS_RECORDS);  // never more by construction of the tile size
+  // word position of record j, and whether its row is missing because of a LOST before it
+  auto posof = [&](int j) -> uint32_t { return IDX ? static_cast<uint32_t>(s.pos[j]) : entry + j * S; };
+  auto gapof = [&](int j) -> bool { return IDX && j >= 0 && s.fl[j] != 0; };
   const bool link0 = C.valid != 0 && C.gap == 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int OWN = 31;  // records owned per warp-iteration (lanes 0..30)
@@ -1040,22 +1122,22 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
     uint64_t ts = 0;
     bk_[g] = BKT_OOR;
     if (jr >= 0 && jr < K) {
-      const uint32_t p = entry + jr * S;
+      const uint32_t p = posof(jr);
       // misc (bits 32..47) is free; type and size must match, and so must nr (three loads
       // issued together, one combined test: no short-circuit branches)
       const uint64_t hd = buf[p], nr = buf[p + pre + 2];
       ts = buf[p + pre + 1];
       const bool mismatch = ((hd & 0xFFFF0000FFFFFFFFull) != want) | (nr != n);
-      if (lane < 31 && mismatch) first_bad = min(first_bad, jr);
+      if (!IDX && lane < 31 && mismatch) first_bad = min(first_bad, jr);
       bk_[g] = bucket_of(P, ts);
     } else if (jr == -1) {
       ts = C.ts;
     }
     const uint64_t nts = __shfl_down_sync(0xffffffffu, ts, 1);
     // row jr+1 exists and goes back in time (gen :156-163)
-    if (lane < 31 && jr + 1 < K && (jr >= 0 || link0) && ts > nts) regress = min(regress, jr + 1);
+    if (lane < 31 && jr + 1 < K && (jr >= 0 || link0) && !gapof(jr + 1) && ts > nts) regress = min(regress, jr + 1);
   }
-  if (!__syncthreads_and(first_bad == 0x7FFFFFFF)) {
+  if (!IDX && !__syncthreads_and(first_bad == 0x7FFFFFFF)) {
     // not uniform to the end: agree on the first record that breaks the run
     if (threadIdx.x == 0) s.red_key = static_cast<uint32_t>(Kall);
     __syncthreads();
@@ -1065,7 +1147,8 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
     __syncthreads();  // red_key may be reused right away
     if (K == 0) return 0;
   }
-  if (regress < K) atomicMin(&s.tile_err, entry + regress * S);
+  if (IDX && K == 0) return 0;
+  if (regress < K) atomicMin(&s.tile_err, posof(regress));
 
   if (MODE == MODE_EMIT) {
     // rows of this segment are consecutive: record jr's row has ordinal jr - (link0 ? 0 : 1)
@@ -1143,7 +1226,7 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
     for (int g = 0; g < MAXG; ++g) {
       const int jr = (g * NWARP + warp) * OWN - 1 + lane;
       if (lane < 31 && jr >= 0 && jr < K) {
-        const uint32_t p = entry + jr * S;
+        const uint32_t p = posof(jr);
         attr_count<true>(P, buf[p + 1]);
         attr_count<false>(P, buf[p + 2]);
       }
@@ -1169,8 +1252,8 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
     const uint32_t bk = bk_[g];
     const uint32_t bk_next = __shfl_down_sync(0xffffffffu, bk, 1);
     const bool own = lane < 31 && jr < K;                    // jr >= -1 always
-    const bool rowA = jr >= 1 || (jr == 0 && link0);         // row jr exists
-    const bool rowB = jr + 1 < K && (jr >= 0 || link0);      // row jr+1 exists
+    const bool rowA = (jr >= 1 || (jr == 0 && link0)) && !gapof(jr);            // row jr exists
+    const bool rowB = jr + 1 < K && (jr >= 0 || link0) && !gapof(jr + 1);       // row jr+1 exists
     const bool cancel = rowA && rowB && bk == bk_next;
     const bool doA = own && rowA && !cancel && bk != BKT_OOR;
     const bool doB = own && rowB && !cancel && bk_next != BKT_OOR;
@@ -1193,7 +1276,7 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
       const uint32_t bkB = __shfl_sync(0xffffffffu, bk_next, srcl);
       if (src >= 0) {
         const int j = j0 + src;
-        const uint32_t p = entry + j * S;
+        const uint32_t p = j < 0 ? 0u : posof(j);
         uint32_t e = e0, woff = woff0;
         for (;;) {
           if (e < F) {
@@ -1221,19 +1304,21 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   // the new carry (other copy): last record of the tile
   if (warp == NWARP - 1) {
     Carry& N = s.c[cur ^ 1];
-    const uint32_t p = entry + (K - 1) * S;
+    const uint32_t p = posof(K - 1);
     for (uint32_t e = lane; e < n; e += 32) N.last[e] = xform(P, e, buf[p + pre + 5 + e]);
     if (lane == 0) {
       N.ts = buf[p + pre + 1];
       N.te = buf[p + pre + 3];
       N.tr = buf[p + pre + 4];
       N.valid = 1;
-      N.gap = 0;
+      N.gap = IDX ? (s.idx_gap & 1u) : 0;  // a LOST behind the last sample of an indexed tile
       N.last_off = tc.tile_abs + 8ull * p;
+      // samples without a row: behind a LOST (indexed tiles), or the first one after an invalid state
+      const uint32_t rowless = (IDX ? (s.idx_gap >> 1) : 0) + ((!link0 && !gapof(0)) ? 1u : 0u);
       s.cnt[C_SAMPLE] += K;
       s.cnt[C_RECORDS] += K;
-      s.cnt[C_ROWS] += link0 ? K : K - 1;
-      s.cnt[C_UNKNOWN] += link0 ? 0 : 1;
+      s.cnt[C_ROWS] += K - rowless;
+      s.cnt[C_UNKNOWN] += rowless;
     }
   }
   return static_cast<uint32_t>(K);
@@ -1520,6 +1605,24 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
             break;
           }
           __syncthreads();  // the segment's carry is published
+          if (MODE == MODE_AGG) {
+            // the tile holds other records too: index the rest of it once (index_tile), then
+            // one pass over the listed samples, however many other records lie in between
+            index_tile<PRE, NEV>(s, P, buf, wt, ew, cur);
+            uint32_t n_idx = 0;
+            const uint32_t ki = uniform_segment<MODE, PRE, NEV, true>(s, P, buf, wt, ew, tc, cur, n_idx);
+            if (ki) cur ^= 1;
+            ew = s.idx_end;
+            if (s.idx_bad != 0xFFFFFFFFu) {
+              // a record consume() stalls on: everything before it is accounted for, the general
+              // path looks at it and owns the error reporting
+              ew = s.idx_bad;
+              __syncthreads();
+              break;
+            }
+            done = true;
+            break;
+          }
           const uint32_t sz = (++odd <= 8) ? odd_record<MODE>(s, P, buf, ew, cur, tc) : 0;
           if (sz == 0) break;
           ew += sz;
