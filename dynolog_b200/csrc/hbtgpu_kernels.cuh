@@ -308,7 +308,7 @@ struct __align__(128) Smem {
   uint32_t wcnt[WPT * NWARP + 1];
   uint32_t scan_a[NWARP], scan_b[NWARP], scan_c[NWARP];
   uint32_t e_idx, term_tgt, term_kind, red_key;
-  uint32_t idx_n, idx_end, idx_gap, idx_bad;  // index_tile: samples listed, chain position after the tile,
+  uint32_t idx_n, idx_end, idx_gap, idx_bad, idx_other;  // index_tile: samples listed, chain position after the tile,
                                               // a LOST after the last sample, word of a record consume() stalls on
   uint32_t tile_err;
   uint32_t cnt[C_SLOTS];          // chunk-local counters (u32), lost is u64 below
@@ -1030,6 +1030,7 @@ __device__ __forceinline__ void index_tile(Smem& s, const Params& P, const uint6
       s.idx_end = p;
       s.idx_gap = (gap ? 1u : 0u) | (n_flagged << 1);  // bit 0: LOST behind the last sample
       s.idx_bad = bad;
+      s.idx_other = n_rec_other;
       s.cnt[C_RECORDS] += n_rec_other;
       s.cnt[C_THROTTLE] += n_thr;
       s.cnt[C_UNTHROTTLE] += n_unthr;
@@ -1568,6 +1569,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
     if (threadIdx.x == 0) issue(0, boff);
     n_issued = 1;
   }
+  bool mixed_prev = false;  // the previous tile held other records than configured SAMPLEs
   for (uint32_t tile_rel = 0, b = boff; tile_rel < chunk_len; tile_rel += tb, b ^= 1) {
     if (tile_rel + tb < chunk_len) {
       if (threadIdx.x == 0) issue(tile_rel + tb, b ^ 1);
@@ -1596,15 +1598,19 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
         // a tile with many of those goes to the general path
         const uint32_t S = 5 + PRE + (NEV ? static_cast<uint32_t>(NEV) : P.n_events);
         for (int odd = 0;;) {
-          uint32_t k_all = 0;
-          const uint32_t k = uniform_segment<MODE, PRE, NEV>(s, P, buf, wt, ew, tc, cur, k_all);
-          if (k) cur ^= 1;
-          ew += k * S;
-          if (k == k_all) {  // ran to the end of the tile
-            done = true;
-            break;
+          // (after a mixed tile the next one is indexed right away: the plain attempt would
+          // only prove the records up to the first other one)
+          if (!(MODE == MODE_AGG && mixed_prev)) {
+            uint32_t k_all = 0;
+            const uint32_t k = uniform_segment<MODE, PRE, NEV>(s, P, buf, wt, ew, tc, cur, k_all);
+            if (k) cur ^= 1;
+            ew += k * S;
+            if (k == k_all) {  // ran to the end of the tile
+              done = true;
+              break;
+            }
+            __syncthreads();  // the segment's carry is published
           }
-          __syncthreads();  // the segment's carry is published
           if (MODE == MODE_AGG) {
             // the tile holds other records too: index the rest of it once (index_tile), then
             // one pass over the listed samples, however many other records lie in between
@@ -1613,6 +1619,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
             const uint32_t ki = uniform_segment<MODE, PRE, NEV, true>(s, P, buf, wt, ew, tc, cur, n_idx);
             if (ki) cur ^= 1;
             ew = s.idx_end;
+            mixed_prev = s.idx_other != 0;
             if (s.idx_bad != 0xFFFFFFFFu) {
               // a record consume() stalls on: everything before it is accounted for, the general
               // path looks at it and owns the error reporting
