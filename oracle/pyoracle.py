@@ -337,3 +337,117 @@ def load(kind="port"):
                 f"{path} missing: run `make -C oracle` (or __graft_entry__.build())")
         _cache[kind] = Oracle(path, prefix)
     return _cache[kind]
+
+
+# --- tagstack slices (oracle/hbtslices_api.h) -----------------------------------------------------
+SLICE_DTYPE = np.dtype([("tstamp", "<u8"), ("duration", "<u8"), ("stack_id", "<u8"),
+                        ("swin_type", "u1"), ("swout_type", "u1"), ("pad", "u1", (6,))])
+EVENT_DTYPE = np.dtype([("tstamp", "<u8"), ("type", "u1"), ("level", "u1"),
+                        ("comp_unit_id", "<u2"), ("tag", "<u4")])
+STACK_DTYPE = np.dtype([("stack_id", "<u8"), ("parent_stack_id", "<u8"), ("tags", "<u4", (6,)),
+                        ("num_set_tags", "u1"), ("known_num_levels", "u1"), ("pad", "u1", (6,)),
+                        ("cum_active_time", "<u8"), ("num_swins", "<u8"), ("num_swouts", "<u8")])
+SLICER_STAT_KEYS = ("num_processed", "num_error_start", "num_error_end", "num_error_out_sync",
+                    "num_dropped", "num_out_of_order", "num_slices_completed", "num_logic_errors")
+TRIM, ABORT_ON_MISSING = 1, 2
+TT_NA, TT_ANALYSIS, TT_PREEMPTED, TT_YIELD, TT_PHASE = 0, 1, 2, 3, 4
+assert SLICE_DTYPE.itemsize == 32 and EVENT_DTYPE.itemsize == 16 and STACK_DTYPE.itemsize == 72
+
+_SLICES_PATHS = {
+    "reference": (os.path.join(HERE, "_ref", "libhbtref_slices.so"), "hbtref"),
+    "port": (os.path.join(HERE, "libhbtoracle.so"), "hbtoracle"),
+}
+_slices_cache = {}
+
+
+def slices_available(kind):
+    return os.path.exists(_SLICES_PATHS[kind][0])
+
+
+def _slices_lib(kind):
+    if kind not in _slices_cache:
+        path, prefix = _SLICES_PATHS[kind]
+        if not os.path.exists(path):
+            raise FileNotFoundError(f"{path} missing: run `make -C oracle`")
+        _slices_cache[kind] = (C.CDLL(path), prefix)
+    return _slices_cache[kind]
+
+
+def make_slices(rows):
+    """rows: iterable of (tstamp, duration, stack_id, swin, swout)."""
+    rows = list(rows)
+    a = np.zeros(len(rows), SLICE_DTYPE)
+    for i, r in enumerate(rows):
+        a[i]["tstamp"], a[i]["duration"], a[i]["stack_id"], a[i]["swin_type"], a[i]["swout_type"] = r
+    return a
+
+
+def slices_as_tuples(a):
+    return [(int(s["tstamp"]), int(s["duration"]), int(s["stack_id"]), int(s["swin_type"]),
+             int(s["swout_type"])) for s in a]
+
+
+def islice_make(kind, slices, offset, tstamp, duration, flags):
+    """One makeIntervalIntersectingSlices call.  Returns (slices or None, consumed);
+    raises ValueError where the reference throws."""
+    lib, prefix = _slices_lib(kind)
+    f = getattr(lib, prefix + "_islice_make")
+    f.restype = C.c_int
+    slices = np.ascontiguousarray(slices, dtype=SLICE_DTYPE)
+    out = np.zeros(max(1, len(slices)), SLICE_DTYPE)
+    n_out, consumed = C.c_uint64(0), C.c_uint64(0)
+    rc = f(C.c_void_p(slices.ctypes.data), C.c_uint64(len(slices)), C.c_uint64(offset),
+           C.c_uint64(tstamp), C.c_uint64(duration), C.c_uint32(flags),
+           C.c_void_p(out.ctypes.data), C.c_uint64(len(out)), C.byref(n_out), C.byref(consumed))
+    if rc < 0:
+        raise ValueError(f"islice_make: reference throws (rc={rc})")
+    if rc == 1:
+        return None, 0
+    return out[:n_out.value].copy(), consumed.value
+
+
+def islice_release(kind, slices, rows, stop_ts, flags, mark=0):
+    """The releaseCountData_ row loop for one comp unit.  rows: [n, stride>=2] u64.
+    Returns dict(rc, counts, slices, mark, n_intervals, err_interval)."""
+    lib, prefix = _slices_lib(kind)
+    f = getattr(lib, prefix + "_islice_release")
+    f.restype = C.c_int
+    slices = np.ascontiguousarray(slices, dtype=SLICE_DTYPE)
+    rows = np.ascontiguousarray(rows, dtype=np.uint64)
+    if rows.ndim == 1:
+        rows = rows.reshape(-1, 2)
+    n_rows, stride = rows.shape
+    counts = np.zeros(max(1, n_rows), np.uint32)
+    cap = len(slices) + 2 * n_rows + 1
+    out = np.zeros(cap, SLICE_DTYPE)
+    m = C.c_uint64(mark)
+    n_out, n_int, err = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+    rc = f(C.c_void_p(slices.ctypes.data), C.c_uint64(len(slices)), _p(rows, C.c_uint64),
+           C.c_uint64(stride), C.c_uint64(n_rows), C.c_uint64(stop_ts), C.c_uint32(flags),
+           C.byref(m), _p(counts, C.c_uint32), C.c_void_p(out.ctypes.data), C.c_uint64(cap),
+           C.byref(n_out), C.byref(n_int), C.byref(err))
+    return {"rc": rc, "counts": counts[:n_int.value].copy(), "slices": out[:n_out.value].copy(),
+            "mark": m.value, "n_intervals": n_int.value, "err_interval": err.value}
+
+
+def slicer_run(kind, events, n_units, cap_per_unit=None, stack_cap=None):
+    """Slicer::processNext over events in stream order.  Returns dict(rc, slices=[per unit],
+    stats, stacks, last_ts)."""
+    lib, prefix = _slices_lib(kind)
+    f = getattr(lib, prefix + "_slicer_run")
+    f.restype = C.c_int
+    events = np.ascontiguousarray(events, dtype=EVENT_DTYPE)
+    cap = cap_per_unit if cap_per_unit is not None else len(events) + 1
+    stack_cap = stack_cap if stack_cap is not None else 8 * len(events) + 8
+    out = np.zeros((n_units, cap), SLICE_DTYPE)
+    n_slices = np.zeros(n_units, np.uint64)
+    stats = np.zeros(len(SLICER_STAT_KEYS), np.uint64)
+    stacks = np.zeros(stack_cap, STACK_DTYPE)
+    n_stacks, last_ts = C.c_uint64(0), C.c_uint64(0)
+    rc = f(C.c_void_p(events.ctypes.data), C.c_uint64(len(events)), C.c_uint32(n_units),
+           C.c_void_p(out.ctypes.data), C.c_uint64(cap), _p(n_slices, C.c_uint64),
+           _p(stats, C.c_uint64), C.c_void_p(stacks.ctypes.data), C.c_uint64(stack_cap),
+           C.byref(n_stacks), C.byref(last_ts))
+    return {"rc": rc, "slices": [out[u, :int(n_slices[u])].copy() for u in range(n_units)],
+            "stats": dict(zip(SLICER_STAT_KEYS, (int(x) for x in stats))),
+            "stacks": stacks[:n_stacks.value].copy(), "last_ts": last_ts.value}
