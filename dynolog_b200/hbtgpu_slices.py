@@ -1,0 +1,135 @@
+"""ctypes binding of the count-interval x slice intersection in libhbtgpu.so (include/hbtgpu.h,
+section "Count intervals x tagstack slices").  Plumbing for tests and probes; no CPU fallback."""
+import ctypes as C
+
+import numpy as np
+
+from . import hbtgpu
+from .hbtgpu import HbtGpuError
+
+SLICE_DTYPE = np.dtype([("tstamp", "<u8"), ("duration", "<u8"), ("stack_id", "<u8"),
+                        ("swin_type", "u1"), ("swout_type", "u1"), ("pad", "u1", (6,))])
+UNIT_DTYPE = np.dtype([("n_intervals", "<u8"), ("n_slices", "<u8"), ("mark", "<u8"), ("status", "<i8"),
+                       ("err_interval", "<u8"), ("exact_path", "<u4"), ("pad", "<u4")])
+assert SLICE_DTYPE.itemsize == 32 and UNIT_DTYPE.itemsize == 48
+
+TRIM, ABORT_ON_MISSING, DEVICE_INPUT, FORCE_EXACT = 1, 2, 4, 8
+
+ABI_SYMBOLS = [
+    "hbtgpu_islice_create", "hbtgpu_islice_destroy", "hbtgpu_islice_last_error",
+    "hbtgpu_islice_release", "hbtgpu_islice_get_units", "hbtgpu_islice_get",
+    "hbtgpu_islice_device_view", "hbtgpu_islice_last_ms",
+]
+
+
+class View(C.Structure):
+    _fields_ = [("slices", C.c_void_p), ("unit_base", C.c_void_p), ("interval_offset", C.c_void_p),
+                ("interval_count", C.c_void_p), ("n_units", C.c_uint32)]
+
+
+_ready = False
+
+
+def _lib():
+    global _ready
+    L = hbtgpu.lib()
+    if not _ready:
+        L.hbtgpu_islice_create.restype = C.c_void_p
+        L.hbtgpu_islice_create.argtypes = [C.c_int]
+        L.hbtgpu_islice_destroy.restype = None
+        L.hbtgpu_islice_destroy.argtypes = [C.c_void_p]
+        L.hbtgpu_islice_last_error.restype = C.c_char_p
+        L.hbtgpu_islice_last_error.argtypes = [C.c_void_p]
+        L.hbtgpu_islice_last_ms.restype = C.c_float
+        L.hbtgpu_islice_last_ms.argtypes = [C.c_void_p]
+        L.hbtgpu_islice_release.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
+                                            C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p,
+                                            C.c_void_p]
+        L.hbtgpu_islice_get_units.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        L.hbtgpu_islice_get.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p,
+                                        C.c_uint64]
+        L.hbtgpu_islice_device_view.argtypes = [C.c_void_p, C.c_void_p]
+        _ready = True
+    return L
+
+
+class IntervalSlicer:
+    """Batch form of tagstack::IntervalSlicer + the releaseCountData_ row loop: all comp units of a
+    window in one call."""
+
+    def __init__(self, device=0):
+        self.L = _lib()
+        self.h = self.L.hbtgpu_islice_create(device)
+        if not self.h:
+            raise HbtGpuError(-19, "hbtgpu_islice_create failed (no CUDA device? there is no CPU fallback)")
+        self.n_units = 0
+
+    def close(self):
+        if self.h:
+            self.L.hbtgpu_islice_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise HbtGpuError(rc, self.L.hbtgpu_islice_last_error(self.h).decode())
+
+    def release(self, slices, slice_begin, rows, row_begin, stop_ts, flags, marks, row_stride=None):
+        """slices: SLICE_DTYPE array (all units), rows: [n, stride] u64; *_begin: [n_units + 1].
+        marks: [n_units] u64, updated in place.  Returns the per-unit summary (UNIT_DTYPE)."""
+        slices = np.ascontiguousarray(slices, dtype=SLICE_DTYPE)
+        rows = np.ascontiguousarray(rows, dtype=np.uint64)
+        if rows.ndim == 1:
+            rows = rows.reshape(-1, row_stride or 2)
+        slice_begin = np.ascontiguousarray(slice_begin, dtype=np.uint64)
+        row_begin = np.ascontiguousarray(row_begin, dtype=np.uint64)
+        n_units = len(slice_begin) - 1
+        assert len(row_begin) == n_units + 1 and len(marks) == n_units and marks.dtype == np.uint64
+        units = np.zeros(n_units, UNIT_DTYPE)
+        self._check(self.L.hbtgpu_islice_release(
+            self.h, slices.ctypes.data, slice_begin.ctypes.data, rows.ctypes.data, rows.shape[1],
+            row_begin.ctypes.data, n_units, stop_ts, flags, marks.ctypes.data, units.ctypes.data))
+        self.n_units = n_units
+        self._units = units
+        return units
+
+    def release_device(self, d_slices, slice_begin, d_rows, row_stride, row_begin, stop_ts, flags, marks):
+        """Same with slices / rows already on the device (raw pointers)."""
+        slice_begin = np.ascontiguousarray(slice_begin, dtype=np.uint64)
+        row_begin = np.ascontiguousarray(row_begin, dtype=np.uint64)
+        n_units = len(slice_begin) - 1
+        units = np.zeros(n_units, UNIT_DTYPE)
+        self._check(self.L.hbtgpu_islice_release(
+            self.h, d_slices, slice_begin.ctypes.data, d_rows, row_stride, row_begin.ctypes.data, n_units,
+            stop_ts, flags | DEVICE_INPUT, marks.ctypes.data, units.ctypes.data))
+        self.n_units = n_units
+        self._units = units
+        return units
+
+    def units(self):
+        u = np.zeros(self.n_units, UNIT_DTYPE)
+        self._check(self.L.hbtgpu_islice_get_units(self.h, u.ctypes.data, self.n_units))
+        return u
+
+    def get(self, unit):
+        """(counts per interval, slices in interval order) of one unit."""
+        u = self._units[unit]
+        counts = np.zeros(max(1, int(u["n_intervals"])), np.uint32)
+        out = np.zeros(max(1, int(u["n_slices"])), SLICE_DTYPE)
+        self._check(self.L.hbtgpu_islice_get(self.h, unit, counts.ctypes.data, len(counts), out.ctypes.data,
+                                             len(out)))
+        return counts[:int(u["n_intervals"])], out[:int(u["n_slices"])]
+
+    def device_view(self):
+        v = View()
+        self._check(self.L.hbtgpu_islice_device_view(self.h, C.byref(v)))
+        return v
+
+    @property
+    def last_ms(self):
+        return float(self.L.hbtgpu_islice_last_ms(self.h))

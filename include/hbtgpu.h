@@ -526,6 +526,84 @@ float hbtgpu_cs_vids_last_ms(const hbtgpu_cs_vids* v);   /* device time of the l
 int hbtgpu_cs_vids_get(hbtgpu_cs_vids* v, hbtgpu_cs_thread* threads, uint64_t thread_cap,
                        hbtgpu_cs_name* names, uint64_t name_cap);
 
+/* ---- Count intervals x tagstack slices (IntervalSlicer side) ---------
+ *
+ * Replaces, for a whole window of count rows at once,
+ *   IntervalSlicer::makeIntervalIntersectingSlices   hbt/src/tagstack/IntervalSlicer.cpp:52-188
+ *   the row loop of TraceMonitor::releaseCountData_  hbt/src/mon/TraceMonitor.cpp:52-96
+ *   IntervalSlicer::consumeSlices                    IntervalSlicer.cpp:195-217 (one row)
+ * For every comp unit (CPU) u the caller hands over the slices its IntervalSlicer holds
+ * (slices[slice_begin[u] .. slice_begin[u+1]), in ring order) and the count rows of the window
+ * (rows[row_begin[u] .. row_begin[u+1]), row_stride u64 words each, word 0 = tstamp, word 1 =
+ * duration: the rows hbtgpu_get_rows returns).  Row by row, in order, exactly as the reference:
+ * stop in front of the first row with tstamp + duration >= stop_ts; otherwise intersect
+ * [tstamp, tstamp + duration) with the slices not yet consumed (marks[u] = the consumer mark,
+ * an index into the unit's slices), trimming the first and last slice to the interval
+ * (HBTGPU_ISLICE_TRIM -> TransitionType::Analysis) and giving up on the interval when the
+ * slices do not cover it (HBTGPU_ISLICE_ABORT_ON_MISSING); the mark advances by the slices the
+ * interval consumed.  Results stay on the device until fetched.
+ *
+ * The reference walks slice by slice; here every interval finds its slices by binary search and
+ * the chain of marks is resolved with a parallel scan.  Units whose input
+ * breaks what that needs (slices out of order or overlapping, rows going back in time, ...) are
+ * walked exactly as the reference does by one thread, so results are the reference's on ANY
+ * input.  Where the reference throws (zero-length interval, zero-length slice in the skipped
+ * prefix, durations exceeding the interval: IntervalSlicer.cpp:64,77,175-183) the unit's status
+ * is -EINVAL and err_interval names the row.
+ */
+
+/* tagstack::slice::Slice, hbt/src/tagstack/Slicer.h:30-49: same size and field order */
+typedef struct {
+  uint64_t tstamp;
+  uint64_t duration;
+  uint64_t stack_id;
+  uint8_t swin_type;  /* Slice::TransitionType, Slicer.h:31-43: 0 NA, 1 Analysis, 2 ThreadPreempted, 3 ThreadYield, 4 PhaseChange */
+  uint8_t swout_type;
+  uint8_t pad[6];
+} hbtgpu_slice;
+
+#define HBTGPU_ISLICE_TRIM 0x1u
+#define HBTGPU_ISLICE_ABORT_ON_MISSING 0x2u
+#define HBTGPU_ISLICE_DEVICE_INPUT 0x4u  /* slices and rows are device pointers (the begin arrays and marks stay host) */
+#define HBTGPU_ISLICE_FORCE_EXACT 0x8u   /* walk every unit serially (the fallback path), for tests */
+
+typedef struct {
+  uint64_t n_intervals;   /* rows processed (the stop_ts rule, TraceMonitor.cpp:63-70) */
+  uint64_t n_slices;      /* slices in all its intervals */
+  uint64_t mark;          /* consumer mark afterwards */
+  int64_t status;         /* 0, or -EINVAL where the reference throws */
+  uint64_t err_interval;  /* the row it throws on (~0 if none) */
+  uint32_t exact_path;    /* 1 if the unit took the serial walk */
+  uint32_t pad;
+} hbtgpu_islice_unit;
+
+typedef struct hbtgpu_islice_ctx hbtgpu_islice_ctx;
+hbtgpu_islice_ctx* hbtgpu_islice_create(int device);
+void hbtgpu_islice_destroy(hbtgpu_islice_ctx* ctx);
+const char* hbtgpu_islice_last_error(hbtgpu_islice_ctx* ctx);
+/* marks: [n_units] in/out.  units: [n_units] out (may be NULL; hbtgpu_islice_get_units later). */
+int hbtgpu_islice_release(hbtgpu_islice_ctx* ctx, const hbtgpu_slice* slices, const uint64_t* slice_begin,
+                          const uint64_t* rows, uint64_t row_stride, const uint64_t* row_begin,
+                          uint32_t n_units, uint64_t stop_ts, uint32_t flags, uint64_t* marks,
+                          hbtgpu_islice_unit* units);
+int hbtgpu_islice_get_units(hbtgpu_islice_ctx* ctx, hbtgpu_islice_unit* units, uint32_t cap);
+/* One unit's PerIntervalSlices (IntervalSlicer.h:17): counts[k] = slices of interval k (0 = the
+ * empty entry pushed for a nullptr result, TraceMonitor.cpp:82-85), slices = all of them in
+ * interval order.  Either pair may be NULL/0. */
+int hbtgpu_islice_get(hbtgpu_islice_ctx* ctx, uint32_t unit, uint32_t* counts, uint64_t counts_cap,
+                      hbtgpu_slice* slices, uint64_t slices_cap);
+/* Device view for consumers on the GPU: unit u's intervals are interval_offset/interval_count
+ * [row_begin[u] + k] (offset relative to unit_base[u]), its slices out[unit_base[u] + ...]. */
+typedef struct {
+  const hbtgpu_slice* slices;
+  const uint64_t* unit_base;        /* [n_units] */
+  const uint32_t* interval_offset;  /* [total rows] */
+  const uint32_t* interval_count;   /* [total rows] */
+  uint32_t n_units;
+} hbtgpu_islice_view;
+int hbtgpu_islice_device_view(hbtgpu_islice_ctx* ctx, hbtgpu_islice_view* view);
+float hbtgpu_islice_last_ms(const hbtgpu_islice_ctx* ctx); /* device time of the kernels of the last release */
+
 #ifdef __cplusplus
 }
 #endif

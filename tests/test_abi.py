@@ -30,8 +30,8 @@ def test_library_exports_every_declared_symbol(built):
     assert len(decl) >= 25
     for s in decl:
         assert hasattr(lib, s), f"{s} declared in include/hbtgpu.h but not exported"
-    from dynolog_b200 import hbtgpu_cs
-    assert sorted(built.ABI_SYMBOLS + hbtgpu_cs.ABI_SYMBOLS) == decl, "ctypes binding lists out of sync with the header"
+    from dynolog_b200 import hbtgpu_cs, hbtgpu_slices
+    assert sorted(built.ABI_SYMBOLS + hbtgpu_cs.ABI_SYMBOLS + hbtgpu_slices.ABI_SYMBOLS) == decl, "ctypes binding lists out of sync with the header"
 
 
 def test_struct_sizes_match_header(built, tmp_path):
@@ -151,3 +151,14 @@ def test_synth_matches_oracles(port_oracle):
                 assert a["counters"] == b["counters"]
                 assert np.array_equal(a["buckets"], b["buckets"])
                 assert np.array_equal(a["rows"], b["rows"])
+
+
+def test_slices_struct_sizes_match_header(built, tmp_path):
+    from dynolog_b200 import hbtgpu_slices as sl
+    src = tmp_path / "szsl.c"
+    src.write_text('#include <stdio.h>\n#include "hbtgpu.h"\nint main(){printf("%zu %zu %zu\\n",'
+                   "sizeof(hbtgpu_slice),sizeof(hbtgpu_islice_unit),sizeof(hbtgpu_islice_view));return 0;}\n")
+    exe = tmp_path / "szsl"
+    subprocess.check_call(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    sizes = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert sizes == [sl.SLICE_DTYPE.itemsize, sl.UNIT_DTYPE.itemsize, ctypes.sizeof(sl.View)]
