@@ -6,11 +6,10 @@
 // skip slices that end before the interval, take slices that start before its end, trim the
 // first and the last, and the next row starts where this one stopped.
 //
-// Parallel form (one CTA per comp unit, a tile of NT rows per step).  Let t_j, e_j = t_j + d_j
-// be start and end of slice j.  When the unit's slices are time ordered and disjoint
-// (d_j > 0, t_j >= e_{j-1}: what tagstack::Slicer writes) and its rows move forward in time
-// (d > 0, next tstamp >= this end: what CpuCountSampleGenerator writes), e and t are strictly
-// increasing, so for the interval [T, Tend):
+// Parallel form.  Let t_j, e_j = t_j + d_j be start and end of slice j.  When a unit's slices
+// are time ordered and disjoint (d_j > 0, t_j >= e_{j-1}: what tagstack::Slicer writes) and its
+// rows move forward in time (next tstamp >= this end: what CpuCountSampleGenerator writes),
+// e and t are strictly increasing, so for the interval [T, Tend):
 //   * the walk's skip loop stops at p = max(mark, lb) with lb = #{j : e_j < T}  (binary search);
 //   * the take loop stops at r = max(p, #{j : t_j < Tend})   (trim)
 //                      or at r = max(p, #{j : e_j <= Tend})  (no trim);
@@ -21,16 +20,25 @@
 //     Tend; a row that produced none leaves it alone.
 // The mark can exceed lb only by one, and only when a slice ends exactly at T and the previous
 // row consumed it (then the row starts at lb + 1; otherwise that slice is taken with length 0,
-// which the reference does too).  So every row is evaluated for both starts, "does row k+1
-// start one further" is a function {0,1} -> {0,1} of the same question for row k, and an
-// inclusive scan under function composition settles all rows of a tile at once.  A prefix sum
-// of the slice counts gives every row its place in the output, and the tile's slices are
-// copied by all threads (one slice each per step, the owning row found by binary search in
-// shared memory).
-//
-// Units that break the preconditions, or whose mark is ahead of the first row, are walked by
-// one thread exactly as the reference does (exact_walk) and emitted by k_islice_emit_exact, so
-// the results are the reference's on any input.  Scratch: G (8 B per slice).
+// which the reference does too).  So a row depends on its predecessor only if a slice ends
+// exactly on its start, and a chain of such rows ends at the first row without one: a row in
+// that situation re-evaluates the (at most LOOKBACK) rows of its chain; every other row is
+// independent.  That makes the work a grid over (unit, tile of NT rows):
+//   k_islice_validate  (unit, tile of VT slices): order / overlap / zero length, tile-local G
+//   k_islice_vscan     per unit: exclusive scan of the tiles' gap sums (G = local + base)
+//   k_islice_bounds    one thread per row tile: the slice window the tile's rows can touch
+//   k_islice_rows      (unit, tile of NT rows): stages the tile's slice window {t, e, G} in
+//                      shared memory (one coalesced pass; windows beyond WMAX slices are
+//                      searched in global memory), resolves every row: first slice, count,
+//                      new mark, throws; tile totals
+//   k_islice_rscan     per unit: exclusive scan of the tile totals, the unit's summary; units
+//                      that broke a precondition anywhere are walked here by one thread exactly
+//                      as the reference does (exact_walk), so results are the reference's on
+//                      ANY input
+//   k_islice_emit      (unit, tile of NT rows): output offsets, copies and trims the slices
+//                      (one slice per thread and step, the owning row found by binary search
+//                      in shared memory)
+// Scratch: G (8 B per slice), per-tile sums, the per-row plan (first, count, offset).
 #include <cuda_runtime.h>
 #include <errno.h>
 #include <stdarg.h>
@@ -46,16 +54,31 @@
 
 namespace {
 
-constexpr int NT = 512;  // threads per CTA = rows per tile
+constexpr int NT = 512;  // threads per CTA = rows per row tile
 constexpr int NW = NT / 32;
+constexpr int VT_SHIFT = 12;
+constexpr int VT = 1 << VT_SHIFT;  // slices per validation tile
+constexpr int WMAX = 2048;         // slices of a row tile's window staged in shared memory
+constexpr int LOOKBACK = 8;        // longest chain of rows that start exactly on a slice end
 constexpr uint8_t TT_ANALYSIS = 1;  // Slice::TransitionType::Analysis, Slicer.h:36
 constexpr uint64_t NONE = ~0ull;
+
+enum : uint32_t { UF_BAD_SLICES = 1, UF_BAD_ROWS = 2, UF_CHAIN = 4, UF_MARK = 8 };
 
 struct Unit {
   uint64_t s0, ns;  // first slice, number of slices
   uint64_t r0, K;   // first row, number of rows
-  uint64_t out0, out_cap;
+  uint64_t out0;    // first output slice (dense, set once the counts are known)
   uint64_t mark;
+  uint32_t vt0, rt0;  // first validation tile, first row tile
+};
+
+struct UState {
+  uint32_t flags;
+  uint32_t pad;
+  unsigned long long n_stop;  // first row the stop rule cuts
+  unsigned long long err_k;   // first row the reference throws on
+  unsigned long long max_c;   // largest new mark
 };
 
 struct Row {
@@ -74,56 +97,69 @@ __device__ __forceinline__ Row ld_row(const uint64_t* rows, uint64_t stride, uin
   return Row{p[0], p[1]};
 }
 
-// #{j in [0, n) : e_j < x}
-__device__ __forceinline__ uint32_t count_end_lt(const hbtgpu_slice* S, uint32_t n, uint64_t x) {
+// last unit whose first tile is <= tile (units without tiles share their successor's first tile)
+template <bool ROWS>
+__device__ __forceinline__ uint32_t find_unit(const Unit* units, uint32_t n, uint32_t tile) {
   uint32_t lo = 0, hi = n;
-  while (lo < hi) {
+  while (hi - lo > 1) {
     const uint32_t mid = (lo + hi) >> 1;
-    if (slice_end(S + mid) < x) lo = mid + 1;
-    else hi = mid;
-  }
-  return lo;
-}
-// #{j : e_j <= x}
-__device__ __forceinline__ uint32_t count_end_le(const hbtgpu_slice* S, uint32_t n, uint64_t x) {
-  uint32_t lo = 0, hi = n;
-  while (lo < hi) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (slice_end(S + mid) <= x) lo = mid + 1;
-    else hi = mid;
-  }
-  return lo;
-}
-// #{j : t_j < x}
-__device__ __forceinline__ uint32_t count_start_lt(const hbtgpu_slice* S, uint32_t n, uint64_t x) {
-  uint32_t lo = 0, hi = n;
-  while (lo < hi) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (S[mid].tstamp < x) lo = mid + 1;
+    if ((ROWS ? units[mid].rt0 : units[mid].vt0) <= tile) lo = mid;
     else hi = mid;
   }
   return lo;
 }
 
+// A unit's slices in global memory.  G(j) = tile-local prefix + the tile's base.
+struct GAcc {
+  const hbtgpu_slice* S;
+  const uint64_t* Gl;
+  const uint64_t* vbase;
+  __device__ __forceinline__ uint64_t t(uint32_t j) const { return S[j].tstamp; }
+  __device__ __forceinline__ uint64_t e(uint32_t j) const { return slice_end(S + j); }
+  __device__ __forceinline__ uint64_t G(uint32_t j) const { return Gl[j] + vbase[j >> VT_SHIFT]; }
+};
+// The window [lo, lo + W) of them in shared memory.  Every index the parallel form touches lies
+// inside for rows and slices that meet the preconditions; for input that is being rejected
+// anyway the clamp keeps the reads in bounds.
+struct WAcc {
+  const uint64_t *wt, *we, *wG;
+  uint32_t lo, Wm1;
+  __device__ __forceinline__ uint32_t at(uint32_t j) const { return min(j - lo, Wm1); }
+  __device__ __forceinline__ uint64_t t(uint32_t j) const { return wt[at(j)]; }
+  __device__ __forceinline__ uint64_t e(uint32_t j) const { return we[at(j)]; }
+  __device__ __forceinline__ uint64_t G(uint32_t j) const { return wG[at(j)]; }
+};
+
+// first j in [a, b) with e_j >= x (b if none) = #{j : e_j < x} when the answer lies in [a, b]
+template <class A>
+__device__ __forceinline__ uint32_t first_end_ge(const A& acc, uint32_t a, uint32_t b, uint64_t x) {
+  while (a < b) {
+    const uint32_t mid = (a + b) >> 1;
+    if (acc.e(mid) < x) a = mid + 1;
+    else b = mid;
+  }
+  return a;
+}
+template <class A>
+__device__ __forceinline__ uint32_t first_end_gt(const A& acc, uint32_t a, uint32_t b, uint64_t x) {
+  while (a < b) {
+    const uint32_t mid = (a + b) >> 1;
+    if (acc.e(mid) <= x) a = mid + 1;
+    else b = mid;
+  }
+  return a;
+}
+template <class A>
+__device__ __forceinline__ uint32_t first_start_ge(const A& acc, uint32_t a, uint32_t b, uint64_t x) {
+  while (a < b) {
+    const uint32_t mid = (a + b) >> 1;
+    if (acc.t(mid) < x) a = mid + 1;
+    else b = mid;
+  }
+  return a;
+}
+
 // ---- block primitives (NT threads, all must call) ------------------------------------------
-__device__ __forceinline__ uint64_t block_min_u64(uint64_t v, uint64_t* sh) {
-  for (int d = 16; d; d >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, d));
-  __syncthreads();
-  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
-  __syncthreads();
-  uint64_t r = sh[0];
-  for (int w = 1; w < NW; ++w) r = min(r, sh[w]);
-  return r;
-}
-__device__ __forceinline__ uint64_t block_max_u64(uint64_t v, uint64_t* sh) {
-  for (int d = 16; d; d >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, d));
-  __syncthreads();
-  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
-  __syncthreads();
-  uint64_t r = sh[0];
-  for (int w = 1; w < NW; ++w) r = max(r, sh[w]);
-  return r;
-}
 // inclusive prefix sum; *total = sum over the block
 __device__ __forceinline__ uint64_t block_incl_sum_u64(uint64_t v, uint64_t* sh, uint64_t* total) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -134,34 +170,17 @@ __device__ __forceinline__ uint64_t block_incl_sum_u64(uint64_t v, uint64_t* sh,
   __syncthreads();
   if (lane == 31) sh[w] = v;
   __syncthreads();
-  uint64_t base = 0, tot = 0;
-  for (int i = 0; i < NW; ++i) {
-    if (i < w) base += sh[i];
-    tot += sh[i];
-  }
-  *total = tot;
-  return v + base;
-}
-// {0,1} -> {0,1} functions packed as f(0) | f(1) << 1; then(a, b)(v) = b(a(v))
-__device__ __forceinline__ uint32_t fn_then(uint32_t a, uint32_t b) {
-  return ((b >> (a & 1u)) & 1u) | (((b >> ((a >> 1) & 1u)) & 1u) << 1);
-}
-constexpr uint32_t FN_ID = 2u;
-// EXCLUSIVE scan under composition: the composition of the functions of all earlier threads
-__device__ __forceinline__ uint32_t block_excl_fn(uint32_t f, uint64_t* sh) {
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int d = 1; d < 32; d <<= 1) {
-    const uint32_t o = __shfl_up_sync(0xffffffffu, f, d);
-    if (lane >= d) f = fn_then(o, f);
+  if (w == 0) {  // the warp totals, scanned by the first warp
+    uint64_t t = lane < NW ? sh[lane] : 0;
+    for (int d = 1; d < NW; d <<= 1) {
+      const uint64_t o = __shfl_up_sync(0xffffffffu, t, d);
+      if (lane >= d) t += o;
+    }
+    if (lane < NW) sh[lane] = t;
   }
   __syncthreads();
-  if (lane == 31) sh[w] = f;
-  __syncthreads();
-  uint32_t base = FN_ID;
-  for (int i = 0; i < w; ++i) base = fn_then(base, static_cast<uint32_t>(sh[i]));
-  uint32_t ex = __shfl_up_sync(0xffffffffu, f, 1);
-  if (lane == 0) ex = FN_ID;
-  return fn_then(base, ex);
+  *total = sh[NW - 1];
+  return v + (w ? sh[w - 1] : 0);
 }
 
 // One slice of an interval's answer: slice j, the i-th of cnt, trimmed as IntervalSlicer.cpp:
@@ -281,239 +300,403 @@ __device__ void exact_walk(const hbtgpu_slice* S, uint64_t ns, const uint64_t* r
   R->pad = 0;
 }
 
+
 struct Eval {
   bool null_res, thrown;
   uint32_t p, r, c;
 };
 
-__global__ void __launch_bounds__(NT)
-k_islice_unit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
-              const Unit* __restrict__ units, hbtgpu_islice_unit* __restrict__ results, uint64_t* __restrict__ Gall,
-              uint32_t* __restrict__ ioff_all, uint32_t* __restrict__ icnt_all, uint32_t* __restrict__ ifirst_all,
-              hbtgpu_slice* __restrict__ out_all, uint64_t stop_ts, uint32_t flags) {
-  __shared__ uint64_t sh_red[32];
-  __shared__ uint64_t sh_T[NT], sh_Tend[NT];
-  __shared__ uint32_t sh_excl[NT + 1], sh_p[NT], sh_lb[NT + 1];
-  __shared__ uint32_t sh_flag;
+// One row of the parallel form, started at slice p (lb or lb + 1).  x = where the take loop
+// stops, q = #{t_j < Tend} (see the file comment).
+template <class A>
+__device__ __forceinline__ Eval eval_row(const A& a, uint32_t ns, uint64_t T, uint64_t D, uint64_t Tend, uint32_t p,
+                                         uint32_t x, uint32_t q, bool trim, bool abort_missing) {
+  Eval e{true, false, p, p, 0};
+  if (p >= ns) return e;                       // IntervalSlicer.cpp:85-89
+  const uint64_t tp = a.t(p);
+  if (abort_missing && tp > T) return e;       // :91-95
+  const uint32_t r = max(p, x);
+  if (r == p) return e;                        // :128-133
+  const uint64_t Gp = a.G(p);
+  if (abort_missing) {
+    // the walk compares every slice it looks at with its predecessor's end (:106-110), including
+    // the one the no-trim break (:113-115) stops on
+    uint32_t hi = trim ? r - 1 : min(r, max(p, q) - 1);
+    hi = min(hi, ns - 1);  // (only reached with rows or slices that are being rejected anyway)
+    if (a.G(hi) != Gp) return e;
+  }
+  const uint64_t er = a.e(r - 1);
+  if (abort_missing && er < Tend) return e;    // :139-143
+  e.null_res = false;
+  e.r = r;
+  e.c = r - (er > Tend ? 1u : 0u);             // :161-164
+  if (!trim) {
+    const uint64_t sumdur = (er - tp) - (a.G(r - 1) - Gp);
+    if (sumdur > D) e.thrown = true;           // :175-177
+  }
+  return e;
+}
 
-  const int tid = threadIdx.x;
-  const Unit U = units[blockIdx.x];
-  const hbtgpu_slice* S = slices + U.s0;
-  uint64_t* G = Gall + U.s0;
-  const uint64_t* rows = rows_all + U.r0 * stride;
-  uint32_t* ioff = ioff_all + U.r0;
-  uint32_t* icnt = icnt_all + U.r0;
-  uint32_t* ifirst = ifirst_all + U.r0;
-  hbtgpu_slice* out = out_all + U.out0;
-  hbtgpu_islice_unit* R = results + blockIdx.x;
-  const bool trim = flags & HBTGPU_ISLICE_TRIM, abort_missing = flags & HBTGPU_ISLICE_ABORT_ON_MISSING;
-  const uint32_t ns = static_cast<uint32_t>(U.ns);
-  const uint64_t K = U.K;
-
-  // ---- pass 1, rows: where the stop rule cuts, the first zero length, the first row that
-  // wraps or whose successor starts before it ends
-  uint64_t n_int = K, z = K, mw = K, mp = K;
-  for (uint64_t k = tid; k < K; k += NT) {
-    const Row rw = ld_row(rows, stride, k);
+// Does row k (which starts exactly on a slice end) find that slice already consumed?  Walks
+// back to the first row of its chain, then forward again.  acc / [a, b) / row_at serve rows
+// k_min and later (a row tile's window in shared memory); *below is raised when the chain
+// reaches further back, and the caller repeats the walk in global memory.
+template <class A, class RL>
+__device__ uint32_t resolve_chain(const A& acc, uint32_t a, uint32_t b, uint32_t ns, RL row_at, uint64_t k,
+                                  uint64_t k_min, uint64_t mark, bool trim, bool abort_missing, bool* give_up,
+                                  bool* below) {
+  uint64_t j = k;
+  uint32_t bsel = 0;
+  int depth = 0;
+  for (;;) {
+    if (j == 0) {
+      bsel = mark > first_end_ge(acc, a, b, row_at(0).T) ? 1u : 0u;
+      break;
+    }
+    if (depth >= LOOKBACK) {
+      *give_up = true;
+      return 0;
+    }
+    if (j == k_min) {
+      *below = true;
+      return 0;
+    }
+    --j;
+    ++depth;
+    const uint64_t Tj = row_at(j).T;
+    const uint32_t lbj = first_end_ge(acc, a, b, Tj);
+    if (!(lbj < ns && acc.e(lbj) == Tj)) {
+      bsel = 0;
+      break;
+    }
+  }
+  for (uint64_t i = j; i < k; ++i) {
+    const Row rw = row_at(i);
     const uint64_t Tend = rw.T + rw.D;
-    if (Tend >= stop_ts) n_int = min(n_int, k);
-    if (rw.D == 0) z = min(z, k);
-    if (Tend < rw.T) mw = min(mw, k);
-    if (k + 1 < K && rows[(k + 1) * stride] < Tend) mp = min(mp, k);
+    const uint32_t lb = first_end_ge(acc, a, b, rw.T);
+    const uint32_t q = first_start_ge(acc, a, b, Tend);
+    const uint32_t x = trim ? q : first_end_gt(acc, a, b, Tend);
+    const Eval e = eval_row(acc, ns, rw.T, rw.D, Tend, lb + bsel, x, q, trim, abort_missing);
+    const uint32_t lbn = first_end_ge(acc, a, b, row_at(i + 1).T);
+    bsel = (!e.null_res && !e.thrown && e.c > lbn) ? 1u : 0u;
   }
-  n_int = block_min_u64(n_int, sh_red);
-  z = block_min_u64(z, sh_red);
-  mw = block_min_u64(mw, sh_red);
-  mp = block_min_u64(mp, sh_red);
-  const uint64_t n_eff = min(n_int, z);  // rows the fast path may evaluate; row z (if < n_int) throws
-  bool slow = (flags & HBTGPU_ISLICE_FORCE_EXACT) || mw < n_eff || mp + 1 < n_eff;
+  return bsel;
+}
 
-  // ---- pass 2, slices: order / overlap / zero length, and the gap prefix G
-  {
-    uint64_t carry = 0;
-    int bad = 0;
-    for (uint32_t base = 0; base < ns; base += NT) {
-      const uint32_t j = base + tid;
-      uint64_t gap = 0;
-      if (j < ns) {
-        const ulonglong2 td = ld_td(S + j);
-        if (td.y == 0 || td.x + td.y < td.x) bad = 1;
-        if (j > 0) {
-          const uint64_t pe = slice_end(S + j - 1);
-          if (td.x < pe) bad = 1;
-          gap = td.x - pe;
-        }
+// ---- (unit, tile of VT slices): validation and the tile-local gap prefix ---------------------
+__global__ void __launch_bounds__(NT)
+k_islice_validate(const hbtgpu_slice* __restrict__ slices, const Unit* __restrict__ units, uint32_t n_units,
+                  UState* __restrict__ ustate, uint64_t* __restrict__ Gl_all, uint64_t* __restrict__ vt_tot) {
+  __shared__ uint64_t sh_red[32];
+  const int tid = threadIdx.x;
+  const uint32_t u = find_unit<false>(units, n_units, blockIdx.x);
+  const Unit U = units[u];
+  const hbtgpu_slice* S = slices + U.s0;
+  uint64_t* Gl = Gl_all + U.s0;
+  const uint32_t ns = static_cast<uint32_t>(U.ns);
+  const uint32_t j0 = (blockIdx.x - U.vt0) << VT_SHIFT;
+  uint64_t carry = 0;
+  int bad = 0;
+  for (uint32_t i = 0; i < VT && j0 + i < ns; i += NT) {
+    const uint32_t j = j0 + i + tid;
+    uint64_t gap = 0;
+    if (j < ns) {
+      const ulonglong2 td = ld_td(S + j);
+      if (td.y == 0 || td.x + td.y < td.x) bad = 1;
+      if (j > 0) {
+        const uint64_t pe = slice_end(S + j - 1);
+        if (td.x < pe) bad = 1;
+        gap = td.x - pe;
       }
-      uint64_t tot;
-      const uint64_t incl = block_incl_sum_u64(gap, sh_red, &tot);
-      if (j < ns) G[j] = carry + incl;
-      carry += tot;
     }
-    if (__syncthreads_or(bad)) slow = true;
+    uint64_t tot;
+    const uint64_t incl = block_incl_sum_u64(gap, sh_red, &tot);
+    if (j < ns) Gl[j] = carry + incl;
+    carry += tot;
   }
+  if (__syncthreads_or(bad) && tid == 0) atomicOr(&ustate[u].flags, UF_BAD_SLICES);
+  if (tid == 0) vt_tot[blockIdx.x] = carry;
+}
 
-  // ---- the mark must not be ahead of the first row's slices
-  if (!slow && n_eff > 0) {
-    if (tid == 0) {
-      const Row rw = ld_row(rows, stride, 0);
-      sh_flag = U.mark > count_end_le(S, ns, rw.T);
+// ---- per unit: bases of the validation tiles (one warp) ---------------------------------------
+__global__ void __launch_bounds__(32)
+k_islice_vscan(const Unit* __restrict__ units, const uint64_t* __restrict__ vt_tot, uint64_t* __restrict__ vt_base) {
+  const Unit U = units[blockIdx.x];
+  const uint32_t n = static_cast<uint32_t>((U.ns + VT - 1) >> VT_SHIFT);
+  const int lane = threadIdx.x;
+  uint64_t carry = 0;
+  for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+    const uint32_t i = i0 + lane;
+    const uint64_t v = i < n ? vt_tot[U.vt0 + i] : 0;
+    uint64_t s = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint64_t o = __shfl_up_sync(0xffffffffu, s, d);
+      if (lane >= d) s += o;
     }
-    __syncthreads();
-    if (sh_flag) slow = true;
-  }
-  if (slow) {
-    if (tid == 0)
-      exact_walk(S, ns, rows, stride, K, stop_ts, trim, abort_missing, U.mark, ioff, icnt, ifirst, R);
-    return;
-  }
-
-  // ---- tiles of NT rows
-  uint64_t mark = U.mark;      // uniform
-  uint64_t run_off = 0;        // slices written so far, uniform
-  uint64_t err_k = NONE;       // first row that throws, uniform
-  if (z < n_int) err_k = z;
-  for (uint64_t k0 = 0; k0 < n_eff && err_k > k0; k0 += NT) {
-    const uint64_t k = k0 + tid;
-    const bool live = k < n_eff;
-    uint64_t T = 0, D = 0, Tend = 0;
-    uint32_t lb = ns, x = ns, q = ns;
-    bool hasB = false;
-    if (live) {
-      const Row rw = ld_row(rows, stride, k);
-      T = rw.T;
-      D = rw.D;
-      Tend = T + D;
-      lb = count_end_lt(S, ns, T);
-      hasB = lb < ns && slice_end(S + lb) == T;
-      q = count_start_lt(S, ns, Tend);
-      x = trim ? q : count_end_le(S, ns, Tend);
-    }
-    __syncthreads();  // previous tile's readers of the shared arrays are done
-    sh_lb[tid] = lb;
-    if (tid == 0) sh_lb[NT] = ns;
-
-    auto eval = [&](uint32_t p) {
-      Eval e{true, false, p, p, 0};
-      if (p >= ns) return e;
-      const ulonglong2 tdp = ld_td(S + p);
-      if (abort_missing && tdp.x > T) return e;
-      const uint32_t r = max(p, x);
-      if (r == p) return e;
-      const uint64_t Gp = G[p];
-      if (abort_missing) {
-        // the walk compares every slice it looks at with its predecessor's end, including the
-        // one the no-trim break stops on
-        const uint32_t hi = trim ? r - 1 : min(r, max(p, q) - 1);
-        if (G[hi] != Gp) return e;
-      }
-      const uint64_t er = slice_end(S + r - 1);
-      if (abort_missing && er < Tend) return e;
-      e.null_res = false;
-      e.r = r;
-      e.c = r - (er > Tend ? 1u : 0u);
-      if (!trim) {
-        const uint64_t sumdur = (er - tdp.x) - (G[r - 1] - Gp);
-        if (sumdur > D) e.thrown = true;
-      }
-      return e;
-    };
-    Eval eA{true, false, 0, 0, 0}, eB{true, false, 0, 0, 0};
-    if (live) {
-      eA = eval(lb);
-      eB = hasB ? eval(lb + 1) : eA;
-    }
-    __syncthreads();
-    // does the next row start one past ITS lb?  Only if this row produced slices and its new
-    // mark is beyond the next row's lb.
-    const uint32_t lb_next = sh_lb[tid + 1];
-    const bool last_in_tile = tid == NT - 1;
-    uint32_t f = 0;
-    if (live && !last_in_tile) {
-      const uint32_t g0 = (!eA.null_res && !eA.thrown && eA.c > lb_next) ? 1u : 0u;
-      const uint32_t g1 = (!eB.null_res && !eB.thrown && eB.c > lb_next) ? 1u : 0u;
-      f = g0 | (g1 << 1);
-    }
-    const uint32_t b_first = (k0 < n_eff && mark > sh_lb[0]) ? 1u : 0u;
-    const uint32_t ex = block_excl_fn(f, sh_red);
-    const uint32_t b = (ex >> b_first) & 1u;
-    const Eval e = b ? eB : eA;
-
-    // first throwing row of the tile (rows after it do not count)
-    uint64_t my_err = (live && e.thrown) ? k : NONE;
-    my_err = block_min_u64(my_err, sh_red);
-    if (my_err < err_k) err_k = my_err;
-    const bool counted = live && k < err_k && !e.null_res;
-    const uint32_t cnt = counted ? e.r - e.p : 0u;
-
-    uint64_t tile_total;
-    const uint64_t incl = block_incl_sum_u64(cnt, sh_red, &tile_total);
-    const uint32_t excl = static_cast<uint32_t>(incl - cnt);
-    sh_excl[tid] = excl;
-    if (tid == 0) sh_excl[NT] = static_cast<uint32_t>(tile_total);
-    sh_p[tid] = e.p;
-    sh_T[tid] = T;
-    sh_Tend[tid] = Tend;
-    if (live && k < err_k) {
-      ioff[k] = static_cast<uint32_t>(run_off + excl);
-      icnt[k] = cnt;
-      ifirst[k] = counted ? e.p : 0u;
-    }
-    const uint64_t new_mark = block_max_u64(counted ? static_cast<uint64_t>(e.c) : 0ull, sh_red);
-    mark = max(mark, new_mark);
-    __syncthreads();
-
-    // copy the tile's slices: output slot -> owning row by binary search over sh_excl
-    if (run_off + tile_total <= U.out_cap) {
-      for (uint32_t o = tid; o < tile_total; o += NT) {
-        uint32_t lo = 0, hi = NT;  // last idx with sh_excl[idx] <= o
-        while (hi - lo > 1) {
-          const uint32_t mid = (lo + hi) >> 1;
-          if (sh_excl[mid] <= o) lo = mid;
-          else hi = mid;
-        }
-        const uint32_t i = o - sh_excl[lo];
-        const uint32_t c = sh_excl[lo + 1] - sh_excl[lo];
-        emit_one(S, sh_p[lo] + i, i, c, sh_T[lo], sh_Tend[lo], trim, out + run_off + o);
-      }
-    } else {
-      err_k = min(err_k, k0);  // cannot happen for valid fast-path input (bound ns + K); reported below
-      if (tid == 0) R->pad = 1;
-    }
-    run_off += tile_total;
-  }
-
-  if (tid == 0) {
-    R->n_intervals = err_k != NONE ? err_k : n_eff;
-    R->n_slices = run_off;
-    R->mark = mark;
-    R->status = err_k != NONE ? -EINVAL : 0;
-    R->err_interval = err_k;
-    R->exact_path = 0;
+    if (i < n) vt_base[U.vt0 + i] = carry + s - v;
+    carry += __shfl_sync(0xffffffffu, s, 31);
   }
 }
 
-// Emission for units that took the serial walk: one warp per row, lanes over its slices.
-__global__ void __launch_bounds__(256)
-k_islice_emit_exact(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
-                    const Unit* __restrict__ units, const uint32_t* __restrict__ unit_ids,
-                    const hbtgpu_islice_unit* __restrict__ results, const uint32_t* __restrict__ ioff_all,
-                    const uint32_t* __restrict__ icnt_all, const uint32_t* __restrict__ ifirst_all,
-                    hbtgpu_slice* __restrict__ out_all, uint32_t flags) {
-  const uint32_t u = unit_ids[blockIdx.x];
+// ---- (unit, tile of NT rows): every row's first slice, count and new mark ---------------------
+template <class A, class RL>
+__device__ __forceinline__ void row_in_tile(const A& acc, const GAcc& g, uint32_t ns, uint32_t a, uint32_t b,
+                                            RL row_at, uint64_t k, uint64_t k0, uint64_t T, uint64_t D, uint64_t Tend,
+                                            uint64_t mark, bool trim, bool abort_missing, Eval* out, uint32_t* flags) {
+  const uint32_t lb = first_end_ge(acc, a, b, T);
+  const bool hasB = lb < ns && acc.e(lb) == T;
+  const uint32_t q = first_start_ge(acc, a, b, Tend);
+  const uint32_t x = trim ? q : first_end_gt(acc, a, b, Tend);
+  uint32_t bsel = 0;
+  if (k == 0 && mark > lb + (hasB ? 1u : 0u)) *flags |= UF_MARK;  // mark ahead of the first row's slices
+  if (hasB) {
+    bool give_up = false, below = false;
+    bsel = resolve_chain(acc, a, b, ns, row_at, k, k0, mark, trim, abort_missing, &give_up, &below);
+    if (below) bsel = resolve_chain(g, 0u, ns, ns, row_at, k, 0ull, mark, trim, abort_missing, &give_up, &below);
+    if (give_up) *flags |= UF_CHAIN;
+  }
+  *out = eval_row(acc, ns, T, D, Tend, lb + bsel, x, q, trim, abort_missing);
+}
+
+// per row tile: the slice window its rows can touch, [lo, ql + 2) with lo = #{e_j < T of its
+// first row} and ql = #{t_j < end of its last row}.  One thread per tile.
+__global__ void __launch_bounds__(128)
+k_islice_bounds(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
+                const Unit* __restrict__ units, uint32_t n_units, uint32_t n_tiles, uint32_t* __restrict__ tile_lo,
+                uint32_t* __restrict__ tile_ql) {
+  const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tile >= n_tiles) return;
+  const uint32_t u = find_unit<true>(units, n_units, tile);
   const Unit U = units[u];
+  const uint64_t* rows = rows_all + U.r0 * stride;
+  const uint32_t ns = static_cast<uint32_t>(U.ns);
+  const uint64_t k0 = static_cast<uint64_t>(tile - U.rt0) * NT;
+  const uint64_t kl = min(U.K, k0 + NT) - 1;
+  const GAcc g{slices + U.s0, nullptr, nullptr};
+  const Row rl = ld_row(rows, stride, kl);
+  tile_lo[tile] = first_end_ge(g, 0, ns, ld_row(rows, stride, k0).T);
+  tile_ql[tile] = first_start_ge(g, 0, ns, rl.T + rl.D);
+}
+
+__global__ void __launch_bounds__(NT, 3)
+k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
+              const Unit* __restrict__ units, uint32_t n_units, UState* __restrict__ ustate,
+              const uint64_t* __restrict__ Gl_all, const uint64_t* __restrict__ vt_base,
+              const uint32_t* __restrict__ tile_lo, const uint32_t* __restrict__ tile_ql,
+              uint32_t* __restrict__ icnt_all, uint32_t* __restrict__ ifirst_all, uint32_t* __restrict__ rt_tot,
+              uint64_t stop_ts, uint32_t flags) {
+  extern __shared__ __align__(16) uint64_t sh_win[];  // wt[WMAX], we[WMAX], wG[WMAX]
+  __shared__ uint64_t sh_red[32];
+  __shared__ uint64_t sh_T[NT], sh_D[NT];
+  __shared__ uint32_t sh_tot, sh_stop, sh_err, sh_maxc, sh_flags;
+
+  const int tid = threadIdx.x;
+  const uint32_t u = find_unit<true>(units, n_units, blockIdx.x);
+  const Unit U = units[u];
+  UState* st = ustate + u;
+  if ((flags & HBTGPU_ISLICE_FORCE_EXACT) || (st->flags & UF_BAD_SLICES)) return;  // the serial walk does the unit
+  const hbtgpu_slice* S = slices + U.s0;
+  const uint64_t* rows = rows_all + U.r0 * stride;
+  const bool trim = flags & HBTGPU_ISLICE_TRIM, abort_missing = flags & HBTGPU_ISLICE_ABORT_ON_MISSING;
+  const uint32_t ns = static_cast<uint32_t>(U.ns);
+  const uint64_t K = U.K;
+  const uint64_t k0 = static_cast<uint64_t>(blockIdx.x - U.rt0) * NT;
+  const uint64_t k = k0 + tid;
+  const bool live = k < K;
+  const GAcc g{S, Gl_all + U.s0, vt_base + U.vt0};
+
+  uint64_t T = 0, D = 0, Tend = 0;
+  uint32_t uflags = 0;
+  bool cut = false;
+  if (live) {
+    const Row rw = ld_row(rows, stride, k);
+    T = rw.T;
+    D = rw.D;
+    Tend = T + D;
+    cut = Tend >= stop_ts;  // TraceMonitor.cpp:63-70
+    // rows must move forward in time (all of them: then the stop rule cuts a suffix)
+    if (Tend < T || (k + 1 < K && rows[(k + 1) * stride] < Tend)) uflags |= UF_BAD_ROWS;
+  }
+  sh_T[tid] = T;
+  sh_D[tid] = D;
+  if (tid == 0) {
+    sh_tot = 0;
+    sh_stop = 0xffffffffu;
+    sh_err = 0xffffffffu;
+    sh_maxc = 0;
+    sh_flags = 0;
+  }
+  // rows of this tile come from shared memory, earlier ones (chains across the tile edge) from global
+  auto row_at = [&](uint64_t kk) { return kk >= k0 ? Row{sh_T[kk - k0], sh_D[kk - k0]} : ld_row(rows, stride, kk); };
+  const bool zero_len = live && !cut && D == 0;  // IntervalSlicer.cpp:64
+  const bool act = live && !cut && D != 0;
+  Eval e{true, false, 0, 0, 0};
+  if (__syncthreads_or(act)) {
+    const uint32_t lo = tile_lo[blockIdx.x], ql = tile_ql[blockIdx.x];
+    const uint32_t hiw = min(ns, ql + 2);
+    const uint32_t W = hiw > lo ? hiw - lo : 0;
+    if (W != 0 && W <= WMAX) {
+      uint64_t *wt = sh_win, *we = sh_win + WMAX, *wG = sh_win + 2 * WMAX;
+      for (uint32_t i = tid; i < W; i += NT) {
+        const ulonglong2 td = ld_td(S + lo + i);
+        wt[i] = td.x;
+        we[i] = td.x + td.y;
+      }
+      __syncthreads();
+      // gap prefix over the window: each thread owns c consecutive slices
+      const uint32_t c = (W + NT - 1) / NT;  // <= WMAX / NT
+      const uint32_t i0 = tid * c;
+      uint64_t loc[WMAX / NT];
+      uint64_t sum = 0;
+#pragma unroll
+      for (uint32_t j = 0; j < WMAX / NT; ++j) {
+        const uint32_t i = i0 + j;
+        if (j < c && i > 0 && i < W) sum += wt[i] - we[i - 1];
+        loc[j] = sum;
+      }
+      uint64_t tot;
+      const uint64_t base = block_incl_sum_u64(sum, sh_red, &tot) - sum;
+#pragma unroll
+      for (uint32_t j = 0; j < WMAX / NT; ++j)
+        if (j < c && i0 + j < W) wG[i0 + j] = base + loc[j];
+      __syncthreads();
+      const WAcc w{wt, we, wG, lo, W - 1};
+      if (act) row_in_tile(w, g, ns, lo, min(ns, ql + 1), row_at, k, k0, T, D, Tend, U.mark, trim, abort_missing, &e, &uflags);
+    } else {
+      if (act) row_in_tile(g, g, ns, 0u, ns, row_at, k, k0, T, D, Tend, U.mark, trim, abort_missing, &e, &uflags);
+    }
+  }
+  const bool counted = act && !e.null_res && !e.thrown;
+  const uint32_t cnt = counted ? e.r - e.p : 0u;
+  if (live) {
+    icnt_all[U.r0 + k] = cnt;
+    ifirst_all[U.r0 + k] = counted ? e.p : 0u;
+  }
+  // tile sums: warp reductions, then one shared atomic per warp
+  {
+    const uint32_t s = __reduce_add_sync(0xffffffffu, cnt);
+    const uint32_t m1 = __reduce_min_sync(0xffffffffu, cut ? static_cast<uint32_t>(tid) : 0xffffffffu);
+    const uint32_t m2 = __reduce_min_sync(0xffffffffu, (zero_len || (act && e.thrown)) ? static_cast<uint32_t>(tid) : 0xffffffffu);
+    const uint32_t mx = __reduce_max_sync(0xffffffffu, counted ? e.c : 0u);
+    const uint32_t fl = __reduce_or_sync(0xffffffffu, uflags);
+    if ((tid & 31) == 0) {
+      if (s) atomicAdd(&sh_tot, s);
+      if (m1 != 0xffffffffu) atomicMin(&sh_stop, m1);
+      if (m2 != 0xffffffffu) atomicMin(&sh_err, m2);
+      if (mx) atomicMax(&sh_maxc, mx);
+      if (fl) atomicOr(&sh_flags, fl);
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    rt_tot[blockIdx.x] = sh_tot;
+    if (sh_stop != 0xffffffffu) atomicMin(&st->n_stop, static_cast<unsigned long long>(k0 + sh_stop));
+    if (sh_err != 0xffffffffu) atomicMin(&st->err_k, static_cast<unsigned long long>(k0 + sh_err));
+    if (sh_maxc) atomicMax(&st->max_c, static_cast<unsigned long long>(sh_maxc));
+    if (sh_flags) atomicOr(&st->flags, sh_flags);
+  }
+}
+
+// ---- per unit: bases of the row tiles, the summary; the serial walk for units that need it ----
+__global__ void __launch_bounds__(NT)
+k_islice_rscan(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
+               const Unit* __restrict__ units, const UState* __restrict__ ustate, const uint32_t* __restrict__ rt_tot,
+               uint64_t* __restrict__ rt_base, uint32_t* __restrict__ ioff_all, uint32_t* __restrict__ icnt_all,
+               uint32_t* __restrict__ ifirst_all, hbtgpu_islice_unit* __restrict__ results, uint64_t stop_ts,
+               uint32_t flags) {
+  __shared__ uint64_t sh_red[32];
+  __shared__ hbtgpu_islice_unit sh_R;
+  const int tid = threadIdx.x;
+  const Unit U = units[blockIdx.x];
+  const UState st = ustate[blockIdx.x];
+  const uint32_t n_tiles = static_cast<uint32_t>((U.K + NT - 1) / NT);
+  const bool trim = flags & HBTGPU_ISLICE_TRIM, abort_missing = flags & HBTGPU_ISLICE_ABORT_ON_MISSING;
+  if ((flags & HBTGPU_ISLICE_FORCE_EXACT) || st.flags != 0) {
+    if (tid == 0) {
+      exact_walk(slices + U.s0, U.ns, rows_all + U.r0 * stride, stride, U.K, stop_ts, trim, abort_missing, U.mark,
+                 ioff_all + U.r0, icnt_all + U.r0, ifirst_all + U.r0, &sh_R);
+      sh_R.pad = st.flags;
+      results[blockIdx.x] = sh_R;
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < n_tiles; i += NT) {
+      const uint64_t kk = static_cast<uint64_t>(i) * NT;
+      rt_base[U.rt0 + i] = kk < sh_R.n_intervals ? ioff_all[U.r0 + kk] : sh_R.n_slices;
+    }
+    return;
+  }
+  uint64_t carry = 0;
+  for (uint32_t i0 = 0; i0 < n_tiles; i0 += NT) {
+    const uint32_t i = i0 + tid;
+    const uint64_t v = i < n_tiles ? rt_tot[U.rt0 + i] : 0;
+    uint64_t tot;
+    const uint64_t incl = block_incl_sum_u64(v, sh_red, &tot);
+    if (i < n_tiles) rt_base[U.rt0 + i] = carry + incl - v;
+    carry += tot;
+  }
+  if (tid == 0) {
+    const uint64_t n_int = min(U.K, static_cast<uint64_t>(st.n_stop));
+    const bool thrown = st.err_k < n_int;
+    hbtgpu_islice_unit R;
+    R.n_intervals = thrown ? st.err_k : n_int;
+    R.n_slices = carry;
+    R.mark = max(U.mark, static_cast<uint64_t>(st.max_c));
+    R.status = thrown ? -EINVAL : (carry > 0xffffffffull ? -EOVERFLOW : 0);
+    R.err_interval = thrown ? st.err_k : NONE;
+    R.exact_path = 0;
+    R.pad = 0;
+    results[blockIdx.x] = R;
+  }
+}
+
+// ---- (unit, tile of NT rows): output offsets, copy + trim --------------------------------------
+__global__ void __launch_bounds__(NT)
+k_islice_emit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
+              const Unit* __restrict__ units, uint32_t n_units, const hbtgpu_islice_unit* __restrict__ results,
+              const uint64_t* __restrict__ rt_base, uint32_t* __restrict__ ioff_all,
+              const uint32_t* __restrict__ icnt_all, const uint32_t* __restrict__ ifirst_all,
+              hbtgpu_slice* __restrict__ out_all, uint32_t flags) {
+  __shared__ uint64_t sh_red[32];
+  __shared__ uint64_t sh_T[NT], sh_Tend[NT];
+  __shared__ uint32_t sh_excl[NT + 1], sh_p[NT];
+  const int tid = threadIdx.x;
+  const uint32_t u = find_unit<true>(units, n_units, blockIdx.x);
+  const Unit U = units[u];
+  const uint64_t n = results[u].n_intervals;
+  const uint64_t k0 = static_cast<uint64_t>(blockIdx.x - U.rt0) * NT;
+  if (k0 >= n || results[u].status == -EOVERFLOW) return;
   const hbtgpu_slice* S = slices + U.s0;
   const uint64_t* rows = rows_all + U.r0 * stride;
   const bool trim = flags & HBTGPU_ISLICE_TRIM;
-  const uint64_t n = results[u].n_intervals;
-  const int lane = threadIdx.x & 31;
-  for (uint64_t k = threadIdx.x >> 5; k < n; k += blockDim.x >> 5) {
-    const uint32_t cnt = icnt_all[U.r0 + k];
-    if (cnt == 0) continue;
-    const Row rw = ld_row(rows, stride, k);
-    const uint64_t first = ifirst_all[U.r0 + k];
-    hbtgpu_slice* dst = out_all + U.out0 + ioff_all[U.r0 + k];
-    for (uint32_t i = lane; i < cnt; i += 32)
-      emit_one(S, first + i, i, cnt, rw.T, rw.T + rw.D, trim, dst + i);
+  const uint64_t k = k0 + tid;
+  const bool in = k < n;
+  const uint32_t cnt = in ? icnt_all[U.r0 + k] : 0u;
+  uint64_t tile_total;
+  const uint64_t incl = block_incl_sum_u64(cnt, sh_red, &tile_total);
+  const uint32_t excl = static_cast<uint32_t>(incl - cnt);
+  const uint64_t base = rt_base[blockIdx.x];
+  sh_excl[tid] = excl;
+  if (tid == 0) sh_excl[NT] = static_cast<uint32_t>(tile_total);
+  if (in) {
+    ioff_all[U.r0 + k] = static_cast<uint32_t>(base + excl);
+    sh_p[tid] = ifirst_all[U.r0 + k];
+    if (cnt) {
+      const Row rw = ld_row(rows, stride, k);
+      sh_T[tid] = rw.T;
+      sh_Tend[tid] = rw.T + rw.D;
+    }
+  }
+  __syncthreads();
+  hbtgpu_slice* out = out_all + U.out0 + base;
+  for (uint32_t o = tid; o < tile_total; o += NT) {
+    uint32_t lo = 0, hi = NT;  // last row with sh_excl[row] <= o
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (sh_excl[mid] <= o) lo = mid;
+      else hi = mid;
+    }
+    const uint32_t i = o - sh_excl[lo];
+    emit_one(S, sh_p[lo] + i, i, sh_excl[lo + 1] - sh_excl[lo], sh_T[lo], sh_Tend[lo], trim, out + o);
   }
 }
 
@@ -523,22 +706,29 @@ struct hbtgpu_islice_ctx {
   int device = 0;
   std::string err;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
   float last_ms = 0.f;
   // device buffers (grown on demand)
   hbtgpu_slice* d_slices = nullptr;  size_t cap_slices = 0;
   uint64_t* d_rows = nullptr;        size_t cap_rows = 0;
   uint64_t* d_G = nullptr;           size_t cap_G = 0;
+  uint64_t* d_vt_tot = nullptr;      size_t cap_vt_tot = 0;
+  uint64_t* d_vt_base = nullptr;     size_t cap_vt_base = 0;
+  uint32_t* d_rt_tot = nullptr;      size_t cap_rt_tot = 0;
+  uint64_t* d_rt_base = nullptr;     size_t cap_rt_base = 0;
+  uint32_t* d_tile_lo = nullptr;     size_t cap_tile_lo = 0;
+  uint32_t* d_tile_ql = nullptr;     size_t cap_tile_ql = 0;
   uint32_t* d_ioff = nullptr;        size_t cap_ioff = 0;
   uint32_t* d_icnt = nullptr;        size_t cap_icnt = 0;
   uint32_t* d_ifirst = nullptr;      size_t cap_ifirst = 0;
   hbtgpu_slice* d_out = nullptr;     size_t cap_out = 0;
   Unit* d_units = nullptr;           size_t cap_units = 0;
+  UState* d_ustate = nullptr;        size_t cap_ustate = 0;
   hbtgpu_islice_unit* d_res = nullptr; size_t cap_res = 0;
-  uint32_t* d_ids = nullptr;         size_t cap_ids = 0;
   uint64_t* d_base = nullptr;        size_t cap_base = 0;
   // last call
   std::vector<Unit> units;
+  std::vector<UState> ustate;
   std::vector<hbtgpu_islice_unit> res;
   bool have = false;
 };
@@ -562,26 +752,21 @@ int ifail(hbtgpu_islice_ctx* c, int code, const char* fmt, ...) {
       return ifail(c, -EIO, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
   } while (0)
 
-// grow *p to need elements; keep = elements to preserve
 template <class T>
-int grow(hbtgpu_islice_ctx* c, T** p, size_t* cap, size_t need, size_t keep = 0) {
+int grow(hbtgpu_islice_ctx* c, T** p, size_t* cap, size_t need) {
   if (need <= *cap && *p) return 0;
   const size_t ncap = std::max<size_t>(std::max(need, *cap + *cap / 2), 16);
-  T* q = nullptr;
-  IK(cudaMalloc(&q, ncap * sizeof(T)));
-  if (keep && *p) {
-    cudaError_t e = cudaMemcpyAsync(q, *p, keep * sizeof(T), cudaMemcpyDeviceToDevice, c->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-    if (e != cudaSuccess) {
-      cudaFree(q);
-      return ifail(c, -EIO, "device copy failed: %s", cudaGetErrorString(e));
-    }
+  if (*p) {
+    cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
   }
-  if (*p) cudaFree(*p);
-  *p = q;
+  IK(cudaMalloc(p, ncap * sizeof(T)));
   *cap = ncap;
   return 0;
 }
+
+constexpr size_t ROWS_SMEM = 3 * WMAX * sizeof(uint64_t);
 
 }  // namespace
 
@@ -594,8 +779,11 @@ hbtgpu_islice_ctx* hbtgpu_islice_create(int device) {
   auto* c = new hbtgpu_islice_ctx();
   c->device = device;
   if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
-    delete c;
+      cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
+      cudaEventCreate(&c->ev2) != cudaSuccess || cudaEventCreate(&c->ev3) != cudaSuccess ||
+      cudaFuncSetAttribute(k_islice_rows, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(ROWS_SMEM)) != cudaSuccess) {
+    hbtgpu_islice_destroy(c);
     return nullptr;
   }
   return c;
@@ -604,11 +792,11 @@ hbtgpu_islice_ctx* hbtgpu_islice_create(int device) {
 void hbtgpu_islice_destroy(hbtgpu_islice_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  cudaFree(c->d_slices); cudaFree(c->d_rows); cudaFree(c->d_G); cudaFree(c->d_ioff); cudaFree(c->d_icnt);
-  cudaFree(c->d_ifirst); cudaFree(c->d_out); cudaFree(c->d_units); cudaFree(c->d_res); cudaFree(c->d_ids);
-  cudaFree(c->d_base);
-  if (c->ev0) cudaEventDestroy(c->ev0);
-  if (c->ev1) cudaEventDestroy(c->ev1);
+  cudaFree(c->d_slices); cudaFree(c->d_rows); cudaFree(c->d_G); cudaFree(c->d_vt_tot); cudaFree(c->d_vt_base);
+  cudaFree(c->d_rt_tot); cudaFree(c->d_rt_base); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_ql); cudaFree(c->d_ioff); cudaFree(c->d_icnt); cudaFree(c->d_ifirst);
+  cudaFree(c->d_out); cudaFree(c->d_units); cudaFree(c->d_ustate); cudaFree(c->d_res); cudaFree(c->d_base);
+  for (cudaEvent_t e : {c->ev0, c->ev1, c->ev2, c->ev3})
+    if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -629,7 +817,7 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
   const uint64_t s_base = slice_begin[0], r_base = row_begin[0];
   const uint64_t total_s = slice_begin[n_units] - s_base, total_r = row_begin[n_units] - r_base;
   c->units.assign(n_units, Unit{});
-  uint64_t out_run = 0;
+  uint64_t n_vt = 0, n_rt = 0;
   for (uint32_t u = 0; u < n_units; ++u) {
     if (slice_begin[u + 1] < slice_begin[u] || row_begin[u + 1] < row_begin[u])
       return ifail(c, -EINVAL, "begin arrays must not decrease (unit %u)", u);
@@ -638,11 +826,14 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
     U.ns = slice_begin[u + 1] - slice_begin[u];
     U.r0 = row_begin[u] - r_base;
     U.K = row_begin[u + 1] - row_begin[u];
-    if (U.ns + U.K >= 0xffffffffull) return ifail(c, -EINVAL, "unit %u: more than 2^32 slices + rows", u);
-    U.out0 = out_run;
-    U.out_cap = U.ns + U.K;  // the parallel path writes at most one extra slice per row
+    if (U.ns >= 0xfffffff0ull || U.K >= 0xfffffff0ull) return ifail(c, -EINVAL, "unit %u: 2^32 or more slices or rows", u);
+    U.out0 = 0;
     U.mark = marks[u];
-    out_run += U.out_cap;
+    U.vt0 = static_cast<uint32_t>(n_vt);
+    U.rt0 = static_cast<uint32_t>(n_rt);
+    n_vt += (U.ns + VT - 1) >> VT_SHIFT;
+    n_rt += (U.K + NT - 1) / NT;
+    if (n_vt >= 0x7fffffffull || n_rt >= 0x7fffffffull) return ifail(c, -EINVAL, "too many tiles");
   }
   if ((total_s && !slices) || (total_r && !rows)) return ifail(c, -EINVAL, "null slices or rows");
 
@@ -674,57 +865,65 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
     stride = 2;
   }
   if (int rc = grow(c, &c->d_G, &c->cap_G, total_s + 1)) return rc;
+  if (int rc = grow(c, &c->d_vt_tot, &c->cap_vt_tot, n_vt + 2)) return rc;
+  if (int rc = grow(c, &c->d_vt_base, &c->cap_vt_base, n_vt + 2)) return rc;
+  if (int rc = grow(c, &c->d_rt_tot, &c->cap_rt_tot, n_rt + 1)) return rc;
+  if (int rc = grow(c, &c->d_rt_base, &c->cap_rt_base, n_rt + 1)) return rc;
+  if (int rc = grow(c, &c->d_tile_lo, &c->cap_tile_lo, n_rt + 1)) return rc;
+  if (int rc = grow(c, &c->d_tile_ql, &c->cap_tile_ql, n_rt + 1)) return rc;
   if (int rc = grow(c, &c->d_ioff, &c->cap_ioff, total_r + 1)) return rc;
   if (int rc = grow(c, &c->d_icnt, &c->cap_icnt, total_r + 1)) return rc;
   if (int rc = grow(c, &c->d_ifirst, &c->cap_ifirst, total_r + 1)) return rc;
-  if (int rc = grow(c, &c->d_out, &c->cap_out, out_run + 1)) return rc;
   if (int rc = grow(c, &c->d_units, &c->cap_units, n_units)) return rc;
+  if (int rc = grow(c, &c->d_ustate, &c->cap_ustate, n_units)) return rc;
   if (int rc = grow(c, &c->d_res, &c->cap_res, n_units)) return rc;
+  c->ustate.assign(n_units, UState{0u, 0u, NONE, NONE, 0ull});
   IK(cudaMemcpyAsync(c->d_units, c->units.data(), n_units * sizeof(Unit), cudaMemcpyHostToDevice, c->stream));
-  IK(cudaMemsetAsync(c->d_res, 0, n_units * sizeof(hbtgpu_islice_unit), c->stream));
+  IK(cudaMemcpyAsync(c->d_ustate, c->ustate.data(), n_units * sizeof(UState), cudaMemcpyHostToDevice, c->stream));
 
   IK(cudaEventRecord(c->ev0, c->stream));
-  k_islice_unit<<<n_units, NT, 0, c->stream>>>(d_slices, d_rows, stride, c->d_units, c->d_res, c->d_G, c->d_ioff,
-                                               c->d_icnt, c->d_ifirst, c->d_out, stop_ts, flags);
+  if (n_vt) {
+    k_islice_validate<<<static_cast<unsigned>(n_vt), NT, 0, c->stream>>>(d_slices, c->d_units, n_units, c->d_ustate,
+                                                                         c->d_G, c->d_vt_tot);
+    k_islice_vscan<<<n_units, 32, 0, c->stream>>>(c->d_units, c->d_vt_tot, c->d_vt_base);
+  }
+  if (n_rt) {
+    k_islice_bounds<<<static_cast<unsigned>((n_rt + 127) / 128), 128, 0, c->stream>>>(
+        d_slices, d_rows, stride, c->d_units, n_units, static_cast<uint32_t>(n_rt), c->d_tile_lo, c->d_tile_ql);
+    k_islice_rows<<<static_cast<unsigned>(n_rt), NT, ROWS_SMEM, c->stream>>>(
+        d_slices, d_rows, stride, c->d_units, n_units, c->d_ustate, c->d_G, c->d_vt_base, c->d_tile_lo, c->d_tile_ql,
+        c->d_icnt, c->d_ifirst, c->d_rt_tot, stop_ts, flags);
+  }
+  k_islice_rscan<<<n_units, NT, 0, c->stream>>>(d_slices, d_rows, stride, c->d_units, c->d_ustate, c->d_rt_tot,
+                                                c->d_rt_base, c->d_ioff, c->d_icnt, c->d_ifirst, c->d_res, stop_ts,
+                                                flags);
   IK(cudaGetLastError());
+  IK(cudaEventRecord(c->ev1, c->stream));
   c->res.assign(n_units, hbtgpu_islice_unit{});
   IK(cudaMemcpyAsync(c->res.data(), c->d_res, n_units * sizeof(hbtgpu_islice_unit), cudaMemcpyDeviceToHost,
                      c->stream));
   IK(cudaStreamSynchronize(c->stream));
 
-  // units that took the serial walk: place their slices (behind the regular region when they
-  // do not fit their own) and copy them
-  std::vector<uint32_t> ids;
-  bool moved = false;
+  // now that the counts are known: dense output, unit after unit
+  uint64_t out_run = 0;
   for (uint32_t u = 0; u < n_units; ++u) {
-    if (!c->res[u].exact_path) {
-      if (c->res[u].pad) return ifail(c, -EIO, "internal: unit %u overflowed its output region", u);
-      continue;
-    }
-    if (c->res[u].status == -EOVERFLOW) continue;
-    if (c->res[u].n_slices == 0) continue;
-    ids.push_back(u);
-    if (c->res[u].n_slices > c->units[u].out_cap) {
-      c->units[u].out0 = out_run;
-      c->units[u].out_cap = c->res[u].n_slices;
-      out_run += c->res[u].n_slices;
-      moved = true;
-    }
+    c->units[u].out0 = out_run;
+    if (c->res[u].status != -EOVERFLOW) out_run += c->res[u].n_slices;
   }
-  if (!ids.empty()) {
-    if (moved) {
-      if (int rc = grow(c, &c->d_out, &c->cap_out, out_run + 1, c->cap_out)) return rc;
-      IK(cudaMemcpyAsync(c->d_units, c->units.data(), n_units * sizeof(Unit), cudaMemcpyHostToDevice, c->stream));
-    }
-    if (int rc = grow(c, &c->d_ids, &c->cap_ids, ids.size())) return rc;
-    IK(cudaMemcpyAsync(c->d_ids, ids.data(), ids.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-    k_islice_emit_exact<<<static_cast<unsigned>(ids.size()), 256, 0, c->stream>>>(
-        d_slices, d_rows, stride, c->d_units, c->d_ids, c->d_res, c->d_ioff, c->d_icnt, c->d_ifirst, c->d_out, flags);
-    IK(cudaGetLastError());
-  }
-  IK(cudaEventRecord(c->ev1, c->stream));
+  if (int rc = grow(c, &c->d_out, &c->cap_out, out_run + 1)) return rc;
+  IK(cudaMemcpyAsync(c->d_units, c->units.data(), n_units * sizeof(Unit), cudaMemcpyHostToDevice, c->stream));
+  IK(cudaEventRecord(c->ev2, c->stream));
+  if (n_rt && out_run)
+    k_islice_emit<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(d_slices, d_rows, stride, c->d_units, n_units,
+                                                                     c->d_res, c->d_rt_base, c->d_ioff, c->d_icnt,
+                                                                     c->d_ifirst, c->d_out, flags);
+  IK(cudaGetLastError());
+  IK(cudaEventRecord(c->ev3, c->stream));
   IK(cudaStreamSynchronize(c->stream));
-  IK(cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
+  float a = 0.f, b = 0.f;
+  IK(cudaEventElapsedTime(&a, c->ev0, c->ev1));
+  IK(cudaEventElapsedTime(&b, c->ev2, c->ev3));
+  c->last_ms = a + b;
 
   for (uint32_t u = 0; u < n_units; ++u) {
     c->res[u].pad = 0;
