@@ -337,48 +337,55 @@ __device__ __forceinline__ Eval eval_row(const A& a, uint32_t ns, uint64_t T, ui
   return e;
 }
 
+// What a row's evaluation starts from: lb = #{e_j < T}, q = #{t_j < Tend}, x = where the take
+// loop stops, hasB = a slice ends exactly at T.
+struct RowInfo {
+  uint64_t T, D;
+  uint32_t lb, q, x;
+  bool hasB;
+};
+
+__device__ RowInfo row_info_global(const GAcc& g, uint32_t ns, const Row rw, bool trim) {
+  RowInfo ri;
+  ri.T = rw.T;
+  ri.D = rw.D;
+  const uint64_t Tend = rw.T + rw.D;
+  ri.lb = first_end_ge(g, 0, ns, rw.T);
+  ri.hasB = ri.lb < ns && g.e(ri.lb) == rw.T;
+  ri.q = first_start_ge(g, 0, ns, Tend);
+  ri.x = trim ? ri.q : first_end_gt(g, 0, ns, Tend);
+  return ri;
+}
+
 // Does row k (which starts exactly on a slice end) find that slice already consumed?  Walks
-// back to the first row of its chain, then forward again.  acc / [a, b) / row_at serve rows
-// k_min and later (a row tile's window in shared memory); *below is raised when the chain
-// reaches further back, and the caller repeats the walk in global memory.
-template <class A, class RL>
-__device__ uint32_t resolve_chain(const A& acc, uint32_t a, uint32_t b, uint32_t ns, RL row_at, uint64_t k,
-                                  uint64_t k_min, uint64_t mark, bool trim, bool abort_missing, bool* give_up,
-                                  bool* below) {
+// back to the first row of its chain, then forward again.  info_at(j) hands out a row's
+// searches (from shared memory for rows of this tile, k0 and later; computed in global memory
+// for earlier ones), acc serves the slices of this tile's rows.
+template <class A, class INFO>
+__device__ uint32_t resolve_chain(const A& acc, const GAcc& g, uint32_t ns, INFO info_at, uint64_t k, uint64_t k0,
+                                  uint64_t mark, bool trim, bool abort_missing, bool* give_up) {
   uint64_t j = k;
   uint32_t bsel = 0;
   int depth = 0;
   for (;;) {
     if (j == 0) {
-      bsel = mark > first_end_ge(acc, a, b, row_at(0).T) ? 1u : 0u;
+      bsel = mark > info_at(0).lb ? 1u : 0u;
       break;
     }
     if (depth >= LOOKBACK) {
       *give_up = true;
       return 0;
     }
-    if (j == k_min) {
-      *below = true;
-      return 0;
-    }
     --j;
     ++depth;
-    const uint64_t Tj = row_at(j).T;
-    const uint32_t lbj = first_end_ge(acc, a, b, Tj);
-    if (!(lbj < ns && acc.e(lbj) == Tj)) {
-      bsel = 0;
-      break;
-    }
+    if (!info_at(j).hasB) break;  // that row starts at its lb whatever came before
   }
   for (uint64_t i = j; i < k; ++i) {
-    const Row rw = row_at(i);
-    const uint64_t Tend = rw.T + rw.D;
-    const uint32_t lb = first_end_ge(acc, a, b, rw.T);
-    const uint32_t q = first_start_ge(acc, a, b, Tend);
-    const uint32_t x = trim ? q : first_end_gt(acc, a, b, Tend);
-    const Eval e = eval_row(acc, ns, rw.T, rw.D, Tend, lb + bsel, x, q, trim, abort_missing);
-    const uint32_t lbn = first_end_ge(acc, a, b, row_at(i + 1).T);
-    bsel = (!e.null_res && !e.thrown && e.c > lbn) ? 1u : 0u;
+    const RowInfo ri = info_at(i);
+    const uint64_t Tend = ri.T + ri.D;
+    const Eval e = i >= k0 ? eval_row(acc, ns, ri.T, ri.D, Tend, ri.lb + bsel, ri.x, ri.q, trim, abort_missing)
+                           : eval_row(g, ns, ri.T, ri.D, Tend, ri.lb + bsel, ri.x, ri.q, trim, abort_missing);
+    bsel = (!e.null_res && !e.thrown && e.c > info_at(i + 1).lb) ? 1u : 0u;
   }
   return bsel;
 }
@@ -439,25 +446,6 @@ k_islice_vscan(const Unit* __restrict__ units, const uint64_t* __restrict__ vt_t
 }
 
 // ---- (unit, tile of NT rows): every row's first slice, count and new mark ---------------------
-template <class A, class RL>
-__device__ __forceinline__ void row_in_tile(const A& acc, const GAcc& g, uint32_t ns, uint32_t a, uint32_t b,
-                                            RL row_at, uint64_t k, uint64_t k0, uint64_t T, uint64_t D, uint64_t Tend,
-                                            uint64_t mark, bool trim, bool abort_missing, Eval* out, uint32_t* flags) {
-  const uint32_t lb = first_end_ge(acc, a, b, T);
-  const bool hasB = lb < ns && acc.e(lb) == T;
-  const uint32_t q = first_start_ge(acc, a, b, Tend);
-  const uint32_t x = trim ? q : first_end_gt(acc, a, b, Tend);
-  uint32_t bsel = 0;
-  if (k == 0 && mark > lb + (hasB ? 1u : 0u)) *flags |= UF_MARK;  // mark ahead of the first row's slices
-  if (hasB) {
-    bool give_up = false, below = false;
-    bsel = resolve_chain(acc, a, b, ns, row_at, k, k0, mark, trim, abort_missing, &give_up, &below);
-    if (below) bsel = resolve_chain(g, 0u, ns, ns, row_at, k, 0ull, mark, trim, abort_missing, &give_up, &below);
-    if (give_up) *flags |= UF_CHAIN;
-  }
-  *out = eval_row(acc, ns, T, D, Tend, lb + bsel, x, q, trim, abort_missing);
-}
-
 // per row tile: the slice window its rows can touch, [lo, ql + 2) with lo = #{e_j < T of its
 // first row} and ql = #{t_j < end of its last row}.  One thread per tile.
 __global__ void __launch_bounds__(128)
@@ -489,6 +477,8 @@ k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
   __shared__ uint64_t sh_red[32];
   __shared__ uint64_t sh_T[NT], sh_D[NT];
   __shared__ uint32_t sh_tot, sh_stop, sh_err, sh_maxc, sh_flags;
+  __shared__ uint32_t sh_lb[NT], sh_q[NT], sh_x[NT];
+  __shared__ uint8_t sh_hb[NT];
 
   const int tid = threadIdx.x;
   const uint32_t u = find_unit<true>(units, n_units, blockIdx.x);
@@ -526,11 +516,51 @@ k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
     sh_maxc = 0;
     sh_flags = 0;
   }
-  // rows of this tile come from shared memory, earlier ones (chains across the tile edge) from global
-  auto row_at = [&](uint64_t kk) { return kk >= k0 ? Row{sh_T[kk - k0], sh_D[kk - k0]} : ld_row(rows, stride, kk); };
   const bool zero_len = live && !cut && D == 0;  // IntervalSlicer.cpp:64
   const bool act = live && !cut && D != 0;
   Eval e{true, false, 0, 0, 0};
+  // One row: its searches (q and x by binary search; lb follows from the previous row's q when
+  // the rows touch, as count rows do), then the chain question, then the evaluation.
+  auto process = [&](const auto& acc, uint32_t a, uint32_t b) {
+    uint32_t lb = 0, q = 0, x = 0;
+    bool hasB = false;
+    if (act) {
+      q = first_start_ge(acc, a, b, Tend);
+      x = trim ? q : first_end_gt(acc, a, b, Tend);
+    }
+    sh_q[tid] = act ? q : 0xffffffffu;
+    __syncthreads();
+    if (act) {
+      const uint32_t qp = tid > 0 ? sh_q[tid - 1] : 0xffffffffu;
+      if (qp != 0xffffffffu && sh_T[tid - 1] + sh_D[tid - 1] == T)
+        lb = (qp > a && acc.e(qp - 1) >= T) ? qp - 1 : qp;  // at most one slice straddles T
+      else
+        lb = first_end_ge(acc, a, b, T);
+      hasB = lb < ns && acc.e(lb) == T;
+    }
+    __syncthreads();
+    sh_q[tid] = q;
+    sh_lb[tid] = lb;
+    sh_x[tid] = x;
+    sh_hb[tid] = hasB;
+    __syncthreads();
+    if (!act) return;
+    uint32_t bsel = 0;
+    if (k == 0 && U.mark > lb + (hasB ? 1u : 0u)) uflags |= UF_MARK;  // mark ahead of the first row's slices
+    if (hasB) {
+      auto info_at = [&](uint64_t kk) {
+        if (kk >= k0) {
+          const uint32_t i = static_cast<uint32_t>(kk - k0);
+          return RowInfo{sh_T[i], sh_D[i], sh_lb[i], sh_q[i], sh_x[i], sh_hb[i] != 0};
+        }
+        return row_info_global(g, ns, ld_row(rows, stride, kk), trim);
+      };
+      bool give_up = false;
+      bsel = resolve_chain(acc, g, ns, info_at, k, k0, U.mark, trim, abort_missing, &give_up);
+      if (give_up) uflags |= UF_CHAIN;
+    }
+    e = eval_row(acc, ns, T, D, Tend, lb + bsel, x, q, trim, abort_missing);
+  };
   if (__syncthreads_or(act)) {
     const uint32_t lo = tile_lo[blockIdx.x], ql = tile_ql[blockIdx.x];
     const uint32_t hiw = min(ns, ql + 2);
@@ -560,10 +590,9 @@ k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
       for (uint32_t j = 0; j < WMAX / NT; ++j)
         if (j < c && i0 + j < W) wG[i0 + j] = base + loc[j];
       __syncthreads();
-      const WAcc w{wt, we, wG, lo, W - 1};
-      if (act) row_in_tile(w, g, ns, lo, min(ns, ql + 1), row_at, k, k0, T, D, Tend, U.mark, trim, abort_missing, &e, &uflags);
+      process(WAcc{wt, we, wG, lo, W - 1}, lo, min(ns, ql + 1));
     } else {
-      if (act) row_in_tile(g, g, ns, 0u, ns, row_at, k, k0, T, D, Tend, U.mark, trim, abort_missing, &e, &uflags);
+      process(g, 0u, ns);
     }
   }
   const bool counted = act && !e.null_res && !e.thrown;

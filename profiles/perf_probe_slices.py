@@ -1,7 +1,8 @@
-"""Count intervals x slices throughput: python profiles/perf_probe_slices.py [units] [slices_per_unit] [rows_per_unit]
+"""Count intervals x slices throughput: python profiles/perf_probe_slices.py [units] [slices_per_unit] [rows_per_unit] [aligned]
 Default: 192 comp units, 200k slices (20k context switches/s x 10 s) and 100k count rows
 (10 kHz x 10 s, BASELINE config 2's sampling) per unit, TRIM | ABORT_ON_MISSING as
-TraceMonitor::releaseCountData_ calls it.
+TraceMonitor::releaseCountData_ calls it.  aligned = fraction of row boundaries that fall exactly on a
+slice end (default 0.001; those rows depend on their predecessor).
 Algorithmic bytes = 32 B per slice read + 32 B per slice written + 16 B per row read + 8 B per
 row written (offset, count).  The CPU line times the reference's own code (real IntervalSlicer,
 oracle/_ref) and the C restatement on ONE unit, single thread (the reference releases unit by
@@ -42,9 +43,11 @@ def main():
     U = int(sys.argv[1]) if len(sys.argv) > 1 else 192
     NS = int(sys.argv[2]) if len(sys.argv) > 2 else 200_000
     K = int(sys.argv[3]) if len(sys.argv) > 3 else 100_000
+    ALIGN = float(sys.argv[4]) if len(sys.argv) > 4 else 0.001
     import torch
     r = np.random.default_rng(1)
-    protos = [gen_unit(r, NS, K) for _ in range(4)]
+    protos = [gen_unit(r, NS, K, align=ALIGN) for _ in range(4)]
+    print(f"units {U}, {NS} slices and {K} rows per unit, {ALIGN} of the row boundaries on a slice end")
     us = [protos[u % 4][0] for u in range(U)]
     ur = [protos[u % 4][1] for u in range(U)]
     sb = np.concatenate([[0], np.cumsum([len(s) for s in us])]).astype(np.uint64)
