@@ -472,7 +472,7 @@ k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
               const uint64_t* __restrict__ Gl_all, const uint64_t* __restrict__ vt_base,
               const uint32_t* __restrict__ tile_lo, const uint32_t* __restrict__ tile_ql,
               uint32_t* __restrict__ icnt_all, uint32_t* __restrict__ ifirst_all, uint32_t* __restrict__ rt_tot,
-              uint64_t stop_ts, uint32_t flags) {
+              ulonglong2* __restrict__ td_all, uint64_t stop_ts, uint32_t flags) {
   extern __shared__ __align__(16) uint64_t sh_win[];  // wt[WMAX], we[WMAX], wG[WMAX]
   __shared__ uint64_t sh_red[32];
   __shared__ uint64_t sh_T[NT], sh_D[NT];
@@ -509,6 +509,7 @@ k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
   }
   sh_T[tid] = T;
   sh_D[tid] = D;
+  if (td_all && live) td_all[U.r0 + k] = make_ulonglong2(T, Tend);  // {start, end} packed for the emit pass
   if (tid == 0) {
     sh_tot = 0;
     sh_stop = 0xffffffffu;
@@ -684,7 +685,7 @@ k_islice_emit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
               const Unit* __restrict__ units, uint32_t n_units, const hbtgpu_islice_unit* __restrict__ results,
               const uint64_t* __restrict__ rt_base, uint32_t* __restrict__ ioff_all,
               const uint32_t* __restrict__ icnt_all, const uint32_t* __restrict__ ifirst_all,
-              hbtgpu_slice* __restrict__ out_all, uint32_t flags) {
+              const ulonglong2* __restrict__ td_all, hbtgpu_slice* __restrict__ out_all, uint32_t flags) {
   __shared__ uint64_t sh_red[32];
   __shared__ uint64_t sh_T[NT], sh_Tend[NT];
   __shared__ uint32_t sh_excl[NT + 1], sh_p[NT];
@@ -710,9 +711,15 @@ k_islice_emit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
     ioff_all[U.r0 + k] = static_cast<uint32_t>(base + excl);
     sh_p[tid] = ifirst_all[U.r0 + k];
     if (cnt) {
-      const Row rw = ld_row(rows, stride, k);
-      sh_T[tid] = rw.T;
-      sh_Tend[tid] = rw.T + rw.D;
+      if (td_all && !results[u].exact_path) {  // (units that took the serial walk may have skipped the rows pass)
+        const ulonglong2 td = td_all[U.r0 + k];
+        sh_T[tid] = td.x;
+        sh_Tend[tid] = td.y;
+      } else {
+        const Row rw = ld_row(rows, stride, k);
+        sh_T[tid] = rw.T;
+        sh_Tend[tid] = rw.T + rw.D;
+      }
     }
   }
   __syncthreads();
@@ -747,6 +754,7 @@ struct hbtgpu_islice_ctx {
   uint64_t* d_rt_base = nullptr;     size_t cap_rt_base = 0;
   uint32_t* d_tile_lo = nullptr;     size_t cap_tile_lo = 0;
   uint32_t* d_tile_ql = nullptr;     size_t cap_tile_ql = 0;
+  ulonglong2* d_td = nullptr;        size_t cap_td = 0;
   uint32_t* d_ioff = nullptr;        size_t cap_ioff = 0;
   uint32_t* d_icnt = nullptr;        size_t cap_icnt = 0;
   uint32_t* d_ifirst = nullptr;      size_t cap_ifirst = 0;
@@ -822,7 +830,7 @@ void hbtgpu_islice_destroy(hbtgpu_islice_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaFree(c->d_slices); cudaFree(c->d_rows); cudaFree(c->d_G); cudaFree(c->d_vt_tot); cudaFree(c->d_vt_base);
-  cudaFree(c->d_rt_tot); cudaFree(c->d_rt_base); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_ql); cudaFree(c->d_ioff); cudaFree(c->d_icnt); cudaFree(c->d_ifirst);
+  cudaFree(c->d_rt_tot); cudaFree(c->d_rt_base); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_ql); cudaFree(c->d_td); cudaFree(c->d_ioff); cudaFree(c->d_icnt); cudaFree(c->d_ifirst);
   cudaFree(c->d_out); cudaFree(c->d_units); cudaFree(c->d_ustate); cudaFree(c->d_res); cudaFree(c->d_base);
   for (cudaEvent_t e : {c->ev0, c->ev1, c->ev2, c->ev3})
     if (e) cudaEventDestroy(e);
@@ -906,6 +914,12 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
   if (int rc = grow(c, &c->d_units, &c->cap_units, n_units)) return rc;
   if (int rc = grow(c, &c->d_ustate, &c->cap_ustate, n_units)) return rc;
   if (int rc = grow(c, &c->d_res, &c->cap_res, n_units)) return rc;
+  // rows wider than {tstamp, duration}: the rows pass packs {start, end} for the emit pass
+  ulonglong2* d_td = nullptr;
+  if (stride > 2 && !(flags & HBTGPU_ISLICE_FORCE_EXACT)) {
+    if (int rc = grow(c, &c->d_td, &c->cap_td, total_r + 1)) return rc;
+    d_td = c->d_td;
+  }
   c->ustate.assign(n_units, UState{0u, 0u, NONE, NONE, 0ull});
   IK(cudaMemcpyAsync(c->d_units, c->units.data(), n_units * sizeof(Unit), cudaMemcpyHostToDevice, c->stream));
   IK(cudaMemcpyAsync(c->d_ustate, c->ustate.data(), n_units * sizeof(UState), cudaMemcpyHostToDevice, c->stream));
@@ -921,7 +935,7 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
         d_slices, d_rows, stride, c->d_units, n_units, static_cast<uint32_t>(n_rt), c->d_tile_lo, c->d_tile_ql);
     k_islice_rows<<<static_cast<unsigned>(n_rt), NT, ROWS_SMEM, c->stream>>>(
         d_slices, d_rows, stride, c->d_units, n_units, c->d_ustate, c->d_G, c->d_vt_base, c->d_tile_lo, c->d_tile_ql,
-        c->d_icnt, c->d_ifirst, c->d_rt_tot, stop_ts, flags);
+        c->d_icnt, c->d_ifirst, c->d_rt_tot, d_td, stop_ts, flags);
   }
   k_islice_rscan<<<n_units, NT, 0, c->stream>>>(d_slices, d_rows, stride, c->d_units, c->d_ustate, c->d_rt_tot,
                                                 c->d_rt_base, c->d_ioff, c->d_icnt, c->d_ifirst, c->d_res, stop_ts,
@@ -945,7 +959,7 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
   if (n_rt && out_run)
     k_islice_emit<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(d_slices, d_rows, stride, c->d_units, n_units,
                                                                      c->d_res, c->d_rt_base, c->d_ioff, c->d_icnt,
-                                                                     c->d_ifirst, c->d_out, flags);
+                                                                     c->d_ifirst, d_td, c->d_out, flags);
   IK(cudaGetLastError());
   IK(cudaEventRecord(c->ev3, c->stream));
   IK(cudaStreamSynchronize(c->stream));

@@ -18,6 +18,12 @@
 //     onCpusThreadSwitchBufferRead :480-484                   onCpuThreadSwitchBufferRead(cpu, slices)
 //     getThreadsInfo()             :476-478                   same (ThreadInfo without /proc strings)
 //   tagstack::Event               tagstack/Event.h:28-56    Event (= hbtgpu_cs_event)
+//   tagstack::slice::Slice        tagstack/Slicer.h:30-84   Slice (= hbtgpu_slice) + makeSlice / tstampEnd
+//   tagstack::PerIntervalSlices   tagstack/IntervalSlicer.h:17-82   PerIntervalSlices
+//   tagstack::IntervalSlicer      tagstack/IntervalSlicer.h:92-238  IntervalSlicer
+//     write / registerConsumerMark / getMark / numActiveSlices / numProcessedSlices /
+//     discardConsumed / makeIntervalIntersectingSlices / consumeSlices          same names
+//   TraceMonitor::releaseCountData_ row loop  mon/TraceMonitor.cpp:52-96   releaseCountRows (all CPUs, one GPU call)
 //
 // Error conventions follow the reference: the hot path returns negative errno in ssize_t
 // (-ENODATA drained, -EPERM bad record / time regression), argument and environment errors
@@ -29,7 +35,10 @@
 #include <sys/types.h>
 
 #include <cstdint>
+#include <deque>
 #include <functional>
+#include <map>
+#include <memory>
 #include <optional>
 #include <stdexcept>
 #include <string>
@@ -379,5 +388,166 @@ inline ssize_t CpuThreadSwitchGenerator::consume(unsigned max_num_records) {
   if (c_.err < 0) return static_cast<ssize_t>(c_.err);
   return -ENODATA;  // drained (:1574-1588)
 }
+
+// ---- tagstack slices x count intervals -------------------------------------------------------
+
+using Slice = hbtgpu_slice;
+enum class TransitionType : uint8_t { NA = 0, Analysis, ThreadPreempted, ThreadYield, PhaseChange };  // Slicer.h:31-43
+inline Slice makeSlice(TimeStamp tstamp, TimeStamp duration, uint64_t stack_id, TransitionType swin,
+                       TransitionType swout) {  // Slice::makeSlice, Slicer.h:51-63
+  Slice s{};
+  s.tstamp = tstamp;
+  s.duration = duration;
+  s.stack_id = stack_id;
+  s.swin_type = static_cast<uint8_t>(swin);
+  s.swout_type = static_cast<uint8_t>(swout);
+  return s;
+}
+inline bool operator==(const Slice& a, const Slice& b) {  // Slicer.h:65-69
+  return a.tstamp == b.tstamp && a.duration == b.duration && a.stack_id == b.stack_id &&
+         a.swin_type == b.swin_type && a.swout_type == b.swout_type;
+}
+using Slices = std::vector<Slice>;
+
+class PerIntervalSlices : public std::deque<Slices> {  // IntervalSlicer.h:17-82
+ public:
+  size_t countSlices() const {
+    size_t n = 0;
+    for (const auto& s : *this) n += s.size();
+    return n;
+  }
+  size_t numIntervals() const { return size(); }
+};
+
+// One comp unit's slice store with consumer marks.  The slices stay in host memory (the Slicer
+// that writes them is host code); every query ships the live ones to the GPU.  For whole
+// windows use releaseCountRows below: all CPUs and all rows in one call.
+class IntervalSlicer {
+ public:
+  IntervalSlicer(size_t min_num_slices, size_t num_slices_drop_if_full, int device = 0)
+      : drop_if_full_{num_slices_drop_if_full} {
+    if (min_num_slices == 0) throw std::invalid_argument("min_num_slices must be positive");
+    capacity_ = 1;
+    while (capacity_ * sizeof(Slice) < min_num_slices * sizeof(Slice)) capacity_ <<= 1;  // nextPow2 of the byte size, RingBuffer.h:69
+    ctx_ = hbtgpu_islice_create(device);
+    if (!ctx_) throw std::runtime_error("hbtgpu_islice_create failed: no CUDA device (there is no CPU path)");
+  }
+  ~IntervalSlicer() { hbtgpu_islice_destroy(ctx_); }
+  IntervalSlicer(const IntervalSlicer&) = delete;
+  IntervalSlicer& operator=(const IntervalSlicer&) = delete;
+
+  ssize_t write(const Slice& slice) {  // IntervalSlicer.h:115-135
+    if (slice.tstamp == kInvalidTimeStamp) throw std::invalid_argument("Invalid timestamp");
+    if (slices_.size() >= capacity_) {
+      if (drop_if_full_ == 0) return -ENOSPC;
+      const size_t n = std::min(drop_if_full_, slices_.size());
+      slices_.erase(slices_.begin(), slices_.begin() + n);
+      num_dropped_ += n;
+    }
+    slices_.push_back(slice);
+    return sizeof(Slice);
+  }
+  void registerConsumerMark(const std::string& key) {
+    if (marks_.count(key)) throw std::invalid_argument("Consumer with key " + key + " already registered.");
+    marks_[key] = num_processed_slices_;
+  }
+  void updateConsumerMark(const std::string& key, size_t new_offset) { getMark(key) = new_offset; }
+  void removeConsumerMark(const std::string& key) { marks_.erase(key); }
+  size_t& getMark(const std::string& key) {
+    auto it = marks_.find(key);
+    if (it == marks_.end()) throw std::invalid_argument("No consumer mark for key: \"" + key + "\"");
+    return it->second;
+  }
+  size_t numActiveSlices() const noexcept { return slices_.size(); }
+  size_t numProcessedSlices() const noexcept { return num_processed_slices_; }
+  void discardConsumed() {  // IntervalSlicer.h:178-207
+    if (marks_.empty()) return;
+    size_t m = ~size_t{0};
+    for (const auto& kv : marks_) m = std::min(m, kv.second);
+    const size_t first = num_processed_slices_ + num_dropped_;  // absolute index of slices_[0]
+    if (m > first) {
+      const size_t n = std::min(m - first, slices_.size());
+      slices_.erase(slices_.begin(), slices_.begin() + n);
+      num_processed_slices_ += n;
+    }
+  }
+
+  // IntervalSlicer.cpp:52-188.  offset counts slices since the slicer was made, as the marks do.
+  std::pair<std::unique_ptr<Slices>, size_t> makeIntervalIntersectingSlices(size_t offset, TimeStamp tstamp,
+                                                                            TimeStamp duration, bool trim,
+                                                                            bool abort_on_missing_slices) {
+    const uint64_t row[2] = {tstamp, duration};
+    std::vector<uint32_t> counts;
+    Slices out;
+    size_t mark = offset;
+    // stop_ts: the row loop's cut does not exist here; ~0 is never reached by a wrapping sum + 1
+    releaseRows(row, 1, 2, ~0ull, trim, abort_on_missing_slices, &mark, &counts, &out, /*no_stop=*/true);
+    if (counts.empty() || counts[0] == 0) return {nullptr, 0};
+    return {std::make_unique<Slices>(std::move(out)), mark - offset};
+  }
+
+  std::unique_ptr<PerIntervalSlices> consumeSlices(const std::string& key, uint64_t tstamp, uint64_t duration,
+                                                   bool trim, bool abort_on_missing_slices) {  // :195-217
+    auto pis = std::make_unique<PerIntervalSlices>();
+    auto& offset = getMark(key);
+    auto [slices, n] = makeIntervalIntersectingSlices(offset, tstamp, duration, trim, abort_on_missing_slices);
+    if (slices == nullptr) pis->push_back({});
+    else pis->push_back(std::move(*slices));
+    offset += n;
+    discardConsumed();
+    return pis;
+  }
+
+  // The row loop of TraceMonitor::releaseCountData_ (TraceMonitor.cpp:52-96) for this unit:
+  // rows = n_rows x row_stride u64 (word 0 tstamp, word 1 duration).  Returns the rows used.
+  size_t releaseCountRows(const std::string& key, const uint64_t* rows, size_t n_rows, size_t row_stride,
+                          TimeStamp stop_ts, PerIntervalSlices* pislices) {
+    std::vector<uint32_t> counts;
+    Slices out;
+    const size_t n = releaseRows(rows, n_rows, row_stride, stop_ts, true, true, &getMark(key), &counts, &out, false);
+    size_t o = 0;
+    for (size_t k = 0; k < n; ++k) {
+      pislices->emplace_back(out.begin() + o, out.begin() + o + counts[k]);
+      o += counts[k];
+    }
+    discardConsumed();
+    return n;
+  }
+
+ private:
+  size_t releaseRows(const uint64_t* rows, size_t n_rows, size_t stride, TimeStamp stop_ts, bool trim, bool abort_missing,
+                     size_t* mark, std::vector<uint32_t>* counts, Slices* out, bool no_stop) {
+    const size_t first = num_processed_slices_ + num_dropped_;
+    // seekInTx clamps the offset into [tail, head] (ringbuffer/Consumer.h:281)
+    uint64_t rel = *mark > first ? *mark - first : 0;
+    const uint64_t rel_in = rel;
+    const uint64_t sb[2] = {0, slices_.size()}, rb[2] = {0, n_rows};
+    hbtgpu_islice_unit u{};
+    const uint32_t flags = (trim ? HBTGPU_ISLICE_TRIM : 0u) | (abort_missing ? HBTGPU_ISLICE_ABORT_ON_MISSING : 0u);
+    std::vector<uint64_t> one;
+    if (no_stop && n_rows == 1 && rows[0] + rows[1] == ~0ull) {
+      // an interval that ends exactly at ~0 would meet the stop rule; it cannot hold slices
+      // that the reference would not also reject (tstamp ~0 is kInvalidTimeStamp)
+      counts->assign(1, 0);
+      return 1;
+    }
+    const int rc = hbtgpu_islice_release(ctx_, slices_.data(), sb, rows, stride, rb, 1, stop_ts, flags, &rel, &u);
+    if (rc != 0) throw std::runtime_error(hbtgpu_islice_last_error(ctx_));
+    if (u.status == -EINVAL) throw std::runtime_error("IntervalSlicer: inconsistent interval (HBT_THROW_ASSERT / HBT_ARG_CHECK in the reference)");
+    if (u.status != 0) throw std::runtime_error("IntervalSlicer: too many slices for one call");
+    counts->resize(u.n_intervals);
+    out->resize(u.n_slices);
+    if (hbtgpu_islice_get(ctx_, 0, counts->data(), counts->size(), out->data(), out->size()) != 0)
+      throw std::runtime_error(hbtgpu_islice_last_error(ctx_));
+    *mark += rel - rel_in;
+    return u.n_intervals;
+  }
+
+  hbtgpu_islice_ctx* ctx_ = nullptr;
+  std::vector<Slice> slices_;  // the live slices, oldest first
+  size_t capacity_ = 0, drop_if_full_ = 0;
+  size_t num_processed_slices_ = 0, num_dropped_ = 0;
+  std::map<std::string, size_t> marks_;
+};
 
 }  // namespace hbtgpu_shim

@@ -177,6 +177,79 @@ int main() {
            info[1].end_timestamp == 1900 && info[0].ppid == -1);
     EXPECT(tsg.getCpuGenerator(1).getNumEntries() == 0);
   }
+
+  // ---- tagstack::IntervalSlicer, after hbt/src/tagstack/tests/IntervalSlicerTest.cpp ----------
+  {
+    const auto A = TransitionType::Analysis;
+    {  // EmptySlices :13-22
+      IntervalSlicer islicer{20, 0};
+      auto [s, n] = islicer.makeIntervalIntersectingSlices(0, 0, 100, false, false);
+      EXPECT(s == nullptr && n == 0 && islicer.numProcessedSlices() == 0);
+      islicer.discardConsumed();
+    }
+    {  // SingleConsumerMultiple :124-204
+      IntervalSlicer islicer{20, 0};
+      auto s1 = makeSlice(0, 99, 1, A, A);
+      EXPECT(islicer.write(s1) >= 0);
+      {
+        auto [s, n] = islicer.makeIntervalIntersectingSlices(0, 0, 100, true, true);
+        EXPECT(s == nullptr && n == 0);
+      }
+      auto s2 = makeSlice(99, 2, 1, A, A);
+      EXPECT(islicer.write(s2) >= 0);
+      {
+        auto [s, n] = islicer.makeIntervalIntersectingSlices(0, 0, 100, true, true);
+        EXPECT(s != nullptr && n == 1 && s->size() == 2 && s->at(0) == s1 && s->at(1) == makeSlice(99, 1, 1, A, A));
+      }
+      {
+        auto [s, n] = islicer.makeIntervalIntersectingSlices(1, 0, 101, true, true);
+        EXPECT(s == nullptr && n == 0);
+      }
+      auto [s, n] = islicer.makeIntervalIntersectingSlices(0, 100, 1, true, true);
+      EXPECT(s != nullptr && n == 2 && s->size() == 1 && s->at(0) == makeSlice(100, 1, 1, A, A));
+    }
+    {  // MultipleSlicerInSequence :206-300 (first part)
+      IntervalSlicer islicer{20, 0};
+      islicer.registerConsumerMark("c1");
+      islicer.registerConsumerMark("c2");
+      auto s1 = makeSlice(0, 99, 1, A, A);
+      EXPECT(islicer.write(s1) >= 0 && islicer.numActiveSlices() == 1);
+      {
+        auto s = islicer.consumeSlices("c1", 0, 100, true, true);
+        EXPECT(islicer.getMark("c1") == 0 && s->size() == 1 && s->at(0).size() == 0 && islicer.numProcessedSlices() == 0);
+      }
+      auto s2 = makeSlice(99, 2, 33, TransitionType::ThreadPreempted, TransitionType::PhaseChange);
+      EXPECT(islicer.write(s2) >= 0 && islicer.numActiveSlices() == 2);
+      {
+        auto s = islicer.consumeSlices("c2", 0, 99, true, true);
+        EXPECT(islicer.getMark("c2") == 1 && islicer.numProcessedSlices() == 0 && s->at(0).at(0) == s1);
+      }
+      {
+        auto s = islicer.consumeSlices("c1", 0, 99, true, true);
+        EXPECT(s->at(0).at(0) == s1 && islicer.getMark("c1") == 1 && islicer.numActiveSlices() == 1);
+      }
+      {
+        auto s = islicer.consumeSlices("c1", 100, 1, true, true);
+        EXPECT(s->size() == 1 && s->at(0).size() == 1 &&
+               s->at(0).at(0) == makeSlice(100, 1, 33, A, TransitionType::PhaseChange));
+      }
+    }
+    {  // a window of count rows in one call (TraceMonitor::releaseCountData_'s loop)
+      IntervalSlicer islicer{64, 0};
+      islicer.registerConsumerMark("counts");
+      for (uint64_t i = 0; i < 10; ++i)
+        EXPECT(islicer.write(makeSlice(1000 + 30 * i, 30, i % 3, TransitionType::ThreadYield, TransitionType::ThreadPreempted)) >= 0);
+      const uint64_t rows[4][3] = {{1000, 45, 7}, {1045, 45, 7}, {1090, 60, 7}, {1150, 500, 7}};
+      PerIntervalSlices pis;
+      const size_t used = islicer.releaseCountRows("counts", &rows[0][0], 4, 3, 1600, &pis);
+      EXPECT(used == 3 && pis.numIntervals() == 3 && pis.countSlices() == 2 + 3 + 2);
+      EXPECT(pis[0][0] == makeSlice(1000, 30, 0, TransitionType::ThreadYield, TransitionType::ThreadPreempted));
+      EXPECT(pis[0][1] == makeSlice(1030, 15, 1, TransitionType::ThreadYield, A));
+      EXPECT(pis[1][0] == makeSlice(1045, 15, 1, A, TransitionType::ThreadPreempted));
+      EXPECT(pis[2][1] == makeSlice(1120, 30, 1, TransitionType::ThreadYield, TransitionType::ThreadPreempted));
+      EXPECT(islicer.getMark("counts") == 5 && islicer.numProcessedSlices() == 5 && islicer.numActiveSlices() == 5);
+    }
+  }
   std::puts("SHIM OK");
   return 0;
 }
