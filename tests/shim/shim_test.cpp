@@ -242,7 +242,7 @@ int main() {
       const uint64_t rows[4][3] = {{1000, 45, 7}, {1045, 45, 7}, {1090, 60, 7}, {1150, 500, 7}};
       PerIntervalSlices pis;
       const size_t used = islicer.releaseCountRows("counts", &rows[0][0], 4, 3, 1600, &pis);
-      EXPECT(used == 3 && pis.numIntervals() == 3 && pis.countSlices() == 2 + 3 + 2);
+      EXPECT(used == 3 && pis.numIntervals() == 3 && pis.countSlices() == 2 + 2 + 2);
       EXPECT(pis[0][0] == makeSlice(1000, 30, 0, TransitionType::ThreadYield, TransitionType::ThreadPreempted));
       EXPECT(pis[0][1] == makeSlice(1030, 15, 1, TransitionType::ThreadYield, A));
       EXPECT(pis[1][0] == makeSlice(1045, 15, 1, A, TransitionType::ThreadPreempted));
