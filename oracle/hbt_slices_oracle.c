@@ -12,6 +12,7 @@
  */
 #include <errno.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "hbtslices_api.h"
@@ -125,5 +126,100 @@ int hbtoracle_islice_release(const hbtslices_slice* slices, uint64_t ns, const u
   }
   *n_intervals = k;
   *n_out = total;
+  return 0;
+}
+
+/* ---- row f1: MonData::stackIdFreqs + binmap::TagStackIdBinner (hbt/src/mon/MonData.h) --------
+ *
+ * Freqs (CuMonData::stackIdFreqs :236-256, summed over the units :382-398): per stack id the
+ * total duration, the number of slices, and the number of intervals it appears in (once per
+ * interval and unit).  Binner (:539-607): bin 0 is the ignored bin; a stack id with
+ * num_intervals >= min_distinct_intervals and duration >= min_duration gets a bin of its own
+ * -- here in ascending stack_id order (the reference walks a std::unordered_map).  The matrix
+ * has one row per count interval of all units; every unit restarts at row 0 (`unsigned i = 0`
+ * sits inside the loop over the units, :563), skips intervals without slices, adds each
+ * slice's duration to [i][bid] unless it is 0 (:581-590), and moves to the next row only if
+ * the interval's durations added up to something (:592-597).
+ */
+static int freq_cmp(const void* a, const void* b) {
+  const uint64_t x = ((const hbtslices_freq*)a)->stack_id, y = ((const hbtslices_freq*)b)->stack_id;
+  return x < y ? -1 : x > y;
+}
+
+static hbtslices_freq* freq_find(hbtslices_freq* f, uint64_t n, uint64_t sid) {
+  uint64_t lo = 0, hi = n;
+  while (lo < hi) {
+    const uint64_t mid = (lo + hi) / 2;
+    if (f[mid].stack_id < sid) lo = mid + 1;
+    else hi = mid;
+  }
+  return (lo < n && f[lo].stack_id == sid) ? &f[lo] : 0;
+}
+
+int hbtoracle_bin(const uint32_t* counts, const uint64_t* int_begin, const hbtslices_slice* slices,
+                  uint32_t n_units, uint64_t min_distinct_intervals, uint64_t min_duration,
+                  hbtslices_freq* freqs, uint64_t freq_cap, uint64_t* n_freqs, uint64_t* durations,
+                  uint64_t dur_cap, uint64_t* num_rows, uint64_t* num_bins) {
+  const uint64_t n_int = int_begin[n_units] - int_begin[0];
+  uint64_t n_slices = 0, n = 0, k, s, i;
+  uint32_t u, next_bid = 1;
+  for (k = int_begin[0]; k < int_begin[n_units]; ++k) n_slices += counts[k];
+  /* distinct stack ids, ascending: collect, sort, unique */
+  for (s = 0; s < n_slices; ++s) {
+    if (n == freq_cap) { /* compact what we have before giving up */
+      uint64_t m = 0;
+      qsort(freqs, n, sizeof(*freqs), freq_cmp);
+      for (i = 0; i < n; ++i)
+        if (m == 0 || freqs[m - 1].stack_id != freqs[i].stack_id) freqs[m++] = freqs[i];
+      n = m;
+      if (n == freq_cap) return -ENOSPC;
+    }
+    memset(&freqs[n], 0, sizeof(*freqs));
+    freqs[n++].stack_id = slices[s].stack_id;
+  }
+  qsort(freqs, n, sizeof(*freqs), freq_cmp);
+  {
+    uint64_t m = 0;
+    for (i = 0; i < n; ++i)
+      if (m == 0 || freqs[m - 1].stack_id != freqs[i].stack_id) freqs[m++] = freqs[i];
+    n = m;
+  }
+  /* stackIdFreqs */
+  s = 0;
+  for (k = int_begin[0]; k < int_begin[n_units]; ++k) {
+    for (i = 0; i < counts[k]; ++i) {
+      hbtslices_freq* f = freq_find(freqs, n, slices[s + i].stack_id);
+      uint64_t j;
+      int seen = 0;
+      ++f->num_obs;
+      f->duration += slices[s + i].duration;
+      for (j = 0; j < i && !seen; ++j) seen = slices[s + j].stack_id == slices[s + i].stack_id;
+      if (!seen) ++f->num_intervals;
+    }
+    s += counts[k];
+  }
+  for (i = 0; i < n; ++i)
+    freqs[i].bid = (freqs[i].num_intervals >= min_distinct_intervals && freqs[i].duration >= min_duration)
+                       ? next_bid++ : 0;
+  *n_freqs = n;
+  *num_rows = n_int;
+  *num_bins = next_bid;
+  if (n_int * next_bid > dur_cap) return -ENOSPC;
+  memset(durations, 0, n_int * next_bid * sizeof(uint64_t));
+  s = 0;
+  for (u = 0; u < n_units; ++u) {
+    uint64_t row = 0;
+    for (k = int_begin[u]; k < int_begin[u + 1]; ++k) {
+      uint64_t row_dur = 0;
+      for (i = 0; i < counts[k]; ++i) {
+        const hbtslices_slice* sl = &slices[s + i];
+        if (sl->duration == 0) continue;
+        row_dur += sl->duration;
+        durations[row * next_bid + freq_find(freqs, n, sl->stack_id)->bid] += sl->duration;
+      }
+      s += counts[k];
+      if (row_dur) ++row;
+    }
+  }
   return 0;
 }

@@ -1,7 +1,7 @@
 /*
  * oracle/hbtslices_api.h -- CPU checkers for the tagstack slice path (SURVEY.md section 8(f)
  * row f3): events -> slices (Slicer) and slices x count intervals -> per-interval slices
- * (IntervalSlicer), plus the per-interval duration matrix of row f1.
+ * (IntervalSlicer), plus the per-interval duration matrix of row f1 (TagStackIdBinner).
  * TEST INFRASTRUCTURE ONLY, like hbtref_api.h.
  *
  *   hbtref_*     oracle/_ref/libhbtref_slices.so: the REAL reference classes
@@ -55,6 +55,13 @@ typedef struct {
   uint64_t cum_active_time, num_swins, num_swouts;
 } hbtslices_stack;
 
+/* One stack id of MonData::stackIdFreqs (SliceFreq, hbt/src/mon/MonData.h:31-51) with the bin
+ * TagStackIdBinner gave it (MonData.h:528-607; bin 0 = ignored_bid). */
+typedef struct {
+  uint64_t stack_id, duration, num_obs, num_intervals;
+  uint32_t bid, pad;
+} hbtslices_freq;
+
 #define HBTSLICES_TRIM 1u
 #define HBTSLICES_ABORT_ON_MISSING 2u
 
@@ -84,8 +91,22 @@ typedef struct {
       hbtslices_slicer_stats* stats, hbtslices_stack* stacks, uint64_t stack_cap,                \
       uint64_t* n_stacks, uint64_t* last_ts);
 
+/* TagStackIdBinner over a MonData whose comp unit u holds n_int = int_begin[u+1] - int_begin[u]
+ * count intervals with counts[int_begin[u] + k] slices each (slices: all of them, unit after
+ * unit, interval after interval).  freqs come out in ascending stack_id order; durations is the
+ * IntervalBinMatrix, num_rows x num_bins, row-major.  The REAL binner numbers the bins in the
+ * iteration order of a std::unordered_map (implementation-defined); the restatement numbers
+ * them in ascending stack_id order -- compare through freqs[].bid.  Returns 0, -ENOSPC. */
+#define HBTSLICES_BIN_DECL(prefix)                                                               \
+  int prefix##_bin(const uint32_t* counts, const uint64_t* int_begin, const hbtslices_slice* slices, \
+      uint32_t n_units, uint64_t min_distinct_intervals, uint64_t min_duration,                  \
+      hbtslices_freq* freqs, uint64_t freq_cap, uint64_t* n_freqs, uint64_t* durations,          \
+      uint64_t dur_cap, uint64_t* num_rows, uint64_t* num_bins);
+
 HBTSLICES_DECL(hbtref)
 HBTSLICES_DECL(hbtoracle)
+HBTSLICES_BIN_DECL(hbtref)
+HBTSLICES_BIN_DECL(hbtoracle)
 
 #ifdef __cplusplus
 }

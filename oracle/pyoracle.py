@@ -451,3 +451,37 @@ def slicer_run(kind, events, n_units, cap_per_unit=None, stack_cap=None):
     return {"rc": rc, "slices": [out[u, :int(n_slices[u])].copy() for u in range(n_units)],
             "stats": dict(zip(SLICER_STAT_KEYS, (int(x) for x in stats))),
             "stacks": stacks[:n_stacks.value].copy(), "last_ts": last_ts.value}
+
+
+FREQ_DTYPE = np.dtype([("stack_id", "<u8"), ("duration", "<u8"), ("num_obs", "<u8"),
+                       ("num_intervals", "<u8"), ("bid", "<u4"), ("pad", "<u4")])
+assert FREQ_DTYPE.itemsize == 40
+
+
+def bin_durations(kind, unit_counts, unit_slices, min_distinct_intervals, min_duration):
+    """TagStackIdBinner over per-unit PerIntervalSlices.  unit_counts[u]: slices per interval,
+    unit_slices[u]: the unit's slices in interval order.  Returns dict(freqs, durations
+    [num_rows, num_bins], num_rows, num_bins); bins numbered as `kind` numbers them."""
+    lib, prefix = _slices_lib(kind)
+    f = getattr(lib, prefix + "_bin")
+    f.restype = C.c_int
+    counts = np.ascontiguousarray(np.concatenate([np.asarray(c, np.uint32) for c in unit_counts])
+                                  if len(unit_counts) else np.zeros(0, np.uint32), dtype=np.uint32)
+    begin = np.concatenate([[0], np.cumsum([len(c) for c in unit_counts])]).astype(np.uint64)
+    slices = np.ascontiguousarray(np.concatenate(unit_slices) if len(unit_slices) else
+                                  np.zeros(0, SLICE_DTYPE), dtype=SLICE_DTYPE)
+    assert int(counts.sum()) == len(slices)
+    freqs = np.zeros(max(1, len(slices)), FREQ_DTYPE)
+    n_freqs, num_rows, num_bins = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+    dur_cap = (len(counts) + 1) * (len(slices) + 2)
+    durations = np.zeros(dur_cap, np.uint64)
+    counts_p = counts if len(counts) else np.zeros(1, np.uint32)
+    rc = f(_p(counts_p, C.c_uint32), _p(begin, C.c_uint64), C.c_void_p(slices.ctypes.data),
+           C.c_uint32(len(unit_counts)), C.c_uint64(min_distinct_intervals), C.c_uint64(min_duration),
+           C.c_void_p(freqs.ctypes.data), C.c_uint64(len(freqs)), C.byref(n_freqs),
+           _p(durations, C.c_uint64), C.c_uint64(dur_cap), C.byref(num_rows), C.byref(num_bins))
+    if rc != 0:
+        raise ValueError(f"bin_durations: rc={rc}")
+    nr, nb = num_rows.value, num_bins.value
+    return {"freqs": freqs[:n_freqs.value].copy(), "durations": durations[:nr * nb].reshape(nr, nb).copy(),
+            "num_rows": nr, "num_bins": nb}

@@ -14,6 +14,7 @@
 #include <fmt/ranges.h>
 
 namespace pfs {
+struct mem_region {};  // named in a declaration of hbt/src/mon/MonData.h:666 only
 struct task {
   std::vector<std::string> get_cmdline() const {
     throw std::system_error(std::make_error_code(std::errc::no_such_file_or_directory));
