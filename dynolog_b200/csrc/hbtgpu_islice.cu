@@ -736,6 +736,167 @@ k_islice_emit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
   }
 }
 
+
+// ==== stack-id frequencies and the interval x bin duration matrix =====
+//
+// Reference: CuMonData::stackIdFreqs (hbt/src/mon/MonData.h:236-256) summed over the units by
+// MonData::stackIdFreqs (:382-398), and binmap::TagStackIdBinner (:528-607), both loops over
+// every slice of every interval.  Here they run over the per-interval slices the release left on
+// the device: an open-addressing table stack_id -> {duration, num_obs, num_intervals} filled with
+// atomics (k_bin_freqs; "first time this stack id shows up in the interval" is a look at the
+// interval's earlier slices), the few distinct stack ids go to the host to be numbered
+// (BinMapper is a host dictionary in the reference too), and k_bin_durations adds every slice's
+// duration to M[row][bin] where row = the interval's rank among the unit's intervals whose
+// durations add up to something (every unit starts at row 0, as `unsigned i = 0` inside the
+// unit loop of :563 does).
+
+struct BinTable {
+  unsigned long long* key;   // stack_id + 1, 0 = empty; slot cap is reserved for stack_id ~0
+  unsigned long long* dur;
+  unsigned long long* obs;
+  unsigned long long* nint;
+  uint32_t* bid;
+  uint32_t cap;  // power of two
+};
+
+__device__ __forceinline__ uint32_t bin_hash(uint64_t x, uint32_t mask) {
+  x ^= x >> 30;
+  x *= 0xbf58476d1ce4e5b9ull;
+  x ^= x >> 27;
+  x *= 0x94d049bb133111ebull;
+  x ^= x >> 31;
+  return static_cast<uint32_t>(x) & mask;
+}
+// slot of sid, inserting it if absent; 0xffffffff when the table is full
+__device__ __forceinline__ uint32_t bin_slot_insert(const BinTable& t, uint64_t sid) {
+  if (sid == NONE) {
+    t.key[t.cap] = 1;  // benign race: everyone writes the same value
+    return t.cap;
+  }
+  const unsigned long long k = sid + 1;
+  uint32_t h = bin_hash(sid, t.cap - 1);
+  for (uint32_t probe = 0; probe < t.cap; ++probe) {
+    const unsigned long long cur = t.key[h];
+    if (cur == k) return h;
+    if (cur == 0) {
+      const unsigned long long old = atomicCAS(&t.key[h], 0ull, k);
+      if (old == 0 || old == k) return h;
+    }
+    h = (h + 1) & (t.cap - 1);
+  }
+  return 0xffffffffu;
+}
+__device__ __forceinline__ uint32_t bin_slot_find(const BinTable& t, uint64_t sid) {
+  if (sid == NONE) return t.cap;
+  const unsigned long long k = sid + 1;
+  uint32_t h = bin_hash(sid, t.cap - 1);
+  while (t.key[h] != k) h = (h + 1) & (t.cap - 1);
+  return h;
+}
+
+// (unit, tile of NT intervals): frequencies; which intervals have a duration; tile counts
+__global__ void __launch_bounds__(NT)
+k_bin_freqs(const Unit* __restrict__ units, uint32_t n_units, const hbtgpu_islice_unit* __restrict__ results,
+            const uint8_t* __restrict__ selected, const hbtgpu_slice* __restrict__ out_all,
+            const uint32_t* __restrict__ ioff_all, const uint32_t* __restrict__ icnt_all, BinTable t,
+            uint8_t* __restrict__ has_all, uint32_t* __restrict__ bt_tot, unsigned long long* __restrict__ counters) {
+  const uint32_t u = find_unit<true>(units, n_units, blockIdx.x);
+  if (selected && !selected[u]) return;
+  const Unit U = units[u];
+  const uint64_t k = static_cast<uint64_t>(blockIdx.x - U.rt0) * NT + threadIdx.x;
+  const bool in = k < results[u].n_intervals;
+  bool has = false, empty_dur = false;
+  if (in) {
+    const uint32_t cnt = icnt_all[U.r0 + k];
+    const hbtgpu_slice* sl = out_all + U.out0 + ioff_all[U.r0 + k];
+    uint64_t row_dur = 0;
+    for (uint32_t i = 0; i < cnt; ++i) {
+      const uint64_t sid = sl[i].stack_id, d = sl[i].duration;
+      const uint32_t slot = bin_slot_insert(t, sid);
+      if (slot == 0xffffffffu) {
+        atomicOr(&counters[0], 1ull);
+        break;
+      }
+      if (d) atomicAdd(&t.dur[slot], static_cast<unsigned long long>(d));
+      atomicAdd(&t.obs[slot], 1ull);
+      bool seen = false;  // the reference's per-interval std::set (:243-252)
+      for (uint32_t j = 0; j < i && !seen; ++j) seen = sl[j].stack_id == sid;
+      if (!seen) atomicAdd(&t.nint[slot], 1ull);
+      row_dur += d;
+    }
+    has = row_dur != 0;
+    empty_dur = cnt != 0 && !has;
+    has_all[U.r0 + k] = has;
+  }
+  const int n_has = __syncthreads_count(has);
+  const int n_skipped = __syncthreads_count(empty_dur);
+  if (threadIdx.x == 0) {
+    bt_tot[blockIdx.x] = n_has;
+    if (n_skipped) atomicAdd(&counters[1], static_cast<unsigned long long>(n_skipped));
+  }
+}
+
+// per unit: exclusive scan of the tile counts
+__global__ void __launch_bounds__(NT)
+k_bin_scan(const Unit* __restrict__ units, const hbtgpu_islice_unit* __restrict__ results,
+           const uint8_t* __restrict__ selected, const uint32_t* __restrict__ bt_tot, uint64_t* __restrict__ bt_base) {
+  __shared__ uint64_t sh_red[32];
+  if (selected && !selected[blockIdx.x]) return;
+  const Unit U = units[blockIdx.x];
+  const uint32_t n_tiles = static_cast<uint32_t>((results[blockIdx.x].n_intervals + NT - 1) / NT);
+  uint64_t carry = 0;
+  for (uint32_t i0 = 0; i0 < n_tiles; i0 += NT) {
+    const uint32_t i = i0 + threadIdx.x;
+    const uint64_t v = i < n_tiles ? bt_tot[U.rt0 + i] : 0;
+    uint64_t tot;
+    const uint64_t incl = block_incl_sum_u64(v, sh_red, &tot);
+    if (i < n_tiles) bt_base[U.rt0 + i] = carry + incl - v;
+    carry += tot;
+  }
+}
+
+// occupied slots -> a dense list (any order); the host sorts and numbers them
+struct BinEntry {
+  uint64_t stack_id, duration, num_obs, num_intervals;
+  uint32_t slot, pad;
+};
+__global__ void k_bin_compact(BinTable t, BinEntry* __restrict__ list, unsigned long long* __restrict__ counters) {
+  const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+  if (h > t.cap || t.key[h] == 0) return;
+  const unsigned long long at = atomicAdd(&counters[2], 1ull);
+  list[at] = BinEntry{h == t.cap ? NONE : t.key[h] - 1, t.dur[h], t.obs[h], t.nint[h], h, 0};
+}
+__global__ void k_bin_set_bids(BinTable t, const uint32_t* __restrict__ slot, const uint32_t* __restrict__ bid, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) t.bid[slot[i]] = bid[i];
+}
+
+// (unit, tile of NT intervals): M[row][bin] += duration
+__global__ void __launch_bounds__(NT)
+k_bin_durations(const Unit* __restrict__ units, uint32_t n_units, const hbtgpu_islice_unit* __restrict__ results,
+                const uint8_t* __restrict__ selected, const hbtgpu_slice* __restrict__ out_all,
+                const uint32_t* __restrict__ ioff_all, const uint32_t* __restrict__ icnt_all, BinTable t,
+                const uint8_t* __restrict__ has_all, const uint64_t* __restrict__ bt_base,
+                unsigned long long* __restrict__ M, uint64_t num_bins) {
+  __shared__ uint64_t sh_red[32];
+  const uint32_t u = find_unit<true>(units, n_units, blockIdx.x);
+  if (selected && !selected[u]) return;
+  const Unit U = units[u];
+  const uint64_t k = static_cast<uint64_t>(blockIdx.x - U.rt0) * NT + threadIdx.x;
+  const bool in = k < results[u].n_intervals;
+  const bool has = in && has_all[U.r0 + k];
+  uint64_t tot;
+  const uint64_t row = bt_base[blockIdx.x] + block_incl_sum_u64(has ? 1 : 0, sh_red, &tot) - (has ? 1 : 0);
+  if (!has) return;
+  const uint32_t cnt = icnt_all[U.r0 + k];
+  const hbtgpu_slice* sl = out_all + U.out0 + ioff_all[U.r0 + k];
+  for (uint32_t i = 0; i < cnt; ++i) {
+    const uint64_t d = sl[i].duration;
+    if (d == 0) continue;  // :581-590
+    atomicAdd(&M[row * num_bins + t.bid[bin_slot_find(t, sl[i].stack_id)]], static_cast<unsigned long long>(d));
+  }
+}
+
 }  // namespace
 
 struct hbtgpu_islice_ctx {
@@ -763,6 +924,20 @@ struct hbtgpu_islice_ctx {
   UState* d_ustate = nullptr;        size_t cap_ustate = 0;
   hbtgpu_islice_unit* d_res = nullptr; size_t cap_res = 0;
   uint64_t* d_base = nullptr;        size_t cap_base = 0;
+  // binner (f1)
+  unsigned long long* d_bin_tab = nullptr; size_t cap_bin_tab = 0;  // key, dur, obs, nint: 4 x (cap + 1)
+  uint32_t* d_bin_bid = nullptr;     size_t cap_bin_bid = 0;
+  uint8_t* d_has = nullptr;          size_t cap_has = 0;
+  uint32_t* d_bt_tot = nullptr;      size_t cap_bt_tot = 0;
+  uint64_t* d_bt_base = nullptr;     size_t cap_bt_base = 0;
+  BinEntry* d_bin_list = nullptr;    size_t cap_bin_list = 0;
+  uint32_t* d_bin_up = nullptr;      size_t cap_bin_up = 0;
+  unsigned long long* d_bin_M = nullptr; size_t cap_bin_M = 0;
+  unsigned long long* d_bin_ctr = nullptr; size_t cap_bin_ctr = 0;
+  uint8_t* d_sel = nullptr;          size_t cap_sel = 0;
+  std::vector<hbtgpu_bin_freq> bin_freqs;
+  hbtgpu_bin_summary bin_summary{};
+  bool have_bin = false;
   // last call
   std::vector<Unit> units;
   std::vector<UState> ustate;
@@ -832,6 +1007,8 @@ void hbtgpu_islice_destroy(hbtgpu_islice_ctx* c) {
   cudaFree(c->d_slices); cudaFree(c->d_rows); cudaFree(c->d_G); cudaFree(c->d_vt_tot); cudaFree(c->d_vt_base);
   cudaFree(c->d_rt_tot); cudaFree(c->d_rt_base); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_ql); cudaFree(c->d_td); cudaFree(c->d_ioff); cudaFree(c->d_icnt); cudaFree(c->d_ifirst);
   cudaFree(c->d_out); cudaFree(c->d_units); cudaFree(c->d_ustate); cudaFree(c->d_res); cudaFree(c->d_base);
+  cudaFree(c->d_bin_tab); cudaFree(c->d_bin_bid); cudaFree(c->d_has); cudaFree(c->d_bt_tot); cudaFree(c->d_bt_base);
+  cudaFree(c->d_bin_list); cudaFree(c->d_bin_up); cudaFree(c->d_bin_M); cudaFree(c->d_bin_ctr); cudaFree(c->d_sel);
   for (cudaEvent_t e : {c->ev0, c->ev1, c->ev2, c->ev3})
     if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -848,6 +1025,7 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
                           hbtgpu_islice_unit* units_out) {
   if (!c) return -EINVAL;
   c->have = false;
+  c->have_bin = false;
   if (!slice_begin || !row_begin || !marks || n_units == 0) return ifail(c, -EINVAL, "null argument or no units");
   if (row_stride < 2) return ifail(c, -EINVAL, "row_stride must be >= 2 (tstamp, duration, ...)");
   IK(cudaSetDevice(c->device));
@@ -1027,6 +1205,132 @@ int hbtgpu_islice_device_view(hbtgpu_islice_ctx* c, hbtgpu_islice_view* view) {
   view->interval_count = c->d_icnt;
   view->n_units = static_cast<uint32_t>(n);
   return 0;
+}
+
+int hbtgpu_islice_bin(hbtgpu_islice_ctx* c, const uint8_t* unit_selected, uint64_t min_distinct_intervals,
+                      uint64_t min_duration, uint64_t max_stack_ids, uint64_t max_matrix_bytes,
+                      hbtgpu_bin_summary* summary) {
+  if (!c) return -EINVAL;
+  c->have_bin = false;
+  if (!c->have) return ifail(c, -EINVAL, "no results: call hbtgpu_islice_release first");
+  if (max_stack_ids == 0 || max_stack_ids > (1ull << 30)) return ifail(c, -EINVAL, "max_stack_ids must be in [1, 2^30]");
+  IK(cudaSetDevice(c->device));
+  const uint32_t n_units = static_cast<uint32_t>(c->units.size());
+  uint64_t num_rows = 0, total_r = 0, n_rt = 0;
+  for (uint32_t u = 0; u < n_units; ++u) {
+    total_r = std::max(total_r, c->units[u].r0 + c->units[u].K);
+    n_rt = std::max<uint64_t>(n_rt, c->units[u].rt0 + (c->units[u].K + NT - 1) / NT);
+    if (unit_selected && !unit_selected[u]) continue;
+    if (c->res[u].status != 0)
+      return ifail(c, -EINVAL, "unit %u has no valid per-interval slices (status %lld)", u, (long long)c->res[u].status);
+    num_rows += c->res[u].n_intervals;  // MonData::numCountIntervals, MonData.h:334-345
+  }
+  uint32_t cap = 64;
+  while (cap < 2 * max_stack_ids) cap <<= 1;
+  const size_t tab_words = 4 * (static_cast<size_t>(cap) + 1);
+  if (int rc = grow(c, &c->d_bin_tab, &c->cap_bin_tab, tab_words)) return rc;
+  if (int rc = grow(c, &c->d_bin_bid, &c->cap_bin_bid, static_cast<size_t>(cap) + 1)) return rc;
+  if (int rc = grow(c, &c->d_has, &c->cap_has, total_r + 1)) return rc;
+  if (int rc = grow(c, &c->d_bt_tot, &c->cap_bt_tot, n_rt + 1)) return rc;
+  if (int rc = grow(c, &c->d_bt_base, &c->cap_bt_base, n_rt + 1)) return rc;
+  if (int rc = grow(c, &c->d_bin_ctr, &c->cap_bin_ctr, 4)) return rc;
+  const uint8_t* d_sel = nullptr;
+  if (unit_selected) {
+    if (int rc = grow(c, &c->d_sel, &c->cap_sel, n_units)) return rc;
+    IK(cudaMemcpyAsync(c->d_sel, unit_selected, n_units, cudaMemcpyHostToDevice, c->stream));
+    d_sel = c->d_sel;
+  }
+  IK(cudaMemsetAsync(c->d_bin_tab, 0, tab_words * sizeof(unsigned long long), c->stream));
+  IK(cudaMemsetAsync(c->d_bin_bid, 0, (static_cast<size_t>(cap) + 1) * sizeof(uint32_t), c->stream));
+  IK(cudaMemsetAsync(c->d_bin_ctr, 0, 4 * sizeof(unsigned long long), c->stream));
+  BinTable t{c->d_bin_tab, c->d_bin_tab + (cap + 1), c->d_bin_tab + 2 * (static_cast<size_t>(cap) + 1),
+             c->d_bin_tab + 3 * (static_cast<size_t>(cap) + 1), c->d_bin_bid, cap};
+  IK(cudaEventRecord(c->ev0, c->stream));
+  if (n_rt) {
+    k_bin_freqs<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(c->d_units, n_units, c->d_res, d_sel, c->d_out,
+                                                                   c->d_ioff, c->d_icnt, t, c->d_has, c->d_bt_tot,
+                                                                   c->d_bin_ctr);
+    k_bin_scan<<<n_units, NT, 0, c->stream>>>(c->d_units, c->d_res, d_sel, c->d_bt_tot, c->d_bt_base);
+  }
+  if (int rc = grow(c, &c->d_bin_list, &c->cap_bin_list, static_cast<size_t>(cap) + 1)) return rc;
+  k_bin_compact<<<(cap + 1 + 255) / 256, 256, 0, c->stream>>>(t, c->d_bin_list, c->d_bin_ctr);
+  IK(cudaGetLastError());
+  IK(cudaEventRecord(c->ev1, c->stream));
+  unsigned long long ctr[4] = {0, 0, 0, 0};
+  IK(cudaMemcpyAsync(ctr, c->d_bin_ctr, sizeof(ctr), cudaMemcpyDeviceToHost, c->stream));
+  IK(cudaStreamSynchronize(c->stream));
+  if (ctr[0] || ctr[2] > max_stack_ids)
+    return ifail(c, -ENOSPC, "more than max_stack_ids = %llu distinct stack ids", (unsigned long long)max_stack_ids);
+  std::vector<BinEntry> list(ctr[2]);
+  if (!list.empty())
+    IK(cudaMemcpy(list.data(), c->d_bin_list, list.size() * sizeof(BinEntry), cudaMemcpyDeviceToHost));
+  std::sort(list.begin(), list.end(), [](const BinEntry& a, const BinEntry& b) { return a.stack_id < b.stack_id; });
+  // BinMapper: bin 0 = ignored_bid, then one bin per stack id that qualifies (MonData.h:539-557),
+  // in ascending stack_id order (the reference walks a std::unordered_map: any order)
+  c->bin_freqs.resize(list.size());
+  std::vector<uint32_t> up(2 * list.size() + 2);
+  uint32_t next_bid = 1;
+  for (size_t i = 0; i < list.size(); ++i) {
+    const bool own = list[i].num_intervals >= min_distinct_intervals && list[i].duration >= min_duration;
+    const uint32_t bid = own ? next_bid++ : 0u;
+    c->bin_freqs[i] = hbtgpu_bin_freq{list[i].stack_id, list[i].duration, list[i].num_obs, list[i].num_intervals, bid, 0};
+    up[i] = list[i].slot;
+    up[list.size() + i] = bid;
+  }
+  c->bin_summary = hbtgpu_bin_summary{num_rows, next_bid, list.size(), ctr[1]};
+  if (summary) *summary = c->bin_summary;
+  const unsigned long long cells = static_cast<unsigned long long>(num_rows) * next_bid;
+  if (cells * 8 > max_matrix_bytes)
+    return ifail(c, -E2BIG, "the matrix needs %llu x %u x 8 bytes, more than max_matrix_bytes",
+                 (unsigned long long)num_rows, next_bid);
+  if (int rc = grow(c, &c->d_bin_M, &c->cap_bin_M, cells + 1)) return rc;
+  IK(cudaMemsetAsync(c->d_bin_M, 0, (cells + 1) * sizeof(unsigned long long), c->stream));
+  if (!list.empty()) {
+    if (int rc = grow(c, &c->d_bin_up, &c->cap_bin_up, up.size())) return rc;
+    IK(cudaMemcpyAsync(c->d_bin_up, up.data(), up.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    IK(cudaEventRecord(c->ev2, c->stream));
+    k_bin_set_bids<<<static_cast<unsigned>((list.size() + 255) / 256), 256, 0, c->stream>>>(
+        t, c->d_bin_up, c->d_bin_up + list.size(), static_cast<uint32_t>(list.size()));
+    if (n_rt)
+      k_bin_durations<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(c->d_units, n_units, c->d_res, d_sel, c->d_out,
+                                                                         c->d_ioff, c->d_icnt, t, c->d_has,
+                                                                         c->d_bt_base, c->d_bin_M, next_bid);
+    IK(cudaGetLastError());
+    IK(cudaEventRecord(c->ev3, c->stream));
+  } else {
+    IK(cudaEventRecord(c->ev2, c->stream));
+    IK(cudaEventRecord(c->ev3, c->stream));
+  }
+  IK(cudaStreamSynchronize(c->stream));
+  float a = 0.f, b = 0.f;
+  IK(cudaEventElapsedTime(&a, c->ev0, c->ev1));
+  IK(cudaEventElapsedTime(&b, c->ev2, c->ev3));
+  c->last_ms = a + b;
+  c->have_bin = true;
+  return 0;
+}
+
+int hbtgpu_islice_bin_get(hbtgpu_islice_ctx* c, hbtgpu_bin_freq* freqs, uint64_t freq_cap, uint64_t* durations,
+                          uint64_t durations_cap) {
+  if (!c) return -EINVAL;
+  if (!c->have_bin) return ifail(c, -EINVAL, "no matrix: call hbtgpu_islice_bin first");
+  IK(cudaSetDevice(c->device));
+  if (freqs) {
+    if (freq_cap < c->bin_freqs.size()) return ifail(c, -ENOSPC, "%zu stack ids, room for %llu", c->bin_freqs.size(),
+                                                     (unsigned long long)freq_cap);
+    if (!c->bin_freqs.empty()) memcpy(freqs, c->bin_freqs.data(), c->bin_freqs.size() * sizeof(hbtgpu_bin_freq));
+  }
+  if (durations) {
+    const uint64_t cells = c->bin_summary.num_rows * c->bin_summary.num_bins;
+    if (durations_cap < cells) return ifail(c, -ENOSPC, "%llu cells, room for %llu", (unsigned long long)cells,
+                                            (unsigned long long)durations_cap);
+    if (cells) IK(cudaMemcpy(durations, c->d_bin_M, cells * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  }
+  return 0;
+}
+
+const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* c) {
+  return (c && c->have_bin) ? reinterpret_cast<const uint64_t*>(c->d_bin_M) : nullptr;
 }
 
 }  // extern "C"

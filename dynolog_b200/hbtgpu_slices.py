@@ -11,7 +11,9 @@ SLICE_DTYPE = np.dtype([("tstamp", "<u8"), ("duration", "<u8"), ("stack_id", "<u
                         ("swin_type", "u1"), ("swout_type", "u1"), ("pad", "u1", (6,))])
 UNIT_DTYPE = np.dtype([("n_intervals", "<u8"), ("n_slices", "<u8"), ("mark", "<u8"), ("status", "<i8"),
                        ("err_interval", "<u8"), ("exact_path", "<u4"), ("pad", "<u4")])
-assert SLICE_DTYPE.itemsize == 32 and UNIT_DTYPE.itemsize == 48
+FREQ_DTYPE = np.dtype([("stack_id", "<u8"), ("duration", "<u8"), ("num_obs", "<u8"), ("num_intervals", "<u8"),
+                       ("bid", "<u4"), ("pad", "<u4")])
+assert SLICE_DTYPE.itemsize == 32 and UNIT_DTYPE.itemsize == 48 and FREQ_DTYPE.itemsize == 40
 
 TRIM, ABORT_ON_MISSING, DEVICE_INPUT, FORCE_EXACT = 1, 2, 4, 8
 
@@ -19,7 +21,13 @@ ABI_SYMBOLS = [
     "hbtgpu_islice_create", "hbtgpu_islice_destroy", "hbtgpu_islice_last_error",
     "hbtgpu_islice_release", "hbtgpu_islice_get_units", "hbtgpu_islice_get",
     "hbtgpu_islice_device_view", "hbtgpu_islice_last_ms",
+    "hbtgpu_islice_bin", "hbtgpu_islice_bin_get", "hbtgpu_islice_bin_durations_device",
 ]
+
+
+class BinSummary(C.Structure):
+    _fields_ = [("num_rows", C.c_uint64), ("num_bins", C.c_uint64), ("num_stack_ids", C.c_uint64),
+                ("rows_skipped", C.c_uint64)]
 
 
 class View(C.Structure):
@@ -49,6 +57,11 @@ def _lib():
         L.hbtgpu_islice_get.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p,
                                         C.c_uint64]
         L.hbtgpu_islice_device_view.argtypes = [C.c_void_p, C.c_void_p]
+        L.hbtgpu_islice_bin.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64,
+                                        C.c_void_p]
+        L.hbtgpu_islice_bin_get.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
+        L.hbtgpu_islice_bin_durations_device.restype = C.c_void_p
+        L.hbtgpu_islice_bin_durations_device.argtypes = [C.c_void_p]
         _ready = True
     return L
 
@@ -129,6 +142,24 @@ class IntervalSlicer:
         v = View()
         self._check(self.L.hbtgpu_islice_device_view(self.h, C.byref(v)))
         return v
+
+    def bin(self, min_distinct_intervals, min_duration, selected=None, max_stack_ids=1 << 20,
+            max_matrix_bytes=1 << 30, fetch=True):
+        """MonData::stackIdFreqs + TagStackIdBinner over the last release.  Returns dict(freqs,
+        durations [num_rows, num_bins] or None, num_rows, num_bins, rows_skipped)."""
+        summ = BinSummary()
+        sel = None if selected is None else np.ascontiguousarray(selected, dtype=np.uint8)
+        self._check(self.L.hbtgpu_islice_bin(self.h, None if sel is None else sel.ctypes.data,
+                                             min_distinct_intervals, min_duration, max_stack_ids, max_matrix_bytes,
+                                             C.byref(summ)))
+        freqs = np.zeros(max(1, summ.num_stack_ids), FREQ_DTYPE)
+        cells = summ.num_rows * summ.num_bins
+        dur = np.zeros(max(1, cells), np.uint64) if fetch else None
+        self._check(self.L.hbtgpu_islice_bin_get(self.h, freqs.ctypes.data, len(freqs),
+                                                 dur.ctypes.data if fetch else None, len(dur) if fetch else 0))
+        return {"freqs": freqs[:summ.num_stack_ids],
+                "durations": dur[:cells].reshape(summ.num_rows, summ.num_bins) if fetch else None,
+                "num_rows": summ.num_rows, "num_bins": summ.num_bins, "rows_skipped": summ.rows_skipped}
 
     @property
     def last_ms(self):

@@ -604,6 +604,41 @@ typedef struct {
 int hbtgpu_islice_device_view(hbtgpu_islice_ctx* ctx, hbtgpu_islice_view* view);
 float hbtgpu_islice_last_ms(const hbtgpu_islice_ctx* ctx); /* device time of the kernels of the last release */
 
+/* ---- Stack-id frequencies and the interval x bin duration matrix ----
+ *
+ * Replaces, over the per-interval slices the last hbtgpu_islice_release left on the device,
+ *   CuMonData::stackIdFreqs / MonData::stackIdFreqs   hbt/src/mon/MonData.h:236-256,382-398
+ *   binmap::TagStackIdBinner (constructor)            hbt/src/mon/MonData.h:528-607
+ *   binmap::BinMapper / IntervalBinMatrix<uint64_t>   :425-523
+ * Per stack id: total duration, number of slices, number of distinct intervals (per unit) it
+ * shows up in.  A stack id with num_intervals >= min_distinct_intervals and duration >=
+ * min_duration gets a bin of its own, all others share bin 0 (ignored_bid); own bins are
+ * numbered in ascending stack_id order (the reference numbers them in the iteration order of a
+ * std::unordered_map, i.e. unspecified).  The matrix has one row per count interval of the
+ * selected units and one column per bin; as in the reference every unit starts adding at row 0,
+ * intervals without slices are passed over, zero-length slices are not added, and an interval
+ * only moves the unit to its next row if its durations added up to something (:563-597).
+ * unit_selected: [n_units] 0/1 (the reference's cpu_set), NULL = all.  max_stack_ids bounds the
+ * device dictionary (-ENOSPC beyond), max_matrix_bytes the dense matrix (-E2BIG beyond; the
+ * summary and the frequencies are valid then).  -EINVAL if a selected unit's release failed. */
+typedef struct {
+  uint64_t stack_id, duration, num_obs, num_intervals;  /* SliceFreq, MonData.h:31-51 */
+  uint32_t bid, pad;                                    /* BinMapper::binkey_to_bid */
+} hbtgpu_bin_freq;
+typedef struct {
+  uint64_t num_rows;       /* IntervalBinMatrix::kNumIntervals = MonData::numCountIntervals */
+  uint64_t num_bins;       /* kNumBids, the ignored bin included */
+  uint64_t num_stack_ids;  /* distinct stack ids = entries of hbtgpu_islice_bin_get's freqs */
+  uint64_t rows_skipped;   /* intervals with slices whose durations are all 0 (num_skipped, :565,595) */
+} hbtgpu_bin_summary;
+int hbtgpu_islice_bin(hbtgpu_islice_ctx* ctx, const uint8_t* unit_selected, uint64_t min_distinct_intervals,
+                      uint64_t min_duration, uint64_t max_stack_ids, uint64_t max_matrix_bytes,
+                      hbtgpu_bin_summary* summary);
+/* freqs in ascending stack_id order; durations = the matrix, num_rows x num_bins, row-major.  Either may be NULL. */
+int hbtgpu_islice_bin_get(hbtgpu_islice_ctx* ctx, hbtgpu_bin_freq* freqs, uint64_t freq_cap, uint64_t* durations,
+                          uint64_t durations_cap);
+const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* ctx); /* the matrix where it was built */
+
 #ifdef __cplusplus
 }
 #endif

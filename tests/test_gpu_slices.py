@@ -186,3 +186,58 @@ def test_device_input_and_view(slicer):
         assert np.array_equal(counts, exp["counts"]) and np.array_equal(fields(out), fields(exp["slices"]))
         assert units[u]["mark"] == exp["mark"]
     assert slicer.last_ms > 0
+
+
+# ---- row f1: frequencies + the interval x bin matrix over the released slices ----------------------
+def bin_compare(slicer, us, ur, flags, min_int, min_dur, selected=None, zero_some=False):
+    n = len(us)
+    stride = ur[0].shape[1]
+    sb = np.concatenate([[0], np.cumsum([len(s) for s in us])]).astype(np.uint64)
+    rb = np.concatenate([[0], np.cumsum([len(r) for r in ur])]).astype(np.uint64)
+    marks = np.zeros(n, np.uint64)
+    units = slicer.release(np.concatenate(us), sb, np.concatenate(ur).reshape(-1, stride), rb, 2**63, flags, marks)
+    assert (units["status"] == 0).all()
+    sel = range(n) if selected is None else [u for u in range(n) if selected[u]]
+    uc, uo = [], []
+    for u in sel:
+        counts, out = slicer.get(u)
+        uc.append(counts)
+        uo.append(out)
+    got = slicer.bin(min_int, min_dur, selected=selected)
+    exp = po.bin_durations("port", uc, uo, min_int, min_dur)      # same numbering: ascending stack id
+    for k in ("stack_id", "duration", "num_obs", "num_intervals", "bid"):
+        assert np.array_equal(got["freqs"][k], exp["freqs"][k]), k
+    assert got["num_rows"] == exp["num_rows"] and got["num_bins"] == exp["num_bins"]
+    assert np.array_equal(got["durations"], exp["durations"])
+    return got
+
+
+@pytest.mark.parametrize("min_int,min_dur", [(0, 0), (1, 1), (3, 200), (1, 10**12)])
+def test_bin_matrix(slicer, min_int, min_dur):
+    r = np.random.default_rng(40 + min_int)
+    for trial in range(4):
+        n_units = int(r.integers(1, 7))
+        us = [slicegen.gen_slices(r, int(r.choice([0, 5, 600, 3000])), hole_prob=0.1, n_stacks=int(r.choice([2, 40, 2000])))
+              for _ in range(n_units)]
+        for s in us:
+            s["stack_id"] += np.uint64(r.choice([0, 1 << 45]))
+            s["stack_id"][r.random(len(s)) < 0.01] = np.uint64(2**64 - 1)        # kInvalidTagStackId as a key
+        ur = [slicegen.gen_rows(r, s, int(r.choice([0, 3, 700, 1100])), stride=4, align_prob=0.3) for s in us]
+        got = bin_compare(slicer, us, ur, int(r.choice([1, 3])), min_int, min_dur)
+        sel = (r.random(n_units) < 0.6).astype(np.uint8)
+        bin_compare(slicer, us, ur, 3, min_int, min_dur, selected=sel)
+    assert got["num_bins"] >= 1
+
+
+def test_bin_zero_length_slices_and_limits(slicer):
+    from dynolog_b200.hbtgpu import HbtGpuError
+    Yd = po.TT_YIELD
+    # an aligned chain leaves zero-length first slices in the intervals (trim without abort)
+    s = po.make_slices([(0, 100, 5, Yd, Yd), (100, 50, 6, Yd, Yd), (150, 50, 5, Yd, Yd), (300, 10, 9, Yd, Yd)])
+    rows = np.array([[100, 50], [150, 50], [200, 50], [290, 30]], np.uint64)
+    got = bin_compare(slicer, [s], [rows], po.TRIM, 1, 1)
+    assert got["rows_skipped"] == 0 and got["num_rows"] == 4
+    with pytest.raises(HbtGpuError):
+        slicer.bin(0, 0, max_stack_ids=1)              # three distinct stack ids do not fit
+    with pytest.raises(HbtGpuError):
+        slicer.bin(0, 0, max_matrix_bytes=8)           # 4 rows x 4 bins do not fit
