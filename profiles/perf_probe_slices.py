@@ -76,6 +76,36 @@ def main():
         print(f"{name:26s} units {Us:4d} slices {n_s/1e6:6.2f} M rows {n_r/1e6:6.2f} M out {n_out/1e6:6.2f} M "
               f"exact {int(units['exact_path'].sum())}  kernels {t:8.3f} ms = {n_s/1e3/t:8.1f} M slices/s, "
               f"{n_r/1e3/t:8.1f} M rows/s, {alg/1e6/t:7.1f} GB/s algorithmic = {100*alg/1e6/t/PEAK:4.1f}% of {PEAK}")
+    # row f1: frequencies + the interval x bin matrix over a released window (256 stack ids)
+    Ub, NSb, Kb = min(U, 192), max(1000, NS // 10), max(500, K // 10)
+    pb = [gen_unit(r, NSb, Kb, align=ALIGN) for _ in range(4)]
+    for s_, _ in pb:
+        s_["stack_id"] %= 256
+    bs = np.concatenate([pb[u % 4][0] for u in range(Ub)])
+    br = np.concatenate([pb[u % 4][1] for u in range(Ub)])
+    bsb = np.concatenate([[0], np.cumsum([len(pb[u % 4][0]) for u in range(Ub)])]).astype(np.uint64)
+    brb = np.concatenate([[0], np.cumsum([len(pb[u % 4][1]) for u in range(Ub)])]).astype(np.uint64)
+    units = g.release(bs, bsb, br, brb, 2**63, 3, np.zeros(Ub, np.uint64))
+    ms = []
+    for it in range(4):
+        res = g.bin(2, 1000, max_matrix_bytes=16 << 30, fetch=False)
+        ms.append(g.last_ms)
+    t = float(np.mean(ms[1:]))
+    n_out = int(units["n_slices"].sum())
+    print(f"bin (f1): units {Ub} intervals {len(br)/1e6:.2f} M slices {n_out/1e6:.2f} M stack ids {len(res['freqs'])} "
+          f"matrix {res['num_rows']} x {res['num_bins']} ({res['num_rows']*res['num_bins']*8/1e9:.2f} GB)  kernels {t:.3f} ms "
+          f"= {n_out/1e3/t:.0f} M slices/s (matrix memset not included)")
+    from oracle import pyoracle as po_
+    t0 = time.time()
+    uc = [g.get(u) for u in range(2)]
+    for kind in ("reference", "port"):
+        if not po_.slices_available(kind):
+            continue
+        t0 = time.time()
+        po_.bin_durations(kind, [uc[0][0], uc[1][0]], [uc[0][1], uc[1][1]], 2, 1000)
+        dt = time.time() - t0
+        print(f"cpu {kind:9s} bin, 2 units, 1 thread: {dt*1e3:.1f} ms = {(len(uc[0][1]) + len(uc[1][1]))/1e6/dt:.2f} M slices/s"
+              f"{' (real MonData + TagStackIdBinner, building the MonData included)' if kind == 'reference' else ''}")
     # end to end from host memory (pinned), counts + slices of every unit back
     pin_s = torch.from_numpy(slices.view(np.uint8)).pin_memory().numpy().view(gs.SLICE_DTYPE)
     pin_r = torch.from_numpy(rows.view(np.int64)).pin_memory().numpy().view(np.uint64).reshape(rows.shape)
