@@ -30,14 +30,18 @@
 //   k_islice_rows      (unit, tile of NT rows): stages the tile's slice window {t, e, G} in
 //                      shared memory (one coalesced pass; windows beyond WMAX slices are
 //                      searched in global memory), resolves every row: first slice, count,
-//                      new mark, throws; tile totals
+//                      new mark, throws; tile totals;
 //   k_islice_rscan     per unit: exclusive scan of the tile totals, the unit's summary; units
 //                      that broke a precondition anywhere are walked here by one thread exactly
 //                      as the reference does (exact_walk), so results are the reference's on
 //                      ANY input
-//   k_islice_emit      (unit, tile of NT rows): output offsets, copies and trims the slices
-//                      (one slice per thread and step, the owning row found by binary search
-//                      in shared memory)
+//                      and copies + trims the tile's slices into the unit's output region (one
+//                      slice per thread and step, the owning row found by binary search over
+//                      the tile's offsets in shared memory).  A tile writes from p + k of its
+//                      first row on: dense inside, at most one unused slot per row between
+//                      tiles, so no scan across tiles is needed before the copy
+//   k_islice_emit      the same copy for units that took the serial walk
+//   k_islice_pack      packs a unit's slices densely when the host asks for them
 // Scratch: G (8 B per slice), per-tile sums, the per-row plan (first, count, offset).
 #include <cuda_runtime.h>
 #include <errno.h>
@@ -54,11 +58,22 @@
 
 namespace {
 
-constexpr int NT = 512;  // threads per CTA = rows per row tile
+#ifndef HBTGPU_ISLICE_NT
+#define HBTGPU_ISLICE_NT 128
+#endif
+constexpr int NT = HBTGPU_ISLICE_NT;  // threads per CTA = rows per row tile
 constexpr int NW = NT / 32;
 constexpr int VT_SHIFT = 12;
 constexpr int VT = 1 << VT_SHIFT;  // slices per validation tile
-constexpr int WMAX = 2048;         // slices of a row tile's window staged in shared memory
+constexpr int WMAX = 4 * NT;       // slices of a row tile's window staged in shared memory
+#ifndef HBTGPU_EMIT_ILP
+#define HBTGPU_EMIT_ILP 1
+#endif
+#ifndef HBTGPU_ROWS_MIN_CTAS
+#define HBTGPU_ROWS_MIN_CTAS 12
+#endif
+constexpr int EMIT_ILP = HBTGPU_EMIT_ILP;  // output slices a thread has in flight in the copy loop
+constexpr int ROWS_MIN_CTAS = HBTGPU_ROWS_MIN_CTAS;
 constexpr int LOOKBACK = 8;        // longest chain of rows that start exactly on a slice end
 constexpr uint8_t TT_ANALYSIS = 1;  // Slice::TransitionType::Analysis, Slicer.h:36
 constexpr uint64_t NONE = ~0ull;
@@ -68,7 +83,8 @@ enum : uint32_t { UF_BAD_SLICES = 1, UF_BAD_ROWS = 2, UF_CHAIN = 4, UF_MARK = 8 
 struct Unit {
   uint64_t s0, ns;  // first slice, number of slices
   uint64_t r0, K;   // first row, number of rows
-  uint64_t out0;    // first output slice (dense, set once the counts are known)
+  uint64_t out0;    // the unit's output region
+  uint64_t out_cap;
   uint64_t mark;
   uint32_t vt0, rt0;  // first validation tile, first row tile
 };
@@ -183,17 +199,40 @@ __device__ __forceinline__ uint64_t block_incl_sum_u64(uint64_t v, uint64_t* sh,
   return v + (w ? sh[w - 1] : 0);
 }
 
-// One slice of an interval's answer: slice j, the i-th of cnt, trimmed as IntervalSlicer.cpp:
-// 146-173 trims front() and back().
-__device__ __forceinline__ void emit_one(const hbtgpu_slice* S, uint64_t j, uint32_t i, uint32_t cnt,
-                                         uint64_t T, uint64_t Tend, bool trim, hbtgpu_slice* dst) {
-  const uint4* src = reinterpret_cast<const uint4*>(S + j);
+// exclusive prefix sum of 32-bit values; *total = sum over the block (sh: NW words)
+__device__ __forceinline__ uint32_t block_excl_sum_u32(uint32_t v, uint32_t* sh, uint32_t* total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t s = v;
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, s, d);
+    if (lane >= d) s += o;
+  }
+  __syncthreads();
+  if (lane == 31) sh[w] = s;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t t = lane < NW ? sh[lane] : 0;
+    for (int d = 1; d < NW; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, t, d);
+      if (lane >= d) t += o;
+    }
+    if (lane < NW) sh[lane] = t;
+  }
+  __syncthreads();
+  *total = sh[NW - 1];
+  return s - v + (w ? sh[w - 1] : 0);
+}
+
+// One slice of an interval's answer: the i-th of cnt, trimmed as IntervalSlicer.cpp:146-173 trims
+// front() and back().
+__device__ __forceinline__ void trim_and_store(const uint4 (&q)[2], uint32_t i, uint32_t cnt, uint64_t T, uint64_t Tend,
+                                               bool trim, hbtgpu_slice* dst) {
   union {
     uint4 q[2];
     hbtgpu_slice s;
   } u;
-  u.q[0] = src[0];
-  u.q[1] = src[1];
+  u.q[0] = q[0];
+  u.q[1] = q[1];
   if (trim) {
     const uint64_t end = u.s.tstamp + u.s.duration;
     if (i == 0 && u.s.tstamp < T) {
@@ -209,6 +248,12 @@ __device__ __forceinline__ void emit_one(const hbtgpu_slice* S, uint64_t j, uint
   uint4* d = reinterpret_cast<uint4*>(dst);
   d[0] = u.q[0];
   d[1] = u.q[1];
+}
+__device__ __forceinline__ void emit_one(const hbtgpu_slice* S, uint64_t j, uint32_t i, uint32_t cnt,
+                                         uint64_t T, uint64_t Tend, bool trim, hbtgpu_slice* dst) {
+  const uint4* src = reinterpret_cast<const uint4*>(S + j);
+  const uint4 q[2] = {src[0], src[1]};
+  trim_and_store(q, i, cnt, T, Tend, trim, dst);
 }
 
 // The reference's walk, row by row.  Fills the plan (first slice, count, output offset per row); nothing is copied.
@@ -466,17 +511,18 @@ k_islice_bounds(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restr
   tile_ql[tile] = first_start_ge(g, 0, ns, rl.T + rl.D);
 }
 
-__global__ void __launch_bounds__(NT, 3)
+__global__ void __launch_bounds__(NT, ROWS_MIN_CTAS)
 k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
               const Unit* __restrict__ units, uint32_t n_units, UState* __restrict__ ustate,
               const uint64_t* __restrict__ Gl_all, const uint64_t* __restrict__ vt_base,
               const uint32_t* __restrict__ tile_lo, const uint32_t* __restrict__ tile_ql,
-              uint32_t* __restrict__ icnt_all, uint32_t* __restrict__ ifirst_all, uint32_t* __restrict__ rt_tot,
-              ulonglong2* __restrict__ td_all, uint64_t stop_ts, uint32_t flags) {
+              uint32_t* __restrict__ ioff_all, uint32_t* __restrict__ icnt_all, uint32_t* __restrict__ ifirst_all,
+              uint32_t* __restrict__ rt_tot, hbtgpu_slice* __restrict__ out_all, uint64_t stop_ts, uint32_t flags) {
   extern __shared__ __align__(16) uint64_t sh_win[];  // wt[WMAX], we[WMAX], wG[WMAX]
   __shared__ uint64_t sh_red[32];
   __shared__ uint64_t sh_T[NT], sh_D[NT];
-  __shared__ uint32_t sh_tot, sh_stop, sh_err, sh_maxc, sh_flags;
+  __shared__ uint32_t sh_stop, sh_err, sh_maxc, sh_flags, sh_firstact;
+  __shared__ uint32_t sh_excl[NT + 1];
   __shared__ uint32_t sh_lb[NT], sh_q[NT], sh_x[NT];
   __shared__ uint8_t sh_hb[NT];
 
@@ -509,9 +555,8 @@ k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
   }
   sh_T[tid] = T;
   sh_D[tid] = D;
-  if (td_all && live) td_all[U.r0 + k] = make_ulonglong2(T, Tend);  // {start, end} packed for the emit pass
   if (tid == 0) {
-    sh_tot = 0;
+    sh_firstact = NT;
     sh_stop = 0xffffffffu;
     sh_err = 0xffffffffu;
     sh_maxc = 0;
@@ -598,28 +643,77 @@ k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
   }
   const bool counted = act && !e.null_res && !e.thrown;
   const uint32_t cnt = counted ? e.r - e.p : 0u;
-  if (live) {
-    icnt_all[U.r0 + k] = cnt;
-    ifirst_all[U.r0 + k] = counted ? e.p : 0u;
-  }
   // tile sums: warp reductions, then one shared atomic per warp
   {
-    const uint32_t s = __reduce_add_sync(0xffffffffu, cnt);
     const uint32_t m1 = __reduce_min_sync(0xffffffffu, cut ? static_cast<uint32_t>(tid) : 0xffffffffu);
     const uint32_t m2 = __reduce_min_sync(0xffffffffu, (zero_len || (act && e.thrown)) ? static_cast<uint32_t>(tid) : 0xffffffffu);
     const uint32_t mx = __reduce_max_sync(0xffffffffu, counted ? e.c : 0u);
     const uint32_t fl = __reduce_or_sync(0xffffffffu, uflags);
+    const uint32_t fa = __reduce_min_sync(0xffffffffu, act ? static_cast<uint32_t>(tid) : 0xffffffffu);
     if ((tid & 31) == 0) {
-      if (s) atomicAdd(&sh_tot, s);
       if (m1 != 0xffffffffu) atomicMin(&sh_stop, m1);
       if (m2 != 0xffffffffu) atomicMin(&sh_err, m2);
       if (mx) atomicMax(&sh_maxc, mx);
       if (fl) atomicOr(&sh_flags, fl);
+      if (fa != 0xffffffffu) atomicMin(&sh_firstact, fa);
     }
+  }
+  // The tile's place in the unit's output region.  Rows take slices [p_k, r_k) and r_k <= p_{k+1} + 1,
+  // so a tile that starts writing at p + k (p, k of its first row) ends before the next tile's start:
+  // dense inside the tile, at most one unused slot per row between tiles, no scan across tiles.
+  uint32_t tile_total;
+  const uint32_t excl = block_excl_sum_u32(cnt, reinterpret_cast<uint32_t*>(sh_red), &tile_total);
+  sh_excl[tid] = excl;
+  if (tid == 0) sh_excl[NT] = tile_total;
+  sh_lb[tid] = e.p;  // (every chain walk is done: block_excl_sum_u32 has barriers)
+  __syncthreads();
+  const uint32_t fa = sh_firstact;
+  const uint64_t base = fa < NT ? static_cast<uint64_t>(sh_lb[fa]) + (k0 + fa) : 0;
+  if (live) {
+    ioff_all[U.r0 + k] = static_cast<uint32_t>(base + excl);
+    icnt_all[U.r0 + k] = cnt;
+    ifirst_all[U.r0 + k] = counted ? e.p : 0u;
+  }
+  if (base + tile_total <= U.out_cap) {
+    // one slice per thread and step, EMIT_ILP steps in flight: the owning row by binary search over
+    // the tile's offsets, then a 32-byte copy with the first / last slice of a row trimmed
+    hbtgpu_slice* out = out_all + U.out0 + base;
+    for (uint32_t o0 = tid; o0 < tile_total; o0 += EMIT_ILP * NT) {
+      uint32_t row[EMIT_ILP];
+#pragma unroll
+      for (int j = 0; j < EMIT_ILP; ++j) {
+        const uint32_t o = min(o0 + j * NT, tile_total - 1);
+        uint32_t lo = 0, hi = NT;  // last row with sh_excl[row] <= o
+        while (hi - lo > 1) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if (sh_excl[mid] <= o) lo = mid;
+          else hi = mid;
+        }
+        row[j] = lo;
+      }
+      uint4 q[EMIT_ILP][2];
+#pragma unroll
+      for (int j = 0; j < EMIT_ILP; ++j) {
+        const uint32_t o = min(o0 + j * NT, tile_total - 1);
+        const uint4* src = reinterpret_cast<const uint4*>(S + sh_lb[row[j]] + (o - sh_excl[row[j]]));
+        q[j][0] = src[0];
+        q[j][1] = src[1];
+      }
+#pragma unroll
+      for (int j = 0; j < EMIT_ILP; ++j) {
+        const uint32_t o = o0 + j * NT;
+        if (o < tile_total) {
+          const uint32_t r_ = row[j], i = o - sh_excl[r_], c = sh_excl[r_ + 1] - sh_excl[r_];
+          trim_and_store(q[j], i, c, sh_T[r_], sh_T[r_] + sh_D[r_], trim, out + o);
+        }
+      }
+    }
+  } else if (tid == 0) {
+    atomicOr(&sh_flags, UF_BAD_ROWS);  // only rows that do not move forward in time can get here
   }
   __syncthreads();
   if (tid == 0) {
-    rt_tot[blockIdx.x] = sh_tot;
+    rt_tot[blockIdx.x] = tile_total;
     if (sh_stop != 0xffffffffu) atomicMin(&st->n_stop, static_cast<unsigned long long>(k0 + sh_stop));
     if (sh_err != 0xffffffffu) atomicMin(&st->err_k, static_cast<unsigned long long>(k0 + sh_err));
     if (sh_maxc) atomicMax(&st->max_c, static_cast<unsigned long long>(sh_maxc));
@@ -679,13 +773,13 @@ k_islice_rscan(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restri
   }
 }
 
-// ---- (unit, tile of NT rows): output offsets, copy + trim --------------------------------------
+// ---- (unit, tile of NT rows) of units that took the serial walk: output offsets, copy + trim ---
 __global__ void __launch_bounds__(NT)
 k_islice_emit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
               const Unit* __restrict__ units, uint32_t n_units, const hbtgpu_islice_unit* __restrict__ results,
               const uint64_t* __restrict__ rt_base, uint32_t* __restrict__ ioff_all,
               const uint32_t* __restrict__ icnt_all, const uint32_t* __restrict__ ifirst_all,
-              const ulonglong2* __restrict__ td_all, hbtgpu_slice* __restrict__ out_all, uint32_t flags) {
+              hbtgpu_slice* __restrict__ out_all, uint32_t flags) {
   __shared__ uint64_t sh_red[32];
   __shared__ uint64_t sh_T[NT], sh_Tend[NT];
   __shared__ uint32_t sh_excl[NT + 1], sh_p[NT];
@@ -694,6 +788,7 @@ k_islice_emit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
   const Unit U = units[u];
   const uint64_t n = results[u].n_intervals;
   const uint64_t k0 = static_cast<uint64_t>(blockIdx.x - U.rt0) * NT;
+  if (!results[u].exact_path) return;  // the rows pass has written the others already
   if (k0 >= n || results[u].status == -EOVERFLOW) return;
   const hbtgpu_slice* S = slices + U.s0;
   const uint64_t* rows = rows_all + U.r0 * stride;
@@ -711,15 +806,9 @@ k_islice_emit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
     ioff_all[U.r0 + k] = static_cast<uint32_t>(base + excl);
     sh_p[tid] = ifirst_all[U.r0 + k];
     if (cnt) {
-      if (td_all && !results[u].exact_path) {  // (units that took the serial walk may have skipped the rows pass)
-        const ulonglong2 td = td_all[U.r0 + k];
-        sh_T[tid] = td.x;
-        sh_Tend[tid] = td.y;
-      } else {
-        const Row rw = ld_row(rows, stride, k);
-        sh_T[tid] = rw.T;
-        sh_Tend[tid] = rw.T + rw.D;
-      }
+      const Row rw = ld_row(rows, stride, k);
+      sh_T[tid] = rw.T;
+      sh_Tend[tid] = rw.T + rw.D;
     }
   }
   __syncthreads();
@@ -734,6 +823,20 @@ k_islice_emit(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restric
     const uint32_t i = o - sh_excl[lo];
     emit_one(S, sh_p[lo] + i, i, sh_excl[lo + 1] - sh_excl[lo], sh_T[lo], sh_Tend[lo], trim, out + o);
   }
+}
+
+
+// a unit's slices, tile after tile, packed densely (for the host getter)
+__global__ void __launch_bounds__(256)
+k_islice_pack(const Unit U, const uint32_t* __restrict__ ioff_all, const uint32_t* __restrict__ rt_tot,
+              const uint64_t* __restrict__ rt_base, const hbtgpu_slice* __restrict__ out_all,
+              hbtgpu_slice* __restrict__ dst) {
+  const uint32_t tile = U.rt0 + blockIdx.x;
+  const uint32_t n = rt_tot[tile];
+  if (n == 0) return;
+  const uint4* src = reinterpret_cast<const uint4*>(out_all + U.out0 + ioff_all[U.r0 + static_cast<uint64_t>(blockIdx.x) * NT]);
+  uint4* d = reinterpret_cast<uint4*>(dst + rt_base[tile]);
+  for (uint32_t i = threadIdx.x; i < 2 * n; i += blockDim.x) d[i] = src[i];
 }
 
 
@@ -915,7 +1018,7 @@ struct hbtgpu_islice_ctx {
   uint64_t* d_rt_base = nullptr;     size_t cap_rt_base = 0;
   uint32_t* d_tile_lo = nullptr;     size_t cap_tile_lo = 0;
   uint32_t* d_tile_ql = nullptr;     size_t cap_tile_ql = 0;
-  ulonglong2* d_td = nullptr;        size_t cap_td = 0;
+  hbtgpu_slice* d_tmp = nullptr;     size_t cap_tmp = 0;
   uint32_t* d_ioff = nullptr;        size_t cap_ioff = 0;
   uint32_t* d_icnt = nullptr;        size_t cap_icnt = 0;
   uint32_t* d_ifirst = nullptr;      size_t cap_ifirst = 0;
@@ -1005,7 +1108,7 @@ void hbtgpu_islice_destroy(hbtgpu_islice_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaFree(c->d_slices); cudaFree(c->d_rows); cudaFree(c->d_G); cudaFree(c->d_vt_tot); cudaFree(c->d_vt_base);
-  cudaFree(c->d_rt_tot); cudaFree(c->d_rt_base); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_ql); cudaFree(c->d_td); cudaFree(c->d_ioff); cudaFree(c->d_icnt); cudaFree(c->d_ifirst);
+  cudaFree(c->d_rt_tot); cudaFree(c->d_rt_base); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_ql); cudaFree(c->d_tmp); cudaFree(c->d_ioff); cudaFree(c->d_icnt); cudaFree(c->d_ifirst);
   cudaFree(c->d_out); cudaFree(c->d_units); cudaFree(c->d_ustate); cudaFree(c->d_res); cudaFree(c->d_base);
   cudaFree(c->d_bin_tab); cudaFree(c->d_bin_bid); cudaFree(c->d_has); cudaFree(c->d_bt_tot); cudaFree(c->d_bt_base);
   cudaFree(c->d_bin_list); cudaFree(c->d_bin_up); cudaFree(c->d_bin_M); cudaFree(c->d_bin_ctr); cudaFree(c->d_sel);
@@ -1032,7 +1135,7 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
   const uint64_t s_base = slice_begin[0], r_base = row_begin[0];
   const uint64_t total_s = slice_begin[n_units] - s_base, total_r = row_begin[n_units] - r_base;
   c->units.assign(n_units, Unit{});
-  uint64_t n_vt = 0, n_rt = 0;
+  uint64_t n_vt = 0, n_rt = 0, out_run = 0;
   for (uint32_t u = 0; u < n_units; ++u) {
     if (slice_begin[u + 1] < slice_begin[u] || row_begin[u + 1] < row_begin[u])
       return ifail(c, -EINVAL, "begin arrays must not decrease (unit %u)", u);
@@ -1042,7 +1145,9 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
     U.r0 = row_begin[u] - r_base;
     U.K = row_begin[u + 1] - row_begin[u];
     if (U.ns >= 0xfffffff0ull || U.K >= 0xfffffff0ull) return ifail(c, -EINVAL, "unit %u: 2^32 or more slices or rows", u);
-    U.out0 = 0;
+    U.out0 = out_run;
+    U.out_cap = U.ns + U.K + NT;  // the rows pass leaves at most one unused slot per row
+    out_run += U.out_cap;
     U.mark = marks[u];
     U.vt0 = static_cast<uint32_t>(n_vt);
     U.rt0 = static_cast<uint32_t>(n_rt);
@@ -1092,12 +1197,7 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
   if (int rc = grow(c, &c->d_units, &c->cap_units, n_units)) return rc;
   if (int rc = grow(c, &c->d_ustate, &c->cap_ustate, n_units)) return rc;
   if (int rc = grow(c, &c->d_res, &c->cap_res, n_units)) return rc;
-  // rows wider than {tstamp, duration}: the rows pass packs {start, end} for the emit pass
-  ulonglong2* d_td = nullptr;
-  if (stride > 2 && !(flags & HBTGPU_ISLICE_FORCE_EXACT)) {
-    if (int rc = grow(c, &c->d_td, &c->cap_td, total_r + 1)) return rc;
-    d_td = c->d_td;
-  }
+  if (int rc = grow(c, &c->d_out, &c->cap_out, out_run + 1)) return rc;
   c->ustate.assign(n_units, UState{0u, 0u, NONE, NONE, 0ull});
   IK(cudaMemcpyAsync(c->d_units, c->units.data(), n_units * sizeof(Unit), cudaMemcpyHostToDevice, c->stream));
   IK(cudaMemcpyAsync(c->d_ustate, c->ustate.data(), n_units * sizeof(UState), cudaMemcpyHostToDevice, c->stream));
@@ -1113,7 +1213,7 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
         d_slices, d_rows, stride, c->d_units, n_units, static_cast<uint32_t>(n_rt), c->d_tile_lo, c->d_tile_ql);
     k_islice_rows<<<static_cast<unsigned>(n_rt), NT, ROWS_SMEM, c->stream>>>(
         d_slices, d_rows, stride, c->d_units, n_units, c->d_ustate, c->d_G, c->d_vt_base, c->d_tile_lo, c->d_tile_ql,
-        c->d_icnt, c->d_ifirst, c->d_rt_tot, d_td, stop_ts, flags);
+        c->d_ioff, c->d_icnt, c->d_ifirst, c->d_rt_tot, c->d_out, stop_ts, flags);
   }
   k_islice_rscan<<<n_units, NT, 0, c->stream>>>(d_slices, d_rows, stride, c->d_units, c->d_ustate, c->d_rt_tot,
                                                 c->d_rt_base, c->d_ioff, c->d_icnt, c->d_ifirst, c->d_res, stop_ts,
@@ -1125,19 +1225,41 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
                      c->stream));
   IK(cudaStreamSynchronize(c->stream));
 
-  // now that the counts are known: dense output, unit after unit
-  uint64_t out_run = 0;
+  // units that took the serial walk: their slices are copied now, behind the regular regions
+  // when they do not fit their own
+  bool any_exact = false, moved = false;
   for (uint32_t u = 0; u < n_units; ++u) {
-    c->units[u].out0 = out_run;
-    if (c->res[u].status != -EOVERFLOW) out_run += c->res[u].n_slices;
+    if (!c->res[u].exact_path || c->res[u].status == -EOVERFLOW || c->res[u].n_slices == 0) continue;
+    any_exact = true;
+    if (c->res[u].n_slices > c->units[u].out_cap) {
+      c->units[u].out0 = out_run;
+      c->units[u].out_cap = c->res[u].n_slices;
+      out_run += c->res[u].n_slices;
+      moved = true;
+    }
   }
-  if (int rc = grow(c, &c->d_out, &c->cap_out, out_run + 1)) return rc;
-  IK(cudaMemcpyAsync(c->d_units, c->units.data(), n_units * sizeof(Unit), cudaMemcpyHostToDevice, c->stream));
+  if (moved) {
+    if (out_run + 1 > c->cap_out) {  // grow, keeping what the rows pass wrote
+      hbtgpu_slice* q = nullptr;
+      const size_t ncap = out_run + 1;
+      IK(cudaMalloc(&q, ncap * sizeof(hbtgpu_slice)));
+      cudaError_t e = cudaMemcpyAsync(q, c->d_out, c->cap_out * sizeof(hbtgpu_slice), cudaMemcpyDeviceToDevice, c->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+      if (e != cudaSuccess) {
+        cudaFree(q);
+        return ifail(c, -EIO, "device copy failed: %s", cudaGetErrorString(e));
+      }
+      cudaFree(c->d_out);
+      c->d_out = q;
+      c->cap_out = ncap;
+    }
+    IK(cudaMemcpyAsync(c->d_units, c->units.data(), n_units * sizeof(Unit), cudaMemcpyHostToDevice, c->stream));
+  }
   IK(cudaEventRecord(c->ev2, c->stream));
-  if (n_rt && out_run)
+  if (n_rt && any_exact)
     k_islice_emit<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(d_slices, d_rows, stride, c->d_units, n_units,
                                                                      c->d_res, c->d_rt_base, c->d_ioff, c->d_icnt,
-                                                                     c->d_ifirst, d_td, c->d_out, flags);
+                                                                     c->d_ifirst, c->d_out, flags);
   IK(cudaGetLastError());
   IK(cudaEventRecord(c->ev3, c->stream));
   IK(cudaStreamSynchronize(c->stream));
@@ -1181,9 +1303,17 @@ int hbtgpu_islice_get(hbtgpu_islice_ctx* c, uint32_t unit, uint32_t* counts, uin
   if (slices) {
     if (slices_cap < R.n_slices) return ifail(c, -ENOSPC, "%llu slices, room for %llu",
                                               (unsigned long long)R.n_slices, (unsigned long long)slices_cap);
-    if (R.n_slices)
-      IK(cudaMemcpyAsync(slices, c->d_out + U.out0, R.n_slices * sizeof(hbtgpu_slice), cudaMemcpyDeviceToHost,
-                         c->stream));
+    if (R.n_slices) {
+      const hbtgpu_slice* src = c->d_out + U.out0;  // the serial walk writes densely
+      if (!R.exact_path) {                          // the rows pass leaves unused slots between tiles
+        if (int rc = grow(c, &c->d_tmp, &c->cap_tmp, R.n_slices)) return rc;
+        const unsigned n_tiles = static_cast<unsigned>((U.K + NT - 1) / NT);
+        k_islice_pack<<<n_tiles, 256, 0, c->stream>>>(U, c->d_ioff, c->d_rt_tot, c->d_rt_base, c->d_out, c->d_tmp);
+        IK(cudaGetLastError());
+        src = c->d_tmp;
+      }
+      IK(cudaMemcpyAsync(slices, src, R.n_slices * sizeof(hbtgpu_slice), cudaMemcpyDeviceToHost, c->stream));
+    }
   }
   IK(cudaStreamSynchronize(c->stream));
   return 0;

@@ -593,7 +593,9 @@ int hbtgpu_islice_get_units(hbtgpu_islice_ctx* ctx, hbtgpu_islice_unit* units, u
 int hbtgpu_islice_get(hbtgpu_islice_ctx* ctx, uint32_t unit, uint32_t* counts, uint64_t counts_cap,
                       hbtgpu_slice* slices, uint64_t slices_cap);
 /* Device view for consumers on the GPU: unit u's intervals are interval_offset/interval_count
- * [row_begin[u] + k] (offset relative to unit_base[u]), its slices out[unit_base[u] + ...]. */
+ * [row_begin[u] + k] (offset relative to unit_base[u]), interval k's slices
+ * slices[unit_base[u] + interval_offset .. + interval_count).  Consecutive intervals need not be
+ * adjacent in memory (unused slots may lie between them); hbtgpu_islice_get packs. */
 typedef struct {
   const hbtgpu_slice* slices;
   const uint64_t* unit_base;        /* [n_units] */
