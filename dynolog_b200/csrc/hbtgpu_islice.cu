@@ -28,7 +28,7 @@
 //   k_islice_vscan     per unit: exclusive scan of the tiles' gap sums (G = local + base)
 //   k_islice_bounds    one thread per row tile: the slice window the tile's rows can touch
 //   k_islice_rows      (unit, tile of NT rows): stages the tile's slice window {t, e, G} in
-//                      shared memory (one coalesced pass; windows beyond WMAX slices are
+//                      shared memory (one coalesced pass; windows beyond WMULT * NT slices are
 //                      searched in global memory), resolves every row: first slice, count,
 //                      new mark, throws; tile totals;
 //   k_islice_rscan     per unit: exclusive scan of the tile totals, the unit's summary; units
@@ -65,15 +65,12 @@ constexpr int NT = HBTGPU_ISLICE_NT;  // threads per CTA = rows per row tile
 constexpr int NW = NT / 32;
 constexpr int VT_SHIFT = 12;
 constexpr int VT = 1 << VT_SHIFT;  // slices per validation tile
-constexpr int WMAX = 4 * NT;       // slices of a row tile's window staged in shared memory
+// slices of a row tile's window staged in shared memory: WMULT * NT, WMULT in {4, 8, 16} picked
+// per call from the slices-per-row density (a bigger window costs resident CTAs)
 #ifndef HBTGPU_EMIT_ILP
 #define HBTGPU_EMIT_ILP 1
 #endif
-#ifndef HBTGPU_ROWS_MIN_CTAS
-#define HBTGPU_ROWS_MIN_CTAS 12
-#endif
 constexpr int EMIT_ILP = HBTGPU_EMIT_ILP;  // output slices a thread has in flight in the copy loop
-constexpr int ROWS_MIN_CTAS = HBTGPU_ROWS_MIN_CTAS;
 constexpr int LOOKBACK = 8;        // longest chain of rows that start exactly on a slice end
 constexpr uint8_t TT_ANALYSIS = 1;  // Slice::TransitionType::Analysis, Slicer.h:36
 constexpr uint64_t NONE = ~0ull;
@@ -511,13 +508,15 @@ k_islice_bounds(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restr
   tile_ql[tile] = first_start_ge(g, 0, ns, rl.T + rl.D);
 }
 
-__global__ void __launch_bounds__(NT, ROWS_MIN_CTAS)
+template <int WMULT, int MIN_CTAS>
+__global__ void __launch_bounds__(NT, MIN_CTAS)
 k_islice_rows(const hbtgpu_slice* __restrict__ slices, const uint64_t* __restrict__ rows_all, uint64_t stride,
               const Unit* __restrict__ units, uint32_t n_units, UState* __restrict__ ustate,
               const uint64_t* __restrict__ Gl_all, const uint64_t* __restrict__ vt_base,
               const uint32_t* __restrict__ tile_lo, const uint32_t* __restrict__ tile_ql,
               uint32_t* __restrict__ ioff_all, uint32_t* __restrict__ icnt_all, uint32_t* __restrict__ ifirst_all,
               uint32_t* __restrict__ rt_tot, hbtgpu_slice* __restrict__ out_all, uint64_t stop_ts, uint32_t flags) {
+  constexpr int WMAX = WMULT * NT;
   extern __shared__ __align__(16) uint64_t sh_win[];  // wt[WMAX], we[WMAX], wG[WMAX]
   __shared__ uint64_t sh_red[32];
   __shared__ uint64_t sh_T[NT], sh_D[NT];
@@ -1081,7 +1080,7 @@ int grow(hbtgpu_islice_ctx* c, T** p, size_t* cap, size_t need) {
   return 0;
 }
 
-constexpr size_t ROWS_SMEM = 3 * WMAX * sizeof(uint64_t);
+constexpr size_t rows_smem(int wmult) { return 3 * static_cast<size_t>(wmult) * NT * sizeof(uint64_t); }
 
 }  // namespace
 
@@ -1096,8 +1095,12 @@ hbtgpu_islice_ctx* hbtgpu_islice_create(int device) {
   if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
       cudaEventCreate(&c->ev2) != cudaSuccess || cudaEventCreate(&c->ev3) != cudaSuccess ||
-      cudaFuncSetAttribute(k_islice_rows, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           static_cast<int>(ROWS_SMEM)) != cudaSuccess) {
+      cudaFuncSetAttribute(k_islice_rows<4, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(rows_smem(4))) != cudaSuccess ||
+      cudaFuncSetAttribute(k_islice_rows<8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(rows_smem(8))) != cudaSuccess ||
+      cudaFuncSetAttribute(k_islice_rows<16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(rows_smem(16))) != cudaSuccess) {
     hbtgpu_islice_destroy(c);
     return nullptr;
   }
@@ -1211,9 +1214,17 @@ int hbtgpu_islice_release(hbtgpu_islice_ctx* c, const hbtgpu_slice* slices, cons
   if (n_rt) {
     k_islice_bounds<<<static_cast<unsigned>((n_rt + 127) / 128), 128, 0, c->stream>>>(
         d_slices, d_rows, stride, c->d_units, n_units, static_cast<uint32_t>(n_rt), c->d_tile_lo, c->d_tile_ql);
-    k_islice_rows<<<static_cast<unsigned>(n_rt), NT, ROWS_SMEM, c->stream>>>(
-        d_slices, d_rows, stride, c->d_units, n_units, c->d_ustate, c->d_G, c->d_vt_base, c->d_tile_lo, c->d_tile_ql,
-        c->d_ioff, c->d_icnt, c->d_ifirst, c->d_rt_tot, c->d_out, stop_ts, flags);
+    // window size by density: a tile of NT rows touches about NT * slices-per-row slices
+    const double density = static_cast<double>(total_s) / static_cast<double>(total_r ? total_r : 1);
+#define ROWS_ARGS d_slices, d_rows, stride, c->d_units, n_units, c->d_ustate, c->d_G, c->d_vt_base, c->d_tile_lo, \
+                  c->d_tile_ql, c->d_ioff, c->d_icnt, c->d_ifirst, c->d_rt_tot, c->d_out, stop_ts, flags
+    if (density < 3.0)
+      k_islice_rows<4, 12><<<static_cast<unsigned>(n_rt), NT, rows_smem(4), c->stream>>>(ROWS_ARGS);
+    else if (density < 6.5)
+      k_islice_rows<8, 8><<<static_cast<unsigned>(n_rt), NT, rows_smem(8), c->stream>>>(ROWS_ARGS);
+    else
+      k_islice_rows<16, 4><<<static_cast<unsigned>(n_rt), NT, rows_smem(16), c->stream>>>(ROWS_ARGS);
+#undef ROWS_ARGS
   }
   k_islice_rscan<<<n_units, NT, 0, c->stream>>>(d_slices, d_rows, stride, c->d_units, c->d_ustate, c->d_rt_tot,
                                                 c->d_rt_base, c->d_ioff, c->d_icnt, c->d_ifirst, c->d_res, stop_ts,
