@@ -1,0 +1,80 @@
+"""The stages in one line: thread-switch ring images -> tagstack events (GPU, f2),
+count-sample ring images -> count rows (GPU, the hot path), events -> slices (the reference's
+Slicer: the one stage without a GPU form yet, run here from oracle/_ref as a stand-in), count
+rows x slices -> per-interval slices (GPU, f3) -> frequencies + interval x bin matrix (GPU, f1).
+Checks that the formats connect (16-byte events, n+2-word rows, 32-byte slices pass from stage to
+stage untouched) and that the GPU stages agree with the CPU checkers on realistic data rather
+than on hand-made vectors."""
+import numpy as np
+import pytest
+
+import gpu_util
+from dynolog_b200 import hbtgpu_cs, hbtgpu_slices as gs, synth
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.skipif(not po.slices_available("reference"), reason="oracle/_ref/libhbtref_slices.so not built")
+def test_images_to_bins():
+    n_cpus = 6
+    # thread switches: ~1500 switch pairs per cpu, 20 us apart, a few LOST records (write errors)
+    cs_streams = synth.cs_capture(n_cpus, 96 * 1024, n_tids=64, life_ppm=20000, comm_ppm=0, lost_ppm=2000,
+                                  throttle_ppm=0, seed=3)
+    dec = hbtgpu_cs.decode(cs_streams, tid_level=0)
+    events = dec["events"]
+    assert all(len(e) > 1000 for e in events)
+    for cu, e in enumerate(events):
+        assert e.dtype.itemsize == 16 and (e["comp_unit_id"] == cu).all()
+    # the Combinator tree's order: by (tstamp, comp unit), each cpu's own order kept
+    merged = np.concatenate(events)
+    order = np.lexsort((merged["comp_unit_id"], merged["tstamp"]))
+    sl = po.slicer_run("reference", merged[order], n_cpus)
+    assert sl["rc"] == 0 and sl["stats"]["num_slices_completed"] > 1000 * n_cpus
+    slices = sl["slices"]
+    assert sl["stats"]["num_error_start"] > 0               # the LOST records made it through as resets
+
+    # count samples over the same stretch of time: 100 us apart, 4-event group
+    spec, streams = synth.capture(1, n_cpus, n_samples=280)
+    params = po.make_params(spec.n_events)
+    got, _ = gpu_util.gpu_decode(params, streams)
+    rows = [g["rows"] for g in got]
+    assert all(r.shape[1] == spec.n_events + 2 and len(r) > 250 for r in rows)
+    t_lo = min(int(s["tstamp"][0]) for s in slices)
+    t_hi = max(int(s["tstamp"][-1]) for s in slices)
+    assert int(rows[0][5, 0]) > t_lo and int(rows[0][5, 0]) < t_hi, "samples and switches must overlap in time"
+
+    # rows x slices on the GPU, TraceMonitor's flags
+    flags = po.TRIM | po.ABORT_ON_MISSING
+    stop_ts = int(rows[0][-10, 0])
+    isl = gs.IntervalSlicer(0)
+    try:
+        sb = np.concatenate([[0], np.cumsum([len(s) for s in slices])]).astype(np.uint64)
+        rb = np.concatenate([[0], np.cumsum([len(r) for r in rows])]).astype(np.uint64)
+        marks = np.zeros(n_cpus, np.uint64)
+        units = isl.release(np.concatenate(slices), sb, np.concatenate(rows), rb, stop_ts, flags, marks)
+        assert (units["status"] == 0).all() and (units["exact_path"] == 0).all()
+        uc, uo = [], []
+        for u in range(n_cpus):
+            exp = po.islice_release("port", slices[u], rows[u], stop_ts, flags, 0)
+            counts, out = isl.get(u)
+            assert units[u]["n_intervals"] == exp["n_intervals"] and marks[u] == exp["mark"]
+            assert np.array_equal(counts, exp["counts"])
+            for k in ("tstamp", "duration", "stack_id", "swin_type", "swout_type"):
+                assert np.array_equal(out[k], exp["slices"][k]), (u, k)
+            uc.append(counts)
+            uo.append(out)
+        covered = sum(int((c > 0).sum()) for c in uc)
+        assert covered > 100 * n_cpus, "most count intervals should be covered by slices"
+        # frequencies and the matrix
+        binned = isl.bin(2, 1000)
+        exp = po.bin_durations("port", uc, uo, 2, 1000)
+        for k in ("stack_id", "duration", "num_obs", "num_intervals", "bid"):
+            assert np.array_equal(binned["freqs"][k], exp["freqs"][k]), k
+        assert np.array_equal(binned["durations"], exp["durations"])
+        assert binned["num_bins"] > 5
+        # every covered interval's durations add up to its length (trim + abort: exact cover)
+        row_sums = binned["durations"].sum(axis=1)
+        assert row_sums[: int((uc[0] > 0).sum())].all()
+    finally:
+        isl.close()
