@@ -11,7 +11,9 @@
  *                driven the way TraceMonitor::releaseCountData_ drives them
  *                (hbt/src/mon/TraceMonitor.cpp:25-103).  boost::intrusive is absent from the
  *                image: oracle/stubs/boost/intrusive/list.hpp stands in for it.
- *   hbtoracle_*  oracle/libhbtoracle.so: plain-C restatement (hbt_slices_oracle.c)
+ *   hbtoracle_*  oracle/libhbtoracle.so: plain-C restatement (hbt_slices_oracle.c); its
+ *                slicer_run covers level-0 thread events only (-ENOTSUP for phase events
+ *                and other levels, which need the general stack dictionary)
  */
 #ifndef HBTSLICES_API_H
 #define HBTSLICES_API_H
