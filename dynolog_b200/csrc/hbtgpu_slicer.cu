@@ -1,0 +1,779 @@
+// hbtgpu_slicer.cu -- tagstack events -> slices on the GPU (Slicer side).
+//
+// Reference: tagstack::slice::Slicer<>::processNext (hbt/src/tagstack/Slicer.h:336-459) and what
+// it calls: one state machine over the time-ordered merge of all comp units' events
+// (Event::happenedBefore, tagstack/Event.h:217-223), a dictionary Stack -> TagStackState whose
+// ids follow the order of creation (:560-584), dormant lists per bottom tag (:308-311), resets.
+//
+// Scope of this form: the events the thread-switch decode emits -- everything at level 0
+// (ThreadCreation / ThreadDestruction / SwitchIn / SwitchOut* / WriteErrors*), every unit's
+// events in time order.  Then the dictionary is E[k] (the empty stack) and T[v][k] (the stack
+// {v}), k = known_num_levels, and:
+//   * a switch-out on unit g closes the slice of g's active state and activates E[1];
+//   * a switch-in of v closes it too and activates T[v][1] if g's previous event was a
+//     switch-out (known levels) and T[v][1] is dormant, else T[v][0]; v = 0 takes T[0][k];
+//   * WriteErrorsStart resets (active states, dormant flags); events between it and its End
+//     are dropped;
+//   * ids: one per createStackState_ call in merge order, parents first; a ThreadCreation of
+//     an existing stack still takes an id.
+// Anything else -- phase events, other levels, a unit whose events go back in time, a switch-in
+// on a unit whose active state is a thread (the reference resets there: a data-dependent reset),
+// a WriteErrorsEnd without its Start -- is refused with -ENOTSUP; nothing is computed on the CPU.
+//
+// Steps: (1) stable radix sort of the events by tstamp (units arrive one after the other, so
+// ties keep comp-unit order = the merge order); (2) scans in merge order: write-error depth ->
+// dropped events, reset epochs; (3) a max-scan in unit-major order gives every switch event its
+// predecessor on the same unit (valid within an epoch): slice bounds, `known`; (4) per thread
+// id v the list {creation, switch-in, the switch-out that parks it} sorted by (v, merge
+// position), walked by one thread per v: which state a switch-in takes, who creates what;
+// (5) creation counts -> exclusive sum -> stack ids; (6) slices, compacted where the duration
+// is 0; statistics by atomics.  cub's radix sort and scans are library code; the rest is here.
+#include <cuda_runtime.h>
+#include <errno.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include "hbtgpu.h"
+
+namespace {
+
+constexpr uint32_t EV_START = 0, EV_END = 1, EV_CREATE = 2, EV_DESTROY = 3, EV_IN = 4, EV_OUT_PREEMPT = 5,
+                   EV_OUT_YIELD = 6, EV_WE_START = 7, EV_WE_END = 8;
+constexpr uint8_t TT_PREEMPTED = 2, TT_YIELD = 3;  // Slice::TransitionType, Slicer.h:31-43
+constexpr uint32_t NA = 0xffffffffu;
+constexpr uint32_t NOIDX = 0xffffffffu;
+constexpr uint64_t NONE64 = ~0ull;
+
+enum : uint32_t {  // why a window is outside the parallel form
+  BAD_TYPE = 1, BAD_LEVEL = 2, BAD_ORDER = 4, BAD_UNIT = 8, BAD_TAG = 16, BAD_DOUBLE_IN = 32, BAD_WE_END = 64
+};
+// per-event creation flags (step 4)
+enum : uint8_t { CF_T1 = 1, CF_BURN = 2, CF_T0 = 4, CF_PICK_T1 = 8, CF_KNOWN = 16, CF_PREV = 32 };
+enum : uint32_t { K_CREATE = 0, K_IN = 1, K_PARK = 2 };
+
+// small device-wide numbers
+struct Globals {
+  unsigned int bad;
+  unsigned int e_first[2];  // merge position where E[k] is first needed
+  unsigned int a_first[2];  // ... T[0][k] (tid 0)
+  unsigned long long n_dropped, n_we_start, n_we_end, n_completed;
+  unsigned int max_tag;
+};
+
+struct MaxOp {
+  __device__ uint32_t operator()(uint32_t a, uint32_t b) const { return a > b ? a : b; }
+};
+
+__device__ __forceinline__ bool is_switch(uint32_t t) { return t >= EV_IN && t <= EV_OUT_YIELD; }
+
+// (1) sort keys, input checks
+__global__ void k_sl_prepare(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ unit_of,
+                             const uint64_t* __restrict__ ub, uint64_t* __restrict__ key, uint32_t* __restrict__ val,
+                             Globals* g) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const hbtgpu_cs_event e = ev[i];
+  key[i] = e.tstamp;
+  val[i] = i;
+  uint32_t bad = 0;
+  const uint32_t u = unit_of[i];
+  if (e.comp_unit_id != u) bad |= BAD_UNIT;
+  if (e.type > EV_WE_END || e.type == EV_START || e.type == EV_END) bad |= BAD_TYPE;
+  if (e.type >= EV_CREATE && e.type <= EV_OUT_YIELD && e.level != 0) bad |= BAD_LEVEL;
+  if ((e.type == EV_CREATE || e.type == EV_IN) && e.tag == NA) bad |= BAD_TAG;
+  if (i > ub[u] && ev[i - 1].tstamp > e.tstamp) bad |= BAD_ORDER;
+  if (bad) atomicOr(&g->bad, bad);
+  if ((e.type == EV_CREATE || e.type == EV_IN) && e.tag != NA) atomicMax(&g->max_tag, e.tag);
+}
+
+__global__ void k_sl_unit_of(const uint64_t* __restrict__ ub, uint32_t n_units, uint32_t* __restrict__ unit_of) {
+  const uint32_t u = blockIdx.x;
+  for (uint64_t i = ub[u] + threadIdx.x; i < ub[u + 1]; i += blockDim.x) unit_of[i] = u;
+}
+
+// (2) merge order: rank, write-error deltas
+__global__ void k_sl_gather(const hbtgpu_cs_event* __restrict__ ev, const uint32_t* __restrict__ order, uint32_t n,
+                            uint32_t* __restrict__ rank, int32_t* __restrict__ delta, uint32_t* __restrict__ start) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  const uint32_t i = order[p];
+  rank[i] = p;
+  const uint32_t t = ev[i].type;
+  delta[p] = t == EV_WE_START ? 1 : (t == EV_WE_END ? -1 : 0);
+  start[p] = t == EV_WE_START;
+}
+
+// (3a) effective events in unit-major order; input of the predecessor scan
+__global__ void k_sl_effective(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
+                               const int32_t* __restrict__ depth_incl, const int32_t* __restrict__ delta,
+                               uint8_t* __restrict__ eff, uint32_t* __restrict__ scan_in, Globals* g) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t t = ev[i].type, p = rank[i];
+  const int32_t before = depth_incl[p] - delta[p];  // num_active_write_errors_ as the event finds it
+  bool e = false;
+  if (t == EV_WE_END) {
+    if (before <= 0) atomicOr(&g->bad, BAD_WE_END);  // the reference's unsigned counter would wrap
+    atomicAdd(&g->n_we_end, 1ull);
+  } else if (t == EV_WE_START) {
+    atomicAdd(&g->n_we_start, 1ull);
+  } else if (before > 0) {
+    atomicAdd(&g->n_dropped, 1ull);  // handleWriteErrors_, Slicer.h:691-701
+  } else {
+    e = true;
+  }
+  eff[i] = e;
+  scan_in[i] = (e && is_switch(t)) ? i + 1 : 0;
+}
+
+// (3b) predecessor / successor on the same unit, `known`, per-thread entry counts
+__global__ void k_sl_links(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ unit_of,
+                           const uint64_t* __restrict__ ub, const uint32_t* __restrict__ rank,
+                           const uint32_t* __restrict__ epoch, const uint8_t* __restrict__ eff,
+                           const uint32_t* __restrict__ prev_scan, uint32_t* __restrict__ prev,
+                           uint32_t* __restrict__ next, uint8_t* __restrict__ cf, Globals* g) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t pv = NOIDX;
+  uint8_t f = 0;
+  const uint32_t t = ev[i].type;
+  if (eff[i] && is_switch(t)) {
+    const uint32_t raw = prev_scan[i];  // last effective switch event before i, + 1
+    if (raw != 0 && raw - 1 >= ub[unit_of[i]]) {
+      const uint32_t r = raw - 1;
+      next[r] = i;  // (each event is the predecessor of at most one)
+      if (epoch[rank[r]] == epoch[rank[i]]) {  // no reset in between
+        pv = r;
+        f |= CF_PREV;
+        if (t == EV_IN) {
+          if (ev[r].type == EV_IN) atomicOr(&g->bad, BAD_DOUBLE_IN);  // handleEventInPreConditionError_, :839-868
+          f |= CF_KNOWN;  // the state left behind is E[1]: known_num_levels
+        }
+      }
+    }
+  }
+  prev[i] = pv;
+  cf[i] = f;
+}
+
+__global__ void k_sl_entry_counts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
+                                  const uint32_t* __restrict__ epoch, const uint8_t* __restrict__ eff,
+                                  const uint32_t* __restrict__ next, uint32_t* __restrict__ ecnt) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t c = 0;
+  if (eff[i] && ev[i].tag != 0) {
+    const uint32_t t = ev[i].type;
+    if (t == EV_CREATE) c = 1;
+    else if (t == EV_IN) {
+      const uint32_t nx = next[i];
+      c = 1 + ((nx != NOIDX && epoch[rank[nx]] == epoch[rank[i]]) ? 1u : 0u);
+    }
+  }
+  ecnt[i] = c;
+}
+
+__global__ void k_sl_entries(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
+                             const uint32_t* __restrict__ next, const uint32_t* __restrict__ ecnt,
+                             const uint32_t* __restrict__ eoff, uint64_t* __restrict__ ekey, uint64_t* __restrict__ eval) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || ecnt[i] == 0) return;
+  const uint64_t tag = ev[i].tag;
+  const uint32_t o = eoff[i];
+  const uint32_t kind = ev[i].type == EV_CREATE ? K_CREATE : K_IN;
+  ekey[o] = (tag << 32) | rank[i];
+  eval[o] = (static_cast<uint64_t>(i) << 2) | kind;
+  if (ecnt[i] == 2) {
+    ekey[o + 1] = (tag << 32) | rank[next[i]];
+    eval[o + 1] = (static_cast<uint64_t>(i) << 2) | K_PARK;
+  }
+}
+
+// (4) one thread per thread id: walk its events in merge order
+__global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __restrict__ eval, uint32_t n_entries,
+                          const uint32_t* __restrict__ rank, const uint32_t* __restrict__ epoch, uint8_t* __restrict__ cf,
+                          uint32_t* __restrict__ t_create /* [n_tags][2]: event that created T[v][k] */) {
+  const uint32_t e0 = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e0 >= n_entries) return;
+  const uint32_t v = static_cast<uint32_t>(ekey[e0] >> 32);
+  if (e0 > 0 && static_cast<uint32_t>(ekey[e0 - 1] >> 32) == v) return;  // not the first entry of v
+  bool ex1 = false, ln1 = false, ex0 = false, ln0 = false;
+  uint32_t cur_epoch = 0;
+  for (uint32_t e = e0; e < n_entries && static_cast<uint32_t>(ekey[e] >> 32) == v; ++e) {
+    const uint32_t kind = static_cast<uint32_t>(eval[e] & 3), i = static_cast<uint32_t>(eval[e] >> 2);
+    const uint32_t ep = epoch[rank[i]];  // (a parking switch-out is in its switch-in's epoch)
+    if (ep != cur_epoch) {               // resetState_, :636-652: dormant lists cleared
+      ln1 = ln0 = false;
+      cur_epoch = ep;
+    }
+    if (kind == K_CREATE) {  // handleThreadLifetime_, :722-732
+      if (!ex1) {
+        ex1 = true;
+        cf[i] |= CF_T1;
+        t_create[2 * v + 1] = i;
+      } else {
+        cf[i] |= CF_BURN;  // emplace fails, next_stack_id_++ was evaluated
+      }
+      ln1 = true;
+    } else if (kind == K_IN) {
+      const bool known = cf[i] & CF_KNOWN;
+      if (known && ex1 && ln1) {  // activateStackStateThatContains_, :611-626
+        ln1 = false;
+        cf[i] |= CF_PICK_T1;
+      } else {                    // {v} with unknown levels, :632-633 / exact match :586-609
+        if (!ex0) {
+          ex0 = true;
+          cf[i] |= CF_T0;
+          t_create[2 * v] = i;
+        }
+        ln0 = false;
+      }
+    } else {  // the next switch event on that unit parks the state: handleLastState_, :761-768
+      if (cf[i] & CF_PICK_T1) ln1 = true;
+      else ln0 = true;
+    }
+  }
+}
+
+// (5a) where E[k] and T[0][k] are first needed
+__global__ void k_sl_firsts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
+                            const uint8_t* __restrict__ eff, const uint8_t* __restrict__ cf, Globals* g) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !eff[i]) return;
+  const uint32_t t = ev[i].type, p = rank[i];
+  const uint8_t f = cf[i];
+  if (t == EV_OUT_PREEMPT || t == EV_OUT_YIELD) atomicMin(&g->e_first[1], p);
+  else if (t == EV_CREATE) {
+    atomicMin(&g->e_first[1], p);  // parent of {v} known (exists already when this one only burns an id)
+    if (ev[i].tag == 0) atomicMin(&g->a_first[1], p);
+  } else if (t == EV_IN) {
+    if (ev[i].tag == 0) {
+      const uint32_t k = (f & CF_KNOWN) ? 1 : 0;
+      atomicMin(&g->a_first[k], p);
+      atomicMin(&g->e_first[k], p);
+    } else if (f & CF_T0) {
+      atomicMin(&g->e_first[0], p);
+    }
+  }
+}
+
+// (5b) ids taken by the event at merge position p
+__global__ void k_sl_id_counts(const hbtgpu_cs_event* __restrict__ ev, const uint32_t* __restrict__ order, uint32_t n,
+                               const uint8_t* __restrict__ eff, const uint8_t* __restrict__ cf, const Globals* g,
+                               uint32_t* __restrict__ idcnt) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  const uint32_t i = order[p];
+  uint32_t c = 0;
+  if (eff[i]) {
+    const uint32_t t = ev[i].type;
+    const uint8_t f = cf[i];
+    if (t == EV_OUT_PREEMPT || t == EV_OUT_YIELD) c = p == g->e_first[1];
+    else if (t == EV_CREATE) {
+      if (ev[i].tag == 0) c = 1 + (p == g->a_first[1] && p == g->e_first[1]);  // create (with parent) or burn
+      else c = ((f & (CF_T1 | CF_BURN)) ? 1u : 0u) + ((f & CF_T1) && p == g->e_first[1]);
+    } else if (t == EV_IN) {
+      if (ev[i].tag == 0) {
+        const uint32_t k = (f & CF_KNOWN) ? 1 : 0;
+        c = (p == g->a_first[k]) + (p == g->a_first[k] && p == g->e_first[k]);
+      } else if (f & CF_T0) {
+        c = 1 + (p == g->e_first[0]);
+      }
+    }
+  }
+  idcnt[p] = c;
+}
+
+// The id of the state event i activated (i: an effective switch event)
+struct Ids {
+  const uint32_t* idbase;    // exclusive sum of idcnt, by merge position
+  const uint32_t* rank;
+  const uint32_t* t_create;  // [n_tags][2]
+  uint64_t e_id[2], a_id[2];
+  uint32_t e_first[2], a_first[2];
+  __device__ __forceinline__ uint64_t thread_state(uint32_t v, uint32_t k) const {
+    const uint32_t p = rank[t_create[2 * v + k]];
+    return static_cast<uint64_t>(idbase[p]) + (p == e_first[k] ? 1u : 0u);  // parent first
+  }
+};
+
+// state slots for the statistics: 0,1 = E[k]; 2,3 = T[0][k]; 4 + 2v + k = T[v][k]
+__device__ __forceinline__ uint32_t state_slot(const hbtgpu_cs_event& e, uint8_t f) {
+  if (e.type != EV_IN) return 1;
+  if (e.tag == 0) return 2 + ((f & CF_KNOWN) ? 1 : 0);
+  return 4 + 2 * e.tag + ((f & CF_PICK_T1) ? 1 : 0);
+}
+__device__ __forceinline__ uint64_t state_id(const Ids& ids, const hbtgpu_cs_event& e, uint8_t f) {
+  if (e.type != EV_IN) return ids.e_id[1];
+  if (e.tag == 0) return ids.a_id[(f & CF_KNOWN) ? 1 : 0];
+  return ids.thread_state(e.tag, (f & CF_PICK_T1) ? 1 : 0);
+}
+
+// (6a) which switch events close a slice with a duration
+__global__ void k_sl_slice_flags(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint8_t* __restrict__ eff,
+                                 const uint32_t* __restrict__ prev, const uint8_t* __restrict__ cf,
+                                 uint32_t* __restrict__ sflag, unsigned long long* __restrict__ st_cum,
+                                 unsigned long long* __restrict__ st_in, unsigned long long* __restrict__ st_out,
+                                 Globals* g) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t fl = 0;
+  if (eff[i] && is_switch(ev[i].type)) {
+    atomicAdd(&st_in[state_slot(ev[i], cf[i])], 1ull);  // markSwitchIn, :231-241
+    const uint32_t r = prev[i];
+    if (r != NOIDX) {
+      const uint64_t dur = ev[i].tstamp - ev[r].tstamp;
+      const uint32_t slot = state_slot(ev[r], cf[r]);
+      if (dur) atomicAdd(&st_cum[slot], static_cast<unsigned long long>(dur));  // markSwitchOut, :243-252
+      atomicAdd(&st_out[slot], 1ull);
+      atomicAdd(&g->n_completed, 1ull);
+      fl = dur != 0;  // completeSlice_ drops slices of no duration, :545-554
+    }
+  }
+  sflag[i] = fl;
+}
+
+// (6b) the slices, unit after unit (the exclusive sum of the flags is their place)
+__global__ void k_sl_emit(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ prev,
+                          const uint8_t* __restrict__ cf, const uint32_t* __restrict__ sflag,
+                          const uint32_t* __restrict__ soff, Ids ids, hbtgpu_slice* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !sflag[i]) return;
+  const uint32_t r = prev[i];
+  const hbtgpu_cs_event a = ev[r], b = ev[i];
+  hbtgpu_slice s;
+  memset(&s, 0, sizeof(s));
+  s.tstamp = a.tstamp;
+  s.duration = b.tstamp - a.tstamp;
+  s.stack_id = state_id(ids, a, cf[r]);
+  s.swin_type = a.type == EV_OUT_PREEMPT ? TT_PREEMPTED : TT_YIELD;  // eventToTransitionType_, :789-805
+  s.swout_type = b.type == EV_OUT_PREEMPT ? TT_PREEMPTED : TT_YIELD;
+  out[soff[i]] = s;
+}
+
+__global__ void k_sl_unit_counts(const uint64_t* __restrict__ ub, uint32_t n_units, uint32_t n,
+                                 const uint32_t* __restrict__ soff, const uint32_t* __restrict__ sflag,
+                                 uint64_t* __restrict__ slice_begin) {
+  const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u > n_units) return;
+  const uint64_t b = u < n_units ? ub[u] : n;
+  slice_begin[u] = b < n ? soff[b] : (n ? soff[n - 1] + sflag[n - 1] : 0);
+}
+
+// (7) the stack table: one entry per state that exists
+__global__ void k_sl_stacks(uint32_t n_tags, Ids ids, const unsigned long long* __restrict__ st_cum,
+                            const unsigned long long* __restrict__ st_in, const unsigned long long* __restrict__ st_out,
+                            hbtgpu_stack_stats* __restrict__ out, unsigned int* __restrict__ n_out) {
+  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= 4 + 2 * n_tags) return;
+  const uint32_t k = slot & 1;
+  uint64_t id, parent = NONE64;
+  uint32_t tag = NA, nset = 0;
+  if (slot < 2) {
+    if (ids.e_first[k] == NOIDX) return;
+    id = ids.e_id[k];
+  } else if (slot < 4) {
+    if (ids.a_first[k] == NOIDX) return;
+    id = ids.a_id[k];
+    parent = ids.e_id[k];
+    tag = 0;
+    nset = 1;
+  } else {
+    const uint32_t v = (slot - 4) >> 1;
+    if (v == 0 || ids.t_create[2 * v + k] == NOIDX) return;
+    id = ids.thread_state(v, k);
+    parent = ids.e_id[k];
+    tag = v;
+    nset = 1;
+  }
+  hbtgpu_stack_stats s;
+  memset(&s, 0, sizeof(s));
+  s.stack_id = id;
+  s.parent_stack_id = parent;
+  for (int t = 0; t < 6; ++t) s.tags[t] = NA;
+  if (nset) s.tags[0] = tag;
+  s.num_set_tags = static_cast<uint8_t>(nset);
+  s.known_num_levels = static_cast<uint8_t>(k);
+  s.cum_active_time = st_cum[slot];
+  s.num_swins = st_in[slot];
+  s.num_swouts = st_out[slot];
+  out[atomicAdd(n_out, 1u)] = s;
+}
+
+}  // namespace
+
+struct hbtgpu_slicer_ctx {
+  int device = 0;
+  std::string err;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  float last_ms = 0.f;
+  char* arena = nullptr;
+  size_t arena_cap = 0, arena_used = 0;
+  char* arena2 = nullptr;
+  size_t arena2_cap = 0;
+  // results of the last run (device pointers into the arena)
+  hbtgpu_slice* d_slices = nullptr;
+  uint64_t* d_slice_begin = nullptr;
+  std::vector<uint64_t> slice_begin;
+  std::vector<hbtgpu_stack_stats> stacks;
+  bool have = false;
+};
+
+namespace {
+
+int sfail(hbtgpu_slicer_ctx* c, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (c) c->err = buf;
+  return code;
+}
+
+#define SK(call)                                                                                    \
+  do {                                                                                              \
+    cudaError_t e_ = (call);                                                                        \
+    if (e_ != cudaSuccess)                                                                          \
+      return sfail(c, -EIO, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+template <class T>
+T* carve(hbtgpu_slicer_ctx* c, size_t n) {
+  const size_t bytes = (n * sizeof(T) + 255) & ~static_cast<size_t>(255);
+  if (c->arena_used + bytes > c->arena_cap) return nullptr;
+  T* p = reinterpret_cast<T*>(c->arena + c->arena_used);
+  c->arena_used += bytes;
+  return p;
+}
+
+inline unsigned blocks(size_t n, unsigned t = 256) { return static_cast<unsigned>((n + t - 1) / t); }
+
+}  // namespace
+
+extern "C" {
+
+hbtgpu_slicer_ctx* hbtgpu_slicer_create(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) return nullptr;  // no CPU fallback
+  if (cudaSetDevice(device) != cudaSuccess) return nullptr;
+  auto* c = new hbtgpu_slicer_ctx();
+  c->device = device;
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
+    hbtgpu_slicer_destroy(c);
+    return nullptr;
+  }
+  return c;
+}
+
+void hbtgpu_slicer_destroy(hbtgpu_slicer_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaFree(c->arena);
+  cudaFree(c->arena2);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+const char* hbtgpu_slicer_last_error(hbtgpu_slicer_ctx* c) { return c ? c->err.c_str() : "no context"; }
+float hbtgpu_slicer_last_ms(const hbtgpu_slicer_ctx* c) { return c ? c->last_ms : 0.f; }
+
+int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const uint64_t* event_begin,
+                      uint32_t n_units, uint32_t flags, hbtgpu_slicer_stats* stats, uint64_t* n_slices,
+                      uint64_t* n_stacks, uint64_t* last_ts) {
+  if (!c) return -EINVAL;
+  c->have = false;
+  if (!event_begin || n_units == 0 || n_units > 65535) return sfail(c, -EINVAL, "null argument or bad unit count");
+  SK(cudaSetDevice(c->device));
+  const uint64_t base = event_begin[0];
+  for (uint32_t u = 0; u < n_units; ++u)
+    if (event_begin[u + 1] < event_begin[u]) return sfail(c, -EINVAL, "event_begin must not decrease");
+  const uint64_t N64 = event_begin[n_units] - base;
+  if (N64 >= 0x7fffffffull) return sfail(c, -EINVAL, "more than 2^31 events in one call");
+  const uint32_t N = static_cast<uint32_t>(N64);
+  if (N && !events) return sfail(c, -EINVAL, "null events");
+  std::vector<uint64_t> ub(n_units + 1);
+  for (uint32_t u = 0; u <= n_units; ++u) ub[u] = event_begin[u] - base;
+
+  // pass 0 sizes: events, unit table, keys
+  cudaStream_t st = c->stream;
+  size_t tmp_sort = 0, tmp_sort2 = 0, tmp_scan = 0, t2 = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
+                                  static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), 0, 64, st);
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort2, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
+                                  static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr), static_cast<int>(2 * N64), 0, 64, st);
+  cub::DeviceScan::InclusiveSum(nullptr, tmp_scan, static_cast<int32_t*>(nullptr), static_cast<int32_t*>(nullptr), static_cast<int>(N), st);
+  cub::DeviceScan::ExclusiveScan(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), MaxOp(), 0u, static_cast<int>(N), st);
+  tmp_scan = std::max(tmp_scan, t2);
+  cub::DeviceScan::ExclusiveSum(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), st);
+  tmp_scan = std::max(tmp_scan, t2);
+  const size_t tmp_bytes = std::max(std::max(tmp_sort, tmp_sort2), tmp_scan) + 256;
+  // The thread table is sized once the largest tag is known; everything else now.
+  const size_t n1 = static_cast<size_t>(N) + 1;
+  size_t need = 0;
+  auto add = [&](size_t n, size_t sz) { need += (n * sz + 255) & ~static_cast<size_t>(255); };
+  add(n1, 16); add(n_units + 1, 8); add(n1, 4);                 // events, unit begins, unit_of
+  add(n1, 8); add(n1, 8); add(n1, 4); add(n1, 4);               // key, key_s, val, order
+  add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);   // rank, delta, depth, start, epoch
+  add(n1, 1); add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);   // eff, scan_in, prev_scan, prev, next
+  add(n1, 1); add(n1, 4); add(n1, 4);                           // cf, ecnt, eoff
+  add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8);  // entries + sorted
+  add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);               // idcnt, idbase, sflag, soff
+  add(n1, 32); add(n_units + 2, 8);                             // slices, slice_begin
+  add(1, sizeof(Globals)); add(4, 4); add(tmp_bytes, 1);
+  const size_t fixed_need = need;
+  if (c->arena_cap < fixed_need) {
+    cudaFree(c->arena);
+    c->arena = nullptr;
+    c->arena_cap = 0;
+    const size_t cap = fixed_need + fixed_need / 4 + (1 << 20);
+    SK(cudaMalloc(&c->arena, cap));
+    c->arena_cap = cap;
+  }
+  c->arena_used = 0;
+  auto* d_ev = carve<hbtgpu_cs_event>(c, n1);
+  auto* d_ub = carve<uint64_t>(c, n_units + 1);
+  auto* d_unit_of = carve<uint32_t>(c, n1);
+  auto* d_key = carve<uint64_t>(c, n1);
+  auto* d_key_s = carve<uint64_t>(c, n1);
+  auto* d_val = carve<uint32_t>(c, n1);
+  auto* d_order = carve<uint32_t>(c, n1);
+  auto* d_rank = carve<uint32_t>(c, n1);
+  auto* d_delta = carve<int32_t>(c, n1);
+  auto* d_depth = carve<int32_t>(c, n1);
+  auto* d_start = carve<uint32_t>(c, n1);
+  auto* d_epoch = carve<uint32_t>(c, n1);
+  auto* d_eff = carve<uint8_t>(c, n1);
+  auto* d_scan_in = carve<uint32_t>(c, n1);
+  auto* d_prev_scan = carve<uint32_t>(c, n1);
+  auto* d_prev = carve<uint32_t>(c, n1);
+  auto* d_next = carve<uint32_t>(c, n1);
+  auto* d_cf = carve<uint8_t>(c, n1);
+  auto* d_ecnt = carve<uint32_t>(c, n1);
+  auto* d_eoff = carve<uint32_t>(c, n1);
+  auto* d_ekey = carve<uint64_t>(c, 2 * n1);
+  auto* d_eval = carve<uint64_t>(c, 2 * n1);
+  auto* d_ekey_s = carve<uint64_t>(c, 2 * n1);
+  auto* d_eval_s = carve<uint64_t>(c, 2 * n1);
+  auto* d_idcnt = carve<uint32_t>(c, n1);
+  auto* d_idbase = carve<uint32_t>(c, n1);
+  auto* d_sflag = carve<uint32_t>(c, n1);
+  auto* d_soff = carve<uint32_t>(c, n1);
+  auto* d_slices = carve<hbtgpu_slice>(c, n1);
+  auto* d_slice_begin = carve<uint64_t>(c, n_units + 2);
+  auto* d_g = carve<Globals>(c, 1);
+  auto* d_small = carve<unsigned int>(c, 4);
+  auto* d_tmp = carve<char>(c, tmp_bytes);
+  if (!d_tmp) return sfail(c, -EIO, "internal: arena too small");
+
+  const hbtgpu_cs_event* ev = d_ev;
+  if (flags & HBTGPU_SLICER_DEVICE_INPUT) {
+    ev = events + base;
+  } else if (N) {
+    SK(cudaMemcpyAsync(d_ev, events + base, static_cast<size_t>(N) * sizeof(hbtgpu_cs_event), cudaMemcpyHostToDevice, st));
+  }
+  SK(cudaMemcpyAsync(d_ub, ub.data(), (n_units + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  Globals g0;
+  memset(&g0, 0, sizeof(g0));
+  g0.e_first[0] = g0.e_first[1] = g0.a_first[0] = g0.a_first[1] = NOIDX;
+  SK(cudaMemcpyAsync(d_g, &g0, sizeof(g0), cudaMemcpyHostToDevice, st));
+  SK(cudaMemsetAsync(d_small, 0, 4 * sizeof(unsigned int), st));
+  SK(cudaEventRecord(c->ev0, st));
+
+  Globals gh = g0;
+  if (N) {
+    size_t t = tmp_bytes;
+    k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of);
+    k_sl_prepare<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_key, d_val, d_g);
+    cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key, d_key_s, d_val, d_order, static_cast<int>(N), 0, 64, st);
+    k_sl_gather<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_rank, d_delta, d_start);
+    t = tmp_bytes;
+    cub::DeviceScan::InclusiveSum(d_tmp, t, d_delta, d_depth, static_cast<int>(N), st);
+    t = tmp_bytes;
+    cub::DeviceScan::InclusiveSum(d_tmp, t, d_start, d_epoch, static_cast<int>(N), st);
+    k_sl_effective<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_depth, d_delta, d_eff, d_scan_in, d_g);
+    t = tmp_bytes;
+    cub::DeviceScan::ExclusiveScan(d_tmp, t, d_scan_in, d_prev_scan, MaxOp(), 0u, static_cast<int>(N), st);
+    SK(cudaMemsetAsync(d_next, 0xff, static_cast<size_t>(N) * sizeof(uint32_t), st));
+    k_sl_links<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_rank, d_epoch, d_eff, d_prev_scan, d_prev, d_next,
+                                          d_cf, d_g);
+    SK(cudaGetLastError());
+    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    if (gh.bad) {
+      const unsigned b = gh.bad;
+      return sfail(c, (b & BAD_UNIT) ? -EINVAL : -ENOTSUP,
+                   "events outside the parallel form:%s%s%s%s%s%s%s",
+                   (b & BAD_TYPE) ? " phase or unknown event types;" : "", (b & BAD_LEVEL) ? " events above level 0;" : "",
+                   (b & BAD_ORDER) ? " a unit's events go back in time;" : "",
+                   (b & BAD_UNIT) ? " comp_unit_id differs from the unit the event was filed under;" : "",
+                   (b & BAD_TAG) ? " switch-in or creation without a tag;" : "",
+                   (b & BAD_DOUBLE_IN) ? " switch-in on a unit whose active state is a thread (the reference resets);" : "",
+                   (b & BAD_WE_END) ? " WriteErrorsEnd without its Start;" : "");
+    }
+  }
+  const uint32_t n_tags = gh.max_tag + 1;
+  if (n_tags > (1u << 27)) return sfail(c, -ENOTSUP, "thread ids up to %u: the per-thread tables would not fit", gh.max_tag);
+  // per-thread tables: their own allocation, sized now that the largest tag is known
+  const size_t n_slots = 4 + 2 * static_cast<size_t>(n_tags);
+  size_t need2 = 0;
+  auto add2 = [&](size_t n, size_t sz) { need2 += (n * sz + 255) & ~static_cast<size_t>(255); };
+  add2(2 * static_cast<size_t>(n_tags), 4); add2(n_slots, 8); add2(n_slots, 8); add2(n_slots, 8);
+  add2(n_slots, sizeof(hbtgpu_stack_stats));
+  if (need2 > c->arena2_cap) {
+    cudaFree(c->arena2);
+    c->arena2 = nullptr;
+    c->arena2_cap = 0;
+    SK(cudaMalloc(&c->arena2, need2 + need2 / 4 + 4096));
+    c->arena2_cap = need2 + need2 / 4 + 4096;
+  }
+  char* a2 = c->arena2;
+  auto carve2 = [&](size_t n, size_t sz) {
+    char* q = a2;
+    a2 += (n * sz + 255) & ~static_cast<size_t>(255);
+    return q;
+  };
+  auto* d_tcreate = reinterpret_cast<uint32_t*>(carve2(2 * static_cast<size_t>(n_tags), 4));
+  auto* d_cum = reinterpret_cast<unsigned long long*>(carve2(n_slots, 8));
+  auto* d_in = reinterpret_cast<unsigned long long*>(carve2(n_slots, 8));
+  auto* d_out = reinterpret_cast<unsigned long long*>(carve2(n_slots, 8));
+  auto* d_stacks = reinterpret_cast<hbtgpu_stack_stats*>(carve2(n_slots, sizeof(hbtgpu_stack_stats)));
+  SK(cudaMemsetAsync(d_tcreate, 0xff, 2 * static_cast<size_t>(n_tags) * sizeof(uint32_t), st));
+  SK(cudaMemsetAsync(d_cum, 0, n_slots * 8, st));
+  SK(cudaMemsetAsync(d_in, 0, n_slots * 8, st));
+  SK(cudaMemsetAsync(d_out, 0, n_slots * 8, st));
+
+  uint64_t total_slices = 0;
+  c->slice_begin.assign(n_units + 1, 0);
+  unsigned int small[4] = {0, 0, 0, 0};
+  if (N) {
+    size_t t = tmp_bytes;
+    k_sl_entry_counts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_epoch, d_eff, d_next, d_ecnt);
+    cub::DeviceScan::ExclusiveSum(d_tmp, t, d_ecnt, d_eoff, static_cast<int>(N), st);
+    uint32_t last_off = 0, last_cnt = 0;
+    SK(cudaMemcpyAsync(&last_off, d_eoff + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+    SK(cudaMemcpyAsync(&last_cnt, d_ecnt + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    const uint32_t n_entries = last_off + last_cnt;
+    if (n_entries) {
+      k_sl_entries<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_next, d_ecnt, d_eoff, d_ekey, d_eval);
+      t = tmp_bytes;
+      cub::DeviceRadixSort::SortPairs(d_tmp, t, d_ekey, d_ekey_s, d_eval, d_eval_s, static_cast<int>(n_entries), 0, 64, st);
+      k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, d_rank, d_epoch, d_cf, d_tcreate);
+    }
+    k_sl_firsts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_eff, d_cf, d_g);
+    k_sl_id_counts<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_eff, d_cf, d_g, d_idcnt);
+    t = tmp_bytes;
+    cub::DeviceScan::ExclusiveSum(d_tmp, t, d_idcnt, d_idbase, static_cast<int>(N), st);
+    SK(cudaGetLastError());
+    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    Ids ids;
+    ids.idbase = d_idbase;
+    ids.rank = d_rank;
+    ids.t_create = d_tcreate;
+    for (int k = 0; k < 2; ++k) {
+      ids.e_first[k] = gh.e_first[k];
+      ids.a_first[k] = gh.a_first[k];
+      ids.e_id[k] = ids.a_id[k] = NONE64;
+    }
+    // ids of the four shared states: E[k] is the parent, created first when one event makes both
+    uint32_t pos_list[4] = {gh.e_first[0], gh.e_first[1], gh.a_first[0], gh.a_first[1]};
+    uint32_t base_at[4] = {0, 0, 0, 0};
+    for (int j = 0; j < 4; ++j)
+      if (pos_list[j] != NOIDX) SK(cudaMemcpyAsync(&base_at[j], d_idbase + pos_list[j], 4, cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    for (int k = 0; k < 2; ++k) {
+      if (gh.e_first[k] != NOIDX) ids.e_id[k] = base_at[k];
+      if (gh.a_first[k] != NOIDX) ids.a_id[k] = static_cast<uint64_t>(base_at[2 + k]) + (gh.a_first[k] == gh.e_first[k] ? 1 : 0);
+    }
+    k_sl_slice_flags<<<blocks(N), 256, 0, st>>>(ev, N, d_eff, d_prev, d_cf, d_sflag, d_cum, d_in, d_out, d_g);
+    t = tmp_bytes;
+    cub::DeviceScan::ExclusiveSum(d_tmp, t, d_sflag, d_soff, static_cast<int>(N), st);
+    k_sl_emit<<<blocks(N), 256, 0, st>>>(ev, N, d_prev, d_cf, d_sflag, d_soff, ids, d_slices);
+    k_sl_unit_counts<<<blocks(n_units + 1), 256, 0, st>>>(d_ub, n_units, N, d_soff, d_sflag, d_slice_begin);
+    k_sl_stacks<<<blocks(n_slots), 256, 0, st>>>(n_tags, ids, d_cum, d_in, d_out, d_stacks, d_small);
+    SK(cudaGetLastError());
+    SK(cudaEventRecord(c->ev1, st));
+    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+    SK(cudaMemcpyAsync(c->slice_begin.data(), d_slice_begin, (n_units + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+    SK(cudaMemcpyAsync(small, d_small, sizeof(small), cudaMemcpyDeviceToHost, st));
+    uint32_t last_idx = 0;
+    SK(cudaMemcpyAsync(&last_idx, d_order + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    hbtgpu_cs_event last_ev;
+    SK(cudaMemcpy(&last_ev, ev + last_idx, sizeof(last_ev), cudaMemcpyDeviceToHost));
+    if (last_ts) *last_ts = last_ev.tstamp;
+    total_slices = c->slice_begin[n_units];
+    SK(cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
+  } else {
+    SK(cudaEventRecord(c->ev1, st));
+    SK(cudaStreamSynchronize(st));
+    if (last_ts) *last_ts = 0;
+    c->last_ms = 0.f;
+  }
+  (void)total_slices;
+  c->stacks.resize(small[0]);
+  if (small[0]) {
+    SK(cudaMemcpy(c->stacks.data(), d_stacks, small[0] * sizeof(hbtgpu_stack_stats), cudaMemcpyDeviceToHost));
+    std::sort(c->stacks.begin(), c->stacks.end(),
+              [](const hbtgpu_stack_stats& a, const hbtgpu_stack_stats& b) { return a.stack_id < b.stack_id; });
+  }
+  if (stats) {
+    memset(stats, 0, sizeof(*stats));
+    stats->num_processed = N;  // every event is processed once (no event is older than its predecessor)
+    stats->num_error_start = gh.n_we_start;
+    stats->num_error_end = gh.n_we_end;
+    stats->num_dropped = gh.n_dropped;
+    stats->num_slices_completed = gh.n_completed;
+  }
+  if (n_slices)
+    for (uint32_t u = 0; u < n_units; ++u) n_slices[u] = c->slice_begin[u + 1] - c->slice_begin[u];
+  if (n_stacks) *n_stacks = c->stacks.size();
+  c->d_slices = d_slices;
+  c->d_slice_begin = d_slice_begin;
+  c->have = true;
+  return 0;
+}
+
+int hbtgpu_slicer_get_slices(hbtgpu_slicer_ctx* c, uint32_t unit, hbtgpu_slice* out, uint64_t cap) {
+  if (!c || !out) return -EINVAL;
+  if (!c->have) return sfail(c, -EINVAL, "no results: call hbtgpu_slicer_run first");
+  if (unit + 1 >= c->slice_begin.size()) return sfail(c, -EINVAL, "unit %u out of range", unit);
+  const uint64_t n = c->slice_begin[unit + 1] - c->slice_begin[unit];
+  if (cap < n) return sfail(c, -ENOSPC, "%llu slices, room for %llu", (unsigned long long)n, (unsigned long long)cap);
+  SK(cudaSetDevice(c->device));
+  if (n) SK(cudaMemcpy(out, c->d_slices + c->slice_begin[unit], n * sizeof(hbtgpu_slice), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int hbtgpu_slicer_get_stacks(hbtgpu_slicer_ctx* c, hbtgpu_stack_stats* out, uint64_t cap) {
+  if (!c || !out) return -EINVAL;
+  if (!c->have) return sfail(c, -EINVAL, "no results: call hbtgpu_slicer_run first");
+  if (cap < c->stacks.size()) return sfail(c, -ENOSPC, "%zu stacks, room for %llu", c->stacks.size(), (unsigned long long)cap);
+  if (!c->stacks.empty()) memcpy(out, c->stacks.data(), c->stacks.size() * sizeof(hbtgpu_stack_stats));
+  return 0;
+}
+
+int hbtgpu_slicer_slices_device(hbtgpu_slicer_ctx* c, const hbtgpu_slice** slices, const uint64_t** slice_begin) {
+  if (!c || !slices || !slice_begin) return -EINVAL;
+  if (!c->have) return sfail(c, -EINVAL, "no results: call hbtgpu_slicer_run first");
+  *slices = c->d_slices;
+  *slice_begin = c->d_slice_begin;
+  return 0;
+}
+
+}  // extern "C"

@@ -17,11 +17,21 @@ assert SLICE_DTYPE.itemsize == 32 and UNIT_DTYPE.itemsize == 48 and FREQ_DTYPE.i
 
 TRIM, ABORT_ON_MISSING, DEVICE_INPUT, FORCE_EXACT = 1, 2, 4, 8
 
+EVENT_DTYPE = np.dtype([("tstamp", "<u8"), ("type", "u1"), ("level", "u1"), ("comp_unit_id", "<u2"), ("tag", "<u4")])
+STACK_DTYPE = np.dtype([("stack_id", "<u8"), ("parent_stack_id", "<u8"), ("tags", "<u4", (6,)),
+                        ("num_set_tags", "u1"), ("known_num_levels", "u1"), ("pad", "u1", (6,)),
+                        ("cum_active_time", "<u8"), ("num_swins", "<u8"), ("num_swouts", "<u8")])
+SLICER_STAT_KEYS = ("num_processed", "num_error_start", "num_error_end", "num_error_out_sync", "num_dropped",
+                    "num_out_of_order", "num_slices_completed", "num_logic_errors")
+assert EVENT_DTYPE.itemsize == 16 and STACK_DTYPE.itemsize == 72
+
 ABI_SYMBOLS = [
     "hbtgpu_islice_create", "hbtgpu_islice_destroy", "hbtgpu_islice_last_error",
     "hbtgpu_islice_release", "hbtgpu_islice_get_units", "hbtgpu_islice_get",
     "hbtgpu_islice_device_view", "hbtgpu_islice_last_ms",
     "hbtgpu_islice_bin", "hbtgpu_islice_bin_get", "hbtgpu_islice_bin_durations_device",
+    "hbtgpu_slicer_create", "hbtgpu_slicer_destroy", "hbtgpu_slicer_last_error", "hbtgpu_slicer_run",
+    "hbtgpu_slicer_get_slices", "hbtgpu_slicer_get_stacks", "hbtgpu_slicer_slices_device", "hbtgpu_slicer_last_ms",
 ]
 
 
@@ -62,6 +72,19 @@ def _lib():
         L.hbtgpu_islice_bin_get.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
         L.hbtgpu_islice_bin_durations_device.restype = C.c_void_p
         L.hbtgpu_islice_bin_durations_device.argtypes = [C.c_void_p]
+        L.hbtgpu_slicer_create.restype = C.c_void_p
+        L.hbtgpu_slicer_create.argtypes = [C.c_int]
+        L.hbtgpu_slicer_destroy.restype = None
+        L.hbtgpu_slicer_destroy.argtypes = [C.c_void_p]
+        L.hbtgpu_slicer_last_error.restype = C.c_char_p
+        L.hbtgpu_slicer_last_error.argtypes = [C.c_void_p]
+        L.hbtgpu_slicer_last_ms.restype = C.c_float
+        L.hbtgpu_slicer_last_ms.argtypes = [C.c_void_p]
+        L.hbtgpu_slicer_run.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hbtgpu_slicer_get_slices.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.hbtgpu_slicer_get_stacks.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        L.hbtgpu_slicer_slices_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _ready = True
     return L
 
@@ -164,3 +187,66 @@ class IntervalSlicer:
     @property
     def last_ms(self):
         return float(self.L.hbtgpu_islice_last_ms(self.h))
+
+
+class Slicer:
+    """tagstack::slice::Slicer over one window of level-0 events of all comp units."""
+
+    def __init__(self, device=0):
+        self.L = _lib()
+        self.h = self.L.hbtgpu_slicer_create(device)
+        if not self.h:
+            raise HbtGpuError(-19, "hbtgpu_slicer_create failed (no CUDA device? there is no CPU fallback)")
+
+    def close(self):
+        if self.h:
+            self.L.hbtgpu_slicer_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise HbtGpuError(rc, self.L.hbtgpu_slicer_last_error(self.h).decode())
+
+    def run(self, unit_events=None, device_events=None, event_begin=None):
+        """unit_events: list of EVENT_DTYPE arrays (one per comp unit, stream order), or
+        device_events (raw pointer) + event_begin.  Returns dict(slices=[per unit], stats, stacks,
+        last_ts)."""
+        if device_events is None:
+            n_units = len(unit_events)
+            event_begin = np.concatenate([[0], np.cumsum([len(e) for e in unit_events])]).astype(np.uint64)
+            ev = np.ascontiguousarray(np.concatenate(unit_events) if n_units else np.zeros(0, EVENT_DTYPE),
+                                      dtype=EVENT_DTYPE)
+            ptr, flags = ev.ctypes.data, 0
+        else:
+            event_begin = np.ascontiguousarray(event_begin, dtype=np.uint64)
+            n_units = len(event_begin) - 1
+            ptr, flags = device_events, 1
+        stats = np.zeros(len(SLICER_STAT_KEYS), np.uint64)
+        n_slices = np.zeros(n_units, np.uint64)
+        n_stacks, last_ts = C.c_uint64(0), C.c_uint64(0)
+        self._check(self.L.hbtgpu_slicer_run(self.h, ptr, event_begin.ctypes.data, n_units, flags, stats.ctypes.data,
+                                             n_slices.ctypes.data, C.byref(n_stacks), C.byref(last_ts)))
+        slices = []
+        for u in range(n_units):
+            out = np.zeros(max(1, int(n_slices[u])), SLICE_DTYPE)
+            self._check(self.L.hbtgpu_slicer_get_slices(self.h, u, out.ctypes.data, len(out)))
+            slices.append(out[:int(n_slices[u])])
+        stacks = np.zeros(max(1, n_stacks.value), STACK_DTYPE)
+        self._check(self.L.hbtgpu_slicer_get_stacks(self.h, stacks.ctypes.data, len(stacks)))
+        return {"slices": slices, "stats": dict(zip(SLICER_STAT_KEYS, (int(x) for x in stats))),
+                "stacks": stacks[:n_stacks.value], "last_ts": last_ts.value, "n_slices": n_slices}
+
+    def slices_device(self):
+        a, b = C.c_void_p(0), C.c_void_p(0)
+        self._check(self.L.hbtgpu_slicer_slices_device(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    @property
+    def last_ms(self):
+        return float(self.L.hbtgpu_slicer_last_ms(self.h))

@@ -641,6 +641,50 @@ int hbtgpu_islice_bin_get(hbtgpu_islice_ctx* ctx, hbtgpu_bin_freq* freqs, uint64
                           uint64_t durations_cap);
 const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* ctx); /* the matrix where it was built */
 
+/* ---- tagstack events -> slices (Slicer side) ----------------------------
+ *
+ * Replaces tagstack::slice::Slicer<>::processNext (hbt/src/tagstack/Slicer.h:336-459, with
+ * createStackState_ :560-584, activateStackState* :515-634, handleWriteErrors_ :668-703,
+ * handleThreadLifetime_ :705-745, handleLastState_ :747-787, completeSlice_ :529-558) for one
+ * window of events of all comp units at once: unit u's events (16-byte tagstack::Event records,
+ * what hbtgpu_cs_get_events / hbtgpu_cs_events_device hand out after the thread dictionary has
+ * run) at events[event_begin[u] .. event_begin[u+1]), each unit in stream order.  The merge of
+ * the units (Event::happenedBefore: tstamp, then comp unit, tagstack/Event.h:217-223), the stack
+ * dictionary with ids in order of creation, the dormant lists and the resets are computed on
+ * the GPU.  Every call is a Slicer of its own, started empty.
+ *
+ * Scope: level-0 events (ThreadCreation / ThreadDestruction / SwitchIn / SwitchOut* /
+ * WriteErrors*), every unit's events in time order, no switch-in on a unit whose active state is
+ * a thread, no WriteErrorsEnd without its Start.  Input outside it is refused with -ENOTSUP and
+ * a message that names the reason (there is no CPU path); comp_unit_id that differs from the
+ * unit an event was filed under is -EINVAL (the reference throws, :351-352).
+ */
+#define HBTGPU_SLICER_DEVICE_INPUT 0x1u /* events is a device pointer (event_begin stays host) */
+typedef struct {  /* SlicerStats, Slicer.h:276-285 */
+  uint64_t num_processed, num_error_start, num_error_end, num_error_out_sync, num_dropped, num_out_of_order,
+      num_slices_completed, num_logic_errors;
+} hbtgpu_slicer_stats;
+typedef struct {  /* one entry of getTagStackStatsDump(), Slicer.h:160-193,478-485 */
+  uint64_t stack_id, parent_stack_id;  /* parent ~0 (kInvalidTagStackId) for the empty stacks */
+  uint32_t tags[6];                    /* tags[i >= num_set_tags] = ~0 (kNA) */
+  uint8_t num_set_tags, known_num_levels, pad[6];
+  uint64_t cum_active_time, num_swins, num_swouts;
+} hbtgpu_stack_stats;
+typedef struct hbtgpu_slicer_ctx hbtgpu_slicer_ctx;
+hbtgpu_slicer_ctx* hbtgpu_slicer_create(int device);
+void hbtgpu_slicer_destroy(hbtgpu_slicer_ctx* ctx);
+const char* hbtgpu_slicer_last_error(hbtgpu_slicer_ctx* ctx);
+/* n_slices: [n_units] slices written for each unit; any output pointer may be NULL. */
+int hbtgpu_slicer_run(hbtgpu_slicer_ctx* ctx, const hbtgpu_cs_event* events, const uint64_t* event_begin,
+                      uint32_t n_units, uint32_t flags, hbtgpu_slicer_stats* stats, uint64_t* n_slices,
+                      uint64_t* n_stacks, uint64_t* last_ts);
+int hbtgpu_slicer_get_slices(hbtgpu_slicer_ctx* ctx, uint32_t unit, hbtgpu_slice* out, uint64_t cap);
+int hbtgpu_slicer_get_stacks(hbtgpu_slicer_ctx* ctx, hbtgpu_stack_stats* out, uint64_t cap); /* by stack_id */
+/* Where the slices are: unit u at slices[slice_begin[u] .. slice_begin[u+1]) (both device pointers;
+ * the layout hbtgpu_islice_release takes with HBTGPU_ISLICE_DEVICE_INPUT). */
+int hbtgpu_slicer_slices_device(hbtgpu_slicer_ctx* ctx, const hbtgpu_slice** slices, const uint64_t** slice_begin);
+float hbtgpu_slicer_last_ms(const hbtgpu_slicer_ctx* ctx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -156,11 +156,13 @@ def test_synth_matches_oracles(port_oracle):
 def test_slices_struct_sizes_match_header(built, tmp_path):
     from dynolog_b200 import hbtgpu_slices as sl
     src = tmp_path / "szsl.c"
-    src.write_text('#include <stdio.h>\n#include "hbtgpu.h"\nint main(){printf("%zu %zu %zu %zu %zu\\n",'
+    src.write_text('#include <stdio.h>\n#include "hbtgpu.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu\\n",'
                    "sizeof(hbtgpu_slice),sizeof(hbtgpu_islice_unit),sizeof(hbtgpu_islice_view),"
-                   "sizeof(hbtgpu_bin_freq),sizeof(hbtgpu_bin_summary));return 0;}\n")
+                   "sizeof(hbtgpu_bin_freq),sizeof(hbtgpu_bin_summary),sizeof(hbtgpu_stack_stats),"
+                   "sizeof(hbtgpu_slicer_stats));return 0;}\n")
     exe = tmp_path / "szsl"
     subprocess.check_call(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
     sizes = [int(x) for x in subprocess.check_output([str(exe)]).split()]
     assert sizes == [sl.SLICE_DTYPE.itemsize, sl.UNIT_DTYPE.itemsize, ctypes.sizeof(sl.View),
-                     sl.FREQ_DTYPE.itemsize, ctypes.sizeof(sl.BinSummary)]
+                     sl.FREQ_DTYPE.itemsize, ctypes.sizeof(sl.BinSummary), sl.STACK_DTYPE.itemsize,
+                     8 * len(sl.SLICER_STAT_KEYS)]

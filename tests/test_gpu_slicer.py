@@ -1,0 +1,156 @@
+"""GPU parity of the Slicer (events -> slices): hbtgpu_slicer_run through the
+C ABI against the C restatement (pinned to the real tagstack::slice::Slicer<> by
+tests/test_slicer_oracle.py) and, where oracle/_ref travelled along, against the real class itself:
+every slice field, the stack table (ids, parents, tags, known levels, active time, switch counts),
+the statistics, the last timestamp.  Input outside the parallel form's scope must be refused
+loudly."""
+import numpy as np
+import pytest
+
+from dynolog_b200 import hbtgpu_cs, hbtgpu_slices as gs, synth
+from dynolog_b200.hbtgpu import HbtGpuError
+from oracle import pyoracle as po
+from test_slicer_oracle import CREATE, IN, NA, OUT_P, OUT_Y, START, WE_END, WE_START, events, random_events
+
+pytestmark = pytest.mark.gpu
+KINDS = ["port"] + (["reference"] if po.slices_available("reference") else [])
+
+
+@pytest.fixture(scope="module")
+def slicer():
+    s = gs.Slicer(0)
+    yield s
+    s.close()
+
+
+def split_units(ev, n_units):
+    """merge-ordered events -> per-unit streams + the merge order the Combinator tree would produce."""
+    units = [ev[ev["comp_unit_id"] == u] for u in range(n_units)]
+    merged = np.concatenate(units) if n_units else ev[:0]
+    order = np.lexsort((merged["comp_unit_id"], merged["tstamp"]))
+    return units, merged[order]
+
+
+def compare(got, exp):
+    assert exp["rc"] == 0
+    assert got["stats"] == exp["stats"]
+    assert got["last_ts"] == exp["last_ts"]
+    for u, (x, y) in enumerate(zip(got["slices"], exp["slices"])):
+        assert po.slices_as_tuples(x) == po.slices_as_tuples(y), u
+    a, b = got["stacks"], exp["stacks"]
+    assert len(a) == len(b)
+    for k in ("stack_id", "parent_stack_id", "num_set_tags", "known_num_levels", "cum_active_time", "num_swins",
+              "num_swouts"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(a["tags"][:, 0], b["tags"][:, 0])
+
+
+def supported(ev, n_units):
+    """does the window stay inside the parallel form? (no switch-in on a unit whose active state is a
+    thread, no WriteErrorsEnd without a Start; decided by running the restatement's bookkeeping)"""
+    depth = 0
+    last = [None] * n_units
+    for e in ev:
+        t = int(e["type"])
+        if t == WE_END:
+            if depth == 0:
+                return False
+            depth -= 1
+        elif t == WE_START:
+            depth += 1
+            last = [None] * n_units
+        elif depth == 0 and t in (IN, OUT_P, OUT_Y):
+            cu = int(e["comp_unit_id"])
+            if t == IN and last[cu] == IN:
+                return False
+            last[cu] = t
+    return True
+
+
+def test_reference_vector(slicer):
+    ev = events([(20, IN, 0, 2), (30, OUT_P, 0, NA), (30, IN, 0, 4), (50, OUT_P, 0, NA), (60, IN, 0, 1), (80, OUT_P, 0, NA)])
+    got = slicer.run([ev])
+    Y, P = po.TT_YIELD, po.TT_PREEMPTED
+    assert po.slices_as_tuples(got["slices"][0]) == [(20, 10, 1, Y, P), (30, 20, 3, Y, P), (50, 10, 2, P, Y), (60, 20, 4, Y, P)]
+    for kind in KINDS:
+        compare(got, po.slicer_run(kind, ev, 1))
+
+
+@pytest.mark.parametrize("kw", [dict(p_double_in=0.0), dict(p_double_in=0.0, p_we=0.0, p_migrate=0.0),
+                                dict(p_double_in=0.0, p_migrate=0.5, p_create=0.2), dict(p_double_in=0.0, p_we=0.1),
+                                dict(p_double_in=0.0, p_tid0=0.9), dict(p_double_in=0.0, p_same_ts=0.7),
+                                dict(p_double_in=0.0, p_create=0.4, p_tid0=0.5)])
+def test_random_windows(slicer, kw):
+    r = np.random.default_rng(len(repr(kw)) + 1)
+    done = 0
+    for trial in range(60):
+        n_units = int(r.integers(1, 7))
+        ev = random_events(r, n_units, int(r.integers(1, 900)), int(r.choice([2, 5, 40, 300])), **kw)
+        units, merged = split_units(ev, n_units)
+        if not supported(merged, n_units):
+            with pytest.raises(HbtGpuError):
+                slicer.run(units)
+            continue
+        got = slicer.run(units)
+        for kind in KINDS:
+            compare(got, po.slicer_run(kind, merged, n_units))
+        done += 1
+    assert done > 20
+
+
+def test_refusals(slicer):
+    with pytest.raises(HbtGpuError, match="switch-in on a unit"):
+        slicer.run([events([(10, IN, 0, 3), (20, IN, 0, 4)])])
+    ev = events([(10, IN, 0, 3), (20, START, 0, 7)])
+    with pytest.raises(HbtGpuError, match="phase"):
+        slicer.run([ev])
+    with pytest.raises(HbtGpuError, match="back in time"):
+        slicer.run([events([(30, IN, 0, 3), (20, OUT_P, 0, NA)])])
+    with pytest.raises(HbtGpuError, match="WriteErrorsEnd"):
+        slicer.run([events([(10, WE_END, 0, NA)])])
+    with pytest.raises(HbtGpuError, match="comp_unit_id"):
+        slicer.run([events([(10, IN, 1, 3)])])
+    ev = events([(10, IN, 0, 3)])
+    ev["level"][0] = 1
+    with pytest.raises(HbtGpuError, match="level 0"):
+        slicer.run([ev])
+
+
+def test_decoded_capture_to_slices_on_the_device(slicer):
+    """thread-switch images -> events (GPU) -> slices (GPU) -> per-interval slices (GPU): the
+    slices never leave the device between the last two stages."""
+    n_cpus = 8
+    streams = synth.cs_capture(n_cpus, 256 * 1024, n_tids=200, life_ppm=20000, comm_ppm=0, lost_ppm=1000,
+                               throttle_ppm=0, seed=5)
+    dec = hbtgpu_cs.decode(streams, tid_level=0)
+    units = dec["events"]
+    merged = np.concatenate(units)
+    merged = merged[np.lexsort((merged["comp_unit_id"], merged["tstamp"]))]
+    got = slicer.run(units)
+    assert got["stats"]["num_slices_completed"] > 3000 * n_cpus and got["stats"]["num_error_start"] > 0
+    for kind in KINDS:
+        compare(got, po.slicer_run(kind, merged, n_cpus))
+    # hand the device-resident slices to the interval slicer
+    import torch
+    d_slices, d_begin = slicer.slices_device()
+    sb = np.concatenate([[0], np.cumsum(got["n_slices"])]).astype(np.uint64)
+    t0 = int(min(s["tstamp"][0] for s in got["slices"] if len(s)))
+    rows = []
+    for u in range(n_cpus):
+        k = np.arange(200, dtype=np.uint64)
+        rows.append(np.stack([np.uint64(t0) + k * np.uint64(100_000), np.full(200, 100_000, np.uint64)], axis=1))
+    rb = np.concatenate([[0], np.cumsum([len(x) for x in rows])]).astype(np.uint64)
+    d_rows = torch.from_numpy(np.concatenate(rows).view(np.int64)).cuda()
+    torch.cuda.synchronize()
+    isl = gs.IntervalSlicer(0)
+    try:
+        marks = np.zeros(n_cpus, np.uint64)
+        flags = po.TRIM | po.ABORT_ON_MISSING
+        u_res = isl.release_device(d_slices, sb, d_rows.data_ptr(), 2, rb, 2**63, flags, marks)
+        assert (u_res["status"] == 0).all()
+        for u in range(n_cpus):
+            exp = po.islice_release("port", got["slices"][u], rows[u], 2**63, flags, 0)
+            counts, out = isl.get(u)
+            assert np.array_equal(counts, exp["counts"]) and po.slices_as_tuples(out) == po.slices_as_tuples(exp["slices"])
+    finally:
+        isl.close()
