@@ -67,6 +67,7 @@ struct Globals {
   unsigned int a_first[2];  // ... T[0][k] (tid 0)
   unsigned long long n_dropped, n_we_start, n_we_end, n_completed;
   unsigned int max_tag;
+  unsigned long long max_ts;
 };
 
 struct MaxOp {
@@ -91,8 +92,20 @@ __global__ void k_sl_prepare(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
   if (e.type >= EV_CREATE && e.type <= EV_OUT_YIELD && e.level != 0) bad |= BAD_LEVEL;
   if ((e.type == EV_CREATE || e.type == EV_IN) && e.tag == NA) bad |= BAD_TAG;
   if (i > ub[u] && ev[i - 1].tstamp > e.tstamp) bad |= BAD_ORDER;
-  if (bad) atomicOr(&g->bad, bad);
-  if ((e.type == EV_CREATE || e.type == EV_IN) && e.tag != NA) atomicMax(&g->max_tag, e.tag);
+  // (threads past the end have left: aggregate over the lanes that are here)
+  const unsigned m = __activemask();
+  const uint32_t wbad = __reduce_or_sync(m, bad);
+  const uint32_t wmax = __reduce_max_sync(m, ((e.type == EV_CREATE || e.type == EV_IN) && e.tag != NA) ? e.tag : 0u);
+  uint64_t wts = e.tstamp;  // (a unit's last event would do, but the check above may fail)
+  for (int o = 16; o; o >>= 1) {
+    const uint64_t other = __shfl_xor_sync(m, wts, o);
+    if ((m >> ((threadIdx.x & 31) ^ o)) & 1u) wts = max(wts, other);
+  }
+  if ((threadIdx.x & 31) == __ffs(m) - 1) {
+    if (wbad) atomicOr(&g->bad, wbad);
+    if (wmax) atomicMax(&g->max_tag, wmax);
+    atomicMax(&g->max_ts, static_cast<unsigned long long>(wts));
+  }
 }
 
 __global__ void k_sl_unit_of(const uint64_t* __restrict__ ub, uint32_t n_units, uint32_t* __restrict__ unit_of) {
@@ -120,16 +133,17 @@ __global__ void k_sl_effective(const hbtgpu_cs_event* __restrict__ ev, uint32_t 
   if (i >= n) return;
   const uint32_t t = ev[i].type, p = rank[i];
   const int32_t before = depth_incl[p] - delta[p];  // num_active_write_errors_ as the event finds it
-  bool e = false;
-  if (t == EV_WE_END) {
-    if (before <= 0) atomicOr(&g->bad, BAD_WE_END);  // the reference's unsigned counter would wrap
-    atomicAdd(&g->n_we_end, 1ull);
-  } else if (t == EV_WE_START) {
-    atomicAdd(&g->n_we_start, 1ull);
-  } else if (before > 0) {
-    atomicAdd(&g->n_dropped, 1ull);  // handleWriteErrors_, Slicer.h:691-701
-  } else {
-    e = true;
+  const bool we_end = t == EV_WE_END, we_start = t == EV_WE_START;
+  const bool dropped = !we_end && !we_start && before > 0;  // handleWriteErrors_, Slicer.h:691-701
+  const bool e = !we_end && !we_start && !dropped;
+  const unsigned m = __activemask();
+  const unsigned b_end = __ballot_sync(m, we_end), b_start = __ballot_sync(m, we_start), b_drop = __ballot_sync(m, dropped);
+  const unsigned b_bad = __ballot_sync(m, we_end && before <= 0);  // the reference's unsigned counter would wrap
+  if ((threadIdx.x & 31) == __ffs(m) - 1) {
+    if (b_end) atomicAdd(&g->n_we_end, static_cast<unsigned long long>(__popc(b_end)));
+    if (b_start) atomicAdd(&g->n_we_start, static_cast<unsigned long long>(__popc(b_start)));
+    if (b_drop) atomicAdd(&g->n_dropped, static_cast<unsigned long long>(__popc(b_drop)));
+    if (b_bad) atomicOr(&g->bad, BAD_WE_END);
   }
   eff[i] = e;
   scan_in[i] = (e && is_switch(t)) ? i + 1 : 0;
@@ -184,31 +198,32 @@ __global__ void k_sl_entry_counts(const hbtgpu_cs_event* __restrict__ ev, uint32
 
 __global__ void k_sl_entries(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
                              const uint32_t* __restrict__ next, const uint32_t* __restrict__ ecnt,
-                             const uint32_t* __restrict__ eoff, uint64_t* __restrict__ ekey, uint64_t* __restrict__ eval) {
+                             const uint32_t* __restrict__ eoff, int pos_bits, uint64_t* __restrict__ ekey,
+                             uint64_t* __restrict__ eval) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n || ecnt[i] == 0) return;
   const uint64_t tag = ev[i].tag;
   const uint32_t o = eoff[i];
   const uint32_t kind = ev[i].type == EV_CREATE ? K_CREATE : K_IN;
-  ekey[o] = (tag << 32) | rank[i];
+  ekey[o] = (tag << pos_bits) | rank[i];
   eval[o] = (static_cast<uint64_t>(i) << 2) | kind;
   if (ecnt[i] == 2) {
-    ekey[o + 1] = (tag << 32) | rank[next[i]];
+    ekey[o + 1] = (tag << pos_bits) | rank[next[i]];
     eval[o + 1] = (static_cast<uint64_t>(i) << 2) | K_PARK;
   }
 }
 
 // (4) one thread per thread id: walk its events in merge order
-__global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __restrict__ eval, uint32_t n_entries,
+__global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __restrict__ eval, uint32_t n_entries, int pos_bits,
                           const uint32_t* __restrict__ rank, const uint32_t* __restrict__ epoch, uint8_t* __restrict__ cf,
                           uint32_t* __restrict__ t_create /* [n_tags][2]: event that created T[v][k] */) {
   const uint32_t e0 = blockIdx.x * blockDim.x + threadIdx.x;
   if (e0 >= n_entries) return;
-  const uint32_t v = static_cast<uint32_t>(ekey[e0] >> 32);
-  if (e0 > 0 && static_cast<uint32_t>(ekey[e0 - 1] >> 32) == v) return;  // not the first entry of v
+  const uint32_t v = static_cast<uint32_t>(ekey[e0] >> pos_bits);
+  if (e0 > 0 && static_cast<uint32_t>(ekey[e0 - 1] >> pos_bits) == v) return;  // not the first entry of v
   bool ex1 = false, ln1 = false, ex0 = false, ln0 = false;
   uint32_t cur_epoch = 0;
-  for (uint32_t e = e0; e < n_entries && static_cast<uint32_t>(ekey[e] >> 32) == v; ++e) {
+  for (uint32_t e = e0; e < n_entries && static_cast<uint32_t>(ekey[e] >> pos_bits) == v; ++e) {
     const uint32_t kind = static_cast<uint32_t>(eval[e] & 3), i = static_cast<uint32_t>(eval[e] >> 2);
     const uint32_t ep = epoch[rank[i]];  // (a parking switch-out is in its switch-in's epoch)
     if (ep != cur_epoch) {               // resetState_, :636-652: dormant lists cleared
@@ -248,21 +263,32 @@ __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __r
 __global__ void k_sl_firsts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
                             const uint8_t* __restrict__ eff, const uint8_t* __restrict__ cf, Globals* g) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || !eff[i]) return;
-  const uint32_t t = ev[i].type, p = rank[i];
-  const uint8_t f = cf[i];
-  if (t == EV_OUT_PREEMPT || t == EV_OUT_YIELD) atomicMin(&g->e_first[1], p);
-  else if (t == EV_CREATE) {
-    atomicMin(&g->e_first[1], p);  // parent of {v} known (exists already when this one only burns an id)
-    if (ev[i].tag == 0) atomicMin(&g->a_first[1], p);
-  } else if (t == EV_IN) {
-    if (ev[i].tag == 0) {
-      const uint32_t k = (f & CF_KNOWN) ? 1 : 0;
-      atomicMin(&g->a_first[k], p);
-      atomicMin(&g->e_first[k], p);
-    } else if (f & CF_T0) {
-      atomicMin(&g->e_first[0], p);
+  uint32_t e0 = NOIDX, e1 = NOIDX, a0 = NOIDX, a1 = NOIDX;
+  if (i < n && eff[i]) {
+    const uint32_t t = ev[i].type, p = rank[i];
+    const uint8_t f = cf[i];
+    if (t == EV_OUT_PREEMPT || t == EV_OUT_YIELD) e1 = p;
+    else if (t == EV_CREATE) {
+      e1 = p;  // parent of {v} known (exists already when this one only burns an id)
+      if (ev[i].tag == 0) a1 = p;
+    } else if (t == EV_IN) {
+      if (ev[i].tag == 0) {
+        if (f & CF_KNOWN) a1 = e1 = p;
+        else a0 = e0 = p;
+      } else if (f & CF_T0) {
+        e0 = p;
+      }
     }
+  }
+  e0 = __reduce_min_sync(0xffffffffu, e0);
+  e1 = __reduce_min_sync(0xffffffffu, e1);
+  a0 = __reduce_min_sync(0xffffffffu, a0);
+  a1 = __reduce_min_sync(0xffffffffu, a1);
+  if ((threadIdx.x & 31) == 0) {
+    if (e0 != NOIDX) atomicMin(&g->e_first[0], e0);
+    if (e1 != NOIDX) atomicMin(&g->e_first[1], e1);
+    if (a0 != NOIDX) atomicMin(&g->a_first[0], a0);
+    if (a1 != NOIDX) atomicMin(&g->a_first[1], a1);
   }
 }
 
@@ -325,21 +351,42 @@ __global__ void k_sl_slice_flags(const hbtgpu_cs_event* __restrict__ ev, uint32_
                                  unsigned long long* __restrict__ st_in, unsigned long long* __restrict__ st_out,
                                  Globals* g) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
   uint32_t fl = 0;
-  if (eff[i] && is_switch(ev[i].type)) {
-    atomicAdd(&st_in[state_slot(ev[i], cf[i])], 1ull);  // markSwitchIn, :231-241
+  uint32_t in_slot = NOIDX, out_slot = NOIDX;
+  uint64_t dur = 0;
+  if (i < n && eff[i] && is_switch(ev[i].type)) {
+    in_slot = state_slot(ev[i], cf[i]);  // markSwitchIn, :231-241
     const uint32_t r = prev[i];
     if (r != NOIDX) {
-      const uint64_t dur = ev[i].tstamp - ev[r].tstamp;
-      const uint32_t slot = state_slot(ev[r], cf[r]);
-      if (dur) atomicAdd(&st_cum[slot], static_cast<unsigned long long>(dur));  // markSwitchOut, :243-252
-      atomicAdd(&st_out[slot], 1ull);
-      atomicAdd(&g->n_completed, 1ull);
-      fl = dur != 0;  // completeSlice_ drops slices of no duration, :545-554
+      dur = ev[i].tstamp - ev[r].tstamp;
+      out_slot = state_slot(ev[r], cf[r]);  // markSwitchOut, :243-252
+      fl = dur != 0;                        // completeSlice_ drops slices of no duration, :545-554
     }
   }
-  sflag[i] = fl;
+  if (i < n) sflag[i] = fl;
+  // The empty stack and tid 0 take half of all updates: one atomic per warp for those four slots,
+  // one per event for the thread states (spread over the table).
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (uint32_t s = 0; s < 4; ++s) {
+    const unsigned b_in = __ballot_sync(0xffffffffu, in_slot == s), b_out = __ballot_sync(0xffffffffu, out_slot == s);
+    if (b_out) {
+      uint64_t d = out_slot == s ? dur : 0;
+      for (int o = 16; o; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+      if (lane == 0) {
+        if (d) atomicAdd(&st_cum[s], static_cast<unsigned long long>(d));
+        atomicAdd(&st_out[s], static_cast<unsigned long long>(__popc(b_out)));
+      }
+    }
+    if (b_in && lane == 0) atomicAdd(&st_in[s], static_cast<unsigned long long>(__popc(b_in)));
+  }
+  if (in_slot != NOIDX && in_slot >= 4) atomicAdd(&st_in[in_slot], 1ull);
+  if (out_slot != NOIDX && out_slot >= 4) {
+    if (dur) atomicAdd(&st_cum[out_slot], static_cast<unsigned long long>(dur));
+    atomicAdd(&st_out[out_slot], 1ull);
+  }
+  const unsigned b_done = __ballot_sync(0xffffffffu, out_slot != NOIDX);
+  if (b_done && lane == 0) atomicAdd(&g->n_completed, static_cast<unsigned long long>(__popc(b_done)));
 }
 
 // (6b) the slices, unit after unit (the exclusive sum of the flags is their place)
@@ -369,10 +416,11 @@ __global__ void k_sl_unit_counts(const uint64_t* __restrict__ ub, uint32_t n_uni
   slice_begin[u] = b < n ? soff[b] : (n ? soff[n - 1] + sflag[n - 1] : 0);
 }
 
-// (7) the stack table: one entry per state that exists
+// (7) the stack table: one entry per state that exists, ordered by id (two passes around a scan)
 __global__ void k_sl_stacks(uint32_t n_tags, Ids ids, const unsigned long long* __restrict__ st_cum,
                             const unsigned long long* __restrict__ st_in, const unsigned long long* __restrict__ st_out,
-                            hbtgpu_stack_stats* __restrict__ out, unsigned int* __restrict__ n_out) {
+                            uint32_t* __restrict__ id_flag, const uint32_t* __restrict__ id_pos,
+                            hbtgpu_stack_stats* __restrict__ out) {
   const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
   if (slot >= 4 + 2 * n_tags) return;
   const uint32_t k = slot & 1;
@@ -395,6 +443,10 @@ __global__ void k_sl_stacks(uint32_t n_tags, Ids ids, const unsigned long long* 
     tag = v;
     nset = 1;
   }
+  if (id_pos == nullptr) {  // first pass: which ids belong to a state (creations of existing stacks burn ids)
+    id_flag[id] = 1;
+    return;
+  }
   hbtgpu_stack_stats s;
   memset(&s, 0, sizeof(s));
   s.stack_id = id;
@@ -406,7 +458,7 @@ __global__ void k_sl_stacks(uint32_t n_tags, Ids ids, const unsigned long long* 
   s.cum_active_time = st_cum[slot];
   s.num_swins = st_in[slot];
   s.num_swouts = st_out[slot];
-  out[atomicAdd(n_out, 1u)] = s;
+  out[id_pos[id]] = s;  // in stack_id order
 }
 
 }  // namespace
@@ -426,6 +478,8 @@ struct hbtgpu_slicer_ctx {
   uint64_t* d_slice_begin = nullptr;
   std::vector<uint64_t> slice_begin;
   std::vector<hbtgpu_stack_stats> stacks;
+  hbtgpu_stack_stats* d_stacks = nullptr;
+  uint64_t n_stacks = 0;
   bool have = false;
 };
 
@@ -518,7 +572,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   cub::DeviceScan::InclusiveSum(nullptr, tmp_scan, static_cast<int32_t*>(nullptr), static_cast<int32_t*>(nullptr), static_cast<int>(N), st);
   cub::DeviceScan::ExclusiveScan(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), MaxOp(), 0u, static_cast<int>(N), st);
   tmp_scan = std::max(tmp_scan, t2);
-  cub::DeviceScan::ExclusiveSum(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), st);
+  cub::DeviceScan::ExclusiveSum(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N64 + 8), st);
   tmp_scan = std::max(tmp_scan, t2);
   const size_t tmp_bytes = std::max(std::max(tmp_sort, tmp_sort2), tmp_scan) + 256;
   // The thread table is sized once the largest tag is known; everything else now.
@@ -533,6 +587,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8);  // entries + sorted
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);               // idcnt, idbase, sflag, soff
   add(n1, 32); add(n_units + 2, 8);                             // slices, slice_begin
+  add(n1 + 8, 4); add(n1 + 8, 4);                               // id flags, id positions
   add(1, sizeof(Globals)); add(4, 4); add(tmp_bytes, 1);
   const size_t fixed_need = need;
   if (c->arena_cap < fixed_need) {
@@ -574,6 +629,8 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   auto* d_soff = carve<uint32_t>(c, n1);
   auto* d_slices = carve<hbtgpu_slice>(c, n1);
   auto* d_slice_begin = carve<uint64_t>(c, n_units + 2);
+  auto* d_idflag = carve<uint32_t>(c, n1 + 8);
+  auto* d_idpos = carve<uint32_t>(c, n1 + 8);
   auto* d_g = carve<Globals>(c, 1);
   auto* d_small = carve<unsigned int>(c, 4);
   auto* d_tmp = carve<char>(c, tmp_bytes);
@@ -598,7 +655,11 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     size_t t = tmp_bytes;
     k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of);
     k_sl_prepare<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_key, d_val, d_g);
-    cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key, d_key_s, d_val, d_order, static_cast<int>(N), 0, 64, st);
+    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    int ts_bits = 1;  // radix passes only over the bits the timestamps use
+    while (ts_bits < 64 && (gh.max_ts >> ts_bits) != 0) ++ts_bits;
+    cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key, d_key_s, d_val, d_order, static_cast<int>(N), 0, ts_bits, st);
     k_sl_gather<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_rank, d_delta, d_start);
     t = tmp_bytes;
     cub::DeviceScan::InclusiveSum(d_tmp, t, d_delta, d_depth, static_cast<int>(N), st);
@@ -669,10 +730,15 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     SK(cudaStreamSynchronize(st));
     const uint32_t n_entries = last_off + last_cnt;
     if (n_entries) {
-      k_sl_entries<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_next, d_ecnt, d_eoff, d_ekey, d_eval);
+      int pos_bits = 1, tag_bits = 1;  // key = tag << pos_bits | merge position
+      while ((static_cast<uint64_t>(N) >> pos_bits) != 0) ++pos_bits;
+      while ((static_cast<uint64_t>(gh.max_tag) >> tag_bits) != 0) ++tag_bits;
+      k_sl_entries<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_next, d_ecnt, d_eoff, pos_bits, d_ekey, d_eval);
       t = tmp_bytes;
-      cub::DeviceRadixSort::SortPairs(d_tmp, t, d_ekey, d_ekey_s, d_eval, d_eval_s, static_cast<int>(n_entries), 0, 64, st);
-      k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, d_rank, d_epoch, d_cf, d_tcreate);
+      cub::DeviceRadixSort::SortPairs(d_tmp, t, d_ekey, d_ekey_s, d_eval, d_eval_s, static_cast<int>(n_entries), 0,
+                                      pos_bits + tag_bits, st);
+      k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, pos_bits, d_rank, d_epoch, d_cf,
+                                                        d_tcreate);
     }
     k_sl_firsts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_eff, d_cf, d_g);
     k_sl_id_counts<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_eff, d_cf, d_g, d_idcnt);
@@ -705,12 +771,21 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     cub::DeviceScan::ExclusiveSum(d_tmp, t, d_sflag, d_soff, static_cast<int>(N), st);
     k_sl_emit<<<blocks(N), 256, 0, st>>>(ev, N, d_prev, d_cf, d_sflag, d_soff, ids, d_slices);
     k_sl_unit_counts<<<blocks(n_units + 1), 256, 0, st>>>(d_ub, n_units, N, d_soff, d_sflag, d_slice_begin);
-    k_sl_stacks<<<blocks(n_slots), 256, 0, st>>>(n_tags, ids, d_cum, d_in, d_out, d_stacks, d_small);
+    // ids handed out: the last event's base + count; flag the ones that belong to a state, scan, place
+    SK(cudaMemcpyAsync(&small[1], d_idbase + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+    SK(cudaMemcpyAsync(&small[2], d_idcnt + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    const uint32_t n_ids = small[1] + small[2];
+    SK(cudaMemsetAsync(d_idflag, 0, (static_cast<size_t>(n_ids) + 1) * 4, st));
+    k_sl_stacks<<<blocks(n_slots), 256, 0, st>>>(n_tags, ids, d_cum, d_in, d_out, d_idflag, nullptr, d_stacks);
+    t = tmp_bytes;
+    cub::DeviceScan::ExclusiveSum(d_tmp, t, d_idflag, d_idpos, static_cast<int>(n_ids + 1), st);
+    k_sl_stacks<<<blocks(n_slots), 256, 0, st>>>(n_tags, ids, d_cum, d_in, d_out, d_idflag, d_idpos, d_stacks);
+    SK(cudaMemcpyAsync(&small[0], d_idpos + n_ids, 4, cudaMemcpyDeviceToHost, st));  // number of states
     SK(cudaGetLastError());
     SK(cudaEventRecord(c->ev1, st));
     SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
     SK(cudaMemcpyAsync(c->slice_begin.data(), d_slice_begin, (n_units + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
-    SK(cudaMemcpyAsync(small, d_small, sizeof(small), cudaMemcpyDeviceToHost, st));
     uint32_t last_idx = 0;
     SK(cudaMemcpyAsync(&last_idx, d_order + (N - 1), 4, cudaMemcpyDeviceToHost, st));
     SK(cudaStreamSynchronize(st));
@@ -726,12 +801,9 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     c->last_ms = 0.f;
   }
   (void)total_slices;
-  c->stacks.resize(small[0]);
-  if (small[0]) {
-    SK(cudaMemcpy(c->stacks.data(), d_stacks, small[0] * sizeof(hbtgpu_stack_stats), cudaMemcpyDeviceToHost));
-    std::sort(c->stacks.begin(), c->stacks.end(),
-              [](const hbtgpu_stack_stats& a, const hbtgpu_stack_stats& b) { return a.stack_id < b.stack_id; });
-  }
+  c->n_stacks = small[0];
+  c->d_stacks = d_stacks;
+  c->stacks.clear();  // fetched when asked for
   if (stats) {
     memset(stats, 0, sizeof(*stats));
     stats->num_processed = N;  // every event is processed once (no event is older than its predecessor)
@@ -742,7 +814,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   }
   if (n_slices)
     for (uint32_t u = 0; u < n_units; ++u) n_slices[u] = c->slice_begin[u + 1] - c->slice_begin[u];
-  if (n_stacks) *n_stacks = c->stacks.size();
+  if (n_stacks) *n_stacks = c->n_stacks;
   c->d_slices = d_slices;
   c->d_slice_begin = d_slice_begin;
   c->have = true;
@@ -763,8 +835,9 @@ int hbtgpu_slicer_get_slices(hbtgpu_slicer_ctx* c, uint32_t unit, hbtgpu_slice* 
 int hbtgpu_slicer_get_stacks(hbtgpu_slicer_ctx* c, hbtgpu_stack_stats* out, uint64_t cap) {
   if (!c || !out) return -EINVAL;
   if (!c->have) return sfail(c, -EINVAL, "no results: call hbtgpu_slicer_run first");
-  if (cap < c->stacks.size()) return sfail(c, -ENOSPC, "%zu stacks, room for %llu", c->stacks.size(), (unsigned long long)cap);
-  if (!c->stacks.empty()) memcpy(out, c->stacks.data(), c->stacks.size() * sizeof(hbtgpu_stack_stats));
+  if (cap < c->n_stacks) return sfail(c, -ENOSPC, "%llu stacks, room for %llu", (unsigned long long)c->n_stacks, (unsigned long long)cap);
+  SK(cudaSetDevice(c->device));
+  if (c->n_stacks) SK(cudaMemcpy(out, c->d_stacks, c->n_stacks * sizeof(hbtgpu_stack_stats), cudaMemcpyDeviceToHost));
   return 0;
 }
 
