@@ -1,7 +1,7 @@
 """The stages in one line: thread-switch ring images -> tagstack events (GPU, f2),
-count-sample ring images -> count rows (GPU, the hot path), events -> slices (the reference's
-Slicer: the one stage without a GPU form yet, run here from oracle/_ref as a stand-in), count
-rows x slices -> per-interval slices (GPU, f3) -> frequencies + interval x bin matrix (GPU, f1).
+count-sample ring images -> count rows (GPU, the hot path), events -> slices (GPU, f3 Slicer side;
+checked here against the reference's own Slicer from oracle/_ref), count rows x slices ->
+per-interval slices (GPU, f3) -> frequencies + interval x bin matrix (GPU, f1).
 Checks that the formats connect (16-byte events, n+2-word rows, 32-byte slices pass from stage to
 stage untouched) and that the GPU stages agree with the CPU checkers on realistic data rather
 than on hand-made vectors."""
@@ -31,8 +31,16 @@ def test_images_to_bins():
     order = np.lexsort((merged["comp_unit_id"], merged["tstamp"]))
     sl = po.slicer_run("reference", merged[order], n_cpus)
     assert sl["rc"] == 0 and sl["stats"]["num_slices_completed"] > 1000 * n_cpus
-    slices = sl["slices"]
     assert sl["stats"]["num_error_start"] > 0               # the LOST records made it through as resets
+    gsl = gs.Slicer(0)
+    try:
+        got_sl = gsl.run(events)
+    finally:
+        gsl.close()
+    assert got_sl["stats"] == sl["stats"]
+    for u in range(n_cpus):
+        assert po.slices_as_tuples(got_sl["slices"][u]) == po.slices_as_tuples(sl["slices"][u]), u
+    slices = got_sl["slices"]
 
     # count samples over the same stretch of time: 100 us apart, 4-event group
     spec, streams = synth.capture(1, n_cpus, n_samples=280)
