@@ -24,6 +24,8 @@
 //     write / registerConsumerMark / getMark / numActiveSlices / numProcessedSlices /
 //     discardConsumed / makeIntervalIntersectingSlices / consumeSlices          same names
 //   TraceMonitor::releaseCountData_ row loop  mon/TraceMonitor.cpp:52-96   releaseCountRows (all CPUs, one GPU call)
+//   tagstack::slice::Slicer       tagstack/Slicer.h:302-869  Slicer (a window of level-0 events per call)
+//     getStats / getTagStackStatsDump / getLastTimeStamp / getSlices         same names
 //
 // Error conventions follow the reference: the hot path returns negative errno in ssize_t
 // (-ENODATA drained, -EPERM bad record / time regression), argument and environment errors
@@ -548,6 +550,71 @@ class IntervalSlicer {
   size_t capacity_ = 0, drop_if_full_ = 0;
   size_t num_processed_slices_ = 0, num_dropped_ = 0;
   std::map<std::string, size_t> marks_;
+};
+
+// ---- tagstack events -> slices -----------------------------------------------------------------
+
+using SlicerStats = hbtgpu_slicer_stats;    // Slicer.h:276-285
+using TagStackStats = hbtgpu_stack_stats;   // Slicer.h:160-193 (stack = tags[0 .. num_set_tags), known_num_levels)
+
+// tagstack::slice::Slicer for the events the thread-switch generators emit (level 0).  The
+// reference pulls events from a merged stream until stop_ts (processNext); here a window of
+// per-CPU events is handed over at once and the slices are written to the per-CPU producers
+// (anything with write(const Slice&), e.g. IntervalSlicer) exactly as completeSlice_ would
+// (Slicer.h:529-558).  Each window is a Slicer started empty.
+template <class TSlices>
+class Slicer {
+ public:
+  using TGroupedSlices = std::vector<std::shared_ptr<TSlices>>;  // GroupedSlices<TSlices>, Slicer.h:273-274
+  explicit Slicer(std::shared_ptr<TGroupedSlices> grouped_slices, int device = 0) : grouped_slices_{grouped_slices} {
+    if (!grouped_slices || grouped_slices->empty()) throw std::invalid_argument("grouped_slices must be populated");
+    ctx_ = hbtgpu_slicer_create(device);
+    if (!ctx_) throw std::runtime_error("hbtgpu_slicer_create failed: no CUDA device (there is no CPU path)");
+  }
+  ~Slicer() { hbtgpu_slicer_destroy(ctx_); }
+  Slicer(const Slicer&) = delete;
+  Slicer& operator=(const Slicer&) = delete;
+
+  // Returns the number of processed events.  events[cpu] = that CPU's events in stream order.
+  size_t processWindow(const std::vector<std::vector<Event>>& events) {
+    if (events.size() != grouped_slices_->size()) throw std::invalid_argument("one event vector per slice producer");
+    std::vector<uint64_t> begin(events.size() + 1, 0);
+    std::vector<Event> all;
+    for (size_t u = 0; u < events.size(); ++u) {
+      all.insert(all.end(), events[u].begin(), events[u].end());
+      begin[u + 1] = all.size();
+    }
+    std::vector<uint64_t> n_slices(events.size());
+    uint64_t n_stacks = 0;
+    const int rc = hbtgpu_slicer_run(ctx_, all.data(), begin.data(), static_cast<uint32_t>(events.size()), 0, &stats_,
+                                     n_slices.data(), &n_stacks, &last_ts_);
+    if (rc != 0) throw std::runtime_error(hbtgpu_slicer_last_error(ctx_));
+    for (size_t u = 0; u < events.size(); ++u) {
+      std::vector<Slice> out(n_slices[u]);
+      if (!out.empty() && hbtgpu_slicer_get_slices(ctx_, static_cast<uint32_t>(u), out.data(), out.size()) != 0)
+        throw std::runtime_error(hbtgpu_slicer_last_error(ctx_));
+      for (const auto& s : out)
+        if ((*grouped_slices_)[u]->write(s) < 0)
+          throw std::runtime_error("Buffer back-pressure when generating slices is not yet supported.");  // :551-553
+    }
+    stacks_.resize(n_stacks);
+    if (n_stacks && hbtgpu_slicer_get_stacks(ctx_, stacks_.data(), n_stacks) != 0)
+      throw std::runtime_error(hbtgpu_slicer_last_error(ctx_));
+    return stats_.num_processed;
+  }
+
+  auto getSlices() { return grouped_slices_; }
+  TimeStamp getLastTimeStamp() const { return last_ts_; }
+  SlicerStats getStats() const { return stats_; }
+  // by stack_id, as the std::map of the reference iterates
+  const std::vector<TagStackStats>& getTagStackStatsDump() const { return stacks_; }
+
+ private:
+  hbtgpu_slicer_ctx* ctx_ = nullptr;
+  std::shared_ptr<TGroupedSlices> grouped_slices_;
+  SlicerStats stats_{};
+  std::vector<TagStackStats> stacks_;
+  TimeStamp last_ts_ = 0;
 };
 
 }  // namespace hbtgpu_shim

@@ -250,6 +250,43 @@ int main() {
       EXPECT(islicer.getMark("counts") == 5 && islicer.numProcessedSlices() == 5 && islicer.numActiveSlices() == 5);
     }
   }
+
+  // ---- tagstack::slice::Slicer, after TagStackSlice.1LevelsOnePhaseWithThreadSwOut -----------
+  // (hbt/src/tagstack/tests/SlicerTest.cpp:65-160), slices written into an IntervalSlicer as
+  // TraceMonitor wires them, then one count interval taken out of it
+  {
+    auto mk = [](uint64_t ts, uint8_t type, uint32_t tag) {
+      Event e{};
+      e.tstamp = ts;
+      e.type = type;
+      e.level = 0;
+      e.comp_unit_id = 0;
+      e.tag = tag;
+      return e;
+    };
+    const uint8_t kIn = 4, kOutPreempt = 5;
+    std::vector<std::vector<Event>> events(1);
+    events[0] = {mk(20, kIn, 2), mk(30, kOutPreempt, ~0u), mk(30, kIn, 4), mk(50, kOutPreempt, ~0u),
+                 mk(60, kIn, 1), mk(80, kOutPreempt, ~0u)};
+    auto grouped = std::make_shared<Slicer<IntervalSlicer>::TGroupedSlices>();
+    grouped->push_back(std::make_shared<IntervalSlicer>(64, 0));
+    Slicer<IntervalSlicer> slicer{grouped};
+    EXPECT(slicer.processWindow(events) == 6);
+    const auto& st = slicer.getTagStackStatsDump();
+    EXPECT(st.size() == 5);                                                       // :97
+    EXPECT(st[0].num_set_tags == 0 && st[0].known_num_levels == 0);               // Stack(0, false), id 0
+    EXPECT(st[1].stack_id == 1 && st[1].tags[0] == 2 && st[1].known_num_levels == 0);
+    EXPECT(st[2].stack_id == 2 && st[2].num_set_tags == 0 && st[2].known_num_levels == 1);
+    EXPECT(st[3].stack_id == 3 && st[3].tags[0] == 4 && st[4].stack_id == 4 && st[4].tags[0] == 1);
+    EXPECT(slicer.getStats().num_slices_completed == 5 && slicer.getLastTimeStamp() == 80);
+    auto& islicer = *(*slicer.getSlices())[0];
+    EXPECT(islicer.numActiveSlices() == 4);                                       // :108
+    auto [s, n] = islicer.makeIntervalIntersectingSlices(0, 25, 30, true, true);  // [25, 55)
+    EXPECT(s != nullptr && s->size() == 3 && n == 2);
+    EXPECT(s->at(0) == makeSlice(25, 5, 1, TransitionType::Analysis, TransitionType::ThreadPreempted));
+    EXPECT(s->at(1) == makeSlice(30, 20, 3, TransitionType::ThreadYield, TransitionType::ThreadPreempted));
+    EXPECT(s->at(2) == makeSlice(50, 5, 2, TransitionType::ThreadPreempted, TransitionType::Analysis));
+  }
   std::puts("SHIM OK");
   return 0;
 }
