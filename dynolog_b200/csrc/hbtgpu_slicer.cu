@@ -52,13 +52,17 @@ constexpr uint8_t TT_PREEMPTED = 2, TT_YIELD = 3;  // Slice::TransitionType, Sli
 constexpr uint32_t NA = 0xffffffffu;
 constexpr uint32_t NOIDX = 0xffffffffu;
 constexpr uint64_t NONE64 = ~0ull;
+// The state a unit was left in by the previous window travels as one extra event in front of the
+// unit's events (level VIRT_K0 / VIRT_K1: the state has unknown / known levels; type DESTROY = none).
+constexpr uint8_t VIRT_K0 = 0xee, VIRT_K1 = 0xef;
+__device__ __forceinline__ bool is_virtual(const hbtgpu_cs_event& e) { return e.level >= VIRT_K0 && e.level <= VIRT_K1; }
 
 enum : uint32_t {  // why a window is outside the parallel form
   BAD_TYPE = 1, BAD_LEVEL = 2, BAD_ORDER = 4, BAD_UNIT = 8, BAD_TAG = 16, BAD_DOUBLE_IN = 32, BAD_WE_END = 64
 };
 // per-event creation flags (step 4)
 enum : uint8_t { CF_T1 = 1, CF_BURN = 2, CF_T0 = 4, CF_PICK_T1 = 8, CF_KNOWN = 16, CF_PREV = 32 };
-enum : uint32_t { K_CREATE = 0, K_IN = 1, K_PARK = 2 };
+enum : uint32_t { K_CREATE = 0, K_IN = 1, K_PARK = 2, K_CARRIED = 3 };
 
 // small device-wide numbers
 struct Globals {
@@ -68,6 +72,9 @@ struct Globals {
   unsigned long long n_dropped, n_we_start, n_we_end, n_completed;
   unsigned int max_tag;
   unsigned long long max_ts;
+  int depth0;                 // write-error depth the window starts with
+  unsigned long long last_ts0;  // last timestamp of the previous window
+  unsigned int have;          // bit k: E[k] exists already, bit 2 + k: T[0][k]
 };
 
 struct MaxOp {
@@ -83,20 +90,25 @@ __global__ void k_sl_prepare(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const hbtgpu_cs_event e = ev[i];
-  key[i] = e.tstamp;
+  const bool virt = is_virtual(e);
+  key[i] = virt ? 0 : e.tstamp;  // carried states sort in front of the window
   val[i] = i;
   uint32_t bad = 0;
   const uint32_t u = unit_of[i];
   if (e.comp_unit_id != u) bad |= BAD_UNIT;
-  if (e.type > EV_WE_END || e.type == EV_START || e.type == EV_END) bad |= BAD_TYPE;
-  if (e.type >= EV_CREATE && e.type <= EV_OUT_YIELD && e.level != 0) bad |= BAD_LEVEL;
-  if ((e.type == EV_CREATE || e.type == EV_IN) && e.tag == NA) bad |= BAD_TAG;
-  if (i > ub[u] && ev[i - 1].tstamp > e.tstamp) bad |= BAD_ORDER;
+  if (!virt) {
+    if (e.type > EV_WE_END || e.type == EV_START || e.type == EV_END) bad |= BAD_TYPE;
+    if (e.type >= EV_CREATE && e.type <= EV_OUT_YIELD && e.level != 0) bad |= BAD_LEVEL;
+    if ((e.type == EV_CREATE || e.type == EV_IN) && e.tag == NA) bad |= BAD_TAG;
+    // slot ub[u] holds the carried state; the unit's events must not go back in time, nor behind
+    // the previous window's last event
+    if (i > ub[u] + 1 ? ev[i - 1].tstamp > e.tstamp : e.tstamp < g->last_ts0) bad |= BAD_ORDER;
+  }
   // (threads past the end have left: aggregate over the lanes that are here)
   const unsigned m = __activemask();
   const uint32_t wbad = __reduce_or_sync(m, bad);
   const uint32_t wmax = __reduce_max_sync(m, ((e.type == EV_CREATE || e.type == EV_IN) && e.tag != NA) ? e.tag : 0u);
-  uint64_t wts = e.tstamp;  // (a unit's last event would do, but the check above may fail)
+  uint64_t wts = virt ? 0 : e.tstamp;  // (a unit's last event would do, but the check above may fail)
   for (int o = 16; o; o >>= 1) {
     const uint64_t other = __shfl_xor_sync(m, wts, o);
     if ((m >> ((threadIdx.x & 31) ^ o)) & 1u) wts = max(wts, other);
@@ -132,10 +144,11 @@ __global__ void k_sl_effective(const hbtgpu_cs_event* __restrict__ ev, uint32_t 
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t t = ev[i].type, p = rank[i];
-  const int32_t before = depth_incl[p] - delta[p];  // num_active_write_errors_ as the event finds it
+  const bool virt = is_virtual(ev[i]);
+  const int32_t before = g->depth0 + depth_incl[p] - delta[p];  // num_active_write_errors_ as the event finds it
   const bool we_end = t == EV_WE_END, we_start = t == EV_WE_START;
-  const bool dropped = !we_end && !we_start && before > 0;  // handleWriteErrors_, Slicer.h:691-701
-  const bool e = !we_end && !we_start && !dropped;
+  const bool dropped = !virt && !we_end && !we_start && before > 0;  // handleWriteErrors_, Slicer.h:691-701
+  const bool e = virt ? is_switch(t) : (!we_end && !we_start && !dropped);
   const unsigned m = __activemask();
   const unsigned b_end = __ballot_sync(m, we_end), b_start = __ballot_sync(m, we_start), b_drop = __ballot_sync(m, dropped);
   const unsigned b_bad = __ballot_sync(m, we_end && before <= 0);  // the reference's unsigned counter would wrap
@@ -175,6 +188,7 @@ __global__ void k_sl_links(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, c
       }
     }
   }
+  if (is_virtual(ev[i]) && ev[i].level == VIRT_K1) f |= ev[i].tag == 0 ? CF_KNOWN : CF_PICK_T1;
   prev[i] = pv;
   cf[i] = f;
 }
@@ -204,7 +218,7 @@ __global__ void k_sl_entries(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
   if (i >= n || ecnt[i] == 0) return;
   const uint64_t tag = ev[i].tag;
   const uint32_t o = eoff[i];
-  const uint32_t kind = ev[i].type == EV_CREATE ? K_CREATE : K_IN;
+  const uint32_t kind = ev[i].type == EV_CREATE ? K_CREATE : (is_virtual(ev[i]) ? K_CARRIED : K_IN);
   ekey[o] = (tag << pos_bits) | rank[i];
   eval[o] = (static_cast<uint64_t>(i) << 2) | kind;
   if (ecnt[i] == 2) {
@@ -216,13 +230,15 @@ __global__ void k_sl_entries(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
 // (4) one thread per thread id: walk its events in merge order
 __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __restrict__ eval, uint32_t n_entries, int pos_bits,
                           const uint32_t* __restrict__ rank, const uint32_t* __restrict__ epoch, uint8_t* __restrict__ cf,
-                          uint32_t* __restrict__ t_create /* [n_tags][2]: event that created T[v][k] */) {
+                          uint32_t* __restrict__ t_create /* [n_tags][2]: event that created T[v][k] */,
+                          uint8_t* __restrict__ pt_flags /* [n_tags][2]: bit 0 exists, bit 1 dormant */,
+                          uint32_t* __restrict__ last_epoch /* [n_tags] */) {
   const uint32_t e0 = blockIdx.x * blockDim.x + threadIdx.x;
   if (e0 >= n_entries) return;
   const uint32_t v = static_cast<uint32_t>(ekey[e0] >> pos_bits);
   if (e0 > 0 && static_cast<uint32_t>(ekey[e0 - 1] >> pos_bits) == v) return;  // not the first entry of v
-  bool ex1 = false, ln1 = false, ex0 = false, ln0 = false;
-  uint32_t cur_epoch = 0;
+  bool ex1 = pt_flags[2 * v + 1] & 1, ln1 = pt_flags[2 * v + 1] & 2, ex0 = pt_flags[2 * v] & 1, ln0 = pt_flags[2 * v] & 2;
+  uint32_t cur_epoch = 0;  // what was carried over is valid until the window's first reset
   for (uint32_t e = e0; e < n_entries && static_cast<uint32_t>(ekey[e] >> pos_bits) == v; ++e) {
     const uint32_t kind = static_cast<uint32_t>(eval[e] & 3), i = static_cast<uint32_t>(eval[e] >> 2);
     const uint32_t ep = epoch[rank[i]];  // (a parking switch-out is in its switch-in's epoch)
@@ -252,11 +268,14 @@ __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __r
         }
         ln0 = false;
       }
-    } else {  // the next switch event on that unit parks the state: handleLastState_, :761-768
+    } else if (kind == K_PARK) {  // the next switch event on that unit parks the state: handleLastState_, :761-768
       if (cf[i] & CF_PICK_T1) ln1 = true;
       else ln0 = true;
-    }
+    }  // K_CARRIED: the state was activated in an earlier window; it is neither created nor unlinked here
   }
+  pt_flags[2 * v + 1] = (ex1 ? 1 : 0) | (ln1 ? 2 : 0);
+  pt_flags[2 * v] = (ex0 ? 1 : 0) | (ln0 ? 2 : 0);
+  last_epoch[v] = cur_epoch;
 }
 
 // (5a) where E[k] and T[0][k] are first needed
@@ -264,7 +283,7 @@ __global__ void k_sl_firsts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, 
                             const uint8_t* __restrict__ eff, const uint8_t* __restrict__ cf, Globals* g) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t e0 = NOIDX, e1 = NOIDX, a0 = NOIDX, a1 = NOIDX;
-  if (i < n && eff[i]) {
+  if (i < n && eff[i] && !is_virtual(ev[i])) {
     const uint32_t t = ev[i].type, p = rank[i];
     const uint8_t f = cf[i];
     if (t == EV_OUT_PREEMPT || t == EV_OUT_YIELD) e1 = p;
@@ -280,6 +299,11 @@ __global__ void k_sl_firsts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, 
       }
     }
   }
+  const unsigned have = g->have;
+  if (have & 1) e0 = NOIDX;
+  if (have & 2) e1 = NOIDX;
+  if (have & 4) a0 = NOIDX;
+  if (have & 8) a1 = NOIDX;
   e0 = __reduce_min_sync(0xffffffffu, e0);
   e1 = __reduce_min_sync(0xffffffffu, e1);
   a0 = __reduce_min_sync(0xffffffffu, a0);
@@ -300,7 +324,7 @@ __global__ void k_sl_id_counts(const hbtgpu_cs_event* __restrict__ ev, const uin
   if (p >= n) return;
   const uint32_t i = order[p];
   uint32_t c = 0;
-  if (eff[i]) {
+  if (eff[i] && !is_virtual(ev[i])) {
     const uint32_t t = ev[i].type;
     const uint8_t f = cf[i];
     if (t == EV_OUT_PREEMPT || t == EV_OUT_YIELD) c = p == g->e_first[1];
@@ -321,16 +345,21 @@ __global__ void k_sl_id_counts(const hbtgpu_cs_event* __restrict__ ev, const uin
 
 // The id of the state event i activated (i: an effective switch event)
 struct Ids {
-  const uint32_t* idbase;    // exclusive sum of idcnt, by merge position
-  const uint32_t* rank;
-  const uint32_t* t_create;  // [n_tags][2]
+  const uint32_t* pt_id;  // [n_tags][2]: id of T[v][k]
   uint64_t e_id[2], a_id[2];
-  uint32_t e_first[2], a_first[2];
-  __device__ __forceinline__ uint64_t thread_state(uint32_t v, uint32_t k) const {
-    const uint32_t p = rank[t_create[2 * v + k]];
-    return static_cast<uint64_t>(idbase[p]) + (p == e_first[k] ? 1u : 0u);  // parent first
-  }
+  __device__ __forceinline__ uint64_t thread_state(uint32_t v, uint32_t k) const { return pt_id[2 * v + k]; }
 };
+
+// ids of the thread states this window created: base of the creating event (+ 1 when the same
+// event created the parent E[k] first)
+__global__ void k_sl_store_ids(uint32_t n_tags, const uint32_t* __restrict__ t_create, const uint32_t* __restrict__ rank,
+                               const uint32_t* __restrict__ idbase, uint32_t id0, const Globals* g,
+                               uint32_t* __restrict__ pt_id) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;  // 2 v + k
+  if (j >= 2 * n_tags || t_create[j] == NOIDX) return;
+  const uint32_t p = rank[t_create[j]];
+  pt_id[j] = id0 + idbase[p] + (p == g->e_first[j & 1] ? 1u : 0u);
+}
 
 // state slots for the statistics: 0,1 = E[k]; 2,3 = T[0][k]; 4 + 2v + k = T[v][k]
 __device__ __forceinline__ uint32_t state_slot(const hbtgpu_cs_event& e, uint8_t f) {
@@ -354,7 +383,7 @@ __global__ void k_sl_slice_flags(const hbtgpu_cs_event* __restrict__ ev, uint32_
   uint32_t fl = 0;
   uint32_t in_slot = NOIDX, out_slot = NOIDX;
   uint64_t dur = 0;
-  if (i < n && eff[i] && is_switch(ev[i].type)) {
+  if (i < n && eff[i] && is_switch(ev[i].type) && !is_virtual(ev[i])) {
     in_slot = state_slot(ev[i], cf[i]);  // markSwitchIn, :231-241
     const uint32_t r = prev[i];
     if (r != NOIDX) {
@@ -417,7 +446,8 @@ __global__ void k_sl_unit_counts(const uint64_t* __restrict__ ub, uint32_t n_uni
 }
 
 // (7) the stack table: one entry per state that exists, ordered by id (two passes around a scan)
-__global__ void k_sl_stacks(uint32_t n_tags, Ids ids, const unsigned long long* __restrict__ st_cum,
+__global__ void k_sl_stacks(uint32_t n_tags, Ids ids, const uint8_t* __restrict__ pt_flags,
+                            const unsigned long long* __restrict__ st_cum,
                             const unsigned long long* __restrict__ st_in, const unsigned long long* __restrict__ st_out,
                             uint32_t* __restrict__ id_flag, const uint32_t* __restrict__ id_pos,
                             hbtgpu_stack_stats* __restrict__ out) {
@@ -427,17 +457,17 @@ __global__ void k_sl_stacks(uint32_t n_tags, Ids ids, const unsigned long long* 
   uint64_t id, parent = NONE64;
   uint32_t tag = NA, nset = 0;
   if (slot < 2) {
-    if (ids.e_first[k] == NOIDX) return;
+    if (ids.e_id[k] == NONE64) return;
     id = ids.e_id[k];
   } else if (slot < 4) {
-    if (ids.a_first[k] == NOIDX) return;
+    if (ids.a_id[k] == NONE64) return;
     id = ids.a_id[k];
     parent = ids.e_id[k];
     tag = 0;
     nset = 1;
   } else {
     const uint32_t v = (slot - 4) >> 1;
-    if (v == 0 || ids.t_create[2 * v + k] == NOIDX) return;
+    if (v == 0 || !(pt_flags[2 * v + k] & 1)) return;
     id = ids.thread_state(v, k);
     parent = ids.e_id[k];
     tag = v;
@@ -461,6 +491,58 @@ __global__ void k_sl_stacks(uint32_t n_tags, Ids ids, const unsigned long long* 
   out[id_pos[id]] = s;  // in stack_id order
 }
 
+// what every unit is left with: the state its last effective switch event activated, unless a
+// reset came after it
+struct Carried {
+  uint64_t tstamp;
+  uint32_t tag;
+  uint8_t type, level, none, pad;
+};
+__global__ void k_sl_final_active(const hbtgpu_cs_event* __restrict__ ev, const uint64_t* __restrict__ ub,
+                                  uint32_t n_units, const uint32_t* __restrict__ rank,
+                                  const uint32_t* __restrict__ epoch, const uint8_t* __restrict__ eff,
+                                  const uint8_t* __restrict__ cf, uint32_t final_epoch, Carried* __restrict__ out) {
+  const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n_units) return;
+  Carried c{0, 0, EV_DESTROY, VIRT_K0, 1, 0};
+  for (uint64_t i = ub[u + 1]; i > ub[u]; --i) {
+    const hbtgpu_cs_event e = ev[i - 1];
+    if (!eff[i - 1] || !is_switch(e.type)) continue;
+    if (epoch[rank[i - 1]] == final_epoch) {
+      const uint8_t f = cf[i - 1];
+      c.tstamp = e.tstamp;
+      c.tag = e.tag;
+      c.type = e.type;
+      // E[1] after a switch-out; T[v][1] / T[0][1] when the switch-in took the known-levels state
+      c.level = (e.type != EV_IN || (e.tag == 0 ? (f & CF_KNOWN) : (f & CF_PICK_T1))) ? VIRT_K1 : VIRT_K0;
+      c.none = 0;
+    }
+    break;
+  }
+  out[u] = c;
+}
+// a reset clears every dormant list, also of threads that had no event after it
+__global__ void k_sl_clear_dormant(uint32_t n_tags, uint32_t final_epoch, const uint32_t* __restrict__ last_epoch,
+                                   uint8_t* __restrict__ pt_flags) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_tags || last_epoch[v] == final_epoch) return;
+  pt_flags[2 * v] &= 1;
+  pt_flags[2 * v + 1] &= 1;
+}
+__global__ void k_sl_put_carried(hbtgpu_cs_event* __restrict__ ev, const uint64_t* __restrict__ ub, uint32_t n_units,
+                                 const Carried* __restrict__ carried) {
+  const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n_units) return;
+  const Carried c = carried[u];
+  hbtgpu_cs_event e;
+  e.tstamp = c.tstamp;
+  e.type = c.none ? EV_DESTROY : c.type;
+  e.level = c.none ? VIRT_K0 : c.level;
+  e.comp_unit_id = static_cast<uint16_t>(u);
+  e.tag = c.tag;
+  ev[ub[u]] = e;
+}
+
 }  // namespace
 
 struct hbtgpu_slicer_ctx {
@@ -469,15 +551,26 @@ struct hbtgpu_slicer_ctx {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   float last_ms = 0.f;
-  char* arena = nullptr;
+  char* arena = nullptr;   // per-run scratch sized by the number of events
   size_t arena_cap = 0, arena_used = 0;
-  char* arena2 = nullptr;
+  char* arena2 = nullptr;  // per-run scratch sized by the number of thread ids / stack ids
   size_t arena2_cap = 0;
-  // results of the last run (device pointers into the arena)
+  // the Slicer's state between windows (HBTGPU_SLICER_CONTINUE)
+  uint8_t* p_flags = nullptr;            // [p_tags][2]: bit 0 exists, bit 1 dormant
+  uint32_t* p_id = nullptr;              // [p_tags][2]
+  unsigned long long *p_cum = nullptr, *p_in = nullptr, *p_out = nullptr;  // [4 + 2 p_tags]
+  uint32_t p_tags = 0;
+  Carried* d_carried = nullptr;
+  uint32_t carried_units = 0;
+  uint64_t e_id[2] = {NONE64, NONE64}, a_id[2] = {NONE64, NONE64};
+  uint64_t next_id = 0, last_ts = 0;
+  int depth = 0;
+  hbtgpu_slicer_stats total{};
+  bool have_state = false;
+  // results of the last run
   hbtgpu_slice* d_slices = nullptr;
   uint64_t* d_slice_begin = nullptr;
   std::vector<uint64_t> slice_begin;
-  std::vector<hbtgpu_stack_stats> stacks;
   hbtgpu_stack_stats* d_stacks = nullptr;
   uint64_t n_stacks = 0;
   bool have = false;
@@ -513,6 +606,60 @@ T* carve(hbtgpu_slicer_ctx* c, size_t n) {
 
 inline unsigned blocks(size_t n, unsigned t = 256) { return static_cast<unsigned>((n + t - 1) / t); }
 
+// a persistent array grown to n elements: old contents kept, the rest zero
+template <class T>
+int regrow(hbtgpu_slicer_ctx* c, T** p, size_t old_n, size_t new_n) {
+  T* q = nullptr;
+  SK(cudaMalloc(&q, std::max<size_t>(new_n, 1) * sizeof(T)));
+  SK(cudaMemsetAsync(q, 0, std::max<size_t>(new_n, 1) * sizeof(T), c->stream));
+  if (*p && old_n) SK(cudaMemcpyAsync(q, *p, old_n * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
+  SK(cudaStreamSynchronize(c->stream));
+  cudaFree(*p);
+  *p = q;
+  return 0;
+}
+
+int ensure_tags(hbtgpu_slicer_ctx* c, uint32_t n_tags) {
+  if (n_tags <= c->p_tags) return 0;
+  const uint32_t nt = std::max(n_tags, c->p_tags + c->p_tags / 2 + 16);
+  if (int rc = regrow(c, &c->p_flags, 2 * static_cast<size_t>(c->p_tags), 2 * static_cast<size_t>(nt))) return rc;
+  if (int rc = regrow(c, &c->p_id, 2 * static_cast<size_t>(c->p_tags), 2 * static_cast<size_t>(nt))) return rc;
+  const size_t os = c->p_tags ? 4 + 2 * static_cast<size_t>(c->p_tags) : 0, ns = 4 + 2 * static_cast<size_t>(nt);
+  if (int rc = regrow(c, &c->p_cum, os, ns)) return rc;
+  if (int rc = regrow(c, &c->p_in, os, ns)) return rc;
+  if (int rc = regrow(c, &c->p_out, os, ns)) return rc;
+  c->p_tags = nt;
+  return 0;
+}
+
+int reset_state(hbtgpu_slicer_ctx* c, uint32_t n_units) {
+  cudaStream_t st = c->stream;
+  if (c->p_tags) {
+    SK(cudaMemsetAsync(c->p_flags, 0, 2 * static_cast<size_t>(c->p_tags), st));
+    SK(cudaMemsetAsync(c->p_id, 0, 2 * static_cast<size_t>(c->p_tags) * 4, st));
+    const size_t ns = 4 + 2 * static_cast<size_t>(c->p_tags);
+    SK(cudaMemsetAsync(c->p_cum, 0, ns * 8, st));
+    SK(cudaMemsetAsync(c->p_in, 0, ns * 8, st));
+    SK(cudaMemsetAsync(c->p_out, 0, ns * 8, st));
+  }
+  if (c->carried_units != n_units) {
+    cudaFree(c->d_carried);
+    c->d_carried = nullptr;
+    SK(cudaMalloc(&c->d_carried, n_units * sizeof(Carried)));
+    c->carried_units = n_units;
+  }
+  std::vector<Carried> none(n_units, Carried{0, 0, static_cast<uint8_t>(EV_DESTROY), VIRT_K0, 1, 0});
+  SK(cudaMemcpyAsync(c->d_carried, none.data(), n_units * sizeof(Carried), cudaMemcpyHostToDevice, st));
+  SK(cudaStreamSynchronize(st));
+  c->e_id[0] = c->e_id[1] = c->a_id[0] = c->a_id[1] = NONE64;
+  c->next_id = 0;
+  c->last_ts = 0;
+  c->depth = 0;
+  memset(&c->total, 0, sizeof(c->total));
+  c->have_state = true;
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -536,6 +683,8 @@ void hbtgpu_slicer_destroy(hbtgpu_slicer_ctx* c) {
   cudaSetDevice(c->device);
   cudaFree(c->arena);
   cudaFree(c->arena2);
+  cudaFree(c->p_flags); cudaFree(c->p_id); cudaFree(c->p_cum); cudaFree(c->p_in); cudaFree(c->p_out);
+  cudaFree(c->d_carried);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -555,27 +704,29 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   const uint64_t base = event_begin[0];
   for (uint32_t u = 0; u < n_units; ++u)
     if (event_begin[u + 1] < event_begin[u]) return sfail(c, -EINVAL, "event_begin must not decrease");
-  const uint64_t N64 = event_begin[n_units] - base;
-  if (N64 >= 0x7fffffffull) return sfail(c, -EINVAL, "more than 2^31 events in one call");
-  const uint32_t N = static_cast<uint32_t>(N64);
-  if (N && !events) return sfail(c, -EINVAL, "null events");
+  const uint64_t Nreal = event_begin[n_units] - base;
+  if (Nreal + n_units >= 0x7fffffffull) return sfail(c, -EINVAL, "more than 2^31 events in one call");
+  if (Nreal && !events) return sfail(c, -EINVAL, "null events");
+  if (!(flags & HBTGPU_SLICER_CONTINUE) || !c->have_state || c->carried_units != n_units)
+    if (int rc = reset_state(c, n_units)) return rc;
+  // every unit gets one slot in front of its events for the state the previous window left it in
+  const uint32_t N = static_cast<uint32_t>(Nreal + n_units);
   std::vector<uint64_t> ub(n_units + 1);
-  for (uint32_t u = 0; u <= n_units; ++u) ub[u] = event_begin[u] - base;
+  for (uint32_t u = 0; u <= n_units; ++u) ub[u] = event_begin[u] - base + u;
 
-  // pass 0 sizes: events, unit table, keys
   cudaStream_t st = c->stream;
   size_t tmp_sort = 0, tmp_sort2 = 0, tmp_scan = 0, t2 = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
                                   static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), 0, 64, st);
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort2, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
-                                  static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr), static_cast<int>(2 * N64), 0, 64, st);
+                                  static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr), static_cast<int>(2 * static_cast<uint64_t>(N)), 0, 64, st);
   cub::DeviceScan::InclusiveSum(nullptr, tmp_scan, static_cast<int32_t*>(nullptr), static_cast<int32_t*>(nullptr), static_cast<int>(N), st);
   cub::DeviceScan::ExclusiveScan(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), MaxOp(), 0u, static_cast<int>(N), st);
   tmp_scan = std::max(tmp_scan, t2);
-  cub::DeviceScan::ExclusiveSum(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N64 + 8), st);
+  cub::DeviceScan::ExclusiveSum(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr),
+                                static_cast<int>(c->next_id + N + 9), st);  // events, or all stack ids so far
   tmp_scan = std::max(tmp_scan, t2);
   const size_t tmp_bytes = std::max(std::max(tmp_sort, tmp_sort2), tmp_scan) + 256;
-  // The thread table is sized once the largest tag is known; everything else now.
   const size_t n1 = static_cast<size_t>(N) + 1;
   size_t need = 0;
   auto add = [&](size_t n, size_t sz) { need += (n * sz + 255) & ~static_cast<size_t>(255); };
@@ -587,14 +738,12 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8);  // entries + sorted
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);               // idcnt, idbase, sflag, soff
   add(n1, 32); add(n_units + 2, 8);                             // slices, slice_begin
-  add(n1 + 8, 4); add(n1 + 8, 4);                               // id flags, id positions
-  add(1, sizeof(Globals)); add(4, 4); add(tmp_bytes, 1);
-  const size_t fixed_need = need;
-  if (c->arena_cap < fixed_need) {
+  add(1, sizeof(Globals)); add(tmp_bytes, 1);
+  if (c->arena_cap < need) {
     cudaFree(c->arena);
     c->arena = nullptr;
     c->arena_cap = 0;
-    const size_t cap = fixed_need + fixed_need / 4 + (1 << 20);
+    const size_t cap = need + need / 4 + (1 << 20);
     SK(cudaMalloc(&c->arena, cap));
     c->arena_cap = cap;
   }
@@ -629,70 +778,72 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   auto* d_soff = carve<uint32_t>(c, n1);
   auto* d_slices = carve<hbtgpu_slice>(c, n1);
   auto* d_slice_begin = carve<uint64_t>(c, n_units + 2);
-  auto* d_idflag = carve<uint32_t>(c, n1 + 8);
-  auto* d_idpos = carve<uint32_t>(c, n1 + 8);
   auto* d_g = carve<Globals>(c, 1);
-  auto* d_small = carve<unsigned int>(c, 4);
   auto* d_tmp = carve<char>(c, tmp_bytes);
   if (!d_tmp) return sfail(c, -EIO, "internal: arena too small");
 
-  const hbtgpu_cs_event* ev = d_ev;
-  if (flags & HBTGPU_SLICER_DEVICE_INPUT) {
-    ev = events + base;
-  } else if (N) {
-    SK(cudaMemcpyAsync(d_ev, events + base, static_cast<size_t>(N) * sizeof(hbtgpu_cs_event), cudaMemcpyHostToDevice, st));
-  }
+  // stage: [carried state, the unit's events] for every unit
   SK(cudaMemcpyAsync(d_ub, ub.data(), (n_units + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  k_sl_put_carried<<<blocks(n_units), 256, 0, st>>>(d_ev, d_ub, n_units, c->d_carried);
+  const cudaMemcpyKind kind = (flags & HBTGPU_SLICER_DEVICE_INPUT) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  for (uint32_t u = 0; u < n_units; ++u) {
+    const uint64_t n = event_begin[u + 1] - event_begin[u];
+    if (n) SK(cudaMemcpyAsync(d_ev + ub[u] + 1, events + event_begin[u], n * sizeof(hbtgpu_cs_event), kind, st));
+  }
+  const hbtgpu_cs_event* ev = d_ev;
   Globals g0;
   memset(&g0, 0, sizeof(g0));
   g0.e_first[0] = g0.e_first[1] = g0.a_first[0] = g0.a_first[1] = NOIDX;
+  g0.depth0 = c->depth;
+  g0.last_ts0 = c->last_ts;
+  g0.have = (c->e_id[0] != NONE64 ? 1u : 0u) | (c->e_id[1] != NONE64 ? 2u : 0u) | (c->a_id[0] != NONE64 ? 4u : 0u) |
+            (c->a_id[1] != NONE64 ? 8u : 0u);
   SK(cudaMemcpyAsync(d_g, &g0, sizeof(g0), cudaMemcpyHostToDevice, st));
-  SK(cudaMemsetAsync(d_small, 0, 4 * sizeof(unsigned int), st));
   SK(cudaEventRecord(c->ev0, st));
 
   Globals gh = g0;
-  if (N) {
-    size_t t = tmp_bytes;
-    k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of);
-    k_sl_prepare<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_key, d_val, d_g);
-    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
-    SK(cudaStreamSynchronize(st));
-    int ts_bits = 1;  // radix passes only over the bits the timestamps use
-    while (ts_bits < 64 && (gh.max_ts >> ts_bits) != 0) ++ts_bits;
-    cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key, d_key_s, d_val, d_order, static_cast<int>(N), 0, ts_bits, st);
-    k_sl_gather<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_rank, d_delta, d_start);
-    t = tmp_bytes;
-    cub::DeviceScan::InclusiveSum(d_tmp, t, d_delta, d_depth, static_cast<int>(N), st);
-    t = tmp_bytes;
-    cub::DeviceScan::InclusiveSum(d_tmp, t, d_start, d_epoch, static_cast<int>(N), st);
-    k_sl_effective<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_depth, d_delta, d_eff, d_scan_in, d_g);
-    t = tmp_bytes;
-    cub::DeviceScan::ExclusiveScan(d_tmp, t, d_scan_in, d_prev_scan, MaxOp(), 0u, static_cast<int>(N), st);
-    SK(cudaMemsetAsync(d_next, 0xff, static_cast<size_t>(N) * sizeof(uint32_t), st));
-    k_sl_links<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_rank, d_epoch, d_eff, d_prev_scan, d_prev, d_next,
-                                          d_cf, d_g);
-    SK(cudaGetLastError());
-    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
-    SK(cudaStreamSynchronize(st));
-    if (gh.bad) {
-      const unsigned b = gh.bad;
-      return sfail(c, (b & BAD_UNIT) ? -EINVAL : -ENOTSUP,
-                   "events outside the parallel form:%s%s%s%s%s%s%s",
-                   (b & BAD_TYPE) ? " phase or unknown event types;" : "", (b & BAD_LEVEL) ? " events above level 0;" : "",
-                   (b & BAD_ORDER) ? " a unit's events go back in time;" : "",
-                   (b & BAD_UNIT) ? " comp_unit_id differs from the unit the event was filed under;" : "",
-                   (b & BAD_TAG) ? " switch-in or creation without a tag;" : "",
-                   (b & BAD_DOUBLE_IN) ? " switch-in on a unit whose active state is a thread (the reference resets);" : "",
-                   (b & BAD_WE_END) ? " WriteErrorsEnd without its Start;" : "");
-    }
+  size_t t = tmp_bytes;
+  k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of);
+  k_sl_prepare<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_key, d_val, d_g);
+  SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+  SK(cudaStreamSynchronize(st));
+  int ts_bits = 1;  // radix passes only over the bits the timestamps use
+  while (ts_bits < 64 && (gh.max_ts >> ts_bits) != 0) ++ts_bits;
+  cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key, d_key_s, d_val, d_order, static_cast<int>(N), 0, ts_bits, st);
+  k_sl_gather<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_rank, d_delta, d_start);
+  t = tmp_bytes;
+  cub::DeviceScan::InclusiveSum(d_tmp, t, d_delta, d_depth, static_cast<int>(N), st);
+  t = tmp_bytes;
+  cub::DeviceScan::InclusiveSum(d_tmp, t, d_start, d_epoch, static_cast<int>(N), st);
+  k_sl_effective<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_depth, d_delta, d_eff, d_scan_in, d_g);
+  t = tmp_bytes;
+  cub::DeviceScan::ExclusiveScan(d_tmp, t, d_scan_in, d_prev_scan, MaxOp(), 0u, static_cast<int>(N), st);
+  SK(cudaMemsetAsync(d_next, 0xff, static_cast<size_t>(N) * sizeof(uint32_t), st));
+  k_sl_links<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_rank, d_epoch, d_eff, d_prev_scan, d_prev, d_next, d_cf,
+                                        d_g);
+  SK(cudaGetLastError());
+  SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+  SK(cudaStreamSynchronize(st));
+  if (gh.bad) {
+    const unsigned b = gh.bad;
+    return sfail(c, (b & BAD_UNIT) ? -EINVAL : -ENOTSUP, "events outside the parallel form:%s%s%s%s%s%s%s",
+                 (b & BAD_TYPE) ? " phase or unknown event types;" : "", (b & BAD_LEVEL) ? " events above level 0;" : "",
+                 (b & BAD_ORDER) ? " a unit's events go back in time;" : "",
+                 (b & BAD_UNIT) ? " comp_unit_id differs from the unit the event was filed under;" : "",
+                 (b & BAD_TAG) ? " switch-in or creation without a tag;" : "",
+                 (b & BAD_DOUBLE_IN) ? " switch-in on a unit whose active state is a thread (the reference resets);" : "",
+                 (b & BAD_WE_END) ? " WriteErrorsEnd without its Start;" : "");
   }
-  const uint32_t n_tags = gh.max_tag + 1;
-  if (n_tags > (1u << 27)) return sfail(c, -ENOTSUP, "thread ids up to %u: the per-thread tables would not fit", gh.max_tag);
-  // per-thread tables: their own allocation, sized now that the largest tag is known
+  if (gh.max_tag >= (1u << 27)) return sfail(c, -ENOTSUP, "thread ids up to %u: the per-thread tables would not fit", gh.max_tag);
+  if (int rc = ensure_tags(c, gh.max_tag + 1)) return rc;
+  const uint32_t n_tags = c->p_tags;
   const size_t n_slots = 4 + 2 * static_cast<size_t>(n_tags);
+
+  // per-run scratch by thread id / stack id
+  const uint64_t ids_bound = c->next_id + N + 8;
   size_t need2 = 0;
   auto add2 = [&](size_t n, size_t sz) { need2 += (n * sz + 255) & ~static_cast<size_t>(255); };
-  add2(2 * static_cast<size_t>(n_tags), 4); add2(n_slots, 8); add2(n_slots, 8); add2(n_slots, 8);
+  add2(2 * static_cast<size_t>(n_tags), 4); add2(n_tags, 4); add2(ids_bound, 4); add2(ids_bound, 4);
   add2(n_slots, sizeof(hbtgpu_stack_stats));
   if (need2 > c->arena2_cap) {
     cudaFree(c->arena2);
@@ -708,112 +859,113 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     return q;
   };
   auto* d_tcreate = reinterpret_cast<uint32_t*>(carve2(2 * static_cast<size_t>(n_tags), 4));
-  auto* d_cum = reinterpret_cast<unsigned long long*>(carve2(n_slots, 8));
-  auto* d_in = reinterpret_cast<unsigned long long*>(carve2(n_slots, 8));
-  auto* d_out = reinterpret_cast<unsigned long long*>(carve2(n_slots, 8));
+  auto* d_last_epoch = reinterpret_cast<uint32_t*>(carve2(n_tags, 4));
+  auto* d_idflag = reinterpret_cast<uint32_t*>(carve2(ids_bound, 4));
+  auto* d_idpos = reinterpret_cast<uint32_t*>(carve2(ids_bound, 4));
   auto* d_stacks = reinterpret_cast<hbtgpu_stack_stats*>(carve2(n_slots, sizeof(hbtgpu_stack_stats)));
   SK(cudaMemsetAsync(d_tcreate, 0xff, 2 * static_cast<size_t>(n_tags) * sizeof(uint32_t), st));
-  SK(cudaMemsetAsync(d_cum, 0, n_slots * 8, st));
-  SK(cudaMemsetAsync(d_in, 0, n_slots * 8, st));
-  SK(cudaMemsetAsync(d_out, 0, n_slots * 8, st));
+  SK(cudaMemsetAsync(d_last_epoch, 0, static_cast<size_t>(n_tags) * sizeof(uint32_t), st));
 
-  uint64_t total_slices = 0;
+  k_sl_entry_counts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_epoch, d_eff, d_next, d_ecnt);
+  t = tmp_bytes;
+  cub::DeviceScan::ExclusiveSum(d_tmp, t, d_ecnt, d_eoff, static_cast<int>(N), st);
+  uint32_t last_off = 0, last_cnt = 0;
+  SK(cudaMemcpyAsync(&last_off, d_eoff + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaMemcpyAsync(&last_cnt, d_ecnt + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaStreamSynchronize(st));
+  const uint32_t n_entries = last_off + last_cnt;
+  if (n_entries) {
+    int pos_bits = 1, tag_bits = 1;  // key = tag << pos_bits | merge position
+    while ((static_cast<uint64_t>(N) >> pos_bits) != 0) ++pos_bits;
+    while ((static_cast<uint64_t>(gh.max_tag) >> tag_bits) != 0) ++tag_bits;
+    k_sl_entries<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_next, d_ecnt, d_eoff, pos_bits, d_ekey, d_eval);
+    t = tmp_bytes;
+    cub::DeviceRadixSort::SortPairs(d_tmp, t, d_ekey, d_ekey_s, d_eval, d_eval_s, static_cast<int>(n_entries), 0,
+                                    pos_bits + tag_bits, st);
+    k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, pos_bits, d_rank, d_epoch, d_cf,
+                                                      d_tcreate, c->p_flags, d_last_epoch);
+  }
+  k_sl_firsts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_eff, d_cf, d_g);
+  k_sl_id_counts<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_eff, d_cf, d_g, d_idcnt);
+  t = tmp_bytes;
+  cub::DeviceScan::ExclusiveSum(d_tmp, t, d_idcnt, d_idbase, static_cast<int>(N), st);
+  SK(cudaGetLastError());
+  SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+  // ids of the shared states created in this window (E[k] is the parent: first when one event makes both),
+  // the number of ids the window took, where it ends
+  uint32_t pos_list[4] = {0, 0, 0, 0}, base_at[4] = {0, 0, 0, 0}, last_base = 0, last_idcnt = 0, final_epoch = 0, last_idx = 0;
+  int32_t depth_last = 0;
+  SK(cudaStreamSynchronize(st));
+  pos_list[0] = gh.e_first[0]; pos_list[1] = gh.e_first[1]; pos_list[2] = gh.a_first[0]; pos_list[3] = gh.a_first[1];
+  for (int j = 0; j < 4; ++j)
+    if (pos_list[j] != NOIDX) SK(cudaMemcpyAsync(&base_at[j], d_idbase + pos_list[j], 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaMemcpyAsync(&last_base, d_idbase + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaMemcpyAsync(&last_idcnt, d_idcnt + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaMemcpyAsync(&final_epoch, d_epoch + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaMemcpyAsync(&depth_last, d_depth + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaMemcpyAsync(&last_idx, d_order + (N - 1), 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaStreamSynchronize(st));
+  const uint32_t id0 = static_cast<uint32_t>(c->next_id);
+  for (int k = 0; k < 2; ++k) {
+    if (gh.e_first[k] != NOIDX) c->e_id[k] = static_cast<uint64_t>(id0) + base_at[k];
+    if (gh.a_first[k] != NOIDX)
+      c->a_id[k] = static_cast<uint64_t>(id0) + base_at[2 + k] + (gh.a_first[k] == gh.e_first[k] ? 1 : 0);
+  }
+  c->next_id += static_cast<uint64_t>(last_base) + last_idcnt;
+  if (c->next_id >= 0xfffffff0ull) return sfail(c, -EOVERFLOW, "more than 2^32 stack ids");
+  k_sl_store_ids<<<blocks(2 * static_cast<size_t>(n_tags)), 256, 0, st>>>(n_tags, d_tcreate, d_rank, d_idbase, id0, d_g,
+                                                                          c->p_id);
+  Ids ids;
+  ids.pt_id = c->p_id;
+  for (int k = 0; k < 2; ++k) {
+    ids.e_id[k] = c->e_id[k];
+    ids.a_id[k] = c->a_id[k];
+  }
+  k_sl_slice_flags<<<blocks(N), 256, 0, st>>>(ev, N, d_eff, d_prev, d_cf, d_sflag, c->p_cum, c->p_in, c->p_out, d_g);
+  t = tmp_bytes;
+  cub::DeviceScan::ExclusiveSum(d_tmp, t, d_sflag, d_soff, static_cast<int>(N), st);
+  k_sl_emit<<<blocks(N), 256, 0, st>>>(ev, N, d_prev, d_cf, d_sflag, d_soff, ids, d_slices);
+  k_sl_unit_counts<<<blocks(n_units + 1), 256, 0, st>>>(d_ub, n_units, N, d_soff, d_sflag, d_slice_begin);
+  // what the next window starts from
+  k_sl_final_active<<<blocks(n_units), 256, 0, st>>>(ev, d_ub, n_units, d_rank, d_epoch, d_eff, d_cf, final_epoch,
+                                                     c->d_carried);
+  if (final_epoch > 0) k_sl_clear_dormant<<<blocks(n_tags), 256, 0, st>>>(n_tags, final_epoch, d_last_epoch, c->p_flags);
+  // the stack table, by id: flag the ids that belong to a state, scan, place
+  const uint32_t n_ids = static_cast<uint32_t>(c->next_id);
+  SK(cudaMemsetAsync(d_idflag, 0, (static_cast<size_t>(n_ids) + 1) * 4, st));
+  k_sl_stacks<<<blocks(n_slots), 256, 0, st>>>(n_tags, ids, c->p_flags, c->p_cum, c->p_in, c->p_out, d_idflag, nullptr,
+                                               d_stacks);
+  t = tmp_bytes;
+  size_t t_ids = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, t_ids, d_idflag, d_idpos, static_cast<int>(n_ids + 1), st);
+  if (t_ids > tmp_bytes) return sfail(c, -EIO, "internal: scan scratch too small");
+  cub::DeviceScan::ExclusiveSum(d_tmp, t, d_idflag, d_idpos, static_cast<int>(n_ids + 1), st);
+  k_sl_stacks<<<blocks(n_slots), 256, 0, st>>>(n_tags, ids, c->p_flags, c->p_cum, c->p_in, c->p_out, d_idflag, d_idpos,
+                                               d_stacks);
+  SK(cudaGetLastError());
+  SK(cudaEventRecord(c->ev1, st));
+  uint32_t n_states = 0;
+  SK(cudaMemcpyAsync(&n_states, d_idpos + n_ids, 4, cudaMemcpyDeviceToHost, st));
+  SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
   c->slice_begin.assign(n_units + 1, 0);
-  unsigned int small[4] = {0, 0, 0, 0};
-  if (N) {
-    size_t t = tmp_bytes;
-    k_sl_entry_counts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_epoch, d_eff, d_next, d_ecnt);
-    cub::DeviceScan::ExclusiveSum(d_tmp, t, d_ecnt, d_eoff, static_cast<int>(N), st);
-    uint32_t last_off = 0, last_cnt = 0;
-    SK(cudaMemcpyAsync(&last_off, d_eoff + (N - 1), 4, cudaMemcpyDeviceToHost, st));
-    SK(cudaMemcpyAsync(&last_cnt, d_ecnt + (N - 1), 4, cudaMemcpyDeviceToHost, st));
-    SK(cudaStreamSynchronize(st));
-    const uint32_t n_entries = last_off + last_cnt;
-    if (n_entries) {
-      int pos_bits = 1, tag_bits = 1;  // key = tag << pos_bits | merge position
-      while ((static_cast<uint64_t>(N) >> pos_bits) != 0) ++pos_bits;
-      while ((static_cast<uint64_t>(gh.max_tag) >> tag_bits) != 0) ++tag_bits;
-      k_sl_entries<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_next, d_ecnt, d_eoff, pos_bits, d_ekey, d_eval);
-      t = tmp_bytes;
-      cub::DeviceRadixSort::SortPairs(d_tmp, t, d_ekey, d_ekey_s, d_eval, d_eval_s, static_cast<int>(n_entries), 0,
-                                      pos_bits + tag_bits, st);
-      k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, pos_bits, d_rank, d_epoch, d_cf,
-                                                        d_tcreate);
-    }
-    k_sl_firsts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_eff, d_cf, d_g);
-    k_sl_id_counts<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_eff, d_cf, d_g, d_idcnt);
-    t = tmp_bytes;
-    cub::DeviceScan::ExclusiveSum(d_tmp, t, d_idcnt, d_idbase, static_cast<int>(N), st);
-    SK(cudaGetLastError());
-    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
-    SK(cudaStreamSynchronize(st));
-    Ids ids;
-    ids.idbase = d_idbase;
-    ids.rank = d_rank;
-    ids.t_create = d_tcreate;
-    for (int k = 0; k < 2; ++k) {
-      ids.e_first[k] = gh.e_first[k];
-      ids.a_first[k] = gh.a_first[k];
-      ids.e_id[k] = ids.a_id[k] = NONE64;
-    }
-    // ids of the four shared states: E[k] is the parent, created first when one event makes both
-    uint32_t pos_list[4] = {gh.e_first[0], gh.e_first[1], gh.a_first[0], gh.a_first[1]};
-    uint32_t base_at[4] = {0, 0, 0, 0};
-    for (int j = 0; j < 4; ++j)
-      if (pos_list[j] != NOIDX) SK(cudaMemcpyAsync(&base_at[j], d_idbase + pos_list[j], 4, cudaMemcpyDeviceToHost, st));
-    SK(cudaStreamSynchronize(st));
-    for (int k = 0; k < 2; ++k) {
-      if (gh.e_first[k] != NOIDX) ids.e_id[k] = base_at[k];
-      if (gh.a_first[k] != NOIDX) ids.a_id[k] = static_cast<uint64_t>(base_at[2 + k]) + (gh.a_first[k] == gh.e_first[k] ? 1 : 0);
-    }
-    k_sl_slice_flags<<<blocks(N), 256, 0, st>>>(ev, N, d_eff, d_prev, d_cf, d_sflag, d_cum, d_in, d_out, d_g);
-    t = tmp_bytes;
-    cub::DeviceScan::ExclusiveSum(d_tmp, t, d_sflag, d_soff, static_cast<int>(N), st);
-    k_sl_emit<<<blocks(N), 256, 0, st>>>(ev, N, d_prev, d_cf, d_sflag, d_soff, ids, d_slices);
-    k_sl_unit_counts<<<blocks(n_units + 1), 256, 0, st>>>(d_ub, n_units, N, d_soff, d_sflag, d_slice_begin);
-    // ids handed out: the last event's base + count; flag the ones that belong to a state, scan, place
-    SK(cudaMemcpyAsync(&small[1], d_idbase + (N - 1), 4, cudaMemcpyDeviceToHost, st));
-    SK(cudaMemcpyAsync(&small[2], d_idcnt + (N - 1), 4, cudaMemcpyDeviceToHost, st));
-    SK(cudaStreamSynchronize(st));
-    const uint32_t n_ids = small[1] + small[2];
-    SK(cudaMemsetAsync(d_idflag, 0, (static_cast<size_t>(n_ids) + 1) * 4, st));
-    k_sl_stacks<<<blocks(n_slots), 256, 0, st>>>(n_tags, ids, d_cum, d_in, d_out, d_idflag, nullptr, d_stacks);
-    t = tmp_bytes;
-    cub::DeviceScan::ExclusiveSum(d_tmp, t, d_idflag, d_idpos, static_cast<int>(n_ids + 1), st);
-    k_sl_stacks<<<blocks(n_slots), 256, 0, st>>>(n_tags, ids, d_cum, d_in, d_out, d_idflag, d_idpos, d_stacks);
-    SK(cudaMemcpyAsync(&small[0], d_idpos + n_ids, 4, cudaMemcpyDeviceToHost, st));  // number of states
-    SK(cudaGetLastError());
-    SK(cudaEventRecord(c->ev1, st));
-    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
-    SK(cudaMemcpyAsync(c->slice_begin.data(), d_slice_begin, (n_units + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
-    uint32_t last_idx = 0;
-    SK(cudaMemcpyAsync(&last_idx, d_order + (N - 1), 4, cudaMemcpyDeviceToHost, st));
-    SK(cudaStreamSynchronize(st));
-    hbtgpu_cs_event last_ev;
-    SK(cudaMemcpy(&last_ev, ev + last_idx, sizeof(last_ev), cudaMemcpyDeviceToHost));
-    if (last_ts) *last_ts = last_ev.tstamp;
-    total_slices = c->slice_begin[n_units];
-    SK(cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
-  } else {
-    SK(cudaEventRecord(c->ev1, st));
-    SK(cudaStreamSynchronize(st));
-    if (last_ts) *last_ts = 0;
-    c->last_ms = 0.f;
-  }
-  (void)total_slices;
-  c->n_stacks = small[0];
-  c->d_stacks = d_stacks;
-  c->stacks.clear();  // fetched when asked for
-  if (stats) {
-    memset(stats, 0, sizeof(*stats));
-    stats->num_processed = N;  // every event is processed once (no event is older than its predecessor)
-    stats->num_error_start = gh.n_we_start;
-    stats->num_error_end = gh.n_we_end;
-    stats->num_dropped = gh.n_dropped;
-    stats->num_slices_completed = gh.n_completed;
-  }
+  SK(cudaMemcpyAsync(c->slice_begin.data(), d_slice_begin, (n_units + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  hbtgpu_cs_event last_ev;
+  SK(cudaMemcpyAsync(&last_ev, ev + last_idx, sizeof(last_ev), cudaMemcpyDeviceToHost, st));
+  SK(cudaStreamSynchronize(st));
+  SK(cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
+  if (Nreal) c->last_ts = std::max<uint64_t>(c->last_ts, last_ev.tstamp);  // (the last in merge order is a real event)
+  c->depth += depth_last;
+  c->total.num_processed += Nreal;  // every event is processed once (none is older than its predecessor)
+  c->total.num_error_start += gh.n_we_start;
+  c->total.num_error_end += gh.n_we_end;
+  c->total.num_dropped += gh.n_dropped;
+  c->total.num_slices_completed += gh.n_completed;
+  if (stats) *stats = c->total;
+  if (last_ts) *last_ts = c->last_ts;
   if (n_slices)
     for (uint32_t u = 0; u < n_units; ++u) n_slices[u] = c->slice_begin[u + 1] - c->slice_begin[u];
+  c->n_stacks = n_states;
+  c->d_stacks = d_stacks;
   if (n_stacks) *n_stacks = c->n_stacks;
   c->d_slices = d_slices;
   c->d_slice_begin = d_slice_begin;

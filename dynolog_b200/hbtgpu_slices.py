@@ -213,7 +213,7 @@ class Slicer:
         if rc != 0:
             raise HbtGpuError(rc, self.L.hbtgpu_slicer_last_error(self.h).decode())
 
-    def run(self, unit_events=None, device_events=None, event_begin=None):
+    def run(self, unit_events=None, device_events=None, event_begin=None, cont=False):
         """unit_events: list of EVENT_DTYPE arrays (one per comp unit, stream order), or
         device_events (raw pointer) + event_begin.  Returns dict(slices=[per unit], stats, stacks,
         last_ts)."""
@@ -223,10 +223,15 @@ class Slicer:
             ev = np.ascontiguousarray(np.concatenate(unit_events) if n_units else np.zeros(0, EVENT_DTYPE),
                                       dtype=EVENT_DTYPE)
             ptr, flags = ev.ctypes.data, 0
+            if len(ev) == 0:
+                ev = np.zeros(1, EVENT_DTYPE)
+                ptr = ev.ctypes.data
         else:
             event_begin = np.ascontiguousarray(event_begin, dtype=np.uint64)
             n_units = len(event_begin) - 1
             ptr, flags = device_events, 1
+        if cont:
+            flags |= 2
         stats = np.zeros(len(SLICER_STAT_KEYS), np.uint64)
         n_slices = np.zeros(n_units, np.uint64)
         n_stacks, last_ts = C.c_uint64(0), C.c_uint64(0)

@@ -651,7 +651,11 @@ const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* ctx); /* t
  * run) at events[event_begin[u] .. event_begin[u+1]), each unit in stream order.  The merge of
  * the units (Event::happenedBefore: tstamp, then comp unit, tagstack/Event.h:217-223), the stack
  * dictionary with ids in order of creation, the dormant lists and the resets are computed on
- * the GPU.  Every call is a Slicer of its own, started empty.
+ * the GPU.  A call starts an empty Slicer unless HBTGPU_SLICER_CONTINUE is
+ * set: then the window follows the previous call's (same units) -- active states with their
+ * switch-in times, the dictionary with its ids and dormant flags, the write-error depth, the
+ * statistics and the last timestamp carry over, exactly as one Slicer fed both windows would
+ * have them.  stats / the stack table / last_ts are cumulative since the last fresh start.
  *
  * Scope: level-0 events (ThreadCreation / ThreadDestruction / SwitchIn / SwitchOut* /
  * WriteErrors*), every unit's events in time order, no switch-in on a unit whose active state is
@@ -660,6 +664,7 @@ const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* ctx); /* t
  * unit an event was filed under is -EINVAL (the reference throws, :351-352).
  */
 #define HBTGPU_SLICER_DEVICE_INPUT 0x1u /* events is a device pointer (event_begin stays host) */
+#define HBTGPU_SLICER_CONTINUE 0x2u     /* this window follows the previous call's: keep the Slicer's state */
 typedef struct {  /* SlicerStats, Slicer.h:276-285 */
   uint64_t num_processed, num_error_start, num_error_end, num_error_out_sync, num_dropped, num_out_of_order,
       num_slices_completed, num_logic_errors;

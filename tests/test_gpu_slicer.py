@@ -154,3 +154,34 @@ def test_decoded_capture_to_slices_on_the_device(slicer):
             assert np.array_equal(counts, exp["counts"]) and po.slices_as_tuples(out) == po.slices_as_tuples(exp["slices"])
     finally:
         isl.close()
+
+
+@pytest.mark.parametrize("kw", [dict(p_double_in=0.0), dict(p_double_in=0.0, p_we=0.05), dict(p_double_in=0.0, p_migrate=0.4, p_create=0.2),
+                                dict(p_double_in=0.0, p_tid0=0.7, p_same_ts=0.3)])
+def test_windows_continue_each_other(slicer, kw):
+    """One stream cut into windows (HBTGPU_SLICER_CONTINUE) gives the slices, the stack table and the
+    statistics of one Slicer fed the whole stream: threads running across a cut, dormant states,
+    write errors open at a cut, ids continuing."""
+    r = np.random.default_rng(len(repr(kw)) + 7)
+    done = 0
+    for trial in range(40):
+        n_units = int(r.integers(1, 6))
+        ev = random_events(r, n_units, int(r.integers(50, 1500)), int(r.choice([3, 10, 80])), **kw)
+        units, merged = split_units(ev, n_units)
+        if not supported(merged, n_units):
+            continue
+        exp = po.slicer_run("port", merged, n_units)
+        # cut at 1-4 timestamps: every unit's events before the cut go to the earlier window
+        cuts = sorted(set(int(x) for x in r.choice(merged["tstamp"], size=int(r.integers(1, 5)))))
+        bounds = [0] + cuts + [2**63]
+        got_slices = [[] for _ in range(n_units)]
+        got = None
+        for w in range(len(bounds) - 1):
+            win = [u_[(u_["tstamp"] >= bounds[w]) & (u_["tstamp"] < bounds[w + 1])] for u_ in units]
+            got = slicer.run(win, cont=w > 0)
+            for u in range(n_units):
+                got_slices[u].append(got["slices"][u])
+        got["slices"] = [np.concatenate(x) for x in got_slices]
+        compare(got, exp)
+        done += 1
+    assert done > 10
