@@ -13,12 +13,15 @@
 //   * a switch-in of v closes it too and activates T[v][1] if g's previous event was a
 //     switch-out (known levels) and T[v][1] is dormant, else T[v][0]; v = 0 takes T[0][k];
 //   * WriteErrorsStart resets (active states, dormant flags); events between it and its End
-//     are dropped;
+//     are dropped; a switch-in on a unit whose active state is a thread closes that slice, resets
+//     everything and activates nothing (:839-868).  Whether a switch-in is such depends on the
+//     resets before it, so these are settled in merge order: link, take the earliest, repeat;
 //   * ids: one per createStackState_ call in merge order, parents first; a ThreadCreation of
 //     an existing stack still takes an id.
-// Anything else -- phase events, other levels, a unit whose events go back in time, a switch-in
-// on a unit whose active state is a thread (the reference resets there: a data-dependent reset),
-// a WriteErrorsEnd without its Start -- is refused with -ENOTSUP; nothing is computed on the CPU.
+// Anything else -- phase events, other levels, a unit whose events go back in time, a
+// WriteErrorsEnd without its Start -- is refused with -ENOTSUP; nothing is computed on the CPU.
+// The state between two windows stays on the device (HBTGPU_SLICER_CONTINUE): a unit's active
+// state travels as one extra event in front of the unit's events.
 //
 // Steps: (1) stable radix sort of the events by tstamp (units arrive one after the other, so
 // ties keep comp-unit order = the merge order); (2) scans in merge order: write-error depth ->
@@ -75,6 +78,7 @@ struct Globals {
   int depth0;                 // write-error depth the window starts with
   unsigned long long last_ts0;  // last timestamp of the previous window
   unsigned int have;          // bit k: E[k] exists already, bit 2 + k: T[0][k]
+  unsigned int cand;          // earliest switch-in on a unit whose active state is a thread (merge position)
 };
 
 struct MaxOp {
@@ -166,8 +170,8 @@ __global__ void k_sl_effective(const hbtgpu_cs_event* __restrict__ ev, uint32_t 
 __global__ void k_sl_links(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ unit_of,
                            const uint64_t* __restrict__ ub, const uint32_t* __restrict__ rank,
                            const uint32_t* __restrict__ epoch, const uint8_t* __restrict__ eff,
-                           const uint32_t* __restrict__ prev_scan, uint32_t* __restrict__ prev,
-                           uint32_t* __restrict__ next, uint8_t* __restrict__ cf, Globals* g) {
+                           const uint8_t* __restrict__ rin, const uint32_t* __restrict__ prev_scan,
+                           uint32_t* __restrict__ prev, uint32_t* __restrict__ next, uint8_t* __restrict__ cf, Globals* g) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint32_t pv = NOIDX;
@@ -178,11 +182,16 @@ __global__ void k_sl_links(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, c
     if (raw != 0 && raw - 1 >= ub[unit_of[i]]) {
       const uint32_t r = raw - 1;
       next[r] = i;  // (each event is the predecessor of at most one)
-      if (epoch[rank[r]] == epoch[rank[i]]) {  // no reset in between
+      // no reset in between; a switch-in that reset everything (rin) belongs to the epoch it ended
+      // and activated nothing
+      if (!rin[r] && epoch[rank[r]] == epoch[rank[i]] - (rin[i] ? 1u : 0u)) {
         pv = r;
         f |= CF_PREV;
         if (t == EV_IN) {
-          if (ev[r].type == EV_IN) atomicOr(&g->bad, BAD_DOUBLE_IN);  // handleEventInPreConditionError_, :839-868
+          // handleEventInPreConditionError_, :839-868: the slice of the thread is closed, then
+          // everything is reset and this switch-in activates nothing.  Only the earliest one is
+          // certain (later ones may disappear with that reset): the host marks it and repeats.
+          if (ev[r].type == EV_IN && !rin[i]) atomicMin(&g->cand, rank[i]);
           f |= CF_KNOWN;  // the state left behind is E[1]: known_num_levels
         }
       }
@@ -195,16 +204,17 @@ __global__ void k_sl_links(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, c
 
 __global__ void k_sl_entry_counts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
                                   const uint32_t* __restrict__ epoch, const uint8_t* __restrict__ eff,
-                                  const uint32_t* __restrict__ next, uint32_t* __restrict__ ecnt) {
+                                  const uint8_t* __restrict__ rin, const uint32_t* __restrict__ next,
+                                  uint32_t* __restrict__ ecnt) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint32_t c = 0;
-  if (eff[i] && ev[i].tag != 0) {
+  if (eff[i] && ev[i].tag != 0 && !rin[i]) {
     const uint32_t t = ev[i].type;
     if (t == EV_CREATE) c = 1;
     else if (t == EV_IN) {
       const uint32_t nx = next[i];
-      c = 1 + ((nx != NOIDX && epoch[rank[nx]] == epoch[rank[i]]) ? 1u : 0u);
+      c = 1 + ((nx != NOIDX && epoch[rank[nx]] - (rin[nx] ? 1u : 0u) == epoch[rank[i]]) ? 1u : 0u);
     }
   }
   ecnt[i] = c;
@@ -280,10 +290,11 @@ __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __r
 
 // (5a) where E[k] and T[0][k] are first needed
 __global__ void k_sl_firsts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
-                            const uint8_t* __restrict__ eff, const uint8_t* __restrict__ cf, Globals* g) {
+                            const uint8_t* __restrict__ eff, const uint8_t* __restrict__ rin,
+                            const uint8_t* __restrict__ cf, Globals* g) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t e0 = NOIDX, e1 = NOIDX, a0 = NOIDX, a1 = NOIDX;
-  if (i < n && eff[i] && !is_virtual(ev[i])) {
+  if (i < n && eff[i] && !is_virtual(ev[i]) && !rin[i]) {
     const uint32_t t = ev[i].type, p = rank[i];
     const uint8_t f = cf[i];
     if (t == EV_OUT_PREEMPT || t == EV_OUT_YIELD) e1 = p;
@@ -318,13 +329,13 @@ __global__ void k_sl_firsts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, 
 
 // (5b) ids taken by the event at merge position p
 __global__ void k_sl_id_counts(const hbtgpu_cs_event* __restrict__ ev, const uint32_t* __restrict__ order, uint32_t n,
-                               const uint8_t* __restrict__ eff, const uint8_t* __restrict__ cf, const Globals* g,
-                               uint32_t* __restrict__ idcnt) {
+                               const uint8_t* __restrict__ eff, const uint8_t* __restrict__ rin,
+                               const uint8_t* __restrict__ cf, const Globals* g, uint32_t* __restrict__ idcnt) {
   const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= n) return;
   const uint32_t i = order[p];
   uint32_t c = 0;
-  if (eff[i] && !is_virtual(ev[i])) {
+  if (eff[i] && !is_virtual(ev[i]) && !rin[i]) {
     const uint32_t t = ev[i].type;
     const uint8_t f = cf[i];
     if (t == EV_OUT_PREEMPT || t == EV_OUT_YIELD) c = p == g->e_first[1];
@@ -375,7 +386,7 @@ __device__ __forceinline__ uint64_t state_id(const Ids& ids, const hbtgpu_cs_eve
 
 // (6a) which switch events close a slice with a duration
 __global__ void k_sl_slice_flags(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint8_t* __restrict__ eff,
-                                 const uint32_t* __restrict__ prev, const uint8_t* __restrict__ cf,
+                                 const uint8_t* __restrict__ rin, const uint32_t* __restrict__ prev, const uint8_t* __restrict__ cf,
                                  uint32_t* __restrict__ sflag, unsigned long long* __restrict__ st_cum,
                                  unsigned long long* __restrict__ st_in, unsigned long long* __restrict__ st_out,
                                  Globals* g) {
@@ -384,7 +395,7 @@ __global__ void k_sl_slice_flags(const hbtgpu_cs_event* __restrict__ ev, uint32_
   uint32_t in_slot = NOIDX, out_slot = NOIDX;
   uint64_t dur = 0;
   if (i < n && eff[i] && is_switch(ev[i].type) && !is_virtual(ev[i])) {
-    in_slot = state_slot(ev[i], cf[i]);  // markSwitchIn, :231-241
+    if (!rin[i]) in_slot = state_slot(ev[i], cf[i]);  // markSwitchIn, :231-241
     const uint32_t r = prev[i];
     if (r != NOIDX) {
       dur = ev[i].tstamp - ev[r].tstamp;
@@ -501,14 +512,15 @@ struct Carried {
 __global__ void k_sl_final_active(const hbtgpu_cs_event* __restrict__ ev, const uint64_t* __restrict__ ub,
                                   uint32_t n_units, const uint32_t* __restrict__ rank,
                                   const uint32_t* __restrict__ epoch, const uint8_t* __restrict__ eff,
-                                  const uint8_t* __restrict__ cf, uint32_t final_epoch, Carried* __restrict__ out) {
+                                  const uint8_t* __restrict__ rin, const uint8_t* __restrict__ cf, uint32_t final_epoch,
+                                  Carried* __restrict__ out) {
   const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= n_units) return;
   Carried c{0, 0, EV_DESTROY, VIRT_K0, 1, 0};
   for (uint64_t i = ub[u + 1]; i > ub[u]; --i) {
     const hbtgpu_cs_event e = ev[i - 1];
     if (!eff[i - 1] || !is_switch(e.type)) continue;
-    if (epoch[rank[i - 1]] == final_epoch) {
+    if (epoch[rank[i - 1]] == final_epoch && !rin[i - 1]) {
       const uint8_t f = cf[i - 1];
       c.tstamp = e.tstamp;
       c.tag = e.tag;
@@ -734,7 +746,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   add(n1, 8); add(n1, 8); add(n1, 4); add(n1, 4);               // key, key_s, val, order
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);   // rank, delta, depth, start, epoch
   add(n1, 1); add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);   // eff, scan_in, prev_scan, prev, next
-  add(n1, 1); add(n1, 4); add(n1, 4);                           // cf, ecnt, eoff
+  add(n1, 1); add(n1, 4); add(n1, 4); add(n1, 1);               // cf, ecnt, eoff, rin
   add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8);  // entries + sorted
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);               // idcnt, idbase, sflag, soff
   add(n1, 32); add(n_units + 2, 8);                             // slices, slice_begin
@@ -768,6 +780,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   auto* d_cf = carve<uint8_t>(c, n1);
   auto* d_ecnt = carve<uint32_t>(c, n1);
   auto* d_eoff = carve<uint32_t>(c, n1);
+  auto* d_rin = carve<uint8_t>(c, n1);
   auto* d_ekey = carve<uint64_t>(c, 2 * n1);
   auto* d_eval = carve<uint64_t>(c, 2 * n1);
   auto* d_ekey_s = carve<uint64_t>(c, 2 * n1);
@@ -794,6 +807,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   Globals g0;
   memset(&g0, 0, sizeof(g0));
   g0.e_first[0] = g0.e_first[1] = g0.a_first[0] = g0.a_first[1] = NOIDX;
+  g0.cand = NOIDX;
   g0.depth0 = c->depth;
   g0.last_ts0 = c->last_ts;
   g0.have = (c->e_id[0] != NONE64 ? 1u : 0u) | (c->e_id[1] != NONE64 ? 2u : 0u) | (c->a_id[0] != NONE64 ? 4u : 0u) |
@@ -818,12 +832,29 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   k_sl_effective<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_depth, d_delta, d_eff, d_scan_in, d_g);
   t = tmp_bytes;
   cub::DeviceScan::ExclusiveScan(d_tmp, t, d_scan_in, d_prev_scan, MaxOp(), 0u, static_cast<int>(N), st);
-  SK(cudaMemsetAsync(d_next, 0xff, static_cast<size_t>(N) * sizeof(uint32_t), st));
-  k_sl_links<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_rank, d_epoch, d_eff, d_prev_scan, d_prev, d_next, d_cf,
-                                        d_g);
-  SK(cudaGetLastError());
-  SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
-  SK(cudaStreamSynchronize(st));
+  SK(cudaMemsetAsync(d_rin, 0, static_cast<size_t>(N), st));
+  // Switch-ins on a unit whose active state is a thread reset everything (Slicer.h:839-868).  Whether
+  // one is such depends on the resets before it, so they are settled in merge order: link, take the
+  // earliest candidate, make it a reset, link again -- until none is left (rarely more than a few).
+  for (int round = 0;; ++round) {
+    SK(cudaMemsetAsync(d_next, 0xff, static_cast<size_t>(N) * sizeof(uint32_t), st));
+    k_sl_links<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_rank, d_epoch, d_eff, d_rin, d_prev_scan, d_prev,
+                                          d_next, d_cf, d_g);
+    SK(cudaGetLastError());
+    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    if (gh.bad || gh.cand == NOIDX) break;
+    if (round >= 4096) return sfail(c, -ENOTSUP, "more than 4096 switch-ins on units whose active state is a thread in one window");
+    uint32_t idx = 0;
+    const uint32_t one = 1, none = NOIDX;
+    SK(cudaMemcpyAsync(&idx, d_order + gh.cand, 4, cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    SK(cudaMemsetAsync(d_rin + idx, 1, 1, st));
+    SK(cudaMemcpyAsync(d_start + gh.cand, &one, 4, cudaMemcpyHostToDevice, st));
+    SK(cudaMemcpyAsync(&d_g->cand, &none, 4, cudaMemcpyHostToDevice, st));
+    t = tmp_bytes;
+    cub::DeviceScan::InclusiveSum(d_tmp, t, d_start, d_epoch, static_cast<int>(N), st);
+  }
   if (gh.bad) {
     const unsigned b = gh.bad;
     return sfail(c, (b & BAD_UNIT) ? -EINVAL : -ENOTSUP, "events outside the parallel form:%s%s%s%s%s%s%s",
@@ -831,7 +862,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
                  (b & BAD_ORDER) ? " a unit's events go back in time;" : "",
                  (b & BAD_UNIT) ? " comp_unit_id differs from the unit the event was filed under;" : "",
                  (b & BAD_TAG) ? " switch-in or creation without a tag;" : "",
-                 (b & BAD_DOUBLE_IN) ? " switch-in on a unit whose active state is a thread (the reference resets);" : "",
+                 (b & BAD_DOUBLE_IN) ? " (internal);" : "",
                  (b & BAD_WE_END) ? " WriteErrorsEnd without its Start;" : "");
   }
   if (gh.max_tag >= (1u << 27)) return sfail(c, -ENOTSUP, "thread ids up to %u: the per-thread tables would not fit", gh.max_tag);
@@ -866,7 +897,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   SK(cudaMemsetAsync(d_tcreate, 0xff, 2 * static_cast<size_t>(n_tags) * sizeof(uint32_t), st));
   SK(cudaMemsetAsync(d_last_epoch, 0, static_cast<size_t>(n_tags) * sizeof(uint32_t), st));
 
-  k_sl_entry_counts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_epoch, d_eff, d_next, d_ecnt);
+  k_sl_entry_counts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_epoch, d_eff, d_rin, d_next, d_ecnt);
   t = tmp_bytes;
   cub::DeviceScan::ExclusiveSum(d_tmp, t, d_ecnt, d_eoff, static_cast<int>(N), st);
   uint32_t last_off = 0, last_cnt = 0;
@@ -885,8 +916,8 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, pos_bits, d_rank, d_epoch, d_cf,
                                                       d_tcreate, c->p_flags, d_last_epoch);
   }
-  k_sl_firsts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_eff, d_cf, d_g);
-  k_sl_id_counts<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_eff, d_cf, d_g, d_idcnt);
+  k_sl_firsts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_eff, d_rin, d_cf, d_g);
+  k_sl_id_counts<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_eff, d_rin, d_cf, d_g, d_idcnt);
   t = tmp_bytes;
   cub::DeviceScan::ExclusiveSum(d_tmp, t, d_idcnt, d_idbase, static_cast<int>(N), st);
   SK(cudaGetLastError());
@@ -921,14 +952,14 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     ids.e_id[k] = c->e_id[k];
     ids.a_id[k] = c->a_id[k];
   }
-  k_sl_slice_flags<<<blocks(N), 256, 0, st>>>(ev, N, d_eff, d_prev, d_cf, d_sflag, c->p_cum, c->p_in, c->p_out, d_g);
+  k_sl_slice_flags<<<blocks(N), 256, 0, st>>>(ev, N, d_eff, d_rin, d_prev, d_cf, d_sflag, c->p_cum, c->p_in, c->p_out, d_g);
   t = tmp_bytes;
   cub::DeviceScan::ExclusiveSum(d_tmp, t, d_sflag, d_soff, static_cast<int>(N), st);
   k_sl_emit<<<blocks(N), 256, 0, st>>>(ev, N, d_prev, d_cf, d_sflag, d_soff, ids, d_slices);
   k_sl_unit_counts<<<blocks(n_units + 1), 256, 0, st>>>(d_ub, n_units, N, d_soff, d_sflag, d_slice_begin);
   // what the next window starts from
-  k_sl_final_active<<<blocks(n_units), 256, 0, st>>>(ev, d_ub, n_units, d_rank, d_epoch, d_eff, d_cf, final_epoch,
-                                                     c->d_carried);
+  k_sl_final_active<<<blocks(n_units), 256, 0, st>>>(ev, d_ub, n_units, d_rank, d_epoch, d_eff, d_rin, d_cf,
+                                                     final_epoch, c->d_carried);
   if (final_epoch > 0) k_sl_clear_dormant<<<blocks(n_tags), 256, 0, st>>>(n_tags, final_epoch, d_last_epoch, c->p_flags);
   // the stack table, by id: flag the ids that belong to a state, scan, place
   const uint32_t n_ids = static_cast<uint32_t>(c->next_id);

@@ -658,9 +658,10 @@ const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* ctx); /* t
  * have them.  stats / the stack table / last_ts are cumulative since the last fresh start.
  *
  * Scope: level-0 events (ThreadCreation / ThreadDestruction / SwitchIn / SwitchOut* /
- * WriteErrors*), every unit's events in time order, no switch-in on a unit whose active state is
- * a thread, no WriteErrorsEnd without its Start.  Input outside it is refused with -ENOTSUP and
- * a message that names the reason (there is no CPU path); comp_unit_id that differs from the
+ * WriteErrors*), every unit's events in time order, no WriteErrorsEnd without its Start.  A
+ * switch-in on a unit whose active state is a thread resets everything, as in the reference
+ * (:839-868).  Input outside the scope is refused with -ENOTSUP and a message that names the
+ * reason (there is no CPU path); comp_unit_id that differs from the
  * unit an event was filed under is -EINVAL (the reference throws, :351-352).
  */
 #define HBTGPU_SLICER_DEVICE_INPUT 0x1u /* events is a device pointer (event_begin stays host) */
