@@ -561,7 +561,7 @@ using TagStackStats = hbtgpu_stack_stats;   // Slicer.h:160-193 (stack = tags[0 
 // reference pulls events from a merged stream until stop_ts (processNext); here a window of
 // per-CPU events is handed over at once and the slices are written to the per-CPU producers
 // (anything with write(const Slice&), e.g. IntervalSlicer) exactly as completeSlice_ would
-// (Slicer.h:529-558).  Each window is a Slicer started empty.
+// (Slicer.h:529-558).  Successive windows continue each other, as the reference's one Slicer does.
 template <class TSlices>
 class Slicer {
  public:
@@ -586,9 +586,11 @@ class Slicer {
     }
     std::vector<uint64_t> n_slices(events.size());
     uint64_t n_stacks = 0;
-    const int rc = hbtgpu_slicer_run(ctx_, all.data(), begin.data(), static_cast<uint32_t>(events.size()), 0, &stats_,
-                                     n_slices.data(), &n_stacks, &last_ts_);
+    const uint64_t before = stats_.num_processed;  // the statistics are cumulative, processNext's result is not
+    const int rc = hbtgpu_slicer_run(ctx_, all.data(), begin.data(), static_cast<uint32_t>(events.size()),
+                                     started_ ? HBTGPU_SLICER_CONTINUE : 0u, &stats_, n_slices.data(), &n_stacks, &last_ts_);
     if (rc != 0) throw std::runtime_error(hbtgpu_slicer_last_error(ctx_));
+    started_ = true;
     for (size_t u = 0; u < events.size(); ++u) {
       std::vector<Slice> out(n_slices[u]);
       if (!out.empty() && hbtgpu_slicer_get_slices(ctx_, static_cast<uint32_t>(u), out.data(), out.size()) != 0)
@@ -600,7 +602,7 @@ class Slicer {
     stacks_.resize(n_stacks);
     if (n_stacks && hbtgpu_slicer_get_stacks(ctx_, stacks_.data(), n_stacks) != 0)
       throw std::runtime_error(hbtgpu_slicer_last_error(ctx_));
-    return stats_.num_processed;
+    return stats_.num_processed - before;
   }
 
   auto getSlices() { return grouped_slices_; }
@@ -615,6 +617,7 @@ class Slicer {
   SlicerStats stats_{};
   std::vector<TagStackStats> stacks_;
   TimeStamp last_ts_ = 0;
+  bool started_ = false;
 };
 
 }  // namespace hbtgpu_shim

@@ -286,6 +286,11 @@ int main() {
     EXPECT(s->at(0) == makeSlice(25, 5, 1, TransitionType::Analysis, TransitionType::ThreadPreempted));
     EXPECT(s->at(1) == makeSlice(30, 20, 3, TransitionType::ThreadYield, TransitionType::ThreadPreempted));
     EXPECT(s->at(2) == makeSlice(50, 5, 2, TransitionType::ThreadPreempted, TransitionType::Analysis));
+    // the next window continues: thread 4 comes back after the idle stretch that began at 80
+    events[0] = {mk(95, kIn, 4), mk(120, kOutPreempt, ~0u)};
+    EXPECT(slicer.processWindow(events) == 2);
+    EXPECT(islicer.numActiveSlices() == 6 && slicer.getStats().num_slices_completed == 7);
+    EXPECT(slicer.getTagStackStatsDump().size() == 5 && slicer.getTagStackStatsDump()[3].num_swins == 2);
   }
   std::puts("SHIM OK");
   return 0;
