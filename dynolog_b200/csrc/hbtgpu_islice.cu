@@ -54,6 +54,9 @@
 #include <string>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
 #include "hbtgpu.h"
 
 namespace {
@@ -968,9 +971,30 @@ __global__ void k_bin_compact(BinTable t, BinEntry* __restrict__ list, unsigned 
   const unsigned long long at = atomicAdd(&counters[2], 1ull);
   list[at] = BinEntry{h == t.cap ? NONE : t.key[h] - 1, t.dur[h], t.obs[h], t.nint[h], h, 0};
 }
-__global__ void k_bin_set_bids(BinTable t, const uint32_t* __restrict__ slot, const uint32_t* __restrict__ bid, uint32_t n) {
+// the dictionary in stack-id order: sort keys, then bins by an exclusive sum over "gets a bin of
+// its own" (BinMapper, MonData.h:539-557; bin 0 = ignored_bid)
+__global__ void k_bin_keys(const BinEntry* __restrict__ list, uint32_t n, uint64_t* __restrict__ key, uint32_t* __restrict__ val) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) t.bid[slot[i]] = bid[i];
+  if (i >= n) return;
+  key[i] = list[i].stack_id;
+  val[i] = i;
+}
+__global__ void k_bin_own(const BinEntry* __restrict__ list, const uint32_t* __restrict__ order, uint32_t n,
+                          uint64_t min_intervals, uint64_t min_duration, uint32_t* __restrict__ own) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const BinEntry e = list[order[i]];
+  own[i] = e.num_intervals >= min_intervals && e.duration >= min_duration;
+}
+__global__ void k_bin_number(BinTable t, const BinEntry* __restrict__ list, const uint32_t* __restrict__ order, uint32_t n,
+                             const uint32_t* __restrict__ own, const uint32_t* __restrict__ own_before,
+                             hbtgpu_bin_freq* __restrict__ freqs) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const BinEntry e = list[order[i]];
+  const uint32_t bid = own[i] ? 1 + own_before[i] : 0;
+  t.bid[e.slot] = bid;
+  freqs[i] = hbtgpu_bin_freq{e.stack_id, e.duration, e.num_obs, e.num_intervals, bid, 0};
 }
 
 // (unit, tile of NT intervals): M[row][bin] += duration
@@ -1037,7 +1061,7 @@ struct hbtgpu_islice_ctx {
   unsigned long long* d_bin_M = nullptr; size_t cap_bin_M = 0;
   unsigned long long* d_bin_ctr = nullptr; size_t cap_bin_ctr = 0;
   uint8_t* d_sel = nullptr;          size_t cap_sel = 0;
-  std::vector<hbtgpu_bin_freq> bin_freqs;
+  hbtgpu_bin_freq* d_bin_freqs = nullptr; size_t cap_bin_freqs = 0;
   hbtgpu_bin_summary bin_summary{};
   bool have_bin = false;
   // last call
@@ -1114,7 +1138,7 @@ void hbtgpu_islice_destroy(hbtgpu_islice_ctx* c) {
   cudaFree(c->d_rt_tot); cudaFree(c->d_rt_base); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_ql); cudaFree(c->d_tmp); cudaFree(c->d_ioff); cudaFree(c->d_icnt); cudaFree(c->d_ifirst);
   cudaFree(c->d_out); cudaFree(c->d_units); cudaFree(c->d_ustate); cudaFree(c->d_res); cudaFree(c->d_base);
   cudaFree(c->d_bin_tab); cudaFree(c->d_bin_bid); cudaFree(c->d_has); cudaFree(c->d_bt_tot); cudaFree(c->d_bt_base);
-  cudaFree(c->d_bin_list); cudaFree(c->d_bin_up); cudaFree(c->d_bin_M); cudaFree(c->d_bin_ctr); cudaFree(c->d_sel);
+  cudaFree(c->d_bin_list); cudaFree(c->d_bin_up); cudaFree(c->d_bin_freqs); cudaFree(c->d_bin_M); cudaFree(c->d_bin_ctr); cudaFree(c->d_sel);
   for (cudaEvent_t e : {c->ev0, c->ev1, c->ev2, c->ev3})
     if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -1402,23 +1426,45 @@ int hbtgpu_islice_bin(hbtgpu_islice_ctx* c, const uint8_t* unit_selected, uint64
   IK(cudaStreamSynchronize(c->stream));
   if (ctr[0] || ctr[2] > max_stack_ids)
     return ifail(c, -ENOSPC, "more than max_stack_ids = %llu distinct stack ids", (unsigned long long)max_stack_ids);
-  std::vector<BinEntry> list(ctr[2]);
-  if (!list.empty())
-    IK(cudaMemcpy(list.data(), c->d_bin_list, list.size() * sizeof(BinEntry), cudaMemcpyDeviceToHost));
-  std::sort(list.begin(), list.end(), [](const BinEntry& a, const BinEntry& b) { return a.stack_id < b.stack_id; });
-  // BinMapper: bin 0 = ignored_bid, then one bin per stack id that qualifies (MonData.h:539-557),
-  // in ascending stack_id order (the reference walks a std::unordered_map: any order)
-  c->bin_freqs.resize(list.size());
-  std::vector<uint32_t> up(2 * list.size() + 2);
-  uint32_t next_bid = 1;
-  for (size_t i = 0; i < list.size(); ++i) {
-    const bool own = list[i].num_intervals >= min_distinct_intervals && list[i].duration >= min_duration;
-    const uint32_t bid = own ? next_bid++ : 0u;
-    c->bin_freqs[i] = hbtgpu_bin_freq{list[i].stack_id, list[i].duration, list[i].num_obs, list[i].num_intervals, bid, 0};
-    up[i] = list[i].slot;
-    up[list.size() + i] = bid;
+  // the dictionary in stack-id order and the bin numbers, on the device
+  const uint32_t n_ids = static_cast<uint32_t>(ctr[2]);
+  size_t tmp_sort = 0, tmp_scan = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
+                                  static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(n_ids), 0, 64,
+                                  c->stream);
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp_scan, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr),
+                                static_cast<int>(n_ids), c->stream);
+  const size_t n8 = (static_cast<size_t>(n_ids) + 32) & ~static_cast<size_t>(31);
+  // scratch: keys, sorted keys (u64), val, order, own, own_before (u32), cub's
+  const size_t words = 2 * n8 + 2 * n8 + (std::max(tmp_sort, tmp_scan) + 7) / 8 + 8;
+  if (int rc = grow(c, &c->d_bin_up, &c->cap_bin_up, 2 * words)) return rc;  // (u32 elements: 8 bytes per word)
+  uint64_t* w = reinterpret_cast<uint64_t*>(c->d_bin_up);
+  uint64_t* d_key = w;
+  uint64_t* d_key_s = w + n8;
+  uint32_t* d_val = reinterpret_cast<uint32_t*>(w + 2 * n8);
+  uint32_t* d_order = d_val + n8;
+  uint32_t* d_own = d_order + n8;
+  uint32_t* d_before = d_own + n8;
+  void* d_cub = w + 4 * n8;
+  if (int rc = grow(c, &c->d_bin_freqs, &c->cap_bin_freqs, static_cast<size_t>(n_ids) + 1)) return rc;
+  uint32_t last_own[2] = {0, 0};
+  if (n_ids) {
+    size_t tb = std::max(tmp_sort, tmp_scan);
+    k_bin_keys<<<(n_ids + 255) / 256, 256, 0, c->stream>>>(c->d_bin_list, n_ids, d_key, d_val);
+    cub::DeviceRadixSort::SortPairs(d_cub, tb, d_key, d_key_s, d_val, d_order, static_cast<int>(n_ids), 0, 64, c->stream);
+    k_bin_own<<<(n_ids + 255) / 256, 256, 0, c->stream>>>(c->d_bin_list, d_order, n_ids, min_distinct_intervals,
+                                                         min_duration, d_own);
+    tb = std::max(tmp_sort, tmp_scan);
+    cub::DeviceScan::ExclusiveSum(d_cub, tb, d_own, d_before, static_cast<int>(n_ids), c->stream);
+    k_bin_number<<<(n_ids + 255) / 256, 256, 0, c->stream>>>(t, c->d_bin_list, d_order, n_ids, d_own, d_before,
+                                                            c->d_bin_freqs);
+    IK(cudaGetLastError());
+    IK(cudaMemcpyAsync(&last_own[0], d_own + (n_ids - 1), 4, cudaMemcpyDeviceToHost, c->stream));
+    IK(cudaMemcpyAsync(&last_own[1], d_before + (n_ids - 1), 4, cudaMemcpyDeviceToHost, c->stream));
+    IK(cudaStreamSynchronize(c->stream));
   }
-  c->bin_summary = hbtgpu_bin_summary{num_rows, next_bid, list.size(), ctr[1]};
+  const uint32_t next_bid = 1 + last_own[0] + last_own[1];
+  c->bin_summary = hbtgpu_bin_summary{num_rows, next_bid, n_ids, ctr[1]};
   if (summary) *summary = c->bin_summary;
   const unsigned long long cells = static_cast<unsigned long long>(num_rows) * next_bid;
   if (cells * 8 > max_matrix_bytes)
@@ -1426,22 +1472,13 @@ int hbtgpu_islice_bin(hbtgpu_islice_ctx* c, const uint8_t* unit_selected, uint64
                  (unsigned long long)num_rows, next_bid);
   if (int rc = grow(c, &c->d_bin_M, &c->cap_bin_M, cells + 1)) return rc;
   IK(cudaMemsetAsync(c->d_bin_M, 0, (cells + 1) * sizeof(unsigned long long), c->stream));
-  if (!list.empty()) {
-    if (int rc = grow(c, &c->d_bin_up, &c->cap_bin_up, up.size())) return rc;
-    IK(cudaMemcpyAsync(c->d_bin_up, up.data(), up.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-    IK(cudaEventRecord(c->ev2, c->stream));
-    k_bin_set_bids<<<static_cast<unsigned>((list.size() + 255) / 256), 256, 0, c->stream>>>(
-        t, c->d_bin_up, c->d_bin_up + list.size(), static_cast<uint32_t>(list.size()));
-    if (n_rt)
-      k_bin_durations<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(c->d_units, n_units, c->d_res, d_sel, c->d_out,
-                                                                         c->d_ioff, c->d_icnt, t, c->d_has,
-                                                                         c->d_bt_base, c->d_bin_M, next_bid);
-    IK(cudaGetLastError());
-    IK(cudaEventRecord(c->ev3, c->stream));
-  } else {
-    IK(cudaEventRecord(c->ev2, c->stream));
-    IK(cudaEventRecord(c->ev3, c->stream));
-  }
+  IK(cudaEventRecord(c->ev2, c->stream));
+  if (n_ids && n_rt)
+    k_bin_durations<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(c->d_units, n_units, c->d_res, d_sel, c->d_out,
+                                                                       c->d_ioff, c->d_icnt, t, c->d_has, c->d_bt_base,
+                                                                       c->d_bin_M, next_bid);
+  IK(cudaGetLastError());
+  IK(cudaEventRecord(c->ev3, c->stream));
   IK(cudaStreamSynchronize(c->stream));
   float a = 0.f, b = 0.f;
   IK(cudaEventElapsedTime(&a, c->ev0, c->ev1));
@@ -1457,9 +1494,10 @@ int hbtgpu_islice_bin_get(hbtgpu_islice_ctx* c, hbtgpu_bin_freq* freqs, uint64_t
   if (!c->have_bin) return ifail(c, -EINVAL, "no matrix: call hbtgpu_islice_bin first");
   IK(cudaSetDevice(c->device));
   if (freqs) {
-    if (freq_cap < c->bin_freqs.size()) return ifail(c, -ENOSPC, "%zu stack ids, room for %llu", c->bin_freqs.size(),
-                                                     (unsigned long long)freq_cap);
-    if (!c->bin_freqs.empty()) memcpy(freqs, c->bin_freqs.data(), c->bin_freqs.size() * sizeof(hbtgpu_bin_freq));
+    const uint64_t nf = c->bin_summary.num_stack_ids;
+    if (freq_cap < nf) return ifail(c, -ENOSPC, "%llu stack ids, room for %llu", (unsigned long long)nf,
+                                    (unsigned long long)freq_cap);
+    if (nf) IK(cudaMemcpy(freqs, c->d_bin_freqs, nf * sizeof(hbtgpu_bin_freq), cudaMemcpyDeviceToHost));
   }
   if (durations) {
     const uint64_t cells = c->bin_summary.num_rows * c->bin_summary.num_bins;
