@@ -118,9 +118,10 @@ __global__ void k_sl_prepare(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
     if ((m >> ((threadIdx.x & 31) ^ o)) & 1u) wts = max(wts, other);
   }
   if ((threadIdx.x & 31) == __ffs(m) - 1) {
-    if (wbad) atomicOr(&g->bad, wbad);
-    if (wmax) atomicMax(&g->max_tag, wmax);
-    atomicMax(&g->max_ts, static_cast<unsigned long long>(wts));
+    // (plain reads as a filter: most warps have nothing new to report)
+    if (wbad & ~g->bad) atomicOr(&g->bad, wbad);
+    if (wmax > g->max_tag) atomicMax(&g->max_tag, wmax);
+    if (wts > g->max_ts) atomicMax(&g->max_ts, static_cast<unsigned long long>(wts));
   }
 }
 
@@ -320,10 +321,10 @@ __global__ void k_sl_firsts(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, 
   a0 = __reduce_min_sync(0xffffffffu, a0);
   a1 = __reduce_min_sync(0xffffffffu, a1);
   if ((threadIdx.x & 31) == 0) {
-    if (e0 != NOIDX) atomicMin(&g->e_first[0], e0);
-    if (e1 != NOIDX) atomicMin(&g->e_first[1], e1);
-    if (a0 != NOIDX) atomicMin(&g->a_first[0], a0);
-    if (a1 != NOIDX) atomicMin(&g->a_first[1], a1);
+    if (e0 < g->e_first[0]) atomicMin(&g->e_first[0], e0);
+    if (e1 < g->e_first[1]) atomicMin(&g->e_first[1], e1);
+    if (a0 < g->a_first[0]) atomicMin(&g->a_first[0], a0);
+    if (a1 < g->a_first[1]) atomicMin(&g->a_first[1], a1);
   }
 }
 
@@ -404,8 +405,12 @@ __global__ void k_sl_slice_flags(const hbtgpu_cs_event* __restrict__ ev, uint32_
     }
   }
   if (i < n) sflag[i] = fl;
-  // The empty stack and tid 0 take half of all updates: one atomic per warp for those four slots,
-  // one per event for the thread states (spread over the table).
+  // The empty stack and tid 0 take half of all updates: those four slots are summed per warp, then
+  // per block in shared memory, and reach global memory once per block; the thread states (spread
+  // over the table) take one atomic per event.
+  __shared__ unsigned long long sh_acc[13];  // cum[4], in[4], out[4], completed
+  if (threadIdx.x < 13) sh_acc[threadIdx.x] = 0;
+  __syncthreads();
   const int lane = threadIdx.x & 31;
 #pragma unroll
   for (uint32_t s = 0; s < 4; ++s) {
@@ -414,11 +419,11 @@ __global__ void k_sl_slice_flags(const hbtgpu_cs_event* __restrict__ ev, uint32_
       uint64_t d = out_slot == s ? dur : 0;
       for (int o = 16; o; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
       if (lane == 0) {
-        if (d) atomicAdd(&st_cum[s], static_cast<unsigned long long>(d));
-        atomicAdd(&st_out[s], static_cast<unsigned long long>(__popc(b_out)));
+        if (d) atomicAdd(&sh_acc[s], static_cast<unsigned long long>(d));
+        atomicAdd(&sh_acc[8 + s], static_cast<unsigned long long>(__popc(b_out)));
       }
     }
-    if (b_in && lane == 0) atomicAdd(&st_in[s], static_cast<unsigned long long>(__popc(b_in)));
+    if (b_in && lane == 0) atomicAdd(&sh_acc[4 + s], static_cast<unsigned long long>(__popc(b_in)));
   }
   if (in_slot != NOIDX && in_slot >= 4) atomicAdd(&st_in[in_slot], 1ull);
   if (out_slot != NOIDX && out_slot >= 4) {
@@ -426,7 +431,13 @@ __global__ void k_sl_slice_flags(const hbtgpu_cs_event* __restrict__ ev, uint32_
     atomicAdd(&st_out[out_slot], 1ull);
   }
   const unsigned b_done = __ballot_sync(0xffffffffu, out_slot != NOIDX);
-  if (b_done && lane == 0) atomicAdd(&g->n_completed, static_cast<unsigned long long>(__popc(b_done)));
+  if (b_done && lane == 0) atomicAdd(&sh_acc[12], static_cast<unsigned long long>(__popc(b_done)));
+  __syncthreads();
+  if (threadIdx.x < 13 && sh_acc[threadIdx.x]) {
+    const int j = threadIdx.x;
+    unsigned long long* dst = j < 4 ? &st_cum[j] : (j < 8 ? &st_in[j - 4] : (j < 12 ? &st_out[j - 8] : &g->n_completed));
+    atomicAdd(dst, sh_acc[j]);
+  }
 }
 
 // (6b) the slices, unit after unit (the exclusive sum of the flags is their place)
