@@ -847,6 +847,24 @@ int hbtgpu_get_rows(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* rows, size_t cap_ro
   return 0;
 }
 
+int hbtgpu_rows_device(hbtgpu_ctx* ctx, const uint64_t** rows, uint64_t* row_begin, uint32_t* row_stride) {
+  if (!ctx || !rows || !row_begin) return -EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  if (int r = ensure_emitted(ctx)) return r;
+  // the row table is dense, stream after stream in cpu order (the chunks are laid out that way)
+  uint64_t run = 0;
+  for (uint32_t cpu = 0; cpu < ctx->cfg.max_cpus; ++cpu) {
+    row_begin[cpu] = run;
+    if (ctx->stream_rows[cpu] && ctx->stream_row_base[cpu] != run)
+      return fail(ctx, -ENOTSUP, "rows of cpu %u are not where the dense layout puts them", cpu);
+    run += ctx->stream_rows[cpu];
+  }
+  row_begin[ctx->cfg.max_cpus] = run;
+  *rows = ctx->d_rows;
+  if (row_stride) *row_stride = ctx->cfg.n_events + 2;
+  return 0;
+}
+
 int hbtgpu_get_records(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* off, uint32_t* type, uint32_t* size,
                        size_t cap, size_t* n_records) {
   if (!ctx || !n_records) return -EINVAL;

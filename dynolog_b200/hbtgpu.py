@@ -87,7 +87,7 @@ class Stats(C.Structure):
 ABI_SYMBOLS = [
     "hbtgpu_create", "hbtgpu_destroy", "hbtgpu_last_error", "hbtgpu_set_carry",
     "hbtgpu_submit_image", "hbtgpu_submit_images", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
-    "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows",
+    "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows", "hbtgpu_rows_device",
     "hbtgpu_get_records", "hbtgpu_get_tid_histogram", "hbtgpu_get_top_ips",
     "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_get_buckets_host_async",
     "hbtgpu_derive",
@@ -276,6 +276,14 @@ class Context:
             self._ck(self.L.hbtgpu_get_rows(self.h, C.c_uint32(cpu), _ptr(out),
                                             C.c_size_t(n.value), C.byref(n)))
         return out
+
+    def rows_device(self):
+        """(device pointer, host row_begin [max_cpus + 1], words per row) of the row table."""
+        ptr = C.c_void_p(0)
+        begin = np.zeros(self.max_cpus + 1, np.uint64)
+        stride = C.c_uint32(0)
+        self._ck(self.L.hbtgpu_rows_device(self.h, C.byref(ptr), C.c_void_p(begin.ctypes.data), C.byref(stride)))
+        return ptr.value, begin, stride.value
 
     def records(self, cpu):
         n = C.c_size_t(0)

@@ -193,6 +193,11 @@ int hbtgpu_get_carry(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_carry* out);
  * consumer callback shape hbt/src/mon/TraceMonitor.h:35-108).  *n_rows is
  * set to the number available; at most `cap_rows` are copied. */
 int hbtgpu_get_rows(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* rows, size_t cap_rows, size_t* n_rows);
+/* The same rows where they were written, for consumers on the GPU (hbtgpu_islice_release with
+ * HBTGPU_ISLICE_DEVICE_INPUT): cpu c's rows are rows[row_begin[c] .. row_begin[c+1]), n_events + 2
+ * words each.  *rows is a device pointer; row_begin is a HOST array of max_cpus + 1 entries that
+ * the call fills.  Valid until the next hbtgpu_run / hbtgpu_reset. */
+int hbtgpu_rows_device(hbtgpu_ctx* ctx, const uint64_t** rows, uint64_t* row_begin, uint32_t* row_stride);
 
 /* Record table of one cpu: (stream byte offset, type, size) of every record the
  * walk visits, in order -- what consume()'s loop steps through (:1415-1572). */

@@ -86,3 +86,42 @@ def test_images_to_bins():
         assert row_sums[: int((uc[0] > 0).sum())].all()
     finally:
         isl.close()
+
+
+def test_rows_and_slices_meet_on_the_device():
+    """Count rows (hbtgpu_rows_device) and slices (hbtgpu_slicer_slices_device) go into
+    hbtgpu_islice_release as device pointers: nothing but summaries crosses PCIe."""
+    from dynolog_b200 import hbtgpu
+    n_cpus = 5
+    dec = hbtgpu_cs.decode(synth.cs_capture(n_cpus, 128 * 1024, n_tids=50, life_ppm=10000, comm_ppm=0, lost_ppm=500,
+                                            throttle_ppm=0, seed=9), tid_level=0)
+    spec, streams = synth.capture(1, n_cpus, n_samples=300)
+    total = sum(len(s) for s in streams)
+    ctx = hbtgpu.Context(n_events=spec.n_events, max_cpus=n_cpus, arena_bytes=total + 4096 * (n_cpus + 8) + (1 << 16))
+    gsl, isl = gs.Slicer(0), gs.IntervalSlicer(0)
+    try:
+        for cpu, s in enumerate(streams):
+            ctx.submit_image(cpu, s)
+        ctx.run()
+        ctx.sync()
+        d_rows, row_begin, stride = ctx.rows_device()
+        assert stride == spec.n_events + 2 and row_begin[-1] > 250 * n_cpus
+        got_sl = gsl.run(dec["events"])
+        d_slices, _ = gsl.slices_device()
+        sb = np.concatenate([[0], np.cumsum(got_sl["n_slices"])]).astype(np.uint64)
+        marks = np.zeros(n_cpus, np.uint64)
+        flags = po.TRIM | po.ABORT_ON_MISSING
+        units = isl.release_device(d_slices, sb, d_rows, stride, row_begin, 2**63, flags, marks)
+        assert (units["status"] == 0).all()
+        for u in range(n_cpus):
+            rows = ctx.rows(u)
+            assert len(rows) == row_begin[u + 1] - row_begin[u]
+            exp = po.islice_release("port", got_sl["slices"][u], rows, 2**63, flags, 0)
+            counts, out = isl.get(u)
+            assert np.array_equal(counts, exp["counts"]) and po.slices_as_tuples(out) == po.slices_as_tuples(exp["slices"])
+            assert marks[u] == exp["mark"]
+        assert units["n_slices"].sum() > 500
+    finally:
+        gsl.close()
+        isl.close()
+        ctx.close()
