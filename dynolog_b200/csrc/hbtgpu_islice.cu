@@ -881,7 +881,12 @@ __device__ __forceinline__ uint32_t bin_slot_insert(const BinTable& t, uint64_t 
   const unsigned long long k = sid + 1;
   uint32_t h = bin_hash(sid, t.cap - 1);
   for (uint32_t probe = 0; probe < t.cap; ++probe) {
-    const unsigned long long cur = t.key[h];
+    unsigned long long cur = t.key[h];
+    if (cur == k) return h;
+    // an empty slot may be a stale L1 line (cached before the id was inserted; slots never change
+    // once set): look again past L1 before going to the atomicCAS, or every later look-up of a hot
+    // id on this SM would end in one
+    if (cur == 0) cur = __ldcg(&t.key[h]);
     if (cur == k) return h;
     if (cur == 0) {
       const unsigned long long old = atomicCAS(&t.key[h], 0ull, k);
@@ -899,42 +904,99 @@ __device__ __forceinline__ uint32_t bin_slot_find(const BinTable& t, uint64_t si
   return h;
 }
 
-// (unit, tile of NT intervals): frequencies; which intervals have a duration; tile counts
+// (unit, tile of NT intervals): frequencies; which intervals have a duration; tile counts.
+// A few stack ids (the idle stack, tid 0) take a large share of all slices: updates go through a
+// direct-mapped cache in shared memory (slot -> sums) that is flushed once per block, so a hot id
+// costs one global atomic per block instead of one per slice; ids that lose their cache line to
+// another id go to global memory directly.
+constexpr uint32_t BIN_CACHE = 256;
 __global__ void __launch_bounds__(NT)
 k_bin_freqs(const Unit* __restrict__ units, uint32_t n_units, const hbtgpu_islice_unit* __restrict__ results,
             const uint8_t* __restrict__ selected, const hbtgpu_slice* __restrict__ out_all,
             const uint32_t* __restrict__ ioff_all, const uint32_t* __restrict__ icnt_all, BinTable t,
             uint8_t* __restrict__ has_all, uint32_t* __restrict__ bt_tot, unsigned long long* __restrict__ counters) {
+  __shared__ uint32_t c_slot[BIN_CACHE];
+  __shared__ unsigned long long c_dur[BIN_CACHE];
+  __shared__ uint32_t c_obs[BIN_CACHE], c_nint[BIN_CACHE];
   const uint32_t u = find_unit<true>(units, n_units, blockIdx.x);
   if (selected && !selected[u]) return;
+  for (uint32_t h = threadIdx.x; h < BIN_CACHE; h += NT) {
+    c_slot[h] = 0xffffffffu;
+    c_dur[h] = 0;
+    c_obs[h] = c_nint[h] = 0;
+  }
+  __syncthreads();
   const Unit U = units[u];
   const uint64_t k = static_cast<uint64_t>(blockIdx.x - U.rt0) * NT + threadIdx.x;
   const bool in = k < results[u].n_intervals;
   bool has = false, empty_dur = false;
-  if (in) {
-    const uint32_t cnt = icnt_all[U.r0 + k];
-    const hbtgpu_slice* sl = out_all + U.out0 + ioff_all[U.r0 + k];
-    uint64_t row_dur = 0;
-    for (uint32_t i = 0; i < cnt; ++i) {
-      const uint64_t sid = sl[i].stack_id, d = sl[i].duration;
-      const uint32_t slot = bin_slot_insert(t, sid);
+  const uint32_t cnt = in ? icnt_all[U.r0 + k] : 0u;
+  const hbtgpu_slice* sl = in ? out_all + U.out0 + ioff_all[U.r0 + k] : nullptr;
+  uint64_t row_dur = 0;
+  bool full = false;
+  // the lanes of a warp walk their intervals in step; lanes that meet the same stack id in a
+  // step (the idle stack, mostly) add up first (__match_any_sync, __reduce_add_sync over the
+  // peers) and send one update
+  const uint32_t steps = __reduce_max_sync(0xffffffffu, cnt);
+  for (uint32_t i = 0; i < steps; ++i) {
+    uint32_t slot = 0xffffffffu;
+    uint64_t d = 0;
+    uint32_t first = 0;
+    if (i < cnt && !full) {
+      const uint64_t sid = sl[i].stack_id;
+      d = sl[i].duration;
+      slot = bin_slot_insert(t, sid);
       if (slot == 0xffffffffu) {
         atomicOr(&counters[0], 1ull);
-        break;
+        full = true;
+      } else {
+        bool seen = false;  // the reference's per-interval std::set (:243-252)
+        for (uint32_t j = 0; j < i && !seen; ++j) seen = sl[j].stack_id == sid;
+        first = !seen;
+        row_dur += d;
       }
-      if (d) atomicAdd(&t.dur[slot], static_cast<unsigned long long>(d));
-      atomicAdd(&t.obs[slot], 1ull);
-      bool seen = false;  // the reference's per-interval std::set (:243-252)
-      for (uint32_t j = 0; j < i && !seen; ++j) seen = sl[j].stack_id == sid;
-      if (!seen) atomicAdd(&t.nint[slot], 1ull);
-      row_dur += d;
     }
+    const unsigned peers = __match_any_sync(0xffffffffu, slot);
+    // 64-bit sum over the peers from three 24-bit limbs (at most 32 terms each)
+    const uint32_t s0 = __reduce_add_sync(peers, static_cast<uint32_t>(d & 0xffffffu));
+    const uint32_t s1 = __reduce_add_sync(peers, static_cast<uint32_t>((d >> 24) & 0xffffffu));
+    const uint32_t s2 = __reduce_add_sync(peers, static_cast<uint32_t>(d >> 48));
+    const uint32_t n_first = __reduce_add_sync(peers, first);
+    if (slot != 0xffffffffu && (threadIdx.x & 31) == static_cast<uint32_t>(__ffs(peers) - 1)) {
+      const unsigned long long dsum = static_cast<unsigned long long>(s0) + (static_cast<unsigned long long>(s1) << 24) +
+                                      (static_cast<unsigned long long>(s2) << 48);
+      const uint32_t n_obs = __popc(peers);
+      const uint32_t h = slot & (BIN_CACHE - 1);
+      uint32_t owner = c_slot[h];
+      if (owner == 0xffffffffu) {
+        owner = atomicCAS(&c_slot[h], 0xffffffffu, slot);
+        if (owner == 0xffffffffu) owner = slot;
+      }
+      if (owner == slot) {
+        if (dsum) atomicAdd(&c_dur[h], dsum);
+        atomicAdd(&c_obs[h], n_obs);
+        if (n_first) atomicAdd(&c_nint[h], n_first);
+      } else {
+        if (dsum) atomicAdd(&t.dur[slot], dsum);
+        atomicAdd(&t.obs[slot], static_cast<unsigned long long>(n_obs));
+        if (n_first) atomicAdd(&t.nint[slot], static_cast<unsigned long long>(n_first));
+      }
+    }
+  }
+  if (in) {
     has = row_dur != 0;
     empty_dur = cnt != 0 && !has;
     has_all[U.r0 + k] = has;
   }
   const int n_has = __syncthreads_count(has);
   const int n_skipped = __syncthreads_count(empty_dur);
+  for (uint32_t h = threadIdx.x; h < BIN_CACHE; h += NT) {
+    const uint32_t slot = c_slot[h];
+    if (slot == 0xffffffffu) continue;
+    if (c_dur[h]) atomicAdd(&t.dur[slot], c_dur[h]);
+    if (c_obs[h]) atomicAdd(&t.obs[slot], static_cast<unsigned long long>(c_obs[h]));
+    if (c_nint[h]) atomicAdd(&t.nint[slot], static_cast<unsigned long long>(c_nint[h]));
+  }
   if (threadIdx.x == 0) {
     bt_tot[blockIdx.x] = n_has;
     if (n_skipped) atomicAdd(&counters[1], static_cast<unsigned long long>(n_skipped));
