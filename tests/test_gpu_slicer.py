@@ -181,3 +181,34 @@ def test_windows_continue_each_other(slicer, kw):
         compare(got, exp)
         done += 1
     assert done > 10
+
+
+def test_large_capture(slicer):
+    """64 CPUs x 2 MiB of thread-switch records (4 M events, ~170 k thread ids, LOST windows): every
+    slice and the whole stack table against the restatement; in two windows as well."""
+    n_cpus = 64
+    streams = synth.cs_capture(n_cpus, 2 << 20, n_tids=4096, life_ppm=2000, comm_ppm=0, lost_ppm=50,
+                               throttle_ppm=0, seed=11)
+    units = hbtgpu_cs.decode(streams, tid_level=0, device_dictionary=True)["events"]
+    merged = np.concatenate(units)
+    merged = merged[np.lexsort((merged["comp_unit_id"], merged["tstamp"]))]
+    exp = po.slicer_run("port", merged, n_cpus)
+    assert exp["rc"] == 0 and len(merged) > 3_000_000
+    got = slicer.run(units)
+    for u in range(n_cpus):
+        for k in ("tstamp", "duration", "stack_id", "swin_type", "swout_type"):
+            assert np.array_equal(got["slices"][u][k], exp["slices"][u][k]), (u, k)
+    assert got["stats"] == exp["stats"] and got["last_ts"] == exp["last_ts"]
+    for k in ("stack_id", "parent_stack_id", "num_set_tags", "known_num_levels", "cum_active_time", "num_swins", "num_swouts"):
+        assert np.array_equal(got["stacks"][k], exp["stacks"][k]), k
+    # the same capture cut in the middle
+    cut = int(np.median(merged["tstamp"]))
+    first = slicer.run([u_[u_["tstamp"] < cut] for u_ in units])
+    second = slicer.run([u_[u_["tstamp"] >= cut] for u_ in units], cont=True)
+    for u in range(n_cpus):
+        both = np.concatenate([first["slices"][u], second["slices"][u]])
+        for k in ("tstamp", "duration", "stack_id", "swin_type", "swout_type"):
+            assert np.array_equal(both[k], exp["slices"][u][k]), (u, k)
+    assert second["stats"] == exp["stats"]
+    for k in ("stack_id", "cum_active_time", "num_swins", "num_swouts"):
+        assert np.array_equal(second["stacks"][k], exp["stacks"][k]), k
