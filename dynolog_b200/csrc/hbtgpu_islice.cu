@@ -1031,6 +1031,7 @@ __global__ void k_bin_compact(BinTable t, BinEntry* __restrict__ list, unsigned 
   const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
   if (h > t.cap || t.key[h] == 0) return;
   const unsigned long long at = atomicAdd(&counters[2], 1ull);
+  atomicMax(&counters[3], h == t.cap ? NONE : t.key[h] - 1);  // largest stack id: how many bits the sort needs
   list[at] = BinEntry{h == t.cap ? NONE : t.key[h] - 1, t.dur[h], t.obs[h], t.nint[h], h, 0};
 }
 // the dictionary in stack-id order: sort keys, then bins by an exclusive sum over "gets a bin of
@@ -1513,7 +1514,10 @@ int hbtgpu_islice_bin(hbtgpu_islice_ctx* c, const uint8_t* unit_selected, uint64
   if (n_ids) {
     size_t tb = std::max(tmp_sort, tmp_scan);
     k_bin_keys<<<(n_ids + 255) / 256, 256, 0, c->stream>>>(c->d_bin_list, n_ids, d_key, d_val);
-    cub::DeviceRadixSort::SortPairs(d_cub, tb, d_key, d_key_s, d_val, d_order, static_cast<int>(n_ids), 0, 64, c->stream);
+    int sid_bits = 1;
+    while (sid_bits < 64 && (ctr[3] >> sid_bits) != 0) ++sid_bits;
+    cub::DeviceRadixSort::SortPairs(d_cub, tb, d_key, d_key_s, d_val, d_order, static_cast<int>(n_ids), 0, sid_bits,
+                                    c->stream);
     k_bin_own<<<(n_ids + 255) / 256, 256, 0, c->stream>>>(c->d_bin_list, d_order, n_ids, min_distinct_intervals,
                                                          min_duration, d_own);
     tb = std::max(tmp_sort, tmp_scan);

@@ -175,14 +175,17 @@ class IntervalSlicer:
         self._check(self.L.hbtgpu_islice_bin(self.h, None if sel is None else sel.ctypes.data,
                                              min_distinct_intervals, min_duration, max_stack_ids, max_matrix_bytes,
                                              C.byref(summ)))
+        out = {"num_rows": summ.num_rows, "num_bins": summ.num_bins, "num_stack_ids": summ.num_stack_ids,
+               "rows_skipped": summ.rows_skipped, "freqs": None, "durations": None}
+        if not fetch:  # frequencies and matrix stay on the device
+            return out
         freqs = np.zeros(max(1, summ.num_stack_ids), FREQ_DTYPE)
         cells = summ.num_rows * summ.num_bins
-        dur = np.zeros(max(1, cells), np.uint64) if fetch else None
-        self._check(self.L.hbtgpu_islice_bin_get(self.h, freqs.ctypes.data, len(freqs),
-                                                 dur.ctypes.data if fetch else None, len(dur) if fetch else 0))
-        return {"freqs": freqs[:summ.num_stack_ids],
-                "durations": dur[:cells].reshape(summ.num_rows, summ.num_bins) if fetch else None,
-                "num_rows": summ.num_rows, "num_bins": summ.num_bins, "rows_skipped": summ.rows_skipped}
+        dur = np.zeros(max(1, cells), np.uint64)
+        self._check(self.L.hbtgpu_islice_bin_get(self.h, freqs.ctypes.data, len(freqs), dur.ctypes.data, len(dur)))
+        out["freqs"] = freqs[:summ.num_stack_ids]
+        out["durations"] = dur[:cells].reshape(summ.num_rows, summ.num_bins)
+        return out
 
     @property
     def last_ms(self):

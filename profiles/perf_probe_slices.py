@@ -92,7 +92,7 @@ def main():
         ms.append(g.last_ms)
     t = float(np.mean(ms[1:]))
     n_out = int(units["n_slices"].sum())
-    print(f"bin (f1): units {Ub} intervals {len(br)/1e6:.2f} M slices {n_out/1e6:.2f} M stack ids {len(res['freqs'])} "
+    print(f"bin (f1): units {Ub} intervals {len(br)/1e6:.2f} M slices {n_out/1e6:.2f} M stack ids {res['num_stack_ids']} "
           f"matrix {res['num_rows']} x {res['num_bins']} ({res['num_rows']*res['num_bins']*8/1e9:.2f} GB)  kernels {t:.3f} ms "
           f"= {n_out/1e3/t:.0f} M slices/s (matrix memset not included)")
     from oracle import pyoracle as po_
