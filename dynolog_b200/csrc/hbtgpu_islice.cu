@@ -842,249 +842,7 @@ k_islice_pack(const Unit U, const uint32_t* __restrict__ ioff_all, const uint32_
 }
 
 
-// ==== stack-id frequencies and the interval x bin duration matrix =====
-//
-// Reference: CuMonData::stackIdFreqs (hbt/src/mon/MonData.h:236-256) summed over the units by
-// MonData::stackIdFreqs (:382-398), and binmap::TagStackIdBinner (:528-607), both loops over
-// every slice of every interval.  Here they run over the per-interval slices the release left on
-// the device: an open-addressing table stack_id -> {duration, num_obs, num_intervals} filled with
-// atomics (k_bin_freqs; "first time this stack id shows up in the interval" is a look at the
-// interval's earlier slices), the few distinct stack ids go to the host to be numbered
-// (BinMapper is a host dictionary in the reference too), and k_bin_durations adds every slice's
-// duration to M[row][bin] where row = the interval's rank among the unit's intervals whose
-// durations add up to something (every unit starts at row 0, as `unsigned i = 0` inside the
-// unit loop of :563 does).
-
-struct BinTable {
-  unsigned long long* key;   // stack_id + 1, 0 = empty; slot cap is reserved for stack_id ~0
-  unsigned long long* dur;
-  unsigned long long* obs;
-  unsigned long long* nint;
-  uint32_t* bid;
-  uint32_t cap;  // power of two
-};
-
-__device__ __forceinline__ uint32_t bin_hash(uint64_t x, uint32_t mask) {
-  x ^= x >> 30;
-  x *= 0xbf58476d1ce4e5b9ull;
-  x ^= x >> 27;
-  x *= 0x94d049bb133111ebull;
-  x ^= x >> 31;
-  return static_cast<uint32_t>(x) & mask;
-}
-// slot of sid, inserting it if absent; 0xffffffff when the table is full
-__device__ __forceinline__ uint32_t bin_slot_insert(const BinTable& t, uint64_t sid) {
-  if (sid == NONE) {
-    t.key[t.cap] = 1;  // benign race: everyone writes the same value
-    return t.cap;
-  }
-  const unsigned long long k = sid + 1;
-  uint32_t h = bin_hash(sid, t.cap - 1);
-  for (uint32_t probe = 0; probe < t.cap; ++probe) {
-    unsigned long long cur = t.key[h];
-    if (cur == k) return h;
-    // an empty slot may be a stale L1 line (cached before the id was inserted; slots never change
-    // once set): look again past L1 before going to the atomicCAS, or every later look-up of a hot
-    // id on this SM would end in one
-    if (cur == 0) cur = __ldcg(&t.key[h]);
-    if (cur == k) return h;
-    if (cur == 0) {
-      const unsigned long long old = atomicCAS(&t.key[h], 0ull, k);
-      if (old == 0 || old == k) return h;
-    }
-    h = (h + 1) & (t.cap - 1);
-  }
-  return 0xffffffffu;
-}
-__device__ __forceinline__ uint32_t bin_slot_find(const BinTable& t, uint64_t sid) {
-  if (sid == NONE) return t.cap;
-  const unsigned long long k = sid + 1;
-  uint32_t h = bin_hash(sid, t.cap - 1);
-  while (t.key[h] != k) h = (h + 1) & (t.cap - 1);
-  return h;
-}
-
-// (unit, tile of NT intervals): frequencies; which intervals have a duration; tile counts.
-// A few stack ids (the idle stack, tid 0) take a large share of all slices: updates go through a
-// direct-mapped cache in shared memory (slot -> sums) that is flushed once per block, so a hot id
-// costs one global atomic per block instead of one per slice; ids that lose their cache line to
-// another id go to global memory directly.
-constexpr uint32_t BIN_CACHE = 256;
-__global__ void __launch_bounds__(NT)
-k_bin_freqs(const Unit* __restrict__ units, uint32_t n_units, const hbtgpu_islice_unit* __restrict__ results,
-            const uint8_t* __restrict__ selected, const hbtgpu_slice* __restrict__ out_all,
-            const uint32_t* __restrict__ ioff_all, const uint32_t* __restrict__ icnt_all, BinTable t,
-            uint8_t* __restrict__ has_all, uint32_t* __restrict__ bt_tot, unsigned long long* __restrict__ counters) {
-  __shared__ uint32_t c_slot[BIN_CACHE];
-  __shared__ unsigned long long c_dur[BIN_CACHE];
-  __shared__ uint32_t c_obs[BIN_CACHE], c_nint[BIN_CACHE];
-  const uint32_t u = find_unit<true>(units, n_units, blockIdx.x);
-  if (selected && !selected[u]) return;
-  for (uint32_t h = threadIdx.x; h < BIN_CACHE; h += NT) {
-    c_slot[h] = 0xffffffffu;
-    c_dur[h] = 0;
-    c_obs[h] = c_nint[h] = 0;
-  }
-  __syncthreads();
-  const Unit U = units[u];
-  const uint64_t k = static_cast<uint64_t>(blockIdx.x - U.rt0) * NT + threadIdx.x;
-  const bool in = k < results[u].n_intervals;
-  bool has = false, empty_dur = false;
-  const uint32_t cnt = in ? icnt_all[U.r0 + k] : 0u;
-  const hbtgpu_slice* sl = in ? out_all + U.out0 + ioff_all[U.r0 + k] : nullptr;
-  uint64_t row_dur = 0;
-  bool full = false;
-  // the lanes of a warp walk their intervals in step; lanes that meet the same stack id in a
-  // step (the idle stack, mostly) add up first (__match_any_sync, __reduce_add_sync over the
-  // peers) and send one update
-  const uint32_t steps = __reduce_max_sync(0xffffffffu, cnt);
-  for (uint32_t i = 0; i < steps; ++i) {
-    uint32_t slot = 0xffffffffu;
-    uint64_t d = 0;
-    uint32_t first = 0;
-    if (i < cnt && !full) {
-      const uint64_t sid = sl[i].stack_id;
-      d = sl[i].duration;
-      slot = bin_slot_insert(t, sid);
-      if (slot == 0xffffffffu) {
-        atomicOr(&counters[0], 1ull);
-        full = true;
-      } else {
-        bool seen = false;  // the reference's per-interval std::set (:243-252)
-        for (uint32_t j = 0; j < i && !seen; ++j) seen = sl[j].stack_id == sid;
-        first = !seen;
-        row_dur += d;
-      }
-    }
-    const unsigned peers = __match_any_sync(0xffffffffu, slot);
-    // 64-bit sum over the peers from three 24-bit limbs (at most 32 terms each)
-    const uint32_t s0 = __reduce_add_sync(peers, static_cast<uint32_t>(d & 0xffffffu));
-    const uint32_t s1 = __reduce_add_sync(peers, static_cast<uint32_t>((d >> 24) & 0xffffffu));
-    const uint32_t s2 = __reduce_add_sync(peers, static_cast<uint32_t>(d >> 48));
-    const uint32_t n_first = __reduce_add_sync(peers, first);
-    if (slot != 0xffffffffu && (threadIdx.x & 31) == static_cast<uint32_t>(__ffs(peers) - 1)) {
-      const unsigned long long dsum = static_cast<unsigned long long>(s0) + (static_cast<unsigned long long>(s1) << 24) +
-                                      (static_cast<unsigned long long>(s2) << 48);
-      const uint32_t n_obs = __popc(peers);
-      const uint32_t h = slot & (BIN_CACHE - 1);
-      uint32_t owner = c_slot[h];
-      if (owner == 0xffffffffu) {
-        owner = atomicCAS(&c_slot[h], 0xffffffffu, slot);
-        if (owner == 0xffffffffu) owner = slot;
-      }
-      if (owner == slot) {
-        if (dsum) atomicAdd(&c_dur[h], dsum);
-        atomicAdd(&c_obs[h], n_obs);
-        if (n_first) atomicAdd(&c_nint[h], n_first);
-      } else {
-        if (dsum) atomicAdd(&t.dur[slot], dsum);
-        atomicAdd(&t.obs[slot], static_cast<unsigned long long>(n_obs));
-        if (n_first) atomicAdd(&t.nint[slot], static_cast<unsigned long long>(n_first));
-      }
-    }
-  }
-  if (in) {
-    has = row_dur != 0;
-    empty_dur = cnt != 0 && !has;
-    has_all[U.r0 + k] = has;
-  }
-  const int n_has = __syncthreads_count(has);
-  const int n_skipped = __syncthreads_count(empty_dur);
-  for (uint32_t h = threadIdx.x; h < BIN_CACHE; h += NT) {
-    const uint32_t slot = c_slot[h];
-    if (slot == 0xffffffffu) continue;
-    if (c_dur[h]) atomicAdd(&t.dur[slot], c_dur[h]);
-    if (c_obs[h]) atomicAdd(&t.obs[slot], static_cast<unsigned long long>(c_obs[h]));
-    if (c_nint[h]) atomicAdd(&t.nint[slot], static_cast<unsigned long long>(c_nint[h]));
-  }
-  if (threadIdx.x == 0) {
-    bt_tot[blockIdx.x] = n_has;
-    if (n_skipped) atomicAdd(&counters[1], static_cast<unsigned long long>(n_skipped));
-  }
-}
-
-// per unit: exclusive scan of the tile counts
-__global__ void __launch_bounds__(NT)
-k_bin_scan(const Unit* __restrict__ units, const hbtgpu_islice_unit* __restrict__ results,
-           const uint8_t* __restrict__ selected, const uint32_t* __restrict__ bt_tot, uint64_t* __restrict__ bt_base) {
-  __shared__ uint64_t sh_red[32];
-  if (selected && !selected[blockIdx.x]) return;
-  const Unit U = units[blockIdx.x];
-  const uint32_t n_tiles = static_cast<uint32_t>((results[blockIdx.x].n_intervals + NT - 1) / NT);
-  uint64_t carry = 0;
-  for (uint32_t i0 = 0; i0 < n_tiles; i0 += NT) {
-    const uint32_t i = i0 + threadIdx.x;
-    const uint64_t v = i < n_tiles ? bt_tot[U.rt0 + i] : 0;
-    uint64_t tot;
-    const uint64_t incl = block_incl_sum_u64(v, sh_red, &tot);
-    if (i < n_tiles) bt_base[U.rt0 + i] = carry + incl - v;
-    carry += tot;
-  }
-}
-
-// occupied slots -> a dense list (any order); the host sorts and numbers them
-struct BinEntry {
-  uint64_t stack_id, duration, num_obs, num_intervals;
-  uint32_t slot, pad;
-};
-__global__ void k_bin_compact(BinTable t, BinEntry* __restrict__ list, unsigned long long* __restrict__ counters) {
-  const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
-  if (h > t.cap || t.key[h] == 0) return;
-  const unsigned long long at = atomicAdd(&counters[2], 1ull);
-  atomicMax(&counters[3], h == t.cap ? NONE : t.key[h] - 1);  // largest stack id: how many bits the sort needs
-  list[at] = BinEntry{h == t.cap ? NONE : t.key[h] - 1, t.dur[h], t.obs[h], t.nint[h], h, 0};
-}
-// the dictionary in stack-id order: sort keys, then bins by an exclusive sum over "gets a bin of
-// its own" (BinMapper, MonData.h:539-557; bin 0 = ignored_bid)
-__global__ void k_bin_keys(const BinEntry* __restrict__ list, uint32_t n, uint64_t* __restrict__ key, uint32_t* __restrict__ val) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  key[i] = list[i].stack_id;
-  val[i] = i;
-}
-__global__ void k_bin_own(const BinEntry* __restrict__ list, const uint32_t* __restrict__ order, uint32_t n,
-                          uint64_t min_intervals, uint64_t min_duration, uint32_t* __restrict__ own) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const BinEntry e = list[order[i]];
-  own[i] = e.num_intervals >= min_intervals && e.duration >= min_duration;
-}
-__global__ void k_bin_number(BinTable t, const BinEntry* __restrict__ list, const uint32_t* __restrict__ order, uint32_t n,
-                             const uint32_t* __restrict__ own, const uint32_t* __restrict__ own_before,
-                             hbtgpu_bin_freq* __restrict__ freqs) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const BinEntry e = list[order[i]];
-  const uint32_t bid = own[i] ? 1 + own_before[i] : 0;
-  t.bid[e.slot] = bid;
-  freqs[i] = hbtgpu_bin_freq{e.stack_id, e.duration, e.num_obs, e.num_intervals, bid, 0};
-}
-
-// (unit, tile of NT intervals): M[row][bin] += duration
-__global__ void __launch_bounds__(NT)
-k_bin_durations(const Unit* __restrict__ units, uint32_t n_units, const hbtgpu_islice_unit* __restrict__ results,
-                const uint8_t* __restrict__ selected, const hbtgpu_slice* __restrict__ out_all,
-                const uint32_t* __restrict__ ioff_all, const uint32_t* __restrict__ icnt_all, BinTable t,
-                const uint8_t* __restrict__ has_all, const uint64_t* __restrict__ bt_base,
-                unsigned long long* __restrict__ M, uint64_t num_bins) {
-  __shared__ uint64_t sh_red[32];
-  const uint32_t u = find_unit<true>(units, n_units, blockIdx.x);
-  if (selected && !selected[u]) return;
-  const Unit U = units[u];
-  const uint64_t k = static_cast<uint64_t>(blockIdx.x - U.rt0) * NT + threadIdx.x;
-  const bool in = k < results[u].n_intervals;
-  const bool has = in && has_all[U.r0 + k];
-  uint64_t tot;
-  const uint64_t row = bt_base[blockIdx.x] + block_incl_sum_u64(has ? 1 : 0, sh_red, &tot) - (has ? 1 : 0);
-  if (!has) return;
-  const uint32_t cnt = icnt_all[U.r0 + k];
-  const hbtgpu_slice* sl = out_all + U.out0 + ioff_all[U.r0 + k];
-  for (uint32_t i = 0; i < cnt; ++i) {
-    const uint64_t d = sl[i].duration;
-    if (d == 0) continue;  // :581-590
-    atomicAdd(&M[row * num_bins + t.bid[bin_slot_find(t, sl[i].stack_id)]], static_cast<unsigned long long>(d));
-  }
-}
+#include "hbtgpu_islice_bin_kernels.inc"
 
 }  // namespace
 
@@ -1435,147 +1193,6 @@ int hbtgpu_islice_device_view(hbtgpu_islice_ctx* c, hbtgpu_islice_view* view) {
   return 0;
 }
 
-int hbtgpu_islice_bin(hbtgpu_islice_ctx* c, const uint8_t* unit_selected, uint64_t min_distinct_intervals,
-                      uint64_t min_duration, uint64_t max_stack_ids, uint64_t max_matrix_bytes,
-                      hbtgpu_bin_summary* summary) {
-  if (!c) return -EINVAL;
-  c->have_bin = false;
-  if (!c->have) return ifail(c, -EINVAL, "no results: call hbtgpu_islice_release first");
-  if (max_stack_ids == 0 || max_stack_ids > (1ull << 30)) return ifail(c, -EINVAL, "max_stack_ids must be in [1, 2^30]");
-  IK(cudaSetDevice(c->device));
-  const uint32_t n_units = static_cast<uint32_t>(c->units.size());
-  uint64_t num_rows = 0, total_r = 0, n_rt = 0;
-  for (uint32_t u = 0; u < n_units; ++u) {
-    total_r = std::max(total_r, c->units[u].r0 + c->units[u].K);
-    n_rt = std::max<uint64_t>(n_rt, c->units[u].rt0 + (c->units[u].K + NT - 1) / NT);
-    if (unit_selected && !unit_selected[u]) continue;
-    if (c->res[u].status != 0)
-      return ifail(c, -EINVAL, "unit %u has no valid per-interval slices (status %lld)", u, (long long)c->res[u].status);
-    num_rows += c->res[u].n_intervals;  // MonData::numCountIntervals, MonData.h:334-345
-  }
-  uint32_t cap = 64;
-  while (cap < 2 * max_stack_ids) cap <<= 1;
-  const size_t tab_words = 4 * (static_cast<size_t>(cap) + 1);
-  if (int rc = grow(c, &c->d_bin_tab, &c->cap_bin_tab, tab_words)) return rc;
-  if (int rc = grow(c, &c->d_bin_bid, &c->cap_bin_bid, static_cast<size_t>(cap) + 1)) return rc;
-  if (int rc = grow(c, &c->d_has, &c->cap_has, total_r + 1)) return rc;
-  if (int rc = grow(c, &c->d_bt_tot, &c->cap_bt_tot, n_rt + 1)) return rc;
-  if (int rc = grow(c, &c->d_bt_base, &c->cap_bt_base, n_rt + 1)) return rc;
-  if (int rc = grow(c, &c->d_bin_ctr, &c->cap_bin_ctr, 4)) return rc;
-  const uint8_t* d_sel = nullptr;
-  if (unit_selected) {
-    if (int rc = grow(c, &c->d_sel, &c->cap_sel, n_units)) return rc;
-    IK(cudaMemcpyAsync(c->d_sel, unit_selected, n_units, cudaMemcpyHostToDevice, c->stream));
-    d_sel = c->d_sel;
-  }
-  IK(cudaMemsetAsync(c->d_bin_tab, 0, tab_words * sizeof(unsigned long long), c->stream));
-  IK(cudaMemsetAsync(c->d_bin_bid, 0, (static_cast<size_t>(cap) + 1) * sizeof(uint32_t), c->stream));
-  IK(cudaMemsetAsync(c->d_bin_ctr, 0, 4 * sizeof(unsigned long long), c->stream));
-  BinTable t{c->d_bin_tab, c->d_bin_tab + (cap + 1), c->d_bin_tab + 2 * (static_cast<size_t>(cap) + 1),
-             c->d_bin_tab + 3 * (static_cast<size_t>(cap) + 1), c->d_bin_bid, cap};
-  IK(cudaEventRecord(c->ev0, c->stream));
-  if (n_rt) {
-    k_bin_freqs<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(c->d_units, n_units, c->d_res, d_sel, c->d_out,
-                                                                   c->d_ioff, c->d_icnt, t, c->d_has, c->d_bt_tot,
-                                                                   c->d_bin_ctr);
-    k_bin_scan<<<n_units, NT, 0, c->stream>>>(c->d_units, c->d_res, d_sel, c->d_bt_tot, c->d_bt_base);
-  }
-  if (int rc = grow(c, &c->d_bin_list, &c->cap_bin_list, static_cast<size_t>(cap) + 1)) return rc;
-  k_bin_compact<<<(cap + 1 + 255) / 256, 256, 0, c->stream>>>(t, c->d_bin_list, c->d_bin_ctr);
-  IK(cudaGetLastError());
-  IK(cudaEventRecord(c->ev1, c->stream));
-  unsigned long long ctr[4] = {0, 0, 0, 0};
-  IK(cudaMemcpyAsync(ctr, c->d_bin_ctr, sizeof(ctr), cudaMemcpyDeviceToHost, c->stream));
-  IK(cudaStreamSynchronize(c->stream));
-  if (ctr[0] || ctr[2] > max_stack_ids)
-    return ifail(c, -ENOSPC, "more than max_stack_ids = %llu distinct stack ids", (unsigned long long)max_stack_ids);
-  // the dictionary in stack-id order and the bin numbers, on the device
-  const uint32_t n_ids = static_cast<uint32_t>(ctr[2]);
-  size_t tmp_sort = 0, tmp_scan = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
-                                  static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(n_ids), 0, 64,
-                                  c->stream);
-  cub::DeviceScan::ExclusiveSum(nullptr, tmp_scan, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr),
-                                static_cast<int>(n_ids), c->stream);
-  const size_t n8 = (static_cast<size_t>(n_ids) + 32) & ~static_cast<size_t>(31);
-  // scratch: keys, sorted keys (u64), val, order, own, own_before (u32), cub's
-  const size_t words = 2 * n8 + 2 * n8 + (std::max(tmp_sort, tmp_scan) + 7) / 8 + 8;
-  if (int rc = grow(c, &c->d_bin_up, &c->cap_bin_up, 2 * words)) return rc;  // (u32 elements: 8 bytes per word)
-  uint64_t* w = reinterpret_cast<uint64_t*>(c->d_bin_up);
-  uint64_t* d_key = w;
-  uint64_t* d_key_s = w + n8;
-  uint32_t* d_val = reinterpret_cast<uint32_t*>(w + 2 * n8);
-  uint32_t* d_order = d_val + n8;
-  uint32_t* d_own = d_order + n8;
-  uint32_t* d_before = d_own + n8;
-  void* d_cub = w + 4 * n8;
-  if (int rc = grow(c, &c->d_bin_freqs, &c->cap_bin_freqs, static_cast<size_t>(n_ids) + 1)) return rc;
-  uint32_t last_own[2] = {0, 0};
-  if (n_ids) {
-    size_t tb = std::max(tmp_sort, tmp_scan);
-    k_bin_keys<<<(n_ids + 255) / 256, 256, 0, c->stream>>>(c->d_bin_list, n_ids, d_key, d_val);
-    int sid_bits = 1;
-    while (sid_bits < 64 && (ctr[3] >> sid_bits) != 0) ++sid_bits;
-    cub::DeviceRadixSort::SortPairs(d_cub, tb, d_key, d_key_s, d_val, d_order, static_cast<int>(n_ids), 0, sid_bits,
-                                    c->stream);
-    k_bin_own<<<(n_ids + 255) / 256, 256, 0, c->stream>>>(c->d_bin_list, d_order, n_ids, min_distinct_intervals,
-                                                         min_duration, d_own);
-    tb = std::max(tmp_sort, tmp_scan);
-    cub::DeviceScan::ExclusiveSum(d_cub, tb, d_own, d_before, static_cast<int>(n_ids), c->stream);
-    k_bin_number<<<(n_ids + 255) / 256, 256, 0, c->stream>>>(t, c->d_bin_list, d_order, n_ids, d_own, d_before,
-                                                            c->d_bin_freqs);
-    IK(cudaGetLastError());
-    IK(cudaMemcpyAsync(&last_own[0], d_own + (n_ids - 1), 4, cudaMemcpyDeviceToHost, c->stream));
-    IK(cudaMemcpyAsync(&last_own[1], d_before + (n_ids - 1), 4, cudaMemcpyDeviceToHost, c->stream));
-    IK(cudaStreamSynchronize(c->stream));
-  }
-  const uint32_t next_bid = 1 + last_own[0] + last_own[1];
-  c->bin_summary = hbtgpu_bin_summary{num_rows, next_bid, n_ids, ctr[1]};
-  if (summary) *summary = c->bin_summary;
-  const unsigned long long cells = static_cast<unsigned long long>(num_rows) * next_bid;
-  if (cells * 8 > max_matrix_bytes)
-    return ifail(c, -E2BIG, "the matrix needs %llu x %u x 8 bytes, more than max_matrix_bytes",
-                 (unsigned long long)num_rows, next_bid);
-  if (int rc = grow(c, &c->d_bin_M, &c->cap_bin_M, cells + 1)) return rc;
-  IK(cudaMemsetAsync(c->d_bin_M, 0, (cells + 1) * sizeof(unsigned long long), c->stream));
-  IK(cudaEventRecord(c->ev2, c->stream));
-  if (n_ids && n_rt)
-    k_bin_durations<<<static_cast<unsigned>(n_rt), NT, 0, c->stream>>>(c->d_units, n_units, c->d_res, d_sel, c->d_out,
-                                                                       c->d_ioff, c->d_icnt, t, c->d_has, c->d_bt_base,
-                                                                       c->d_bin_M, next_bid);
-  IK(cudaGetLastError());
-  IK(cudaEventRecord(c->ev3, c->stream));
-  IK(cudaStreamSynchronize(c->stream));
-  float a = 0.f, b = 0.f;
-  IK(cudaEventElapsedTime(&a, c->ev0, c->ev1));
-  IK(cudaEventElapsedTime(&b, c->ev2, c->ev3));
-  c->last_ms = a + b;
-  c->have_bin = true;
-  return 0;
-}
-
-int hbtgpu_islice_bin_get(hbtgpu_islice_ctx* c, hbtgpu_bin_freq* freqs, uint64_t freq_cap, uint64_t* durations,
-                          uint64_t durations_cap) {
-  if (!c) return -EINVAL;
-  if (!c->have_bin) return ifail(c, -EINVAL, "no matrix: call hbtgpu_islice_bin first");
-  IK(cudaSetDevice(c->device));
-  if (freqs) {
-    const uint64_t nf = c->bin_summary.num_stack_ids;
-    if (freq_cap < nf) return ifail(c, -ENOSPC, "%llu stack ids, room for %llu", (unsigned long long)nf,
-                                    (unsigned long long)freq_cap);
-    if (nf) IK(cudaMemcpy(freqs, c->d_bin_freqs, nf * sizeof(hbtgpu_bin_freq), cudaMemcpyDeviceToHost));
-  }
-  if (durations) {
-    const uint64_t cells = c->bin_summary.num_rows * c->bin_summary.num_bins;
-    if (durations_cap < cells) return ifail(c, -ENOSPC, "%llu cells, room for %llu", (unsigned long long)cells,
-                                            (unsigned long long)durations_cap);
-    if (cells) IK(cudaMemcpy(durations, c->d_bin_M, cells * sizeof(uint64_t), cudaMemcpyDeviceToHost));
-  }
-  return 0;
-}
-
-const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* c) {
-  return (c && c->have_bin) ? reinterpret_cast<const uint64_t*>(c->d_bin_M) : nullptr;
-}
+#include "hbtgpu_islice_bin_host.inc"
 
 }  // extern "C"
