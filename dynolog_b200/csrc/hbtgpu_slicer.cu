@@ -224,22 +224,22 @@ __global__ void k_sl_entry_counts(const hbtgpu_cs_event* __restrict__ ev, uint32
 __global__ void k_sl_entries(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
                              const uint32_t* __restrict__ next, const uint32_t* __restrict__ ecnt,
                              const uint32_t* __restrict__ eoff, int pos_bits, uint64_t* __restrict__ ekey,
-                             uint64_t* __restrict__ eval) {
+                             uint32_t* __restrict__ eval) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n || ecnt[i] == 0) return;
   const uint64_t tag = ev[i].tag;
   const uint32_t o = eoff[i];
   const uint32_t kind = ev[i].type == EV_CREATE ? K_CREATE : (is_virtual(ev[i]) ? K_CARRIED : K_IN);
   ekey[o] = (tag << pos_bits) | rank[i];
-  eval[o] = (static_cast<uint64_t>(i) << 2) | kind;
+  eval[o] = (i << 2) | kind;  // (fewer than 2^30 events per call)
   if (ecnt[i] == 2) {
     ekey[o + 1] = (tag << pos_bits) | rank[next[i]];
-    eval[o + 1] = (static_cast<uint64_t>(i) << 2) | K_PARK;
+    eval[o + 1] = (i << 2) | K_PARK;
   }
 }
 
 // (4) one thread per thread id: walk its events in merge order
-__global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __restrict__ eval, uint32_t n_entries, int pos_bits,
+__global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint32_t* __restrict__ eval, uint32_t n_entries, int pos_bits,
                           const uint32_t* __restrict__ rank, const uint32_t* __restrict__ epoch, uint8_t* __restrict__ cf,
                           uint32_t* __restrict__ t_create /* [n_tags][2]: event that created T[v][k] */,
                           uint8_t* __restrict__ pt_flags /* [n_tags][2]: bit 0 exists, bit 1 dormant */,
@@ -251,7 +251,7 @@ __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint64_t* __r
   bool ex1 = pt_flags[2 * v + 1] & 1, ln1 = pt_flags[2 * v + 1] & 2, ex0 = pt_flags[2 * v] & 1, ln0 = pt_flags[2 * v] & 2;
   uint32_t cur_epoch = 0;  // what was carried over is valid until the window's first reset
   for (uint32_t e = e0; e < n_entries && static_cast<uint32_t>(ekey[e] >> pos_bits) == v; ++e) {
-    const uint32_t kind = static_cast<uint32_t>(eval[e] & 3), i = static_cast<uint32_t>(eval[e] >> 2);
+    const uint32_t kind = eval[e] & 3, i = eval[e] >> 2;
     const uint32_t ep = epoch[rank[i]];  // (a parking switch-out is in its switch-in's epoch)
     if (ep != cur_epoch) {               // resetState_, :636-652: dormant lists cleared
       ln1 = ln0 = false;
@@ -728,7 +728,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   for (uint32_t u = 0; u < n_units; ++u)
     if (event_begin[u + 1] < event_begin[u]) return sfail(c, -EINVAL, "event_begin must not decrease");
   const uint64_t Nreal = event_begin[n_units] - base;
-  if (Nreal + n_units >= 0x7fffffffull) return sfail(c, -EINVAL, "more than 2^31 events in one call");
+  if (Nreal + n_units >= 0x3fffffffull) return sfail(c, -EINVAL, "more than 2^30 events in one call");
   if (Nreal && !events) return sfail(c, -EINVAL, "null events");
   if (!(flags & HBTGPU_SLICER_CONTINUE) || !c->have_state || c->carried_units != n_units)
     if (int rc = reset_state(c, n_units)) return rc;
@@ -742,7 +742,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
                                   static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), 0, 64, st);
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort2, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
-                                  static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr), static_cast<int>(2 * static_cast<uint64_t>(N)), 0, 64, st);
+                                  static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(2 * static_cast<uint64_t>(N)), 0, 64, st);
   cub::DeviceScan::InclusiveSum(nullptr, tmp_scan, static_cast<int32_t*>(nullptr), static_cast<int32_t*>(nullptr), static_cast<int>(N), st);
   cub::DeviceScan::ExclusiveScan(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), MaxOp(), 0u, static_cast<int>(N), st);
   tmp_scan = std::max(tmp_scan, t2);
@@ -758,7 +758,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);   // rank, delta, depth, start, epoch
   add(n1, 1); add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);   // eff, scan_in, prev_scan, prev, next
   add(n1, 1); add(n1, 4); add(n1, 4); add(n1, 1);               // cf, ecnt, eoff, rin
-  add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8); add(2 * n1, 8);  // entries + sorted
+  add(2 * n1, 8); add(2 * n1, 4); add(2 * n1, 8); add(2 * n1, 4);  // entries + sorted
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);               // idcnt, idbase, sflag, soff
   add(n1, 32); add(n_units + 2, 8);                             // slices, slice_begin
   add(1, sizeof(Globals)); add(tmp_bytes, 1);
@@ -793,9 +793,9 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   auto* d_eoff = carve<uint32_t>(c, n1);
   auto* d_rin = carve<uint8_t>(c, n1);
   auto* d_ekey = carve<uint64_t>(c, 2 * n1);
-  auto* d_eval = carve<uint64_t>(c, 2 * n1);
+  auto* d_eval = carve<uint32_t>(c, 2 * n1);
   auto* d_ekey_s = carve<uint64_t>(c, 2 * n1);
-  auto* d_eval_s = carve<uint64_t>(c, 2 * n1);
+  auto* d_eval_s = carve<uint32_t>(c, 2 * n1);
   auto* d_idcnt = carve<uint32_t>(c, n1);
   auto* d_idbase = carve<uint32_t>(c, n1);
   auto* d_sflag = carve<uint32_t>(c, n1);
