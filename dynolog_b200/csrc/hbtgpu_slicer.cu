@@ -72,7 +72,7 @@ struct Globals {
   unsigned int bad;
   unsigned int e_first[2];  // merge position where E[k] is first needed
   unsigned int a_first[2];  // ... T[0][k] (tid 0)
-  unsigned long long n_dropped, n_we_start, n_we_end, n_completed;
+  unsigned long long n_dropped, n_we_start, n_we_end, n_completed, n_logic;
   unsigned int max_tag;
   unsigned long long max_ts;
   int depth0;                 // write-error depth the window starts with
@@ -99,10 +99,12 @@ __global__ void k_sl_prepare(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
   val[i] = i;
   uint32_t bad = 0;
   const uint32_t u = unit_of[i];
+  if (virt && i != ub[u]) bad |= BAD_LEVEL;  // levels 0xee / 0xef mark the carried state in slot ub[u] only
   if (e.comp_unit_id != u) bad |= BAD_UNIT;
   if (!virt) {
     if (e.type > EV_WE_END || e.type == EV_START || e.type == EV_END) bad |= BAD_TYPE;
-    if (e.type >= EV_CREATE && e.type <= EV_OUT_YIELD && e.level != 0) bad |= BAD_LEVEL;
+    // (a thread lifetime event at another level is dropped with a logic error, as in the reference)
+    if (e.type >= EV_IN && e.type <= EV_OUT_YIELD && e.level != 0) bad |= BAD_LEVEL;
     if ((e.type == EV_CREATE || e.type == EV_IN) && e.tag == NA) bad |= BAD_TAG;
     // slot ub[u] holds the carried state; the unit's events must not go back in time, nor behind
     // the previous window's last event
@@ -153,15 +155,19 @@ __global__ void k_sl_effective(const hbtgpu_cs_event* __restrict__ ev, uint32_t 
   const int32_t before = g->depth0 + depth_incl[p] - delta[p];  // num_active_write_errors_ as the event finds it
   const bool we_end = t == EV_WE_END, we_start = t == EV_WE_START;
   const bool dropped = !virt && !we_end && !we_start && before > 0;  // handleWriteErrors_, Slicer.h:691-701
-  const bool e = virt ? is_switch(t) : (!we_end && !we_start && !dropped);
+  // handleThreadLifetime_, :711-720: a lifetime event that is not at level 0 is dropped as a logic error
+  const bool logic = !virt && !dropped && (t == EV_CREATE || t == EV_DESTROY) && ev[i].level != 0;
+  const bool e = virt ? is_switch(t) : (!we_end && !we_start && !dropped && !logic);
   const unsigned m = __activemask();
   const unsigned b_end = __ballot_sync(m, we_end), b_start = __ballot_sync(m, we_start), b_drop = __ballot_sync(m, dropped);
   const unsigned b_bad = __ballot_sync(m, we_end && before <= 0);  // the reference's unsigned counter would wrap
+  const unsigned b_logic = __ballot_sync(m, logic);
   if ((threadIdx.x & 31) == __ffs(m) - 1) {
     if (b_end) atomicAdd(&g->n_we_end, static_cast<unsigned long long>(__popc(b_end)));
     if (b_start) atomicAdd(&g->n_we_start, static_cast<unsigned long long>(__popc(b_start)));
     if (b_drop) atomicAdd(&g->n_dropped, static_cast<unsigned long long>(__popc(b_drop)));
     if (b_bad) atomicOr(&g->bad, BAD_WE_END);
+    if (b_logic) atomicAdd(&g->n_logic, static_cast<unsigned long long>(__popc(b_logic)));
   }
   eff[i] = e;
   scan_in[i] = (e && is_switch(t)) ? i + 1 : 0;
@@ -1000,7 +1006,8 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   c->total.num_processed += Nreal;  // every event is processed once (none is older than its predecessor)
   c->total.num_error_start += gh.n_we_start;
   c->total.num_error_end += gh.n_we_end;
-  c->total.num_dropped += gh.n_dropped;
+  c->total.num_dropped += gh.n_dropped + gh.n_logic;
+  c->total.num_logic_errors += gh.n_logic;
   c->total.num_slices_completed += gh.n_completed;
   if (stats) *stats = c->total;
   if (last_ts) *last_ts = c->last_ts;

@@ -662,8 +662,8 @@ const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* ctx); /* t
  * statistics and the last timestamp carry over, exactly as one Slicer fed both windows would
  * have them.  stats / the stack table / last_ts are cumulative since the last fresh start.
  *
- * Scope: level-0 events (ThreadCreation / ThreadDestruction / SwitchIn / SwitchOut* /
- * WriteErrors*), every unit's events in time order, no WriteErrorsEnd without its Start.  A
+ * Scope: switch events at level 0 (SwitchIn / SwitchOut*), thread lifetime events (those at
+ * another level are dropped as logic errors, as in the reference, :711-720), WriteErrors*, every unit's events in time order, no WriteErrorsEnd without its Start.  A
  * switch-in on a unit whose active state is a thread resets everything, as in the reference
  * (:839-868).  Input outside the scope is refused with -ENOTSUP and a message that names the
  * reason (there is no CPU path); comp_unit_id that differs from the

@@ -91,6 +91,22 @@ def test_random_windows(slicer, kw):
     assert done > 20
 
 
+def test_lifetime_events_at_other_levels_are_dropped(slicer):
+    r = np.random.default_rng(77)
+    for trial in range(20):
+        n_units = int(r.integers(1, 5))
+        ev = random_events(r, n_units, int(r.integers(20, 600)), 12, p_create=0.3, p_double_in=0.05)
+        life = (ev["type"] == CREATE) | (ev["type"] == 3)
+        ev["level"][life & (r.random(len(ev)) < 0.4)] = 2
+        units, merged = split_units(ev, n_units)
+        if not supported(merged, n_units):
+            continue
+        got = slicer.run(units)
+        for kind in KINDS:
+            compare(got, po.slicer_run(kind, merged, n_units))
+        assert got["stats"]["num_logic_errors"] >= 0
+
+
 def test_refusals(slicer):
     # (a switch-in on a unit whose active state is a thread is not refused: it resets, as in the reference)
     got = slicer.run([events([(10, IN, 0, 3), (20, IN, 0, 4), (30, OUT_P, 0, NA), (40, IN, 0, 3), (50, OUT_Y, 0, NA)])])
@@ -108,6 +124,10 @@ def test_refusals(slicer):
         slicer.run([events([(10, IN, 1, 3)])])
     ev = events([(10, IN, 0, 3)])
     ev["level"][0] = 1
+    with pytest.raises(HbtGpuError, match="level 0"):
+        slicer.run([ev])
+    ev = events([(10, CREATE, 0, 3), (20, IN, 0, 3)])
+    ev["level"][0] = 0xEE                     # the marker of a carried state is not a level an event may have
     with pytest.raises(HbtGpuError, match="level 0"):
         slicer.run([ev])
 
