@@ -883,6 +883,8 @@ struct hbtgpu_islice_ctx {
   unsigned long long* d_bin_ctr = nullptr; size_t cap_bin_ctr = 0;
   uint8_t* d_sel = nullptr;          size_t cap_sel = 0;
   hbtgpu_bin_freq* d_bin_freqs = nullptr; size_t cap_bin_freqs = 0;
+  uint64_t* d_ext_ids = nullptr;     size_t cap_ext_ids = 0;
+  uint32_t* d_ext_bids = nullptr;    size_t cap_ext_bids = 0;
   hbtgpu_bin_summary bin_summary{};
   bool have_bin = false;
   // last call
@@ -959,7 +961,7 @@ void hbtgpu_islice_destroy(hbtgpu_islice_ctx* c) {
   cudaFree(c->d_rt_tot); cudaFree(c->d_rt_base); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_ql); cudaFree(c->d_tmp); cudaFree(c->d_ioff); cudaFree(c->d_icnt); cudaFree(c->d_ifirst);
   cudaFree(c->d_out); cudaFree(c->d_units); cudaFree(c->d_ustate); cudaFree(c->d_res); cudaFree(c->d_base);
   cudaFree(c->d_bin_tab); cudaFree(c->d_bin_bid); cudaFree(c->d_has); cudaFree(c->d_bt_tot); cudaFree(c->d_bt_base);
-  cudaFree(c->d_bin_list); cudaFree(c->d_bin_up); cudaFree(c->d_bin_freqs); cudaFree(c->d_bin_M); cudaFree(c->d_bin_ctr); cudaFree(c->d_sel);
+  cudaFree(c->d_bin_list); cudaFree(c->d_bin_up); cudaFree(c->d_bin_freqs); cudaFree(c->d_ext_ids); cudaFree(c->d_ext_bids); cudaFree(c->d_bin_M); cudaFree(c->d_bin_ctr); cudaFree(c->d_sel);
   for (cudaEvent_t e : {c->ev0, c->ev1, c->ev2, c->ev3})
     if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);

@@ -29,7 +29,7 @@ ABI_SYMBOLS = [
     "hbtgpu_islice_create", "hbtgpu_islice_destroy", "hbtgpu_islice_last_error",
     "hbtgpu_islice_release", "hbtgpu_islice_get_units", "hbtgpu_islice_get",
     "hbtgpu_islice_device_view", "hbtgpu_islice_last_ms",
-    "hbtgpu_islice_bin", "hbtgpu_islice_bin_get", "hbtgpu_islice_bin_durations_device",
+    "hbtgpu_islice_bin", "hbtgpu_islice_bin_with", "hbtgpu_islice_bin_get", "hbtgpu_islice_bin_durations_device",
     "hbtgpu_slicer_create", "hbtgpu_slicer_destroy", "hbtgpu_slicer_last_error", "hbtgpu_slicer_run",
     "hbtgpu_slicer_get_slices", "hbtgpu_slicer_get_stacks", "hbtgpu_slicer_slices_device", "hbtgpu_slicer_last_ms",
 ]
@@ -70,6 +70,8 @@ def _lib():
         L.hbtgpu_islice_bin.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64,
                                         C.c_void_p]
         L.hbtgpu_islice_bin_get.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
+        L.hbtgpu_islice_bin_with.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64,
+                                             C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p]
         L.hbtgpu_islice_bin_durations_device.restype = C.c_void_p
         L.hbtgpu_islice_bin_durations_device.argtypes = [C.c_void_p]
         L.hbtgpu_slicer_create.restype = C.c_void_p
@@ -167,14 +169,23 @@ class IntervalSlicer:
         return v
 
     def bin(self, min_distinct_intervals, min_duration, selected=None, max_stack_ids=1 << 20,
-            max_matrix_bytes=1 << 30, fetch=True):
+            max_matrix_bytes=1 << 30, fetch=True, numbering=None):
         """MonData::stackIdFreqs + TagStackIdBinner over the last release.  Returns dict(freqs,
-        durations [num_rows, num_bins] or None, num_rows, num_bins, rows_skipped)."""
+        durations [num_rows, num_bins], num_rows, num_bins, num_stack_ids, rows_skipped).
+        numbering = (stack_ids ascending, bids, num_bins, num_rows): bins agreed between ranks
+        (hbtgpu_islice_bin_with) instead of the thresholds."""
         summ = BinSummary()
         sel = None if selected is None else np.ascontiguousarray(selected, dtype=np.uint8)
-        self._check(self.L.hbtgpu_islice_bin(self.h, None if sel is None else sel.ctypes.data,
-                                             min_distinct_intervals, min_duration, max_stack_ids, max_matrix_bytes,
-                                             C.byref(summ)))
+        sel_p = None if sel is None else sel.ctypes.data
+        if numbering is None:
+            self._check(self.L.hbtgpu_islice_bin(self.h, sel_p, min_distinct_intervals, min_duration, max_stack_ids,
+                                                 max_matrix_bytes, C.byref(summ)))
+        else:
+            ids = np.ascontiguousarray(numbering[0], dtype=np.uint64)
+            bids = np.ascontiguousarray(numbering[1], dtype=np.uint32)
+            self._check(self.L.hbtgpu_islice_bin_with(self.h, sel_p, ids.ctypes.data, bids.ctypes.data, len(ids),
+                                                      int(numbering[2]), int(numbering[3]), max_stack_ids,
+                                                      max_matrix_bytes, C.byref(summ)))
         out = {"num_rows": summ.num_rows, "num_bins": summ.num_bins, "num_stack_ids": summ.num_stack_ids,
                "rows_skipped": summ.rows_skipped, "freqs": None, "durations": None}
         if not fetch:  # frequencies and matrix stay on the device
@@ -186,6 +197,9 @@ class IntervalSlicer:
         out["freqs"] = freqs[:summ.num_stack_ids]
         out["durations"] = dur[:cells].reshape(summ.num_rows, summ.num_bins)
         return out
+
+    def bin_durations_device(self):
+        return self.L.hbtgpu_islice_bin_durations_device(self.h)
 
     @property
     def last_ms(self):

@@ -53,3 +53,41 @@ def all_gather_stubs(heads, tails, device=None):
     outs = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(outs, mine)
     return [unpack_stubs(o.cpu().numpy(), n_cpus) for o in outs]
+
+
+# --- the binner over comp units spread across ranks -----------------------
+def merge_bin_freqs(freq_lists, min_distinct_intervals, min_duration):
+    """freq_lists: per rank, a structured array with stack_id / duration / num_obs / num_intervals
+    (what hbtgpu_islice_bin_get returns; the units of different ranks are disjoint, so the sums are
+    MonData::stackIdFreqs over all of them).  Returns (merged, num_bins): merged sorted by stack_id
+    with the agreed `bid` (0 = ignored, own bins in ascending stack_id order)."""
+    parts = [f for f in freq_lists if len(f)]
+    if not parts:
+        return np.zeros(0, freq_lists[0].dtype if freq_lists else np.uint64), 1
+    allf = np.concatenate(parts)
+    order = np.argsort(allf["stack_id"], kind="stable")
+    allf = allf[order]
+    ids, start = np.unique(allf["stack_id"], return_index=True)
+    merged = np.zeros(len(ids), allf.dtype)
+    merged["stack_id"] = ids
+    for k in ("duration", "num_obs", "num_intervals"):
+        merged[k] = np.add.reduceat(allf[k], start)          # wrapping u64 sums, as the reference adds
+    own = (merged["num_intervals"] >= np.uint64(min_distinct_intervals)) & (merged["duration"] >= np.uint64(min_duration))
+    merged["bid"] = np.where(own, np.cumsum(own), 0).astype(np.uint32)
+    return merged, int(own.sum()) + 1
+
+
+def all_gather_bin_freqs(freqs):
+    """Every rank's frequency list (small: one record per distinct stack id)."""
+    import torch.distributed as dist
+    outs = [None] * dist.get_world_size()
+    dist.all_gather_object(outs, freqs)
+    return outs
+
+
+def all_reduce_matrix(matrix):
+    """Sum of the ranks' interval x bin matrices (u64, wrapping): `matrix` is a torch int64 tensor
+    (on the GPU with NCCL, on the host with gloo), reduced in place."""
+    import torch.distributed as dist
+    dist.all_reduce(matrix, op=dist.ReduceOp.SUM)
+    return matrix

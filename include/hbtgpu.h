@@ -641,6 +641,17 @@ typedef struct {
 int hbtgpu_islice_bin(hbtgpu_islice_ctx* ctx, const uint8_t* unit_selected, uint64_t min_distinct_intervals,
                       uint64_t min_duration, uint64_t max_stack_ids, uint64_t max_matrix_bytes,
                       hbtgpu_bin_summary* summary);
+/* The same with the numbering of the bins taken from outside, for comp units spread over several
+ * GPUs (no counterpart in the reference, which bins one MonData in one process): every rank
+ * runs hbtgpu_islice_bin with thresholds 0 / 0 or reads its frequencies another way, the ranks
+ * add the frequencies of equal stack ids up, apply the thresholds to the sums and number the bins
+ * (dynolog_b200/shard.py: merge_bin_freqs), then each rank builds its matrix with the agreed
+ * numbering -- stack_ids strictly ascending, bids[i] < num_bins, num_rows = the intervals of all
+ * ranks -- and the matrices are summed (one integer all-reduce: every unit starts at row 0 in the
+ * reference too).  -EINVAL if a local stack id is missing from the numbering. */
+int hbtgpu_islice_bin_with(hbtgpu_islice_ctx* ctx, const uint8_t* unit_selected, const uint64_t* stack_ids,
+                           const uint32_t* bids, uint64_t n_ids, uint64_t num_bins, uint64_t num_rows,
+                           uint64_t max_stack_ids, uint64_t max_matrix_bytes, hbtgpu_bin_summary* summary);
 /* freqs in ascending stack_id order; durations = the matrix, num_rows x num_bins, row-major.  Either may be NULL. */
 int hbtgpu_islice_bin_get(hbtgpu_islice_ctx* ctx, hbtgpu_bin_freq* freqs, uint64_t freq_cap, uint64_t* durations,
                           uint64_t durations_cap);

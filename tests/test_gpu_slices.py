@@ -241,3 +241,41 @@ def test_bin_zero_length_slices_and_limits(slicer):
         slicer.bin(0, 0, max_stack_ids=1)              # three distinct stack ids do not fit
     with pytest.raises(HbtGpuError):
         slicer.bin(0, 0, max_matrix_bytes=8)           # 4 rows x 4 bins do not fit
+
+
+def test_bin_over_two_ranks(slicer):
+    """Units split between two contexts (two GPUs' worth): frequencies merged, bins agreed
+    (shard.merge_bin_freqs), each side builds its matrix with hbtgpu_islice_bin_with, the sum is the
+    matrix of one context holding all units."""
+    from dynolog_b200 import shard
+    r = np.random.default_rng(91)
+    us = [slicegen.gen_slices(r, int(r.integers(100, 2000)), hole_prob=0.05, n_stacks=int(r.choice([4, 90]))) for _ in range(7)]
+    ur = [slicegen.gen_rows(r, s, int(r.integers(20, 500)), stride=3, align_prob=0.2) for s in us]
+
+    def release(ctx, lo, hi):
+        sb = np.concatenate([[0], np.cumsum([len(s) for s in us[lo:hi]])]).astype(np.uint64)
+        rb = np.concatenate([[0], np.cumsum([len(x) for x in ur[lo:hi]])]).astype(np.uint64)
+        units = ctx.release(np.concatenate(us[lo:hi]), sb, np.concatenate(ur[lo:hi]), rb, 2**63, 3, np.zeros(hi - lo, np.uint64))
+        assert (units["status"] == 0).all()
+        return int(units["n_intervals"].sum())
+
+    other = gs.IntervalSlicer(0)
+    try:
+        for min_int, min_dur in [(0, 0), (2, 100), (4, 10**7)]:
+            release(slicer, 0, 7)
+            whole = slicer.bin(min_int, min_dur)
+            rows_a, rows_b = release(slicer, 0, 3), release(other, 3, 7)
+            fa, fb = slicer.bin(0, 0)["freqs"], other.bin(0, 0)["freqs"]
+            merged, num_bins = shard.merge_bin_freqs([fa, fb], min_int, min_dur)
+            for k in ("stack_id", "duration", "num_obs", "num_intervals", "bid"):
+                assert np.array_equal(merged[k], whole["freqs"][k]), k
+            numbering = (merged["stack_id"], merged["bid"], num_bins, rows_a + rows_b)
+            ma = slicer.bin(0, 0, numbering=numbering)
+            mb = other.bin(0, 0, numbering=numbering)
+            assert ma["num_bins"] == whole["num_bins"] and ma["num_rows"] == whole["num_rows"]
+            assert np.array_equal(ma["durations"] + mb["durations"], whole["durations"])
+        from dynolog_b200.hbtgpu import HbtGpuError
+        with pytest.raises(HbtGpuError):
+            slicer.bin(0, 0, numbering=(merged["stack_id"][1:], merged["bid"][1:], num_bins, rows_a + rows_b))
+    finally:
+        other.close()

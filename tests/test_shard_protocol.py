@@ -157,3 +157,76 @@ def test_compose_tail_cases():
     h.lost_before = 1                          # no SAMPLE but a LOST: invalidated, last_ kept
     out = hbtgpu.compose_tail(prev, h, own)
     assert out.valid == 0 and out.last[0] == 1
+
+
+# ---- the binner over units spread across ranks (SURVEY 8(f) f1 x 8(e)) ------------------------------
+def _bin_case(seed=5, n_units=6):
+    import slicegen
+    from oracle import pyoracle as po
+    r = np.random.default_rng(seed)
+    uc, us = [], []
+    for u in range(n_units):
+        s = slicegen.gen_slices(r, int(r.integers(50, 400)), hole_prob=0.05, n_stacks=int(r.choice([5, 60])))
+        rows = slicegen.gen_rows(r, s, int(r.integers(10, 120)), align_prob=0.2)
+        res = po.islice_release("port", s, rows, 2**63, 3)
+        uc.append(res["counts"])
+        us.append(res["slices"])
+    return uc, us
+
+
+def _local_matrix_in_global_bins(po, uc, us, merged, num_bins, num_rows):
+    """what hbtgpu_islice_bin_with computes on a rank, from the restatement: own numbering with
+    thresholds 0 / 0, columns moved to the agreed bins, rows padded."""
+    loc = po.bin_durations("port", uc, us, 0, 0)
+    m = np.zeros((num_rows, num_bins), np.uint64)
+    bid_of = dict(zip(merged["stack_id"].tolist(), merged["bid"].tolist()))
+    for f in loc["freqs"]:
+        col = loc["durations"][:, int(f["bid"])]
+        m[: len(col), bid_of[int(f["stack_id"])]] += col
+    return loc["freqs"], m
+
+
+def test_merge_bin_freqs_matches_one_process():
+    from dynolog_b200 import shard
+    from oracle import pyoracle as po
+    uc, us = _bin_case()
+    for min_int, min_dur in [(0, 0), (2, 50), (5, 10**6)]:
+        whole = po.bin_durations("port", uc, us, min_int, min_dur)
+        parts = [po.bin_durations("port", uc[:2], us[:2], 0, 0)["freqs"], po.bin_durations("port", uc[2:], us[2:], 0, 0)["freqs"]]
+        merged, num_bins = shard.merge_bin_freqs(parts, min_int, min_dur)
+        for k in ("stack_id", "duration", "num_obs", "num_intervals", "bid"):
+            assert np.array_equal(merged[k], whole["freqs"][k]), k
+        assert num_bins == whole["num_bins"]
+        num_rows = whole["num_rows"]
+        m = sum(_local_matrix_in_global_bins(po, c, s, merged, num_bins, num_rows)[1] for c, s in ((uc[:2], us[:2]), (uc[2:], us[2:])))
+        assert np.array_equal(m, whole["durations"])
+
+
+def _bin_worker(rank, world, tmpdir):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from dynolog_b200 import shard
+    from oracle import pyoracle as po
+    dist.init_process_group("gloo", init_method=f"file://{tmpdir}/rdzv_bin", rank=rank, world_size=world)
+    try:
+        uc, us = _bin_case()
+        mine = slice(0, 3) if rank == 0 else slice(3, None)
+        whole = po.bin_durations("port", uc, us, 2, 50)
+        local_freqs = po.bin_durations("port", uc[mine], us[mine], 0, 0)["freqs"]
+        merged, num_bins = shard.merge_bin_freqs(shard.all_gather_bin_freqs(local_freqs), 2, 50)
+        rows = torch.tensor([sum(len(c) for c in uc[mine])], dtype=torch.int64)
+        dist.all_reduce(rows)
+        _, m = _local_matrix_in_global_bins(po, uc[mine], us[mine], merged, num_bins, int(rows[0]))
+        t = torch.from_numpy(m.view(np.int64).copy())
+        shard.all_reduce_matrix(t)
+        assert np.array_equal(t.numpy().view(np.uint64), whole["durations"])
+        assert np.array_equal(merged["bid"], whole["freqs"]["bid"])
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_binner_gloo(port_oracle, tmp_path):
+    import torch.multiprocessing as mp
+    mp.spawn(_bin_worker, args=(2, str(tmp_path)), nprocs=2, join=True)
