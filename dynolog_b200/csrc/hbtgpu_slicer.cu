@@ -178,9 +178,11 @@ __global__ void k_sl_links(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, c
                            const uint64_t* __restrict__ ub, const uint32_t* __restrict__ rank,
                            const uint32_t* __restrict__ epoch, const uint8_t* __restrict__ eff,
                            const uint8_t* __restrict__ rin, const uint32_t* __restrict__ prev_scan,
-                           uint32_t* __restrict__ prev, uint32_t* __restrict__ next, uint8_t* __restrict__ cf, Globals* g) {
+                           uint32_t* __restrict__ prev, uint32_t* __restrict__ next, uint8_t* __restrict__ cf,
+                           uint32_t* __restrict__ own_epoch, Globals* g) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  own_epoch[i] = epoch[rank[i]];  // by event, for the per-thread walks (one look-up instead of two)
   uint32_t pv = NOIDX;
   uint8_t f = 0;
   const uint32_t t = ev[i].type;
@@ -246,7 +248,7 @@ __global__ void k_sl_entries(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
 
 // (4) one thread per thread id: walk its events in merge order
 __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint32_t* __restrict__ eval, uint32_t n_entries, int pos_bits,
-                          const uint32_t* __restrict__ rank, const uint32_t* __restrict__ epoch, uint8_t* __restrict__ cf,
+                          const uint32_t* __restrict__ own_epoch, uint8_t* __restrict__ cf,
                           uint32_t* __restrict__ t_create /* [n_tags][2]: event that created T[v][k] */,
                           uint8_t* __restrict__ pt_flags /* [n_tags][2]: bit 0 exists, bit 1 dormant */,
                           uint32_t* __restrict__ last_epoch /* [n_tags] */) {
@@ -258,7 +260,7 @@ __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint32_t* __r
   uint32_t cur_epoch = 0;  // what was carried over is valid until the window's first reset
   for (uint32_t e = e0; e < n_entries && static_cast<uint32_t>(ekey[e] >> pos_bits) == v; ++e) {
     const uint32_t kind = eval[e] & 3, i = eval[e] >> 2;
-    const uint32_t ep = epoch[rank[i]];  // (a parking switch-out is in its switch-in's epoch)
+    const uint32_t ep = own_epoch[i];  // (a parking switch-out is in its switch-in's epoch)
     if (ep != cur_epoch) {               // resetState_, :636-652: dormant lists cleared
       ln1 = ln0 = false;
       cur_epoch = ep;
@@ -763,7 +765,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   add(n1, 8); add(n1, 8); add(n1, 4); add(n1, 4);               // key, key_s, val, order
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);   // rank, delta, depth, start, epoch
   add(n1, 1); add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);   // eff, scan_in, prev_scan, prev, next
-  add(n1, 1); add(n1, 4); add(n1, 4); add(n1, 1);               // cf, ecnt, eoff, rin
+  add(n1, 1); add(n1, 4); add(n1, 4); add(n1, 1); add(n1, 4);   // cf, ecnt, eoff, rin, own_epoch
   add(2 * n1, 8); add(2 * n1, 4); add(2 * n1, 8); add(2 * n1, 4);  // entries + sorted
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);               // idcnt, idbase, sflag, soff
   add(n1, 32); add(n_units + 2, 8);                             // slices, slice_begin
@@ -798,6 +800,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   auto* d_ecnt = carve<uint32_t>(c, n1);
   auto* d_eoff = carve<uint32_t>(c, n1);
   auto* d_rin = carve<uint8_t>(c, n1);
+  auto* d_own_epoch = carve<uint32_t>(c, n1);
   auto* d_ekey = carve<uint64_t>(c, 2 * n1);
   auto* d_eval = carve<uint32_t>(c, 2 * n1);
   auto* d_ekey_s = carve<uint64_t>(c, 2 * n1);
@@ -856,7 +859,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   for (int round = 0;; ++round) {
     SK(cudaMemsetAsync(d_next, 0xff, static_cast<size_t>(N) * sizeof(uint32_t), st));
     k_sl_links<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_rank, d_epoch, d_eff, d_rin, d_prev_scan, d_prev,
-                                          d_next, d_cf, d_g);
+                                          d_next, d_cf, d_own_epoch, d_g);
     SK(cudaGetLastError());
     SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
     SK(cudaStreamSynchronize(st));
@@ -930,7 +933,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     t = tmp_bytes;
     cub::DeviceRadixSort::SortPairs(d_tmp, t, d_ekey, d_ekey_s, d_eval, d_eval_s, static_cast<int>(n_entries), 0,
                                     pos_bits + tag_bits, st);
-    k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, pos_bits, d_rank, d_epoch, d_cf,
+    k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, pos_bits, d_own_epoch, d_cf,
                                                       d_tcreate, c->p_flags, d_last_epoch);
   }
   k_sl_firsts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_eff, d_rin, d_cf, d_g);
