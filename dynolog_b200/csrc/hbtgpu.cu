@@ -28,6 +28,10 @@ struct HostImage {
   uint32_t stream;
 };
 
+struct PeerState;                  // hbtgpu_peer.inc
+void peer_release(hbtgpu_ctx* ctx);
+int peer_poll_error(hbtgpu_ctx* ctx);
+
 }  // namespace
 
 struct hbtgpu_ctx {
@@ -51,6 +55,8 @@ struct hbtgpu_ctx {
   hbtgpu_head_stub* d_head = nullptr;
   uint64_t* d_counters = nullptr;
   uint64_t* d_acc = nullptr;
+  uint64_t* d_acc_total = nullptr;  // hbtgpu_merge: sums over all ranks
+  uint64_t* acc_cur = nullptr;      // what getters / derive read: d_acc, or d_acc_total after a merge
   uint64_t* d_scaled = nullptr;
   double* d_metric = nullptr;
   uint32_t* d_valid = nullptr;
@@ -66,11 +72,15 @@ struct hbtgpu_ctx {
   size_t cap_chunks = 0, cap_io = 0, cap_images = 0;
   uint64_t *d_rows = nullptr, *d_rec_off = nullptr;
   uint32_t *d_rec_type = nullptr, *d_rec_size = nullptr;
-  size_t cap_rows = 0, cap_recs = 0;
+  size_t cap_rows = 0, cap_rec_off = 0, cap_rec_type = 0, cap_rec_size = 0;
   void* d_math = nullptr;
   size_t cap_math = 0;
   uint64_t* d_series = nullptr;  // hbtgpu_series_reduce results
   uint64_t* d_boundary_cell = nullptr;  // [max_cpus] cell a shard-boundary row was added to, or ~0
+  HeadExtra* d_head_extra = nullptr;    // [max_cpus] shard mode: records in front of the first SAMPLE
+  uint32_t* d_dead = nullptr;           // [max_cpus] shard mode: an earlier shard of this cpu stalled
+  uint64_t* d_stub_block = nullptr;     // this rank's packed stubs (host getters)
+  PeerState* peer = nullptr;     // peer-memory exchange (hbtgpu_peer.inc)
   bool derived = false;                 // k_derive has run over the current accumulators
   size_t cap_series = 0;
 
@@ -115,11 +125,19 @@ int fail(hbtgpu_ctx* c, int code, const char* fmt, ...) {
 
 template <class T>
 int ensure(hbtgpu_ctx* ctx, T** p, size_t* cap, size_t need) {
-  if (need <= *cap) return 0;
-  if (*p) CK(cudaFree(*p));
-  *p = nullptr;
-  size_t ncap = std::max(need, *cap * 2);
-  CK(cudaMalloc(reinterpret_cast<void**>(p), ncap * sizeof(T)));
+  if (need <= *cap && *p) return 0;
+  // allocate first, then swap: a failed cudaMalloc leaves the old buffer and its capacity intact
+  const size_t ncap = std::max(need, *cap * 2);
+  T* fresh = nullptr;
+  CK(cudaMalloc(reinterpret_cast<void**>(&fresh), ncap * sizeof(T)));
+  if (*p) {
+    const cudaError_t e = cudaFree(*p);
+    if (e != cudaSuccess) {
+      cudaFree(fresh);
+      return fail(ctx, -EIO, "cudaFree failed: %s", cudaGetErrorString(e));
+    }
+  }
+  *p = fresh;
   *cap = ncap;
   return 0;
 }
@@ -147,11 +165,7 @@ int build_table(hbtgpu_ctx* ctx) {
   for (auto& im : ctx->images) total += im.len;
   // enough chunks to fill 148 SMs several times over, but not smaller than one tile
   uint64_t target = total / (148ull * 12ull);
-  uint64_t cap = 512ull << 10;
-  if (const char* e = getenv("HBTGPU_CHUNK_KB")) {  // tuning knob
-    const long kb = atol(e);
-    if (kb >= 16 && kb <= 4096) cap = static_cast<uint64_t>(kb) << 10;
-  }
+  const uint64_t cap = 512ull << 10;
   const uint64_t cb = chunk_bytes_for(target, cap, ctx_tile_bytes(ctx));
   ctx->chunk_bytes = cb;
 
@@ -232,6 +246,7 @@ Params make_params(hbtgpu_ctx* ctx) {
   P.carry_in = ctx->d_carry_in;
   P.carry_out = ctx->d_carry_out;
   P.head = ctx->d_head;
+  P.head_extra = ctx->d_head_extra;
   P.counters = ctx->d_counters;
   P.acc = ctx->d_acc;
   P.flags = ctx->d_flags;
@@ -277,7 +292,7 @@ Params make_params(hbtgpu_ctx* ctx) {
 
 DeriveParams derive_params(hbtgpu_ctx* ctx) {
   DeriveParams D{};
-  D.acc = ctx->d_acc;
+  D.acc = ctx->acc_cur;
   D.scaled = ctx->d_scaled;
   D.metric = ctx->d_metric;
   D.valid = ctx->d_valid;
@@ -316,7 +331,7 @@ int launch_derive(hbtgpu_ctx* ctx) {
 int derive_after_boundaries(hbtgpu_ctx* ctx) {
   if (!ctx->derived) return launch_derive(ctx);
   const uint32_t ns = ctx->cfg.max_cpus;
-  k_derive_cells<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(derive_params(ctx), ctx->d_boundary_cell, ns);
+  k_derive_cells<<<ns, 128, 0, ctx->stream>>>(derive_params(ctx), ctx->d_boundary_cell, ctx->cfg.n_buckets);
   CK(cudaGetLastError());
   return 0;
 }
@@ -382,11 +397,9 @@ int ensure_emitted(hbtgpu_ctx* ctx) {
   const uint32_t n = ctx->cfg.n_events;
   if (int r = ensure(ctx, &ctx->d_rows, &ctx->cap_rows, std::max<uint64_t>(rows, 1) * (n + 2))) return r;
   {
-    size_t c0 = ctx->cap_recs, c1 = ctx->cap_recs, c2 = ctx->cap_recs;
-    if (int r = ensure(ctx, &ctx->d_rec_off, &c0, std::max<uint64_t>(recs, 1))) return r;
-    if (int r = ensure(ctx, &ctx->d_rec_type, &c1, std::max<uint64_t>(recs, 1))) return r;
-    if (int r = ensure(ctx, &ctx->d_rec_size, &c2, std::max<uint64_t>(recs, 1))) return r;
-    ctx->cap_recs = c0;
+    if (int r = ensure(ctx, &ctx->d_rec_off, &ctx->cap_rec_off, std::max<uint64_t>(recs, 1))) return r;
+    if (int r = ensure(ctx, &ctx->d_rec_type, &ctx->cap_rec_type, std::max<uint64_t>(recs, 1))) return r;
+    if (int r = ensure(ctx, &ctx->d_rec_size, &ctx->cap_rec_size, std::max<uint64_t>(recs, 1))) return r;
   }
   if (nc) {
     Params P = make_params(ctx);
@@ -514,6 +527,7 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_head), ns * sizeof(hbtgpu_head_stub)));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_counters), ns * C_SLOTS * 8));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_acc), ctx->acc_words * 8));
+  ctx->acc_cur = ctx->d_acc;
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_scaled), ctx->n_cells * n * 8));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_metric),
                  std::max<uint64_t>(ctx->n_cells * cfg->n_metrics, 1) * 8));
@@ -521,6 +535,10 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_flags), FLAG_COUNT * 4));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_streams), ns * sizeof(StreamDesc)));
   CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_boundary_cell), ns * 8ull));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_head_extra), ns * sizeof(HeadExtra)));
+  CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_dead), ns * 4ull));
+  CKC(cudaMemsetAsync(ctx->d_head_extra, 0, ns * sizeof(HeadExtra), ctx->stream));
+  CKC(cudaMemsetAsync(ctx->d_dead, 0, ns * 4ull, ctx->stream));
   if (cfg->sample_format == HBTGPU_SAMPLE_IP_TID_TIME_READ) {
     const uint32_t tl = cfg->tid_table_log2 ? cfg->tid_table_log2 : 16, il = cfg->ip_table_log2 ? cfg->ip_table_log2 : 22;
     if (tl < 4 || tl > 28 || il < 4 || il > 28) {
@@ -561,11 +579,13 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  peer_release(ctx);
   void* ptrs[] = {ctx->arena, ctx->d_carry_in, ctx->d_carry_out, ctx->d_carry_init, ctx->d_head, ctx->d_counters,
                   ctx->d_acc, ctx->d_scaled, ctx->d_metric, ctx->d_valid, ctx->d_flags,
                   ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
                   ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_tid_keys,
-                  ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special, ctx->d_series, ctx->d_boundary_cell};
+                  ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special, ctx->d_series, ctx->d_boundary_cell,
+                  ctx->d_head_extra, ctx->d_dead, ctx->d_stub_block, ctx->d_acc_total};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
@@ -730,6 +750,7 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   CK(cudaMemcpyAsync(ctx->d_carry_out, ctx->d_carry_in, ns * sizeof(hbtgpu_carry),
                      cudaMemcpyDeviceToDevice, ctx->stream));
   ctx->derived = false;
+  ctx->acc_cur = ctx->d_acc;
   const bool timed = ctx->ev_pending < hbtgpu_ctx::kEvRing;
   if (nc) {
     if (timed) CK(cudaEventRecord(ctx->ev_dec0[ctx->ev_pending], ctx->stream));
@@ -773,6 +794,7 @@ int hbtgpu_sync(hbtgpu_ctx* ctx) {
   CK(cudaSetDevice(ctx->device));
   CK(cudaStreamSynchronize(ctx->stream));
   CK(cudaStreamSynchronize(ctx->d2h_stream));
+  if (int r = peer_poll_error(ctx)) return r;
   if (ctx->ran) CK(cudaEventElapsedTime(&ctx->stats.last_run_ms, ctx->ev_run0, ctx->ev_run1));
   for (int i = 0; i < ctx->ev_pending; ++i) {
     float ms = 0.f;
@@ -966,7 +988,7 @@ int hbtgpu_get_top_ips(hbtgpu_ctx* ctx, uint32_t k, uint64_t* ip, uint64_t* coun
 
 int hbtgpu_get_buckets_device(hbtgpu_ctx* ctx, hbtgpu_bucket_view* v) {
   if (!ctx || !v) return -EINVAL;
-  v->acc = ctx->d_acc;
+  v->acc = ctx->acc_cur;
   v->scaled = ctx->d_scaled;
   v->metric = ctx->d_metric;
   v->valid = ctx->d_valid;
@@ -982,7 +1004,7 @@ int hbtgpu_get_buckets_host(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scaled, do
   if (!ctx) return -EINVAL;
   CK(cudaSetDevice(ctx->device));
   const uint32_t n = ctx->cfg.n_events;
-  if (acc) CK(cudaMemcpyAsync(acc, ctx->d_acc, ctx->acc_words * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (acc) CK(cudaMemcpyAsync(acc, ctx->acc_cur, ctx->acc_words * 8, cudaMemcpyDeviceToHost, ctx->stream));
   if (scaled) CK(cudaMemcpyAsync(scaled, ctx->d_scaled, ctx->n_cells * n * 8, cudaMemcpyDeviceToHost, ctx->stream));
   if (metric && ctx->cfg.n_metrics)
     CK(cudaMemcpyAsync(metric, ctx->d_metric, ctx->n_cells * ctx->cfg.n_metrics * 8,
@@ -1000,7 +1022,7 @@ int hbtgpu_get_buckets_host_async(hbtgpu_ctx* ctx, uint64_t* acc, uint64_t* scal
   CK(cudaEventRecord(ctx->ev_results, ctx->stream));
   CK(cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_results, 0));
   cudaStream_t s2 = ctx->d2h_stream;
-  if (acc) CK(cudaMemcpyAsync(acc, ctx->d_acc, ctx->acc_words * 8, cudaMemcpyDeviceToHost, s2));
+  if (acc) CK(cudaMemcpyAsync(acc, ctx->acc_cur, ctx->acc_words * 8, cudaMemcpyDeviceToHost, s2));
   if (scaled) CK(cudaMemcpyAsync(scaled, ctx->d_scaled, ctx->n_cells * n * 8, cudaMemcpyDeviceToHost, s2));
   if (metric && ctx->cfg.n_metrics)
     CK(cudaMemcpyAsync(metric, ctx->d_metric, ctx->n_cells * ctx->cfg.n_metrics * 8, cudaMemcpyDeviceToHost, s2));
@@ -1047,7 +1069,7 @@ int hbtgpu_apply_boundaries(hbtgpu_ctx* ctx, const hbtgpu_carry* prev_tails) {
   // d_carry_in is free in shard mode (the decode used an invalid state): stage prev_tails there
   CK(cudaMemcpyAsync(ctx->d_carry_in, prev_tails, ns * sizeof(hbtgpu_carry), cudaMemcpyHostToDevice, ctx->stream));
   Params P = make_params(ctx);
-  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in, ctx->d_boundary_cell);
+  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in, nullptr, ctx->d_boundary_cell);
   CK(cudaGetLastError());
   // streams without a SAMPLE pass the previous state through: fix their carry-out on the host side
   CK(cudaStreamSynchronize(ctx->stream));  // prev_tails may be reused by the caller after this
@@ -1057,7 +1079,7 @@ int hbtgpu_apply_boundaries(hbtgpu_ctx* ctx, const hbtgpu_carry* prev_tails) {
 }
 
 size_t hbtgpu_stub_bytes(const hbtgpu_ctx* ctx) {
-  return ctx ? static_cast<size_t>(ctx->cfg.max_cpus) * (sizeof(hbtgpu_head_stub) + sizeof(hbtgpu_carry)) : 0;
+  return ctx ? static_cast<size_t>(ctx->cfg.max_cpus) * stub_words(ctx->cfg.n_events) * 8 : 0;
 }
 
 int hbtgpu_export_stubs_device(hbtgpu_ctx* ctx, void* device_dst) {
@@ -1066,11 +1088,10 @@ int hbtgpu_export_stubs_device(hbtgpu_ctx* ctx, void* device_dst) {
   if (!(ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY))
     return fail(ctx, -EINVAL, "context was not created with HBTGPU_F_EXTERNAL_CARRY");
   CK(cudaSetDevice(ctx->device));
-  const size_t ns = ctx->cfg.max_cpus;
-  uint8_t* d = static_cast<uint8_t*>(device_dst);
-  CK(cudaMemcpyAsync(d, ctx->d_head, ns * sizeof(hbtgpu_head_stub), cudaMemcpyDeviceToDevice, ctx->stream));
-  CK(cudaMemcpyAsync(d + ns * sizeof(hbtgpu_head_stub), ctx->d_carry_out, ns * sizeof(hbtgpu_carry),
-                     cudaMemcpyDeviceToDevice, ctx->stream));
+  const uint32_t total = ctx->cfg.max_cpus * stub_words(ctx->cfg.n_events);
+  k_pack_stubs<<<(total + 255) / 256, 256, 0, ctx->stream>>>(make_params(ctx), static_cast<uint64_t*>(device_dst));
+  CK(cudaGetLastError());
+  ctx->stats.kernel_launches += 1;
   return 0;
 }
 
@@ -1085,9 +1106,9 @@ int hbtgpu_apply_boundaries_gathered(hbtgpu_ctx* ctx, const void* device_gathere
   const uint32_t ns = ctx->cfg.max_cpus;
   Params P = make_params(ctx);
   // d_carry_in is free in shard mode (the decode used an invalid state): it receives the fold
-  k_fold<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(static_cast<const uint8_t*>(device_gathered), rank,
-                                                    ns, ctx->d_carry_init, ctx->d_carry_in);
-  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in, ctx->d_boundary_cell);
+  k_fold<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(P, static_cast<const uint64_t*>(device_gathered), world, rank,
+                                                    ctx->d_carry_init, ctx->d_carry_in, ctx->d_dead, nullptr);
+  k_boundary<<<ns, 128, 0, ctx->stream>>>(P, ctx->d_carry_in, ctx->d_dead, ctx->d_boundary_cell);
   CK(cudaGetLastError());
   ctx->counters_valid = false;
   ctx->emitted = false;
@@ -1460,5 +1481,6 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
 
 }  // extern "C"
 
+#include "hbtgpu_peer.inc"
 #include "hbtgpu_series.inc"
 #include "hbtgpu_cs_host.inc"

@@ -144,7 +144,14 @@ struct StreamDesc {
 // per-stream counters as u64 slots
 enum {
   C_LOST = 0, C_THROTTLE, C_UNTHROTTLE, C_SAMPLE, C_READ, C_RECORDS, C_UNKNOWN, C_ROWS, C_OOR,
-  C_ERR, C_ERR_OFF, C_LAST_TS, C_SLOTS = 16
+  C_ERR, C_ERR_OFF, C_LAST_TS, C_LAST_SAMPLE_TS, C_SLOTS = 16
+};
+
+// Shard mode: the records in front of a shard's first SAMPLE, as consume() accounts for them.
+// Needed when that SAMPLE turns out to go back in time against the previous shard: the walk
+// stalls there (PerCpuCountSampleGenerator.h:156-163) and only these records were consumed.
+struct HeadExtra {
+  uint64_t records, lost, throttle, unthrottle, read;
 };
 
 struct Params {
@@ -156,6 +163,7 @@ struct Params {
   const hbtgpu_carry* carry_in;
   hbtgpu_carry* carry_out;
   hbtgpu_head_stub* head;
+  struct HeadExtra* head_extra;  // shard mode: what the walk met before the first SAMPLE
   uint64_t* counters;  // [stream][C_SLOTS]
   uint64_t* acc;       // [stream][bucket][F]
   uint32_t* flags;
@@ -1706,6 +1714,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
         co.te = C.te;
         co.tr = C.tr;
         ctr[C_LAST_TS] = co.tstamp;
+        ctr[C_LAST_SAMPLE_TS] = C.valid ? C.ts : 0;  // time of the last SAMPLE, LOST behind it or not
       }
     }
   }
@@ -1939,6 +1948,7 @@ __global__ void __launch_bounds__(RES_THREADS) k_resolve(const Params P) {
   ctr[C_ERR] = static_cast<uint64_t>(err);
   ctr[C_ERR_OFF] = err_off;
   ctr[C_LAST_TS] = co.tstamp;
+  ctr[C_LAST_SAMPLE_TS] = last_off == PRED_CARRY_IN ? 0 : st_ts;
 }
 
 // zero result buffers when the exact path has to recompute them
@@ -2040,94 +2050,261 @@ __global__ void __launch_bounds__(TOPK_THREADS) k_topk_pick(const TopBest* parti
 // Shard mode (HBTGPU_F_EXTERNAL_CARRY): head stubs and boundary rows.
 
 // One thread per stream: walk from the stream start to its first SAMPLE (normally the very
-// first record).  The stream start is a record boundary, so this walk is exact.
+// first record).  The stream start is a record boundary, so this walk is exact.  The records it
+// steps over are counted as consume() counts them (HeadExtra).
 __global__ void k_head(const Params P) {
   const uint32_t sidx = blockIdx.x * blockDim.x + threadIdx.x;
   if (sidx >= P.n_streams) return;
   hbtgpu_head_stub& hs = P.head[sidx];
+  HeadExtra hx{0, 0, 0, 0, 0};
   hs.has_sample = 0;
   hs.lost_before = 0;
   hs.offset = 0;
   const StreamDesc sd = P.streams[sidx];
   const uint32_t n = P.n_events;
-  for (uint32_t ii = 0; ii < sd.n_images; ++ii) {
+  bool done = false;
+  for (uint32_t ii = 0; ii < sd.n_images && !done; ++ii) {
     const ImageDesc im = P.images[sd.first_image + ii];
     uint64_t pos = 0;
     while (pos < im.len) {
       const uint64_t* r = reinterpret_cast<const uint64_t*>(P.arena + im.base + pos);
       const uint64_t h = r[0];
       const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
-      if (size < 8 || (size & 7) || pos + size > im.len) return;  // the decode reports the error
+      if (size < 8 || (size & 7) || pos + size > im.len) {  // the decode reports the error
+        done = true;
+        break;
+      }
       if (type == REC_SAMPLE) {
         const uint32_t pre = P.pre;
-        if (size < P.fix || r[pre + 2] != ((size - P.fix) >> 3) || r[pre + 2] != n) return;
-        hs.tstamp = r[pre + 1];
-        hs.te = r[pre + 3];
-        hs.tr = r[pre + 4];
-        for (uint32_t e = 0; e < n; ++e) hs.value[e] = xform(P, e, r[pre + 5 + e]);
-        hs.offset = im.stream_pos + pos;
-        hs.has_sample = 1;
-        return;
+        if (!(size < P.fix || r[pre + 2] != ((size - P.fix) >> 3) || r[pre + 2] != n)) {
+          hs.tstamp = r[pre + 1];
+          hs.te = r[pre + 3];
+          hs.tr = r[pre + 4];
+          for (uint32_t e = 0; e < n; ++e) hs.value[e] = xform(P, e, r[pre + 5 + e]);
+          hs.offset = im.stream_pos + pos;
+          hs.has_sample = 1;
+        }
+        done = true;
+        break;
       }
       if (type == REC_LOST) {
-        if (size < 24) return;
+        if (size < 24) {
+          done = true;
+          break;
+        }
         hs.lost_before = 1;
+        hx.lost += r[2];
       } else if (type == REC_READ) {
-        if (size < 40 || r[2] != ((size - 40u) >> 3)) return;
+        if (size < 40 || r[2] != ((size - 40u) >> 3)) {
+          done = true;
+          break;
+        }
+        hx.read += 1;
+      } else if (type == REC_THROTTLE) {
+        hx.throttle += 1;
+      } else if (type == REC_UNTHROTTLE) {
+        hx.unthrottle += 1;
       }
+      hx.records += 1;
       pos += size;
     }
   }
+  if (P.head_extra) P.head_extra[sidx] = hx;
 }
 
-// Device form of hbtgpu_compose_tail folded over the ranks before `rank`: one thread per cpu.
-// gathered = `world` blocks of [n_streams head stubs | n_streams tails].
-__global__ void k_fold(const uint8_t* gathered, uint32_t rank, uint32_t n_streams,
-                       const hbtgpu_carry* init, hbtgpu_carry* prev_out) {
-  const uint32_t cpu = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cpu >= n_streams) return;
-  const size_t block = static_cast<size_t>(n_streams) * (sizeof(hbtgpu_head_stub) + sizeof(hbtgpu_carry));
-  const hbtgpu_carry* src = &init[cpu];
-  bool invalidated = false;
-  for (uint32_t r = 0; r < rank; ++r) {
-    const uint8_t* b = gathered + static_cast<size_t>(r) * block;
-    const hbtgpu_head_stub& hs = reinterpret_cast<const hbtgpu_head_stub*>(b)[cpu];
-    const hbtgpu_carry* tails =
-        reinterpret_cast<const hbtgpu_carry*>(b + static_cast<size_t>(n_streams) * sizeof(hbtgpu_head_stub));
-    if (hs.has_sample) {
-      src = &tails[cpu];  // a shard with a SAMPLE determines the state by itself
-      invalidated = false;
-    } else if (hs.lost_before) {
-      invalidated = true;  // only LOSTs: count_.tstamp invalid, last_[] kept
+// ---- packed stubs: what one rank tells the others about its shard, per cpu ----------------
+// u64 words: [0] flags  [1] stream offset of the first SAMPLE  [2] bytes of the shard's stream
+//            [3..5] first SAMPLE: time, time_enabled, time_running
+//            [6..8] state after the shard: count_.tstamp (~0 if invalid), te, tr of the last SAMPLE
+//            [9] time of the last SAMPLE  [10..10+n) values of the first SAMPLE  [10+n..10+2n) last_[]
+enum : uint64_t { SF_HAS_SAMPLE = 1, SF_LOST_BEFORE = 2, SF_TAIL_VALID = 4, SF_STALLED = 8 };
+enum { SW_FLAGS = 0, SW_HEAD_OFF, SW_STREAM_LEN, SW_HEAD_TS, SW_HEAD_TE, SW_HEAD_TR, SW_TAIL_TS, SW_TAIL_TE,
+       SW_TAIL_TR, SW_LAST_SAMPLE_TS, SW_VALUES };
+__host__ __device__ inline uint32_t stub_words(uint32_t n_events) { return SW_VALUES + 2 * n_events; }
+
+// word w of the packed stub of stream `cpu` (any thread may ask for any word)
+__device__ __forceinline__ uint64_t stub_word(const Params& P, uint32_t cpu, uint32_t w) {
+  const hbtgpu_head_stub& hs = P.head[cpu];
+  const hbtgpu_carry& co = P.carry_out[cpu];
+  const uint64_t* ctr = P.counters + static_cast<uint64_t>(cpu) * C_SLOTS;
+  const uint32_t n = P.n_events;
+  switch (w) {
+    case SW_FLAGS:
+      return (hs.has_sample ? SF_HAS_SAMPLE : 0) | (hs.lost_before ? SF_LOST_BEFORE : 0) |
+             (co.valid ? SF_TAIL_VALID : 0) | (ctr[C_ERR] ? SF_STALLED : 0);
+    case SW_HEAD_OFF: return hs.offset;
+    case SW_STREAM_LEN: {
+      const StreamDesc sd = P.streams[cpu];
+      uint64_t len = 0;
+      for (uint32_t i = 0; i < sd.n_images; ++i) len += P.images[sd.first_image + i].len;
+      return len;
     }
+    case SW_HEAD_TS: return hs.tstamp;
+    case SW_HEAD_TE: return hs.te;
+    case SW_HEAD_TR: return hs.tr;
+    case SW_TAIL_TS: return co.tstamp;
+    case SW_TAIL_TE: return co.te;
+    case SW_TAIL_TR: return co.tr;
+    case SW_LAST_SAMPLE_TS: return ctr[C_LAST_SAMPLE_TS];
+    default: return w < SW_VALUES + n ? hs.value[w - SW_VALUES] : co.last[w - SW_VALUES - n];
   }
-  hbtgpu_carry o = *src;
-  if (invalidated) {
-    o.valid = 0;
-    o.tstamp = ~0ull;
-  }
-  prev_out[cpu] = o;
 }
 
-// One block per stream: add the row that straddles the shard boundary.
+// this rank's block of packed stubs -> dst (device memory of this GPU or, over NVLink, of a peer)
+__global__ void __launch_bounds__(256) k_pack_stubs(const Params P, uint64_t* dst) {
+  const uint32_t sw = stub_words(P.n_events);
+  const uint32_t total = P.n_streams * sw;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const uint32_t cpu = i / sw;
+    dst[i] = stub_word(P, cpu, i - cpu * sw);
+  }
+}
+
+// Replay of the generator's state over the shards in rank order: one thread per cpu.
+// gathered = `world` blocks of n_streams packed stubs.  Mirrors handleRecordLost /
+// handleRecordSample (PerCpuCountSampleGenerator.h:110-124,135-163,198-199): a shard with a
+// SAMPLE determines the state by itself; one without passes the previous state through,
+// invalidated if it holds a LOST.  The walk of a cpu STALLS for good at the first record it
+// fails on (consume() keeps returning the error, :1505,1521, gen :162): at a shard's own decode
+// error, or at a shard's first SAMPLE when it goes back in time against the state before it.
+// Shards behind a stall contribute nothing.  Outputs for `rank`: the state in front of its shard
+// and dead[cpu] (1: an earlier shard stalled); for every rank r: the bucket range its rows can
+// have touched (ranges[r * n_streams + cpu] = lo | hi << 32, lo > hi: none), if ranges != null.
+__global__ void k_fold(const Params P, const uint64_t* gathered, uint32_t world, uint32_t rank,
+                       const hbtgpu_carry* init, hbtgpu_carry* prev_out, uint32_t* dead_out,
+                       uint64_t* ranges) {
+  const uint32_t cpu = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t ns = P.n_streams;
+  if (cpu >= ns) return;
+  const uint32_t n = P.n_events, sw = stub_words(n);
+  // the state is (valid, tstamp) plus a pointer to where te / tr / last[] come from
+  bool valid = init[cpu].valid != 0;
+  uint64_t tstamp = init[cpu].tstamp;
+  const uint64_t* src = nullptr;  // packed stub whose tail holds te, tr, last[]; null: init
+  bool dead = false;
+  for (uint32_t r = 0; r < world; ++r) {
+    if (r == rank) {
+      hbtgpu_carry o;
+      if (src) {
+        o.te = src[SW_TAIL_TE];
+        o.tr = src[SW_TAIL_TR];
+        for (uint32_t e = 0; e < n; ++e) o.last[e] = src[SW_VALUES + n + e];
+      } else {
+        o = init[cpu];
+      }
+      o.valid = valid ? 1 : 0;
+      o.tstamp = valid ? tstamp : ~0ull;
+      // only the first n values are meaningful; write field by field (the struct is 544 bytes)
+      hbtgpu_carry& d = prev_out[cpu];
+      d.valid = o.valid;
+      d.tstamp = o.tstamp;
+      d.te = o.te;
+      d.tr = o.tr;
+      for (uint32_t e = 0; e < n; ++e) d.last[e] = o.last[e];
+      dead_out[cpu] = dead ? 1u : 0u;
+      if (!ranges) return;
+    }
+    const uint64_t* st = gathered + (static_cast<size_t>(r) * ns + cpu) * sw;
+    const uint64_t fl = st[SW_FLAGS];
+    uint32_t lo = 1, hi = 0;
+    if (!dead) {
+      const bool has = (fl & SF_HAS_SAMPLE) != 0, lostb = (fl & SF_LOST_BEFORE) != 0;
+      if (has && !lostb && valid && tstamp > st[SW_HEAD_TS]) {
+        dead = true;  // stalls on this shard's first SAMPLE: nothing of the shard is aggregated
+      } else {
+        if (has) {
+          // rows of the shard lie between its first and its last SAMPLE
+          const uint64_t d0 = st[SW_HEAD_TS] - P.t0, d1 = st[SW_LAST_SAMPLE_TS] - P.t0;
+          const bool below0 = st[SW_HEAD_TS] < P.t0, below1 = st[SW_LAST_SAMPLE_TS] < P.t0;
+          if (!below1 && !(!below0 && d0 >= P.range_ns)) {
+            lo = below0 ? 0u : bucket_of(P, st[SW_HEAD_TS]);
+            hi = d1 >= P.range_ns ? P.n_buckets - 1 : bucket_of(P, st[SW_LAST_SAMPLE_TS]);
+          }
+          src = st;
+          valid = (fl & SF_TAIL_VALID) != 0;
+          tstamp = st[SW_TAIL_TS];
+        } else if (lostb) {
+          valid = false;
+        }
+        if (fl & SF_STALLED) dead = true;  // the shard's own walk stalled: later shards are never reached
+      }
+    }
+    if (ranges) ranges[static_cast<size_t>(r) * ns + cpu] = static_cast<uint64_t>(lo) | (static_cast<uint64_t>(hi) << 32);
+  }
+  if (rank >= world) {  // the state after the last shard (no rank owns it)
+    hbtgpu_carry& d = prev_out[cpu];
+    d.valid = valid ? 1 : 0;
+    d.tstamp = valid ? tstamp : ~0ull;
+    d.te = src ? src[SW_TAIL_TE] : init[cpu].te;
+    d.tr = src ? src[SW_TAIL_TR] : init[cpu].tr;
+    for (uint32_t e = 0; e < n; ++e) d.last[e] = src ? src[SW_VALUES + n + e] : init[cpu].last[e];
+    dead_out[cpu] = dead ? 1u : 0u;
+  }
+}
+
+// One block per stream: add the row that straddles the shard boundary -- or, where the walk of
+// this cpu stalled before or at this shard's first SAMPLE, take the shard's contribution out.
+// dead: per cpu, 1 if an earlier shard stalled (null: none did).
 __global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_carry* prev_tails,
-                                                  uint64_t* touched_cell) {
+                                                  const uint32_t* dead, uint64_t* touched_cell) {
   const uint32_t sidx = blockIdx.x;
   if (threadIdx.x == 0) touched_cell[sidx] = ~0ull;  // which (cpu, bucket) cell got the boundary row
   const hbtgpu_head_stub& hs = P.head[sidx];
   const hbtgpu_carry& pt = prev_tails[sidx];
-  // handleRecordSample emits a row iff the state is valid when the SAMPLE arrives (:135,165-182)
-  if (!hs.has_sample || hs.lost_before || !pt.valid) return;
   uint64_t* ctr = P.counters + static_cast<uint64_t>(sidx) * C_SLOTS;
-  if (ctr[C_ERR] != 0 && ctr[C_ERR_OFF] <= hs.offset) return;  // the walk never got this far
-  if (pt.tstamp > hs.tstamp) {  // time regression across the boundary (:156-163)
+  const uint32_t n = P.n_events;
+  const bool is_dead = dead && dead[sidx];
+  const bool row = hs.has_sample && !hs.lost_before && pt.valid;
+  // handleRecordSample emits a row iff the state is valid when the SAMPLE arrives (:135,165-182)
+  const bool reached = !(ctr[C_ERR] != 0 && ctr[C_ERR_OFF] <= hs.offset);  // the shard's own walk got to that SAMPLE
+  const bool regress = !is_dead && row && reached && pt.tstamp > hs.tstamp;  // (:156-163)
+  if (is_dead || regress) {
+    // consume() never gets past the stall: of this shard only the records in front of its first
+    // SAMPLE (regress) or nothing at all (dead) were walked
+    uint64_t* acc = P.acc + static_cast<uint64_t>(sidx) * P.n_buckets * (n + 3);
+    const uint64_t words = static_cast<uint64_t>(P.n_buckets) * (n + 3);
+    for (uint64_t i = threadIdx.x; i < words; i += blockDim.x) acc[i] = 0;
     if (threadIdx.x == 0) {
+      HeadExtra hx{0, 0, 0, 0, 0};
+      if (regress && P.head_extra) hx = P.head_extra[sidx];
+      ctr[C_LOST] = hx.lost;
+      ctr[C_THROTTLE] = hx.throttle;
+      ctr[C_UNTHROTTLE] = hx.unthrottle;
+      ctr[C_READ] = hx.read;
+      ctr[C_RECORDS] = hx.records;
+      ctr[C_SAMPLE] = 0;
+      ctr[C_UNKNOWN] = 0;
+      ctr[C_ROWS] = 0;
+      ctr[C_OOR] = 0;
       ctr[C_ERR] = static_cast<uint64_t>(-1);
-      ctr[C_ERR_OFF] = hs.offset;
+      ctr[C_ERR_OFF] = regress ? hs.offset : 0;
+      // the state stays what it was in front of the shard; a regression invalidates count_.tstamp
+      hbtgpu_carry& co = P.carry_out[sidx];
+      co.valid = regress ? 0 : pt.valid;
+      co.tstamp = (regress || !pt.valid) ? ~0ull : pt.tstamp;
+      co.te = pt.te;
+      co.tr = pt.tr;
+      ctr[C_LAST_TS] = co.tstamp;
+      touched_cell[sidx] = ~0ull - 1;  // "the whole row changed": derive_after_boundaries re-derives everything
+    }
+    for (uint32_t e = threadIdx.x; e < n; e += blockDim.x) P.carry_out[sidx].last[e] = pt.last[e];
+    return;
+  }
+  if (!hs.has_sample) {
+    // no SAMPLE in the shard: the state in front of it passes through (a LOST invalidates it)
+    hbtgpu_carry& co = P.carry_out[sidx];
+    for (uint32_t e = threadIdx.x; e < n; e += blockDim.x) co.last[e] = pt.last[e];
+    if (threadIdx.x == 0) {
+      const bool v = pt.valid && !hs.lost_before;
+      co.valid = v;
+      co.tstamp = v ? pt.tstamp : ~0ull;
+      co.te = pt.te;
+      co.tr = pt.tr;
+      ctr[C_LAST_TS] = co.tstamp;
     }
     return;
   }
-  const uint32_t n = P.n_events;
+  if (!row || !reached) return;
   const uint32_t bk = bucket_of(P, hs.tstamp);
   if (threadIdx.x == 0) {
     ctr[C_ROWS] += 1;
@@ -2217,19 +2394,26 @@ __global__ void __launch_bounds__(256) k_derive(const DeriveParams D) {
   D.valid[i] = derive_metrics(D, sc, tr, D.metric + i * D.n_metrics);
 }
 
-// the same for a short list of cells (those a shard-boundary row was added to after the full
-// derive had already run); entries of ~0 are skipped
-__global__ void __launch_bounds__(128) k_derive_cells(const DeriveParams D, const uint64_t* cells, uint32_t n_cells) {
-  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n_cells) return;
-  const uint64_t i = cells[t];
-  if (i == ~0ull) return;
+// the same for the cells a shard-boundary row was added to after the full derive had already
+// run: one block per cpu, cells[cpu] = the cell, ~0 for none, ~0 - 1 for "the whole row of this
+// cpu changed" (its walk stalled at or before this shard's first SAMPLE)
+__device__ __forceinline__ void derive_cell(const DeriveParams& D, uint64_t i) {
   const uint32_t n = D.n_events;
   const uint64_t* a = D.acc + i * (n + 3);
   const uint64_t te = a[n], tr = a[n + 1];
   uint64_t* sc = D.scaled + i * n;
   for (uint32_t e = 0; e < n; ++e) sc[e] = get_count(a[e], te, tr);
   D.valid[i] = derive_metrics(D, sc, tr, D.metric + i * D.n_metrics);
+}
+__global__ void __launch_bounds__(128) k_derive_cells(const DeriveParams D, const uint64_t* cells, uint32_t n_buckets) {
+  const uint64_t i = cells[blockIdx.x];
+  if (i == ~0ull) return;
+  if (i == ~0ull - 1) {
+    const uint64_t row = static_cast<uint64_t>(blockIdx.x) * n_buckets;
+    for (uint32_t b = threadIdx.x; b < n_buckets; b += blockDim.x) derive_cell(D, row + b);
+  } else if (threadIdx.x == 0) {
+    derive_cell(D, i);
+  }
 }
 
 // tiled form: a block stages the accumulators of blockDim.x cells with coalesced loads, each

@@ -93,6 +93,8 @@ ABI_SYMBOLS = [
     "hbtgpu_derive",
     "hbtgpu_get_stubs", "hbtgpu_compose_tail", "hbtgpu_apply_boundaries", "hbtgpu_stub_bytes",
     "hbtgpu_export_stubs_device", "hbtgpu_apply_boundaries_gathered", "hbtgpu_acc_device", "hbtgpu_stream",
+    "hbtgpu_peer_export", "hbtgpu_peer_attach", "hbtgpu_peer_attach_local", "hbtgpu_peer_detach",
+    "hbtgpu_exchange_boundaries", "hbtgpu_merge",
     "hbtgpu_math_get_count", "hbtgpu_math_rate", "hbtgpu_math_add_reduce",
     "hbtgpu_math_tsc_to_ktime", "hbtgpu_math_ktime_to_tsc", "hbtgpu_math_per_second_mega",
     "hbtgpu_math_running_ratio", "hbtgpu_get_stats", "hbtgpu_version",
@@ -100,6 +102,7 @@ ABI_SYMBOLS = [
 ]
 
 NOALLOC_MAX_IMAGE_BYTES = 64 << 20
+PEER_HANDLE_BYTES = 192
 
 _lib = None
 
@@ -380,6 +383,33 @@ class Context:
     def apply_boundaries_gathered(self, device_gathered, world, rank):
         self._ck(self.L.hbtgpu_apply_boundaries_gathered(self.h, C.c_void_p(device_gathered),
                                                          C.c_uint32(world), C.c_uint32(rank)))
+
+    # ---- exchange and merge over peer memory (one process per GPU, or contexts of one process)
+    def peer_export(self, world):
+        """This rank's handle (bytes) for hbtgpu_peer_attach on the other ranks."""
+        buf = C.create_string_buffer(PEER_HANDLE_BYTES)
+        self._ck(self.L.hbtgpu_peer_export(self.h, C.c_uint32(world), buf))
+        return buf.raw
+
+    def peer_attach(self, world, rank, handles):
+        """handles: list of `world` byte strings from peer_export, in rank order."""
+        blob = b"".join(handles)
+        assert len(blob) == world * PEER_HANDLE_BYTES
+        self._ck(self.L.hbtgpu_peer_attach(self.h, C.c_uint32(world), C.c_uint32(rank), blob))
+
+    def peer_attach_local(self, world, rank, ctxs):
+        """ctxs: the `world` Context objects of this process, in rank order."""
+        arr = (C.c_void_p * world)(*[c.h for c in ctxs])
+        self._ck(self.L.hbtgpu_peer_attach_local(self.h, C.c_uint32(world), C.c_uint32(rank), arr))
+
+    def peer_detach(self):
+        self._ck(self.L.hbtgpu_peer_detach(self.h))
+
+    def exchange_boundaries(self):
+        self._ck(self.L.hbtgpu_exchange_boundaries(self.h))
+
+    def merge(self):
+        self._ck(self.L.hbtgpu_merge(self.h))
 
     def apply_boundaries(self, prev_tails):
         """prev_tails: ctypes array (Carry * max_cpus): state before this shard, per cpu."""

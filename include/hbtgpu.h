@@ -270,14 +270,19 @@ void hbtgpu_compose_tail(const hbtgpu_carry* prev, const hbtgpu_head_stub* head,
  * the derive step. Call once per hbtgpu_run. */
 int hbtgpu_apply_boundaries(hbtgpu_ctx* ctx, const hbtgpu_carry* prev_tails);
 
-/* The same exchange without host round trips (what bench.py uses at N > 1): the stubs stay in
- * device memory, the collective (e.g. ncclAllGather through torch.distributed, enqueued on
- * hbtgpu_stream) moves them, and the fold runs in a kernel.
- *   hbtgpu_stub_bytes            size of one rank's stub block: max_cpus heads, then max_cpus tails
- *   hbtgpu_export_stubs_device   copy this rank's block to device_dst (async, context stream)
+/* The same exchange without host round trips: the stubs stay in device memory, a collective
+ * (e.g. ncclAllGather through torch.distributed, enqueued on hbtgpu_stream) moves them, and the
+ * fold runs in a kernel.  A rank's block is opaque to the caller (packed: 10 + 2 * n_events words
+ * per cpu).  Unlike the host protocol above, the device fold also reproduces what the reference
+ * does after an error: a cpu's walk stalls for good at the first record consume() fails on
+ * (hbt/src/perf_event/PerfEventsGroup.h:1505,1521, PerCpuCountSampleGenerator.h:156-163), so the
+ * shards behind it -- and a shard whose first SAMPLE goes back in time against the previous shard
+ * -- contribute nothing: their sums for that cpu are cleared and their counters say err = -EPERM.
+ *   hbtgpu_stub_bytes            size of one rank's stub block
+ *   hbtgpu_export_stubs_device   pack this rank's block into device_dst (async, context stream)
  *   hbtgpu_apply_boundaries_gathered
- *                                device_gathered = `world` blocks in rank order; folds the tails
- *                                of ranks < rank starting from the carry set with
+ *                                device_gathered = `world` blocks in rank order; replays the
+ *                                generator state over the ranks starting from the carry set with
  *                                hbtgpu_set_carry, adds the boundary rows, runs the derive step
  *                                (all async on the context stream).  If hbtgpu_derive was
  *                                called after hbtgpu_run (say, while the collective was in
@@ -287,6 +292,40 @@ size_t hbtgpu_stub_bytes(const hbtgpu_ctx* ctx);
 int hbtgpu_export_stubs_device(hbtgpu_ctx* ctx, void* device_dst);
 int hbtgpu_apply_boundaries_gathered(hbtgpu_ctx* ctx, const void* device_gathered, uint32_t world,
                                      uint32_t rank);
+
+/* ---- the exchange and the merge over peer memory (NVLink), no collective library ---------
+ *
+ * SURVEY.md 8(b)/(e) asks for hbtgpu_merge: "only the small per-shard partial aggregates are
+ * merged".  There is no reference code for this (hbt is one process on one host,
+ * hbt/src/mon/TraceCollector.h:501-550).  One process per GPU (or several contexts in one
+ * process): every rank exports a handle, the handles are exchanged by any means (a few bytes:
+ * torch.distributed.all_gather_object, MPI, a file), every rank attaches, and from then on a step
+ * is   hbtgpu_run -> hbtgpu_exchange_boundaries -> [hbtgpu_merge]   with no host round trip:
+ *   hbtgpu_exchange_boundaries  stores this rank's packed stubs into every peer's mailbox,
+ *                               waits for everybody's, then does what
+ *                               hbtgpu_apply_boundaries_gathered does
+ *   hbtgpu_merge                every rank ends up with the sums of ALL ranks: the bucket ranges
+ *                               each rank's rows can have touched are known from the stubs, so a
+ *                               rank reads exactly those from its peers' accumulators (ordinary
+ *                               loads over NVLink) and runs the derive step on the totals.
+ *                               Afterwards the bucket getters return the totals (until the next
+ *                               hbtgpu_run); hbtgpu_acc_device keeps returning this rank's own
+ *                               partial sums.  Requires the same t0 / bucket_ns / n_buckets /
+ *                               metrics on all ranks.  Integer sums: bit-identical to one
+ *                               context over the whole capture, whatever the order.
+ * All ranks must issue the same sequence of these calls.  A rank that waits longer than 4 s for
+ * a peer gives up: the next hbtgpu_sync returns -ETIMEDOUT (nothing hangs).
+ * Contexts must have HBTGPU_F_EXTERNAL_CARRY.  hbtgpu_destroy detaches. */
+#define HBTGPU_PEER_HANDLE_BYTES 192
+int hbtgpu_peer_export(hbtgpu_ctx* ctx, uint32_t world, void* handle /* HBTGPU_PEER_HANDLE_BYTES */);
+/* handles: world * HBTGPU_PEER_HANDLE_BYTES, in rank order (this rank's own included) */
+int hbtgpu_peer_attach(hbtgpu_ctx* ctx, uint32_t world, uint32_t rank, const void* handles);
+/* the same for contexts that live in this process (peers[rank] is ignored) */
+int hbtgpu_peer_attach_local(hbtgpu_ctx* ctx, uint32_t world, uint32_t rank, hbtgpu_ctx* const* peers);
+int hbtgpu_peer_detach(hbtgpu_ctx* ctx);
+int hbtgpu_exchange_boundaries(hbtgpu_ctx* ctx);
+int hbtgpu_merge(hbtgpu_ctx* ctx);
+
 /* Device address/size of the acc tensor, for a collective (NCCL all-reduce over u64 as i64). */
 int hbtgpu_acc_device(hbtgpu_ctx* ctx, void** device_ptr, size_t* bytes);
 /* The CUDA stream the context launches on (a cudaStream_t). */

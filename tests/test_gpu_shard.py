@@ -140,3 +140,121 @@ def test_derive_before_boundaries_equals_derive_after():
     for k in ("acc", "scaled", "metric", "valid"):
         assert np.array_equal(outs[0][k].view(np.uint8), outs[1][k].view(np.uint8)), k
     assert outs[0]["scaled"].any()
+
+
+# ---- exchange + merge over peer memory (hbtgpu_peer_*, hbtgpu_exchange_boundaries, hbtgpu_merge) ----
+def _run_peer_world(shards, init, nb, n=N, flags=0, metrics=(), merge=True, bucket_ns=BNS):
+    """shards[cpu][rank] = bytes.  One context per rank on this GPU, attached to each other as
+    peers; returns per rank (buckets dict, [counters per cpu], [carry per cpu])."""
+    ncpu, world = len(shards), len(shards[0])
+    ctxs, out = [], []
+    try:
+        for r in range(world):
+            total = sum(len(shards[c][r]) for c in range(ncpu))
+            g = hbtgpu.Context(n_events=n, max_cpus=ncpu, n_buckets=nb, t0=T0, bucket_ns=bucket_ns,
+                               arena_bytes=total + (1 << 16), metrics=metrics,
+                               flags=flags | hbtgpu.F_EXTERNAL_CARRY)
+            for c in range(ncpu):
+                g.set_carry(c, to_gpu_carry(init[c]))
+                g.submit_image(c, shards[c][r])
+            ctxs.append(g)
+        for r, g in enumerate(ctxs):
+            g.peer_attach_local(world, r, ctxs)
+        for rep in range(2):  # twice: the mailbox copies alternate, results must not change
+            for g in ctxs:
+                g.run()
+            for g in ctxs:  # nothing below blocks the host: the waits of one rank are met by the others
+                g.exchange_boundaries()
+            if merge:
+                for g in ctxs:
+                    g.merge()
+            for g in ctxs:
+                g.sync()
+        for g in ctxs:
+            out.append((g.buckets(), [g.counters(c) for c in range(ncpu)], [g.carry(c) for c in range(ncpu)]))
+    finally:
+        for g in ctxs:
+            g.close()
+    return out
+
+
+@pytest.mark.parametrize("flags", [0, hbtgpu.F_FORCE_EXACT])
+def test_peer_exchange_and_merge_match_single_stream(port_oracle, flags):
+    world = 3
+    raw = _streams()
+    streams, shards = [], []
+    for cpu, (d, _) in enumerate(raw):
+        if isinstance(d, tuple):
+            pieces = [rg.to_u8(b"".join(p)) for p in d]
+            streams.append(np.concatenate(pieces))
+            shards.append(pieces)
+        else:
+            c = _cut(port_oracle, d, [0.31, 0.77])
+            streams.append(d)
+            shards.append([d[c[i]:c[i + 1]] for i in range(world)])
+    t_end = max(t for _, t in raw)
+    nb = int((t_end - T0) // BNS) + 2
+    params = po.make_params(N, n_buckets=nb, t0=T0, bucket_ns=BNS)
+    ncpu = len(streams)
+    init = [po.make_carry(valid=(cpu != 1), tstamp=T0 - 3, te=1, tr=1, last=[2] * N) for cpu in range(ncpu)]
+    res = _run_peer_world(shards, init, nb, flags=flags, metrics=[(hbtgpu.METRIC_RATE, [1, 0])])
+    for c in range(ncpu):
+        exp = port_oracle.decode_stream(params, streams[c], init[c])
+        scaled = port_oracle.scale_buckets(params, exp["buckets"])
+        for r in range(world):  # every rank holds the totals
+            assert np.array_equal(res[r][0]["acc"][c], exp["buckets"]), f"cpu {c} rank {r}: merged sums differ"
+            assert np.array_equal(res[r][0]["scaled"][c], scaled), f"cpu {c} rank {r}: scaled counts differ"
+        for k in ("num_rows", "num_unknown_count_interval", "lost", "num_records", "sample", "throttle"):
+            assert sum(res[r][1][c][k] for r in range(world)) == exp["counters"][k], (c, k)
+        co = exp["carry_out"]  # the last rank's carry-out is the stream's
+        last = res[world - 1][2][c]
+        assert int(last.valid) == int(co.valid)
+        if co.valid:
+            assert int(last.tstamp) == int(co.tstamp)
+        assert [int(last.last[i]) for i in range(N)] == [int(co.last[i]) for i in range(N)]
+
+
+def test_stalled_walk_masks_the_shards_behind_it(port_oracle):
+    """The reference stalls a cpu for good at the first record consume() fails on
+    (PerfEventsGroup.h:1505, PerCpuCountSampleGenerator.h:156-163).  Sharded, the ranks behind the
+    stall must contribute nothing, and a shard whose first SAMPLE goes back in time against the
+    previous shard must contribute only the records in front of that SAMPLE."""
+    world = 3
+
+    def run(k0, k1):
+        return [rg.sample(T0 + 1000 * i, i, i, [i, 2 * i, 3 * i, 4 * i]) for i in range(k0, k1)]
+
+    shards = []
+    # cpu 0: a SAMPLE with a wrong size in the middle of shard 1
+    shards.append([b"".join(run(1, 40)),
+                   b"".join(run(40, 60) + [rg.sample(T0 + 60_000, 60, 60, [1, 2, 3, 4], size=64)] + run(61, 80)),
+                   b"".join(run(80, 120))])
+    # cpu 1: time goes back exactly at the boundary between shard 1 and shard 2
+    shards.append([b"".join(run(1, 40)), b"".join(run(40, 80)), b"".join(run(70, 110))])
+    # cpu 2: the same with THROTTLE / UNTHROTTLE / another record in front of the offending SAMPLE
+    shards.append([b"".join(run(1, 40)), b"".join(run(40, 80)),
+                   b"".join([rg.throttle(1), rg.unthrottle(2), rg.other(33, [5, 6])] + run(75, 110))])
+    # cpu 3: time goes back at the boundary, but a LOST in front re-bases: no stall
+    shards.append([b"".join(run(1, 40)), b"".join(run(40, 80)), b"".join([rg.lost(9)] + run(70, 110))])
+    # cpu 4: healthy
+    shards.append([b"".join(run(1, 40)), b"".join(run(40, 80)), b"".join(run(80, 120))])
+    # cpu 5: time goes back at the FIRST boundary: shards 1 and 2 are both behind the stall
+    shards.append([b"".join(run(10, 40)), b"".join(run(5, 80)), b"".join(run(80, 120))])
+    shards = [[rg.to_u8(x) for x in s] for s in shards]
+    ncpu = len(shards)
+    nb = 4
+    params = po.make_params(N, n_buckets=nb, t0=T0, bucket_ns=50_000)
+    init = [po.make_carry(valid=True, tstamp=T0, te=0, tr=0, last=[0] * N) for _ in range(ncpu)]
+    res = _run_peer_world(shards, init, nb, bucket_ns=50_000)
+    for c in range(ncpu):
+        exp = port_oracle.decode_stream(params, np.concatenate(shards[c]), init[c])
+        for r in range(world):
+            assert np.array_equal(res[r][0]["acc"][c], exp["buckets"]), f"cpu {c} rank {r}: merged sums differ"
+        for k in ("num_rows", "num_unknown_count_interval", "lost", "num_records", "sample", "throttle", "unthrottle"):
+            assert sum(res[r][1][c][k] for r in range(world)) == exp["counters"][k], (c, k)
+        assert (exp["counters"]["err"] != 0) == any(res[r][1][c]["err"] != 0 for r in range(world)), c
+    # the ranks behind a stall say so
+    assert res[2][1][0]["err"] != 0 and res[2][1][0]["num_records"] == 0
+    assert res[2][1][1]["err"] != 0 and res[2][1][2]["num_records"] == 3
+    assert res[1][1][5]["err"] != 0 and res[2][1][5]["err"] != 0
+    assert res[2][1][3]["err"] == 0 and res[2][1][4]["err"] == 0
