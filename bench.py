@@ -4,17 +4,28 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 A "step" is one pass of the hot path over one capture: decode every ring image,
-aggregate into (cpu, event, 1 ms bucket) sums, multiplex-scale, IPC / miss-rate.
-Workload at every N: BASELINE.json configs[1] per GPU -- 192 CPUs, 8-event group,
-10 kHz for 10 s (19.2 M SAMPLE records of 104 B = 2.0 GB) -- i.e. weak scaling:
-rank r holds time window r of the same 192 CPUs.
+aggregate into (cpu, event, time bucket) sums, multiplex-scale, IPC / miss-rate.
 
-Prints ONE JSON line (rank 0).  `value` = records/s with the capture resident in
-HBM; `e2e` = the same through the C ABI with HOST (pinned) buffers, H2D of the
-images and D2H of the results inside the timed region.  `--impl reference` times
-the reference's own CPU code (oracle/_ref, the real hbt sources) on the host cores.
+Top-level keys (the headline, BASELINE.json configs[1], the configuration the metric is quoted
+on): 192 CPUs, 8-event group, 10 kHz for 10 s (19.2 M SAMPLE records of 104 B = 2.0 GB), 1 ms
+buckets, PER GPU -- weak scaling: rank r holds time window r of the same 192 CPUs; what crosses
+ranks is the per-cpu stubs of the shard boundaries (peer memory over NVLink).
+`value` = records/s with the capture resident in HBM; `e2e` = the same through the C ABI with
+HOST (pinned) buffers, H2D of the images and D2H of the results inside the timed region.
+
+"strong" (BASELINE.json configs[4]): ONE capture of 24 time windows x 192 CPUs x 16 MiB
+(77 GB), sharded by window over the N GPUs, boundary rows exchanged and the bucket sums of all
+ranks MERGED inside the timed region (hbtgpu_exchange_boundaries + hbtgpu_merge), every rank
+checked against the CPU oracle afterwards ("parity_checked").
+
+"configs" (N = 1): the other single-GPU configurations of BASELINE.json, each with kernel time,
+step time, fraction of the HBM roofline and a parity flag from a post-run oracle comparison.
+
+`--impl reference` times the reference's own CPU code (oracle/_ref, the real hbt sources) on
+the host cores, on the headline configuration.
 """
 import argparse
+import ctypes as C
 import json
 import os
 import statistics
@@ -34,17 +45,16 @@ N_BUCKETS = 10_000 + 100  # 10 s of 1 ms buckets (+ slack for period jitter)
 RECORD_BYTES = 40 + 8 * N_EVENTS
 METRIC = "perf_records_decoded_aggregated_per_s"
 UNIT = "records/s"
-WORKLOAD = ("cfg2: 192-CPU capture, 8-event group, 10 kHz x 10 s, 1 ms buckets, "
-            "IPC + LLC-miss-rate (synthetic, 19.2M SAMPLE records, 2.0 GB per GPU)")
+WORKLOAD = ("cfg2 (BASELINE.json configs[1], the configuration the metric is quoted on): 192-CPU capture, "
+            "8-event group, 10 kHz x 10 s, 1 ms buckets, IPC + LLC-miss-rate (synthetic, 19.2M SAMPLE "
+            "records, 2.0 GB per GPU); the other configurations are under \"configs\" and \"strong\"")
+T_START = 1_000_000_000
 
-
-def ncu_traffic():
-    """dram read+write bytes per launch of the dominant kernel, from the committed ncu capture."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(p):
-        with open(p) as f:
-            return float(json.load(f)["traffic_bytes_per_launch"])
-    return None
+# the strong-scaled capture (BASELINE.json configs[4])
+STRONG_WINDOWS = 24
+STRONG_WINDOW_BYTES = 16 << 20
+STRONG_BUCKET_NS = 100_000_000  # 100 ms: "only the small per-shard partial aggregates are merged"
+STRONG_WINDOW_SPAN_NS = 17_000_000_000  # a 16 MiB window holds < 161 320 samples of <= 105 us
 
 
 def measured_peaks():
@@ -53,6 +63,16 @@ def measured_peaks():
         with open(p) as f:
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    """dram read+write bytes per launch of the dominant kernel, from the committed ncu capture."""
+    for name in ("r02_traffic.json", "r01_traffic.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            with open(p) as f:
+                return float(json.load(f)["traffic_bytes_per_launch"]), f"profiles/{name}"
+    return None, None
 
 
 class ClockSampler:
@@ -113,39 +133,51 @@ class ClockSampler:
                     "samples": 0}
 
 
-def gen_capture(rank, pinned=True):
-    """Time window `rank` of the 192-CPU capture, in pinned host memory. Returns (streams, keepalive)."""
-    import numpy as np
+def mem_available_bytes():
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) * 1024
+    except OSError:
+        pass
+    return 1 << 62
+
+
+def host_buffer(nbytes, pinned=True):
     import torch
-    from dynolog_b200 import synth
-    spec = synth.make_spec(2)
-    cap = synth.Capture(spec, N_CPUS)
-    per_cpu = ((SAMPLES_PER_CPU * RECORD_BYTES + 4096) + 127) // 128 * 128
     if pinned and torch.cuda.is_available():
-        host = torch.empty(N_CPUS * per_cpu, dtype=torch.uint8, pin_memory=True)
-    else:
-        host = torch.empty(N_CPUS * per_cpu, dtype=torch.uint8)
-    buf = host.numpy()
-    streams = None
-    for w in range(rank + 1):  # the generator is sequential in time: skip to our window
-        streams = cap.window(n_samples=SAMPLES_PER_CPU, max_bytes_per_cpu=per_cpu, out=buf)
-    t_start = synth.T_START + rank * SAMPLES_PER_CPU * 100_000  # nominal window start
-    return streams, host, t_start
+        return torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    return torch.empty(nbytes, dtype=torch.uint8)
 
 
-def cpu_reference_run(streams, t0, n_threads, reps, kind):
+def gen_capture(rank, pinned=True, n_threads=None):
+    """Time window `rank` of the 192-CPU capture, in pinned host memory."""
+    from dynolog_b200 import synth
+    cap = synth.Capture(synth.make_spec(2), N_CPUS, n_threads=n_threads)
+    per_cpu = ((SAMPLES_PER_CPU * RECORD_BYTES + 4096) + 127) // 128 * 128
+    host = host_buffer(N_CPUS * per_cpu, pinned)
+    for w in range(rank):  # the generator is sequential in time: move past the earlier windows
+        cap.window(n_samples=SAMPLES_PER_CPU, max_bytes_per_cpu=per_cpu, dry=True)
+    streams = cap.window(n_samples=SAMPLES_PER_CPU, max_bytes_per_cpu=per_cpu, out=host.numpy())
+    return streams, host
+
+
+def cpu_reference_run(streams, t0, n_threads, reps, kind, n_events=N_EVENTS, n_buckets=N_BUCKETS,
+                      bucket_ns=BUCKET_NS, pre=0):
     """One timed pass = reference consume() on every stream + row drain + bucket sums."""
     from oracle import pyoracle as po
     o = po.load(kind)
-    p = po.make_params(N_EVENTS, n_buckets=N_BUCKETS, t0=t0, bucket_ns=BUCKET_NS)
-    carries = [po.make_carry(valid=True, tstamp=t0, last=[0] * N_EVENTS) for _ in streams]
+    p = po.make_params(n_events, n_buckets=n_buckets, t0=t0, bucket_ns=bucket_ns)
+    p.pre = pre
+    carries = [po.make_carry(valid=True, tstamp=t0, last=[0] * n_events) for _ in streams]
     times = []
     nrec = 0
     for _ in range(reps):
         secs, _, ctrs = o.run_capture(p, streams, carries, n_threads=n_threads, batch=4096,
                                       want_buckets=True)
         times.append(secs)
-        nrec = sum(c["sample"] + c["throttle"] + c["unthrottle"] + c["read"] for c in ctrs)
+        nrec = sum(c["num_records"] for c in ctrs)
     return times, nrec, o.description
 
 
@@ -159,16 +191,28 @@ def pick_cpu_kind():
     return "port", "port"
 
 
+def nolog_oracle():
+    """The reference with HBT_LOG_* compiled out (oracle/_ref/libhbtref_nolog.so), or None."""
+    from oracle import pyoracle as po
+    p = os.path.join(ROOT, "oracle", "_ref", "libhbtref_nolog.so")
+    if not os.path.exists(p):
+        return None
+    try:
+        return po.Oracle(p, "hbtref")
+    except Exception:
+        return None
+
+
 def run_reference_arm(args, rank, world):
     """--impl reference: the reference's CPU implementation on the host cores (rank 0 only)."""
     if rank != 0:
         return
     lib_kind, kind = pick_cpu_kind()
-    streams, keep, t0 = gen_capture(0, pinned=False)
+    streams, keep = gen_capture(0, pinned=False)
     cores = os.cpu_count() or 1
     n_threads = min(cores, N_CPUS)
-    cpu_reference_run(streams, t0, n_threads, max(1, args.warmup), lib_kind)
-    times, nrec, desc = cpu_reference_run(streams, t0, n_threads, args.steps, lib_kind)
+    cpu_reference_run(streams, T_START, n_threads, max(1, args.warmup), lib_kind)
+    times, nrec, desc = cpu_reference_run(streams, T_START, n_threads, args.steps, lib_kind)
     ms = 1e3 * sum(times) / len(times)
     value = nrec / (ms * 1e-3)
     line = {
@@ -187,6 +231,381 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+# ---------------------------------------------------------------------------------------------
+# parity of one rank's shard against the CPU oracle (after the timed regions)
+
+def _oracle_carry(po, c, n):
+    return po.make_carry(valid=bool(c.valid), tstamp=int(c.tstamp), te=int(c.te), tr=int(c.tr),
+                         last=[int(c.last[i]) for i in range(n)])
+
+
+def _carry_key(c, n):
+    v = int(c.valid)
+    return [v, int(c.tstamp) if v else 0, int(c.te), int(c.tr)] + [int(c.last[i]) for i in range(n)]
+
+
+def shard_parity(ctx, shard_streams, cpus, n_events, n_buckets, t0, bucket_ns, world, rank, initial, dist,
+                 merged_expected=False):
+    """Compares this rank's counters and bucket sums of `cpus` with the oracle fed the same bytes
+    and the state the device fold put in front of the shard; closes the chain over the ranks by
+    checking that state against the previous rank's ORACLE carry-out.  With merged_expected the
+    caller then merges, and the totals are checked against an NCCL all-reduce of the partial sums.
+    Returns (ok, detail)."""
+    import numpy as np
+    from oracle import pyoracle as po
+    port = po.load("port")
+    params = po.make_params(n_events, n_buckets=n_buckets, t0=t0, bucket_ns=bucket_ns)
+    ctx.sync()
+    partial = ctx.buckets(want_scaled=False, want_metric=False, want_valid=False)["acc"]
+    carries, prevs = [], []
+    for cpu in cpus:
+        prev = ctx.prev_tail(cpu) if world > 1 else initial
+        prevs.append(_carry_key(prev, n_events))
+        carries.append(_oracle_carry(po, prev, n_events))
+    ok, why = True, []
+    outs = {}
+    for i, cpu in enumerate(cpus):
+        exp = port.decode_stream(params, shard_streams[cpu], carries[i], want_records=False, want_rows=False)
+        got = ctx.counters(cpu)
+        for k in ("lost", "throttle", "unthrottle", "sample", "num_records", "num_rows",
+                  "num_unknown_count_interval", "rows_out_of_range", "err"):
+            if got[k] != exp["counters"][k]:
+                ok = False
+                why.append(f"cpu {cpu} counter {k}: gpu {got[k]} oracle {exp['counters'][k]}")
+        if not np.array_equal(partial[cpu], exp["buckets"]):
+            ok = False
+            why.append(f"cpu {cpu}: bucket sums differ")
+        outs[cpu] = _carry_key(exp["carry_out"], n_events)  # the ORACLE's state after this shard
+        if _carry_key(ctx.carry(cpu), n_events) != outs[cpu]:
+            ok = False
+            why.append(f"cpu {cpu}: carry-out differs")
+    # one cpu through the compiled reference itself (where it travelled to this box)
+    ref_used = False
+    if po.available("reference"):
+        ref = po.load("reference")
+        cpu = cpus[0]
+        exp = ref.decode_stream(params, shard_streams[cpu], carries[0], want_records=False, want_rows=False)
+        ref_used = True
+        if not np.array_equal(partial[cpu], exp["buckets"]):
+            ok = False
+            why.append(f"cpu {cpu}: bucket sums differ from the compiled reference")
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, outs)
+        for i, cpu in enumerate(cpus):
+            want = gathered[rank - 1][cpu] if rank > 0 else _carry_key(initial, n_events)
+            if prevs[i] != want:
+                ok = False
+                why.append(f"cpu {cpu}: state in front of the shard differs from rank {rank - 1}'s oracle carry-out")
+    detail = {"cpus_checked": list(cpus), "compiled_reference_cpu": cpus[0] if ref_used else None}
+    if merged_expected and world > 1:
+        import torch
+        t = torch.from_numpy(partial.view(np.int64).copy()).cuda()
+        dist.all_reduce(t)  # NCCL: an independent path to the same integer sums
+        ctx.merge()
+        ctx.sync()
+        total = ctx.buckets(want_scaled=False, want_metric=False, want_valid=False)["acc"]
+        if not np.array_equal(total.view(np.int64), t.cpu().numpy()):
+            ok = False
+            why.append("merged totals differ from an NCCL all-reduce of the partial sums")
+        detail["merge_checked_against"] = "NCCL all-reduce (int64) of the ranks' partial sums"
+    if why:
+        detail["differences"] = why[:8]
+    return ok, detail
+
+
+def all_ranks_ok(ok, world, dist):
+    if world == 1:
+        return ok
+    import torch
+    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(int(t.item()))
+
+
+# ---------------------------------------------------------------------------------------------
+# the other single-GPU configurations (N = 1)
+
+def run_config_entry(name, hbtgpu, streams, n_events, n_buckets, bucket_ns, peak, steps, warmup, device,
+                     sample_format=0, check_attr=False, nolog=False, note=None):
+    import numpy as np
+    import torch
+    from oracle import pyoracle as po
+    image_bytes = int(sum(len(s) for s in streams))
+    ncpu = len(streams)
+    ctx = hbtgpu.Context(n_events=n_events, max_cpus=ncpu, n_buckets=n_buckets, t0=T_START,
+                         bucket_ns=bucket_ns, arena_bytes=image_bytes + 256 * ncpu + (1 << 20),
+                         metrics=[(hbtgpu.METRIC_RATE, [0, 1])] if n_events >= 2 else (),
+                         device=device, sample_format=sample_format)
+    entry = {"name": name, "image_bytes": image_bytes, "n_cpus": ncpu, "n_events": n_events,
+             "bucket_ns": bucket_ns}
+    if note:
+        entry["note"] = note
+    try:
+        carry = hbtgpu.make_carry(valid=True, tstamp=T_START, last=[0] * n_events)
+        for cpu in range(ncpu):
+            ctx.set_carry(cpu, carry)
+        ctx.submit_images(list(range(ncpu)), streams)
+        ext = torch.cuda.ExternalStream(ctx.stream(), device=device)
+        for _ in range(warmup):
+            ctx.run()
+        ctx.sync()
+        st0 = ctx.stats()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(ext)
+        for _ in range(steps):
+            ctx.run()
+        ev1.record(ext)
+        ctx.sync()
+        st1 = ctx.stats()
+        ms = ev0.elapsed_time(ev1) / steps
+        kms = (st1["decode_ms_sum"] - st0["decode_ms_sum"]) / max(1, st1["decode_runs"] - st0["decode_runs"])
+        nrec = sum(ctx.counters(c)["num_records"] for c in range(ncpu))
+        entry.update({
+            "records": nrec, "ms_per_step": ms, "kernel_ms": kms, "exact_runs": st1["exact_runs"],
+            "records_per_s": nrec / (ms * 1e-3),
+            "frac": (image_bytes / 1e9) / (kms * 1e-3) / peak if kms > 0 else None,
+            "step_frac": (image_bytes / 1e9) / (ms * 1e-3) / peak,
+            "l2": ("flushed by the step itself: images + result tensors exceed L2" if image_bytes > (200 << 20)
+                   else "NOT flushed: the 4 MiB ring stays L2-resident between steps (latency-bound case)"),
+        })
+        # ---- parity: every cpu against the C restatement on all cores
+        port = po.load("port")
+        p = po.make_params(n_events, n_buckets=n_buckets, t0=T_START, bucket_ns=bucket_ns)
+        p.pre = 2 if sample_format else 0
+        carries = [po.make_carry(valid=True, tstamp=T_START, last=[0] * n_events) for _ in streams]
+        cores = os.cpu_count() or 1
+        secs, acc, ctrs = port.run_capture(p, streams, carries, n_threads=min(cores, ncpu))
+        b = ctx.buckets(want_metric=False, want_valid=False)
+        ok = bool(np.array_equal(b["acc"], acc)) and all(ctx.counters(c) == ctrs[c] for c in range(ncpu))
+        for cpu in range(0, ncpu, max(1, ncpu // 4)):
+            ok = ok and bool(np.array_equal(b["scaled"][cpu], port.scale_buckets(p, acc[cpu])))
+        if check_attr:
+            hist = ctx.tid_histogram()
+            top = ctx.top_ips(100)
+            tids, ips = [], []
+            for s, cin in zip(streams, carries):
+                a, c2 = port.collect_ip_tid(p, s, cin)
+                tids.append(a)
+                ips.append(c2)
+            tids, ips = np.concatenate(tids), np.concatenate(ips)
+            tk, tc = np.unique(tids, return_counts=True)
+            ok = ok and hist == {(int(k & 0xFFFFFFFF), int(k >> 32)): int(c) for k, c in zip(tk, tc)}
+            ik, ic = np.unique(ips, return_counts=True)
+            order = np.lexsort((ik, -ic.astype(np.int64)))[:100]
+            ok = ok and top == [(int(ik[i]), int(ic[i])) for i in order]
+            entry["parity_note"] = "spec extension: checker = C restatement's walk + numpy counting (parity unpinned)"
+        entry["parity"] = ok
+        entry["cpu_port"] = {"records_per_s": nrec / secs, "cores": min(cores, ncpu), "kind": "port"}
+        if po.available("reference") and not sample_format:
+            t, n2, _ = cpu_reference_run(streams, T_START, min(cores, ncpu), 1, "reference", n_events, n_buckets,
+                                         bucket_ns)
+            entry["cpu_reference"] = {"records_per_s": n2 / t[0], "cores": min(cores, ncpu), "kind": "reference",
+                                      "variant": "as shipped (hbt logs every LOST / THROTTLE record; stderr to /dev/null)"}
+            if nolog:
+                o = nolog_oracle()
+                if o is not None:
+                    secs2, _, c3 = o.run_capture(p, streams, carries, n_threads=min(cores, ncpu), batch=4096)
+                    entry["cpu_reference_nolog"] = {
+                        "records_per_s": sum(c["num_records"] for c in c3) / secs2, "cores": min(cores, ncpu),
+                        "kind": "reference", "variant": "HBT_LOG_WARNING / HBT_LOG_ERROR compiled out"}
+    finally:
+        ctx.close()
+    return entry
+
+
+def run_configs(hbtgpu, peak, device, quick):
+    """cfg1 (+ forged), cfg3, cfg4 shape, one cfg5 window set."""
+    from dynolog_b200 import synth
+    out = []
+    steps, warmup = (5, 3) if quick else (10, 3)
+    for forge in (0, 10_000):
+        spec, streams = synth.capture(1, 1, max_bytes_per_cpu=4 << 20, forge_ppm=forge)
+        out.append(run_config_entry("cfg1: 1 CPU, 4 MiB ring, 4-event group" + (", 1 % of the counter values forged to look like headers" if forge else ""),
+                                    hbtgpu, streams, 4, 6000, 1_000_000, peak, steps * 4, warmup, device))
+        del streams
+    per_cpu = (16 << 20) if quick else (64 << 20)
+    spec, streams = synth.capture(3, 64, max_bytes_per_cpu=per_cpu)
+    out.append(run_config_entry(f"cfg3: 64 CPUs x {per_cpu >> 20} MiB, 8-event group, multiplexed, LOST + THROTTLE interleaved",
+                                hbtgpu, streams, 8, (per_cpu // 104) // 10 + 4000, 1_000_000, peak, steps, warmup, device,
+                                nolog=True))
+    del streams
+    per_cpu = (4 << 20) if quick else (11 << 20)
+    spec, streams = synth.capture(4, N_CPUS, max_bytes_per_cpu=per_cpu)
+    out.append(run_config_entry(f"cfg4 shape: {N_CPUS} CPUs x {per_cpu >> 20} MiB of 88 B IP|TID|TIME|READ samples, (pid,tid) histogram + top-100 IPs",
+                                hbtgpu, streams, 4, (per_cpu // 88) // 10 + 2000, 1_000_000, peak, steps, warmup, device,
+                                sample_format=1, check_attr=True,
+                                note="1 B records = 88 GB stream through the same context in chunks (accumulate mode), see profiles/"))
+    del streams
+    per_cpu = (4 << 20) if quick else (16 << 20)
+    spec, streams = synth.capture(5, N_CPUS, max_bytes_per_cpu=per_cpu)
+    out.append(run_config_entry(f"cfg5: one window set, {N_CPUS} CPUs x {per_cpu >> 20} MiB, 8-event group, LOST interleaved, 1 ms buckets",
+                                hbtgpu, streams, 8, (per_cpu // 104) // 10 + 2000, 1_000_000, peak, steps, warmup, device))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# the strong-scaled capture
+
+def run_strong(args, hbtgpu, torch, dist, rank, world, local_rank, peak, attach):
+    import numpy as np
+    from dynolog_b200 import synth
+    W = args.strong_windows
+    # host memory: this rank keeps its windows in pinned memory for the end-to-end leg
+    note = None
+    ranks_here = world
+    while W > world and (W // world) * N_CPUS * STRONG_WINDOW_BYTES * ranks_here * 1.2 + (16 << 30) > mem_available_bytes():
+        W //= 2
+        note = f"reduced to {W} windows: the host has {mem_available_bytes() >> 30} GiB available"
+    W = max(W - W % world, world)
+    w_lo, w_hi = rank * W // world, (rank + 1) * W // world
+    cores = os.cpu_count() or 1
+    cap = synth.Capture(synth.make_spec(5), N_CPUS, n_threads=max(2, cores // world))
+    t_gen = time.perf_counter()
+    for w in range(w_lo):
+        cap.window(max_bytes_per_cpu=STRONG_WINDOW_BYTES, dry=True)
+    hosts, windows = [], []
+    for w in range(w_lo, w_hi):
+        h = host_buffer(N_CPUS * STRONG_WINDOW_BYTES)
+        hosts.append(h)
+        windows.append(cap.window(max_bytes_per_cpu=STRONG_WINDOW_BYTES, out=h.numpy()))
+    t_gen = time.perf_counter() - t_gen
+    shard_bytes = int(sum(len(s) for w in windows for s in w))
+    n_buckets = int(W * STRONG_WINDOW_SPAN_NS // STRONG_BUCKET_NS) + 16
+    metrics = [(hbtgpu.METRIC_RATE, [0, 1]), (hbtgpu.METRIC_RATE, [2, 0])]
+    ctx = hbtgpu.Context(n_events=N_EVENTS, max_cpus=N_CPUS, n_buckets=n_buckets, t0=T_START,
+                         bucket_ns=STRONG_BUCKET_NS, arena_bytes=shard_bytes + 256 * N_CPUS * len(windows) + (1 << 20),
+                         metrics=metrics, device=local_rank, flags=hbtgpu.F_EXTERNAL_CARRY if world > 1 else 0)
+    initial = hbtgpu.make_carry(valid=True, tstamp=T_START, last=[0] * N_EVENTS)
+    for cpu in range(N_CPUS):
+        ctx.set_carry(cpu, initial)
+    exchange = "none (one GPU)"
+    if world > 1:
+        exchange = attach(ctx)
+    ext = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    if world > 1 and exchange != "peer":
+        sb = ctx.stub_bytes()
+        send = torch.empty(sb, dtype=torch.uint8, device="cuda")
+        recv = torch.empty(world * sb, dtype=torch.uint8, device="cuda")
+    cpus_all = list(range(N_CPUS))
+
+    def submit_all():
+        for w in windows:
+            ctx.submit_images(cpus_all, w)
+
+    def step():
+        ctx.run()
+        if world > 1:
+            if exchange == "peer":
+                ctx.exchange_boundaries(no_derive=True)
+                ctx.merge()
+            else:  # fallback when peer memory cannot be attached: NCCL all-gather of the stubs
+                with torch.cuda.stream(ext):
+                    ctx.export_stubs_device(send.data_ptr())
+                    dist.all_gather_into_tensor(recv, send)
+                    ctx.apply_boundaries_gathered(recv.data_ptr(), world, rank)
+
+    submit_all()
+    for _ in range(max(3, args.warmup)):
+        step()
+    ctx.sync()
+    st0 = ctx.stats()
+    n_records = sum(ctx.counters(c)["num_records"] for c in range(N_CPUS))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    steps = max(3, min(args.steps, 10))
+    barrier()
+    ev0.record(ext)
+    for _ in range(steps):
+        step()
+    ev1.record(ext)
+    ctx.sync()
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    st1 = ctx.stats()
+    dec_ms = (st1["decode_ms_sum"] - st0["decode_ms_sum"]) / max(1, st1["decode_runs"] - st0["decode_runs"])
+
+    # ---- end to end: this rank's windows from pinned host memory, the totals back to rank 0's host
+    n_cells = N_CPUS * n_buckets
+    out_scaled = torch.empty((n_cells, N_EVENTS), dtype=torch.int64, pin_memory=True)
+    out_metric = torch.empty((n_cells, len(metrics)), dtype=torch.float64, pin_memory=True)
+    out_valid = torch.empty((n_cells,), dtype=torch.int32, pin_memory=True)
+    d2h = (out_scaled.numel() * 8 + out_metric.numel() * 8 + out_valid.numel() * 4) if rank == 0 else 0
+
+    def e2e_step():
+        ctx.reset(keep_carry=False)
+        submit_all()
+        step()
+        if rank == 0:
+            ctx._ck(ctx.L.hbtgpu_get_buckets_host_async(ctx.h, C.c_void_p(0), C.c_void_p(out_scaled.data_ptr()),
+                                                        C.c_void_p(out_metric.data_ptr()),
+                                                        C.c_void_p(out_valid.data_ptr())))
+    e2e_steps = 2
+    e2e_step()
+    ctx.sync()
+    barrier()
+    t_a = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    ctx.sync()
+    barrier()
+    e2e_ms = 1e3 * (time.perf_counter() - t_a) / e2e_steps
+
+    # ---- parity on every rank
+    ctx.run()
+    if world > 1 and exchange == "peer":
+        ctx.exchange_boundaries(no_derive=True)
+    elif world > 1:
+        with torch.cuda.stream(ext):
+            ctx.export_stubs_device(send.data_ptr())
+            dist.all_gather_into_tensor(recv, send)
+            ctx.apply_boundaries_gathered(recv.data_ptr(), world, rank)
+    check = [0, 23, 47, 71, 95, 119, 143, 191] if not args.quick else [0, 191]
+    shard_streams = {c: np.concatenate([w[c] for w in windows]) for c in check}
+    ok, detail = shard_parity(ctx, shard_streams, check, N_EVENTS, n_buckets, T_START, STRONG_BUCKET_NS, world, rank,
+                              initial, dist, merged_expected=(exchange == "peer"))
+    ok = all_ranks_ok(ok, world, dist)
+
+    t = torch.tensor([ms_total, e2e_ms, dec_ms], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([float(n_records), float(shard_bytes)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms_total, e2e_ms, dec_ms = [float(x) for x in t.tolist()]
+    all_records, all_bytes = [float(x) for x in tot.tolist()]
+    ms_step = ms_total / steps
+    acc_bytes = N_CPUS * n_buckets * (N_EVENTS + 3) * 8
+    res = {
+        "workload": (f"cfg5 (BASELINE.json configs[4]): one capture of {W} time windows x {N_CPUS} CPUs x 16 MiB, "
+                     "8-event group, LOST interleaved, sharded by window range over the GPUs; boundary rows, merge of "
+                     "the bucket sums of all ranks and the derive step on the totals inside the timed region"),
+        "scaling": "strong", "n_gpus": world, "steps": steps, "value": all_records / (ms_step * 1e-3), "unit": UNIT,
+        "ms_per_step": ms_step, "records": all_records, "capture_bytes": all_bytes,
+        "bucket_ns": STRONG_BUCKET_NS, "n_buckets": n_buckets, "windows": W, "windows_per_rank": w_hi - w_lo,
+        "kernel_ms": dec_ms, "kernel_frac": (shard_bytes / 1e9) / (dec_ms * 1e-3) / peak if dec_ms > 0 else None,
+        "step_gbs": (all_bytes / 1e9) / (ms_step * 1e-3),
+        "step_frac_of_n_peaks": (all_bytes / 1e9) / (ms_step * 1e-3) / (peak * world),
+        "exchange": exchange,
+        "merge_nvlink_bytes_per_rank": int(acc_bytes * (world - 1) / world) if world > 1 else 0,
+        "stub_bytes_per_rank": ctx.stub_bytes() if world > 1 else 0,
+        "e2e": {"value": all_records / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                "h2d_bytes_per_step": int(all_bytes), "d2h_bytes_per_step": d2h,
+                "h2d_gbs_aggregate": (all_bytes / 1e9) / (e2e_ms * 1e-3)},
+        "parity_checked": ok, "parity": detail, "exact_runs": st1["exact_runs"],
+        "gen_seconds": t_gen,
+    }
+    if note:
+        res["note"] = note
+    ctx.close()
+    del hosts, windows
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -195,6 +614,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaled cfg5 leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the other single-GPU configurations")
+    ap.add_argument("--strong-windows", type=int, default=STRONG_WINDOWS)
+    ap.add_argument("--quick", action="store_true", help="small variants of the extra legs (development)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -216,28 +639,54 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    cores = os.cpu_count() or 1
+    peak, peak_src = measured_peaks()
 
-    streams, keep, t_win = gen_capture(rank)
+    def attach(ctx):
+        """Every rank exports its handle, the handles go round with one all_gather, every rank
+        attaches.  Returns "peer", or the reason for falling back to NCCL."""
+        try:
+            mine = ctx.peer_export(world)
+            handles = [None] * world
+            dist.all_gather_object(handles, mine)
+            ctx.peer_attach(world, rank, handles)
+            ok = True
+        except Exception as e:  # e.g. a container that forbids CUDA IPC
+            ok = False
+            err = str(e)
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        if int(t.item()):
+            return "peer"
+        if ok:
+            ctx.peer_detach()
+        return "nccl (peer memory unavailable" + ("" if ok else ": " + err[:80]) + ")"
+
+    # =========================== headline: cfg2 per GPU, weak scaling ===========================
+    streams, keep = gen_capture(rank, n_threads=max(2, cores // world))
     image_bytes = int(sum(len(s) for s in streams))
-    t0 = 1_000_000_000 + rank * SAMPLES_PER_CPU * 100_000
+    t0 = T_START + rank * SAMPLES_PER_CPU * 100_000
     metrics = [(hbtgpu.METRIC_RATE, [0, 1]),  # IPC = instructions / cycles (BuiltinMetrics.cpp:616-666)
                (hbtgpu.METRIC_RATE, [2, 0])]  # LLC misses per instruction (BuiltinMetrics.cpp:792-818)
     # N > 1: time-window shards; every rank decodes from an invalid state and the rows that
-    # straddle shard boundaries are added after a small all_gather of per-cpu stubs
+    # straddle shard boundaries are added after the exchange of per-cpu stubs
     ctx = hbtgpu.Context(n_events=N_EVENTS, max_cpus=N_CPUS, n_buckets=N_BUCKETS, t0=t0,
                          bucket_ns=BUCKET_NS, arena_bytes=image_bytes + (1 << 20), metrics=metrics,
                          device=local_rank, flags=hbtgpu.F_EXTERNAL_CARRY if world > 1 else 0)
-    carry = hbtgpu.make_carry(valid=True, tstamp=1_000_000_000, last=[0] * N_EVENTS)
+    carry = hbtgpu.make_carry(valid=True, tstamp=T_START, last=[0] * N_EVENTS)
     for cpu in range(N_CPUS):
         ctx.set_carry(cpu, carry)
     ext = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
+    exchange = "none (one GPU)"
+    if world > 1:
+        exchange = attach(ctx)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    if world > 1:
+    if world > 1 and exchange != "peer":
         sb = ctx.stub_bytes()
         send = torch.empty(sb, dtype=torch.uint8, device="cuda")
         recv = torch.empty(world * sb, dtype=torch.uint8, device="cuda")
@@ -246,14 +695,16 @@ def main():
         """One pass of the hot path over this rank's resident shard (+ the boundary exchange)."""
         ctx.run()
         if world > 1:
-            with torch.cuda.stream(ext):
-                ctx.export_stubs_device(send.data_ptr())
-                dist.all_gather_into_tensor(recv, send)  # NCCL, ordered on the context stream
-                ctx.apply_boundaries_gathered(recv.data_ptr(), world, rank)
+            if exchange == "peer":
+                ctx.exchange_boundaries()
+            else:
+                with torch.cuda.stream(ext):
+                    ctx.export_stubs_device(send.data_ptr())
+                    dist.all_gather_into_tensor(recv, send)  # NCCL, ordered on the context stream
+                    ctx.apply_boundaries_gathered(recv.data_ptr(), world, rank)
 
     # ---- resident leg: images already in HBM --------------------------------------------
-    for cpu, s in enumerate(streams):
-        ctx.submit_image(cpu, s)
+    ctx.submit_images(list(range(N_CPUS)), streams)
     for _ in range(args.warmup):
         gpu_step()
     ctx.sync()
@@ -277,14 +728,12 @@ def main():
     dec_runs = st1["decode_runs"] - st0["decode_runs"]
     dec_ms = (st1["decode_ms_sum"] - st0["decode_ms_sum"]) / max(1, dec_runs)
     launches_per_step = st1["kernel_launches"]
-    exact_runs = st1["exact_runs"]
 
     # ---- end-to-end leg: host buffers in, host results out ---------------------------------
     # two sets of pinned result buffers: step k+1 must not overwrite what step k is still copying
     out_scaled = [torch.empty((N_CPUS, N_BUCKETS, N_EVENTS), dtype=torch.int64, pin_memory=True) for _ in range(2)]
     out_metric = [torch.empty((N_CPUS, N_BUCKETS, len(metrics)), dtype=torch.float64, pin_memory=True) for _ in range(2)]
     out_valid = [torch.empty((N_CPUS, N_BUCKETS), dtype=torch.int32, pin_memory=True) for _ in range(2)]
-    import ctypes as C
 
     def e2e_step():
         ctx.reset(keep_carry=False)
@@ -311,6 +760,13 @@ def main():
     e2e_ms = max(eva.elapsed_time(evb) / args.e2e_steps, e2e_wall_ms)
     d2h = out_scaled[0].numel() * 8 + out_metric[0].numel() * 8 + out_valid[0].numel() * 4
 
+    # ---- parity on every rank (a slice of the cpus; tests/ check all of them) ---------------
+    gpu_step()
+    check = [0, 63, 127, 191]
+    ok, pdetail = shard_parity(ctx, {c: streams[c] for c in check}, check, N_EVENTS, N_BUCKETS, t0, BUCKET_NS,
+                               world, rank, carry, dist)
+    parity_ok = all_ranks_ok(ok, world, dist)
+
     # ---- max over ranks, whole-job aggregate ---------------------------------------------------
     t = torch.tensor([ms_total, e2e_ms, dec_ms], dtype=torch.float64, device="cuda")
     tot = torch.tensor([float(n_records), float(image_bytes)], dtype=torch.float64, device="cuda")
@@ -323,8 +779,8 @@ def main():
 
     line = None
     if rank == 0:
-        peak, peak_src = measured_peaks()
         achieved = (image_bytes / 1e9) / (dec_ms * 1e-3)  # per GPU: algorithmic bytes / kernel time
+        traffic, traffic_src = ncu_traffic()
         line = {
             "metric": METRIC, "value": all_records / (ms_step * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
@@ -333,22 +789,24 @@ def main():
             "config": {"workload": WORKLOAD, "n_cpus": N_CPUS, "n_events": N_EVENTS,
                        "bucket_ns": BUCKET_NS, "image_bytes_per_gpu": image_bytes,
                        "l2": "inputs (2.0 GB) larger than L2 (126 MB); no flush needed",
-                       "step_gbs": (all_bytes / 1e9) / (ms_step * 1e-3)},
+                       "step_gbs": (all_bytes / 1e9) / (ms_step * 1e-3),
+                       "step_frac": (image_bytes / 1e9) / (ms_step * 1e-3) / peak,
+                       "exchange": exchange},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
-                         "traffic_source": "profiles/r01_traffic.json (ncu --set full, dram read+write per launch)",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "traffic_source": f"{traffic_src} (ncu --set full, dram read+write per launch)",
                          "kernel": "k_decode<spec,agg>", "kernel_ms": dec_ms,
                          "algorithmic_bytes_per_launch": image_bytes,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "e2e": {"value": all_records / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": image_bytes, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms},
+                    "ms_per_step": e2e_ms, "h2d_gbs_aggregate": (all_bytes / 1e9) / (e2e_ms * 1e-3)},
             "gpu_launches": int(launches_per_step * args.steps),
             "clocks": clocks,
+            "parity_checked": parity_ok, "parity": pdetail, "exact_runs": st1["exact_runs"],
         }
         if not args.no_cpu_baseline and world == 1:
             lib_kind, kind = pick_cpu_kind()
-            cores = os.cpu_count() or 1
             n_threads = min(cores, N_CPUS)
             times, nrec, desc = cpu_reference_run(streams, t0, n_threads, 3, lib_kind)
             best = min(times)
@@ -358,9 +816,26 @@ def main():
                 "sample": f"the full capture ({nrec} records), best of 3 passes, {n_threads} threads "
                           f"by CPU partition; {desc}; single-thread: {n1 / t1[0]:.3e} records/s on 8 streams",
                 "single_thread_value": n1 / t1[0]}
-        print(json.dumps(line), flush=True)
     ctx.close()
+    del streams, keep, out_scaled, out_metric, out_valid
+
+    # =========================== the other legs ==================================================
+    if not args.no_strong:
+        try:
+            strong = run_strong(args, hbtgpu, torch, dist, rank, world, local_rank, peak, attach)
+        except Exception as e:  # the headline line must still come out
+            strong = {"error": f"{type(e).__name__}: {e}"[:300]}
+        if rank == 0:
+            line["strong"] = strong
+    if rank == 0 and world == 1 and not args.no_configs:
+        try:
+            line["configs"] = run_configs(hbtgpu, peak, local_rank, args.quick)
+        except Exception as e:
+            line["configs"] = [{"error": f"{type(e).__name__}: {e}"[:300]}]
+    if rank == 0:
+        print(json.dumps(line), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

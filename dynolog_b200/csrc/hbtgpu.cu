@@ -1116,6 +1116,17 @@ int hbtgpu_apply_boundaries_gathered(hbtgpu_ctx* ctx, const void* device_gathere
   return derive_after_boundaries(ctx);
 }
 
+int hbtgpu_get_prev_tail(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_carry* out) {
+  if (!ctx || !out) return -EINVAL;
+  if (cpu >= ctx->cfg.max_cpus) return fail(ctx, -EINVAL, "cpu %u out of range", cpu);
+  if (!(ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY))
+    return fail(ctx, -EINVAL, "context was not created with HBTGPU_F_EXTERNAL_CARRY");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaMemcpyAsync(out, &ctx->d_carry_in[cpu], sizeof(hbtgpu_carry), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
 int hbtgpu_acc_device(hbtgpu_ctx* ctx, void** device_ptr, size_t* bytes) {
   if (!ctx || !device_ptr || !bytes) return -EINVAL;
   *device_ptr = ctx->d_acc;

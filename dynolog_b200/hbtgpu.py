@@ -94,7 +94,7 @@ ABI_SYMBOLS = [
     "hbtgpu_get_stubs", "hbtgpu_compose_tail", "hbtgpu_apply_boundaries", "hbtgpu_stub_bytes",
     "hbtgpu_export_stubs_device", "hbtgpu_apply_boundaries_gathered", "hbtgpu_acc_device", "hbtgpu_stream",
     "hbtgpu_peer_export", "hbtgpu_peer_attach", "hbtgpu_peer_attach_local", "hbtgpu_peer_detach",
-    "hbtgpu_exchange_boundaries", "hbtgpu_merge",
+    "hbtgpu_exchange_boundaries", "hbtgpu_merge", "hbtgpu_get_prev_tail",
     "hbtgpu_math_get_count", "hbtgpu_math_rate", "hbtgpu_math_add_reduce",
     "hbtgpu_math_tsc_to_ktime", "hbtgpu_math_ktime_to_tsc", "hbtgpu_math_per_second_mega",
     "hbtgpu_math_running_ratio", "hbtgpu_get_stats", "hbtgpu_version",
@@ -405,8 +405,14 @@ class Context:
     def peer_detach(self):
         self._ck(self.L.hbtgpu_peer_detach(self.h))
 
-    def exchange_boundaries(self):
-        self._ck(self.L.hbtgpu_exchange_boundaries(self.h))
+    def exchange_boundaries(self, no_derive=False):
+        self._ck(self.L.hbtgpu_exchange_boundaries(self.h, C.c_uint32(1 if no_derive else 0)))
+
+    def prev_tail(self, cpu):
+        """Shard mode: the state in front of this rank's shard (after the boundaries were applied)."""
+        c = Carry()
+        self._ck(self.L.hbtgpu_get_prev_tail(self.h, C.c_uint32(cpu), C.byref(c)))
+        return c
 
     def merge(self):
         self._ck(self.L.hbtgpu_merge(self.h))

@@ -80,10 +80,11 @@ class Capture:
         self.state_size = int(self.L.hbtsynth_state_size())
         self.states = np.zeros(n_cpus * self.state_size, np.uint8)
 
-    def window(self, n_samples=None, max_bytes_per_cpu=None, out=None):
+    def window(self, n_samples=None, max_bytes_per_cpu=None, out=None, dry=False):
         """Next window: up to n_samples samples (or max_bytes_per_cpu bytes) per CPU.
         `out`: optional uint8 array of n_cpus*cap bytes (e.g. a view of pinned memory).
-        Returns list of per-CPU uint8 views."""
+        Returns list of per-CPU uint8 views.  dry=True: nothing is written, the generator only
+        moves past the window (how a rank skips to its own time windows); returns the lengths."""
         n = self.spec.n_events
         rec = 40 + 8 * n + (16 if self.spec.sample_format == 1 else 0)
         if n_samples is None:
@@ -95,10 +96,16 @@ class Capture:
             if max_bytes_per_cpu is not None:
                 cap = min(cap, int(max_bytes_per_cpu))
         cap = (cap + 127) // 128 * 128
+        lens = np.zeros(self.n_cpus, np.uint64)
+        if dry:
+            self.L.hbtsynth_window(C.byref(self.spec), C.c_void_p(self.states.ctypes.data),
+                                   C.c_uint32(self.first_cpu), C.c_uint32(self.n_cpus),
+                                   C.c_uint64(n_samples), C.c_void_p(0), C.c_uint64(cap),
+                                   C.c_void_p(lens.ctypes.data), C.c_uint32(self.n_threads))
+            return [int(x) for x in lens]
         if out is None:
             out = np.empty(self.n_cpus * cap, np.uint8)
         assert out.size >= self.n_cpus * cap
-        lens = np.zeros(self.n_cpus, np.uint64)
         self.L.hbtsynth_window(C.byref(self.spec), C.c_void_p(self.states.ctypes.data),
                                C.c_uint32(self.first_cpu), C.c_uint32(self.n_cpus),
                                C.c_uint64(n_samples), C.c_void_p(out.ctypes.data), C.c_uint64(cap),

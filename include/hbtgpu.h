@@ -323,9 +323,13 @@ int hbtgpu_peer_attach(hbtgpu_ctx* ctx, uint32_t world, uint32_t rank, const voi
 /* the same for contexts that live in this process (peers[rank] is ignored) */
 int hbtgpu_peer_attach_local(hbtgpu_ctx* ctx, uint32_t world, uint32_t rank, hbtgpu_ctx* const* peers);
 int hbtgpu_peer_detach(hbtgpu_ctx* ctx);
-int hbtgpu_exchange_boundaries(hbtgpu_ctx* ctx);
+#define HBTGPU_EXCHANGE_NO_DERIVE 0x1u /* hbtgpu_merge follows and derives from the totals */
+int hbtgpu_exchange_boundaries(hbtgpu_ctx* ctx, uint32_t flags);
 int hbtgpu_merge(hbtgpu_ctx* ctx);
 
+/* Shard mode, after the boundaries were applied (any of the three ways): the generator state in
+ * front of this rank's shard, as the fold over the earlier ranks found it. */
+int hbtgpu_get_prev_tail(hbtgpu_ctx* ctx, uint32_t cpu, hbtgpu_carry* out);
 /* Device address/size of the acc tensor, for a collective (NCCL all-reduce over u64 as i64). */
 int hbtgpu_acc_device(hbtgpu_ctx* ctx, void** device_ptr, size_t* bytes);
 /* The CUDA stream the context launches on (a cudaStream_t). */

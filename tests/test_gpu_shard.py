@@ -164,7 +164,7 @@ def _run_peer_world(shards, init, nb, n=N, flags=0, metrics=(), merge=True, buck
             for g in ctxs:
                 g.run()
             for g in ctxs:  # nothing below blocks the host: the waits of one rank are met by the others
-                g.exchange_boundaries()
+                g.exchange_boundaries(no_derive=merge)
             if merge:
                 for g in ctxs:
                     g.merge()
