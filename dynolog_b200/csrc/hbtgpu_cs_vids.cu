@@ -460,10 +460,12 @@ int hbtgpu_cs_assign_vids_device(hbtgpu_cs_ctx* ctx, hbtgpu_cs_vids* v) {
     b.take<uint8_t>(std::max(tmp_sort, tmp_scan));
     need1 = b.off + 256;
   }
-  if (need1 > v->cap_scratch) {
-    if (v->scratch) VK(cudaFree(v->scratch));
-    v->scratch = nullptr;
-    VK(cudaMalloc(&v->scratch, need1));
+  if (need1 > v->cap_scratch || !v->scratch) {
+    // allocate first, then swap: a failed cudaMalloc leaves the old buffer and its capacity intact
+    void* fresh = nullptr;
+    VK(cudaMalloc(&fresh, need1));
+    if (v->scratch) cudaFree(v->scratch);
+    v->scratch = fresh;
     v->cap_scratch = need1;
   }
   Bump b{static_cast<uint8_t*>(v->scratch)};

@@ -2170,12 +2170,10 @@ __global__ void __launch_bounds__(256) k_pack_stubs(const Params P, uint64_t* ds
 // Shards behind a stall contribute nothing.  Outputs for `rank`: the state in front of its shard
 // and dead[cpu] (1: an earlier shard stalled); for every rank r: the bucket range its rows can
 // have touched (ranges[r * n_streams + cpu] = lo | hi << 32, lo > hi: none), if ranges != null.
-__global__ void k_fold(const Params P, const uint64_t* gathered, uint32_t world, uint32_t rank,
-                       const hbtgpu_carry* init, hbtgpu_carry* prev_out, uint32_t* dead_out,
-                       uint64_t* ranges) {
-  const uint32_t cpu = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void fold_cpu(const Params& P, uint32_t cpu, const uint64_t* gathered, uint32_t world,
+                                         uint32_t rank, const hbtgpu_carry* init, hbtgpu_carry* prev_out,
+                                         uint32_t* dead_out, uint64_t* ranges) {
   const uint32_t ns = P.n_streams;
-  if (cpu >= ns) return;
   const uint32_t n = P.n_events, sw = stub_words(n);
   // the state is (valid, tstamp) plus a pointer to where te / tr / last[] come from
   bool valid = init[cpu].valid != 0;
@@ -2242,13 +2240,21 @@ __global__ void k_fold(const Params P, const uint64_t* gathered, uint32_t world,
   }
 }
 
+__global__ void k_fold(const Params P, const uint64_t* gathered, uint32_t world, uint32_t rank,
+                       const hbtgpu_carry* init, hbtgpu_carry* prev_out, uint32_t* dead_out,
+                       uint64_t* ranges) {
+  const uint32_t cpu = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cpu < P.n_streams) fold_cpu(P, cpu, gathered, world, rank, init, prev_out, dead_out, ranges);
+}
+
 // One block per stream: add the row that straddles the shard boundary -- or, where the walk of
 // this cpu stalled before or at this shard's first SAMPLE, take the shard's contribution out.
 // dead: per cpu, 1 if an earlier shard stalled (null: none did).
-__global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_carry* prev_tails,
-                                                  const uint32_t* dead, uint64_t* touched_cell) {
-  const uint32_t sidx = blockIdx.x;
-  if (threadIdx.x == 0) touched_cell[sidx] = ~0ull;  // which (cpu, bucket) cell got the boundary row
+// tid / nthr: the calling thread's index among the nthr threads that work on this stream together
+__device__ __forceinline__ void boundary_cpu(const Params& P, uint32_t sidx, const hbtgpu_carry* prev_tails,
+                                             const uint32_t* dead, uint64_t* touched_cell, uint32_t tid,
+                                             uint32_t nthr) {
+  if (tid == 0) touched_cell[sidx] = ~0ull;  // which (cpu, bucket) cell got the boundary row
   const hbtgpu_head_stub& hs = P.head[sidx];
   const hbtgpu_carry& pt = prev_tails[sidx];
   uint64_t* ctr = P.counters + static_cast<uint64_t>(sidx) * C_SLOTS;
@@ -2258,13 +2264,14 @@ __global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_c
   // handleRecordSample emits a row iff the state is valid when the SAMPLE arrives (:135,165-182)
   const bool reached = !(ctr[C_ERR] != 0 && ctr[C_ERR_OFF] <= hs.offset);  // the shard's own walk got to that SAMPLE
   const bool regress = !is_dead && row && reached && pt.tstamp > hs.tstamp;  // (:156-163)
+  if (nthr > 1) __syncthreads();  // every thread has read the counters before thread 0 rewrites them
   if (is_dead || regress) {
     // consume() never gets past the stall: of this shard only the records in front of its first
     // SAMPLE (regress) or nothing at all (dead) were walked
     uint64_t* acc = P.acc + static_cast<uint64_t>(sidx) * P.n_buckets * (n + 3);
     const uint64_t words = static_cast<uint64_t>(P.n_buckets) * (n + 3);
-    for (uint64_t i = threadIdx.x; i < words; i += blockDim.x) acc[i] = 0;
-    if (threadIdx.x == 0) {
+    for (uint64_t i = tid; i < words; i += nthr) acc[i] = 0;
+    if (tid == 0) {
       HeadExtra hx{0, 0, 0, 0, 0};
       if (regress && P.head_extra) hx = P.head_extra[sidx];
       ctr[C_LOST] = hx.lost;
@@ -2287,14 +2294,14 @@ __global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_c
       ctr[C_LAST_TS] = co.tstamp;
       touched_cell[sidx] = ~0ull - 1;  // "the whole row changed": derive_after_boundaries re-derives everything
     }
-    for (uint32_t e = threadIdx.x; e < n; e += blockDim.x) P.carry_out[sidx].last[e] = pt.last[e];
+    for (uint32_t e = tid; e < n; e += nthr) P.carry_out[sidx].last[e] = pt.last[e];
     return;
   }
   if (!hs.has_sample) {
     // no SAMPLE in the shard: the state in front of it passes through (a LOST invalidates it)
     hbtgpu_carry& co = P.carry_out[sidx];
-    for (uint32_t e = threadIdx.x; e < n; e += blockDim.x) co.last[e] = pt.last[e];
-    if (threadIdx.x == 0) {
+    for (uint32_t e = tid; e < n; e += nthr) co.last[e] = pt.last[e];
+    if (tid == 0) {
       const bool v = pt.valid && !hs.lost_before;
       co.valid = v;
       co.tstamp = v ? pt.tstamp : ~0ull;
@@ -2306,15 +2313,15 @@ __global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_c
   }
   if (!row || !reached) return;
   const uint32_t bk = bucket_of(P, hs.tstamp);
-  if (threadIdx.x == 0) {
+  if (tid == 0) {
     ctr[C_ROWS] += 1;
     ctr[C_UNKNOWN] -= 1;  // the shard counted its first SAMPLE as a re-base
     if (bk == BKT_OOR) ctr[C_OOR] += 1;
   }
   if (bk == BKT_OOR) return;
-  if (threadIdx.x == 0) touched_cell[sidx] = static_cast<uint64_t>(sidx) * P.n_buckets + bk;
+  if (tid == 0) touched_cell[sidx] = static_cast<uint64_t>(sidx) * P.n_buckets + bk;
   uint64_t* base = P.acc + (static_cast<uint64_t>(sidx) * P.n_buckets + bk) * (n + 3);
-  for (uint32_t e = threadIdx.x; e < n + 3; e += blockDim.x) {
+  for (uint32_t e = tid; e < n + 3; e += nthr) {
     uint64_t v;
     if (e < n) v = hs.value[e] - pt.last[e];
     else if (e == n) v = hs.te - pt.te;
@@ -2322,6 +2329,11 @@ __global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_c
     else v = 1;
     red_add(base + e, v);
   }
+}
+
+__global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_carry* prev_tails,
+                                                  const uint32_t* dead, uint64_t* touched_cell) {
+  boundary_cpu(P, blockIdx.x, prev_tails, dead, touched_cell, threadIdx.x, blockDim.x);
 }
 
 // ------------------------------------------------------------------------------------

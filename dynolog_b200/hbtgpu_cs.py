@@ -21,7 +21,7 @@ assert THREAD_DTYPE.itemsize == 40 and NAME_DTYPE.itemsize == 32
 
 ABI_SYMBOLS = [
     "hbtgpu_cs_create", "hbtgpu_cs_destroy", "hbtgpu_cs_last_error", "hbtgpu_cs_set_state",
-    "hbtgpu_cs_submit_image", "hbtgpu_cs_reset", "hbtgpu_cs_run", "hbtgpu_cs_sync",
+    "hbtgpu_cs_submit_image", "hbtgpu_cs_submit_image_slices", "hbtgpu_cs_reset", "hbtgpu_cs_run", "hbtgpu_cs_sync",
     "hbtgpu_cs_get_counters", "hbtgpu_cs_get_state", "hbtgpu_cs_num_events", "hbtgpu_cs_get_events",
     "hbtgpu_cs_get_ops", "hbtgpu_cs_events_device", "hbtgpu_cs_get_stats",
     "hbtgpu_cs_threads_create", "hbtgpu_cs_threads_destroy", "hbtgpu_cs_assign_vids",

@@ -10,7 +10,8 @@
 //     getNumEntries()               gen :86-89                  same (rows available)
 //   PerCpuCountSampleGenerator    gen :234-347              PerCpuCountSampleGenerator
 //     getCpuGenerator(cpu)          PerCpuBase.h                same
-//     accumUntil(batch, stop_ts)    PerCpuSampleGeneratorBase.h:69-94   same (decodes everything submitted)
+//     accumUntil(batch, stop_ts)    PerCpuSampleGeneratorBase.h:69-94   same (batch and stop_ts honoured record by record)
+//   GroupReadValues               PerfEventsGroup.h:386-586  GroupReadValues (arithmetic through hbtgpu_math_*)
 //   TraceMonitor::applyToCountSamplesAndConsume  mon/TraceMonitor.h:35-108   applyToCountSamples
 //   CpuThreadSwitchGenerator      PerCpuThreadSwitchGenerator.h:168-446   CpuThreadSwitchGenerator
 //     consume / getNumRecord* / getLastTimeStamp / getNumEntries         same names
@@ -36,7 +37,9 @@
 #include <errno.h>
 #include <sys/types.h>
 
+#include <algorithm>
 #include <cstdint>
+#include <cstring>
 #include <deque>
 #include <functional>
 #include <map>
@@ -78,12 +81,16 @@ struct TscConversionParams {  // hbt/src/common/System.h:184-188
 
 class PerCpuCountSampleGenerator;
 
-// Per-CPU view; same accessor names as the reference's generator.
+// Per-CPU view; same accessor names as the reference's generator.  The counters are lifetime
+// counters, as in the reference (PerfEventsGroup.h:887-897): they grow by what consume() walks.
 class CpuCountSampleGenerator {
  public:
-  /// Decode what was submitted for this CPU (all CPUs are decoded together on the GPU).
-  /// Return convention of PerfEventsGroup::consume (:1574-1588): the errno wins whenever
-  /// the ring was drained or a record stalled the walk.
+  /// PerfEventsGroup::consume (:1394-1589): walks up to max_num_records records of what was
+  /// handed over for this CPU.  Same return convention (:1572-1588): the number of records, or
+  /// -ENODATA when the ring drained before max_num_records, or the errno of the record the walk
+  /// stalls on (-EPERM).  The GPU has decoded the whole window by then; this releases its
+  /// results record by record, so rows and counters become visible exactly when the reference
+  /// makes them visible.
   ssize_t consume(unsigned max_num_records);
 
   uint64_t getNumRecordLost() const { return c_.lost; }
@@ -97,8 +104,11 @@ class CpuCountSampleGenerator {
   uint64_t getNumRecordAux() const { return c_.aux; }
   uint64_t getNumRecordItraceStart() const { return c_.itrace_start; }
   uint64_t getNumRecordSwitchCpuWide() const { return c_.switch_cpu_wide; }
-  TimeStamp getLastTimeStamp() const { return c_.last_tstamp; }
-  size_t getNumEntries() const { return c_.num_rows; }
+  uint64_t getNumUnknownCountInterval() const { return c_.num_unknown_count_interval; }
+  /// count_.tstamp (gen :209-211): kInvalidTimeStamp after a LOST or a time regression
+  TimeStamp getLastTimeStamp() const { return tstamp_; }
+  /// rows in the output ring: released by consume(), not yet taken by applyToCountSamples
+  size_t getNumEntries() const { return out_.size(); }
   CpuId getCpu() const { return cpu_; }
 
  private:
@@ -106,7 +116,20 @@ class CpuCountSampleGenerator {
   CpuCountSampleGenerator(PerCpuCountSampleGenerator* owner, CpuId cpu) : owner_{owner}, cpu_{cpu} {}
   PerCpuCountSampleGenerator* owner_;
   CpuId cpu_;
-  hbtgpu_counters c_{};
+  hbtgpu_counters c_{};                 // lifetime
+  TimeStamp tstamp_ = kInvalidTimeStamp;  // generator state behind the last consumed record
+  // the current window: the unconsumed tail of earlier images followed by the new ones
+  std::vector<uint8_t> bytes_;          // host copy (timestamps / values at record offsets)
+  size_t in_arena_ = 0;                 // bytes_[0, in_arena_) were decoded by the last run
+  hbtgpu_carry start_{};                // generator state in front of bytes_[0]
+  std::vector<uint64_t> rec_off_;       // record table of the decoded window
+  std::vector<uint32_t> rec_type_, rec_size_;
+  std::vector<uint64_t> rows_;          // its rows, n + 2 words each
+  size_t rec_cur_ = 0, row_cur_ = 0;    // consumed so far
+  size_t last_sample_ = SIZE_MAX;       // record index of the last consumed SAMPLE of this window
+  int64_t err_ = 0;                     // the window's walk stalls behind the last record of the table
+  uint64_t err_off_ = 0;
+  std::deque<std::vector<uint64_t>> out_;
 };
 
 class PerCpuCountSampleGenerator {
@@ -132,6 +155,7 @@ class PerCpuCountSampleGenerator {
     cfg.n_events = static_cast<uint32_t>(event_names.size());
     for (size_t i = 0; i < opt.tsc_to_kernel_time.size() && i < event_names.size(); ++i)
       if (opt.tsc_to_kernel_time[i]) cfg.tsc_mask |= 1ull << i;
+    tsc_mask_ = cfg.tsc_mask;
     cfg.time_shift = opt.tsc.time_shift;
     cfg.time_mult = opt.tsc.time_mult;
     cfg.time_zero = opt.tsc.time_zero;
@@ -157,57 +181,73 @@ class PerCpuCountSampleGenerator {
 
   /// State enableImpl() leaves (gen :91-106): interval starts at `now`, last_ = 0.
   void enable(CpuId cpu, TimeStamp now) {
-    hbtgpu_carry c{};
-    c.valid = 1;
-    c.tstamp = now;
-    check(hbtgpu_set_carry(ctx_, static_cast<uint32_t>(cpu), &c));
+    auto& g = gens_.at(static_cast<size_t>(cpu));
+    g.start_ = hbtgpu_carry{};
+    g.start_.valid = 1;
+    g.start_.tstamp = now;
+    g.tstamp_ = now;
+    dirty_ = true;
   }
 
-  /// The callback to hand to PerfEventsGroup::onCpuDataBufferRead (:1592-1637).
+  /// The callback to hand to PerfEventsGroup::onCpuDataBufferRead (:1592-1637), consume = true:
+  /// the bytes are copied, the ring may move on.  They join the CPU's stream behind whatever an
+  /// earlier accumUntil left unconsumed.
   void onCpuDataBufferRead(CpuId cpu, const RbDataSlices& s) {
-    check(hbtgpu_submit_image(ctx_, static_cast<uint32_t>(cpu), s.first.from, s.first.size,
-                              s.second ? s.second->from : nullptr, s.second ? s.second->size : 0));
-    decoded_ = false;
+    auto& g = gens_.at(static_cast<size_t>(cpu));
+    const auto* p1 = static_cast<const uint8_t*>(s.first.from);
+    g.bytes_.insert(g.bytes_.end(), p1, p1 + s.first.size);
+    if (s.second) {
+      const auto* p2 = static_cast<const uint8_t*>(s.second->from);
+      g.bytes_.insert(g.bytes_.end(), p2, p2 + s.second->size);
+    }
+    dirty_ = true;
   }
 
   CpuCountSampleGenerator& getCpuGenerator(CpuId cpu) { return gens_.at(static_cast<size_t>(cpu)); }
 
-  /// PerCpuSampleGeneratorBase::accumUntil (:69-94): consume every CPU until drained; returns
-  /// the number of CPUs that finished without an unexpected error; throws on one, as the
-  /// reference does (HBT_THROW_ASSERT_IF, :76-79).
-  unsigned accumUntil(unsigned batch_size, TimeStamp /*stop_ts*/) {
+  /// PerCpuSampleGeneratorBase::accumUntil (:69-94), statement by statement: per CPU, consume
+  /// batches while the generator's last timestamp is <= stop_ts; -ENODATA ends the CPU quietly,
+  /// any other error throws (HBT_THROW_ASSERT_IF, :76-79).  Returns the number of CPUs that
+  /// finished without an error.  (As in the reference, a generator whose state is invalid --
+  /// after a LOST or a time regression -- reports kInvalidTimeStamp and is not consumed.)
+  unsigned accumUntil(unsigned batch_size, TimeStamp stop_ts) {
     if (batch_size == 0) throw std::invalid_argument("batch_size must be > 0");  // HBT_ARG_CHECK_GT
-    unsigned done = 0;
+    unsigned num_done = 0;
     for (auto& g : gens_) {
-      ssize_t ret = g.consume(batch_size);
-      if (ret < 0 && ret != -ENODATA && ret != -EAGAIN)
-        throw std::runtime_error("Unexpected error processing batch: " + std::to_string(ret));
-      ++done;
+      ssize_t ret = 0;
+      while (g.getLastTimeStamp() <= stop_ts) {
+        ret = g.consume(batch_size);
+        if (ret < 0 && ret != -ENODATA && ret != -EAGAIN)
+          throw std::runtime_error("Unexpected error processing batch: " + std::to_string(ret));
+        if (ret == -ENODATA) {
+          ret = 0;
+          break;
+        }
+      }
+      if (ret >= 0) ++num_done;
     }
-    return done;
+    return num_done;
   }
 
   /// TraceMonitor::applyToCountSamplesAndConsume (mon/TraceMonitor.h:35-108):
-  /// func(cpu, count_idx, nicknames, tstamp, duration, counts, n)
+  /// func(cpu, count_idx, nicknames, tstamp, duration, counts, n) for every row in the output
+  /// rings, which are emptied.
   using CountFunc = std::function<void(CpuId, size_t, const std::vector<std::string>&, TimeStamp,
                                        TimeStamp, const uint64_t*, size_t)>;
   void applyToCountSamples(const CountFunc& func) {
-    decode();
     const size_t n = getNumEvents();
-    std::vector<uint64_t> rows;
     for (auto& g : gens_) {
-      size_t have = 0;
-      check(hbtgpu_get_rows(ctx_, static_cast<uint32_t>(g.cpu_), nullptr, 0, &have));
-      rows.resize(have * (n + 2));
-      if (have) check(hbtgpu_get_rows(ctx_, static_cast<uint32_t>(g.cpu_), rows.data(), have, &have));
-      for (size_t i = 0; i < have; ++i) {
-        const uint64_t* r = &rows[i * (n + 2)];
-        func(g.cpu_, i, event_names_, r[0], r[1], r + 2, n);
+      size_t i = 0;
+      while (!g.out_.empty()) {
+        const std::vector<uint64_t>& r = g.out_.front();
+        func(g.cpu_, i++, event_names_, r[0], r[1], r.data() + 2, n);
+        g.out_.pop_front();
       }
     }
   }
 
-  /// Bucketed aggregates (scaled counts, metrics, validity) on the host.
+  /// Bucketed aggregates (scaled counts, metrics, validity) of the window as the GPU decoded it
+  /// (everything handed over and not yet consumed by an earlier window; stop_ts does not apply).
   void getBuckets(std::vector<uint64_t>* acc, std::vector<uint64_t>* scaled, std::vector<double>* metric,
                   std::vector<uint32_t>* valid) {
     decode();
@@ -229,29 +269,228 @@ class PerCpuCountSampleGenerator {
     if (rc == -EINVAL) throw std::invalid_argument(hbtgpu_last_error(ctx_));
     if (rc != 0) throw std::runtime_error(hbtgpu_last_error(ctx_));
   }
+  static uint64_t word(const std::vector<uint8_t>& b, size_t off) {
+    uint64_t v;
+    std::memcpy(&v, b.data() + off, 8);
+    return v;
+  }
+
+  // A new window on the GPU: every CPU's stream restarts at its first unconsumed record, from
+  // the generator state in front of it; the arena holds nothing older (no O(history) re-decode).
   void decode() {
-    if (decoded_) return;
+    if (!dirty_) return;
+    const size_t n = getNumEvents();
+    std::vector<uint64_t> raw_vals, xf_vals;  // values of carried samples that need the TSC transform
+    for (auto& g : gens_) {
+      if (g.rec_cur_ > 0 || g.in_arena_ > 0) {
+        // the carry behind the consumed records: time / validity from the live state, te / tr /
+        // last_[] from the last consumed SAMPLE of the window (else unchanged)
+        if (g.last_sample_ != SIZE_MAX) {
+          const size_t off = static_cast<size_t>(g.rec_off_[g.last_sample_]);
+          g.start_.te = word(g.bytes_, off + 24);
+          g.start_.tr = word(g.bytes_, off + 32);
+          for (size_t e = 0; e < n; ++e) {
+            g.start_.last[e] = word(g.bytes_, off + 40 + 8 * e);
+            if ((tsc_mask_ >> e) & 1) raw_vals.push_back(g.start_.last[e]);
+          }
+        }
+        const size_t cut = g.rec_cur_ < g.rec_off_.size() ? static_cast<size_t>(g.rec_off_[g.rec_cur_])
+                                                          : (g.err_ ? static_cast<size_t>(g.err_off_) : g.in_arena_);
+        g.bytes_.erase(g.bytes_.begin(), g.bytes_.begin() + static_cast<std::ptrdiff_t>(cut));
+      }
+      g.start_.valid = g.tstamp_ != kInvalidTimeStamp;
+      g.start_.tstamp = g.tstamp_;
+    }
+    if (!raw_vals.empty()) {  // carried values are stored transformed (gen :145-150)
+      xf_vals.resize(raw_vals.size());
+      check(hbtgpu_math_tsc_to_ktime(ctx_, raw_vals.data(), xf_vals.data(), raw_vals.size()));
+      size_t k = 0;
+      for (auto& g : gens_)
+        if ((g.rec_cur_ > 0 || g.in_arena_ > 0) && g.last_sample_ != SIZE_MAX)
+          for (size_t e = 0; e < n; ++e)
+            if ((tsc_mask_ >> e) & 1) g.start_.last[e] = xf_vals[k++];
+    }
+    check(hbtgpu_reset(ctx_, 0));
+    for (auto& g : gens_) {
+      check(hbtgpu_set_carry(ctx_, static_cast<uint32_t>(g.cpu_), &g.start_));
+      if (!g.bytes_.empty())
+        check(hbtgpu_submit_image(ctx_, static_cast<uint32_t>(g.cpu_), g.bytes_.data(), g.bytes_.size(), nullptr, 0));
+      g.in_arena_ = g.bytes_.size();
+    }
     check(hbtgpu_run(ctx_));
     check(hbtgpu_sync(ctx_));
-    for (auto& g : gens_) check(hbtgpu_get_counters(ctx_, static_cast<uint32_t>(g.cpu_), &g.c_));
-    decoded_ = true;
+    for (auto& g : gens_) {
+      hbtgpu_counters c{};
+      check(hbtgpu_get_counters(ctx_, static_cast<uint32_t>(g.cpu_), &c));
+      g.err_ = c.err;
+      g.err_off_ = c.err_offset;
+      size_t nr = 0, rows = 0;
+      check(hbtgpu_get_records(ctx_, static_cast<uint32_t>(g.cpu_), nullptr, nullptr, nullptr, 0, &nr));
+      g.rec_off_.resize(nr);
+      g.rec_type_.resize(nr);
+      g.rec_size_.resize(nr);
+      if (nr)
+        check(hbtgpu_get_records(ctx_, static_cast<uint32_t>(g.cpu_), g.rec_off_.data(), g.rec_type_.data(),
+                                 g.rec_size_.data(), nr, &nr));
+      check(hbtgpu_get_rows(ctx_, static_cast<uint32_t>(g.cpu_), nullptr, 0, &rows));
+      g.rows_.resize(rows * (n + 2));
+      if (rows) check(hbtgpu_get_rows(ctx_, static_cast<uint32_t>(g.cpu_), g.rows_.data(), rows, &rows));
+      g.rec_cur_ = g.row_cur_ = 0;
+      g.last_sample_ = SIZE_MAX;
+    }
+    dirty_ = false;
   }
 
   std::vector<std::string> event_names_;
   Options opt_;
+  uint64_t tsc_mask_ = 0;
   hbtgpu_ctx* ctx_ = nullptr;
   std::vector<CpuCountSampleGenerator> gens_;
-  bool decoded_ = false;
+  bool dirty_ = true;
 };
 
 inline ssize_t CpuCountSampleGenerator::consume(unsigned max_num_records) {
-  if (max_num_records == 0) return 0;
   owner_->decode();
-  if (c_.err < 0) return static_cast<ssize_t>(c_.err);  // stalled on a bad record: -EPERM
-  // everything submitted was walked: the ring is drained, and consume() reports that as
-  // -ENODATA instead of the count (quirk at :1574-1588)
-  return -ENODATA;
+  const size_t n = owner_->getNumEvents();
+  unsigned num_records = 0;
+  while (num_records < max_num_records && rec_cur_ < rec_off_.size()) {
+    const uint32_t type = rec_type_[rec_cur_];
+    const size_t off = static_cast<size_t>(rec_off_[rec_cur_]);
+    switch (type) {
+      case 9: {  // PERF_RECORD_SAMPLE -> handleRecordSample (gen :132-202)
+        ++c_.sample;
+        if (tstamp_ == kInvalidTimeStamp) {
+          ++c_.num_unknown_count_interval;
+        } else {
+          const uint64_t* r = &rows_[row_cur_ * (n + 2)];
+          out_.emplace_back(r, r + n + 2);
+          ++row_cur_;
+          ++c_.num_rows;
+        }
+        tstamp_ = PerCpuCountSampleGenerator::word(bytes_, off + 8);
+        last_sample_ = rec_cur_;
+        break;
+      }
+      case 2:  // PERF_RECORD_LOST (:1440-1450, gen :110-124)
+        c_.lost += PerCpuCountSampleGenerator::word(bytes_, off + 16);
+        tstamp_ = kInvalidTimeStamp;
+        break;
+      case 5: ++c_.throttle; break;
+      case 6: ++c_.unthrottle; break;
+      case 8: ++c_.read; break;
+      default: break;  // skipped by size (:1565-1567)
+    }
+    ++c_.num_records;
+    ++num_records;
+    ++rec_cur_;
+  }
+  if (rec_cur_ == rec_off_.size() && num_records < max_num_records) {
+    if (err_ < 0) {
+      // the walk stalls on the next record.  A well-formed SAMPLE there means time went back:
+      // the reference invalidates count_.tstamp and returns -EPERM (gen :156-163); the next
+      // consume() meets the same SAMPLE with an invalid state and re-bases on it.
+      const size_t off = static_cast<size_t>(err_off_);
+      if (off + 24 <= bytes_.size()) {
+        const uint64_t h = PerCpuCountSampleGenerator::word(bytes_, off);
+        const bool sample_ok = static_cast<uint32_t>(h) == 9 && (h >> 48) == 40 + 8 * n &&
+                               PerCpuCountSampleGenerator::word(bytes_, off + 16) == n;
+        if (sample_ok && tstamp_ != kInvalidTimeStamp) {
+          tstamp_ = kInvalidTimeStamp;
+          owner_->dirty_ = true;  // decode again from the stalled record, state invalid
+        }
+      }
+      c_.err = err_;
+      c_.err_offset = err_off_;
+      return static_cast<ssize_t>(err_);
+    }
+    return -ENODATA;  // drained (:1574-1576)
+  }
+  return static_cast<ssize_t>(num_records);
 }
+
+/// GroupReadValues<mode::Counting> (PerfEventsGroup.h:386-586) with its arithmetic computed by the
+/// library (hbtgpu_math_*, the same device functions the bucket path uses).  accum / diff are
+/// wrapping integer adds (:548-573).
+class GroupReadValues {
+ public:
+  GroupReadValues(hbtgpu_ctx* ctx, size_t num_events) : ctx_{ctx}, count_(num_events, 0) {}
+  size_t getNumEvents() const { return count_.size(); }
+  void setTimeEnabled(uint64_t v) { time_enabled_ = v; }
+  void setTimeRunning(uint64_t v) { time_running_ = v; }
+  void setCount(size_t i, uint64_t v) { count_.at(i) = v; }
+  uint64_t getTimeEnabled() const { return time_enabled_; }
+  uint64_t getTimeRunning() const { return time_running_; }
+  uint64_t getRawCount(size_t i) const { return count_.at(i); }
+  void zero() {
+    time_enabled_ = time_running_ = 0;
+    std::fill(count_.begin(), count_.end(), 0);
+  }
+  /// :467-481
+  uint64_t getCount(size_t i) const {
+    uint64_t out = 0;
+    ck(hbtgpu_math_get_count(ctx_, &count_.at(i), &time_enabled_, &time_running_, &out, 1));
+    return out;
+  }
+  std::vector<uint64_t> getCounts() const {
+    const size_t n = count_.size();
+    std::vector<uint64_t> te(n, time_enabled_), tr(n, time_running_), out(n);
+    ck(hbtgpu_math_get_count(ctx_, count_.data(), te.data(), tr.data(), out.data(), n));
+    return out;
+  }
+  /// :513-522 (returns te / tr, as the reference does despite its comment)
+  float getRunningRatio() const {
+    float r = 0;
+    uint64_t ri = 0;
+    uint8_t m = 0;
+    ck(hbtgpu_math_running_ratio(ctx_, &time_enabled_, &time_running_, &r, &ri, &m, 1));
+    return r;
+  }
+  /// getRunningRatioInteger<100> (:527-535)
+  uint64_t getRunningRatioInteger100() const {
+    float r = 0;
+    uint64_t ri = 0;
+    uint8_t m = 0;
+    ck(hbtgpu_math_running_ratio(ctx_, &time_enabled_, &time_running_, &r, &ri, &m, 1));
+    return ri;
+  }
+  bool hasMultiplexing() const { return time_enabled_ != 0 && time_running_ != time_enabled_; }  // :538-540
+  void accum(const GroupReadValues& o) {  // :548-556
+    time_enabled_ += o.time_enabled_;
+    time_running_ += o.time_running_;
+    for (size_t i = 0; i < count_.size(); ++i) count_[i] += o.count_.at(i);
+  }
+  void diff(const GroupReadValues& o) {  // :558-573
+    time_enabled_ -= o.time_enabled_;
+    time_running_ -= o.time_running_;
+    for (size_t i = 0; i < count_.size(); ++i) count_[i] -= o.count_.at(i);
+  }
+  /// getReducedCount (:502-511) with getRateReducer (BuiltinMetrics.cpp:102-118)
+  std::optional<double> getRateReducedCount() const {
+    if (count_.size() == 1) return static_cast<double>(getCount(0));
+    if (count_.size() != 2) return std::nullopt;
+    const std::vector<uint64_t> v = getCounts();
+    double out = 0;
+    uint8_t valid = 0;
+    ck(hbtgpu_math_rate(ctx_, &v[0], &v[1], &out, &valid, 1));
+    return valid ? std::optional<double>(out) : std::nullopt;
+  }
+  /// ... with getAddReducer (BuiltinMetrics.cpp:88-97, int accumulator)
+  std::optional<double> getAddReducedCount() const {
+    if (count_.size() == 1) return static_cast<double>(getCount(0));
+    const std::vector<uint64_t> v = getCounts();
+    double out = 0;
+    ck(hbtgpu_math_add_reduce(ctx_, v.data(), v.size(), &out, 1));
+    return out;
+  }
+
+ private:
+  void ck(int rc) const {
+    if (rc != 0) throw std::runtime_error(hbtgpu_last_error(ctx_));
+  }
+  hbtgpu_ctx* ctx_;
+  uint64_t time_enabled_ = 0, time_running_ = 0;
+  std::vector<uint64_t> count_;
+};
 
 // ---- ContextSwitch mode ---------------------------------------------------------------------
 using Event = hbtgpu_cs_event;  // layout of tagstack::Event
@@ -326,8 +565,10 @@ class PerCpuThreadSwitchGenerator {
       check(hbtgpu_cs_reset(ctx_));
       decoded_ = false;
     }
-    check(hbtgpu_cs_submit_image(ctx_, static_cast<uint32_t>(cpu), s.first.from, s.first.size));
-    if (s.second) check(hbtgpu_cs_submit_image(ctx_, static_cast<uint32_t>(cpu), s.second->from, s.second->size));
+    // a wrapped ring is cut wherever the byte count says, usually inside a record: both slices
+    // become ONE image (consume() reassembles such a record, PerfEventsGroup.h:1425-1437)
+    check(hbtgpu_cs_submit_image_slices(ctx_, static_cast<uint32_t>(cpu), s.first.from, s.first.size,
+                                        s.second ? s.second->from : nullptr, s.second ? s.second->size : 0));
   }
 
   std::vector<ThreadInfo> getThreadsInfo() const {

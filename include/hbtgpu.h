@@ -497,6 +497,12 @@ int hbtgpu_cs_set_state(hbtgpu_cs_ctx* ctx, uint32_t cpu, const hbtgpu_cs_state*
 /* Append one ring image (whole records, oldest first) of one cpu; host memory, copied
  * asynchronously (pin it for speed).  Images of a cpu form its stream in submission order. */
 int hbtgpu_cs_submit_image(hbtgpu_cs_ctx* ctx, uint32_t cpu, const void* bytes, uint64_t len);
+/* The same for the two borrowed slices onCpuDataBufferRead hands out when the unread span wraps
+ * around the end of the ring (RbDataSlices, PerfEventsGroup.h:45-62,1592-1637): first ++ second is
+ * one image.  The cut may fall anywhere, also inside a record (consume() reassembles such a
+ * record through its aux buffer, :1425-1437); here both slices land back to back in the arena. */
+int hbtgpu_cs_submit_image_slices(hbtgpu_cs_ctx* ctx, uint32_t cpu, const void* first, uint64_t n1,
+                                  const void* second, uint64_t n2);
 /* Forget the submitted images (states are kept). */
 int hbtgpu_cs_reset(hbtgpu_cs_ctx* ctx);
 /* Decode everything submitted since the last reset.  Asynchronous on the context's stream
