@@ -1346,7 +1346,8 @@ int na_device_setup(int dev, NaScratch** out) {
     if (e != cudaSuccess || !p)
       return na_fail(-EIO, "cudaGetSymbolAddress(scratch) failed on device %d: %s", dev,
                      cudaGetErrorString(e));
-    for (auto k : {(const void*)k_decode<true, MODE_AGG, 0>, (const void*)k_decode<false, MODE_AGG, 0>}) {
+    for (auto k : {(const void*)k_decode<true, MODE_AGG, 0>, (const void*)k_decode<true, MODE_AGG, 0, 8>,
+                   (const void*)k_decode<true, MODE_AGG, 0, 4>, (const void*)k_decode<false, MODE_AGG, 0>}) {
       e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(decode_smem_bytes<MODE_AGG, 0>(TILE_MAX_BYTES)));
       if (e != cudaSuccess)
@@ -1452,7 +1453,10 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
     const bool force_exact = (cfg->flags & HBTGPU_F_FORCE_EXACT) != 0;
     if (force_exact) NCK(cudaMemsetAsync(&sc->flags[FLAG_NEED_EXACT], 1, 1, st));
     if (!force_exact) {
-      k_decode<true, MODE_AGG, 0><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
+      // the same kernels hbtgpu_run launches: the builds specialised for 8- and 4-event groups where they apply
+      if (n == 8) k_decode<true, MODE_AGG, 0, 8><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
+      else if (n == 4) k_decode<true, MODE_AGG, 0, 4><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
+      else k_decode<true, MODE_AGG, 0><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
       k_verify<<<(nc + 255) / 256, 256, 0, st>>>(P);
     }
     k_resolve<<<1, RES_THREADS, 0, st>>>(P);

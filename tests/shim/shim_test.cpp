@@ -25,6 +25,11 @@ static uint64_t hdr(uint32_t type, uint32_t size) { return type | (uint64_t(size
     }                                                                      \
   } while (0)
 
+#define EXPECT_V(cond)                                                      \
+  do {                                                                      \
+    if (!(cond)) std::fprintf(stderr, "EXPECT failed: %s (line %d)\n", #cond, __LINE__); \
+  } while (0)
+
 int main() {
   std::vector<uint8_t> ring;
   for (int i = 0; i < 10; ++i) {
@@ -112,7 +117,7 @@ int main() {
   EXPECT(bad.getCpuGenerator(0).getNumRecordSample() == 1);
   bool threw = false;
   try {
-    bad.accumUntil(10, 0);
+    bad.accumUntil(10, 1000);  // last timestamp 10 <= stop_ts: consume() runs into the bad record
   } catch (const std::runtime_error&) {
     threw = true;  // accumUntil throws on unexpected errors (:76-79)
   }
@@ -124,6 +129,111 @@ int main() {
     threw = true;
   }
   EXPECT(threw);
+
+  // ---- accumUntil(batch, stop_ts), PerCpuSampleGeneratorBase.h:69-94: a CPU is consumed batch by
+  // batch while its last timestamp is <= stop_ts; what lies behind stays in the ring for the next call
+  {
+    auto put_sample = [&](std::vector<uint8_t>& b, uint64_t ts, uint64_t v) {
+      put(b, hdr(9, 56));
+      put(b, ts);
+      put(b, 2);
+      put(b, ts);
+      put(b, ts);
+      put(b, v);
+      put(b, 2 * v);
+    };
+    PerCpuCountSampleGenerator::Options o2;
+    o2.num_cpus = 1;
+    o2.t0 = 0;
+    o2.bucket_ns = 1000;
+    o2.n_buckets = 8;
+    PerCpuCountSampleGenerator g2({"a", "b"}, o2);
+    g2.enable(0, 50);
+    std::vector<uint8_t> w1;
+    for (int i = 1; i <= 10; ++i) put_sample(w1, 100 * i, 10 * i);  // samples at 100 .. 1000
+    g2.onCpuDataBufferRead(0, RbDataSlices(w1.data(), w1.size()));
+    auto& c0 = g2.getCpuGenerator(0);
+    // batch 3, stop at 450: batches [100,200,300] (last 300 <= 450) and [400,500,600] (last 600 > 450)
+    EXPECT(g2.accumUntil(3, 450) == 1);
+    EXPECT(c0.getNumRecordSample() == 6 && c0.getNumEntries() == 6 && c0.getLastTimeStamp() == 600);
+    // nothing more happens while stop_ts is behind the last timestamp
+    EXPECT(g2.accumUntil(3, 450) == 1 && c0.getNumRecordSample() == 6);
+    size_t seen = 0;
+    uint64_t last_ts = 0, last_delta = 0;
+    g2.applyToCountSamples([&](CpuId, size_t idx, const std::vector<std::string>&, TimeStamp ts, TimeStamp dur,
+                               const uint64_t* counts, size_t) {
+      EXPECT_V(idx == seen);
+      ++seen;
+      last_ts = ts + dur;
+      last_delta = counts[0];
+    });
+    EXPECT(seen == 6 && last_ts == 600 && last_delta == 10 && c0.getNumEntries() == 0);
+    // the next window arrives while four records are still unconsumed: a daemon's loop
+    std::vector<uint8_t> w2;
+    for (int i = 11; i <= 14; ++i) put_sample(w2, 100 * i, 10 * i);
+    const size_t cut = 56 + 24;  // the ring wrapped inside the second record
+    g2.onCpuDataBufferRead(0, RbDataSlices(w2.data(), cut, w2.data() + cut, w2.size() - cut));
+    EXPECT(g2.accumUntil(100, 100000) == 1);  // drains: -ENODATA ends the CPU quietly
+    EXPECT(c0.getNumRecordSample() == 14 && c0.getNumEntries() == 8 && c0.getLastTimeStamp() == 1400);
+    seen = 0;
+    uint64_t first_ts = 0, first_delta = 0;
+    g2.applyToCountSamples([&](CpuId, size_t idx, const std::vector<std::string>&, TimeStamp ts, TimeStamp,
+                               const uint64_t* counts, size_t) {
+      if (idx == 0) {
+        first_ts = ts;
+        first_delta = counts[1];
+      }
+      ++seen;
+    });
+    EXPECT(seen == 8 && first_ts == 600 && first_delta == 20);  // row 700: continues from the sample at 600
+    // a third window: only the new bytes are decoded (lifetime counters keep growing)
+    std::vector<uint8_t> w3;
+    put_sample(w3, 1500, 150);
+    put(w3, hdr(2, 24));  // LOST: count_.tstamp becomes invalid ...
+    put(w3, 7);
+    put(w3, 5);
+    put_sample(w3, 1600, 160);
+    g2.onCpuDataBufferRead(0, RbDataSlices(w3.data(), w3.size()));
+    EXPECT(g2.accumUntil(2, 100000) == 1);
+    // ... and an invalid timestamp (the maximum) is never <= stop_ts: the reference stops consuming
+    // this CPU right there, and so does the shim
+    EXPECT(c0.getNumRecordSample() == 15 && c0.getNumRecordLost() == 5 && c0.getLastTimeStamp() == kInvalidTimeStamp);
+    EXPECT(c0.consume(10) == -ENODATA && c0.getNumRecordSample() == 16 && c0.getNumUnknownCountInterval() == 1);
+    EXPECT(c0.getLastTimeStamp() == 1600 && c0.getNumEntries() == 1);
+
+    // time going back: -EPERM once, count_.tstamp invalidated, the next consume() re-bases (gen :156-163)
+    PerCpuCountSampleGenerator g3({"a", "b"}, o2);
+    g3.enable(0, 50);
+    std::vector<uint8_t> w4;
+    put_sample(w4, 100, 1);
+    put_sample(w4, 200, 2);
+    put_sample(w4, 150, 3);
+    put_sample(w4, 300, 4);
+    g3.onCpuDataBufferRead(0, RbDataSlices(w4.data(), w4.size()));
+    auto& d0 = g3.getCpuGenerator(0);
+    EXPECT(d0.consume(10) == -EPERM && d0.getNumRecordSample() == 2 && d0.getLastTimeStamp() == kInvalidTimeStamp);
+    EXPECT(d0.consume(10) == -ENODATA && d0.getNumRecordSample() == 4 && d0.getNumEntries() == 3);
+    EXPECT(d0.getNumUnknownCountInterval() == 1 && d0.getLastTimeStamp() == 300);
+
+    // GroupReadValues (PerfEventsGroup.h:386-586) over the library's arithmetic; known answers of
+    // hbt/src/mon/tests/MonitorMockTest.cpp:86-88,121-126
+    GroupReadValues rv(g3.raw(), 2);
+    rv.setTimeEnabled(4);
+    rv.setTimeRunning(2);
+    rv.setCount(0, 200);
+    rv.setCount(1, 100);
+    EXPECT(rv.getCount(0) == 400 && rv.hasMultiplexing() && rv.getRunningRatioInteger100() == 50);
+    EXPECT(rv.getRateReducedCount().value() == 2.0);
+    GroupReadValues rw(g3.raw(), 2);
+    rw.setTimeEnabled(1);
+    rw.setTimeRunning(1);
+    rw.setCount(0, 100);
+    EXPECT(rw.getCount(0) == 100 && !rw.hasMultiplexing());
+    rv.accum(rw);
+    EXPECT(rv.getRawCount(0) == 300 && rv.getTimeEnabled() == 5);
+    rv.diff(rw);
+    EXPECT(rv.getRawCount(0) == 200 && rv.getTimeRunning() == 2);  // PerCpuGeneratorsTest.cpp:195-232
+  }
   // ---- ContextSwitch mode: the stream of tests/test_cs_oracle.py::test_known_answer_small ----
   {
     const uint32_t T = 5000001;
@@ -156,7 +266,10 @@ int main() {
     sid(T + 8, T + 9, 1900);
     sw(2000, 0, 0);                        // idle in
     PerCpuThreadSwitchGenerator tsg(2, 3);
-    tsg.onCpuThreadSwitchBufferRead(0, RbDataSlices(cs.data(), cs.size()));
+    // the ring wrapped in the middle of the FORK record (a wrap almost never falls on a
+    // record boundary; consume() reassembles the record, PerfEventsGroup.h:1425-1437)
+    const size_t wrap = 32 + 32 + 40 + 32 + 20;
+    tsg.onCpuThreadSwitchBufferRead(0, RbDataSlices(cs.data(), wrap, cs.data() + wrap, cs.size() - wrap));
     auto& t0 = tsg.getCpuGenerator(0);
     ssize_t r = t0.consume(1000);
     EXPECT(r >= 0 || r == -ENODATA);

@@ -188,3 +188,28 @@ def test_cfg4_ip_tid_attribution(port_oracle):
     assert top == [(int(ik[i]), int(ic[i])) for i in order]
     _, acc_ref, _ = port_oracle.run_capture(p, streams, carries, n_threads=16)
     assert np.array_equal(acc, acc_ref)
+
+
+def test_cfg2_slice_against_the_compiled_reference(ref_oracle):
+    """Closes the chain GPU == restatement == reference on the box itself: 24 of cfg2's 192 CPUs
+    (2.4 M records) against oracle/_ref, the unmodified hbt code (real consume() + row drain;
+    its harness sums delta[] and n_rows per bucket -- the rows carry no time_enabled/running)."""
+    n, nb, t0, bns, ncpu = 8, 10_100, synth.T_START, 1_000_000, 24
+    spec, streams = synth.capture(2, ncpu, n_samples=100_000)
+    g = _run_gpu(streams, n, nb, t0, bns)
+    try:
+        p = po.make_params(n, n_buckets=nb, t0=t0, bucket_ns=bns)
+        carries = [po.make_carry(valid=True, tstamp=t0, last=[0] * n) for _ in streams]
+        _, acc, ctrs = ref_oracle.run_capture(p, streams, carries, n_threads=8, batch=4096)
+        b = g.buckets(want_scaled=False, want_metric=False, want_valid=False)["acc"]
+        cols = list(range(n)) + [n + 2]
+        assert np.array_equal(b[:, :, cols], acc[:, :, cols]), "bucket sums differ from the compiled reference"
+        for cpu in range(ncpu):
+            got = g.counters(cpu)
+            for k in ("sample", "lost", "throttle", "unthrottle", "num_rows"):
+                assert got[k] == ctrs[cpu][k], (cpu, k)
+        # one cpu completely (te / tr sums, carry-out) through the reference's decode_stream
+        exp = ref_oracle.decode_stream(p, streams[5], carries[5], want_records=False, want_rows=False)
+        assert np.array_equal(b[5], exp["buckets"])
+    finally:
+        g.close()

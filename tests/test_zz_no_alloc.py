@@ -79,6 +79,37 @@ def test_noalloc_matches_context_twice_in_a_row():
         del img_dev
 
 
+@pytest.mark.parametrize("n", [8, 4, 3])
+def test_noalloc_matches_the_oracle(n):
+    """The same entry point against the CPU oracle directly (not only against the context path),
+    for the group sizes that have a specialised kernel build (8, 4) and one that has not (3)."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from dynolog_b200 import synth
+    from oracle import pyoracle as po
+    import ringgen as rg
+    nb, t0, bns = 3000, synth.T_START, 1_000_000
+    data, _ = rg.random_stream(77 + n, 20_000, n, p_lost=0.002, p_throttle=0.002, mux=True)
+    port = po.load("port")
+    params = po.make_params(n, n_buckets=nb, t0=t0, bucket_ns=bns)
+    exp = port.decode_stream(params, data, po.make_carry(valid=True, tstamp=t0, last=[0] * n),
+                             want_records=False, want_rows=False)
+    cfg = hbtgpu.Config()
+    cfg.device, cfg.n_events, cfg.n_buckets, cfg.t0, cfg.bucket_ns = 0, n, nb, t0, bns
+    cfg.time_mult, cfg.max_cpus = 1, 1
+    acc_dev = torch.empty(nb * (n + 3), dtype=torch.int64, device="cuda:0")
+    img_dev = torch.from_numpy(data).to("cuda:0")
+    for _ in range(2):
+        acc_dev.fill_(-1)
+        torch.cuda.synchronize()
+        ctr, cout = hbtgpu.decode_image_noalloc(cfg, img_dev.data_ptr(), len(data), acc_dev.data_ptr(),
+                                                carry_in=hbtgpu.make_carry(valid=True, tstamp=t0, last=[0] * n))
+        got = acc_dev.cpu().numpy().view(np.uint64).reshape(nb, n + 3)
+        assert ctr == exp["counters"]
+        assert np.array_equal(got, exp["buckets"])
+        assert _carry_tuple(cout, n) == _carry_tuple(exp["carry_out"], n)
+
+
 def test_noalloc_rejects_oversized_image():
     if not torch.cuda.is_available():
         pytest.skip("needs a CUDA device")
