@@ -975,6 +975,115 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
   __syncthreads();
 }
 
+// General path, MODE_AGG: check and count the reachable records of one staged (sub-)tile as
+// decode_tile does, but instead of aggregating them list the SAMPLEs exactly as index_tile does
+// (s.pos[k] = word position, s.fl[k] = a LOST lies between sample k-1 and k; s.idx_n, s.idx_gap),
+// so that ONE aggregation routine (uniform_segment<..., IDX = true>) serves every path.
+// Leaves the carry alone except for "a LOST and no SAMPLE behind it".  Contains barriers.
+template <int PRE>
+__device__ __forceinline__ void list_tile(Smem& s, const Params& P, const uint64_t* buf, uint32_t K,
+                                          uint32_t cur) {
+  const uint32_t n = P.n_events;
+  const uint32_t ipt = (K + NT - 1) / NT;  // candidates per thread (blocked)
+  const uint32_t j0 = threadIdx.x * ipt;
+  const uint32_t j1 = min(j0 + ipt, K);
+  if (threadIdx.x == 0) s.red_key = 0;  // number of samples with a LOST in front
+  // pass 0: type checks, counters of everything that is not a SAMPLE, scan inputs
+  uint32_t a = 0, b = 0;
+  uint32_t n_thr = 0, n_unthr = 0, n_read = 0, n_other = 0;
+  unsigned long long lost = 0;
+  for (uint32_t j = j0; j < j1; ++j) {
+    uint8_t f = s.fl[j];
+    if (f & FL_REACH) {
+      const uint32_t p = s.pos[j];
+      const uint64_t h = buf[p];
+      const uint32_t type = static_cast<uint32_t>(h);
+      const uint32_t size = static_cast<uint32_t>(h >> 48);
+      if (type == REC_SAMPLE) {
+        const uint64_t nr = (size + 16 >= (40u + 8u * PRE)) ? buf[p + PRE + 2] : ~0ull;
+        if (size < (40u + 8u * PRE) || nr != ((size - (40u + 8u * PRE)) >> 3) || nr != n) {
+          atomicMin(&s.tile_err, p);
+        } else {
+          f |= FL_SAMPLE;
+          a = __vmaxu2(a, (j + 1) << 16);
+          b += 1;
+        }
+      } else {
+        ++n_other;
+        if (type == REC_LOST) {
+          if (size < 24) {
+            atomicMin(&s.tile_err, p);
+          } else {
+            f |= FL_LOST;
+            a = __vmaxu2(a, j + 1);
+            lost += buf[p + 2];  // num_lost (:1448)
+          }
+        } else if (type == REC_READ) {
+          const uint64_t nr = (size >= 24) ? buf[p + 2] : ~0ull;
+          if (size < 40 || nr != ((size - 40u) >> 3)) atomicMin(&s.tile_err, p);  // :1518-1523
+          else ++n_read;
+        } else if (type == REC_THROTTLE) {
+          ++n_thr;
+        } else if (type == REC_UNTHROTTLE) {
+          ++n_unthr;
+        }
+      }
+      s.fl[j] = f;
+    }
+  }
+  uint32_t ex_a, ex_b, tot_a, tot_b;
+  block_scan(s, a, b, ex_a, ex_b, tot_a, tot_b);
+  // pass 1: every sample's rank among the samples and whether a LOST precedes it inside the tile
+  uint32_t run_a = ex_a, ord = ex_b, flagged = 0;
+  for (uint32_t j = j0; j < j1; ++j) {
+    const uint8_t f = s.fl[j];
+    if (f & FL_SAMPLE) {
+      const uint32_t prev_s = run_a >> 16, prev_l = run_a & 0xFFFFu;
+      const bool lost_before = prev_s != 0 ? (prev_l > prev_s) : (prev_l != 0);
+      s.u.de.bkt[ord] = static_cast<uint32_t>(s.pos[j]) | (lost_before ? 0x10000u : 0u);
+      flagged += lost_before ? 1u : 0u;
+      run_a = __vmaxu2(run_a, (j + 1) << 16);
+      ++ord;
+    } else if (f & FL_LOST) {
+      run_a = __vmaxu2(run_a, j + 1);
+    }
+  }
+  {
+    const uint32_t vals[5] = {n_thr, n_unthr, n_read, n_other, flagged};
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const uint32_t v = __reduce_add_sync(0xffffffffu, vals[k]);
+      if ((threadIdx.x & 31) == 0 && v) {
+        if (k == 0) atomicAdd(&s.cnt[C_THROTTLE], v);
+        else if (k == 1) atomicAdd(&s.cnt[C_UNTHROTTLE], v);
+        else if (k == 2) atomicAdd(&s.cnt[C_READ], v);
+        else if (k == 3) atomicAdd(&s.cnt[C_RECORDS], v);
+        else atomicAdd(&s.red_key, v);
+      }
+    }
+    if (__any_sync(0xffffffffu, lost != 0)) {
+      unsigned long long l = lost;
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) l += __shfl_xor_sync(0xffffffffu, l, d);
+      if ((threadIdx.x & 31) == 0) atomicAdd(&s.lost_sum, l);
+    }
+  }
+  __syncthreads();  // the list is complete; pos / fl of the candidates are no longer needed
+  const uint32_t ns = tot_b, last_s = tot_a >> 16, last_l = tot_a & 0xFFFFu;
+  for (uint32_t k = threadIdx.x; k < ns; k += NT) {
+    const uint32_t v = s.u.de.bkt[k];
+    s.pos[k] = static_cast<uint16_t>(v);
+    s.fl[k] = static_cast<uint8_t>(v >> 16);
+  }
+  if (threadIdx.x == 0) {
+    s.idx_n = ns;
+    s.idx_gap = (last_l > last_s ? 1u : 0u) | (s.red_key << 1);  // bit 0: a LOST behind the last sample
+    s.idx_bad = 0xFFFFFFFFu;
+    if (ns == 0 && last_l != 0) s.c[cur].gap = 1;  // no sample behind the LOST: the carry remembers it
+  }
+  __syncthreads();
+}
+
 // Index of a mixed tile (MODE_AGG).  A tile that holds other records than configured SAMPLEs
 // (THROTTLE / UNTHROTTLE pairs under a high sample rate, LOST) used to be cut at each of them
 // and every piece cost a full pass.  Instead warp 0 walks the chain once -- runs of SAMPLEs 32
@@ -1659,7 +1768,16 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
           const uint32_t tk = s.term_kind, tt = s.term_tgt;
           tc.tile_abs = tile_abs + 8ull * w0;
           tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base) + 8ull * w0;
-          decode_tile<false, MODE, PRE>(s, P, sb, K, tc, cur);
+          if (MODE == MODE_AGG) {
+            // one aggregation routine for every path: list the samples, then the indexed pass
+            list_tile<PRE>(s, P, sb, K, cur);
+            uint32_t n_idx = 0;
+            const uint32_t ki = uniform_segment<MODE, PRE, NEV, true>(s, P, sb, wh, 0, tc, cur, n_idx);
+            if (ki) cur ^= 1;
+            __syncthreads();  // the new carry and s.tile_err are published
+          } else {
+            decode_tile<false, MODE, PRE>(s, P, sb, K, tc, cur);
+          }
           term_kind = (tk != 0 || s.tile_err != 0xFFFFFFFFu) ? 1u + tk : 0u;
           ew = w0 + tt;
         }
@@ -2170,9 +2288,11 @@ __global__ void __launch_bounds__(256) k_pack_stubs(const Params P, uint64_t* ds
 // Shards behind a stall contribute nothing.  Outputs for `rank`: the state in front of its shard
 // and dead[cpu] (1: an earlier shard stalled); for every rank r: the bucket range its rows can
 // have touched (ranges[r * n_streams + cpu] = lo | hi << 32, lo > hi: none), if ranges != null.
+// tid / nthr: the calling thread's index among the nthr threads (1 or a warp) that work on this
+// cpu together; all of them follow the same control flow, the copies of last_[] are split.
 __device__ __forceinline__ void fold_cpu(const Params& P, uint32_t cpu, const uint64_t* gathered, uint32_t world,
                                          uint32_t rank, const hbtgpu_carry* init, hbtgpu_carry* prev_out,
-                                         uint32_t* dead_out, uint64_t* ranges) {
+                                         uint32_t* dead_out, uint64_t* ranges, uint32_t tid, uint32_t nthr) {
   const uint32_t ns = P.n_streams;
   const uint32_t n = P.n_events, sw = stub_words(n);
   // the state is (valid, tstamp) plus a pointer to where te / tr / last[] come from
@@ -2180,26 +2300,20 @@ __device__ __forceinline__ void fold_cpu(const Params& P, uint32_t cpu, const ui
   uint64_t tstamp = init[cpu].tstamp;
   const uint64_t* src = nullptr;  // packed stub whose tail holds te, tr, last[]; null: init
   bool dead = false;
+  auto emit = [&]() {  // the state as it is now -> prev_out[cpu]
+    hbtgpu_carry& d = prev_out[cpu];
+    if (tid == 0) {
+      d.valid = valid ? 1 : 0;
+      d.tstamp = valid ? tstamp : ~0ull;
+      d.te = src ? src[SW_TAIL_TE] : init[cpu].te;
+      d.tr = src ? src[SW_TAIL_TR] : init[cpu].tr;
+      dead_out[cpu] = dead ? 1u : 0u;
+    }
+    for (uint32_t e = tid; e < n; e += nthr) d.last[e] = src ? src[SW_VALUES + n + e] : init[cpu].last[e];
+  };
   for (uint32_t r = 0; r < world; ++r) {
     if (r == rank) {
-      hbtgpu_carry o;
-      if (src) {
-        o.te = src[SW_TAIL_TE];
-        o.tr = src[SW_TAIL_TR];
-        for (uint32_t e = 0; e < n; ++e) o.last[e] = src[SW_VALUES + n + e];
-      } else {
-        o = init[cpu];
-      }
-      o.valid = valid ? 1 : 0;
-      o.tstamp = valid ? tstamp : ~0ull;
-      // only the first n values are meaningful; write field by field (the struct is 544 bytes)
-      hbtgpu_carry& d = prev_out[cpu];
-      d.valid = o.valid;
-      d.tstamp = o.tstamp;
-      d.te = o.te;
-      d.tr = o.tr;
-      for (uint32_t e = 0; e < n; ++e) d.last[e] = o.last[e];
-      dead_out[cpu] = dead ? 1u : 0u;
+      emit();
       if (!ranges) return;
     }
     const uint64_t* st = gathered + (static_cast<size_t>(r) * ns + cpu) * sw;
@@ -2207,16 +2321,18 @@ __device__ __forceinline__ void fold_cpu(const Params& P, uint32_t cpu, const ui
     uint32_t lo = 1, hi = 0;
     if (!dead) {
       const bool has = (fl & SF_HAS_SAMPLE) != 0, lostb = (fl & SF_LOST_BEFORE) != 0;
-      if (has && !lostb && valid && tstamp > st[SW_HEAD_TS]) {
+      const uint64_t head_ts = st[SW_HEAD_TS];
+      if (has && !lostb && valid && tstamp > head_ts) {
         dead = true;  // stalls on this shard's first SAMPLE: nothing of the shard is aggregated
       } else {
         if (has) {
           // rows of the shard lie between its first and its last SAMPLE
-          const uint64_t d0 = st[SW_HEAD_TS] - P.t0, d1 = st[SW_LAST_SAMPLE_TS] - P.t0;
-          const bool below0 = st[SW_HEAD_TS] < P.t0, below1 = st[SW_LAST_SAMPLE_TS] < P.t0;
+          const uint64_t last_ts = st[SW_LAST_SAMPLE_TS];
+          const uint64_t d0 = head_ts - P.t0, d1 = last_ts - P.t0;
+          const bool below0 = head_ts < P.t0, below1 = last_ts < P.t0;
           if (!below1 && !(!below0 && d0 >= P.range_ns)) {
-            lo = below0 ? 0u : bucket_of(P, st[SW_HEAD_TS]);
-            hi = d1 >= P.range_ns ? P.n_buckets - 1 : bucket_of(P, st[SW_LAST_SAMPLE_TS]);
+            lo = below0 ? 0u : bucket_of(P, head_ts);
+            hi = d1 >= P.range_ns ? P.n_buckets - 1 : bucket_of(P, last_ts);
           }
           src = st;
           valid = (fl & SF_TAIL_VALID) != 0;
@@ -2227,24 +2343,17 @@ __device__ __forceinline__ void fold_cpu(const Params& P, uint32_t cpu, const ui
         if (fl & SF_STALLED) dead = true;  // the shard's own walk stalled: later shards are never reached
       }
     }
-    if (ranges) ranges[static_cast<size_t>(r) * ns + cpu] = static_cast<uint64_t>(lo) | (static_cast<uint64_t>(hi) << 32);
+    if (ranges && tid == 0)
+      ranges[static_cast<size_t>(r) * ns + cpu] = static_cast<uint64_t>(lo) | (static_cast<uint64_t>(hi) << 32);
   }
-  if (rank >= world) {  // the state after the last shard (no rank owns it)
-    hbtgpu_carry& d = prev_out[cpu];
-    d.valid = valid ? 1 : 0;
-    d.tstamp = valid ? tstamp : ~0ull;
-    d.te = src ? src[SW_TAIL_TE] : init[cpu].te;
-    d.tr = src ? src[SW_TAIL_TR] : init[cpu].tr;
-    for (uint32_t e = 0; e < n; ++e) d.last[e] = src ? src[SW_VALUES + n + e] : init[cpu].last[e];
-    dead_out[cpu] = dead ? 1u : 0u;
-  }
+  if (rank >= world) emit();  // the state after the last shard (no rank owns it)
 }
 
 __global__ void k_fold(const Params P, const uint64_t* gathered, uint32_t world, uint32_t rank,
                        const hbtgpu_carry* init, hbtgpu_carry* prev_out, uint32_t* dead_out,
                        uint64_t* ranges) {
   const uint32_t cpu = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cpu < P.n_streams) fold_cpu(P, cpu, gathered, world, rank, init, prev_out, dead_out, ranges);
+  if (cpu < P.n_streams) fold_cpu(P, cpu, gathered, world, rank, init, prev_out, dead_out, ranges, 0, 1);
 }
 
 // One block per stream: add the row that straddles the shard boundary -- or, where the walk of
@@ -2264,7 +2373,9 @@ __device__ __forceinline__ void boundary_cpu(const Params& P, uint32_t sidx, con
   // handleRecordSample emits a row iff the state is valid when the SAMPLE arrives (:135,165-182)
   const bool reached = !(ctr[C_ERR] != 0 && ctr[C_ERR_OFF] <= hs.offset);  // the shard's own walk got to that SAMPLE
   const bool regress = !is_dead && row && reached && pt.tstamp > hs.tstamp;  // (:156-163)
-  if (nthr > 1) __syncthreads();  // every thread has read the counters before thread 0 rewrites them
+  // every thread has read the counters before thread 0 rewrites them
+  if (nthr == 32) __syncwarp();
+  else if (nthr > 1) __syncthreads();
   if (is_dead || regress) {
     // consume() never gets past the stall: of this shard only the records in front of its first
     // SAMPLE (regress) or nothing at all (dead) were walked
