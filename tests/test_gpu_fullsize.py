@@ -82,7 +82,7 @@ def test_cfg3_multiplexed_lost_throttle_4gib(port_oracle):
     nb = 70_000
     g = _run_gpu(streams, n, nb, t0, bns)
     try:
-        assert g.stats()["exact_runs"] == 0
+        assert g.stats()["exact_runs"] == 0, g.stats()
         acc, ctrs = _check_against_oracle(g, port_oracle, streams, n, nb, t0, bns)
         assert sum(c["lost"] for c in ctrs) > 10_000 and sum(c["throttle"] for c in ctrs) > 1_000
         assert all(c["err"] == 0 for c in ctrs)
