@@ -67,9 +67,6 @@ struct hbtgpu_ctx {
   uint32_t tid_slots = 0, ip_slots = 0;
   ChunkDesc* d_chunks = nullptr;
   ChunkIO* d_io = nullptr;
-  ChunkAgg* d_agg = nullptr;          // plain-store aggregation: per chunk, what it left open
-  uint64_t* d_agg_vals = nullptr;
-  size_t cap_agg = 0, cap_agg_vals = 0;
   ImageDesc* d_images = nullptr;
   StreamDesc* d_streams = nullptr;
   size_t cap_chunks = 0, cap_io = 0, cap_images = 0;
@@ -225,10 +222,6 @@ int build_table(hbtgpu_ctx* ctx) {
   if (int r = ensure(ctx, &ctx->d_chunks, &ctx->cap_chunks, std::max<size_t>(nc, 1))) return r;
   if (int r = ensure(ctx, &ctx->d_io, &ctx->cap_io, std::max<size_t>(nc, 1))) return r;
   if (int r = ensure(ctx, &ctx->d_images, &ctx->cap_images, std::max<size_t>(ni, 1))) return r;
-  if (int r = ensure(ctx, &ctx->d_agg, &ctx->cap_agg, std::max<size_t>(nc, 1))) return r;
-  if (int r = ensure(ctx, &ctx->d_agg_vals, &ctx->cap_agg_vals,
-                     std::max<size_t>(nc, 1) * 2 * (ctx->cfg.n_events + 3)))
-    return r;
   if (nc) CK(cudaMemcpyAsync(ctx->d_chunks, ctx->chunks.data(), nc * sizeof(ChunkDesc),
                              cudaMemcpyHostToDevice, ctx->stream));
   if (ni) CK(cudaMemcpyAsync(ctx->d_images, ctx->img_descs.data(), ni * sizeof(ImageDesc),
@@ -256,8 +249,6 @@ Params make_params(hbtgpu_ctx* ctx) {
   P.head_extra = ctx->d_head_extra;
   P.counters = ctx->d_counters;
   P.acc = ctx->d_acc;
-  P.agg = ctx->d_agg;
-  P.agg_vals = ctx->d_agg_vals;
   P.flags = ctx->d_flags;
   P.rows = ctx->d_rows;
   P.rec_off = ctx->d_rec_off;
@@ -413,9 +404,8 @@ int ensure_emitted(hbtgpu_ctx* ctx) {
   if (nc) {
     Params P = make_params(ctx);
     CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
-    const DeriveParams D = derive_params(ctx);
-    if (P.pre) k_decode<false, MODE_EMIT, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_EMIT, 2>(P.tile_bytes), ctx->stream>>>(P, D);
-    else k_decode<false, MODE_EMIT, 0><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_EMIT, 0>(P.tile_bytes), ctx->stream>>>(P, D);
+    if (P.pre) k_decode<false, MODE_EMIT, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_EMIT, 2>(P.tile_bytes), ctx->stream>>>(P);
+    else k_decode<false, MODE_EMIT, 0><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_EMIT, 0>(P.tile_bytes), ctx->stream>>>(P);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ctx->ev_run1, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -578,11 +568,7 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
       set_smem(ctx, k_decode<false, MODE_EMIT, 0>, decode_smem_bytes<MODE_EMIT, 0>(TILE_MAX_BYTES)) ||
       set_smem(ctx, k_decode<true, MODE_AGG, 2>, decode_smem_bytes<MODE_AGG, 2>(TILE_MAX_BYTES)) ||
       set_smem(ctx, k_decode<false, MODE_AGG, 2>, decode_smem_bytes<MODE_AGG, 2>(TILE_MAX_BYTES)) ||
-      set_smem(ctx, k_decode<false, MODE_EMIT, 2>, decode_smem_bytes<MODE_EMIT, 2>(TILE_MAX_BYTES)) ||
-      set_smem(ctx, k_decode<true, MODE_AGG, 0, 0, true>, decode_smem_bytes<MODE_AGG, 0>(TILE_MAX_BYTES)) ||
-      set_smem(ctx, k_decode<true, MODE_AGG, 0, 8, true>, decode_smem_bytes<MODE_AGG, 0>(TILE_MAX_BYTES)) ||
-      set_smem(ctx, k_decode<true, MODE_AGG, 0, 4, true>, decode_smem_bytes<MODE_AGG, 0>(TILE_MAX_BYTES)) ||
-      set_smem(ctx, k_decode<true, MODE_AGG, 2, 0, true>, decode_smem_bytes<MODE_AGG, 2>(TILE_MAX_BYTES)))
+      set_smem(ctx, k_decode<false, MODE_EMIT, 2>, decode_smem_bytes<MODE_EMIT, 2>(TILE_MAX_BYTES)))
     return bail(-EIO);
 #undef CKC
   *out = ctx;
@@ -599,8 +585,7 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
                   ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
                   ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_tid_keys,
                   ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special, ctx->d_series, ctx->d_boundary_cell,
-                  ctx->d_head_extra, ctx->d_dead, ctx->d_stub_block, ctx->d_acc_total,
-                  ctx->d_agg, ctx->d_agg_vals};
+                  ctx->d_head_extra, ctx->d_dead, ctx->d_stub_block, ctx->d_acc_total};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
@@ -742,21 +727,13 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   const uint32_t ns = ctx->cfg.max_cpus;
   const size_t nc = ctx->chunks.size();
   const bool force_exact = (ctx->cfg.flags & HBTGPU_F_FORCE_EXACT) != 0;
-  // Fast path: every bucket is written once, by plain stores, and derived where it is written
-  // (k_decode<..., STORE> + k_stitch): the accumulator is neither zeroed nor read again.  The
-  // exact path (and groups too wide for the open sums to fit beside the tile) keeps the REDs
-  // into a zeroed accumulator and the separate derive pass.
-  const bool store = !force_exact && ctx->cfg.n_events + 3 <= STORE_MAX_F;
   uint32_t launches = 0;
   Params P = make_params(ctx);
 
-  if (ctx->d2h_pending) {  // the result tensors may still be copied out
-    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));
-    ctx->d2h_pending = false;
-  }
+  if (ctx->d2h_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));  // acc may still be copied out
   CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
   CK(cudaMemsetAsync(ctx->d_counters, 0, ns * C_SLOTS * 8, ctx->stream));
-  if (!store) CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
   CK(cudaMemsetAsync(ctx->d_flags, force_exact ? 1 : 0, 1, ctx->stream));  // byte 0 of NEED_EXACT
   CK(cudaMemsetAsync(reinterpret_cast<uint8_t*>(ctx->d_flags) + 1, 0, FLAG_COUNT * 4 - 1, ctx->stream));
   const bool external = (ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY) != 0;
@@ -774,55 +751,33 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
                      cudaMemcpyDeviceToDevice, ctx->stream));
   ctx->derived = false;
   ctx->acc_cur = ctx->d_acc;
-  const DeriveParams D = derive_params(ctx);
   const bool timed = ctx->ev_pending < hbtgpu_ctx::kEvRing;
-  const unsigned g = static_cast<unsigned>(nc);
-  if (nc || store) {
+  if (nc) {
     if (timed) CK(cudaEventRecord(ctx->ev_dec0[ctx->ev_pending], ctx->stream));
-    if (nc && store) {
-      if (P.pre) k_decode<true, MODE_AGG, 2, 0, true><<<g, NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P, D);
-      else if (P.n_events == 8) k_decode<true, MODE_AGG, 0, 8, true><<<g, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P, D);
-      else if (P.n_events == 4) k_decode<true, MODE_AGG, 0, 4, true><<<g, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P, D);
-      else k_decode<true, MODE_AGG, 0, 0, true><<<g, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P, D);
-      ++launches;
-    } else if (nc && !force_exact) {
-      if (P.pre) k_decode<true, MODE_AGG, 2><<<g, NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P, D);
-      else if (P.n_events == 8) k_decode<true, MODE_AGG, 0, 8><<<g, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P, D);
-      else if (P.n_events == 4) k_decode<true, MODE_AGG, 0, 4><<<g, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P, D);
-      else k_decode<true, MODE_AGG, 0><<<g, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P, D);
+    if (!force_exact) {
+      if (P.pre) k_decode<true, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P);
+      else if (P.n_events == 8) k_decode<true, MODE_AGG, 0, 8><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
+      else if (P.n_events == 4) k_decode<true, MODE_AGG, 0, 4><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
+      else k_decode<true, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
       ++launches;
     }
     if (timed) CK(cudaEventRecord(ctx->ev_dec1[ctx->ev_pending++], ctx->stream));
-    if (store) {
-      // one warp per chunk, one per stream (streams without images are filled here)
-      const size_t warps = nc + ns;
-      k_stitch<<<static_cast<unsigned>((warps * 32 + STITCH_THREADS - 1) / STITCH_THREADS), STITCH_THREADS, 0, ctx->stream>>>(P, D);
-      ++launches;
-    } else if (nc && !force_exact) {
+    if (!force_exact) {
       k_verify<<<static_cast<unsigned>((nc + 255) / 256), 256, 0, ctx->stream>>>(P);
       ++launches;
     }
-    if (nc) {
-      k_resolve<<<ns, RES_THREADS, 0, ctx->stream>>>(P);
-      k_clear<<<148 * 4, 256, 0, ctx->stream>>>(P, force_exact ? 0 : ctx->acc_words);
-      if (P.pre) k_decode<false, MODE_AGG, 2><<<g, NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P, D);
-      else k_decode<false, MODE_AGG, 0><<<g, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P, D);
-      launches += 3;
-    }
+    k_resolve<<<ns, RES_THREADS, 0, ctx->stream>>>(P);
+    k_clear<<<148 * 4, 256, 0, ctx->stream>>>(P, force_exact ? 0 : ctx->acc_words);
+    if (P.pre) k_decode<false, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P);
+    else k_decode<false, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
+    launches += 3;
     CK(cudaGetLastError());
   }
   if (external) {
     k_head<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(P);
     CK(cudaGetLastError());
     ++launches;
-  }
-  if (store) {
-    // only if the fast path was refuted: derive what the exact path recomputed
-    k_derive_if_exact<<<148 * 8, 256, 0, ctx->stream>>>(D, ctx->d_flags);
-    CK(cudaGetLastError());
-    ++launches;
-    ctx->derived = true;
-  } else if (!external) {
+  } else {
     if (int r = launch_derive(ctx)) return r;
     ++launches;
   }
@@ -1499,14 +1454,14 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
     if (force_exact) NCK(cudaMemsetAsync(&sc->flags[FLAG_NEED_EXACT], 1, 1, st));
     if (!force_exact) {
       // the same kernels hbtgpu_run launches: the builds specialised for 8- and 4-event groups where they apply
-      if (n == 8) k_decode<true, MODE_AGG, 0, 8><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P, DeriveParams{});
-      else if (n == 4) k_decode<true, MODE_AGG, 0, 4><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P, DeriveParams{});
-      else k_decode<true, MODE_AGG, 0><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P, DeriveParams{});
+      if (n == 8) k_decode<true, MODE_AGG, 0, 8><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
+      else if (n == 4) k_decode<true, MODE_AGG, 0, 4><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
+      else k_decode<true, MODE_AGG, 0><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
       k_verify<<<(nc + 255) / 256, 256, 0, st>>>(P);
     }
     k_resolve<<<1, RES_THREADS, 0, st>>>(P);
     k_clear<<<148 * 4, 256, 0, st>>>(P, force_exact ? 0 : acc_words);
-    k_decode<false, MODE_AGG, 0><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P, DeriveParams{});
+    k_decode<false, MODE_AGG, 0><<<nc, NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), st>>>(P);
   }
   NCK(cudaGetLastError());
 

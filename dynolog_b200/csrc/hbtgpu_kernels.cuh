@@ -92,8 +92,7 @@ enum { FLAG_NEED_EXACT = 0, FLAG_INTERNAL = 1, FLAG_WHY = 2, FLAG_WHERE = 3, FLA
 enum : uint32_t {
   WHY_HALO_NO_START = 1, WHY_HALO_DEAD = 2, WHY_HALO_ERR = 3, WHY_HALO_NO_SAMPLE = 4,
   WHY_IMAGE_SEAM = 5, WHY_TILE_DEAD = 6, WHY_TILE_ERR = 7, WHY_PAST_END = 8,
-  WHY_V_ENTRY = 10, WHY_V_PRED = 11, WHY_V_GAP = 12, WHY_V_IMAGE_END = 13, WHY_V_FIRST = 14,
-  WHY_BACKWARDS = 20, WHY_V_BUCKET = 21
+  WHY_V_ENTRY = 10, WHY_V_PRED = 11, WHY_V_GAP = 12, WHY_V_IMAGE_END = 13, WHY_V_FIRST = 14
 };
 
 __device__ __forceinline__ void raise_exact(uint32_t* flags, uint32_t why, uint32_t where) {
@@ -155,16 +154,6 @@ struct HeadExtra {
   uint64_t records, lost, throttle, unthrottle, read;
 };
 
-// Per chunk, plain-store aggregation (k_decode<..., STORE>): what the chunk could not finish by
-// itself.  Buckets are addressed by SLOT = bucket + 1; slot 0 = no bucket (no predecessor, or a
-// time before t0), slot n_buckets + 1 = behind the range.
-struct ChunkAgg {
-  uint32_t hb;           // slot of the bucket that is open on entry (the predecessor SAMPLE's)
-  uint32_t tb;           // slot of the bucket that is open on exit (the last SAMPLE's)
-  uint32_t closed_head;  // the chunk met a later bucket: vals[0] (H) = its share of slot hb
-  uint32_t backwards;    // a bucket transition went back in time (possible behind a LOST): exact path
-};
-
 struct Params {
   const uint8_t* arena;
   const ChunkDesc* chunks;
@@ -177,8 +166,6 @@ struct Params {
   struct HeadExtra* head_extra;  // shard mode: what the walk met before the first SAMPLE
   uint64_t* counters;  // [stream][C_SLOTS]
   uint64_t* acc;       // [stream][bucket][F]
-  ChunkAgg* agg;       // STORE: [chunk]
-  uint64_t* agg_vals;  // STORE: [chunk][2][F]: H (share of slot hb), T (share of slot tb)
   uint32_t* flags;
   uint64_t* rows;      // MODE_EMIT
   uint64_t* rec_off;   // MODE_EMIT
@@ -332,10 +319,6 @@ struct __align__(128) Smem {
   uint32_t idx_n, idx_end, idx_gap, idx_bad, idx_other;  // index_tile: samples listed, chain position after the tile,
                                               // a LOST after the last sample, word of a record consume() stalls on
   uint32_t tile_err;
-  // STORE: bucket transitions / samples without a row, one bit per lane and warp (uniform_segment),
-  // and the state of the chunk: is its head bucket still open, did time go backwards
-  uint32_t tmask[NWARP], gmask[NWARP];
-  uint32_t head_open, backwards, agg_hb;
   uint32_t cnt[C_SLOTS];          // chunk-local counters (u32), lost is u64 below
   unsigned long long lost_sum;
 };
@@ -621,18 +604,6 @@ __device__ __forceinline__ uint32_t bucket_of(const Params& P, uint64_t ts) {
   return static_cast<uint32_t>(q);
 }
 
-// slot = bucket + 1; 0 in front of the range, n_buckets + 1 behind it
-__device__ __forceinline__ uint32_t slot_of_bucket(const Params& P, uint32_t bk, uint64_t ts) {
-  return bk != BKT_OOR ? bk + 1 : (ts < P.t0 ? 0u : P.n_buckets + 1);
-}
-__device__ __forceinline__ uint32_t slot_of(const Params& P, uint64_t ts) { return slot_of_bucket(P, bucket_of(P, ts), ts); }
-// STORE: the open partial sums (two copies, like the carry) live in s.next, which only the halo
-// scout and the row emission use: F <= STORE_MAX_F words each
-constexpr uint32_t STORE_MAX_F = MAXC * 2 / 8 / 2;  // 48
-__device__ __forceinline__ uint64_t* open_partial(Smem& s, uint32_t which) {
-  return reinterpret_cast<uint64_t*>(s.next) + which * STORE_MAX_F;
-}
-
 __device__ __forceinline__ uint64_t xform(const Params& P, uint32_t e, uint64_t v) {
   if (P.tsc_mask == 0) return v;  // uniform: no event is transformed (the usual case)
   return ((P.tsc_mask >> e) & 1ull) ? tsc_to_ktime(v, P.time_shift, P.time_mult, P.time_zero) : v;
@@ -766,65 +737,6 @@ __device__ __forceinline__ void attr_cache_flush(const Params& P) {
     if (A.tid_key[i] != ATTR_EMPTY) attr_global<false>(P, A.tid_key[i], A.tid_cnt[i]);
 }
 
-// ------------------------------------------------------------------------------------
-// k_derive: per (cpu,bucket): scaled = getCount(acc), metrics = reducers(scaled)
-struct DeriveParams {
-  const uint64_t* acc;
-  uint64_t* scaled;
-  double* metric;
-  uint32_t* valid;
-  uint64_t n_cells;  // cpus * buckets
-  uint32_t n_events, n_metrics;
-  uint64_t n_magic;  // ceil(2^32 / n_events): x / n == (x * n_magic) >> 32 for x < 2^16
-  hbtgpu_metric metrics[HBTGPU_MAX_METRICS];
-};
-
-__device__ __forceinline__ double add_reduce_int(const uint64_t* v, uint32_t k) {
-  // std::accumulate(begin, end, 0): int accumulator (BuiltinMetrics.cpp:94)
-  int32_t acc = 0;
-  for (uint32_t i = 0; i < k; ++i)
-    acc = static_cast<int32_t>(static_cast<uint32_t>(static_cast<uint64_t>(static_cast<int64_t>(acc)) + v[i]));
-  return static_cast<double>(acc);
-}
-
-// metrics of one cell from its scaled counts `sc` (any address space) and accumulated time_running
-__device__ __forceinline__ uint32_t derive_metrics(const DeriveParams& D, const uint64_t* sc, uint64_t tr,
-                                                   double* out_row) {
-  uint32_t vmask = 0;
-  for (uint32_t m = 0; m < D.n_metrics; ++m) {
-    const hbtgpu_metric& md = D.metrics[m];
-    double out = 0.0;
-    bool ok = false;
-    if (md.kind == HBTGPU_METRIC_RATE) {
-      // getRateReducer: exactly two values, denominator != 0 (BuiltinMetrics.cpp:104-116)
-      if (md.n_idx == 2) {
-        const uint64_t num = sc[md.idx[0]], den = sc[md.idx[1]];
-        if (den != 0) {
-          out = __ddiv_rn(__ull2double_rn(num), __ull2double_rn(den));
-          ok = true;
-        }
-      }
-    } else if (md.kind == HBTGPU_METRIC_ADD) {
-      if (md.n_idx > 0) {
-        uint64_t v[HBTGPU_MAX_METRIC_EVENTS];
-        for (uint32_t k = 0; k < md.n_idx; ++k) v[k] = sc[md.idx[k]];
-        out = add_reduce_int(v, md.n_idx);
-        ok = true;
-      }
-    } else if (md.kind == HBTGPU_METRIC_PER_SECOND_MEGA) {
-      // float(double(count) * 1e3 / double(time_running)) (PerfMonitor.cpp:63-66)
-      const double c = __ull2double_rn(sc[md.idx[0]]);
-      const float f = __double2float_rn(__ddiv_rn(__dmul_rn(c, 1e3), __ull2double_rn(tr)));
-      out = static_cast<double>(f);
-      ok = true;
-    }
-    out_row[m] = out;
-    if (ok) vmask |= 1u << m;
-  }
-  return vmask;
-}
-
-
 struct TileCtx {
   uint64_t tile_abs;    // arena offset of word 0 of the buffer
   uint64_t stream_off;  // stream byte offset of word 0 of the buffer
@@ -832,7 +744,6 @@ struct TileCtx {
   uint32_t rows_before, recs_before;  // MODE_EMIT: already emitted in this chunk
   uint64_t row_base, rec_base;
   uint64_t* acc_s;      // MODE_AGG: accumulator records of this stream (computed once per chunk)
-  uint32_t chunk;       // STORE: this chunk's index (ChunkAgg / agg_vals)
 };
 
 // Decode the reachable records of one staged tile and fold them into the carry, the
@@ -1290,7 +1201,7 @@ __host__ __device__ constexpr size_t decode_smem_bytes(uint32_t tile_bytes) {
 
 // IDX: the records are the s.idx_n samples index_tile listed (MODE_AGG only): positions from
 // s.pos, s.fl[j] = a LOST lies before sample j; they are valid by construction, so no vote.
-template <int MODE, int PRE, int NEV, bool IDX = false, bool STORE = false>
+template <int MODE, int PRE, int NEV, bool IDX = false>
 __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, const uint64_t* buf,
                                                     uint32_t wt, uint32_t entry, TileCtx& tc,
                                                     uint32_t cur, uint32_t& k_all) {
@@ -1319,7 +1230,6 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
 
   // pass 1: check every record, compute its bucket
   uint32_t bk_[MAXG];
-  uint32_t slot = 0;            // STORE: slot (bucket + 1) of this lane's record; the carry's for record -1
   int first_bad = 0x7FFFFFFF;   // first record index that is not such a SAMPLE (this lane's view)
   int regress = 0x7FFFFFFF;     // first record index whose row would go back in time
 #pragma unroll
@@ -1338,32 +1248,13 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
       const bool mismatch = ((hd & 0xFFFF0000FFFFFFFFull) != want) | (nr != n);
       if (!IDX && lane < 31 && mismatch) first_bad = min(first_bad, jr);
       bk_[g] = bucket_of(P, ts);
-      if (STORE) slot = slot_of_bucket(P, bk_[g], ts);
     } else if (jr == -1) {
       ts = C.ts;
-      if (STORE) slot = C.valid ? slot_of(P, ts) : 0u;
     }
     const uint64_t nts = __shfl_down_sync(0xffffffffu, ts, 1);
     // row jr+1 exists and goes back in time (gen :156-163)
     if (lane < 31 && jr + 1 < K && (jr >= 0 || link0) && !gapof(jr + 1) && ts > nts) regress = min(regress, jr + 1);
   }
-  // STORE: where does the bucket change (pair jr | jr+1), which samples have no row -- one bit per
-  // lane, published per warp so that a lane can look across the whole tile
-  uint32_t slot_next = 0, tm = 0;
-  const bool head_open = STORE && s.head_open != 0;  // read here: cleared behind the barrier below
-  auto publish_masks = [&]() {
-    const int jr = warp * OWN - 1 + lane;
-    slot_next = __shfl_down_sync(0xffffffffu, slot, 1);
-    const bool trans = lane < 31 && jr + 1 < K && slot != slot_next;
-    const bool norow = lane < 31 && jr >= 0 && jr < K && ((jr == 0 && !link0) || gapof(jr));
-    tm = __ballot_sync(0xffffffffu, trans);
-    const uint32_t gm = __ballot_sync(0xffffffffu, norow);
-    if (lane == 0) {
-      s.tmask[warp] = tm;
-      s.gmask[warp] = gm;
-    }
-  };
-  if (STORE) publish_masks();
   if (!IDX && !__syncthreads_and(first_bad == 0x7FFFFFFF)) {
     // not uniform to the end: agree on the first record that breaks the run
     if (threadIdx.x == 0) s.red_key = static_cast<uint32_t>(Kall);
@@ -1373,13 +1264,8 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
     K = static_cast<int>(s.red_key);
     __syncthreads();  // red_key may be reused right away
     if (K == 0) return 0;
-    if (STORE) {  // the run is shorter than assumed: the masks again, for the records that are committed
-      publish_masks();
-      __syncthreads();
-    }
   }
   if (IDX && K == 0) return 0;
-  if (IDX && STORE) __syncthreads();  // (the plain path's vote above is the barrier behind publish_masks)
   if (regress < K) atomicMin(&s.tile_err, posof(regress));
 
   if (MODE == MODE_EMIT) {
@@ -1475,128 +1361,9 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
   uint64_t* const acc_s = tc.acc_s;                       // this stream's accumulator records
   uint64_t* const acc_lane = acc_s + e0;                  // ... and this lane's field in bucket 0
   const bool lane_tsc = any_tsc && e0 < n && ((P.tsc_mask >> e0) & 1ull);  // field e0 is transformed
-  if (STORE) {
-    // ---- plain stores: every bucket that closes inside the tile is complete ----------------
-    // Samples j = 0..K-1 (record -1 = the carry); D_j = V_j - V_{j-1} is sample j's row, 0 if the
-    // row does not exist.  A bucket covers a run of consecutive samples; its sum is
-    // V_q - V_p - (the D of its rowless samples), p | p+1 and q | q+1 being the pairs where the
-    // bucket changes.  The bucket that is open when the tile starts also has s.P (what earlier
-    // tiles of the chunk saw of it); the chunk's first bucket goes to agg_vals (its beginning lies
-    // in an earlier chunk), every other one is stored where the result lives.  Buckets skipped
-    // between two samples are stored as zeros.  The new open sum goes to the other copy of s.P.
-    const int j0 = warp * OWN - 1;
-    const int jr = j0 + lane;
-    const uint64_t* const Pold = open_partial(s, cur);
-    uint64_t* const Pnew = open_partial(s, cur ^ 1);
-    uint32_t gm_all = 0;
-#pragma unroll
-    for (int w = 0; w < NWARP; ++w) gm_all |= s.gmask[w];
-    // value of field e of record j (-1: the carry)
-    auto field = [&](int j, uint32_t e, uint32_t woff, bool tsc) -> uint64_t {
-      if (e == n + 2) return static_cast<uint64_t>(static_cast<int64_t>(j));  // ordinal
-      if (j < 0) return e < n ? C.last[e] : (e == n ? C.te : C.tr);
-      uint64_t v = buf[posof(j) + woff];
-      if (tsc) v = xform(P, e, v);
-      return v;
-    };
-    // sum of D over the rowless samples in [from, to] of field e
-    auto rowless_sum = [&](int from, int to, uint32_t e, uint32_t woff, bool tsc) -> uint64_t {
-      uint64_t c = 0;
-      if (gm_all == 0) return 0;
-      for (int w = 0; w < NWARP; ++w) {
-        uint32_t m = s.gmask[w];
-        while (m) {
-          const int g = w * OWN - 1 + (__ffs(m) - 1);
-          m &= m - 1;
-          if (g >= from && g <= to) c += field(g, e, woff, tsc) - field(g - 1, e, woff, tsc);
-        }
-      }
-      return c;
-    };
-    // the pair in front of this lane's pair where the bucket changed (-2: none in this tile)
-    int prev = -2;
-    const bool trans = (tm >> lane) & 1u;
-    if (trans && slot_next < slot) s.backwards = 1;  // only possible behind a LOST: the exact path takes over
-    if (trans) {
-      const uint32_t below = tm & ((1u << lane) - 1u);
-      if (below) {
-        prev = j0 + (31 - __clz(below));
-      } else {
-        for (int w = warp - 1; w >= 0; --w) {
-          const uint32_t mw = s.tmask[w];
-          if (mw) {
-            prev = w * OWN - 1 + (31 - __clz(mw));
-            break;
-          }
-        }
-      }
-    }
-    // rows that fall outside the bucket range are only counted
-    {
-      const bool rowA = (jr >= 1 || (jr == 0 && link0)) && !gapof(jr);
-      n_oor += __popc(__ballot_sync(0xffffffffu, lane < 31 && jr >= 0 && jr < K && rowA &&
-                                                    (slot == 0 || slot == P.n_buckets + 1)));
-    }
-    const bool two = F <= 16;
-    const uint32_t e0 = two ? (lane & 15) : lane;
-    uint32_t mask = tm;
-    while (mask) {
-      int src = __ffs(mask) - 1;
-      mask &= mask - 1;
-      if (two) {
-        const int b1 = mask ? __ffs(mask) - 1 : -1;
-        mask &= mask - 1;
-        if (lane >= 16) src = b1;
-      }
-      const int srcl = src < 0 ? 0 : src;
-      const uint32_t S = __shfl_sync(0xffffffffu, slot, srcl);
-      const uint32_t Sn = __shfl_sync(0xffffffffu, slot_next, srcl);
-      const int pv = __shfl_sync(0xffffffffu, prev, srcl);
-      if (src >= 0) {
-        const int q = j0 + src;
-        const bool first = pv == -2;             // the bucket was open when the tile started
-        const bool to_head = first && head_open;  // ... and when the chunk started
-        const bool real = S >= 1 && S <= P.n_buckets;
-        for (uint32_t e = e0; e < F; e += (two ? 16u : 32u)) {
-          if (real) {
-            const uint32_t woff = pre + (e < n ? 5 + e : (e == n ? 3 : 4));
-            const bool tsc = any_tsc && e < n && ((P.tsc_mask >> e) & 1ull);
-            const uint64_t v = (first ? Pold[e] : 0ull) + field(q, e, woff, tsc) - field(first ? -1 : pv, e, woff, tsc) -
-                               rowless_sum(first ? 0 : pv + 1, q, e, woff, tsc);
-            if (to_head) P.agg_vals[(static_cast<uint64_t>(tc.chunk) * 2) * F + e] = v;
-            else tc.acc_s[static_cast<uint64_t>(S - 1) * F + e] = v;
-          }
-        }
-        // buckets nobody has a row for
-        if (Sn > S + 1) {
-          const uint64_t w0 = static_cast<uint64_t>(S) * F;  // first word of slot S + 1
-          const uint64_t w1 = static_cast<uint64_t>(Sn - 1 < P.n_buckets ? Sn - 1 : P.n_buckets) * F;
-          for (uint64_t w = w0 + e0; w < w1; w += (two ? 16u : 32u)) tc.acc_s[w] = 0;
-        }
-      }
-    }
-    // the bucket that stays open, and the chunk's head
-    if (warp == NWARP - 1) {
-      int last = -2;
-      for (int w = NWARP - 1; w >= 0; --w) {
-        const uint32_t mw = s.tmask[w];
-        if (mw) {
-          last = w * OWN - 1 + (31 - __clz(mw));
-          break;
-        }
-      }
-      for (uint32_t e = lane; e < F; e += 32) {
-        const uint32_t woff = pre + (e < n ? 5 + e : (e == n ? 3 : 4));
-        const bool tsc = any_tsc && e < n && ((P.tsc_mask >> e) & 1ull);
-        Pnew[e] = (last == -2 ? Pold[e] : 0ull) + field(K - 1, e, woff, tsc) - field(last == -2 ? -1 : last, e, woff, tsc) -
-                  rowless_sum(last == -2 ? 0 : last + 1, K - 1, e, woff, tsc);
-      }
-      if (lane == 0 && last != -2) s.head_open = 0;  // (read above by everybody before the tile's last barrier)
-    }
-  }
 #pragma unroll
   for (int g = 0; g < MAXG; ++g) {
-    if (MODE != MODE_AGG || STORE) break;
+    if (MODE != MODE_AGG) break;
     const int j0 = (g * NWARP + warp) * OWN - 1;
     if (j0 >= K) break;
     const int jr = j0 + lane;
@@ -1751,43 +1518,8 @@ __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t st
 #ifndef HBT_MINB
 #define HBT_MINB 5
 #endif
-// In-kernel derive of a run of cells this chunk has stored (STORE): the sums are read back
-// through L2 into a tile buffer with coalesced loads, one thread scales one cell, the scaled
-// counts leave coalesced.  cells [first, first + count) of one stream; all threads call it.
-__device__ __forceinline__ void derive_run(const DeriveParams& D, const uint64_t* acc_s, uint64_t cell0_global,
-                                           uint64_t first, uint64_t count, uint64_t* stage, uint32_t stage_words) {
-  const uint32_t n = D.n_events, F = n + 3;
-  const uint32_t batch = min(static_cast<uint32_t>(NT), stage_words / F);
-  for (uint64_t c0 = 0; c0 < count; c0 += batch) {
-    const uint32_t cnt = static_cast<uint32_t>(umin64(batch, count - c0));
-    const uint64_t* src = acc_s + (first + c0) * F;
-    for (uint32_t i = threadIdx.x; i < cnt * F; i += NT) stage[i] = __ldcg(src + i);
-    __syncthreads();
-    if (threadIdx.x < cnt) {
-      uint64_t* a = stage + threadIdx.x * F;
-      const uint64_t te = a[n], tr = a[n + 1];
-      for (uint32_t e = 0; e < n; ++e) a[e] = get_count(a[e], te, tr);
-      const uint64_t i = cell0_global + first + c0 + threadIdx.x;
-      D.valid[i] = derive_metrics(D, a, tr, D.metric + i * D.n_metrics);
-    }
-    __syncthreads();
-    uint64_t* dst = D.scaled + (cell0_global + first + c0) * n;
-    for (uint32_t o = threadIdx.x; o < cnt * n; o += NT) {
-      const uint32_t c = static_cast<uint32_t>((static_cast<uint64_t>(o) * D.n_magic) >> 32);  // o / n, o < 2^16
-      dst[o] = stage[c * F + (o - c * n)];
-    }
-    __syncthreads();
-  }
-}
-
-// STORE (SPEC && MODE_AGG only): aggregate with plain stores and derive in the kernel -- no
-// zeroed accumulator, no separate derive pass (see uniform_segment and k_stitch).  Without it
-// the sums are formed with REDs into a zeroed accumulator (the exact path, the no-alloc entry
-// point, groups of more than STORE_MAX_F - 3 events).
-template <bool SPEC, int MODE, int PRE, int NEV = 0, bool STORE = false>
-__global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_MINB) k_decode(const Params P,
-                                                                                             const DeriveParams D) {
-  static_assert(!STORE || (SPEC && MODE == MODE_AGG), "STORE is a variant of the speculative aggregation pass");
+template <bool SPEC, int MODE, int PRE, int NEV = 0>
+__global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_MINB) k_decode(const Params P) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   if (!SPEC && MODE == MODE_AGG && P.flags[FLAG_NEED_EXACT] == 0) return;  // exact pass not needed
@@ -1944,24 +1676,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
   // record can leave it by at most 64 KiB)
   const uint64_t chunk_end_abs = min(cd.img_base + cd.end, limit_abs);
   TileCtx tc{0, 0, cd.stream, 0, 0, io.row_base, io.rec_base,
-             P.acc + static_cast<uint64_t>(cd.stream) * P.n_buckets * (P.n_events + 3), c};
-  if (STORE) {
-    // the bucket of the predecessor SAMPLE is open; what this chunk sees of it starts at zero.
-    // A stream's first chunk also owns the buckets in front of it: nobody has a row for them.
-    const uint32_t F = P.n_events + 3;
-    const uint32_t hb = s.c[0].valid ? slot_of(P, s.c[0].ts) : 0u;
-    for (uint32_t e = threadIdx.x; e < F; e += NT) open_partial(s, 0)[e] = 0;
-    if (threadIdx.x == 0) {
-      s.head_open = 1;
-      s.backwards = 0;
-      s.agg_hb = hb;
-    }
-    if ((cd.flags & CH_FIRST_OF_STREAM) && hb > 1) {
-      const uint64_t w1 = static_cast<uint64_t>(hb - 1 < P.n_buckets ? hb - 1 : P.n_buckets) * F;
-      for (uint64_t w = threadIdx.x; w < w1; w += NT) tc.acc_s[w] = 0;
-    }
-    __syncthreads();
-  }
+             P.acc + static_cast<uint64_t>(cd.stream) * P.n_buckets * (P.n_events + 3)};
   const bool any_work = entry_abs < chunk_end_abs;  // also false for exact-mode "skip" (~0)
   const uint32_t chunk_len = any_work ? static_cast<uint32_t>(chunk_end_abs - chunk_abs) : 0;
   const uint32_t limit_rel = static_cast<uint32_t>(umin64(limit_abs - chunk_abs, 0xFFFFFFF0ull));
@@ -2004,7 +1719,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
           // only prove the records up to the first other one)
           if (!(MODE == MODE_AGG && mixed_prev)) {
             uint32_t k_all = 0;
-            const uint32_t k = uniform_segment<MODE, PRE, NEV, false, STORE>(s, P, buf, wt, ew, tc, cur, k_all);
+            const uint32_t k = uniform_segment<MODE, PRE, NEV>(s, P, buf, wt, ew, tc, cur, k_all);
             if (k) cur ^= 1;
             ew += k * S;
             if (k == k_all) {  // ran to the end of the tile
@@ -2018,7 +1733,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
             // one pass over the listed samples, however many other records lie in between
             index_tile<PRE, NEV>(s, P, buf, wt, ew, cur);
             uint32_t n_idx = 0;
-            const uint32_t ki = uniform_segment<MODE, PRE, NEV, true, STORE>(s, P, buf, wt, ew, tc, cur, n_idx);
+            const uint32_t ki = uniform_segment<MODE, PRE, NEV, true>(s, P, buf, wt, ew, tc, cur, n_idx);
             if (ki) cur ^= 1;
             ew = s.idx_end;
             mixed_prev = s.idx_other != 0;
@@ -2057,7 +1772,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
             // one aggregation routine for every path: list the samples, then the indexed pass
             list_tile<PRE>(s, P, sb, K, cur);
             uint32_t n_idx = 0;
-            const uint32_t ki = uniform_segment<MODE, PRE, NEV, true, STORE>(s, P, sb, wh, 0, tc, cur, n_idx);
+            const uint32_t ki = uniform_segment<MODE, PRE, NEV, true>(s, P, sb, wh, 0, tc, cur, n_idx);
             if (ki) cur ^= 1;
             __syncthreads();  // the new carry and s.tile_err are published
           } else {
@@ -2090,27 +1805,6 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
   __syncthreads();
   if (MODE == MODE_AGG && PRE == 2) attr_cache_flush(P);
   const Carry& C = s.c[cur];
-  if (STORE) {
-    // what is left open goes to k_stitch; everything this chunk stored is derived here, while
-    // the sums are still in L2
-    const uint32_t F = P.n_events + 3;
-    const uint32_t hb = s.agg_hb, tb = C.valid ? slot_of(P, C.ts) : 0u;
-    const bool closed = s.head_open == 0;
-    for (uint32_t e = threadIdx.x; e < F; e += NT) P.agg_vals[(static_cast<uint64_t>(c) * 2 + 1) * F + e] = open_partial(s, cur)[e];
-    if (threadIdx.x == 0) P.agg[c] = ChunkAgg{hb, tb, closed ? 1u : 0u, s.backwards};
-    const uint64_t cell0 = static_cast<uint64_t>(cd.stream) * P.n_buckets;
-    const uint32_t stage_words = 2 * stage_bytes / 8;  // both tile buffers
-    const uint32_t nb = P.n_buckets;
-    if (!bad && !s.backwards) {
-      // slots [1, hb - 1] of a stream's first chunk, slots [hb + 1, tb - 1] once the head is closed
-      if ((cd.flags & CH_FIRST_OF_STREAM) && hb > 1)
-        derive_run(D, tc.acc_s, cell0, 0, (hb - 1 < nb ? hb - 1 : nb), data0, stage_words);
-      if (closed && tb > hb + 1 && hb < nb) {
-        const uint64_t last = tb - 1 < nb ? tb - 1 : nb;  // last slot to derive
-        if (last >= hb + 1) derive_run(D, tc.acc_s, cell0, hb, last - hb, data0, stage_words);
-      }
-    }
-  }
   if (threadIdx.x == 0) {
     io.out_exit = next_abs;
     io.out_last = C.last_off;
@@ -2170,126 +1864,6 @@ __global__ void k_verify(const Params P) {
   if (!why && (cd.flags & CH_LAST_OF_IMAGE) && io.out_exit != cd.img_base + cd.img_len)
     why = WHY_V_IMAGE_END;
   if (why) raise_exact(P.flags, why, c);
-}
-
-// ------------------------------------------------------------------------------------
-// k_stitch (STORE): k_verify's induction plus the cells no chunk could finish by itself.  One
-// warp per chunk c, and one per stream for streams without any chunk:
-//   * verify c against c-1 exactly as k_verify does;
-//   * if c closed its head bucket (slot hb): that cell = H(c) + T(c-1) + T(c-2) + ... back to the
-//     first chunk that closed its own head (chunks that lie inside one bucket pass it through);
-//   * if c is the stream's last chunk: the bucket open at its end likewise, and every bucket
-//     behind it is empty;
-//   * the cells are derived on the spot.
-// A stream whose chunks' buckets do not line up (hb(c) != tb(c-1): a refuted speculation) or in
-// which time went backwards raises NEED_EXACT; the exact path then recomputes everything.
-constexpr int STITCH_THREADS = 128;
-
-__device__ __forceinline__ void derive_cell(const DeriveParams& D, uint64_t i) {
-  const uint32_t n = D.n_events;
-  const uint64_t* a = D.acc + i * (n + 3);
-  const uint64_t te = __ldcg(a + n), tr = __ldcg(a + n + 1);
-  uint64_t* sc = D.scaled + i * n;
-  for (uint32_t e = 0; e < n; ++e) sc[e] = get_count(__ldcg(a + e), te, tr);
-  D.valid[i] = derive_metrics(D, sc, tr, D.metric + i * D.n_metrics);
-}
-
-// empty cells [first, first + count) of stream `stream`: zero sums and what derives from them
-__device__ __forceinline__ void fill_empty_cells(const Params& P, const DeriveParams& D, uint32_t stream, uint64_t first,
-                                                 uint64_t count, uint32_t lane) {
-  if (count == 0) return;
-  const uint32_t n = P.n_events, F = n + 3;
-  const uint64_t cell0 = static_cast<uint64_t>(stream) * P.n_buckets + first;
-  uint64_t* acc = P.acc + cell0 * F;
-  for (uint64_t w = lane; w < count * F; w += 32) acc[w] = 0;
-  uint64_t* sc = D.scaled + cell0 * n;
-  for (uint64_t w = lane; w < count * n; w += 32) sc[w] = 0;  // getCount: 0 if time_enabled == 0 (:468)
-  // the metrics of an all-zero cell are the same for every such cell: computed once per lane
-  uint64_t zero[HBTGPU_MAX_EVENTS];
-  double m0[HBTGPU_MAX_METRICS];
-  for (uint32_t e = 0; e < n; ++e) zero[e] = 0;
-  const uint32_t v0 = derive_metrics(D, zero, 0, m0);
-  for (uint64_t i = lane; i < count; i += 32) {
-    D.valid[cell0 + i] = v0;
-    for (uint32_t m = 0; m < D.n_metrics; ++m) D.metric[(cell0 + i) * D.n_metrics + m] = m0[m];
-  }
-}
-
-__global__ void __launch_bounds__(STITCH_THREADS) k_stitch(const Params P, const DeriveParams D) {
-  const uint32_t w = (blockIdx.x * STITCH_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  const uint32_t n = P.n_events, F = n + 3, nb = P.n_buckets;
-  if (w >= P.n_chunks) {
-    // a stream nobody submitted an image for: all its cells are empty
-    const uint32_t sidx = w - P.n_chunks;
-    if (sidx < P.n_streams && P.streams[sidx].n_images == 0) fill_empty_cells(P, D, sidx, 0, nb, lane);
-    return;
-  }
-  const uint32_t c = w;
-  const ChunkDesc cd = P.chunks[c];
-  const ChunkIO& io = P.io[c];
-  const ChunkAgg ag = P.agg[c];
-  const bool first_of_stream = (cd.flags & CH_FIRST_OF_STREAM) != 0;
-  uint32_t why = 0;
-  if (first_of_stream) {
-    if (!(io.in_entry == cd.img_base + cd.begin && io.in_pred == PRED_CARRY_IN && io.in_gap == 0))
-      why = WHY_V_FIRST;
-  } else {
-    const ChunkDesc pd = P.chunks[c - 1];
-    const ChunkIO& pio = P.io[c - 1];
-    if (cd.flags & CH_FIRST_OF_IMAGE) {
-      if (!(pio.out_exit == pd.img_base + pd.img_len && io.in_entry == cd.img_base)) why = WHY_V_ENTRY;
-    } else if (pio.out_exit != io.in_entry) {
-      why = WHY_V_ENTRY;
-    }
-    if (!why && pio.out_last != io.in_pred) why = WHY_V_PRED;
-    if (!why && pio.out_gap != io.in_gap) why = WHY_V_GAP;
-    if (!why && P.agg[c - 1].tb != ag.hb) why = WHY_V_BUCKET;
-  }
-  if (!why && (cd.flags & CH_LAST_OF_IMAGE) && io.out_exit != cd.img_base + cd.img_len)
-    why = WHY_V_IMAGE_END;
-  if (!why && ag.backwards) why = WHY_BACKWARDS;
-  if (why) {
-    if (lane == 0) raise_exact(P.flags, why, c);
-    return;  // the exact path recomputes every cell
-  }
-  uint64_t* acc_s = P.acc + static_cast<uint64_t>(cd.stream) * nb * F;
-  const uint64_t cell0 = static_cast<uint64_t>(cd.stream) * nb;
-  // sum over the chunks k = from, from-1, ... of T(k), back to (and including) the first one that
-  // closed its own head, added to `v` (lane l holds fields l, l + 32)
-  auto chain = [&](uint32_t from, uint64_t& v0, uint64_t& v1) {
-    uint32_t k = from;
-    for (;;) {
-      const uint64_t* T = P.agg_vals + (static_cast<uint64_t>(k) * 2 + 1) * F;
-      if (lane < F) v0 += T[lane];
-      if (lane + 32 < F) v1 += T[lane + 32];
-      if (P.agg[k].closed_head || (P.chunks[k].flags & CH_FIRST_OF_STREAM)) break;
-      --k;
-    }
-  };
-  auto put_cell = [&](uint32_t slot, uint64_t v0, uint64_t v1) {
-    uint64_t* a = acc_s + static_cast<uint64_t>(slot - 1) * F;
-    if (lane < F) a[lane] = v0;
-    if (lane + 32 < F) a[lane + 32] = v1;
-    __syncwarp();
-    if (lane == 0) derive_cell(D, cell0 + slot - 1);
-    __syncwarp();
-  };
-  if (ag.closed_head && ag.hb >= 1 && ag.hb <= nb) {
-    const uint64_t* H = P.agg_vals + static_cast<uint64_t>(c) * 2 * F;
-    uint64_t v0 = lane < F ? H[lane] : 0, v1 = lane + 32 < F ? H[lane + 32] : 0;
-    if (!first_of_stream) chain(c - 1, v0, v1);
-    put_cell(ag.hb, v0, v1);
-  }
-  if (cd.flags & CH_LAST_OF_STREAM) {
-    if (ag.tb >= 1 && ag.tb <= nb) {
-      uint64_t v0 = 0, v1 = 0;
-      chain(c, v0, v1);
-      put_cell(ag.tb, v0, v1);
-    }
-    // behind the last SAMPLE's bucket (or everywhere, if the stream has no SAMPLE in range at all)
-    // hb of the stream's first chunk marks where its own fill began: with tb == 0 nothing was stored
-    if (ag.tb <= nb) fill_empty_cells(P, D, cd.stream, ag.tb, nb - ag.tb, lane);
-  }
 }
 
 // ------------------------------------------------------------------------------------
@@ -2874,7 +2448,63 @@ __global__ void __launch_bounds__(128) k_boundary(const Params P, const hbtgpu_c
 }
 
 // ------------------------------------------------------------------------------------
-// k_derive kernels (DeriveParams and the per-cell arithmetic are defined in front of k_decode)
+// k_derive: per (cpu,bucket): scaled = getCount(acc), metrics = reducers(scaled)
+struct DeriveParams {
+  const uint64_t* acc;
+  uint64_t* scaled;
+  double* metric;
+  uint32_t* valid;
+  uint64_t n_cells;  // cpus * buckets
+  uint32_t n_events, n_metrics;
+  uint64_t n_magic;  // ceil(2^32 / n_events): x / n == (x * n_magic) >> 32 for x < 2^16
+  hbtgpu_metric metrics[HBTGPU_MAX_METRICS];
+};
+
+__device__ __forceinline__ double add_reduce_int(const uint64_t* v, uint32_t k) {
+  // std::accumulate(begin, end, 0): int accumulator (BuiltinMetrics.cpp:94)
+  int32_t acc = 0;
+  for (uint32_t i = 0; i < k; ++i)
+    acc = static_cast<int32_t>(static_cast<uint32_t>(static_cast<uint64_t>(static_cast<int64_t>(acc)) + v[i]));
+  return static_cast<double>(acc);
+}
+
+// metrics of one cell from its scaled counts `sc` (any address space) and accumulated time_running
+__device__ __forceinline__ uint32_t derive_metrics(const DeriveParams& D, const uint64_t* sc, uint64_t tr,
+                                                   double* out_row) {
+  uint32_t vmask = 0;
+  for (uint32_t m = 0; m < D.n_metrics; ++m) {
+    const hbtgpu_metric& md = D.metrics[m];
+    double out = 0.0;
+    bool ok = false;
+    if (md.kind == HBTGPU_METRIC_RATE) {
+      // getRateReducer: exactly two values, denominator != 0 (BuiltinMetrics.cpp:104-116)
+      if (md.n_idx == 2) {
+        const uint64_t num = sc[md.idx[0]], den = sc[md.idx[1]];
+        if (den != 0) {
+          out = __ddiv_rn(__ull2double_rn(num), __ull2double_rn(den));
+          ok = true;
+        }
+      }
+    } else if (md.kind == HBTGPU_METRIC_ADD) {
+      if (md.n_idx > 0) {
+        uint64_t v[HBTGPU_MAX_METRIC_EVENTS];
+        for (uint32_t k = 0; k < md.n_idx; ++k) v[k] = sc[md.idx[k]];
+        out = add_reduce_int(v, md.n_idx);
+        ok = true;
+      }
+    } else if (md.kind == HBTGPU_METRIC_PER_SECOND_MEGA) {
+      // float(double(count) * 1e3 / double(time_running)) (PerfMonitor.cpp:63-66)
+      const double c = __ull2double_rn(sc[md.idx[0]]);
+      const float f = __double2float_rn(__ddiv_rn(__dmul_rn(c, 1e3), __ull2double_rn(tr)));
+      out = static_cast<double>(f);
+      ok = true;
+    }
+    out_row[m] = out;
+    if (ok) vmask |= 1u << m;
+  }
+  return vmask;
+}
+
 // generic form: one thread per cell, straight from global memory (any n_events)
 __global__ void __launch_bounds__(256) k_derive(const DeriveParams D) {
   const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -2890,6 +2520,14 @@ __global__ void __launch_bounds__(256) k_derive(const DeriveParams D) {
 // the same for the cells a shard-boundary row was added to after the full derive had already
 // run: one block per cpu, cells[cpu] = the cell, ~0 for none, ~0 - 1 for "the whole row of this
 // cpu changed" (its walk stalled at or before this shard's first SAMPLE)
+__device__ __forceinline__ void derive_cell(const DeriveParams& D, uint64_t i) {
+  const uint32_t n = D.n_events;
+  const uint64_t* a = D.acc + i * (n + 3);
+  const uint64_t te = a[n], tr = a[n + 1];
+  uint64_t* sc = D.scaled + i * n;
+  for (uint32_t e = 0; e < n; ++e) sc[e] = get_count(a[e], te, tr);
+  D.valid[i] = derive_metrics(D, sc, tr, D.metric + i * D.n_metrics);
+}
 __global__ void __launch_bounds__(128) k_derive_cells(const DeriveParams D, const uint64_t* cells, uint32_t n_buckets) {
   const uint64_t i = cells[blockIdx.x];
   if (i == ~0ull) return;
@@ -2899,15 +2537,6 @@ __global__ void __launch_bounds__(128) k_derive_cells(const DeriveParams D, cons
   } else if (threadIdx.x == 0) {
     derive_cell(D, i);
   }
-}
-
-// the exact path's derive step when the fast path derives in its own kernels: a grid-stride form
-// that returns at once unless NEED_EXACT was raised
-__global__ void __launch_bounds__(256) k_derive_if_exact(const DeriveParams D, const uint32_t* flags) {
-  if (flags[FLAG_NEED_EXACT] == 0) return;
-  const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
-  for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < D.n_cells; i += stride)
-    derive_cell(D, i);
 }
 
 // tiled form: a block stages the accumulators of blockDim.x cells with coalesced loads, each
