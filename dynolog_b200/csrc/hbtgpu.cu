@@ -13,6 +13,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <cmath>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -166,7 +167,27 @@ int build_table(hbtgpu_ctx* ctx) {
   // enough chunks to fill 148 SMs several times over, but not smaller than one tile
   uint64_t target = total / (148ull * 12ull);
   const uint64_t cap = 512ull << 10;
-  const uint64_t cb = chunk_bytes_for(target, cap, ctx_tile_bytes(ctx));
+  uint64_t cb = chunk_bytes_for(target, cap, ctx_tile_bytes(ctx));
+  {
+    // 148 SMs x 5 resident CTAs take 740 chunks at a time: among the chunk sizes around the
+    // target pick the one whose last wave is fullest (4032 chunks were 5.45 waves)
+    const uint64_t tile = ctx_tile_bytes(ctx);
+    const uint64_t k0 = cb / tile;
+    double best = -1.0;
+    uint64_t best_k = k0;
+    for (uint64_t k = std::max<uint64_t>(1, k0 - k0 / 4); k <= k0 + k0 / 4 && k * tile <= cap + tile / 2; ++k) {
+      uint64_t n = 0;
+      for (auto& im : ctx->images) n += (im.len + k * tile - 1) / (k * tile);
+      if (n < 740) continue;
+      const double waves = static_cast<double>(n) / 740.0;
+      const double fill = waves / std::ceil(waves);
+      if (fill > best + 1e-9) {
+        best = fill;
+        best_k = k;
+      }
+    }
+    cb = best_k * tile;
+  }
   ctx->chunk_bytes = cb;
 
   std::vector<std::vector<uint32_t>> per_stream(ns);
@@ -732,13 +753,15 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
 
   if (ctx->d2h_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));  // acc may still be copied out
   CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
-  CK(cudaMemsetAsync(ctx->d_counters, 0, ns * C_SLOTS * 8, ctx->stream));
   CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
-  CK(cudaMemsetAsync(ctx->d_flags, force_exact ? 1 : 0, 1, ctx->stream));  // byte 0 of NEED_EXACT
-  CK(cudaMemsetAsync(reinterpret_cast<uint8_t*>(ctx->d_flags) + 1, 0, FLAG_COUNT * 4 - 1, ctx->stream));
   const bool external = (ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY) != 0;
-  // shard mode: every stream starts from an invalid state; the boundary row is added later
-  if (external) CK(cudaMemsetAsync(ctx->d_carry_in, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
+  // counters, flags, carry-out of streams without images; shard mode: every stream starts from
+  // an invalid state (the boundary row is added later)
+  {
+    const uint32_t words = ns * static_cast<uint32_t>(sizeof(hbtgpu_carry) / 8);
+    k_prologue<<<(words + 255) / 256, 256, 0, ctx->stream>>>(P, ctx->d_carry_in, force_exact ? 1u : 0u);
+    ++launches;
+  }
   if (ctx->tid_slots) {  // attribution tables start empty
     CK(cudaMemsetAsync(ctx->d_tid_keys, 0xFF, ctx->tid_slots * 8ull, ctx->stream));
     CK(cudaMemsetAsync(ctx->d_tid_cnt, 0, ctx->tid_slots * 8ull, ctx->stream));
@@ -746,9 +769,6 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
     CK(cudaMemsetAsync(ctx->d_ip_cnt, 0, ctx->ip_slots * 8ull, ctx->stream));
     CK(cudaMemsetAsync(ctx->d_attr_special, 0, 4 * 8, ctx->stream));
   }
-  // streams without images keep their carry: carry_out := carry_in
-  CK(cudaMemcpyAsync(ctx->d_carry_out, ctx->d_carry_in, ns * sizeof(hbtgpu_carry),
-                     cudaMemcpyDeviceToDevice, ctx->stream));
   ctx->derived = false;
   ctx->acc_cur = ctx->d_acc;
   const bool timed = ctx->ev_pending < hbtgpu_ctx::kEvRing;

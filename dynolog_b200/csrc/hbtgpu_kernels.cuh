@@ -1675,7 +1675,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
   // ---- tiles ----  (positions are chunk-relative bytes in 32 bits: a chunk is <= 1 MiB and a
   // record can leave it by at most 64 KiB)
   const uint64_t chunk_end_abs = min(cd.img_base + cd.end, limit_abs);
-  TileCtx tc{0, 0, cd.stream, 0, 0, io.row_base, io.rec_base,
+  TileCtx tc{0, 0, cd.stream, 0, 0, MODE == MODE_EMIT ? io.row_base : 0, MODE == MODE_EMIT ? io.rec_base : 0,
              P.acc + static_cast<uint64_t>(cd.stream) * P.n_buckets * (P.n_events + 3)};
   const bool any_work = entry_abs < chunk_end_abs;  // also false for exact-mode "skip" (~0)
   const uint32_t chunk_len = any_work ? static_cast<uint32_t>(chunk_end_abs - chunk_abs) : 0;
@@ -1767,7 +1767,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
           recover_chain(s, sb, wh, K, ew - w0, P.force_general != 0);
           const uint32_t tk = s.term_kind, tt = s.term_tgt;
           tc.tile_abs = tile_abs + 8ull * w0;
-          tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base) + 8ull * w0;
+          if (MODE == MODE_EMIT) tc.stream_off = cd.stream_pos + (tile_abs - cd.img_base) + 8ull * w0;
           if (MODE == MODE_AGG) {
             // one aggregation routine for every path: list the samples, then the indexed pass
             list_tile<PRE>(s, P, sb, K, cur);
@@ -1805,25 +1805,31 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
   __syncthreads();
   if (MODE == MODE_AGG && PRE == 2) attr_cache_flush(P);
   const Carry& C = s.c[cur];
+  // (the chunk's stream and flags are read again here rather than kept in registers through the
+  // tile loop, which has none to spare)
+  const uint32_t c_end = blockIdx.x;
+  const uint32_t cd_stream = *reinterpret_cast<const volatile uint32_t*>(&P.chunks[c_end].stream);
+  const uint32_t cd_flags = *reinterpret_cast<const volatile uint32_t*>(&P.chunks[c_end].flags);
   if (threadIdx.x == 0) {
-    io.out_exit = next_abs;
-    io.out_last = C.last_off;
-    io.out_gap = C.gap;
-    io.n_records = s.cnt[C_RECORDS];
-    io.n_rows = s.cnt[C_ROWS];
+    ChunkIO& ioe = P.io[c_end];
+    ioe.out_exit = next_abs;
+    ioe.out_last = C.last_off;
+    ioe.out_gap = C.gap;
+    ioe.n_records = s.cnt[C_RECORDS];
+    ioe.n_rows = s.cnt[C_ROWS];
     if (bad) {
-      if (SPEC) raise_exact(P.flags, bad, c);
+      if (SPEC) raise_exact(P.flags, bad, c_end);
       else atomicExch(&P.flags[FLAG_INTERNAL], bad);
     }
   }
   if (MODE == MODE_AGG) {
-    uint64_t* ctr = P.counters + static_cast<uint64_t>(cd.stream) * C_SLOTS;
+    uint64_t* ctr = P.counters + static_cast<uint64_t>(cd_stream) * C_SLOTS;
     if (threadIdx.x < C_SLOTS && threadIdx.x != C_LOST && s.cnt[threadIdx.x])
       red_add(&ctr[threadIdx.x], s.cnt[threadIdx.x]);
     if (threadIdx.x == 0 && s.lost_sum) red_add(&ctr[C_LOST], s.lost_sum);
     // stream carry-out: in exact mode k_resolve owns it
-    if (SPEC && (cd.flags & CH_LAST_OF_STREAM)) {
-      hbtgpu_carry& co = P.carry_out[cd.stream];
+    if (SPEC && (cd_flags & CH_LAST_OF_STREAM)) {
+      hbtgpu_carry& co = P.carry_out[cd_stream];
       for (uint32_t e = threadIdx.x; e < P.n_events; e += NT) co.last[e] = C.last[e];
       if (threadIdx.x == 0) {
         const bool v = C.valid && !C.gap;
@@ -2088,6 +2094,21 @@ __global__ void k_clear(const Params P, uint64_t acc_words) {
       P.ip_cnt[i] = 0;
     }
     if (i0 < 4) P.attr_special[i0] = 0;
+  }
+}
+
+// what a run starts from, in one launch: zeroed counters and flags, carry_out := carry_in for
+// streams without images (shard mode: every stream starts from an invalid state)
+__global__ void __launch_bounds__(256) k_prologue(const Params P, hbtgpu_carry* carry_in, uint32_t force_exact) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < P.n_streams * C_SLOTS) P.counters[i] = 0;
+  if (i < FLAG_COUNT) P.flags[i] = (i == FLAG_NEED_EXACT && force_exact) ? 1u : 0u;
+  constexpr uint32_t W = sizeof(hbtgpu_carry) / 8;
+  if (i < P.n_streams * W) {
+    uint64_t* in = reinterpret_cast<uint64_t*>(carry_in);
+    uint64_t* out = reinterpret_cast<uint64_t*>(P.carry_out);
+    if (P.external_carry) in[i] = 0;
+    out[i] = in[i];
   }
 }
 
