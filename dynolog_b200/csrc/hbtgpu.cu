@@ -66,6 +66,10 @@ struct hbtgpu_ctx {
   uint64_t *d_tid_keys = nullptr, *d_ip_keys = nullptr;
   unsigned long long *d_tid_cnt = nullptr, *d_ip_cnt = nullptr, *d_attr_special = nullptr;
   uint32_t tid_slots = 0, ip_slots = 0;
+  // HBTGPU_F_ACCUMULATE_ATTR: the totals over the runs since the last hbtgpu_attr_clear
+  uint64_t *d_tid_keys_tot = nullptr, *d_ip_keys_tot = nullptr;
+  unsigned long long *d_tid_cnt_tot = nullptr, *d_ip_cnt_tot = nullptr, *d_attr_special_tot = nullptr;
+  bool accumulate = false;
   ChunkDesc* d_chunks = nullptr;
   ChunkIO* d_io = nullptr;
   ImageDesc* d_images = nullptr;
@@ -573,6 +577,19 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
     CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_keys), ctx->ip_slots * 8ull));
     CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_cnt), ctx->ip_slots * 8ull));
     CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_attr_special), 4 * 8));
+    if (cfg->flags & HBTGPU_F_ACCUMULATE_ATTR) {
+      ctx->accumulate = true;
+      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tid_keys_tot), ctx->tid_slots * 8ull));
+      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tid_cnt_tot), ctx->tid_slots * 8ull));
+      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_keys_tot), ctx->ip_slots * 8ull));
+      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_cnt_tot), ctx->ip_slots * 8ull));
+      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_attr_special_tot), 4 * 8));
+      CKC(cudaMemsetAsync(ctx->d_tid_keys_tot, 0xFF, ctx->tid_slots * 8ull, ctx->stream));
+      CKC(cudaMemsetAsync(ctx->d_tid_cnt_tot, 0, ctx->tid_slots * 8ull, ctx->stream));
+      CKC(cudaMemsetAsync(ctx->d_ip_keys_tot, 0xFF, ctx->ip_slots * 8ull, ctx->stream));
+      CKC(cudaMemsetAsync(ctx->d_ip_cnt_tot, 0, ctx->ip_slots * 8ull, ctx->stream));
+      CKC(cudaMemsetAsync(ctx->d_attr_special_tot, 0, 4 * 8, ctx->stream));
+    }
   }
   CKC(cudaMemsetAsync(ctx->d_carry_in, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
   CKC(cudaMemsetAsync(ctx->d_carry_out, 0, ns * sizeof(hbtgpu_carry), ctx->stream));
@@ -606,7 +623,8 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
                   ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
                   ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_tid_keys,
                   ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special, ctx->d_series, ctx->d_boundary_cell,
-                  ctx->d_head_extra, ctx->d_dead, ctx->d_stub_block, ctx->d_acc_total};
+                  ctx->d_head_extra, ctx->d_dead, ctx->d_stub_block, ctx->d_acc_total,
+                  ctx->d_tid_keys_tot, ctx->d_tid_cnt_tot, ctx->d_ip_keys_tot, ctx->d_ip_cnt_tot, ctx->d_attr_special_tot};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
@@ -793,6 +811,15 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
     launches += 3;
     CK(cudaGetLastError());
   }
+  if (ctx->accumulate && nc) {
+    k_attr_merge<<<148 * 4, 256, 0, ctx->stream>>>(ctx->d_tid_keys, ctx->d_tid_cnt, ctx->tid_slots - 1, ctx->d_tid_keys_tot,
+                                                  ctx->d_tid_cnt_tot, ctx->tid_slots - 1, ctx->d_attr_special_tot + 2);
+    k_attr_merge<<<148 * 8, 256, 0, ctx->stream>>>(ctx->d_ip_keys, ctx->d_ip_cnt, ctx->ip_slots - 1, ctx->d_ip_keys_tot,
+                                                  ctx->d_ip_cnt_tot, ctx->ip_slots - 1, ctx->d_attr_special_tot + 3);
+    k_attr_merge_special<<<1, 32, 0, ctx->stream>>>(ctx->d_attr_special, ctx->d_attr_special_tot);
+    CK(cudaGetLastError());
+    launches += 3;
+  }
   if (external) {
     k_head<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(P);
     CK(cudaGetLastError());
@@ -935,9 +962,10 @@ int hbtgpu_get_tid_histogram(hbtgpu_ctx* ctx, uint32_t* pid, uint32_t* tid, uint
   if (int r = fetch_counters(ctx)) return r;  // surfaces exact-path / internal errors first
   std::vector<uint64_t> keys(ctx->tid_slots), cnt(ctx->tid_slots);
   unsigned long long special[4];
-  CK(cudaMemcpyAsync(keys.data(), ctx->d_tid_keys, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaMemcpyAsync(cnt.data(), ctx->d_tid_cnt, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaMemcpyAsync(special, ctx->d_attr_special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
+  const bool tot = ctx->accumulate;
+  CK(cudaMemcpyAsync(keys.data(), tot ? ctx->d_tid_keys_tot : ctx->d_tid_keys, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(cnt.data(), tot ? ctx->d_tid_cnt_tot : ctx->d_tid_cnt, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(special, tot ? ctx->d_attr_special_tot : ctx->d_attr_special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   if (special[2]) return fail(ctx, -ENOSPC, "(pid,tid) table overflowed: raise hbtgpu_config.tid_table_log2");
   size_t k = 0;
@@ -977,11 +1005,13 @@ int hbtgpu_get_top_ips(hbtgpu_ctx* ctx, uint32_t k, uint64_t* ip, uint64_t* coun
   unsigned long long* rcnt = mb.take<unsigned long long>(k);
   unsigned int* d_m = mb.take<unsigned int>(1);
   CK(cudaMemsetAsync(d_m, 0, 4, ctx->stream));
-  k_attr_compact<<<148 * 8, 256, 0, ctx->stream>>>(ctx->d_ip_keys, ctx->d_ip_cnt, ctx->ip_slots - 1, ckey, ccnt, d_m);
+  const bool tot = ctx->accumulate;
+  k_attr_compact<<<148 * 8, 256, 0, ctx->stream>>>(tot ? ctx->d_ip_keys_tot : ctx->d_ip_keys, tot ? ctx->d_ip_cnt_tot : ctx->d_ip_cnt,
+                                                  ctx->ip_slots - 1, ckey, ccnt, d_m);
   unsigned int m = 0;
   unsigned long long special[4];
   CK(cudaMemcpyAsync(&m, d_m, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaMemcpyAsync(special, ctx->d_attr_special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(special, tot ? ctx->d_attr_special_tot : ctx->d_attr_special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   if (special[3]) return fail(ctx, -ENOSPC, "IP table overflowed: raise hbtgpu_config.ip_table_log2");
   if (special[1]) {  // samples whose ip equals the empty-slot marker live in a side counter
@@ -1003,6 +1033,18 @@ int hbtgpu_get_top_ips(hbtgpu_ctx* ctx, uint32_t k, uint64_t* ip, uint64_t* coun
     CK(cudaStreamSynchronize(ctx->stream));
   }
   *n = kk;
+  return 0;
+}
+
+int hbtgpu_attr_clear(hbtgpu_ctx* ctx) {
+  if (!ctx) return -EINVAL;
+  if (!ctx->accumulate) return fail(ctx, -EINVAL, "context was not created with HBTGPU_F_ACCUMULATE_ATTR");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaMemsetAsync(ctx->d_tid_keys_tot, 0xFF, ctx->tid_slots * 8ull, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_tid_cnt_tot, 0, ctx->tid_slots * 8ull, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_ip_keys_tot, 0xFF, ctx->ip_slots * 8ull, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_ip_cnt_tot, 0, ctx->ip_slots * 8ull, ctx->stream));
+  CK(cudaMemsetAsync(ctx->d_attr_special_tot, 0, 4 * 8, ctx->stream));
   return 0;
 }
 

@@ -2128,6 +2128,22 @@ __global__ void k_attr_compact(const uint64_t* keys, const unsigned long long* c
   }
 }
 
+// HBTGPU_F_ACCUMULATE_ATTR: add one run's table to the totals (after the exact path, if it ran,
+// has settled the run's counts)
+__global__ void k_attr_merge(const uint64_t* keys, const unsigned long long* cnt, uint32_t mask, uint64_t* tot_keys,
+                             unsigned long long* tot_cnt, uint32_t tot_mask, unsigned long long* overflow) {
+  const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+  for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i <= mask; i += stride) {
+    const uint64_t k = keys[i];
+    if (k == ATTR_EMPTY) continue;
+    const uint32_t slot = attr_hash(k) & tot_mask;
+    attr_add_from(tot_keys, tot_cnt, tot_mask, k, cnt[i], overflow, slot, reinterpret_cast<volatile uint64_t*>(tot_keys)[slot]);
+  }
+}
+__global__ void k_attr_merge_special(const unsigned long long* run, unsigned long long* tot) {
+  if (threadIdx.x < 4) tot[threadIdx.x] += run[threadIdx.x];
+}
+
 struct TopBest {
   unsigned long long cnt;
   uint64_t key;

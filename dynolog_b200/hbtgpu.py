@@ -20,6 +20,7 @@ MAX_METRIC_EVENTS = 8
 F_FORCE_EXACT = 0x1
 F_FORCE_GENERAL = 0x2
 F_EXTERNAL_CARRY = 0x4
+F_ACCUMULATE_ATTR = 0x8
 
 SAMPLE_TIME_READ = 0
 SAMPLE_IP_TID_TIME_READ = 1
@@ -88,7 +89,7 @@ ABI_SYMBOLS = [
     "hbtgpu_create", "hbtgpu_destroy", "hbtgpu_last_error", "hbtgpu_set_carry",
     "hbtgpu_submit_image", "hbtgpu_submit_images", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
     "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows", "hbtgpu_rows_device",
-    "hbtgpu_get_records", "hbtgpu_get_tid_histogram", "hbtgpu_get_top_ips",
+    "hbtgpu_get_records", "hbtgpu_get_tid_histogram", "hbtgpu_get_top_ips", "hbtgpu_attr_clear",
     "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_get_buckets_host_async",
     "hbtgpu_derive",
     "hbtgpu_get_stubs", "hbtgpu_compose_tail", "hbtgpu_apply_boundaries", "hbtgpu_stub_bytes",
@@ -321,6 +322,9 @@ class Context:
         n = C.c_size_t(0)
         self._ck(self.L.hbtgpu_get_top_ips(self.h, C.c_uint32(k), _ptr(ip), _ptr(cnt), C.byref(n)))
         return [(int(a), int(b)) for a, b in zip(ip[:n.value], cnt[:n.value])]
+
+    def attr_clear(self):
+        self._ck(self.L.hbtgpu_attr_clear(self.h))
 
     def buckets(self, want_acc=True, want_scaled=True, want_metric=True, want_valid=True):
         """Returns dict of host arrays: acc[cpu,bucket,n+3], scaled[cpu,bucket,n], metric, valid."""

@@ -41,6 +41,9 @@ extern "C" {
 #define HBTGPU_F_FORCE_EXACT 0x1u   /* always run the exact (sequential-resolver) path */
 #define HBTGPU_F_FORCE_GENERAL 0x2u /* always run pointer-jumping, never the contiguous-chain shortcut */
 #define HBTGPU_F_EXTERNAL_CARRY 0x4u /* shard mode: predecessor of each stream lives on another GPU (see hbtgpu_get_stubs) */
+#define HBTGPU_F_ACCUMULATE_ATTR 0x8u /* IP|TID format: the (pid,tid) histogram and the IP counts add up over runs
+                                        (a capture larger than the arena is streamed through in pieces: submit,
+                                        run, hbtgpu_reset(keep_carry = 1), ...) until hbtgpu_attr_clear */
 
 /* hbtgpu_config.sample_format: layout of PERF_RECORD_SAMPLE.
  * TIME_READ is what hbt's Sampling mode opens (sample_type = TIME|READ,
@@ -213,6 +216,9 @@ int hbtgpu_get_tid_histogram(hbtgpu_ctx* ctx, uint32_t* pid, uint32_t* tid, uint
 /* The k most-sampled instruction pointers over all cpus, ordered by (count descending, ip
  * ascending).  *n = min(k, distinct IPs).  -ENOSPC if the IP table overflowed. */
 int hbtgpu_get_top_ips(hbtgpu_ctx* ctx, uint32_t k, uint64_t* ip, uint64_t* count, size_t* n);
+
+/* HBTGPU_F_ACCUMULATE_ATTR: start the histogram and the IP counts from zero again. */
+int hbtgpu_attr_clear(hbtgpu_ctx* ctx);
 
 /* Bucket tensors.  _device returns pointers into the context's device memory
  * (valid until destroy; contents change on run/reset); _host copies them into

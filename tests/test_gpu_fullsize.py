@@ -213,3 +213,48 @@ def test_cfg2_slice_against_the_compiled_reference(ref_oracle):
         assert np.array_equal(b[5], exp["buckets"])
     finally:
         g.close()
+
+
+def test_cfg4_attribution_accumulates_over_windows_100m_samples(port_oracle):
+    """BASELINE config 4 streamed through one context in pieces (HBTGPU_F_ACCUMULATE_ATTR): 8 windows
+    x 192 cpus x 6.9 MiB = 10.6 GB = 120 M samples; histogram and top-100 over ALL of them against
+    the C restatement's walk (spec extension: parity unpinned by construction)."""
+    n, ncpu, W, per_cpu = 4, 192, 8, 7_200_000
+    cap = synth.Capture(synth.make_spec(4), ncpu)
+    t0, nb = synth.T_START, 1000
+    p = po.make_params(n, n_buckets=nb, t0=t0, bucket_ns=1_000_000, pre=2)
+    buf = np.empty(ncpu * ((per_cpu + 127) // 128 * 128), np.uint8)
+    tid_counts = np.zeros(4096, np.int64)
+    ip_counts = np.zeros(1 << 20, np.int64)
+    carries = [po.make_carry(valid=True, tstamp=t0, last=[0] * n) for _ in range(ncpu)]
+    total = 0
+    with hbtgpu.Context(n_events=n, max_cpus=ncpu, n_buckets=nb, t0=t0, bucket_ns=1_000_000,
+                        arena_bytes=buf.size + (1 << 20), sample_format=hbtgpu.SAMPLE_IP_TID_TIME_READ,
+                        flags=hbtgpu.F_ACCUMULATE_ATTR) as g:
+        c = hbtgpu.make_carry(valid=True, tstamp=t0, last=[0] * n)
+        for cpu in range(ncpu):
+            g.set_carry(cpu, c)
+        for w in range(W):
+            streams = cap.window(max_bytes_per_cpu=per_cpu, out=buf)
+            if w:
+                g.reset(keep_carry=True)
+            g.submit_images(list(range(ncpu)), streams)
+            g.run()
+            g.sync()
+            assert g.stats()["exact_runs"] == 0
+            total += sum(g.counters(i)["sample"] for i in range(ncpu))
+            for i, s in enumerate(streams):
+                tids, ips = port_oracle.collect_ip_tid(p, s, carries[i])
+                tid_counts += np.bincount((tids >> np.uint64(32)).astype(np.int64) - 5000, minlength=4096)
+                ip_counts += np.bincount(((ips - np.uint64(0xffffffff81000000)) >> np.uint64(4)).astype(np.int64),
+                                         minlength=1 << 20)
+        hist = g.tid_histogram()
+        top = g.top_ips(100)
+        g.attr_clear()
+        g.sync()
+        assert g.tid_histogram() == {}
+    assert total > 100_000_000 and total == int(tid_counts.sum()) == int(ip_counts.sum())
+    exp_hist = {(1000 + r // 8, 5000 + r): int(k) for r, k in enumerate(tid_counts) if k}
+    assert hist == exp_hist
+    order = np.lexsort((np.arange(1 << 20), -ip_counts))[:100]
+    assert top == [(0xffffffff81000000 + 16 * int(r), int(ip_counts[r])) for r in order]
