@@ -319,6 +319,7 @@ struct __align__(128) Smem {
   uint32_t idx_n, idx_end, idx_gap, idx_bad, idx_other;  // index_tile: samples listed, chain position after the tile,
                                               // a LOST after the last sample, word of a record consume() stalls on
   uint32_t tile_err;
+  uint32_t ix[NWARP][8];          // index_tile: what each warp's walk found (IX_*)
   uint32_t cnt[C_SLOTS];          // chunk-local counters (u32), lost is u64 below
   unsigned long long lost_sum;
 };
@@ -1093,70 +1094,253 @@ __device__ __forceinline__ void list_tile(Smem& s, const Params& P, const uint64
 // s.fl[j] = 1 if a LOST lies between sample j-1 and j (its row does not exist, gen :110-124).
 // One pass of uniform_segment<..., IDX = true> over the list then does what the plain pass does
 // for a contiguous run.  Must be called by all threads; contains barriers.
-template <int PRE, int NEV>
-__device__ __forceinline__ void index_tile(Smem& s, const Params& P, const uint64_t* buf, uint32_t wt,
-                                           uint32_t ew, uint32_t cur) {
-  if (threadIdx.x < 32) {
-    const uint32_t lane = threadIdx.x;
-    const uint32_t n = NEV ? static_cast<uint32_t>(NEV) : P.n_events;
-    const uint32_t S = 5 + PRE + n;
-    const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
-    uint32_t p = ew, nrec = 0, bad = 0xFFFFFFFFu, n_flagged = 0;
-    uint32_t n_rec_other = 0, n_thr = 0, n_unthr = 0, n_read = 0;
-    unsigned long long lost = 0;
-    bool gap = false;  // a LOST since the last listed sample
-    while (p < wt) {
-      const uint32_t q = p + lane * S;
-      const bool ok = q < wt && (buf[q] & 0xFFFF0000FFFFFFFFull) == want && buf[q + PRE + 2] == n;
-      const uint32_t okm = __ballot_sync(0xffffffffu, ok);
-      const uint32_t run = okm == 0xFFFFFFFFu ? 32u : static_cast<uint32_t>(__ffs(~okm) - 1);
-      if (run > 0) {
-        if (lane < run) {
-          s.pos[nrec + lane] = static_cast<uint16_t>(q);
-          s.fl[nrec + lane] = (lane == 0 && gap) ? 1 : 0;
-        }
-        nrec += run;
-        n_flagged += gap ? 1 : 0;
-        gap = false;
-        p += run * S;
-        continue;
-      }
-      const uint64_t h = buf[p];
-      const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
-      // what consume() stalls on (or the fences of DESIGN.md): the general path reports it
-      if (size < 8 || (size & 7) || type == REC_SAMPLE || (type == REC_LOST && size < 24) ||
-          (type == REC_READ && (size < 40 || buf[p + 2] != ((size - 40u) >> 3)))) {
-        bad = p;
+enum { IX_ENTRY = 0, IX_END, IX_NREC, IX_FLAGS, IX_OTHER, IX_BAD, IX_THR_UNTHR, IX_READ };
+enum : uint32_t { IXF_GAP_END = 1, IXF_GAP_FIRST = 2, IXF_OVERFLOW = 4 };
+constexpr uint32_t IX_LIST = 64;  // listed samples per warp (a tile holds at most PASS_RECORDS = 185)
+
+// One warp walks the chain from word `p` until it reaches `stop` (or a record consume() stalls on):
+// runs of configured SAMPLEs 32 at a time (lane l tests the record at p + l*S), any other record by
+// its size with consume()'s checks.  The SAMPLEs go to out[k] = position | (a LOST lies between
+// sample k-1 and k) << 16; res[] gets the IX_* summary; lost_out the sum of num_lost.
+// DIRECT: the list goes straight to s.pos / s.fl (a single walker), res[IX_READ + ...] unchanged,
+// and the number of flagged samples is returned in res[IX_ENTRY].
+template <int PRE, int NEV, bool DIRECT = false>
+__device__ __forceinline__ void index_walk(const Params& P, const uint64_t* buf, uint32_t wt, uint32_t p,
+                                           uint32_t stop, uint32_t* out, uint32_t cap, uint32_t* res,
+                                           unsigned long long* lost_out, Smem* sm = nullptr) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t n = NEV ? static_cast<uint32_t>(NEV) : P.n_events;
+  const uint32_t S = 5 + PRE + n;
+  const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
+  uint32_t nrec = 0, bad = 0xFFFFFFFFu, n_other = 0, n_thr = 0, n_unthr = 0, n_read = 0, flags = 0, n_flagged = 0;
+  unsigned long long lost = 0;
+  bool gap = false;  // a LOST since the last listed sample
+  (void)wt;
+  while (p < stop) {
+    const uint32_t q = p + lane * S;
+    const bool ok = q < stop && (buf[q] & 0xFFFF0000FFFFFFFFull) == want && buf[q + PRE + 2] == n;
+    const uint32_t okm = __ballot_sync(0xffffffffu, ok);
+    const uint32_t run = okm == 0xFFFFFFFFu ? 32u : static_cast<uint32_t>(__ffs(~okm) - 1);
+    if (run > 0) {
+      if (nrec + run > cap) {
+        flags |= IXF_OVERFLOW;
         break;
       }
-      n_rec_other += 1;
-      if (type == REC_LOST) {
-        lost += buf[p + 2];
-        gap = true;
-      } else if (type == REC_THROTTLE) {
-        n_thr += 1;
-      } else if (type == REC_UNTHROTTLE) {
-        n_unthr += 1;
-      } else if (type == REC_READ) {
-        n_read += 1;
+      if (DIRECT) {
+        if (lane < run) {
+          sm->pos[nrec + lane] = static_cast<uint16_t>(q);
+          sm->fl[nrec + lane] = (lane == 0 && gap) ? 1 : 0;
+        }
+        n_flagged += gap ? 1 : 0;
+      } else if (lane < run) {
+        out[nrec + lane] = q | ((lane == 0 && gap) ? 0x10000u : 0u);
       }
-      p += size >> 3;
+      if (nrec == 0 && gap) flags |= IXF_GAP_FIRST;
+      nrec += run;
+      gap = false;
+      p += run * S;
+      continue;
     }
-    if (lane == 0) {
-      s.idx_n = nrec;
-      s.idx_end = p;
-      s.idx_gap = (gap ? 1u : 0u) | (n_flagged << 1);  // bit 0: LOST behind the last sample
-      s.idx_bad = bad;
-      s.idx_other = n_rec_other;
-      s.cnt[C_RECORDS] += n_rec_other;
-      s.cnt[C_THROTTLE] += n_thr;
-      s.cnt[C_UNTHROTTLE] += n_unthr;
-      s.cnt[C_READ] += n_read;
-      s.lost_sum += lost;
-      // no sample behind the last LOST of this tile: the carry remembers it
-      if (nrec == 0 && gap) s.c[cur].gap = 1;
+    const uint64_t h = buf[p];
+    const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
+    // what consume() stalls on (or the fences of DESIGN.md): the general path reports it
+    if (size < 8 || (size & 7) || type == REC_SAMPLE || (type == REC_LOST && size < 24) ||
+        (type == REC_READ && (size < 40 || buf[p + 2] != ((size - 40u) >> 3)))) {
+      bad = p;
+      break;
+    }
+    n_other += 1;
+    if (type == REC_LOST) {
+      lost += buf[p + 2];
+      gap = true;
+    } else if (type == REC_THROTTLE) {
+      n_thr += 1;
+    } else if (type == REC_UNTHROTTLE) {
+      n_unthr += 1;
+    } else if (type == REC_READ) {
+      n_read += 1;
+    }
+    p += size >> 3;
+  }
+  if (lane == 0) {
+    if (DIRECT) res[IX_ENTRY] = n_flagged;
+    res[IX_END] = p;
+    res[IX_NREC] = nrec;
+    res[IX_FLAGS] = flags | (gap ? IXF_GAP_END : 0u);
+    res[IX_OTHER] = n_other;
+    res[IX_BAD] = bad;
+    res[IX_THR_UNTHR] = n_thr | (n_unthr << 16);
+    res[IX_READ] = n_read;
+    *lost_out = lost;
+  }
+}
+
+// Index of a mixed tile (MODE_AGG).  A tile that holds other records than configured SAMPLEs
+// (THROTTLE / UNTHROTTLE pairs under a high sample rate, LOST) is not cut at each of them:
+// the chain from word `ew` to the end of the tile is walked once and the SAMPLEs are listed --
+// s.pos[j] = word position, s.fl[j] = 1 if a LOST lies between sample j-1 and j (its row does
+// not exist, gen :110-124) -- with the checks and the accounting of consume() (:1440-1450 LOST,
+// :1476-1487 THROTTLE, :1515-1530 READ, :1565-1570 anything else); one pass of
+// uniform_segment<..., IDX = true> over the list then does what the plain pass does for a run.
+// All NWARP warps walk at once: warp 0 from `ew`, warp w from the first word of its sixth of the
+// tile that looks like a configured SAMPLE (a guess), each up to the next warp's entry.  The
+// guesses are proven the way k_verify proves chunks: warp w's entry must be exactly where the
+// walk before it ended.  From the first entry that is not, one warp walks the rest.
+// parallel = false: only warp 0 walks (cheaper when the tile holds one or two other records, as in
+// BASELINE config 3: fewer barriers, no guesses to prove).
+template <int PRE, int NEV>
+__device__ __forceinline__ void index_tile(Smem& s, const Params& P, const uint64_t* buf, uint32_t wt,
+                                           uint32_t ew, uint32_t cur, bool parallel) {
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t n = NEV ? static_cast<uint32_t>(NEV) : P.n_events;
+  const uint32_t S = 5 + PRE + n;
+  const uint64_t want = static_cast<uint64_t>(REC_SAMPLE) | (static_cast<uint64_t>(S * 8) << 48);
+  unsigned long long* const lostw = reinterpret_cast<unsigned long long*>(s.u.de.pred);  // [NWARP], 8-byte aligned
+  uint32_t* const list = s.u.de.bkt;                                                      // [NWARP][IX_LIST]
+  if (!parallel) {
+    // one walker, one barrier
+    if (warp == 0) {
+      index_walk<PRE, NEV, true>(P, buf, wt, ew, wt, nullptr, MAXC, s.ix[0], &lostw[0], &s);
+      __syncwarp();
+      const uint32_t nr = s.ix[0][IX_NREC];
+      const uint32_t f = s.ix[0][IX_ENTRY];
+      if (lane == 0) {
+        const bool gap = (s.ix[0][IX_FLAGS] & IXF_GAP_END) != 0;
+        s.cnt[C_RECORDS] += s.ix[0][IX_OTHER];
+        s.cnt[C_THROTTLE] += s.ix[0][IX_THR_UNTHR] & 0xFFFFu;
+        s.cnt[C_UNTHROTTLE] += s.ix[0][IX_THR_UNTHR] >> 16;
+        s.cnt[C_READ] += s.ix[0][IX_READ];
+        s.lost_sum += lostw[0];
+        s.idx_n = nr;
+        s.idx_end = s.ix[0][IX_END];
+        s.idx_bad = s.ix[0][IX_BAD];
+        s.idx_other = s.ix[0][IX_OTHER];
+        s.idx_gap = (gap ? 1u : 0u) | (f << 1);
+        if (nr == 0 && gap) s.c[cur].gap = 1;  // no sample behind the last LOST of this tile: the carry remembers it
+      }
+    }
+    __syncthreads();
+    return;
+  }
+  // ---- entries
+  const uint32_t span = wt > ew ? wt - ew : 0;
+  const uint32_t sub = (span + NWARP - 1) / NWARP;
+  uint32_t entry = 0xFFFFFFFFu;
+  if (warp == 0) {
+    entry = ew;
+  } else if (sub >= S) {
+    const uint32_t lo = ew + warp * sub, hi = min(lo + sub, wt);
+    for (uint32_t q0 = lo; q0 < hi && entry == 0xFFFFFFFFu; q0 += 32) {
+      const uint32_t q = q0 + lane;
+      const bool m = q < hi && q + PRE + 2 < wt + OV_BYTES / 8 && (buf[q] & 0xFFFF0000FFFFFFFFull) == want &&
+                     buf[q + PRE + 2] == n;
+      const uint32_t bal = __ballot_sync(0xffffffffu, m);
+      if (bal) entry = q0 + (__ffs(bal) - 1);
     }
   }
+  if (lane == 0) s.ix[warp][IX_ENTRY] = entry;
+  __syncthreads();
+  // ---- walks
+  if (entry != 0xFFFFFFFFu) {
+    uint32_t stop = wt;
+    for (uint32_t w = warp + 1; w < NWARP; ++w) {
+      const uint32_t e = s.ix[w][IX_ENTRY];
+      if (e != 0xFFFFFFFFu) {
+        stop = e;
+        break;
+      }
+    }
+    index_walk<PRE, NEV>(P, buf, wt, entry, stop, list + warp * IX_LIST, IX_LIST, s.ix[warp], &lostw[warp]);
+  }
+  __syncthreads();
+  // ---- proof of the guesses, and what is good of the lists (every thread computes the same)
+  uint32_t good = 0;          // warps 0..good-1 are consistent
+  uint32_t pos_end = ew;      // where the proven chain stands
+  uint32_t total = 0, others = 0, bad = 0xFFFFFFFFu;
+  uint32_t base_of_mine = 0;  // where this warp's list goes
+  bool gap = false, mine_good = false, first_gap_mine = false;
+  for (uint32_t w = 0; w < NWARP; ++w) {
+    const uint32_t e = s.ix[w][IX_ENTRY];
+    if (e == 0xFFFFFFFFu) {  // no guess: the walk before it goes on through this warp's part
+      good = w + 1;
+      continue;
+    }
+    if (e != pos_end || bad != 0xFFFFFFFFu) break;
+    const uint32_t fl = s.ix[w][IX_FLAGS];
+    if (fl & IXF_OVERFLOW) break;
+    const uint32_t nr = s.ix[w][IX_NREC];
+    if (w == warp) {
+      mine_good = true;
+      base_of_mine = total;
+      first_gap_mine = gap;
+    }
+    gap = nr > 0 ? (fl & IXF_GAP_END) != 0 : (gap || (fl & IXF_GAP_END) != 0);
+    total += nr;
+    others += s.ix[w][IX_OTHER];
+    pos_end = s.ix[w][IX_END];
+    bad = s.ix[w][IX_BAD];
+    good = w + 1;
+  }
+  // ---- the lists of the proven walks, in order; counters
+  if (mine_good) {
+    const uint32_t nr = s.ix[warp][IX_NREC];
+    for (uint32_t k = lane; k < nr; k += 32) {
+      const uint32_t v = list[warp * IX_LIST + k];
+      s.pos[base_of_mine + k] = static_cast<uint16_t>(v);
+      s.fl[base_of_mine + k] = static_cast<uint8_t>((v >> 16) | ((k == 0 && first_gap_mine) ? 1u : 0u));
+    }
+    if (lane == 0) {
+      atomicAdd(&s.cnt[C_RECORDS], s.ix[warp][IX_OTHER]);
+      const uint32_t tu = s.ix[warp][IX_THR_UNTHR];
+      if (tu & 0xFFFFu) atomicAdd(&s.cnt[C_THROTTLE], tu & 0xFFFFu);
+      if (tu >> 16) atomicAdd(&s.cnt[C_UNTHROTTLE], tu >> 16);
+      if (s.ix[warp][IX_READ]) atomicAdd(&s.cnt[C_READ], s.ix[warp][IX_READ]);
+      if (lostw[warp]) atomicAdd(&s.lost_sum, lostw[warp]);
+    }
+  }
+  __syncthreads();
+  // ---- a refuted guess: one warp walks the rest of the tile from where the proven chain stands
+  const bool rest = good < NWARP && bad == 0xFFFFFFFFu && pos_end < wt;
+  if (rest && warp == 0) {
+    index_walk<PRE, NEV>(P, buf, wt, pos_end, wt, list, MAXC, s.ix[0], &lostw[0]);
+    __syncwarp();
+    const uint32_t nr = s.ix[0][IX_NREC];
+    for (uint32_t k = lane; k < nr; k += 32) {
+      const uint32_t v = list[k];
+      s.pos[total + k] = static_cast<uint16_t>(v);
+      s.fl[total + k] = static_cast<uint8_t>((v >> 16) | ((k == 0 && gap) ? 1u : 0u));
+    }
+    if (lane == 0) {
+      s.cnt[C_RECORDS] += s.ix[0][IX_OTHER];
+      s.cnt[C_THROTTLE] += s.ix[0][IX_THR_UNTHR] & 0xFFFFu;
+      s.cnt[C_UNTHROTTLE] += s.ix[0][IX_THR_UNTHR] >> 16;
+      s.cnt[C_READ] += s.ix[0][IX_READ];
+      s.lost_sum += lostw[0];
+    }
+  }
+  __syncthreads();
+  if (rest) {
+    const uint32_t nr = s.ix[0][IX_NREC], fl = s.ix[0][IX_FLAGS];
+    gap = nr > 0 ? (fl & IXF_GAP_END) != 0 : (gap || (fl & IXF_GAP_END) != 0);
+    total += nr;
+    others += s.ix[0][IX_OTHER];
+    pos_end = s.ix[0][IX_END];
+    bad = s.ix[0][IX_BAD];
+  }
+  // samples without a row = the flagged entries of the final list
+  uint32_t f = 0;
+  for (uint32_t k = threadIdx.x; k < total; k += NT) f += s.fl[k] ? 1u : 0u;
+  f = __reduce_add_sync(0xffffffffu, f);
+  if (threadIdx.x == 0) {
+    s.idx_n = total;
+    s.idx_end = pos_end;
+    s.idx_bad = bad;
+    s.idx_other = others;
+    s.idx_gap = gap ? 1u : 0u;  // bit 0: a LOST behind the last sample; the count of flagged samples is added below
+    if (total == 0 && gap) s.c[cur].gap = 1;  // no sample behind the last LOST of this tile: the carry remembers it
+  }
+  __syncthreads();
+  if (lane == 0 && f) atomicAdd(&s.idx_gap, f << 1);
   __syncthreads();
 }
 
@@ -1687,6 +1871,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
     n_issued = 1;
   }
   bool mixed_prev = false;  // the previous tile held other records than configured SAMPLEs
+  bool dense_prev = false;  // ... half a dozen or more
   for (uint32_t tile_rel = 0, b = boff; tile_rel < chunk_len; tile_rel += tb, b ^= 1) {
     if (tile_rel + tb < chunk_len) {
       if (threadIdx.x == 0) issue(tile_rel + tb, b ^ 1);
@@ -1731,12 +1916,13 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
           if (MODE == MODE_AGG) {
             // the tile holds other records too: index the rest of it once (index_tile), then
             // one pass over the listed samples, however many other records lie in between
-            index_tile<PRE, NEV>(s, P, buf, wt, ew, cur);
+            index_tile<PRE, NEV>(s, P, buf, wt, ew, cur, dense_prev);
             uint32_t n_idx = 0;
             const uint32_t ki = uniform_segment<MODE, PRE, NEV, true>(s, P, buf, wt, ew, tc, cur, n_idx);
             if (ki) cur ^= 1;
             ew = s.idx_end;
             mixed_prev = s.idx_other != 0;
+            dense_prev = s.idx_other >= 6;  // many other records: the next tile is indexed by all warps
             if (s.idx_bad != 0xFFFFFFFFu) {
               // a record consume() stalls on: everything before it is accounted for, the general
               // path looks at it and owns the error reporting
