@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <math.h>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -1560,4 +1561,5 @@ int hbtgpu_decode_image_noalloc(const hbtgpu_config* cfg, const hbtgpu_carry* ca
 
 #include "hbtgpu_peer.inc"
 #include "hbtgpu_series.inc"
+#include "hbtcap.inc"
 #include "hbtgpu_cs_host.inc"

@@ -100,6 +100,8 @@ ABI_SYMBOLS = [
     "hbtgpu_math_tsc_to_ktime", "hbtgpu_math_ktime_to_tsc", "hbtgpu_math_per_second_mega",
     "hbtgpu_math_running_ratio", "hbtgpu_get_stats", "hbtgpu_version",
     "hbtgpu_decode_image_noalloc", "hbtgpu_noalloc_last_error", "hbtgpu_series_reduce",
+    "hbtcap_create", "hbtcap_append", "hbtcap_finish", "hbtcap_open", "hbtcap_describe", "hbtcap_config",
+    "hbtcap_image", "hbtcap_submit", "hbtcap_close", "hbtcap_last_error", "hbtgpu_log_series",
 ]
 
 NOALLOC_MAX_IMAGE_BYTES = 64 << 20

@@ -12,6 +12,7 @@
 //     getCpuGenerator(cpu)          PerCpuBase.h                same
 //     accumUntil(batch, stop_ts)    PerCpuSampleGeneratorBase.h:69-94   same (batch and stop_ts honoured record by record)
 //   GroupReadValues               PerfEventsGroup.h:386-586  GroupReadValues (arithmetic through hbtgpu_math_*)
+//   dynolog::Logger               dynolog/src/Logger.h:26-48  Logger + logSeries (MetricSeries reductions of the buckets)
 //   TraceMonitor::applyToCountSamplesAndConsume  mon/TraceMonitor.h:35-108   applyToCountSamples
 //   CpuThreadSwitchGenerator      PerCpuThreadSwitchGenerator.h:168-446   CpuThreadSwitchGenerator
 //     consume / getNumRecord* / getLastTimeStamp / getNumEntries         same names
@@ -491,6 +492,35 @@ class GroupReadValues {
   uint64_t time_enabled_ = 0, time_running_ = 0;
   std::vector<uint64_t> count_;
 };
+
+/// dynolog::Logger (dynolog/src/Logger.h:26-48): the interface a sink implements.
+class Logger {
+ public:
+  virtual ~Logger() = default;
+  virtual void logInt(const std::string& key, int64_t val) = 0;
+  virtual void logFloat(const std::string& key, float val) = 0;
+  virtual void logUint(const std::string& key, uint64_t val) = 0;
+  virtual void logStr(const std::string& key, const std::string& val) = 0;
+  virtual void finalize() = 0;
+};
+
+/// The bucket series of the current window, reduced on the GPU the way dynolog's MetricSeries
+/// reduces a metric before it is logged (avg, percentile, diff, rate) and published through a
+/// Logger: one entry per CPU, keys "<nickname>_avg.cpu<N>" etc. (hbtgpu_log_series).
+inline void logSeries(PerCpuCountSampleGenerator& gen, Logger& logger, uint32_t first_bucket, uint32_t count,
+                      float percentage, int64_t period_ns, int64_t duration_ns) {
+  gen.getBuckets(nullptr, nullptr, nullptr, nullptr);  // decodes what was handed over, if it has not been yet
+  hbtgpu_logger lg{};
+  lg.user = &logger;
+  lg.log_uint = [](void* u, const char* key, uint64_t v) { static_cast<Logger*>(u)->logUint(key, v); };
+  lg.log_float = [](void* u, const char* key, float v) { static_cast<Logger*>(u)->logFloat(key, v); };
+  lg.finalize = [](void* u) { static_cast<Logger*>(u)->finalize(); };
+  std::vector<const char*> names;
+  for (const auto& nm : gen.getEventNicknames()) names.push_back(nm.c_str());
+  const int rc = hbtgpu_log_series(gen.raw(), &lg, names.data(), first_bucket, count, percentage, period_ns, duration_ns);
+  if (rc == -EINVAL) throw std::invalid_argument(hbtgpu_last_error(gen.raw()));
+  if (rc != 0) throw std::runtime_error(hbtgpu_last_error(gen.raw()));
+}
 
 // ---- ContextSwitch mode ---------------------------------------------------------------------
 using Event = hbtgpu_cs_event;  // layout of tagstack::Event

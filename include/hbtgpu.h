@@ -439,6 +439,55 @@ int hbtgpu_series_reduce(hbtgpu_ctx* ctx, uint32_t first_bucket, uint32_t count,
                          int64_t period_ns, int64_t duration_ns, double* avg_f64, uint64_t* avg_u64,
                          uint64_t* percentile, uint64_t* diff, double* rate_f64, uint64_t* rate_u64);
 
+/* ---- capture container and Logger sink ----------------------------------
+ *
+ * The reference defines no capture file format: ring images exist only as the borrowed slices
+ * that PerfEventsGroup::onCpuDataBufferRead hands to a callback (PerfEventsGroup.h:45-64,
+ * 1592-1637).  hbtcap_* is the smallest container that lets a daemon write what it read and a GPU
+ * box decode it later: what the decoder has to know about the group (events with their
+ * nicknames and TscToKernelTime flags, hbt/src/perf_event/PmuEvent.h:248-256; the TSC conversion
+ * parameters of perf_event_mmap_page, PerfEventsGroup.h:829-841; the SAMPLE layout), the images
+ * (128-byte aligned) and an index (window, cpu) -> (offset, length).  Host code only.
+ * Writer: hbtcap_create, hbtcap_append per (window, cpu) in any order, hbtcap_finish.
+ * Reader: hbtcap_open (mmap; -EINVAL for anything that is not a well-formed capture),
+ * hbtcap_config fills the decoder's configuration from it, hbtcap_submit hands the images of the
+ * windows [window_lo, window_hi) to a context in time order (hbtgpu_submit_images). */
+#define HBTCAP_NAME_BYTES 32
+typedef struct {
+  uint32_t n_events, sample_format, n_cpus, n_windows;
+  uint32_t time_shift, time_mult;
+  uint64_t time_zero, tsc_mask;
+  char event_names[HBTGPU_MAX_EVENTS][HBTCAP_NAME_BYTES]; /* nicknames, NUL-terminated */
+} hbtcap_desc;
+typedef struct hbtcap hbtcap;
+int hbtcap_create(const char* path, const hbtcap_desc* desc, hbtcap** out);
+int hbtcap_append(hbtcap* cap, uint32_t window, uint32_t cpu, const void* first, size_t n1, const void* second,
+                  size_t n2);
+int hbtcap_finish(hbtcap* cap); /* writes index and header, closes, frees */
+int hbtcap_open(const char* path, hbtcap** out);
+int hbtcap_describe(const hbtcap* cap, hbtcap_desc* out);
+int hbtcap_config(const hbtcap* cap, hbtgpu_config* cfg); /* n_events, sample_format, tsc_*, time_*; raises max_cpus */
+int hbtcap_image(const hbtcap* cap, uint32_t window, uint32_t cpu, const void** bytes, size_t* n);
+int hbtcap_submit(const hbtcap* cap, hbtgpu_ctx* ctx, uint32_t window_lo, uint32_t window_hi);
+void hbtcap_close(hbtcap* cap);
+const char* hbtcap_last_error(const hbtcap* cap);
+
+/* dynolog::Logger (dynolog/src/Logger.h:26-48) as C callbacks: logUint / logFloat / finalize.
+ * hbtgpu_log_series reduces every (cpu, event) series of scaled counts over the buckets
+ * [first_bucket, first_bucket + count) on the GPU (hbtgpu_series_reduce, i.e. MetricSeries avg /
+ * percentile / diff / rate, dynolog/src/metric_frame/MetricSeries.h:198-263) and publishes one log
+ * entry per cpu: keys "<nickname>_avg.cpu<N>", "_rate" (logFloat), "_p<percent>", "_diff"
+ * (logUint) -- "<metric>.<entity>", the form dynolog::splitKey takes apart -- then finalize(). */
+typedef struct {
+  void* user;
+  void (*log_uint)(void* user, const char* key, uint64_t value);
+  void (*log_float)(void* user, const char* key, float value);
+  void (*finalize)(void* user);
+} hbtgpu_logger;
+int hbtgpu_log_series(hbtgpu_ctx* ctx, const hbtgpu_logger* logger, const char* const* event_names,
+                      uint32_t first_bucket, uint32_t count, float percentage, int64_t period_ns,
+                      int64_t duration_ns);
+
 /* ---- ContextSwitch-mode decode -------------------------------------
  *
  * Replaces, for captured ring images of hbt's ContextSwitch mode (sample_type TIME|TID with

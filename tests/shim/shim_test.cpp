@@ -215,6 +215,20 @@ int main() {
     EXPECT(d0.consume(10) == -ENODATA && d0.getNumRecordSample() == 4 && d0.getNumEntries() == 3);
     EXPECT(d0.getNumUnknownCountInterval() == 1 && d0.getLastTimeStamp() == 300);
 
+    // the sink: MetricSeries reductions of the buckets through a dynolog::Logger-shaped object
+    struct Collect : Logger {
+      std::map<std::string, uint64_t> u;
+      std::map<std::string, float> f;
+      int entries = 0;
+      void logInt(const std::string&, int64_t) override {}
+      void logFloat(const std::string& k, float v) override { f[k] = v; }
+      void logUint(const std::string& k, uint64_t v) override { u[k] = v; }
+      void logStr(const std::string&, const std::string&) override {}
+      void finalize() override { ++entries; }
+    } sink;
+    logSeries(g3, sink, 0, o2.n_buckets, 0.5f, 1000, 1000);
+    EXPECT(sink.entries == 1 && sink.u.count("a_diff.cpu0") == 1 && sink.f.count("b_avg.cpu0") == 1);
+
     // GroupReadValues (PerfEventsGroup.h:386-586) over the library's arithmetic; known answers of
     // hbt/src/mon/tests/MonitorMockTest.cpp:86-88,121-126
     GroupReadValues rv(g3.raw(), 2);

@@ -21,7 +21,7 @@ def built():
 def declared_symbols():
     src = open(os.path.join(ROOT, "include", "hbtgpu.h")).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(hbtgpu_[a-z0-9_]+)\s*\(", src)))
+    return sorted(set(re.findall(r"\b(hbt(?:gpu|cap)_[a-z0-9_]+)\s*\(", src)))
 
 
 def test_library_exports_every_declared_symbol(built):
