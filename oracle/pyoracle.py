@@ -432,9 +432,11 @@ def islice_release(kind, slices, rows, stop_ts, flags, mark=0):
 
 def slicer_run(kind, events, n_units, cap_per_unit=None, stack_cap=None):
     """Slicer::processNext over events in stream order.  Returns dict(rc, slices=[per unit],
-    stats, stacks, last_ts)."""
-    lib, prefix = _slices_lib(kind)
-    f = getattr(lib, prefix + "_slicer_run")
+    stats, stacks, last_ts).  kind "port_general": the restatement with the general stack
+    dictionary (oracle/hbt_slicer_general.c: any level, phase events)."""
+    general = kind == "port_general"
+    lib, prefix = _slices_lib("port" if general else kind)
+    f = getattr(lib, prefix + ("_slicer_general_run" if general else "_slicer_run"))
     f.restype = C.c_int
     events = np.ascontiguousarray(events, dtype=EVENT_DTYPE)
     cap = cap_per_unit if cap_per_unit is not None else len(events) + 1
