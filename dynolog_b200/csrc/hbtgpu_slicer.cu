@@ -576,6 +576,8 @@ __global__ void k_sl_put_carried(hbtgpu_cs_event* __restrict__ ev, const uint64_
 
 }  // namespace
 
+#include "hbtgpu_slicer_general.inc"
+
 struct hbtgpu_slicer_ctx {
   int device = 0;
   std::string err;
@@ -598,6 +600,9 @@ struct hbtgpu_slicer_ctx {
   int depth = 0;
   hbtgpu_slicer_stats total{};
   bool have_state = false;
+  // the general path (any level, phase events): its dictionary, and whether this Slicer runs on it
+  GenHost gen;
+  bool general_mode = false;
   // results of the last run
   hbtgpu_slice* d_slices = nullptr;
   uint64_t* d_slice_begin = nullptr;
@@ -693,6 +698,238 @@ int reset_state(hbtgpu_slicer_ctx* c, uint32_t n_units) {
 
 }  // namespace
 
+namespace {
+
+template <class T>
+int gen_grow(hbtgpu_slicer_ctx* c, T** p, size_t* cap, size_t need) {
+  if (need <= *cap && *p) return 0;
+  const size_t ncap = std::max(need, *cap * 2);
+  T* fresh = nullptr;
+  SK(cudaMalloc(reinterpret_cast<void**>(&fresh), ncap * sizeof(T)));
+  if (*p) cudaFree(*p);
+  *p = fresh;
+  *cap = ncap;
+  return 0;
+}
+
+void gen_free(GenHost& g) {
+  for (void* p : {static_cast<void*>(g.h.s), static_cast<void*>(g.h.hslot), static_cast<void*>(g.h.dkey),
+                  static_cast<void*>(g.h.dhead), static_cast<void*>(g.h.depoch), static_cast<void*>(g.h.active),
+                  static_cast<void*>(g.h.swin_ts), static_cast<void*>(g.h.swin_type), static_cast<void*>(g.d),
+                  static_cast<void*>(g.stacks)})
+    if (p) cudaFree(p);
+  g = GenHost{};
+}
+
+// room for `need_states` stacks: the state array grows by copy, the tables are rebuilt
+int gen_reserve(hbtgpu_slicer_ctx* c, uint32_t n_units, uint64_t need_states) {
+  GenHost& g = c->gen;
+  cudaStream_t st = c->stream;
+  if (need_states >= 0x40000000ull) return sfail(c, -EOVERFLOW, "more than 2^30 stacks");
+  if (!g.d) SK(cudaMalloc(reinterpret_cast<void**>(&g.d), sizeof(GenDev)));
+  if (g.h.n_units != n_units) {
+    for (void* p : {static_cast<void*>(g.h.active), static_cast<void*>(g.h.swin_ts), static_cast<void*>(g.h.swin_type)})
+      if (p) cudaFree(p);
+    SK(cudaMalloc(reinterpret_cast<void**>(&g.h.active), n_units * sizeof(int32_t)));
+    SK(cudaMalloc(reinterpret_cast<void**>(&g.h.swin_ts), n_units * sizeof(uint64_t)));
+    SK(cudaMalloc(reinterpret_cast<void**>(&g.h.swin_type), n_units));
+    SK(cudaMemsetAsync(g.h.active, 0xff, n_units * sizeof(int32_t), st));
+    SK(cudaMemsetAsync(g.h.swin_ts, 0xff, n_units * sizeof(uint64_t), st));
+    SK(cudaMemsetAsync(g.h.swin_type, 0, n_units, st));
+    g.h.n_units = n_units;
+  }
+  if (need_states > g.h.cap) {
+    uint32_t cap = 1024;
+    while (cap < need_states) cap <<= 1;
+    GState* ns = nullptr;
+    SK(cudaMalloc(reinterpret_cast<void**>(&ns), static_cast<size_t>(cap) * sizeof(GState)));
+    if (g.h.n) SK(cudaMemcpyAsync(ns, g.h.s, static_cast<size_t>(g.h.n) * sizeof(GState), cudaMemcpyDeviceToDevice, st));
+    SK(cudaStreamSynchronize(st));
+    for (void* p : {static_cast<void*>(g.h.s), static_cast<void*>(g.h.hslot), static_cast<void*>(g.h.dkey),
+                    static_cast<void*>(g.h.dhead), static_cast<void*>(g.h.depoch)})
+      if (p) cudaFree(p);
+    g.h.s = ns;
+    g.h.cap = cap;
+    g.h.hcap = cap * 4;
+    SK(cudaMalloc(reinterpret_cast<void**>(&g.h.hslot), static_cast<size_t>(g.h.hcap) * 4));
+    SK(cudaMalloc(reinterpret_cast<void**>(&g.h.dkey), static_cast<size_t>(g.h.hcap) * 4));
+    SK(cudaMalloc(reinterpret_cast<void**>(&g.h.dhead), static_cast<size_t>(g.h.hcap) * 4));
+    SK(cudaMalloc(reinterpret_cast<void**>(&g.h.depoch), static_cast<size_t>(g.h.hcap) * 4));
+    SK(cudaMemsetAsync(g.h.hslot, 0xff, static_cast<size_t>(g.h.hcap) * 4, st));
+    SK(cudaMemsetAsync(g.h.depoch, 0, static_cast<size_t>(g.h.hcap) * 4, st));
+    if (g.h.n) {
+      k_gen_rehash<<<blocks(g.h.n), 256, 0, st>>>(g.h.s, g.h.n, g.h.hslot, g.h.hcap);
+      k_gen_reheads<<<blocks(g.h.n), 256, 0, st>>>(g.h.s, g.h.n, g.h.epoch, g.h.dkey, g.h.dhead, g.h.depoch, g.h.hcap);
+      SK(cudaGetLastError());
+    }
+  }
+  return 0;
+}
+
+// an empty Slicer on the general path
+int gen_reset(hbtgpu_slicer_ctx* c, uint32_t n_units) {
+  GenHost& g = c->gen;
+  cudaStream_t st = c->stream;
+  if (g.h.n_units != n_units && g.h.active) {  // gen_reserve makes them anew
+    cudaFree(g.h.active); cudaFree(g.h.swin_ts); cudaFree(g.h.swin_type);
+    g.h.active = nullptr; g.h.swin_ts = nullptr; g.h.swin_type = nullptr;
+    g.h.n_units = 0;
+  }
+  g.h.n = 0;
+  g.h.next_id = 0;
+  g.h.last_ts = 0;
+  g.h.we_depth = 0;
+  g.h.epoch = 1;
+  memset(&g.h.stats, 0, sizeof(g.h.stats));
+  g.h.rc = 0;
+  g.h.rc_at = 0;
+  if (g.h.hcap) {
+    SK(cudaMemsetAsync(g.h.hslot, 0xff, static_cast<size_t>(g.h.hcap) * 4, st));
+    SK(cudaMemsetAsync(g.h.depoch, 0, static_cast<size_t>(g.h.hcap) * 4, st));
+  }
+  if (g.h.active) {
+    SK(cudaMemsetAsync(g.h.active, 0xff, n_units * sizeof(int32_t), st));
+    SK(cudaMemsetAsync(g.h.swin_ts, 0xff, n_units * sizeof(uint64_t), st));
+  }
+  return 0;
+}
+
+// hbtgpu_slicer_run on the general path (hbtgpu_slicer_general.inc)
+int run_general(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const uint64_t* event_begin, uint32_t n_units,
+                uint32_t flags, hbtgpu_slicer_stats* stats, uint64_t* n_slices, uint64_t* n_stacks, uint64_t* last_ts) {
+  GenHost& g = c->gen;
+  cudaStream_t st = c->stream;
+  const uint64_t base = event_begin[0];
+  const uint64_t N64 = event_begin[n_units] - base;
+  const uint32_t N = static_cast<uint32_t>(N64);
+  const bool fresh = !(flags & HBTGPU_SLICER_CONTINUE) || !c->have_state || !c->general_mode || g.h.n_units != n_units;
+  if (fresh)
+    if (int rc = gen_reset(c, n_units)) return rc;
+  c->have_state = false;  // until this window is through: an error leaves no state to continue from
+  c->general_mode = true;
+  // most events find their stack in the dictionary: start with room for a fraction, grow when the walk asks
+  if (int rc = gen_reserve(c, n_units, static_cast<uint64_t>(g.h.n) + std::min<uint64_t>(7 * N64, 4096 + N64 / 8) + 8)) return rc;
+
+  std::vector<uint64_t> ub(n_units + 1);
+  for (uint32_t u = 0; u <= n_units; ++u) ub[u] = event_begin[u] - base;
+  size_t tmp_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
+                                  static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), 0, 64, st);
+  tmp_bytes += 256;
+  const size_t n1 = static_cast<size_t>(N) + 1;
+  size_t need = 0;
+  auto add = [&](size_t n, size_t sz) { need += (n * sz + 255) & ~static_cast<size_t>(255); };
+  add(n1, 16); add(n_units + 1, 8); add(n1, 4);        // events, unit begins, unit_of
+  add(n1, 8); add(n1, 8); add(n1, 4); add(n1, 4);      // key, key_s, val, order
+  add(n1, 32); add(n1, 32);                            // slices by unit slot, slices packed
+  add(n_units + 2, 8); add(n_units + 2, 8);            // slices per unit, slice_begin
+  add(1, sizeof(Globals)); add(tmp_bytes, 1);
+  if (c->arena_cap < need) {
+    cudaFree(c->arena);
+    c->arena = nullptr;
+    c->arena_cap = 0;
+    const size_t cap = need + need / 4 + (1 << 20);
+    SK(cudaMalloc(&c->arena, cap));
+    c->arena_cap = cap;
+  }
+  c->arena_used = 0;
+  auto* d_ev = carve<hbtgpu_cs_event>(c, n1);
+  auto* d_ub = carve<uint64_t>(c, n_units + 1);
+  auto* d_unit_of = carve<uint32_t>(c, n1);
+  auto* d_key = carve<uint64_t>(c, n1);
+  auto* d_key_s = carve<uint64_t>(c, n1);
+  auto* d_val = carve<uint32_t>(c, n1);
+  auto* d_order = carve<uint32_t>(c, n1);
+  auto* d_raw = carve<hbtgpu_slice>(c, n1);
+  auto* d_slices = carve<hbtgpu_slice>(c, n1);
+  auto* d_nout = carve<uint64_t>(c, n_units + 2);
+  auto* d_slice_begin = carve<uint64_t>(c, n_units + 2);
+  auto* d_g = carve<Globals>(c, 1);
+  auto* d_tmp = carve<char>(c, tmp_bytes);
+  if (!d_tmp) return sfail(c, -EIO, "internal: arena too small");
+
+  SK(cudaMemcpyAsync(d_ub, ub.data(), (n_units + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  const cudaMemcpyKind kind = (flags & HBTGPU_SLICER_DEVICE_INPUT) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  if (N) SK(cudaMemcpyAsync(d_ev, events + base, static_cast<size_t>(N) * sizeof(hbtgpu_cs_event), kind, st));
+  SK(cudaMemsetAsync(d_g, 0, sizeof(Globals), st));
+  SK(cudaMemsetAsync(d_nout, 0, (n_units + 2) * sizeof(uint64_t), st));
+  SK(cudaEventRecord(c->ev0, st));
+  Globals gh;
+  memset(&gh, 0, sizeof(gh));
+  if (N) {
+    k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of);
+    k_gen_prepare<<<blocks(N), 256, 0, st>>>(d_ev, N, d_unit_of, d_ub, g.h.last_ts, d_key, d_val, d_g);
+    SK(cudaGetLastError());
+    SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    if (gh.bad) {
+      const unsigned b = gh.bad;
+      return sfail(c, (b & BAD_ORDER) ? -ENOTSUP : -EINVAL, "events the Slicer cannot take:%s%s%s",
+                   (b & BAD_TYPE) ? " unknown event types;" : "",
+                   (b & BAD_ORDER) ? " a unit's events go back in time;" : "",
+                   (b & BAD_UNIT) ? " comp_unit_id differs from the unit the event was filed under;" : "");
+    }
+    int ts_bits = 1;
+    while (ts_bits < 64 && (gh.max_ts >> ts_bits) != 0) ++ts_bits;
+    size_t t = tmp_bytes;
+    cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key, d_key_s, d_val, d_order, static_cast<int>(N), 0, ts_bits, st);
+  }
+  for (uint32_t p0 = 0;;) {
+    SK(cudaMemcpyAsync(g.d, &g.h, sizeof(GenDev), cudaMemcpyHostToDevice, st));
+    k_gen_walk<<<1, 32, 0, st>>>(g.d, d_ev, d_order, p0, N, d_ub, d_raw, d_nout);
+    SK(cudaGetLastError());
+    SK(cudaMemcpyAsync(&g.h, g.d, sizeof(GenDev), cudaMemcpyDeviceToHost, st));
+    SK(cudaStreamSynchronize(st));
+    if (g.h.rc != -ENOSPC) break;
+    p0 = g.h.rc_at;
+    g.h.rc = 0;
+    if (int rc = gen_reserve(c, n_units, 2 * static_cast<uint64_t>(g.h.cap))) return rc;
+  }
+  if (g.h.rc) {
+    const int rc = g.h.rc;
+    hbtgpu_cs_event bad_ev;
+    uint32_t idx = 0;
+    memset(&bad_ev, 0, sizeof(bad_ev));
+    if (g.h.rc_at < N) {
+      SK(cudaMemcpy(&idx, d_order + g.h.rc_at, 4, cudaMemcpyDeviceToHost));
+      SK(cudaMemcpy(&bad_ev, d_ev + idx, sizeof(bad_ev), cudaMemcpyDeviceToHost));
+    }
+    return sfail(c, rc, "%s at event %u of the merged stream (tstamp %llu, type %u, level %u, unit %u)",
+                 rc == -ENOTSUP ? "an event above the active stack's height: the reference reads tags it never set there (TagStack.h:103-118)"
+                                : "the Slicer's argument checks fail (level >= 6, or a slice that would end before it began)",
+                 g.h.rc_at, static_cast<unsigned long long>(bad_ev.tstamp), static_cast<unsigned>(bad_ev.type),
+                 static_cast<unsigned>(bad_ev.level), static_cast<unsigned>(bad_ev.comp_unit_id));
+  }
+  // slices: unit after unit, densely
+  std::vector<uint64_t> nout(n_units);
+  SK(cudaMemcpyAsync(nout.data(), d_nout, n_units * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  SK(cudaStreamSynchronize(st));
+  c->slice_begin.assign(n_units + 1, 0);
+  for (uint32_t u = 0; u < n_units; ++u) c->slice_begin[u + 1] = c->slice_begin[u] + nout[u];
+  SK(cudaMemcpyAsync(d_slice_begin, c->slice_begin.data(), (n_units + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  k_gen_pack<<<n_units, 256, 0, st>>>(d_raw, d_ub, d_slice_begin, d_slices);
+  if (int rc = gen_grow(c, &g.stacks, &g.cap_stacks, std::max<size_t>(g.h.n, 1))) return rc;
+  if (g.h.n) k_gen_stacks<<<blocks(g.h.n), 256, 0, st>>>(g.h.s, g.h.n, g.stacks);
+  SK(cudaGetLastError());
+  SK(cudaEventRecord(c->ev1, st));
+  SK(cudaStreamSynchronize(st));
+  SK(cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
+  if (stats) *stats = g.h.stats;
+  if (last_ts) *last_ts = g.h.last_ts;
+  if (n_slices)
+    for (uint32_t u = 0; u < n_units; ++u) n_slices[u] = nout[u];
+  c->n_stacks = g.h.n;
+  c->d_stacks = g.stacks;
+  if (n_stacks) *n_stacks = c->n_stacks;
+  c->d_slices = d_slices;
+  c->d_slice_begin = d_slice_begin;
+  c->have_state = true;
+  c->have = true;
+  return 0;
+}
+
+}  // namespace
+
 extern "C" {
 
 hbtgpu_slicer_ctx* hbtgpu_slicer_create(int device) {
@@ -716,6 +953,7 @@ void hbtgpu_slicer_destroy(hbtgpu_slicer_ctx* c) {
   cudaFree(c->arena2);
   cudaFree(c->p_flags); cudaFree(c->p_id); cudaFree(c->p_cum); cudaFree(c->p_in); cudaFree(c->p_out);
   cudaFree(c->d_carried);
+  gen_free(c->gen);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -738,8 +976,15 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   const uint64_t Nreal = event_begin[n_units] - base;
   if (Nreal + n_units >= 0x3fffffffull) return sfail(c, -EINVAL, "more than 2^30 events in one call");
   if (Nreal && !events) return sfail(c, -EINVAL, "null events");
-  if (!(flags & HBTGPU_SLICER_CONTINUE) || !c->have_state || c->carried_units != n_units)
+  const bool continues = (flags & HBTGPU_SLICER_CONTINUE) && c->have_state;
+  if ((flags & HBTGPU_SLICER_GENERAL) || (continues && c->general_mode)) {
+    if (continues && !c->general_mode)
+      return sfail(c, -ENOTSUP, "this Slicer runs the parallel form: HBTGPU_SLICER_GENERAL must be given from its first window on");
+    return run_general(c, events, event_begin, n_units, flags, stats, n_slices, n_stacks, last_ts);
+  }
+  if (!continues || c->carried_units != n_units)
     if (int rc = reset_state(c, n_units)) return rc;
+  c->general_mode = false;
   // every unit gets one slot in front of its events for the state the previous window left it in
   const uint32_t N = static_cast<uint32_t>(Nreal + n_units);
   std::vector<uint64_t> ub(n_units + 1);
@@ -877,6 +1122,15 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   }
   if (gh.bad) {
     const unsigned b = gh.bad;
+    // phases, or switches above level 0: the general path has an answer, if this Slicer may still change over
+    constexpr unsigned general_has_it = BAD_TYPE | BAD_LEVEL | BAD_WE_END;
+    if (!(b & ~general_has_it)) {
+      if (!continues) return run_general(c, events, event_begin, n_units, flags, stats, n_slices, n_stacks, last_ts);
+      c->have_state = true;  // (nothing of the window was applied)
+      return sfail(c, -ENOTSUP, "phase events, events above level 0 or a WriteErrorsEnd without its Start in a later "
+                                "window of a Slicer that runs the parallel form: give HBTGPU_SLICER_GENERAL from the "
+                                "first window on");
+    }
     return sfail(c, (b & BAD_UNIT) ? -EINVAL : -ENOTSUP, "events outside the parallel form:%s%s%s%s%s%s%s",
                  (b & BAD_TYPE) ? " phase or unknown event types;" : "", (b & BAD_LEVEL) ? " events above level 0;" : "",
                  (b & BAD_ORDER) ? " a unit's events go back in time;" : "",

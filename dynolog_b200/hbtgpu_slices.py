@@ -207,7 +207,7 @@ class IntervalSlicer:
 
 
 class Slicer:
-    """tagstack::slice::Slicer over one window of level-0 events of all comp units."""
+    """tagstack::slice::Slicer over one window of events of all comp units."""
 
     def __init__(self, device=0):
         self.L = _lib()
@@ -230,10 +230,11 @@ class Slicer:
         if rc != 0:
             raise HbtGpuError(rc, self.L.hbtgpu_slicer_last_error(self.h).decode())
 
-    def run(self, unit_events=None, device_events=None, event_begin=None, cont=False):
+    def run(self, unit_events=None, device_events=None, event_begin=None, cont=False, general=False):
         """unit_events: list of EVENT_DTYPE arrays (one per comp unit, stream order), or
-        device_events (raw pointer) + event_begin.  Returns dict(slices=[per unit], stats, stacks,
-        last_ts)."""
+        device_events (raw pointer) + event_begin.  general: HBTGPU_SLICER_GENERAL (the path for
+        phases and any level; a fresh window that needs it takes it by itself).  Returns
+        dict(slices=[per unit], stats, stacks, last_ts)."""
         if device_events is None:
             n_units = len(unit_events)
             event_begin = np.concatenate([[0], np.cumsum([len(e) for e in unit_events])]).astype(np.uint64)
@@ -249,6 +250,8 @@ class Slicer:
             ptr, flags = device_events, 1
         if cont:
             flags |= 2
+        if general:
+            flags |= 4
         stats = np.zeros(len(SLICER_STAT_KEYS), np.uint64)
         n_slices = np.zeros(n_units, np.uint64)
         n_stacks, last_ts = C.c_uint64(0), C.c_uint64(0)

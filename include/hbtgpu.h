@@ -777,15 +777,31 @@ const uint64_t* hbtgpu_islice_bin_durations_device(hbtgpu_islice_ctx* ctx); /* t
  * statistics and the last timestamp carry over, exactly as one Slicer fed both windows would
  * have them.  stats / the stack table / last_ts are cumulative since the last fresh start.
  *
- * Scope: switch events at level 0 (SwitchIn / SwitchOut*), thread lifetime events (those at
- * another level are dropped as logic errors, as in the reference, :711-720), WriteErrors*, every unit's events in time order, no WriteErrorsEnd without its Start.  A
- * switch-in on a unit whose active state is a thread resets everything, as in the reference
- * (:839-868).  Input outside the scope is refused with -ENOTSUP and a message that names the
- * reason (there is no CPU path); comp_unit_id that differs from the
- * unit an event was filed under is -EINVAL (the reference throws, :351-352).
+ * Two forms, both on the device.  The PARALLEL form (scans and sorts over all events at once) takes
+ * switch events at level 0 (SwitchIn / SwitchOut*), thread lifetime events (those at another
+ * level are dropped as logic errors, as in the reference, :711-720) and WriteErrors* without a
+ * WriteErrorsEnd in front of its Start; a switch-in on a unit whose active state is a thread
+ * resets everything, as in the reference (:839-868).  The GENERAL form takes every event the
+ * reference takes -- phases (Start / End) and switches at any of the six levels -- by keeping the
+ * reference's order: the units are merged on the GPU and one thread walks the merged events with
+ * the stack dictionary in device memory (about a microsecond per event: phase events are few).
+ * A fresh window whose events need the general form takes it by itself; HBTGPU_SLICER_GENERAL asks
+ * for it outright, and a Slicer that continues over windows stays on the form its first window
+ * took (a later window with phases on a parallel Slicer is -ENOTSUP and leaves the state as it
+ * was: give HBTGPU_SLICER_GENERAL from the first window on).
+ *
+ * Refused by both forms: a unit's events that go back in time, or start before the previous
+ * window's last timestamp (-ENOTSUP: the merge would not be the reference's); comp_unit_id that
+ * differs from the unit an event was filed under (-EINVAL, the reference throws, :351-352);
+ * unknown event types and levels >= 6 (-EINVAL, HBT_DCHECK_LT :431).  Refused by the general
+ * form with -ENOTSUP: an event at a level above the active stack's height -- there the reference
+ * copies tags it never initialised (Stack::copyTruncated / copyFillUpTo, TagStack.h:103-118) and
+ * its answer depends on what the memory held.  After an error the Slicer's state is undefined
+ * unless stated otherwise: start afresh.  There is no CPU path.
  */
 #define HBTGPU_SLICER_DEVICE_INPUT 0x1u /* events is a device pointer (event_begin stays host) */
 #define HBTGPU_SLICER_CONTINUE 0x2u     /* this window follows the previous call's: keep the Slicer's state */
+#define HBTGPU_SLICER_GENERAL 0x4u      /* take the general path (below) whatever the events are */
 typedef struct {  /* SlicerStats, Slicer.h:276-285 */
   uint64_t num_processed, num_error_start, num_error_end, num_error_out_sync, num_dropped, num_out_of_order,
       num_slices_completed, num_logic_errors;

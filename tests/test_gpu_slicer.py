@@ -113,23 +113,180 @@ def test_refusals(slicer):
     for kind in KINDS:
         compare(got, po.slicer_run(kind, events([(10, IN, 0, 3), (20, IN, 0, 4), (30, OUT_P, 0, NA), (40, IN, 0, 3),
                                                  (50, OUT_Y, 0, NA)]), 1))
-    ev = events([(10, IN, 0, 3), (20, START, 0, 7)])
-    with pytest.raises(HbtGpuError, match="phase"):
-        slicer.run([ev])
+    # phases in a LATER window of a Slicer that began on the parallel form: refused, the state stays
+    slicer.run([events([(10, IN, 0, 3)])])
+    with pytest.raises(HbtGpuError, match="HBTGPU_SLICER_GENERAL"):
+        slicer.run([events([(20, START, 0, 7)])], cont=True)
+    got = slicer.run([events([(20, OUT_P, 0, NA)])], cont=True)
+    compare(got, po.slicer_run("port", events([(10, IN, 0, 3), (20, OUT_P, 0, NA)]), 1))
     with pytest.raises(HbtGpuError, match="back in time"):
         slicer.run([events([(30, IN, 0, 3), (20, OUT_P, 0, NA)])])
-    with pytest.raises(HbtGpuError, match="WriteErrorsEnd"):
-        slicer.run([events([(10, WE_END, 0, NA)])])
     with pytest.raises(HbtGpuError, match="comp_unit_id"):
         slicer.run([events([(10, IN, 1, 3)])])
+    with pytest.raises(HbtGpuError, match="comp_unit_id"):
+        slicer.run([events([(10, IN, 1, 3)])], general=True)
+    with pytest.raises(HbtGpuError, match="back in time"):
+        slicer.run([events([(30, IN, 0, 3), (20, OUT_P, 0, NA)])], general=True)
     ev = events([(10, IN, 0, 3)])
-    ev["level"][0] = 1
-    with pytest.raises(HbtGpuError, match="level 0"):
+    ev["type"][0] = 9
+    with pytest.raises(HbtGpuError, match="unknown event types"):
         slicer.run([ev])
+    ev = events([(10, IN, 0, 3)])
+    ev["level"][0] = 6                        # HBT_DCHECK_LT(level, kNumLevels)
+    with pytest.raises(HbtGpuError, match="level >= 6"):
+        slicer.run([ev])
+    # the marker of a carried state is not a level an event may have: as any lifetime event off level 0, dropped
     ev = events([(10, CREATE, 0, 3), (20, IN, 0, 3)])
-    ev["level"][0] = 0xEE                     # the marker of a carried state is not a level an event may have
-    with pytest.raises(HbtGpuError, match="level 0"):
-        slicer.run([ev])
+    ev["level"][0] = 0xEE
+    compare(slicer.run([ev]), po.slicer_run("port_general", ev, 1))
+
+
+# ---- the general path: phases, switches at any level (hbtgpu_slicer_general.inc) -----------------------------
+from test_slicer_oracle import END, events_l, random_phase_events, same_general, stack_rows  # noqa: E402
+
+PH = 4
+
+
+def run_general(slicer, ev, n_units, **kw):
+    units = [ev[ev["comp_unit_id"] == u] for u in range(n_units)]
+    got = slicer.run(units, **kw)
+    got["rc"] = 0
+    return got
+
+
+def merge_order(ev):
+    return ev[np.lexsort((ev["comp_unit_id"], ev["tstamp"]))] if len(ev) else ev
+
+
+def test_general_reference_vectors(slicer):
+    """TagStackSlice.* of hbt/src/tagstack/tests/SlicerTest.cpp: expected stack ids and slices, and the oracle."""
+    Y, P = po.TT_YIELD, po.TT_PREEMPTED
+    t = 100
+    cases = [
+        (1, [(20, IN, 1, 0, 2), (30, OUT_P, 1, 0, NA), (31, IN, 1, 0, 2), (32, OUT_P, 1, 0, NA)],
+         [(0, [], 0, 0), (1, [NA], 1, 0), (2, [NA, 2], 2, 0), (3, [], 0, 1), (4, [NA], 1, 1), (5, [NA, 2], 2, 1)],
+         {0: [(20, 10, 2, Y, P), (30, 1, 4, P, Y), (31, 1, 5, Y, P)]}),
+        (1, [(100, IN, 0, 0, 0), (130, OUT_P, 0, 0, NA), (131, IN, 0, 0, 1), (140, START, 1, 0, 10), (160, OUT_P, 0, 0, NA),
+             (170, IN, 0, 0, 1), (190, OUT_Y, 0, 0, NA)],
+         [(0, [], 0, 0), (1, [0], 1, 0), (2, [], 0, 1), (3, [1], 1, 0), (4, [1], 1, 1), (5, [1, 10], 2, 1)],
+         {0: [(100, 30, 1, Y, P), (130, 1, 2, P, Y), (131, 9, 3, Y, PH), (140, 20, 5, PH, P), (160, 10, 2, P, Y),
+              (170, 20, 5, Y, Y)]}),
+        (1, [(0, OUT_P, 0, 0, NA), (0, IN, 0, 0, t), (0, OUT_P, 0, 0, NA), (1, IN, 0, 0, t), (30, OUT_P, 0, 0, NA),
+             (30, IN, 0, 0, t), (35, OUT_P, 0, 0, NA), (36, IN, 0, 0, t), (40, OUT_P, 0, 0, NA), (42, IN, 0, 0, t),
+             (42, OUT_P, 0, 0, NA), (50, IN, 0, 0, t)],
+         [(0, [], 0, 1), (1, [], 0, 0), (2, [t], 1, 0)],
+         {0: [(0, 1, 0, P, Y), (1, 29, 2, Y, P), (30, 5, 2, Y, P), (35, 1, 0, P, Y), (36, 4, 2, Y, P), (40, 2, 0, P, Y),
+              (42, 8, 0, P, Y)]}),
+        (2, [(0, OUT_P, 0, 0, NA), (0, IN, 0, 0, t), (0, OUT_P, 0, 0, NA), (1, IN, 0, 1, t), (30, OUT_P, 0, 1, NA),
+             (31, IN, 0, 0, t), (35, OUT_P, 0, 0, NA)],
+         [(0, [], 0, 1), (1, [], 0, 0), (2, [t], 1, 0)],
+         {1: [(1, 29, 2, Y, P)], 0: [(0, 31, 0, P, Y), (31, 4, 2, Y, P)]}),
+    ]
+    for n_units, rows, stacks, slices in cases:
+        ev = events_l(rows)
+        got = run_general(slicer, ev, n_units, general=True)
+        assert stack_rows(got) == stacks
+        for u, exp in slices.items():
+            assert po.slices_as_tuples(got["slices"][u]) == exp
+        same_general(got, po.slicer_run("port_general", merge_order(ev), n_units))
+
+
+def cut_at_fence(ev, n_units):
+    """the longest prefix the restatement accepts (past it the reference reads tags it never set)"""
+    ev = merge_order(ev)
+    port = po.slicer_run("port_general", ev, n_units)
+    fenced = port["rc"] == -95
+    if fenced:
+        lo, hi = 0, len(ev)  # rc is monotone in the prefix length
+        while lo < hi:
+            mid = (lo + hi + 1) // 2
+            if po.slicer_run("port_general", ev[:mid], n_units)["rc"] == -95:
+                hi = mid - 1
+            else:
+                lo = mid
+        ev = ev[:lo]
+        port = po.slicer_run("port_general", ev, n_units)
+    return ev, port, fenced
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(p_bad=0.0, p_we=0.0), dict(p_phase=0.7), dict(p_bad=0.1), dict(p_create=0.2),
+                                dict(p_we=0.08)])
+def test_general_random_phase_streams(slicer, kw):
+    r = np.random.default_rng(70 + len(repr(kw)))
+    n_fenced = 0
+    for trial in range(25):
+        n_units = int(r.integers(1, 5))
+        full = random_phase_events(r, n_units, int(r.integers(1, 600)), int(r.choice([3, 6, 30])), **kw)
+        ev, port, fenced = cut_at_fence(full, n_units)
+        assert port["rc"] == 0
+        same_general(run_general(slicer, ev, n_units), port)            # (phases: the fresh window changes over by itself)
+        if po.slices_available("reference"):
+            same_general(po.slicer_run("reference", ev, n_units), port)
+        if fenced:                                                        # ... and the whole stream is refused as the oracle refuses it
+            n_fenced += 1
+            with pytest.raises(HbtGpuError, match="never set") as ei:
+                run_general(slicer, merge_order(full), n_units, general=True)
+            assert ei.value.code == -95
+    assert kw.get("p_bad", 0.02) == 0.0 or n_fenced >= 0
+
+
+def test_general_level0_streams_match_the_parallel_form(slicer):
+    r = np.random.default_rng(12)
+    for kw in (dict(), dict(p_double_in=0.2), dict(p_migrate=0.5, p_create=0.2), dict(p_we=0.1)):
+        for trial in range(8):
+            n_units = int(r.integers(1, 6))
+            ev = merge_order(random_events(r, n_units, int(r.integers(1, 400)), int(r.choice([2, 5, 40])), **kw))
+            exp = po.slicer_run("port_general", ev, n_units)
+            same_general(run_general(slicer, ev, n_units, general=True), exp)
+            if supported(ev, n_units):
+                compare(run_general(slicer, ev, n_units), exp)
+            else:                          # a WriteErrorsEnd without its Start: the fresh window changes over by itself
+                same_general(run_general(slicer, ev, n_units), exp)
+
+
+def test_general_windows_continue_each_other(slicer):
+    r = np.random.default_rng(13)
+    done = 0
+    while done < 12:
+        n_units = int(r.integers(1, 5))
+        ev, exp, _ = cut_at_fence(random_phase_events(r, n_units, int(r.integers(50, 800)), int(r.choice([3, 6, 30])), p_we=0.03),
+                                  n_units)
+        if len(ev) < 10:
+            continue
+        cuts = sorted(set(int(x) for x in r.choice(ev["tstamp"], size=int(r.integers(1, 5)))))
+        slices = [[] for _ in range(n_units)]
+        lo = 0
+        for k, cut in enumerate(cuts + [int(ev["tstamp"].max()) + 1]):
+            w = ev[(ev["tstamp"] >= lo) & (ev["tstamp"] < cut)]
+            got = run_general(slicer, w, n_units, cont=k > 0, general=True)
+            for u in range(n_units):
+                slices[u].append(got["slices"][u])
+            lo = cut
+        got["slices"] = [np.concatenate(x) for x in slices]
+        same_general(got, exp)
+        done += 1
+
+
+def test_general_grows_its_dictionary(slicer):
+    """more stacks than the first reservation holds: the walk stops in front of the event, the tables are
+    rebuilt (hash slots and the heads of the dormant lists), the walk goes on"""
+    n = 40_000
+    rows = []
+    for i in range(n):                 # every thread runs one phase of its own: 3 new stacks each, all parked
+        t = 1000 + 10 * i
+        rows += [(t, IN, 0, 0, 10 + i), (t + 2, START, 1, 0, 1 + i % 7), (t + 5, END, 1, 0, NA), (t + 7, OUT_Y, 0, 0, NA)]
+    for i in range(0, n, 97):          # ... and comes back: found in its dormant list
+        t = 1000 + 10 * n + 10 * i
+        rows += [(t, IN, 0, 0, 10 + i), (t + 3, OUT_P, 0, 0, NA)]
+    ev = events_l(rows)
+    exp = po.slicer_run("port_general", ev, 1)
+    assert exp["rc"] == 0 and len(exp["stacks"]) > 2 * n
+    same_general(run_general(slicer, ev, 1), exp)
+    half = len(ev) // 2                # the same over two windows: the second one grows tables that hold lists
+    a = run_general(slicer, ev[:half], 1, general=True)
+    b = run_general(slicer, ev[half:], 1, general=True, cont=True)
+    b["slices"] = [np.concatenate([a["slices"][0], b["slices"][0]])]
+    same_general(b, exp)
 
 
 def test_decoded_capture_to_slices_on_the_device(slicer):
