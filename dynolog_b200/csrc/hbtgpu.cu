@@ -70,6 +70,13 @@ struct hbtgpu_ctx {
   // HBTGPU_F_ACCUMULATE_ATTR: the totals over the runs since the last hbtgpu_attr_clear
   uint64_t *d_tid_keys_tot = nullptr, *d_ip_keys_tot = nullptr;
   unsigned long long *d_tid_cnt_tot = nullptr, *d_ip_cnt_tot = nullptr, *d_attr_special_tot = nullptr;
+  // hbtgpu_attr_merge: the totals over all ranks
+  uint64_t *d_tid_keys_all = nullptr, *d_ip_keys_all = nullptr;
+  unsigned long long *d_tid_cnt_all = nullptr, *d_ip_cnt_all = nullptr, *d_attr_special_all = nullptr;
+  // every set of tables is one allocation {tid keys, tid counts, ip keys, ip counts, special[4]}
+  // (one IPC handle per set): attr_carve
+  uint64_t *d_attr_block = nullptr, *d_attr_block_tot = nullptr, *d_attr_block_all = nullptr;
+  bool attr_all_valid = false;  // the getters read the merged tables (until the next run)
   bool accumulate = false;
   ChunkDesc* d_chunks = nullptr;
   ChunkIO* d_io = nullptr;
@@ -262,6 +269,17 @@ int build_table(hbtgpu_ctx* ctx) {
   return 0;
 }
 
+// IP|TID format: words of one set of attribution tables, and the tables inside such a block
+size_t attr_block_words(const hbtgpu_ctx* ctx) { return 2ull * ctx->tid_slots + 2ull * ctx->ip_slots + 4; }
+void attr_carve(const hbtgpu_ctx* ctx, uint64_t* block, uint64_t** tid_keys, unsigned long long** tid_cnt,
+                uint64_t** ip_keys, unsigned long long** ip_cnt, unsigned long long** special) {
+  *tid_keys = block;
+  *tid_cnt = reinterpret_cast<unsigned long long*>(block + ctx->tid_slots);
+  *ip_keys = block + 2ull * ctx->tid_slots;
+  *ip_cnt = reinterpret_cast<unsigned long long*>(block + 2ull * ctx->tid_slots + ctx->ip_slots);
+  *special = reinterpret_cast<unsigned long long*>(block + 2ull * ctx->tid_slots + 2ull * ctx->ip_slots);
+}
+
 Params make_params(hbtgpu_ctx* ctx) {
   Params P{};
   P.arena = ctx->arena;
@@ -314,6 +332,20 @@ Params make_params(hbtgpu_ctx* ctx) {
     P.s_magic = static_cast<uint32_t>(((1ull << 32) + S - 1) / S);
   }
   return P;
+}
+
+// the attribution tables the getters read: all ranks' (after hbtgpu_attr_merge), this context's
+// totals over its runs (HBTGPU_F_ACCUMULATE_ATTR), or the last run's
+struct AttrView {
+  const uint64_t *tid_keys, *ip_keys;
+  const unsigned long long *tid_cnt, *ip_cnt, *special;
+};
+AttrView attr_view(const hbtgpu_ctx* ctx) {
+  if (ctx->attr_all_valid)
+    return {ctx->d_tid_keys_all, ctx->d_ip_keys_all, ctx->d_tid_cnt_all, ctx->d_ip_cnt_all, ctx->d_attr_special_all};
+  if (ctx->accumulate)
+    return {ctx->d_tid_keys_tot, ctx->d_ip_keys_tot, ctx->d_tid_cnt_tot, ctx->d_ip_cnt_tot, ctx->d_attr_special_tot};
+  return {ctx->d_tid_keys, ctx->d_ip_keys, ctx->d_tid_cnt, ctx->d_ip_cnt, ctx->d_attr_special};
 }
 
 DeriveParams derive_params(hbtgpu_ctx* ctx) {
@@ -573,18 +605,13 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
     }
     ctx->tid_slots = 1u << tl;
     ctx->ip_slots = 1u << il;
-    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tid_keys), ctx->tid_slots * 8ull));
-    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tid_cnt), ctx->tid_slots * 8ull));
-    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_keys), ctx->ip_slots * 8ull));
-    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_cnt), ctx->ip_slots * 8ull));
-    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_attr_special), 4 * 8));
+    CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_attr_block), attr_block_words(ctx) * 8));
+    attr_carve(ctx, ctx->d_attr_block, &ctx->d_tid_keys, &ctx->d_tid_cnt, &ctx->d_ip_keys, &ctx->d_ip_cnt, &ctx->d_attr_special);
     if (cfg->flags & HBTGPU_F_ACCUMULATE_ATTR) {
       ctx->accumulate = true;
-      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tid_keys_tot), ctx->tid_slots * 8ull));
-      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tid_cnt_tot), ctx->tid_slots * 8ull));
-      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_keys_tot), ctx->ip_slots * 8ull));
-      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_ip_cnt_tot), ctx->ip_slots * 8ull));
-      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_attr_special_tot), 4 * 8));
+      CKC(cudaMalloc(reinterpret_cast<void**>(&ctx->d_attr_block_tot), attr_block_words(ctx) * 8));
+      attr_carve(ctx, ctx->d_attr_block_tot, &ctx->d_tid_keys_tot, &ctx->d_tid_cnt_tot, &ctx->d_ip_keys_tot,
+                 &ctx->d_ip_cnt_tot, &ctx->d_attr_special_tot);
       CKC(cudaMemsetAsync(ctx->d_tid_keys_tot, 0xFF, ctx->tid_slots * 8ull, ctx->stream));
       CKC(cudaMemsetAsync(ctx->d_tid_cnt_tot, 0, ctx->tid_slots * 8ull, ctx->stream));
       CKC(cudaMemsetAsync(ctx->d_ip_keys_tot, 0xFF, ctx->ip_slots * 8ull, ctx->stream));
@@ -622,10 +649,9 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
   void* ptrs[] = {ctx->arena, ctx->d_carry_in, ctx->d_carry_out, ctx->d_carry_init, ctx->d_head, ctx->d_counters,
                   ctx->d_acc, ctx->d_scaled, ctx->d_metric, ctx->d_valid, ctx->d_flags,
                   ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
-                  ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_tid_keys,
-                  ctx->d_tid_cnt, ctx->d_ip_keys, ctx->d_ip_cnt, ctx->d_attr_special, ctx->d_series, ctx->d_boundary_cell,
-                  ctx->d_head_extra, ctx->d_dead, ctx->d_stub_block, ctx->d_acc_total,
-                  ctx->d_tid_keys_tot, ctx->d_tid_cnt_tot, ctx->d_ip_keys_tot, ctx->d_ip_cnt_tot, ctx->d_attr_special_tot};
+                  ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_attr_block,
+                  ctx->d_attr_block_tot, ctx->d_attr_block_all, ctx->d_series, ctx->d_boundary_cell,
+                  ctx->d_head_extra, ctx->d_dead, ctx->d_stub_block, ctx->d_acc_total};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : {ctx->ev_run0, ctx->ev_run1})
@@ -789,6 +815,7 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
     CK(cudaMemsetAsync(ctx->d_attr_special, 0, 4 * 8, ctx->stream));
   }
   ctx->derived = false;
+  ctx->attr_all_valid = false;
   ctx->acc_cur = ctx->d_acc;
   const bool timed = ctx->ev_pending < hbtgpu_ctx::kEvRing;
   if (nc) {
@@ -963,10 +990,10 @@ int hbtgpu_get_tid_histogram(hbtgpu_ctx* ctx, uint32_t* pid, uint32_t* tid, uint
   if (int r = fetch_counters(ctx)) return r;  // surfaces exact-path / internal errors first
   std::vector<uint64_t> keys(ctx->tid_slots), cnt(ctx->tid_slots);
   unsigned long long special[4];
-  const bool tot = ctx->accumulate;
-  CK(cudaMemcpyAsync(keys.data(), tot ? ctx->d_tid_keys_tot : ctx->d_tid_keys, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaMemcpyAsync(cnt.data(), tot ? ctx->d_tid_cnt_tot : ctx->d_tid_cnt, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaMemcpyAsync(special, tot ? ctx->d_attr_special_tot : ctx->d_attr_special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
+  const AttrView av = attr_view(ctx);
+  CK(cudaMemcpyAsync(keys.data(), av.tid_keys, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(cnt.data(), av.tid_cnt, ctx->tid_slots * 8ull, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(special, av.special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   if (special[2]) return fail(ctx, -ENOSPC, "(pid,tid) table overflowed: raise hbtgpu_config.tid_table_log2");
   size_t k = 0;
@@ -1006,13 +1033,12 @@ int hbtgpu_get_top_ips(hbtgpu_ctx* ctx, uint32_t k, uint64_t* ip, uint64_t* coun
   unsigned long long* rcnt = mb.take<unsigned long long>(k);
   unsigned int* d_m = mb.take<unsigned int>(1);
   CK(cudaMemsetAsync(d_m, 0, 4, ctx->stream));
-  const bool tot = ctx->accumulate;
-  k_attr_compact<<<148 * 8, 256, 0, ctx->stream>>>(tot ? ctx->d_ip_keys_tot : ctx->d_ip_keys, tot ? ctx->d_ip_cnt_tot : ctx->d_ip_cnt,
-                                                  ctx->ip_slots - 1, ckey, ccnt, d_m);
+  const AttrView av = attr_view(ctx);
+  k_attr_compact<<<148 * 8, 256, 0, ctx->stream>>>(av.ip_keys, av.ip_cnt, ctx->ip_slots - 1, ckey, ccnt, d_m);
   unsigned int m = 0;
   unsigned long long special[4];
   CK(cudaMemcpyAsync(&m, d_m, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaMemcpyAsync(special, tot ? ctx->d_attr_special_tot : ctx->d_attr_special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(special, av.special, sizeof(special), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   if (special[3]) return fail(ctx, -ENOSPC, "IP table overflowed: raise hbtgpu_config.ip_table_log2");
   if (special[1]) {  // samples whose ip equals the empty-slot marker live in a side counter
@@ -1046,6 +1072,7 @@ int hbtgpu_attr_clear(hbtgpu_ctx* ctx) {
   CK(cudaMemsetAsync(ctx->d_ip_keys_tot, 0xFF, ctx->ip_slots * 8ull, ctx->stream));
   CK(cudaMemsetAsync(ctx->d_ip_cnt_tot, 0, ctx->ip_slots * 8ull, ctx->stream));
   CK(cudaMemsetAsync(ctx->d_attr_special_tot, 0, 4 * 8, ctx->stream));
+  ctx->attr_all_valid = false;
   return 0;
 }
 

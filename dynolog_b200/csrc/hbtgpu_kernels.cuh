@@ -2320,14 +2320,14 @@ __global__ void k_attr_merge(const uint64_t* keys, const unsigned long long* cnt
                              unsigned long long* tot_cnt, uint32_t tot_mask, unsigned long long* overflow) {
   const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
   for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i <= mask; i += stride) {
-    const uint64_t k = keys[i];
+    const uint64_t k = __ldcv(keys + i);  // (the source may be a peer's memory: never through a stale line)
     if (k == ATTR_EMPTY) continue;
     const uint32_t slot = attr_hash(k) & tot_mask;
-    attr_add_from(tot_keys, tot_cnt, tot_mask, k, cnt[i], overflow, slot, reinterpret_cast<volatile uint64_t*>(tot_keys)[slot]);
+    attr_add_from(tot_keys, tot_cnt, tot_mask, k, __ldcv(cnt + i), overflow, slot, reinterpret_cast<volatile uint64_t*>(tot_keys)[slot]);
   }
 }
 __global__ void k_attr_merge_special(const unsigned long long* run, unsigned long long* tot) {
-  if (threadIdx.x < 4) tot[threadIdx.x] += run[threadIdx.x];
+  if (threadIdx.x < 4) tot[threadIdx.x] += __ldcv(run + threadIdx.x);
 }
 
 struct TopBest {

@@ -95,7 +95,7 @@ ABI_SYMBOLS = [
     "hbtgpu_get_stubs", "hbtgpu_compose_tail", "hbtgpu_apply_boundaries", "hbtgpu_stub_bytes",
     "hbtgpu_export_stubs_device", "hbtgpu_apply_boundaries_gathered", "hbtgpu_acc_device", "hbtgpu_stream",
     "hbtgpu_peer_export", "hbtgpu_peer_attach", "hbtgpu_peer_attach_local", "hbtgpu_peer_detach",
-    "hbtgpu_exchange_boundaries", "hbtgpu_merge", "hbtgpu_get_prev_tail",
+    "hbtgpu_exchange_boundaries", "hbtgpu_merge", "hbtgpu_attr_merge", "hbtgpu_get_prev_tail",
     "hbtgpu_math_get_count", "hbtgpu_math_rate", "hbtgpu_math_add_reduce",
     "hbtgpu_math_tsc_to_ktime", "hbtgpu_math_ktime_to_tsc", "hbtgpu_math_per_second_mega",
     "hbtgpu_math_running_ratio", "hbtgpu_get_stats", "hbtgpu_version",
@@ -105,7 +105,7 @@ ABI_SYMBOLS = [
 ]
 
 NOALLOC_MAX_IMAGE_BYTES = 64 << 20
-PEER_HANDLE_BYTES = 192
+PEER_HANDLE_BYTES = 256
 
 _lib = None
 
@@ -422,6 +422,10 @@ class Context:
 
     def merge(self):
         self._ck(self.L.hbtgpu_merge(self.h))
+
+    def attr_merge(self):
+        """IP|TID format: the (pid,tid) histogram and the IP counts of all ranks (peer memory)."""
+        self._ck(self.L.hbtgpu_attr_merge(self.h))
 
     def apply_boundaries(self, prev_tails):
         """prev_tails: ctypes array (Carry * max_cpus): state before this shard, per cpu."""

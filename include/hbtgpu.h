@@ -319,10 +319,22 @@ int hbtgpu_apply_boundaries_gathered(hbtgpu_ctx* ctx, const void* device_gathere
  *                               partial sums.  Requires the same t0 / bucket_ns / n_buckets /
  *                               metrics on all ranks.  Integer sums: bit-identical to one
  *                               context over the whole capture, whatever the order.
+ *   hbtgpu_attr_merge           IP|TID format (last bullet): every rank ends up
+ *                               with the (pid,tid) histogram and the sampled-IP counts of ALL
+ *                               ranks.  A rank offers its totals over its runs
+ *                               (HBTGPU_F_ACCUMULATE_ATTR) or else its last run's tables; every
+ *                               rank inserts every rank's entries into an empty table of its own
+ *                               (ordinary loads over NVLink) -- the full merge, exact: no top-K'
+ *                               candidates, no recount.  Afterwards hbtgpu_get_tid_histogram /
+ *                               hbtgpu_get_top_ips return the merged tables (until the next
+ *                               hbtgpu_run or hbtgpu_attr_clear).  Same table sizes on all ranks;
+ *                               a merged table that overflows is reported by the getters
+ *                               (-ENOSPC), never silently truncated.  Needs no
+ *                               hbtgpu_exchange_boundaries first.
  * All ranks must issue the same sequence of these calls.  A rank that waits longer than 4 s for
  * a peer gives up: the next hbtgpu_sync returns -ETIMEDOUT (nothing hangs).
  * Contexts must have HBTGPU_F_EXTERNAL_CARRY.  hbtgpu_destroy detaches. */
-#define HBTGPU_PEER_HANDLE_BYTES 192
+#define HBTGPU_PEER_HANDLE_BYTES 256
 int hbtgpu_peer_export(hbtgpu_ctx* ctx, uint32_t world, void* handle /* HBTGPU_PEER_HANDLE_BYTES */);
 /* handles: world * HBTGPU_PEER_HANDLE_BYTES, in rank order (this rank's own included) */
 int hbtgpu_peer_attach(hbtgpu_ctx* ctx, uint32_t world, uint32_t rank, const void* handles);
@@ -332,6 +344,7 @@ int hbtgpu_peer_detach(hbtgpu_ctx* ctx);
 #define HBTGPU_EXCHANGE_NO_DERIVE 0x1u /* hbtgpu_merge follows and derives from the totals */
 int hbtgpu_exchange_boundaries(hbtgpu_ctx* ctx, uint32_t flags);
 int hbtgpu_merge(hbtgpu_ctx* ctx);
+int hbtgpu_attr_merge(hbtgpu_ctx* ctx);
 
 /* Shard mode, after the boundaries were applied (any of the three ways): the generator state in
  * front of this rank's shard, as the fold over the earlier ranks found it. */
