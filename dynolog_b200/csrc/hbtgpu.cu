@@ -84,6 +84,8 @@ struct hbtgpu_ctx {
   StreamDesc* d_streams = nullptr;
   size_t cap_chunks = 0, cap_io = 0, cap_images = 0;
   uint64_t *d_rows = nullptr, *d_rec_off = nullptr;
+  uint64_t* d_row_times = nullptr;  // [row][2]: tstamp, duration again, densely
+  size_t cap_row_times = 0;
   uint32_t *d_rec_type = nullptr, *d_rec_size = nullptr;
   size_t cap_rows = 0, cap_rec_off = 0, cap_rec_type = 0, cap_rec_size = 0;
   void* d_math = nullptr;
@@ -295,6 +297,7 @@ Params make_params(hbtgpu_ctx* ctx) {
   P.acc = ctx->d_acc;
   P.flags = ctx->d_flags;
   P.rows = ctx->d_rows;
+  P.row_times = ctx->d_row_times;
   P.rec_off = ctx->d_rec_off;
   P.rec_type = ctx->d_rec_type;
   P.rec_size = ctx->d_rec_size;
@@ -454,6 +457,7 @@ int ensure_emitted(hbtgpu_ctx* ctx) {
   }
   const uint32_t n = ctx->cfg.n_events;
   if (int r = ensure(ctx, &ctx->d_rows, &ctx->cap_rows, std::max<uint64_t>(rows, 1) * (n + 2))) return r;
+  if (int r = ensure(ctx, &ctx->d_row_times, &ctx->cap_row_times, std::max<uint64_t>(rows, 1) * 2)) return r;
   {
     if (int r = ensure(ctx, &ctx->d_rec_off, &ctx->cap_rec_off, std::max<uint64_t>(recs, 1))) return r;
     if (int r = ensure(ctx, &ctx->d_rec_type, &ctx->cap_rec_type, std::max<uint64_t>(recs, 1))) return r;
@@ -648,7 +652,7 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
   peer_release(ctx);
   void* ptrs[] = {ctx->arena, ctx->d_carry_in, ctx->d_carry_out, ctx->d_carry_init, ctx->d_head, ctx->d_counters,
                   ctx->d_acc, ctx->d_scaled, ctx->d_metric, ctx->d_valid, ctx->d_flags,
-                  ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows,
+                  ctx->d_chunks, ctx->d_io, ctx->d_images, ctx->d_streams, ctx->d_rows, ctx->d_row_times,
                   ctx->d_rec_off, ctx->d_rec_type, ctx->d_rec_size, ctx->d_math, ctx->d_attr_block,
                   ctx->d_attr_block_tot, ctx->d_attr_block_all, ctx->d_series, ctx->d_boundary_cell,
                   ctx->d_head_extra, ctx->d_dead, ctx->d_stub_block, ctx->d_acc_total};
@@ -959,6 +963,15 @@ int hbtgpu_rows_device(hbtgpu_ctx* ctx, const uint64_t** rows, uint64_t* row_beg
   row_begin[ctx->cfg.max_cpus] = run;
   *rows = ctx->d_rows;
   if (row_stride) *row_stride = ctx->cfg.n_events + 2;
+  return 0;
+}
+
+int hbtgpu_row_times_device(hbtgpu_ctx* ctx, const uint64_t** times, uint64_t* row_begin) {
+  if (!ctx || !times) return -EINVAL;
+  const uint64_t* rows = nullptr;
+  std::vector<uint64_t> rb(ctx->cfg.max_cpus + 1);
+  if (int r = hbtgpu_rows_device(ctx, &rows, row_begin ? row_begin : rb.data(), nullptr)) return r;
+  *times = ctx->d_row_times;
   return 0;
 }
 

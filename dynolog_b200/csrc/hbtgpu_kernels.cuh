@@ -168,6 +168,7 @@ struct Params {
   uint64_t* acc;       // [stream][bucket][F]
   uint32_t* flags;
   uint64_t* rows;      // MODE_EMIT
+  uint64_t* row_times; // MODE_EMIT: {tstamp, duration} of every row again, densely (what the interval slicer reads)
   uint64_t* rec_off;   // MODE_EMIT
   uint32_t* rec_type;
   uint32_t* rec_size;
@@ -938,6 +939,7 @@ __device__ __forceinline__ void decode_tile(Smem& s, const Params& P, const uint
             uint64_t* row = P.rows + (tc.row_base + tc.rows_before + ex_row) * (n + 2);
             row[0] = pts;
             row[1] = ts - pts;
+            reinterpret_cast<ulonglong2*>(P.row_times)[tc.row_base + tc.rows_before + ex_row] = make_ulonglong2(pts, ts - pts);
             for (uint32_t e = 0; e < n; ++e) {
               const uint64_t cur = xform(P, e, buf[p + PRE + 5 + e]);
               const uint64_t prv = (pj != IDX_NONE) ? xform(P, e, buf[pp + PRE + 5 + e]) : C.last[e];
@@ -1470,6 +1472,13 @@ __device__ __forceinline__ uint32_t uniform_segment(Smem& s, const Params& P, co
         P.rec_size[gi] = 8 * S;
       }
       const int jlo = max(max(j0, 0), skip), jhi = min(j0 + 31, K);  // records with a row here
+      if (lane < 31 && jr >= jlo && jr < jhi) {  // the compact copy of the row's times: 16 bytes per lane, consecutive
+        const uint32_t p = entry + jr * S;
+        const uint64_t ts = buf[p + pre + 1];
+        const uint64_t pts = jr ? buf[p - S + pre + 1] : C.ts;
+        reinterpret_cast<ulonglong2*>(P.row_times)[tc.row_base + tc.rows_before + static_cast<uint64_t>(jr - skip)] =
+            make_ulonglong2(pts, ts - pts);
+      }
       if (RW > EMIT_MAX_ROW_WORDS) {
         // wide rows (more than 14 events) do not fit the stage and do not need it: the warp's
         // rows are one contiguous run of words in the output; lane l computes words l, l+32, ...

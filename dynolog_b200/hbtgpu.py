@@ -88,7 +88,7 @@ class Stats(C.Structure):
 ABI_SYMBOLS = [
     "hbtgpu_create", "hbtgpu_destroy", "hbtgpu_last_error", "hbtgpu_set_carry",
     "hbtgpu_submit_image", "hbtgpu_submit_images", "hbtgpu_submit_image_device", "hbtgpu_reset", "hbtgpu_run",
-    "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows", "hbtgpu_rows_device",
+    "hbtgpu_sync", "hbtgpu_get_counters", "hbtgpu_get_carry", "hbtgpu_get_rows", "hbtgpu_rows_device", "hbtgpu_row_times_device",
     "hbtgpu_get_records", "hbtgpu_get_tid_histogram", "hbtgpu_get_top_ips", "hbtgpu_attr_clear",
     "hbtgpu_get_buckets_device", "hbtgpu_get_buckets_host", "hbtgpu_get_buckets_host_async",
     "hbtgpu_derive",
@@ -290,6 +290,12 @@ class Context:
         stride = C.c_uint32(0)
         self._ck(self.L.hbtgpu_rows_device(self.h, C.byref(ptr), C.c_void_p(begin.ctypes.data), C.byref(stride)))
         return ptr.value, begin, stride.value
+
+    def row_times_device(self):
+        """device pointer to {tstamp, duration} of every row, two words per row (row_begin as rows_device)."""
+        ptr = C.c_void_p(0)
+        self._ck(self.L.hbtgpu_row_times_device(self.h, C.byref(ptr), C.c_void_p(0)))
+        return ptr.value
 
     def records(self, cpu):
         n = C.c_size_t(0)

@@ -201,6 +201,11 @@ int hbtgpu_get_rows(hbtgpu_ctx* ctx, uint32_t cpu, uint64_t* rows, size_t cap_ro
  * words each.  *rows is a device pointer; row_begin is a HOST array of max_cpus + 1 entries that
  * the call fills.  Valid until the next hbtgpu_run / hbtgpu_reset. */
 int hbtgpu_rows_device(hbtgpu_ctx* ctx, const uint64_t** rows, uint64_t* row_begin, uint32_t* row_stride);
+/* {tstamp, duration} of the same rows once more, two words per row, densely: all that
+ * IntervalSlicer::makeIntervalIntersectingSlices reads of a row (TraceMonitor.cpp:52-96), so
+ * hbtgpu_islice_release(..., rows = times, row_stride = 2, ...) touches 16 bytes per row instead of
+ * every 64-byte segment of the full rows.  row_begin as above (may be NULL). */
+int hbtgpu_row_times_device(hbtgpu_ctx* ctx, const uint64_t** times, uint64_t* row_begin);
 
 /* Record table of one cpu: (stream byte offset, type, size) of every record the
  * walk visits, in order -- what consume()'s loop steps through (:1415-1572). */

@@ -44,9 +44,10 @@ def main():
     NS = int(sys.argv[2]) if len(sys.argv) > 2 else 200_000
     K = int(sys.argv[3]) if len(sys.argv) > 3 else 100_000
     ALIGN = float(sys.argv[4]) if len(sys.argv) > 4 else 0.001
+    STRIDE = int(sys.argv[5]) if len(sys.argv) > 5 else 10  # words per count row (2: the decode's compact {tstamp, duration})
     import torch
     r = np.random.default_rng(1)
-    protos = [gen_unit(r, NS, K, align=ALIGN) for _ in range(4)]
+    protos = [gen_unit(r, NS, K, align=ALIGN, stride=STRIDE) for _ in range(4)]
     print(f"units {U}, {NS} slices and {K} rows per unit, {ALIGN} of the row boundaries on a slice end")
     us = [protos[u % 4][0] for u in range(U)]
     ur = [protos[u % 4][1] for u in range(U)]

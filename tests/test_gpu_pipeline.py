@@ -121,6 +121,23 @@ def test_rows_and_slices_meet_on_the_device():
             assert np.array_equal(counts, exp["counts"]) and po.slices_as_tuples(out) == po.slices_as_tuples(exp["slices"])
             assert marks[u] == exp["mark"]
         assert units["n_slices"].sum() > 500
+        # the compact copy of the rows' times (hbtgpu_row_times_device) gives the same release
+        from cuda.bindings import runtime as cudart
+        d_times = ctx.row_times_device()
+        n_rows = int(row_begin[-1])
+        times = np.zeros((n_rows, 2), np.uint64)
+        err, = cudart.cudaMemcpy(times.ctypes.data, d_times, 16 * n_rows, cudart.cudaMemcpyKind.cudaMemcpyDeviceToHost)
+        assert int(err) == 0
+        for u in range(n_cpus):
+            assert np.array_equal(times[int(row_begin[u]):int(row_begin[u + 1])], ctx.rows(u)[:, :2])
+        marks2 = np.zeros(n_cpus, np.uint64)
+        units2 = isl.release_device(d_slices, sb, d_times, 2, row_begin, 2**63, flags, marks2)
+        assert np.array_equal(units2["status"], units["status"]) and np.array_equal(units2["n_slices"], units["n_slices"])
+        assert np.array_equal(marks2, marks)
+        for u in range(n_cpus):
+            exp = po.islice_release("port", got_sl["slices"][u], ctx.rows(u), 2**63, flags, 0)
+            counts, out = isl.get(u)
+            assert np.array_equal(counts, exp["counts"]) and po.slices_as_tuples(out) == po.slices_as_tuples(exp["slices"])
     finally:
         gsl.close()
         isl.close()
