@@ -802,7 +802,8 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
 
   if (ctx->d2h_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));  // acc may still be copied out
   CK(cudaEventRecord(ctx->ev_run0, ctx->stream));
-  CK(cudaMemsetAsync(ctx->d_acc, 0, ctx->acc_words * 8, ctx->stream));
+  if (ctx->acc_words & 1) CK(cudaMemsetAsync(ctx->d_acc + ctx->acc_words - 1, 0, 8, ctx->stream));
+  k_zero_desc<<<148 * 8, 256, 0, ctx->stream>>>(reinterpret_cast<ulonglong2*>(ctx->d_acc), ctx->acc_words / 2);
   const bool external = (ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY) != 0;
   // counters, flags, carry-out of streams without images; shard mode: every stream starts from
   // an invalid state (the boundary row is added later)

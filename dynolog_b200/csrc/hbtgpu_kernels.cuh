@@ -2292,6 +2292,15 @@ __global__ void k_clear(const Params P, uint64_t acc_words) {
   }
 }
 
+// The bucket sums start at zero.  Written from the end to the start: what is written last stays
+// in L2, and the decode starts with the first cpu's records -- its first REDs find their lines
+// there instead of reading them back from DRAM.
+__global__ void __launch_bounds__(256) k_zero_desc(ulonglong2* p, uint64_t n16) {
+  const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+  for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n16; i += stride)
+    p[n16 - 1 - i] = make_ulonglong2(0, 0);
+}
+
 // what a run starts from, in one launch: zeroed counters and flags, carry_out := carry_in for
 // streams without images (shard mode: every stream starts from an invalid state)
 __global__ void __launch_bounds__(256) k_prologue(const Params P, hbtgpu_carry* carry_in, uint32_t force_exact) {
@@ -2779,7 +2788,8 @@ template <uint32_t CB>  // cells per block = threads per block (compile-time: th
 __global__ void __launch_bounds__(CB) k_derive_tiled(const DeriveParams D) {
   extern __shared__ __align__(16) uint64_t dsm[];  // [CB][n + 3]
   const uint32_t n = D.n_events, F = n + 3;
-  const uint64_t cell0 = static_cast<uint64_t>(blockIdx.x) * CB;
+  // last cells first: what the decode wrote last is still in L2
+  const uint64_t cell0 = static_cast<uint64_t>(gridDim.x - 1 - blockIdx.x) * CB;
   const uint32_t cells = static_cast<uint32_t>(umin64(CB, D.n_cells - cell0));
   const uint64_t* src = D.acc + cell0 * F;
   for (uint32_t i = threadIdx.x; i < cells * F; i += CB) dsm[i] = src[i];
