@@ -48,7 +48,7 @@ constexpr uint32_t EV_CREATE = 2, EV_DESTROY = 3, EV_IN = 4, EV_WE_START = 7;
 constexpr uint32_t REC_COMM = 3, REC_EXIT = 4, REC_FORK = 7;
 constexpr uint64_t INVALID_TS = ~0ull;
 
-enum { VF_TID0 = 1, VF_DOUBLE_FORK = 2, VF_INTERNAL = 4 };
+enum { VF_TID0 = 1, VF_DOUBLE_FORK = 2, VF_INTERNAL = 4, VF_WIDE_TID = 8 };
 
 struct IsLost {
   const hbtgpu_cs_event* ev;
@@ -104,9 +104,12 @@ struct VidArgs {
   uint32_t n_ops, n_comm, n_touch, n_lost, n_seed, n_items;
   uint32_t next_vid0;
   // items, visiting order
-  uint64_t* key;      // epoch << 32 | tid
-  uint32_t* src;      // kind << 30 | index
+  uint64_t* key;      // epoch << tid_bits | tid: only the bits in use are sorted
+  uint32_t tid_bits;  // 32, or fewer when every thread id fits (VF_WIDE_TID is raised when one does not)
+  uint32_t* src;      // kind << 30 | ET_* << 28 | index
   uint32_t* pos_iota;
+  uint32_t* touch_pos;  // [n_touch] visiting position of every touch event
+  uint32_t* vid_pos;    // by visiting position: the vid the item got (k_vid_apply -> k_vid_tag)
   // sorted
   const uint64_t* key_s;
   const uint32_t* pos_s;
@@ -124,6 +127,16 @@ struct VidArgs {
   unsigned int* flags;
 };
 
+// src of an item: kind (2 bits) | what the touched event is (2 bits: ET_*) | index (28 bits)
+enum : uint32_t { ET_OTHER = 0, ET_CREATE = 1, ET_DESTROY = 2 };
+constexpr uint32_t SRC_IDX_MASK = 0x0FFFFFFFu;
+__device__ __forceinline__ uint32_t src_kind(uint32_t src) { return src >> 30; }
+__device__ __forceinline__ uint32_t src_et(uint32_t src) { return (src >> 28) & 3u; }
+__device__ __forceinline__ uint32_t src_idx(uint32_t src) { return src & SRC_IDX_MASK; }
+
+__device__ __forceinline__ uint32_t key_tid(const VidArgs& A, uint64_t key) {
+  return static_cast<uint32_t>(A.tid_bits < 32 ? key & ((1ull << A.tid_bits) - 1) : key & 0xFFFFFFFFull);
+}
 __device__ __forceinline__ uint32_t comm_gidx(const VidArgs& A, uint32_t c) { return A.op_gidx[A.comm_idx[c]]; }
 
 // items in visiting order: seeds, then touch events and COMM records merged by position
@@ -131,6 +144,7 @@ __global__ void k_vid_items(const VidArgs A) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < A.n_seed) {
     A.key[t] = A.seed_tid[t];  // epoch 0
+    if (A.tid_bits < 32 && (A.seed_tid[t] >> A.tid_bits)) atomicOr(A.flags, VF_WIDE_TID);
     A.src[t] = (KIND_SEED << 30) | t;
     A.pos_iota[t] = t;
     return;
@@ -147,9 +161,14 @@ __global__ void k_vid_items(const VidArgs A) {
     }
     const uint32_t p = A.n_seed + u + lo;
     const uint64_t epoch = lower_bound_u32(A.lost_idx, A.n_lost, gi);
-    A.key[p] = (epoch << 32) | A.ev[gi].tag;
-    A.src[p] = (KIND_EVENT << 30) | u;
+    const hbtgpu_cs_event e = A.ev[gi];
+    const uint32_t tid = e.tag;
+    if (A.tid_bits < 32 && (tid >> A.tid_bits)) atomicOr(A.flags, VF_WIDE_TID);
+    A.key[p] = (epoch << A.tid_bits) | tid;
+    const uint32_t et = e.type == EV_CREATE ? ET_CREATE : e.type == EV_DESTROY ? ET_DESTROY : ET_OTHER;
+    A.src[p] = (KIND_EVENT << 30) | (et << 28) | u;
     A.pos_iota[p] = p;
+    A.touch_pos[u] = p;
   } else if (u < A.n_touch + A.n_comm) {
     const uint32_t c = u - A.n_touch;
     const uint32_t cg = comm_gidx(A, c);
@@ -158,14 +177,16 @@ __global__ void k_vid_items(const VidArgs A) {
     const uint64_t epoch = lower_bound_u32(A.lost_idx, A.n_lost, cg);
     const uint32_t tid = static_cast<uint32_t>(A.ops[A.comm_idx[c]].tid);
     if (tid == 0) atomicOr(A.flags, VF_TID0);
-    A.key[p] = (epoch << 32) | tid;
+    if (A.tid_bits < 32 && (tid >> A.tid_bits)) atomicOr(A.flags, VF_WIDE_TID);
+    A.key[p] = (epoch << A.tid_bits) | tid;
     A.src[p] = (KIND_COMM << 30) | c;
     A.pos_iota[p] = p;
   }
 }
 
 __device__ __forceinline__ bool item_is_exit(const VidArgs& A, uint32_t src) {
-  return (src >> 30) == KIND_EVENT && A.ev[A.touch_idx[src & 0x3FFFFFFFu]].type == EV_DESTROY;
+  (void)A;
+  return src_kind(src) == KIND_EVENT && src_et(src) == ET_DESTROY;
 }
 
 // sorted order: which touches create a vid
@@ -177,7 +198,7 @@ __global__ void k_vid_new(const VidArgs A) {
   bool nw = false;
   if ((src >> 30) != KIND_SEED) {
     nw = k == 0 || A.key_s[k] != A.key_s[k - 1] || item_is_exit(A, A.src[A.pos_s[k - 1]]);
-    if (static_cast<uint32_t>(A.key_s[k]) == 0) atomicOr(A.flags, VF_TID0);  // COMM/EXIT/FORK of tid 0
+    if (key_tid(A, A.key_s[k]) == 0) atomicOr(A.flags, VF_TID0);  // COMM/EXIT/FORK of tid 0
   }
   A.newflag[p] = nw;
 }
@@ -188,7 +209,7 @@ __global__ void k_vid_def(const VidArgs A) {
   const uint32_t p = A.pos_s[k];
   const uint32_t src = A.src[p];
   uint32_t d = 0;
-  if ((src >> 30) == KIND_SEED) d = A.seed_vid[src & 0x3FFFFFFFu];
+  if (src_kind(src) == KIND_SEED) d = A.seed_vid[src_idx(src)];
   else if (A.newflag[p]) d = A.next_vid0 + A.rank[p];
   A.def[k] = d;
 }
@@ -206,14 +227,14 @@ __global__ void k_vid_create(const VidArgs A) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= A.n_items) return;
   const uint32_t p = A.pos_s[k];
-  const uint32_t src = A.src[p], kind = src >> 30, idx = src & 0x3FFFFFFFu;
+  const uint32_t src = A.src[p], kind = src_kind(src), idx = src_idx(src);
   if (kind == KIND_SEED || !A.newflag[p]) return;
   const uint32_t vid = A.vid_s[k];
   if (vid == 0) {
     atomicOr(A.flags, VF_INTERNAL);
     return;
   }
-  const int32_t tid = static_cast<int32_t>(static_cast<uint32_t>(A.key_s[k]));
+  const int32_t tid = static_cast<int32_t>(key_tid(A, A.key_s[k]));
   hbtgpu_cs_thread ti{vid, -1, -1, -1, tid, 0, INVALID_TS, INVALID_TS};
   if (kind == KIND_COMM) {
     ti.pid = A.ops[A.comm_idx[idx]].pid;
@@ -242,33 +263,33 @@ __global__ void k_vid_apply(const VidArgs A) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= A.n_items) return;
   const uint32_t p = A.pos_s[k];
-  const uint32_t src = A.src[p], kind = src >> 30, idx = src & 0x3FFFFFFFu;
+  const uint32_t src = A.src[p], kind = src_kind(src), idx = src_idx(src);
   const uint32_t vid = A.vid_s[k];
   const uint64_t key = A.key_s[k];
-  const uint32_t tid = static_cast<uint32_t>(key);
+  const uint32_t tid = key_tid(A, key);
   if (vid == 0) {
     atomicOr(A.flags, VF_INTERNAL);
     return;
   }
   bool is_exit = false;
   if (kind == KIND_EVENT) {
-    const uint32_t gi = A.touch_idx[idx];
-    const hbtgpu_cs_event e = A.ev[gi];
-    A.ev_out[gi].tag = vid;
-    if (e.type == EV_CREATE) {
+    // the event's tag is written by k_vid_tag, in event order: from here it would be one access
+    // to a random event per item, and that -- not the sort -- was 2/3 of the dictionary's time
+    A.vid_pos[p] = vid;
+    const uint32_t et = src_et(src);
+    if (et == ET_CREATE) {
       // a FORK of a thread that already has a fork time throws in the reference (:322-325):
       // look back over this vid's run for another FORK or for the seed of a forked thread
       for (uint32_t j = k; j > 0;) {
         --j;
         if (A.key_s[j] != key || A.vid_s[j] != vid) break;
         const uint32_t sj = A.src[A.pos_s[j]];
-        if ((sj >> 30) == KIND_EVENT && A.ev[A.touch_idx[sj & 0x3FFFFFFFu]].type == EV_CREATE)
-          atomicOr(A.flags, VF_DOUBLE_FORK);
-        if ((sj >> 30) == KIND_SEED && A.info[vid - 1].fork_ts != INVALID_TS) atomicOr(A.flags, VF_DOUBLE_FORK);
+        if (src_kind(sj) == KIND_EVENT && src_et(sj) == ET_CREATE) atomicOr(A.flags, VF_DOUBLE_FORK);
+        if (src_kind(sj) == KIND_SEED && A.info[vid - 1].fork_ts != INVALID_TS) atomicOr(A.flags, VF_DOUBLE_FORK);
       }
-      A.info[vid - 1].fork_ts = e.tstamp;
-    } else if (e.type == EV_DESTROY) {
-      A.info[vid - 1].end_ts = e.tstamp;
+      A.info[vid - 1].fork_ts = A.ev[A.touch_idx[idx]].tstamp;
+    } else if (et == ET_DESTROY) {
+      A.info[vid - 1].end_ts = A.ev[A.touch_idx[idx]].tstamp;
       is_exit = true;
     }
   } else if (kind == KIND_COMM) {
@@ -284,11 +305,19 @@ __global__ void k_vid_apply(const VidArgs A) {
   }
   // still active after the window: last touch of its group, in the last epoch, not an EXIT
   const bool last_of_group = k + 1 == A.n_items || A.key_s[k + 1] != key;
-  if (last_of_group && (key >> 32) == A.n_lost && !is_exit) {
+  if (last_of_group && (key >> A.tid_bits) == A.n_lost && !is_exit) {
     const unsigned int s = atomicAdd(A.n_out, 1u);
     A.out_tid[s] = tid;
     A.out_vid[s] = vid;
   }
+}
+
+// ... and the touch events take their virtual ids, in event order
+__global__ void k_vid_tag(const VidArgs A) {
+  const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= A.n_touch) return;
+  const uint32_t vid = A.vid_pos[A.touch_pos[u]];
+  if (vid) A.ev_out[A.touch_idx[u]].tag = vid;  // (0: an item without a vid, reported by k_vid_apply)
 }
 
 // switch-ins of tid 0 keep tag 0 (selectNextVid :97-101): nothing to do.  Everything else that
@@ -457,6 +486,7 @@ int hbtgpu_cs_assign_vids_device(hbtgpu_cs_ctx* ctx, hbtgpu_cs_vids* v) {
     b.take<uint32_t>(N_max);  // vid_s
     b.take<uint32_t>(N_max);  // out_tid
     b.take<uint32_t>(N_max);  // out_vid
+    b.take<uint32_t>(N_max);  // touch_pos
     b.take<uint8_t>(std::max(tmp_sort, tmp_scan));
     need1 = b.off + 256;
   }
@@ -487,6 +517,7 @@ int hbtgpu_cs_assign_vids_device(hbtgpu_cs_ctx* ctx, hbtgpu_cs_vids* v) {
   uint32_t* vid_s = b.take<uint32_t>(N_max);
   uint32_t* out_tid = b.take<uint32_t>(N_max);
   uint32_t* out_vid = b.take<uint32_t>(N_max);
+  uint32_t* touch_pos = b.take<uint32_t>(N_max);
   uint8_t* tmp1 = b.take<uint8_t>(std::max(tmp_sort, tmp_scan));
 
   // ---- selections ----
@@ -507,6 +538,8 @@ int hbtgpu_cs_assign_vids_device(hbtgpu_cs_ctx* ctx, hbtgpu_cs_vids* v) {
   VK(cudaStreamSynchronize(st));
   const uint32_t n_comm = h_small[3], n_touch = h_small[4], n_lost = h_small[5];
   const uint32_t N = v->n_seed + n_touch + n_comm;
+  if (static_cast<uint64_t>(v->n_seed) + n_touch + n_comm > SRC_IDX_MASK)
+    return vfail(v, -EOVERFLOW, "more than 2^28 touches of thread ids in one window");
 
   // the thread table can grow by at most one entry per touch; names by one per COMM
   if (int r = grow(v, &v->info, &v->cap_info, static_cast<size_t>(v->next_vid - 1) + n_touch + n_comm + 1,
@@ -536,6 +569,8 @@ int hbtgpu_cs_assign_vids_device(hbtgpu_cs_ctx* ctx, hbtgpu_cs_vids* v) {
   A.key = key;
   A.src = src;
   A.pos_iota = pos_iota;
+  A.touch_pos = touch_pos;
+  A.vid_pos = pos_iota;  // (the sort has consumed pos_iota by the time k_vid_apply writes here)
   A.key_s = key_s;
   A.pos_s = pos_s;
   A.newflag = newflag;
@@ -553,9 +588,23 @@ int hbtgpu_cs_assign_vids_device(hbtgpu_cs_ctx* ctx, hbtgpu_cs_vids* v) {
   uint32_t n_new = 0, n_out = 0;
   if (N) {
     const unsigned grid = (N + 255) / 256;
+    // The sort key is (epoch, tid): radix passes only over the bits in use.  Thread ids are below
+    // 2^22 on Linux (pid_max); 24 bits are tried first, and a window that holds a wider one (the
+    // items kernel notices) is keyed again with all 32.
+    int epoch_bits = 1;
+    while ((static_cast<uint64_t>(n_lost) >> epoch_bits) != 0) ++epoch_bits;
+    A.tid_bits = 24;
     k_vid_items<<<grid, 256, 0, st>>>(A);
+    unsigned int wide = 0;
+    VK(cudaMemcpyAsync(&wide, v->d_small + 2, sizeof(wide), cudaMemcpyDeviceToHost, st));
+    VK(cudaStreamSynchronize(st));
+    if (wide & VF_WIDE_TID) {
+      A.tid_bits = 32;
+      k_vid_items<<<grid, 256, 0, st>>>(A);
+    }
     size_t t = tmp_sort;
-    cub::DeviceRadixSort::SortPairs(tmp1, t, key, key_s, pos_iota, pos_s, static_cast<int>(N), 0, 64, st);
+    cub::DeviceRadixSort::SortPairs(tmp1, t, key, key_s, pos_iota, pos_s, static_cast<int>(N), 0,
+                                    static_cast<int>(A.tid_bits) + epoch_bits, st);
     k_vid_new<<<grid, 256, 0, st>>>(A);
     t = tmp_scan;
     cub::DeviceScan::ExclusiveSum(tmp1, t, newflag, rank, static_cast<int>(N), st);
@@ -564,6 +613,7 @@ int hbtgpu_cs_assign_vids_device(hbtgpu_cs_ctx* ctx, hbtgpu_cs_vids* v) {
     cub::DeviceScan::InclusiveScan(tmp1, t, def, vid_s, LastNonZero(), static_cast<int>(N), st);
     k_vid_create<<<grid, 256, 0, st>>>(A);
     k_vid_apply<<<grid, 256, 0, st>>>(A);
+    if (n_touch) k_vid_tag<<<(n_touch + 255) / 256, 256, 0, st>>>(A);
     VK(cudaGetLastError());
     // number of vids created = rank of the last position + its flag
     uint32_t last_rank = 0, last_flag = 0;

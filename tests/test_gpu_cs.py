@@ -176,6 +176,20 @@ def test_device_dictionary_matches_reference_order(seed, kw):
     assert got["names"] == want["names"]
 
 
+@pytest.mark.parametrize("tid_base", [(1 << 24) - 20, 2_000_000_000])  # (pid_t is signed: below 2^31)
+def test_device_dictionary_with_thread_ids_wider_than_24_bits(tid_base):
+    """The dictionary's sort key is keyed for 24-bit thread ids first (pid_max is 2^22); a window
+    with a wider one is noticed and keyed again with all 32 bits."""
+    streams = rg.random_cs_streams(11, 3, 4000, n_tids=48, p_lost=0.004, p_life=0.05, p_comm=0.03, tid_base=tid_base)
+    want = pyoracle.cs_run("port", streams, tid_level=2)
+    got = hbtgpu_cs.decode(streams, tid_level=2, device_dictionary=True)
+    for cpu in range(len(streams)):
+        for f in ("tstamp", "type", "level", "comp_unit_id", "tag"):
+            assert np.array_equal(got["events"][cpu][f], want["events"][cpu][f]), (cpu, f)
+    assert got["threads"] == want["threads"]
+    assert got["names"] == want["names"]
+
+
 def test_device_dictionary_carries_over_windows():
     """Windows decoded one after the other: the device dictionary keeps the active tids and the
     thread table, so the result equals the host mirror fed the same windows in the same order."""
