@@ -43,6 +43,8 @@
 #include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_select.cuh>
+#include <cub/iterator/counting_input_iterator.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include "hbtgpu.h"
@@ -74,7 +76,8 @@ struct Globals {
   unsigned int a_first[2];  // ... T[0][k] (tid 0)
   unsigned long long n_dropped, n_we_start, n_we_end, n_completed, n_logic;
   unsigned int max_tag;
-  unsigned long long max_ts;
+  unsigned long long max_ts;  // largest sort key (time since min_ts, + 1)
+  unsigned long long min_ts;  // earliest event of the window (every unit's first one is its earliest)
   int depth0;                 // write-error depth the window starts with
   unsigned long long last_ts0;  // last timestamp of the previous window
   unsigned int have;          // bit k: E[k] exists already, bit 2 + k: T[0][k]
@@ -89,13 +92,18 @@ __device__ __forceinline__ bool is_switch(uint32_t t) { return t >= EV_IN && t <
 
 // (1) sort keys, input checks
 __global__ void k_sl_prepare(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ unit_of,
-                             const uint64_t* __restrict__ ub, uint64_t* __restrict__ key, uint32_t* __restrict__ val,
-                             Globals* g) {
+                             const uint64_t* __restrict__ ub, uint64_t* __restrict__ key, uint32_t* __restrict__ key32,
+                             uint32_t* __restrict__ val, Globals* g) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const hbtgpu_cs_event e = ev[i];
   const bool virt = is_virtual(e);
-  key[i] = virt ? 0 : e.tstamp;  // carried states sort in front of the window
+  // Sort key: time since the window's earliest event, + 1; carried states (0) sort in front.
+  // Absolute kernel times have 50 bits, a window's span about 32: fewer radix passes, and
+  // mostly over 4-byte keys (key32 is what is sorted when every key fits)
+  const uint64_t k = virt ? 0 : e.tstamp - g->min_ts + 1;
+  key[i] = k;
+  key32[i] = static_cast<uint32_t>(k);
   val[i] = i;
   uint32_t bad = 0;
   const uint32_t u = unit_of[i];
@@ -114,7 +122,7 @@ __global__ void k_sl_prepare(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
   const unsigned m = __activemask();
   const uint32_t wbad = __reduce_or_sync(m, bad);
   const uint32_t wmax = __reduce_max_sync(m, ((e.type == EV_CREATE || e.type == EV_IN) && e.tag != NA) ? e.tag : 0u);
-  uint64_t wts = virt ? 0 : e.tstamp;  // (a unit's last event would do, but the check above may fail)
+  uint64_t wts = k;  // (a unit's last event would do, but the check above may fail)
   for (int o = 16; o; o >>= 1) {
     const uint64_t other = __shfl_xor_sync(m, wts, o);
     if ((m >> ((threadIdx.x & 31) ^ o)) & 1u) wts = max(wts, other);
@@ -127,9 +135,13 @@ __global__ void k_sl_prepare(const hbtgpu_cs_event* __restrict__ ev, uint32_t n,
   }
 }
 
-__global__ void k_sl_unit_of(const uint64_t* __restrict__ ub, uint32_t n_units, uint32_t* __restrict__ unit_of) {
+__global__ void k_sl_unit_of(const uint64_t* __restrict__ ub, uint32_t n_units, uint32_t* __restrict__ unit_of,
+                             const hbtgpu_cs_event* __restrict__ ev, Globals* g) {
   const uint32_t u = blockIdx.x;
   for (uint64_t i = ub[u] + threadIdx.x; i < ub[u + 1]; i += blockDim.x) unit_of[i] = u;
+  // (parallel form only: slot ub[u] holds the carried state, the unit's first event follows)
+  if (g != nullptr && threadIdx.x == 0 && ub[u] + 1 < ub[u + 1])
+    atomicMin(&g->min_ts, static_cast<unsigned long long>(ev[ub[u] + 1].tstamp));
 }
 
 // (2) merge order: rank, write-error deltas
@@ -231,36 +243,84 @@ __global__ void k_sl_entry_counts(const hbtgpu_cs_event* __restrict__ ev, uint32
 
 __global__ void k_sl_entries(const hbtgpu_cs_event* __restrict__ ev, uint32_t n, const uint32_t* __restrict__ rank,
                              const uint32_t* __restrict__ next, const uint32_t* __restrict__ ecnt,
-                             const uint32_t* __restrict__ eoff, int pos_bits, uint64_t* __restrict__ ekey,
-                             uint32_t* __restrict__ eval) {
+                             const uint32_t* __restrict__ eoff, const uint8_t* __restrict__ cf, int pos_bits,
+                             uint64_t* __restrict__ ekey, uint32_t* __restrict__ eval) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n || ecnt[i] == 0) return;
   const uint64_t tag = ev[i].tag;
   const uint32_t o = eoff[i];
   const uint32_t kind = ev[i].type == EV_CREATE ? K_CREATE : (is_virtual(ev[i]) ? K_CARRIED : K_IN);
-  ekey[o] = (tag << pos_bits) | rank[i];
+  // key: thread id | merge position | `known` of a switch-in -- everything the walk needs of the
+  // event travels with the entry, so that the walk reads its list and nothing else
+  ekey[o] = (tag << (pos_bits + 1)) | (static_cast<uint64_t>(rank[i]) << 1) | ((cf[i] & CF_KNOWN) ? 1u : 0u);
   eval[o] = (i << 2) | kind;  // (fewer than 2^30 events per call)
   if (ecnt[i] == 2) {
-    ekey[o + 1] = (tag << pos_bits) | rank[next[i]];
+    ekey[o + 1] = (tag << (pos_bits + 1)) | (static_cast<uint64_t>(rank[next[i]]) << 1);
     eval[o + 1] = (i << 2) | K_PARK;
   }
 }
 
-// (4) one thread per thread id: walk its events in merge order
+// (4) one thread per thread id: walk its events in merge order.  The steps of a walk depend on
+// each other, so a step must not wait for memory: it reads its list (consecutive entries), finds
+// the reset epoch of an entry by its merge position in the short list of reset positions, keeps
+// the one switch-in it may have to come back to in registers, and sends its flags off with
+// atomics that return nothing.  (Reading own_epoch[i] and cf[i] of a random event in every step
+// made the longest list, times a memory latency per entry, the duration of the kernel.)
+__device__ __forceinline__ void cf_or(uint8_t* cf, uint32_t i, uint32_t flag) {
+  atomicOr(reinterpret_cast<unsigned int*>(cf + (i & ~3u)), flag << (8 * (i & 3u)));
+}
+// (the first entry of every thread id's list, for cub::DeviceSelect::If over the entry indices: the
+// walkers are then neighbours in their warps -- one thread per ENTRY that returns unless it is a
+// first one left one lane in fifty working)
+struct IsListHead {
+  const uint64_t* ekey;
+  int sh;
+  __device__ bool operator()(uint32_t e) const { return e == 0 || (ekey[e] >> sh) != (ekey[e - 1] >> sh); }
+};
 __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint32_t* __restrict__ eval, uint32_t n_entries, int pos_bits,
-                          const uint32_t* __restrict__ own_epoch, uint8_t* __restrict__ cf,
+                          const uint32_t* __restrict__ heads, const uint32_t* __restrict__ n_heads,
+                          const uint32_t* __restrict__ rpos /* merge positions of the resets, ascending */,
+                          const uint32_t* __restrict__ n_rpos, const uint32_t* __restrict__ own_epoch, uint8_t* cf,
                           uint32_t* __restrict__ t_create /* [n_tags][2]: event that created T[v][k] */,
                           uint8_t* __restrict__ pt_flags /* [n_tags][2]: bit 0 exists, bit 1 dormant */,
                           uint32_t* __restrict__ last_epoch /* [n_tags] */) {
-  const uint32_t e0 = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e0 >= n_entries) return;
-  const uint32_t v = static_cast<uint32_t>(ekey[e0] >> pos_bits);
-  if (e0 > 0 && static_cast<uint32_t>(ekey[e0 - 1] >> pos_bits) == v) return;  // not the first entry of v
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= *n_heads) return;
+  const uint32_t e0 = heads[j];
+  const int sh = pos_bits + 1;
+  const uint32_t v = static_cast<uint32_t>(ekey[e0] >> sh);
   bool ex1 = pt_flags[2 * v + 1] & 1, ln1 = pt_flags[2 * v + 1] & 2, ex0 = pt_flags[2 * v] & 1, ln0 = pt_flags[2 * v] & 2;
   uint32_t cur_epoch = 0;  // what was carried over is valid until the window's first reset
-  for (uint32_t e = e0; e < n_entries && static_cast<uint32_t>(ekey[e] >> pos_bits) == v; ++e) {
+  const uint32_t R = *n_rpos;
+  uint32_t r = 0;          // resets at merge positions <= the current entry's
+  uint32_t in_i = NOIDX, in_ep = 0;  // the activation a parking entry most likely belongs to
+  bool in_pick = false;
+  const uint64_t pos_mask = (1ull << pos_bits) - 1;
+  for (uint32_t e = e0; e < n_entries; ++e) {
+    const uint64_t key = ekey[e];
+    if (static_cast<uint32_t>(key >> sh) != v) break;
     const uint32_t kind = eval[e] & 3, i = eval[e] >> 2;
-    const uint32_t ep = own_epoch[i];  // (a parking switch-out is in its switch-in's epoch)
+    uint32_t ep;  // (a parking switch-out is in its switch-in's epoch)
+    if (kind == K_PARK) {
+      ep = i == in_i ? in_ep : own_epoch[i];
+    } else {
+      const uint32_t pos = static_cast<uint32_t>((key >> 1) & pos_mask);
+      if (r < R && rpos[r] <= pos) {  // gallop, then bisect: positions only move forward
+        uint32_t step = 1, lo = r;
+        while (lo + step < R && rpos[lo + step] <= pos) {
+          lo += step;
+          step <<= 1;
+        }
+        uint32_t hi = lo + step < R ? lo + step : R;  // rpos[lo] <= pos, rpos[hi] > pos (or hi == R)
+        while (hi - lo > 1) {
+          const uint32_t mid = lo + (hi - lo) / 2;
+          if (rpos[mid] <= pos) lo = mid;
+          else hi = mid;
+        }
+        r = hi;
+      }
+      ep = r;
+    }
     if (ep != cur_epoch) {               // resetState_, :636-652: dormant lists cleared
       ln1 = ln0 = false;
       cur_epoch = ep;
@@ -268,29 +328,39 @@ __global__ void k_sl_walk(const uint64_t* __restrict__ ekey, const uint32_t* __r
     if (kind == K_CREATE) {  // handleThreadLifetime_, :722-732
       if (!ex1) {
         ex1 = true;
-        cf[i] |= CF_T1;
+        cf_or(cf, i, CF_T1);
         t_create[2 * v + 1] = i;
       } else {
-        cf[i] |= CF_BURN;  // emplace fails, next_stack_id_++ was evaluated
+        cf_or(cf, i, CF_BURN);  // emplace fails, next_stack_id_++ was evaluated
       }
       ln1 = true;
     } else if (kind == K_IN) {
-      const bool known = cf[i] & CF_KNOWN;
+      const bool known = key & 1;
+      in_i = i;
+      in_ep = ep;
       if (known && ex1 && ln1) {  // activateStackStateThatContains_, :611-626
         ln1 = false;
-        cf[i] |= CF_PICK_T1;
+        in_pick = true;
+        cf_or(cf, i, CF_PICK_T1);
       } else {                    // {v} with unknown levels, :632-633 / exact match :586-609
+        in_pick = false;
         if (!ex0) {
           ex0 = true;
-          cf[i] |= CF_T0;
+          cf_or(cf, i, CF_T0);
           t_create[2 * v] = i;
         }
         ln0 = false;
       }
     } else if (kind == K_PARK) {  // the next switch event on that unit parks the state: handleLastState_, :761-768
-      if (cf[i] & CF_PICK_T1) ln1 = true;
+      // (not the latest activation: the thread runs on two units at once -- read what that one took)
+      const bool pick = i == in_i ? in_pick : (*reinterpret_cast<volatile uint8_t*>(cf + i) & CF_PICK_T1) != 0;
+      if (pick) ln1 = true;
       else ln0 = true;
-    }  // K_CARRIED: the state was activated in an earlier window; it is neither created nor unlinked here
+    } else {  // K_CARRIED: the state was activated in an earlier window; it is neither created nor unlinked here
+      in_i = i;
+      in_ep = ep;
+      in_pick = (cf[i] & CF_PICK_T1) != 0;
+    }
   }
   pt_flags[2 * v + 1] = (ex1 ? 1 : 0) | (ln1 ? 2 : 0);
   pt_flags[2 * v] = (ex0 ? 1 : 0) | (ln0 ? 2 : 0);
@@ -857,7 +927,7 @@ int run_general(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const uint6
   Globals gh;
   memset(&gh, 0, sizeof(gh));
   if (N) {
-    k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of);
+    k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of, nullptr, nullptr);
     k_gen_prepare<<<blocks(N), 256, 0, st>>>(d_ev, N, d_unit_of, d_ub, g.h.last_ts, d_key, d_val, d_g);
     SK(cudaGetLastError());
     SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
@@ -996,11 +1066,20 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
                                   static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), 0, 64, st);
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort2, static_cast<uint64_t*>(nullptr), static_cast<uint64_t*>(nullptr),
                                   static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(2 * static_cast<uint64_t>(N)), 0, 64, st);
+  cub::DeviceRadixSort::SortPairs(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr),
+                                  static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), 0, 32, st);
+  tmp_sort = std::max(tmp_sort, t2);
   cub::DeviceScan::InclusiveSum(nullptr, tmp_scan, static_cast<int32_t*>(nullptr), static_cast<int32_t*>(nullptr), static_cast<int>(N), st);
   cub::DeviceScan::ExclusiveScan(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), MaxOp(), 0u, static_cast<int>(N), st);
   tmp_scan = std::max(tmp_scan, t2);
   cub::DeviceScan::ExclusiveSum(nullptr, t2, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr),
                                 static_cast<int>(c->next_id + N + 9), st);  // events, or all stack ids so far
+  tmp_scan = std::max(tmp_scan, t2);
+  cub::DeviceSelect::Flagged(nullptr, t2, cub::CountingInputIterator<uint32_t>(0), static_cast<uint32_t*>(nullptr),
+                             static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(N), st);
+  tmp_scan = std::max(tmp_scan, t2);
+  cub::DeviceSelect::If(nullptr, t2, cub::CountingInputIterator<uint32_t>(0), static_cast<uint32_t*>(nullptr),
+                        static_cast<uint32_t*>(nullptr), static_cast<int>(2 * static_cast<uint64_t>(N)), IsListHead{nullptr, 0}, st);
   tmp_scan = std::max(tmp_scan, t2);
   const size_t tmp_bytes = std::max(std::max(tmp_sort, tmp_sort2), tmp_scan) + 256;
   const size_t n1 = static_cast<size_t>(N) + 1;
@@ -1014,6 +1093,8 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   add(2 * n1, 8); add(2 * n1, 4); add(2 * n1, 8); add(2 * n1, 4);  // entries + sorted
   add(n1, 4); add(n1, 4); add(n1, 4); add(n1, 4);               // idcnt, idbase, sflag, soff
   add(n1, 32); add(n_units + 2, 8);                             // slices, slice_begin
+  add(n1, 4); add(64, 4); add(n1, 4);                           // reset positions, their number (and the lists'), list heads
+  add(n1, 4); add(n1, 4);                                       // 4-byte sort keys
   add(1, sizeof(Globals)); add(tmp_bytes, 1);
   if (c->arena_cap < need) {
     cudaFree(c->arena);
@@ -1056,6 +1137,11 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   auto* d_soff = carve<uint32_t>(c, n1);
   auto* d_slices = carve<hbtgpu_slice>(c, n1);
   auto* d_slice_begin = carve<uint64_t>(c, n_units + 2);
+  auto* d_rpos = carve<uint32_t>(c, n1);
+  auto* d_nrpos = carve<uint32_t>(c, 64);
+  auto* d_heads = carve<uint32_t>(c, n1);
+  auto* d_key32 = carve<uint32_t>(c, n1);
+  auto* d_key32_s = carve<uint32_t>(c, n1);
   auto* d_g = carve<Globals>(c, 1);
   auto* d_tmp = carve<char>(c, tmp_bytes);
   if (!d_tmp) return sfail(c, -EIO, "internal: arena too small");
@@ -1073,6 +1159,7 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
   memset(&g0, 0, sizeof(g0));
   g0.e_first[0] = g0.e_first[1] = g0.a_first[0] = g0.a_first[1] = NOIDX;
   g0.cand = NOIDX;
+  g0.min_ts = ~0ull;
   g0.depth0 = c->depth;
   g0.last_ts0 = c->last_ts;
   g0.have = (c->e_id[0] != NONE64 ? 1u : 0u) | (c->e_id[1] != NONE64 ? 2u : 0u) | (c->a_id[0] != NONE64 ? 4u : 0u) |
@@ -1082,13 +1169,16 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
 
   Globals gh = g0;
   size_t t = tmp_bytes;
-  k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of);
-  k_sl_prepare<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_key, d_val, d_g);
+  k_sl_unit_of<<<n_units, 256, 0, st>>>(d_ub, n_units, d_unit_of, ev, d_g);
+  k_sl_prepare<<<blocks(N), 256, 0, st>>>(ev, N, d_unit_of, d_ub, d_key, d_key32, d_val, d_g);
   SK(cudaMemcpyAsync(&gh, d_g, sizeof(gh), cudaMemcpyDeviceToHost, st));
   SK(cudaStreamSynchronize(st));
-  int ts_bits = 1;  // radix passes only over the bits the timestamps use
+  int ts_bits = 1;  // radix passes only over the bits the keys use
   while (ts_bits < 64 && (gh.max_ts >> ts_bits) != 0) ++ts_bits;
-  cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key, d_key_s, d_val, d_order, static_cast<int>(N), 0, ts_bits, st);
+  if (ts_bits <= 32)
+    cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key32, d_key32_s, d_val, d_order, static_cast<int>(N), 0, ts_bits, st);
+  else
+    cub::DeviceRadixSort::SortPairs(d_tmp, t, d_key, d_key_s, d_val, d_order, static_cast<int>(N), 0, ts_bits, st);
   k_sl_gather<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_rank, d_delta, d_start);
   t = tmp_bytes;
   cub::DeviceScan::InclusiveSum(d_tmp, t, d_delta, d_depth, static_cast<int>(N), st);
@@ -1183,12 +1273,19 @@ int hbtgpu_slicer_run(hbtgpu_slicer_ctx* c, const hbtgpu_cs_event* events, const
     int pos_bits = 1, tag_bits = 1;  // key = tag << pos_bits | merge position
     while ((static_cast<uint64_t>(N) >> pos_bits) != 0) ++pos_bits;
     while ((static_cast<uint64_t>(gh.max_tag) >> tag_bits) != 0) ++tag_bits;
-    k_sl_entries<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_next, d_ecnt, d_eoff, pos_bits, d_ekey, d_eval);
+    k_sl_entries<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_next, d_ecnt, d_eoff, d_cf, pos_bits, d_ekey, d_eval);
     t = tmp_bytes;
     cub::DeviceRadixSort::SortPairs(d_tmp, t, d_ekey, d_ekey_s, d_eval, d_eval_s, static_cast<int>(n_entries), 0,
-                                    pos_bits + tag_bits, st);
-    k_sl_walk<<<blocks(n_entries, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, pos_bits, d_own_epoch, d_cf,
-                                                      d_tcreate, c->p_flags, d_last_epoch);
+                                    pos_bits + 1 + tag_bits, st);
+    // the merge positions where a reset happens (few): the walks find an entry's epoch there
+    t = tmp_bytes;
+    cub::DeviceSelect::Flagged(d_tmp, t, cub::CountingInputIterator<uint32_t>(0), d_start, d_rpos, d_nrpos, static_cast<int>(N), st);
+    t = tmp_bytes;
+    cub::DeviceSelect::If(d_tmp, t, cub::CountingInputIterator<uint32_t>(0), d_heads, d_nrpos + 1, static_cast<int>(n_entries),
+                          IsListHead{d_ekey_s, pos_bits + 1}, st);
+    const uint32_t max_lists = static_cast<uint32_t>(std::min<uint64_t>(n_entries, static_cast<uint64_t>(gh.max_tag) + 1));
+    k_sl_walk<<<blocks(max_lists, 128), 128, 0, st>>>(d_ekey_s, d_eval_s, n_entries, pos_bits, d_heads, d_nrpos + 1, d_rpos,
+                                                      d_nrpos, d_own_epoch, d_cf, d_tcreate, c->p_flags, d_last_epoch);
   }
   k_sl_firsts<<<blocks(N), 256, 0, st>>>(ev, N, d_rank, d_eff, d_rin, d_cf, d_g);
   k_sl_id_counts<<<blocks(N), 256, 0, st>>>(ev, d_order, N, d_eff, d_rin, d_cf, d_g, d_idcnt);
