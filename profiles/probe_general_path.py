@@ -1,0 +1,14 @@
+"""One configuration of profiles/perf_probe.py alone, for ncu: the forced general path (classify every
+word, pointer jumping, listed samples) on a cfg3-like capture.
+  ncu --set full -k regex:k_decode -s 2 -c 1 ... python profiles/probe_general_path.py [general|mixed]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import perf_probe
+from dynolog_b200 import hbtgpu
+
+what = sys.argv[1] if len(sys.argv) > 1 else "general"
+if what == "general":
+    perf_probe.probe("cfg3 force_general", 3, 64, 8, 70000, max_bytes_per_cpu=16 << 20, flags=hbtgpu.F_FORCE_GENERAL)
+else:
+    perf_probe.probe("cfg3-like, THROTTLE pair every 5-10", 3, 64, 8, 70000, max_bytes_per_cpu=16 << 20,
+                     throttle=(5, 10), lost=(200, 2000))
