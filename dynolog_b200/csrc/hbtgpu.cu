@@ -637,6 +637,7 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
       set_smem(ctx, k_decode<false, MODE_AGG, 0>, decode_smem_bytes<MODE_AGG, 0>(TILE_MAX_BYTES)) ||
       set_smem(ctx, k_decode<false, MODE_EMIT, 0>, decode_smem_bytes<MODE_EMIT, 0>(TILE_MAX_BYTES)) ||
       set_smem(ctx, k_decode<true, MODE_AGG, 2>, decode_smem_bytes<MODE_AGG, 2>(TILE_MAX_BYTES)) ||
+      set_smem(ctx, k_decode<true, MODE_AGG, 2, 4>, decode_smem_bytes<MODE_AGG, 2>(TILE_MAX_BYTES)) ||
       set_smem(ctx, k_decode<false, MODE_AGG, 2>, decode_smem_bytes<MODE_AGG, 2>(TILE_MAX_BYTES)) ||
       set_smem(ctx, k_decode<false, MODE_EMIT, 2>, decode_smem_bytes<MODE_EMIT, 2>(TILE_MAX_BYTES)))
     return bail(-EIO);
@@ -826,7 +827,8 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   if (nc) {
     if (timed) CK(cudaEventRecord(ctx->ev_dec0[ctx->ev_pending], ctx->stream));
     if (!force_exact) {
-      if (P.pre) k_decode<true, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P);
+      if (P.pre && P.n_events == 4) k_decode<true, MODE_AGG, 2, 4><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P);
+      else if (P.pre) k_decode<true, MODE_AGG, 2><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 2>(P.tile_bytes), ctx->stream>>>(P);
       else if (P.n_events == 8) k_decode<true, MODE_AGG, 0, 8><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
       else if (P.n_events == 4) k_decode<true, MODE_AGG, 0, 4><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
       else k_decode<true, MODE_AGG, 0><<<static_cast<unsigned>(nc), NT, decode_smem_bytes<MODE_AGG, 0>(P.tile_bytes), ctx->stream>>>(P);
