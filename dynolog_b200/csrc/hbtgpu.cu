@@ -42,6 +42,9 @@ struct hbtgpu_ctx {
   cudaStream_t stream = nullptr;
   cudaStream_t d2h_stream = nullptr;  // result copies that overlap the next submit
   cudaEvent_t ev_results = nullptr, ev_d2h = nullptr;
+  // shard mode: the head stubs need only the images, so k_head runs beside the decode
+  cudaStream_t aux_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool d2h_pending = false;
   cudaEvent_t ev_run0 = nullptr, ev_run1 = nullptr;
   // one event pair per hbtgpu_run around the decode+aggregate kernel, harvested at sync
@@ -569,6 +572,9 @@ int hbtgpu_create(const hbtgpu_config* cfg, hbtgpu_ctx** out) {
   CKC(cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking));
   CKC(cudaEventCreateWithFlags(&ctx->ev_results, cudaEventDisableTiming));
   CKC(cudaEventCreateWithFlags(&ctx->ev_d2h, cudaEventDisableTiming));
+  CKC(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
   CKC(cudaEventCreate(&ctx->ev_run0));
   CKC(cudaEventCreate(&ctx->ev_run1));
   for (int i = 0; i < hbtgpu_ctx::kEvRing; ++i) {
@@ -669,7 +675,11 @@ void hbtgpu_destroy(hbtgpu_ctx* ctx) {
     cudaStreamSynchronize(ctx->d2h_stream);
     cudaStreamDestroy(ctx->d2h_stream);
   }
-  for (cudaEvent_t e : {ctx->ev_results, ctx->ev_d2h})
+  if (ctx->aux_stream) {
+    cudaStreamSynchronize(ctx->aux_stream);
+    cudaStreamDestroy(ctx->aux_stream);
+  }
+  for (cudaEvent_t e : {ctx->ev_results, ctx->ev_d2h, ctx->ev_fork, ctx->ev_join})
     if (e) cudaEventDestroy(e);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -806,6 +816,16 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   if (ctx->acc_words & 1) CK(cudaMemsetAsync(ctx->d_acc + ctx->acc_words - 1, 0, 8, ctx->stream));
   k_zero_desc<<<148 * 8, 256, 0, ctx->stream>>>(reinterpret_cast<ulonglong2*>(ctx->d_acc), ctx->acc_words / 2);
   const bool external = (ctx->cfg.flags & HBTGPU_F_EXTERNAL_CARRY) != 0;
+  if (external) {
+    // what lies in front of every cpu's first SAMPLE (the head stubs): read from the images alone,
+    // so it runs on a second stream beside the decode and is joined at the end of the run
+    CK(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
+    k_head<<<(ns + 127) / 128, 128, 0, ctx->aux_stream>>>(P);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev_join, ctx->aux_stream));
+    ++launches;
+  }
   // counters, flags, carry-out of streams without images; shard mode: every stream starts from
   // an invalid state (the boundary row is added later)
   {
@@ -856,9 +876,7 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
     launches += 3;
   }
   if (external) {
-    k_head<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(P);
-    CK(cudaGetLastError());
-    ++launches;
+    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
   } else {
     if (int r = launch_derive(ctx)) return r;
     ++launches;
