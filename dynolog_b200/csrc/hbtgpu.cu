@@ -368,8 +368,11 @@ DeriveParams derive_params(hbtgpu_ctx* ctx) {
   return D;
 }
 
-int launch_derive(hbtgpu_ctx* ctx) {
-  if (ctx->d2h_pending) {  // do not overwrite tensors that are still being copied out
+// st: the stream (default: the context's); only_if: launch a pass that returns at once unless
+// *only_if != 0 (the exact path has replaced the sums)
+int launch_derive(hbtgpu_ctx* ctx, cudaStream_t st = nullptr, const uint32_t* only_if = nullptr) {
+  if (!st) st = ctx->stream;
+  if (ctx->d2h_pending && st == ctx->stream) {  // do not overwrite tensors that are still being copied out
     CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));
     ctx->d2h_pending = false;
   }
@@ -381,10 +384,10 @@ int launch_derive(hbtgpu_ctx* ctx) {
   const uint64_t blocks = (ctx->n_cells + cb - 1) / cb;
   const size_t smem = static_cast<size_t>(cb) * F * 8;
   const unsigned grid = static_cast<unsigned>(blocks);
-  if (cb == 256) k_derive_tiled<256><<<grid, 256, smem, ctx->stream>>>(D);
-  else if (cb == 128) k_derive_tiled<128><<<grid, 128, smem, ctx->stream>>>(D);
-  else if (cb == 64) k_derive_tiled<64><<<grid, 64, smem, ctx->stream>>>(D);
-  else k_derive_tiled<32><<<grid, 32, smem, ctx->stream>>>(D);
+  if (cb == 256) k_derive_tiled<256><<<grid, 256, smem, st>>>(D, only_if);
+  else if (cb == 128) k_derive_tiled<128><<<grid, 128, smem, st>>>(D, only_if);
+  else if (cb == 64) k_derive_tiled<64><<<grid, 64, smem, st>>>(D, only_if);
+  else k_derive_tiled<32><<<grid, 32, smem, st>>>(D, only_if);
   CK(cudaGetLastError());
   ctx->derived = true;
   return 0;
@@ -809,6 +812,7 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   const size_t nc = ctx->chunks.size();
   const bool force_exact = (ctx->cfg.flags & HBTGPU_F_FORCE_EXACT) != 0;
   uint32_t launches = 0;
+  bool derive_forked = false;
   Params P = make_params(ctx);
 
   if (ctx->d2h_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h, 0));  // acc may still be copied out
@@ -855,6 +859,17 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
       ++launches;
     }
     if (timed) CK(cudaEventRecord(ctx->ev_dec1[ctx->ev_pending++], ctx->stream));
+    if (!force_exact && !external) {
+      // The derive step starts on the second stream as soon as the sums are there, beside the
+      // verification and the (nearly always idle) launches of the exact path; if that path does
+      // run, a second derive pass follows it (below), else that pass returns at once.
+      CK(cudaEventRecord(ctx->ev_fork, ctx->stream));
+      CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
+      if (int r = launch_derive(ctx, ctx->aux_stream)) return r;
+      CK(cudaEventRecord(ctx->ev_join, ctx->aux_stream));
+      derive_forked = true;
+      ++launches;
+    }
     if (!force_exact) {
       k_verify<<<static_cast<unsigned>((nc + 255) / 256), 256, 0, ctx->stream>>>(P);
       ++launches;
@@ -877,6 +892,10 @@ int hbtgpu_run(hbtgpu_ctx* ctx) {
   }
   if (external) {
     CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+  } else if (derive_forked) {
+    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+    if (int r = launch_derive(ctx, ctx->stream, ctx->d_flags + FLAG_NEED_EXACT)) return r;
+    ++launches;
   } else {
     if (int r = launch_derive(ctx)) return r;
     ++launches;

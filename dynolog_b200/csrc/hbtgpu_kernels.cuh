@@ -2785,7 +2785,8 @@ __global__ void __launch_bounds__(128) k_derive_cells(const DeriveParams D, cons
 // picks CB (a power of two <= 256) so that the tile fits ~40 KiB of shared memory.
 constexpr int DERIVE_CELLS = 256;
 template <uint32_t CB>  // cells per block = threads per block (compile-time: the copy loops unroll)
-__global__ void __launch_bounds__(CB) k_derive_tiled(const DeriveParams D) {
+__global__ void __launch_bounds__(CB) k_derive_tiled(const DeriveParams D, const uint32_t* only_if = nullptr) {
+  if (only_if != nullptr && *only_if == 0) return;  // (the pass after the exact path: it did not run)
   extern __shared__ __align__(16) uint64_t dsm[];  // [CB][n + 3]
   const uint32_t n = D.n_events, F = n + 3;
   // last cells first: what the decode wrote last is still in L2
