@@ -70,6 +70,7 @@ struct CsSmem {
   uint32_t pred_lost;           // ... and whether it was a LOST (in_write_errors_)
   uint32_t n_ev, n_ops;         // events / ops of this chunk so far
   uint32_t seg_k, ew, bad, wl;
+  uint32_t wmin[NWARP];         // per warp: first record of the run that is no 32-byte SWITCH
   uint32_t cnt[16];
 };
 
@@ -339,33 +340,41 @@ __device__ __forceinline__ void cs_chunk(const Params& P, const CsOut& O, CsSmem
     const uint32_t wt = min(static_cast<uint32_t>(CS_TILE_BYTES), chunk_len - tile_rel) / 8;
     if (next_rel < tile_rel + 8 * wt) {
       uint32_t ew = (next_rel - tile_rel) / 8;  // chain position, tile-relative words
+      bool mixed = false;  // the tile has shown another record: look one record per thread ahead only
       for (;;) {
         // ---- a run of 32-byte SWITCH records from ew on ----
         const uint32_t Kall = (wt - ew + 3) / 4;
+        // (a tile with other records in it is walked in runs that end at the next of them: testing
+        // the whole rest of the tile for every run would be quadratic)
+        const uint32_t Kscan = mixed ? min(Kall, static_cast<uint32_t>(NT)) : Kall;
         uint32_t first_bad = 0xFFFFFFFFu;
         uint64_t hd[CS_RPT];
 #pragma unroll
         for (int i = 0; i < CS_RPT; ++i) {
           const uint32_t j = threadIdx.x + i * NT;
           hd[i] = 0;
-          if (j < Kall) {
+          if (j < Kscan) {
             hd[i] = buf[ew + 4 * j];
             // the last record of the image may be cut short: it is not part of the run
             const bool whole = chunk_abs + tile_rel + 8ull * (ew + 4 * j) + 32 <= limit_abs;
             if (!(cs_is_switch32(hd[i]) && whole)) first_bad = min(first_bad, j);
           }
         }
-        uint32_t K = Kall;
-        if (!__syncthreads_and(first_bad == 0xFFFFFFFFu)) {
-          if (threadIdx.x == 0) s.seg_k = Kall;
-          __syncthreads();
-          if (first_bad != 0xFFFFFFFFu) atomicMin(&s.seg_k, first_bad);
-          __syncthreads();
-          K = s.seg_k;
+        // where the run ends: one barrier (a warp's minimum by __reduce_min_sync, the block's from
+        // the six words) -- a tile with many other records pays this once per record
+        {
+          const uint32_t wm = __reduce_min_sync(0xffffffffu, first_bad);
+          if ((threadIdx.x & 31) == 0) s.wmin[threadIdx.x >> 5] = wm;
         }
+        __syncthreads();
+        uint32_t K = Kscan;
+#pragma unroll
+        for (int w = 0; w < NWARP; ++w) K = min(K, s.wmin[w]);
+        uint32_t e_base_of_run = 0;
         if (K > 0) {
           const uint32_t pl = s.pred_lost;      // read before thread 0 updates it below
           const uint32_t e_base = s.n_ev + pl;  // chunk-relative index of record 0's own event
+          e_base_of_run = e_base;
           if (EMIT) {
 #pragma unroll
             for (int i = 0; i < CS_RPT; ++i) {
@@ -382,20 +391,25 @@ __device__ __forceinline__ void cs_chunk(const Params& P, const CsOut& O, CsSmem
               }
             }
           }
-          __syncthreads();  // everyone has read pred_lost / n_ev
+        }
+        __syncthreads();  // everyone has read pred_lost / n_ev / wmin
+        if (K > 0) {
           if (threadIdx.x == 0) {
             const uint32_t p = ew + 4 * (K - 1);
             s.pred_ts = buf[p + 3];
             s.pred_off = chunk_abs + tile_rel + 8ull * p;
             s.pred_lost = 0;
-            s.n_ev = e_base + K;
+            s.n_ev = e_base_of_run + K;
             s.cnt[CSC_SWITCH] += K;
             s.cnt[CSC_RECORDS] += K;
           }
           ew += 4 * K;
         }
         if (K == Kall) break;  // ran to the end of the tile (block-uniform)
-        // ---- the record at ew is something else: thread 0 follows it ----
+        if (K == Kscan) continue;  // ... or to the end of what was looked at: the run goes on
+        mixed = true;
+        // ---- the record at ew is something else: thread 0 follows it (in the same breath as the
+        // run's bookkeeping above: no barrier in between) ----
         if (threadIdx.x == 0) {
           const uint64_t abs_off = chunk_abs + tile_rel + 8ull * ew;
           const uint64_t room = limit_abs - abs_off;
@@ -410,8 +424,7 @@ __device__ __forceinline__ void cs_chunk(const Params& P, const CsOut& O, CsSmem
           s.seg_k = sz;
         }
         __syncthreads();
-        const uint32_t sz = s.seg_k;
-        __syncthreads();  // seg_k may be rewritten by the next run
+        const uint32_t sz = s.seg_k;  // (written again only behind the next run's two barriers)
         if (sz == 0) {
           bad = WHY_CS_RECORD;
           break;
