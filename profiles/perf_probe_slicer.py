@@ -43,7 +43,29 @@ def main():
           f"{int(stats[1])} write-error windows, {int(stats[4])} dropped")
     print(f"  device {t:8.3f} ms = {n_ev/1e3/t:8.1f} M events/s, {alg/1e6/t:7.1f} GB/s algorithmic = {100*alg/1e6/t/PEAK:4.1f}% of {PEAK}"
           f"   (call incl. host synchronisations and the stack table: {w:.2f} ms)")
+    # the general form (phases, any level): a serial walk on the device
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+    from test_slicer_oracle import random_phase_events
     from oracle import pyoracle as po
+    r = np.random.default_rng(5)
+    gev = random_phase_events(r, 16, 400_000, 300, p_phase=0.35, p_we=0.0005, p_create=0.01, p_bad=0.0)
+    gev = gev[np.lexsort((gev["comp_unit_id"], gev["tstamp"]))]
+    k = len(gev)
+    while po.slicer_run("port_general", gev[:k], 16)["rc"] == -95:  # (cut in front of the reference's uninitialised-tag reads)
+        k = k * 9 // 10
+    gev = gev[:k]
+    gunits = [gev[gev["comp_unit_id"] == u] for u in range(16)]
+    gms = []
+    for it in range(3):
+        got = sl.run(gunits, general=True)
+        gms.append(sl.last_ms)
+    t0 = time.time()
+    exp = po.slicer_run("port_general", gev, 16)
+    dt = time.time() - t0
+    same = all(np.array_equal(a, b) for a, b in zip(got["slices"], exp["slices"])) and got["stats"] == exp["stats"]
+    print(f"  general form: 16 units, {len(gev)/1e3:.0f} k events with phases at levels 1..3 -> {int(sum(len(x) for x in got['slices']))/1e3:.0f} k slices, "
+          f"{len(got['stacks'])} stacks: device {min(gms):.1f} ms = {len(gev)/1e3/min(gms):.2f} M events/s ({1e3*min(gms)/len(gev):.2f} us per event); "
+          f"cpu restatement {dt*1e3:.1f} ms; equal: {same}")
     if po.slices_available("reference"):
         n_ref = min(ncpu, 16)
         sub = np.concatenate(units[:n_ref])
