@@ -41,6 +41,12 @@ constexpr int CS_OV_BYTES = 64;      // a 32-byte SWITCH whose header is in the 
 constexpr int CS_STAGE_WORDS = (CS_TILE_BYTES + CS_OV_BYTES) / 8;
 constexpr int CS_HALO_BYTES = 1024;  // <= NT * 8: one halo word per thread
 constexpr int CS_RPT = (CS_TILE_BYTES / 32 + NT - 1) / NT;  // SWITCH records per thread and tile
+// A stretch of a tile that is dense with other records is cut into elements -- runs of 32-byte
+// SWITCH records and single other records -- by one warp, and the elements are then handled side
+// by side (cs_mixed_stretch).
+constexpr int CS_MAXE = 96;                 // elements per stretch
+constexpr uint32_t CS_MIXED_AFTER = 2;      // other records in a tile before the rest of it goes that way
+constexpr uint16_t CS_E_OTHER = 0xFFFF;     // CsSmem::e_len of an element that is one other record
 static_assert(CS_HALO_BYTES <= NT * 8, "scout takes one halo word per thread");
 
 // per-stream counters (u64 slots of Params::counters)
@@ -71,6 +77,13 @@ struct CsSmem {
   uint32_t n_ev, n_ops;         // events / ops of this chunk so far
   uint32_t seg_k, ew, bad, wl;
   uint32_t wmin[NWARP];         // per warp: first record of the run that is no 32-byte SWITCH
+  // cs_mixed_stretch: the elements (word position in the tile, records of a run or CS_E_OTHER),
+  // what each leaves behind (E_*), its events / ops (counts, then exclusive prefix sums)
+  uint16_t e_pos[CS_MAXE], e_len[CS_MAXE];
+  uint8_t e_fl[CS_MAXE];
+  uint32_t e_ev[CS_MAXE + 1], e_op[CS_MAXE + 1];
+  uint64_t e_ts[CS_MAXE];
+  uint32_t e_n, e_end;
   uint32_t cnt[16];
 };
 
@@ -179,6 +192,265 @@ __device__ __forceinline__ uint32_t cs_odd_record(CsSmem& s, const CsOut& O, con
   s.pred_off = abs_off;
   s.pred_lost = type == REC_LOST;
   return size;
+}
+
+enum : uint8_t { E_HANDLED = 1, E_LOST = 2, E_EVENT = 4, E_OP = 8 };
+
+// The stretch of a tile from word `ew` on, as elements handled side by side.  What the walk of
+// consume() + the handlers does record after record (cs_odd_record, the SWITCH runs of cs_chunk)
+// depends, for one record, only on the handled record before it (was it a LOST, its time) and on
+// how many events / ops came before: warp 0 finds the elements (the one serial part: a record's
+// size says where the next one starts -- a header read and a vote per element), every element
+// looks back for its predecessor, a scan gives the output positions, and then all other records
+// and all runs are written at once.  Stops in front of anything it does not take (a record that
+// trips a fence or is not fully staged, the CS_MAXE-th element): the caller goes on from the
+// word returned, record by record if need be.  Block-uniform; returns the new chain position.
+template <bool EMIT>
+__device__ __forceinline__ uint32_t cs_mixed_stretch(CsSmem& s, const CsOut& O, const uint64_t* buf, uint32_t wt, uint32_t ew,
+                                                     uint32_t staged, uint64_t tile_abs, uint64_t limit_abs, uint32_t cu,
+                                                     uint64_t ev0, uint64_t op0) {
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // ---- 1. the elements ----
+  if (warp == 0) {
+    uint32_t w = ew, n = 0;
+    bool other_next = true;  // (the caller found that the record at ew is no 32-byte SWITCH)
+    while (w < wt && n < CS_MAXE) {
+      if (!other_next) {
+        // a run of SWITCH records from w on: 32 at a step
+        uint32_t run = 0;
+        bool tile_end = false;
+        for (;;) {
+          const uint32_t Kall = (wt - (w + 4 * run) + 3) / 4;
+          const uint32_t p = w + 4 * run + 4 * lane;
+          const bool ok = lane < Kall && cs_is_switch32(buf[p]) && tile_abs + 8ull * p + 32 <= limit_abs;
+          const uint32_t nok = ~__ballot_sync(0xffffffffu, ok);
+          const uint32_t k = nok ? static_cast<uint32_t>(__ffs(nok) - 1) : 32u;
+          run += k;
+          tile_end = k == Kall;
+          if (k < 32 || tile_end || run >= 0xFF00u) break;
+        }
+        if (run) {
+          if (lane == 0) {
+            s.e_pos[n] = static_cast<uint16_t>(w);
+            s.e_len[n] = static_cast<uint16_t>(run);
+          }
+          ++n;
+          w += 4 * run;
+          if (tile_end || run >= 0xFF00u) continue;  // (the loop condition ends the walk, or the run goes on)
+          if (n == CS_MAXE) break;
+        }
+        // the record at w is no 32-byte SWITCH (or runs past the end of the image)
+      }
+      other_next = false;
+      // another record at w: does the walk take it?  (the fences of cs_odd_record)
+      const uint64_t h = buf[w];
+      const uint32_t type = static_cast<uint32_t>(h), size = static_cast<uint32_t>(h >> 48);
+      const uint64_t room = limit_abs - (tile_abs + 8ull * w);
+      if (size < 8 || (size & 7) || size > room || size < cs_min_size(type) || w + size / 8 > staged) break;
+      if (lane == 0) {
+        s.e_pos[n] = static_cast<uint16_t>(w);
+        s.e_len[n] = CS_E_OTHER;
+      }
+      ++n;
+      w += size / 8;
+    }
+    if (lane == 0) {
+      s.e_n = n;
+      s.e_end = w;
+    }
+  }
+  __syncthreads();
+  const uint32_t n = s.e_n;
+  if (n == 0) return ew;
+  // ---- 2. what every element leaves behind ----
+  const uint32_t k = threadIdx.x;
+  uint32_t pos = 0, len = 0, type = 0, size = 0, misc = 0, fl = 0;
+  uint64_t ts = 0;
+  if (k < n) {
+    pos = s.e_pos[k];
+    len = s.e_len[k];
+    if (len != CS_E_OTHER) {
+      fl = E_HANDLED;
+      ts = buf[pos + 4 * (len - 1) + 3];  // the run's last record
+    } else {
+      const uint64_t h = buf[pos];
+      type = static_cast<uint32_t>(h);
+      misc = static_cast<uint32_t>(h >> 32) & 0xFFFFu;
+      size = static_cast<uint32_t>(h >> 48);
+      if (cs_handled(type)) {
+        ts = cs_time(buf + pos, type, size);
+        fl = E_HANDLED | (type == REC_LOST ? E_LOST : 0) | (type != REC_COMM ? E_EVENT : 0) |
+             (type != REC_SWITCH_CPU_WIDE ? E_OP : 0);
+      }
+    }
+    s.e_fl[k] = static_cast<uint8_t>(fl);
+    s.e_ts[k] = ts;
+  }
+  __syncthreads();
+  // ---- 3. the handled record before it, events and ops it writes ----
+  uint32_t pl = 0;      // in_write_errors_ when the element is reached
+  uint64_t pts = 0;     // last_tstamp_
+  if (k < n) {
+    int j = static_cast<int>(k) - 1;
+    while (j >= 0 && !(s.e_fl[j] & E_HANDLED)) --j;
+    if (j >= 0) {
+      pl = (s.e_fl[j] & E_LOST) ? 1u : 0u;
+      pts = s.e_ts[j];
+    } else {
+      pl = s.pred_lost;
+      pts = s.pred_ts;
+    }
+    uint32_t cev = 0, cop = 0;
+    if (fl & E_HANDLED) {
+      cev = pl + (len != CS_E_OTHER ? len : ((fl & E_EVENT) ? 1u : 0u));
+      cop = (fl & E_OP) ? 1u : 0u;
+    }
+    s.e_ev[k] = cev;
+    s.e_op[k] = cop;
+  }
+  __syncthreads();
+  if (warp == 0) {  // exclusive prefix sums over the (at most 96) elements, three per lane
+    uint32_t a[3], b[3], sa = 0, sb = 0;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const uint32_t e = 3 * lane + i;
+      a[i] = e < n ? s.e_ev[e] : 0;
+      b[i] = e < n ? s.e_op[e] : 0;
+      sa += a[i];
+      sb += b[i];
+    }
+    uint32_t xa = sa, xb = sb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t ya = __shfl_up_sync(0xffffffffu, xa, o), yb = __shfl_up_sync(0xffffffffu, xb, o);
+      if (lane >= static_cast<uint32_t>(o)) {
+        xa += ya;
+        xb += yb;
+      }
+    }
+    uint32_t ra = xa - sa, rb = xb - sb;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const uint32_t e = 3 * lane + i;
+      if (e < n) {
+        s.e_ev[e] = ra;
+        s.e_op[e] = rb;
+      }
+      ra += a[i];
+      rb += b[i];
+    }
+    if (lane == 31) {
+      s.e_ev[CS_MAXE] = xa;  // totals
+      s.e_op[CS_MAXE] = xb;
+    }
+  }
+  __syncthreads();
+  const uint32_t nev0 = s.n_ev, nop0 = s.n_ops;
+  // ---- 4. the other records: counters, events, ops (one thread each) ----
+  if (k < n && len == CS_E_OTHER) {
+    const uint64_t* r = buf + pos;
+    atomicAdd(&s.cnt[CSC_RECORDS], 1u);
+    if (type == REC_THROTTLE) atomicAdd(&s.cnt[CSC_THROTTLE], 1u);
+    if (type == REC_UNTHROTTLE) atomicAdd(&s.cnt[CSC_UNTHROTTLE], 1u);
+    if (fl & E_HANDLED) {
+      const uint32_t e_at = nev0 + s.e_ev[k];
+      if (pl && EMIT) cs_store_event(O, ev0 + e_at, ts, 8, CS_INVALID_LEVEL, cu, CS_KNA, 0);  // pendingRecordLost_ :424-435
+      const uint64_t last = pl ? ts : pts;  // last_tstamp_ when the handler body runs
+      uint32_t etype = 0, tag = CS_KNA, pid = 0, level = O.level;
+      uint64_t ets = ts;
+      hbtgpu_cs_op op{};
+      op.type = type;
+      op.misc = misc;
+      op.tstamp = ts;
+      if (type == REC_LOST) {  // :219-253
+        etype = 7;
+        ets = last + 1;
+        level = CS_INVALID_LEVEL;
+        atomicAdd(&s.lost_sum, static_cast<unsigned long long>(r[2]));
+        op.pid = static_cast<int32_t>(r[3]);
+        op.tid = static_cast<int32_t>(r[3] >> 32);
+      } else if (type == REC_COMM) {  // :255-292
+        atomicAdd(&s.cnt[CSC_COMM], 1u);
+        op.pid = static_cast<int32_t>(r[1]);
+        op.tid = static_cast<int32_t>(r[1] >> 32);
+        op.name_len = size - 32;
+        if (EMIT) {
+          const uint32_t nw = min(op.name_len / 8, 2u);
+          for (uint32_t i = 0; i < nw; ++i) reinterpret_cast<uint64_t*>(op.name)[i] = r[2 + i];
+        }
+      } else if (type == REC_EXIT || type == REC_FORK) {  // :294-372
+        etype = type == REC_EXIT ? 3 : 2;
+        atomicAdd(&s.cnt[type == REC_EXIT ? CSC_EXIT : CSC_FORK], 1u);
+        op.pid = static_cast<int32_t>(r[1]);
+        op.ppid = static_cast<int32_t>(r[1] >> 32);
+        op.tid = static_cast<int32_t>(r[2]);
+        op.ptid = static_cast<int32_t>(r[2] >> 32);
+        tag = static_cast<uint32_t>(op.tid);
+        pid = static_cast<uint32_t>(op.pid);
+      } else {  // SWITCH_CPU_WIDE of an unusual size :374-414
+        atomicAdd(&s.cnt[CSC_SWITCH], 1u);
+        if (misc & MISC_SWITCH_OUT) {
+          etype = (misc & MISC_SWITCH_OUT_PREEMPT) ? 5 : 6;
+        } else {
+          etype = 4;
+          pid = static_cast<uint32_t>(r[2]);
+          tag = static_cast<uint32_t>(r[2] >> 32);
+        }
+      }
+      if (EMIT) {
+        if (fl & E_OP) {
+          op.event_index = e_at + pl + ev0 - O.ev_base[cu];
+          O.ops[op0 + nop0 + s.e_op[k]] = op;
+        }
+        if (etype) cs_store_event(O, ev0 + e_at + pl, ets, etype, level, cu, tag, pid);
+      }
+    }
+  }
+  // ---- 5. the runs: a warp per run, 32 records a step ----
+  for (uint32_t e = warp; e < n; e += NWARP) {
+    const uint32_t rl = s.e_len[e];
+    if (rl == CS_E_OTHER) continue;
+    const uint32_t rp = s.e_pos[e];
+    if (lane == 0) {
+      atomicAdd(&s.cnt[CSC_SWITCH], rl);
+      atomicAdd(&s.cnt[CSC_RECORDS], rl);
+    }
+    if (EMIT) {
+      // (its predecessor: as in step 3)
+      int j = static_cast<int>(e) - 1;
+      while (j >= 0 && !(s.e_fl[j] & E_HANDLED)) --j;
+      const uint32_t rpl = j >= 0 ? ((s.e_fl[j] & E_LOST) ? 1u : 0u) : s.pred_lost;
+      const uint32_t e_at = nev0 + s.e_ev[e];
+      for (uint32_t q = lane; q < rl; q += 32) {
+        const uint32_t p = rp + 4 * q;
+        const uint64_t h = buf[p];
+        const uint32_t m2 = static_cast<uint32_t>(h >> 32) & 0xFFFFu;
+        const uint64_t id = buf[p + 2], t2 = buf[p + 3];
+        const bool out = (m2 & MISC_SWITCH_OUT) != 0;
+        const uint32_t et = out ? ((m2 & MISC_SWITCH_OUT_PREEMPT) ? 5u : 6u) : 4u;
+        if (q == 0 && rpl) cs_store_event(O, ev0 + e_at, t2, 8, CS_INVALID_LEVEL, cu, CS_KNA, 0);
+        cs_store_event(O, ev0 + e_at + rpl + q, t2, et, O.level, cu, out ? CS_KNA : static_cast<uint32_t>(id >> 32),
+                       out ? 0u : static_cast<uint32_t>(id));
+      }
+    }
+  }
+  __syncthreads();  // everybody has read the state the stretch started from
+  // ---- 6. the state behind the stretch ----
+  if (threadIdx.x == 0) {
+    int j = static_cast<int>(n) - 1;
+    while (j >= 0 && !(s.e_fl[j] & E_HANDLED)) --j;
+    if (j >= 0) {
+      const uint32_t jl = s.e_len[j], jp = s.e_pos[j];
+      s.pred_ts = s.e_ts[j];
+      s.pred_lost = (s.e_fl[j] & E_LOST) ? 1u : 0u;
+      s.pred_off = tile_abs + 8ull * (jl == CS_E_OTHER ? jp : jp + 4 * (jl - 1));
+    }
+    s.n_ev = nev0 + s.e_ev[CS_MAXE];
+    s.n_ops = nop0 + s.e_op[CS_MAXE];
+  }
+  const uint32_t end = s.e_end;
+  __syncthreads();
+  return end;
 }
 
 // state of the generator after the handled record at arena offset `off`
@@ -341,6 +613,7 @@ __device__ __forceinline__ void cs_chunk(const Params& P, const CsOut& O, CsSmem
     if (next_rel < tile_rel + 8 * wt) {
       uint32_t ew = (next_rel - tile_rel) / 8;  // chain position, tile-relative words
       bool mixed = false;  // the tile has shown another record: look one record per thread ahead only
+      uint32_t n_other = 0;  // other records met in this tile, one by one
       for (;;) {
         // ---- a run of 32-byte SWITCH records from ew on ----
         const uint32_t Kall = (wt - ew + 3) / 4;
@@ -408,6 +681,18 @@ __device__ __forceinline__ void cs_chunk(const Params& P, const CsOut& O, CsSmem
         if (K == Kall) break;  // ran to the end of the tile (block-uniform)
         if (K == Kscan) continue;  // ... or to the end of what was looked at: the run goes on
         mixed = true;
+        if (n_other >= CS_MIXED_AFTER) {
+          // a tile dense with other records: the rest of it as elements handled side by side
+          const uint32_t staged = min(avail_rel - tile_rel, static_cast<uint32_t>(CS_TILE_BYTES + CS_OV_BYTES)) / 8;
+          const uint32_t nw = cs_mixed_stretch<EMIT>(s, O, buf, wt, ew, staged, chunk_abs + tile_rel, limit_abs, cu, ev0, op0);
+          if (nw != ew) {
+            ew = nw;
+            if (ew >= wt) break;
+            continue;
+          }
+          // (it took nothing: the record at ew trips a fence or is not staged -- thread 0 looks at it)
+        }
+        ++n_other;
         // ---- the record at ew is something else: thread 0 follows it (in the same breath as the
         // run's bookkeeping above: no barrier in between) ----
         if (threadIdx.x == 0) {
