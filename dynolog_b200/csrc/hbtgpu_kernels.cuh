@@ -1708,6 +1708,9 @@ __device__ __forceinline__ void load_carry(Smem& s, const Params& P, uint32_t st
   }
 }
 
+#ifndef HBT_ODD_FIRST
+#define HBT_ODD_FIRST 2  // other records of a tile followed one by one before the rest of it is indexed
+#endif
 #ifndef HBT_MIXED_MIN
 #define HBT_MIXED_MIN 2
 #endif
@@ -1925,7 +1928,7 @@ __global__ void __launch_bounds__(NT, (PRE == 2 && MODE == MODE_AGG) ? 4 : HBT_M
             }
             __syncthreads();  // the segment's carry is published
           }
-          if (MODE == MODE_AGG) {
+          if (MODE == MODE_AGG && (odd >= HBT_ODD_FIRST || mixed_prev)) {
             // the tile holds other records too: index the rest of it once (index_tile), then
             // one pass over the listed samples, however many other records lie in between
             index_tile<PRE, NEV>(s, P, buf, wt, ew, cur, dense_prev);
