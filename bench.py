@@ -100,18 +100,30 @@ class ClockSampler:
         except Exception:
             self._nvml = None
 
-    def _poll(self):
+    def _sample(self):
         nv = self._nvml
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+        r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+        for bit, name in self.REASONS.items():
+            if r & bit:
+                self.reasons.add(name)
+
+    def _poll(self):
         while not self._stop.is_set():
             try:
-                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
-                r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
-                for bit, name in self.REASONS.items():
-                    if r & bit:
-                        self.reasons.add(name)
+                self._sample()
             except Exception:
                 break
             time.sleep(0.001)
+
+    def sample_now(self):
+        """One sample from the calling thread (the poll thread gets few turns while the main
+        thread launches): called with the timed steps queued and still running."""
+        if self._nvml is not None:
+            try:
+                self._sample()
+            except Exception:
+                pass
 
     def stop(self):
         if self._nvml is None:
@@ -722,6 +734,7 @@ def main():
     for _ in range(args.steps):
         gpu_step()
     ev1.record(ext)
+    sampler.sample_now()
     ctx.sync()
     barrier()
     clocks = sampler.stop()
