@@ -2325,8 +2325,8 @@ __global__ void __launch_bounds__(256) k_prologue(const Params P, hbtgpu_carry* 
 }
 
 // ------------------------------------------------------------------------------------
-// top-K of the sampled-IP table by (count descending, ip ascending): compact the table, then
-// K rounds of arg-max (a few MB per round; K is ~100).
+// top-K of the sampled-IP table by (count descending, ip ascending): compact the table; the host
+// side sorts the pairs (hbtgpu_get_top_ips).
 __global__ void k_attr_compact(const uint64_t* keys, const unsigned long long* cnt, uint32_t mask,
                                uint64_t* out_key, unsigned long long* out_cnt, unsigned int* n_out) {
   const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
@@ -2354,63 +2354,6 @@ __global__ void k_attr_merge(const uint64_t* keys, const unsigned long long* cnt
 }
 __global__ void k_attr_merge_special(const unsigned long long* run, unsigned long long* tot) {
   if (threadIdx.x < 4) tot[threadIdx.x] += __ldcv(run + threadIdx.x);
-}
-
-struct TopBest {
-  unsigned long long cnt;
-  uint64_t key;
-  uint32_t idx;
-};
-__device__ __forceinline__ bool top_better(unsigned long long c, uint64_t k, unsigned long long bc, uint64_t bk) {
-  return c > bc || (c == bc && k < bk);
-}
-constexpr int TOPK_BLOCKS = 296, TOPK_THREADS = 256;
-
-// stage 1: every block finds its best remaining entry (count 0 = already taken / none)
-__global__ void __launch_bounds__(TOPK_THREADS) k_topk_partial(const uint64_t* key, const unsigned long long* cnt,
-                                                               uint32_t m, TopBest* partial) {
-  __shared__ TopBest sh[TOPK_THREADS];
-  TopBest b{0, ~0ull, 0xFFFFFFFFu};
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
-    const unsigned long long c = cnt[i];
-    const uint64_t k = key[i];
-    if (c && top_better(c, k, b.cnt, b.key)) b = TopBest{c, k, i};
-  }
-  sh[threadIdx.x] = b;
-  __syncthreads();
-  for (int d = TOPK_THREADS / 2; d > 0; d >>= 1) {
-    if (threadIdx.x < d) {
-      const TopBest o = sh[threadIdx.x + d];
-      if (o.cnt && top_better(o.cnt, o.key, sh[threadIdx.x].cnt, sh[threadIdx.x].key)) sh[threadIdx.x] = o;
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
-}
-// stage 2: one block picks the winner, records it as result `r`, and takes it out of the pool
-__global__ void __launch_bounds__(TOPK_THREADS) k_topk_pick(const TopBest* partial, uint32_t n_partial,
-                                                            unsigned long long* cnt, uint32_t r,
-                                                            uint64_t* out_key, unsigned long long* out_cnt) {
-  __shared__ TopBest sh[TOPK_THREADS];
-  TopBest b{0, ~0ull, 0xFFFFFFFFu};
-  for (uint32_t i = threadIdx.x; i < n_partial; i += blockDim.x) {
-    const TopBest o = partial[i];
-    if (o.cnt && top_better(o.cnt, o.key, b.cnt, b.key)) b = o;
-  }
-  sh[threadIdx.x] = b;
-  __syncthreads();
-  for (int d = TOPK_THREADS / 2; d > 0; d >>= 1) {
-    if (threadIdx.x < d) {
-      const TopBest o = sh[threadIdx.x + d];
-      if (o.cnt && top_better(o.cnt, o.key, sh[threadIdx.x].cnt, sh[threadIdx.x].key)) sh[threadIdx.x] = o;
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) {
-    out_key[r] = sh[0].key;
-    out_cnt[r] = sh[0].cnt;
-    if (sh[0].cnt) cnt[sh[0].idx] = 0;
-  }
 }
 
 // ------------------------------------------------------------------------------------
