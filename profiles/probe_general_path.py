@@ -12,5 +12,5 @@ if what == "cfg4":
 elif what == "general":
     perf_probe.probe("cfg3 force_general", 3, 64, 8, 70000, max_bytes_per_cpu=16 << 20, flags=hbtgpu.F_FORCE_GENERAL)
 else:
-    perf_probe.probe("cfg3-like, THROTTLE pair every 5-10", 3, 64, 8, 70000, max_bytes_per_cpu=16 << 20,
-                     throttle=(5, 10), lost=(200, 2000))
+    perf_probe.probe("cfg3-like, THROTTLE pair every 20-40", 3, 64, 8, 70000, max_bytes_per_cpu=16 << 20,
+                     throttle=(20, 40), lost=(200, 2000))
